@@ -1,0 +1,86 @@
+// Shared helpers for the libctdet_b200 kernels (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/ctdet_b200.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "libctdet_b200 is written for sm_100a (B200) only"
+#endif
+
+namespace ctdet {
+
+constexpr int kNumSMs = 148;          // B200: 2 dies x 74 SMs
+
+void set_last_cuda_error(cudaError_t e);
+
+// Checks the launch that was just enqueued; maps to the C ABI code.
+inline int check_launch() {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
+  return CTDET_OK;
+}
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ int warp_sum(int v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// Monotone map float -> uint32 (larger float => larger uint), and back.
+__device__ __forceinline__ uint32_t float_to_ordered(float f) {
+  uint32_t u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float ordered_to_float(uint32_t o) {
+  uint32_t u = (o & 0x80000000u) ? (o & 0x7fffffffu) : ~o;
+  return __uint_as_float(u);
+}
+
+// Division of a uint32 < 2^31 by a runtime constant: one multiply-high and a shift.
+struct FastDiv {
+  uint32_t mul, shr, d;
+  FastDiv() : mul(0), shr(0), d(1) {}
+  explicit FastDiv(uint32_t div) : mul(0), shr(0), d(div) {
+    if (div > 1) {
+      uint32_t lg = 0;
+      while ((1ull << lg) < div) ++lg;                 // ceil(log2 d)
+      const uint32_t p = 31 + lg;
+      mul = (uint32_t)(((1ull << p) + div - 1) / div);
+      shr = p - 32;
+    }
+  }
+  __host__ __device__ __forceinline__ uint32_t div(uint32_t n) const {
+#ifdef __CUDA_ARCH__
+    return d == 1 ? n : (__umulhi(n, mul) >> shr);
+#else
+    return n / d;
+#endif
+  }
+};
+
+// streaming (read-once) 128-bit load: bypass L1 allocation
+__device__ __forceinline__ float4 ldg_stream4(const float* p) {
+  float4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ void stg_stream4(float* p, float4 v) {
+  asm volatile("st.global.cs.v4.f32 [%0], {%1,%2,%3,%4};"
+               :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+}  // namespace ctdet

@@ -1,0 +1,157 @@
+// Small operators of the reference surface that sit either side of the hot kernels, plus the
+// library's version / error plumbing.
+#include "common.cuh"
+
+namespace ctdet {
+
+static thread_local char g_last_cuda_error[256] = "";
+
+void set_last_cuda_error(cudaError_t e) {
+  const char* s = cudaGetErrorString(e);
+  int i = 0;
+  for (; s && s[i] && i < 255; ++i) g_last_cuda_error[i] = s[i];
+  g_last_cuda_error[i] = 0;
+}
+
+// heat*keep of _nms (centernet.py:399-405), dense output.  One thread per cell; the 3x3
+// neighbourhood comes through L1/L2 (this is the API-compatible standalone op, not the hot path:
+// ctdet_decode fuses the peak test and never materialises this tensor).
+__global__ void nms_kernel(const float* __restrict__ heat, int H, int W, size_t total,
+                           float* __restrict__ out) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const int x = (int)(i % W);
+  const int y = (int)((i / W) % H);
+  const float v = heat[i];
+  float m = v;
+#pragma unroll
+  for (int dy = -1; dy <= 1; ++dy) {
+    const int yy = y + dy;
+    if (yy < 0 || yy >= H) continue;
+#pragma unroll
+    for (int dx = -1; dx <= 1; ++dx) {
+      const int xx = x + dx;
+      if (xx < 0 || xx >= W) continue;
+      m = fmaxf(m, __ldg(heat + i + (ptrdiff_t)dy * W + dx));
+    }
+  }
+  out[i] = (m == v) ? v : v * 0.f;      // heat * keep.float()
+}
+
+// out[b,k,c] = feat[b,c,ind[b,k]]  (_transpose_and_gather_feat, centernet.py:383-397)
+__global__ void gather_feat_kernel(const float* __restrict__ feat, const int64_t* __restrict__ ind,
+                                   int Ch, int HW, int K, size_t total, float* __restrict__ out) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const int c = (int)(i % Ch);
+  const size_t bk = i / Ch;
+  const size_t b = bk / K;
+  const int64_t sp = ind[bk];
+  out[i] = (sp >= 0 && sp < HW) ? feat[(b * Ch + c) * (size_t)HW + sp] : 0.f;
+}
+
+// inference_single_image (centernet.py:251-261) + detector_postprocess
+// (modeling/postprocessing.py:10-74), one warp-sized CTA group per image; order preserving.
+__global__ void postprocess_kernel(float* __restrict__ boxes, float* __restrict__ scores,
+                                   int32_t* __restrict__ classes, const int32_t* __restrict__ sizes,
+                                   int K, int max_dets, float thresh, int32_t* __restrict__ n_keep) {
+  extern __shared__ float s_box[];                  // [K][4] scaled + clipped, then flags
+  __shared__ int s_pos[CTDET_MAX_K + 1];
+  const int b = blockIdx.x, tid = threadIdx.x;
+  const int in_h = sizes[4 * b], in_w = sizes[4 * b + 1];
+  const int out_h = sizes[4 * b + 2], out_w = sizes[4 * b + 3];
+  const float sx = (float)((double)out_w / (double)in_w);   // postprocessing.py:39-42: python-float
+  const float sy = (float)((double)out_h / (double)in_h);   // quotient, applied to an fp32 tensor
+  const int n = min(max_dets, K);                   // centernet.py:252
+  float* bx = boxes + (size_t)b * K * 4;
+  float* sc = scores + (size_t)b * K;
+  int32_t* cl = classes + (size_t)b * K;
+  for (int k = tid; k < K; k += blockDim.x) {
+    float x1 = bx[4 * k] * sx, y1 = bx[4 * k + 1] * sy;          // Boxes.scale (boxes.py:271)
+    float x2 = bx[4 * k + 2] * sx, y2 = bx[4 * k + 3] * sy;
+    x1 = fminf(fmaxf(x1, 0.f), (float)out_w); x2 = fminf(fmaxf(x2, 0.f), (float)out_w);   // Boxes.clip (:184)
+    y1 = fminf(fmaxf(y1, 0.f), (float)out_h); y2 = fminf(fmaxf(y2, 0.f), (float)out_h);
+    s_box[4 * k] = x1; s_box[4 * k + 1] = y1; s_box[4 * k + 2] = x2; s_box[4 * k + 3] = y2;
+    const bool keep = (k < n) && (sc[k] > thresh) &&              // strict > (centernet.py:258)
+                      ((x2 - x1) > 0.f) && ((y2 - y1) > 0.f);     // Boxes.nonempty (:199)
+    s_pos[k] = keep ? 1 : 0;
+  }
+  __syncthreads();
+  if (tid == 0) {                                   // K <= 1024: a serial scan is negligible
+    int run = 0;
+    for (int k = 0; k < K; ++k) { const int f = s_pos[k]; s_pos[k] = f ? run : -1; run += f; }
+    s_pos[K] = run;
+    n_keep[b] = run;
+  }
+  __syncthreads();
+  // read everything that moves before anything is overwritten
+  for (int base = 0; base < K; base += blockDim.x) {
+    const int k = base + tid;
+    float s = 0.f; int c = 0; int dst = -1;
+    if (k < K) { dst = s_pos[k]; s = sc[k]; c = cl[k]; }
+    __syncthreads();
+    if (dst >= 0) {
+      sc[dst] = s; cl[dst] = c;
+      bx[4 * dst] = s_box[4 * k]; bx[4 * dst + 1] = s_box[4 * k + 1];
+      bx[4 * dst + 2] = s_box[4 * k + 2]; bx[4 * dst + 3] = s_box[4 * k + 3];
+    }
+    __syncthreads();
+  }
+}
+
+}  // namespace ctdet
+
+extern "C" int ctdet_abi_version(void) { return CTDET_ABI_VERSION; }
+
+extern "C" const char* ctdet_error_string(int code) {
+  switch (code) {
+    case CTDET_OK: return "ok";
+    case CTDET_EINVAL: return "invalid shape, size or flag";
+    case CTDET_ENULL: return "required pointer is NULL";
+    case CTDET_EALIGN: return "pointer is not aligned as required";
+    case CTDET_EWORKSPACE: return "workspace too small";
+    case CTDET_ECUDA: return "CUDA error";
+    case CTDET_EUNSUPPORTED: return "unsupported configuration";
+    default: return "unknown error code";
+  }
+}
+
+extern "C" const char* ctdet_last_cuda_error(void) { return ctdet::g_last_cuda_error; }
+
+extern "C" int ctdet_nms(const float* heat, int B, int C, int H, int W, float* out,
+                         ctdet_stream_t stream) {
+  using namespace ctdet;
+  if (B < 0 || C <= 0 || H <= 0 || W <= 0) return CTDET_EINVAL;
+  if (B == 0) return CTDET_OK;
+  if (!heat || !out) return CTDET_ENULL;
+  const size_t total = (size_t)B * C * H * W;
+  const size_t blocks = (total + 255) / 256;
+  if (blocks > 0x7fffffffull) return CTDET_EINVAL;
+  nms_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(heat, H, W, total, out);
+  return check_launch();
+}
+
+extern "C" int ctdet_gather_feat(const float* feat, const int64_t* ind, int B, int Ch, int HW, int K,
+                                 float* out, ctdet_stream_t stream) {
+  using namespace ctdet;
+  if (B < 0 || Ch <= 0 || HW <= 0 || K < 0) return CTDET_EINVAL;
+  const size_t total = (size_t)B * K * Ch;
+  if (total == 0) return CTDET_OK;
+  if (!feat || !ind || !out) return CTDET_ENULL;
+  const size_t blocks = (total + 255) / 256;
+  if (blocks > 0x7fffffffull) return CTDET_EINVAL;
+  gather_feat_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(feat, ind, Ch, HW, K, total, out);
+  return check_launch();
+}
+
+extern "C" int ctdet_postprocess(float* boxes, float* scores, int32_t* classes, const int32_t* sizes,
+                                 int B, int K, int max_dets, float score_thresh, int32_t* n_keep,
+                                 ctdet_stream_t stream) {
+  using namespace ctdet;
+  if (B < 0 || K <= 0 || K > CTDET_MAX_K || max_dets < 0) return CTDET_EINVAL;
+  if (B == 0) return CTDET_OK;
+  if (!boxes || !scores || !classes || !sizes || !n_keep) return CTDET_ENULL;
+  postprocess_kernel<<<B, 128, (size_t)K * 4 * sizeof(float), (cudaStream_t)stream>>>(
+      boxes, scores, classes, sizes, K, max_dets, score_thresh, n_keep);
+  return check_launch();
+}

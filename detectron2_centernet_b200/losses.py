@@ -1,0 +1,161 @@
+"""ctdet losses on the GPU -- the operator surface of detectron2/modeling/meta_arch/centernet.py:
+`FocalLoss` (:323), `_neg_loss` (:333), `RegL1Loss` (:372) and the fused `CenterNet.losses`
+(:191-212), backed by the single-pass forward+backward kernel `ctdet_loss_fwd_bwd`.
+"""
+import ctypes
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+
+_FLAG_PROB = 1
+
+
+def alpha_tensor(alpha, num_classes, device):
+    """alpha handling of _neg_loss (centernet.py:341-349) -> f32[C] on `device`.  Unlike the
+    reference the caller's list is not mutated (`alpha.extend` at :348)."""
+    if isinstance(alpha, torch.Tensor):
+        a = alpha.to(device=device, dtype=torch.float32).reshape(-1)
+        if a.numel() == 1:
+            a = a.expand(num_classes)
+        return a.contiguous()
+    if alpha is None:
+        vals = [1.0] * num_classes
+    elif not isinstance(alpha, (list, tuple)):
+        vals = [float(alpha)] * num_classes
+    else:
+        vals = [float(v) for v in alpha]
+        if len(vals) == 1:
+            vals = vals * num_classes
+        elif len(vals) != num_classes:
+            vals = vals + [1.0] * (num_classes - len(vals))
+    return torch.tensor(vals, dtype=torch.float32).to(device, non_blocking=True)
+
+
+def _call(hm, wh, reg, gt_hm, reg_mask, ind, gt_wh, gt_reg, alpha, num_pos, norm, flags, weights,
+          need_grad):
+    lib = _lib.load()
+    ref = hm if hm is not None else (wh if wh is not None else reg)
+    dev = ref.device
+    if hm is not None:
+        B, C, H, W = hm.shape
+    else:
+        B, _, H, W = ref.shape
+        C = 1
+    M = ind.shape[1] if ind is not None else 1
+    losses = torch.empty(3, dtype=torch.float32, device=dev)
+    d_hm = torch.empty_like(hm) if (need_grad and hm is not None) else None
+    d_wh = torch.empty_like(wh) if (need_grad and wh is not None) else None
+    d_reg = torch.empty_like(reg) if (need_grad and reg is not None) else None
+    nbytes = lib.ctdet_loss_workspace_bytes()
+    ws = _lib.zero_workspace("loss", nbytes, dev)
+    with torch.cuda.device(dev):
+        rc = lib.ctdet_loss_fwd_bwd(
+            _lib.ptr(hm), _lib.ptr(wh), _lib.ptr(reg), _lib.ptr(gt_hm), _lib.ptr(reg_mask),
+            _lib.ptr(ind), _lib.ptr(gt_wh), _lib.ptr(gt_reg), _lib.ptr(alpha), _lib.ptr(num_pos),
+            _lib.ptr(norm), B, C, H, W, M, flags, weights[0], weights[1], weights[2],
+            _lib.ptr(losses), _lib.ptr(d_hm), _lib.ptr(d_wh), _lib.ptr(d_reg),
+            _lib.ptr(ws), ctypes.c_size_t(ws.numel()), _lib.stream_ptr(dev))
+    _lib.check(rc, "ctdet_loss_fwd_bwd")
+    return losses, d_hm, d_wh, d_reg
+
+
+def _scaled(d, g):
+    """d *= g on the device; the kernel exits immediately when g == 1 (no host sync)."""
+    if d is None:
+        return None
+    lib = _lib.load()
+    g = g.to(dtype=torch.float32).contiguous()
+    with torch.cuda.device(d.device):
+        rc = lib.ctdet_scale_grad(_lib.ptr(d), ctypes.c_size_t(d.numel()), _lib.ptr(g),
+                                  _lib.stream_ptr(d.device))
+    _lib.check(rc, "ctdet_scale_grad")
+    return d
+
+
+class _FusedLoss(torch.autograd.Function):
+    """losses[3] = (hm, wh, off) * weights; gradients are produced by the same forward sweep and
+    only rescaled in backward if the upstream gradient differs from 1."""
+
+    @staticmethod
+    def forward(ctx, hm, wh, reg, gt_hm, reg_mask, ind, gt_wh, gt_reg, alpha, num_pos, norm, flags,
+                weights):
+        need = any(t is not None and t.requires_grad for t in (hm, wh, reg))
+        losses, d_hm, d_wh, d_reg = _call(hm, wh, reg, gt_hm, reg_mask, ind, gt_wh, gt_reg, alpha,
+                                          num_pos, norm, flags, weights, need)
+        ctx.grads = (d_hm, d_wh, d_reg)
+        return losses
+
+    @staticmethod
+    def backward(ctx, g):
+        d_hm, d_wh, d_reg = ctx.grads
+        ctx.grads = None
+        g = g.contiguous()
+        return (_scaled(d_hm, g[0:1]), _scaled(d_wh, g[1:2]), _scaled(d_reg, g[2:3]),
+                None, None, None, None, None, None, None, None, None, None)
+
+
+def _prep(t, what):
+    if t is None:
+        return None
+    _lib.require_cuda(what, t)
+    return _lib.f32c(t, what)
+
+
+def ctdet_losses(outputs, targets, alpha=None, weights=(1.0, 0.1, 1.0), norm=None):
+    """Fused CenterNet.losses (centernet.py:191-212).
+
+    outputs: {'hm': logits [B,C,H,W], 'wh': [B,2,H,W], 'reg': [B,2,H,W]} -- the raw head outputs
+    (sigmoid + clamp of :204 happen inside; unlike the reference `outputs['hm']` is NOT modified in
+    place).  targets: dict hm/reg_mask/ind/wh/reg (+ optional num_pos i32[B]) as produced by
+    gen_heatmap_batch.  norm: optional f32[2] device tensor {num_pos, sum(reg_mask)} overriding the
+    local normalisers (used for the cross-rank all-reduce).  Returns the reference's dict."""
+    hm = _prep(outputs["hm"], "ctdet losses")
+    wh = _prep(outputs["wh"], "ctdet losses")
+    reg = _prep(outputs["reg"], "ctdet losses")
+    gt_hm = _prep(targets["hm"], "ctdet losses")
+    if gt_hm.shape != hm.shape:
+        raise RuntimeError("gt hm shape %s != hm shape %s" % (tuple(gt_hm.shape), tuple(hm.shape)))
+    a = alpha_tensor(alpha, hm.shape[1], hm.device)
+    out = _FusedLoss.apply(hm, wh, reg, gt_hm, targets["reg_mask"].contiguous(),
+                           targets["ind"].contiguous(), _prep(targets["wh"], "gt wh"),
+                           _prep(targets["reg"], "gt reg"), a, targets.get("num_pos"), norm, 0,
+                           tuple(float(w) for w in weights))
+    return {"hm_loss": out[0], "wh_loss": out[1], "off_loss": out[2]}
+
+
+def _neg_loss(pred, gt, alpha=None, num_pos=None):
+    """Drop-in for centernet.py:333: pred = clamp(sigmoid(.)) probabilities [B,C,H,W]."""
+    pred = _prep(pred, "_neg_loss")
+    gt = _prep(gt, "_neg_loss")
+    a = alpha_tensor(alpha, pred.shape[1], pred.device)
+    out = _FusedLoss.apply(pred, None, None, gt, None, None, None, None, a, num_pos, None,
+                           _FLAG_PROB, (1.0, 0.0, 0.0))
+    return out[0]
+
+
+class FocalLoss(nn.Module):
+    """nn.Module wrapper for the focal loss, centernet.py:323-331."""
+
+    def __init__(self, alpha):
+        super().__init__()
+        self.neg_loss = _neg_loss
+        self.alpha = alpha
+
+    def forward(self, out, target):
+        return self.neg_loss(out, target, self.alpha)
+
+
+class RegL1Loss(nn.Module):
+    """centernet.py:372-381: output [B,2,H,W], mask u8/bool [B,M], ind i64 [B,M], target [B,M,2]."""
+
+    def forward(self, output, mask, ind, target):
+        output = _prep(output, "RegL1Loss")
+        if output.shape[1] != 2:
+            raise NotImplementedError("RegL1Loss kernel handles the 2-channel wh/reg heads")
+        mask = mask.to(torch.uint8).contiguous()
+        out = _FusedLoss.apply(None, output, None, None, mask, ind.contiguous(),
+                               _prep(target, "RegL1Loss target"), None, None, None, None, 0,
+                               (0.0, 1.0, 0.0))
+        return out[1]

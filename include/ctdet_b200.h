@@ -1,0 +1,141 @@
+/*
+ * ctdet_b200.h -- C ABI of libctdet_b200.so: the CenterNet "ctdet" heatmap hot path as
+ * hand-written sm_100a CUDA kernels (no torch types, no CPU fallback).
+ *
+ * All pointers are DEVICE pointers on the current CUDA device unless stated otherwise; the
+ * caller owns every buffer (outputs and workspaces included), the library never allocates or
+ * frees device memory and keeps no state between calls.  Every entry point enqueues its work on
+ * `stream` (a cudaStream_t passed as void*) and returns without synchronising.
+ * Return value: 0 on success, otherwise a CTDET_E* code (see ctdet_error_string).
+ *
+ * Reference interfaces replaced (paths relative to the ShawnNew/Detectron2-CenterNet root):
+ *   ctdet_target_gen     detectron2/data/detection_utils.py:600  gen_heatmap (+ :654 gaussian_radius,
+ *                        :682 gaussian2D, :690 draw_umich_gaussian) and the torch.cat/.to(device) of
+ *                        detectron2/modeling/meta_arch/centernet.py:197-201
+ *   ctdet_loss_fwd_bwd   centernet.py:191-212 CenterNet.losses = :204 sigmoid_+clamp, :323-369
+ *                        FocalLoss/_neg_loss, :372-381 RegL1Loss (+ :383 _transpose_and_gather_feat)
+ *                        and their autograd backward
+ *   ctdet_decode         centernet.py:426 ctdet_decode = :399 _nms, :408 _topk, :383 gather, boxes
+ *   ctdet_nms / ctdet_gather_feat   centernet.py:399 _nms / :383 _transpose_and_gather_feat
+ *   ctdet_postprocess    centernet.py:236-266 inference_single_image (slice + score threshold) and
+ *                        detectron2/modeling/postprocessing.py:10-74 detector_postprocess (scale, clip, nonempty)
+ *   dcnv2_forward        detectron2/layers/csrc/deformable/deform_conv.h:262 modulated_deform_conv_forward
+ *                        -> deform_conv_cuda.cu:804 modulated_deform_conv_cuda_forward
+ *                        (im2col kernel deform_conv_cuda_kernel.cu:786 + addmm_ :904 + bias :924)
+ */
+#ifndef CTDET_B200_H_
+#define CTDET_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CTDET_ABI_VERSION 1
+#define CTDET_MAX_OBJS 128   /* slot count hard-coded at detection_utils.py:611-616 */
+#define CTDET_MAX_K 1024     /* largest top-K supported by ctdet_decode */
+
+enum {
+  CTDET_OK = 0,
+  CTDET_EINVAL = 1,      /* bad shape / size / flag combination           */
+  CTDET_ENULL = 2,       /* required pointer is NULL                       */
+  CTDET_EALIGN = 3,      /* pointer not aligned as documented              */
+  CTDET_EWORKSPACE = 4,  /* workspace too small                            */
+  CTDET_ECUDA = 5,       /* CUDA launch / runtime error (cudaGetLastError) */
+  CTDET_EUNSUPPORTED = 6 /* valid request this build does not implement    */
+};
+
+typedef void* ctdet_stream_t; /* cudaStream_t */
+
+int ctdet_abi_version(void);
+const char* ctdet_error_string(int code);
+/* last CUDA error string seen by this thread inside the library ("" if none) */
+const char* ctdet_last_cuda_error(void);
+
+/* ---------------------------------------------------------------- target generation ----
+ * boxes   f32 [total,4]  XYXY, input-pixel units (divided by the hard-coded 4 inside)
+ * classes i64 [total]    in [0,C)
+ * offsets i32 [B+1]      image b owns objects offsets[b] .. offsets[b+1]-1 (only the first 128 are used)
+ * outputs: hm f32 [B,C,H,W] (every cell written exactly once, zero fill fused),
+ *          reg_mask u8 [B,128], ind i64 [B,128], wh f32 [B,128,2], reg f32 [B,128,2],
+ *          num_pos i32 [B] = number of cells of image b with hm == 1 (may be NULL).
+ * hm must be 16-byte aligned. */
+int ctdet_target_gen(const float* boxes, const int64_t* classes, const int32_t* offsets,
+                     int B, int C, int H, int W,
+                     float* hm, uint8_t* reg_mask, int64_t* ind, float* wh, float* reg,
+                     int32_t* num_pos, ctdet_stream_t stream);
+
+/* ---------------------------------------------------------------- fused losses ---------
+ * One pass over the heatmap: p = clamp(sigmoid(hm_logits),1e-4,1-1e-4), penalty-reduced focal
+ * loss, RegL1 for wh and reg, and (when d_hm != NULL) the gradients of
+ *   w_hm*hm_loss + w_wh*wh_loss + w_off*off_loss   w.r.t. hm_logits / wh / reg.
+ * Sections are optional: hm == NULL skips the focal term (losses[0] = 0), wh == NULL / reg == NULL
+ * skip that RegL1 head; gradients are written for the sections present when their d_* pointer is
+ * non-NULL (d_* must not alias an input).  With CTDET_LOSS_INPUT_PROB `hm` holds probabilities
+ * (the `pred` argument of FocalLoss.forward, centernet.py:330) and d_hm is d/d(pred).
+ * hm, gt_hm, d_hm: f32 [B,C,H,W];  wh, reg, d_wh, d_reg: f32 [B,2,H,W];
+ * reg_mask u8 [B,M]; ind i64 [B,M]; gt_wh, gt_reg f32 [B,M,2]; alpha f32 [C] (per class,
+ * applied to the positive term only, centernet.py:361).
+ * Normaliser, first match wins:
+ *   norm_override  f32 [2] = {num_pos, sum(reg_mask)} (e.g. all-reduced over ranks), else
+ *   num_pos_img    i32 [B] as written by ctdet_target_gen (summed in-kernel), else
+ *   a counting pre-pass over gt_hm (costs one extra read of gt_hm).
+ * losses f32 [3] = {hm_loss*w_hm, wh_loss*w_wh, off_loss*w_off}.
+ * workspace: ctdet_loss_workspace_bytes() bytes, zero-filled ONCE by the caller before first
+ * use; every call leaves it zero-filled again.  Not re-entrant on two streams with the same
+ * workspace. */
+#define CTDET_LOSS_INPUT_PROB 1
+size_t ctdet_loss_workspace_bytes(void);
+int ctdet_loss_fwd_bwd(const float* hm, const float* wh, const float* reg,
+                       const float* gt_hm, const uint8_t* reg_mask, const int64_t* ind,
+                       const float* gt_wh, const float* gt_reg, const float* alpha,
+                       const int32_t* num_pos_img, const float* norm_override,
+                       int B, int C, int H, int W, int M, int flags,
+                       float w_hm, float w_wh, float w_off,
+                       float* losses, float* d_hm, float* d_wh, float* d_reg,
+                       void* workspace, size_t workspace_bytes, ctdet_stream_t stream);
+
+/* d[i] *= *g for i < n, entirely skipped on the device when *g == 1 (autograd upstream gradient,
+ * no host sync).  g: f32 device scalar. */
+int ctdet_scale_grad(float* d, size_t n, const float* g, ctdet_stream_t stream);
+
+/* ---------------------------------------------------------------- decode ---------------
+ * heat f32 [B,C,H,W]: probabilities in (0,1] (centernet.py:161), or raw logits with
+ * CTDET_DECODE_LOGITS (ranking on logits, score = clamp(sigmoid) of the winners).
+ * wh f32 [B,2,H,W] (or [B,2C,H,W] with CTDET_DECODE_CAT_SPEC_WH); reg f32 [B,2,H,W] or NULL (+0.5).
+ * Outputs: boxes f32 [B,K,4] XYXY * down_ratio, scores f32 [B,K] descending, classes i32 [B,K],
+ * inds i64 [B,K] spatial index y*W+x (may be NULL).
+ * Tie rule: higher score first, then lower flat index c*H*W + y*W + x.  Requires K <= H*W,
+ * K <= CTDET_MAX_K, C*H*W < 2^32. */
+#define CTDET_DECODE_LOGITS 1
+#define CTDET_DECODE_CAT_SPEC_WH 2
+#define CTDET_DECODE_NO_NMS 4 /* rank every cell (the bare _topk of centernet.py:408) */
+size_t ctdet_decode_workspace_bytes(int B, int C, int H, int W, int K);
+int ctdet_decode(const float* heat, const float* wh, const float* reg,
+                 int B, int C, int H, int W, int K, float down_ratio, int flags,
+                 float* boxes, float* scores, int32_t* classes, int64_t* inds,
+                 void* workspace, size_t workspace_bytes, ctdet_stream_t stream);
+
+/* heat*keep of centernet.py:399-405, dense: out f32 [B,C,H,W]. */
+int ctdet_nms(const float* heat, int B, int C, int H, int W, float* out, ctdet_stream_t stream);
+
+/* _transpose_and_gather_feat, centernet.py:383: feat f32 [B,Ch,H*W], ind i64 [B,K] ->
+ * out f32 [B,K,Ch] with out[b,k,c] = feat[b,c,ind[b,k]] (no NHWC copy). */
+int ctdet_gather_feat(const float* feat, const int64_t* ind, int B, int Ch, int HW, int K,
+                      float* out, ctdet_stream_t stream);
+
+/* Batched inference_single_image + detector_postprocess: for image b keep the first
+ * min(max_dets,K) detections with score > score_thresh, scale boxes by
+ * (out_w/in_w, out_h/in_h), clip to the output size, drop empty boxes; survivors are compacted
+ * to the front (order preserved).  sizes i32 [B,4] = {in_h, in_w, out_h, out_w}; n_keep i32 [B].
+ * In place on boxes/scores/classes [B,K,...]. */
+int ctdet_postprocess(float* boxes, float* scores, int32_t* classes, const int32_t* sizes,
+                      int B, int K, int max_dets, float score_thresh, int32_t* n_keep,
+                      ctdet_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CTDET_B200_H_ */

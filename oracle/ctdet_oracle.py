@@ -1,0 +1,263 @@
+"""TEST INFRASTRUCTURE ONLY -- CPU restatement ("port") of the reference's ctdet hot path.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+import this module; the product package (detectron2_centernet_b200) never does and fails
+loudly when its CUDA library is missing.
+
+Parity status: PINNED.  Every function here is checked (tests/test_oracle_golden.py) against
+golden vectors produced by running the reference's own, unmodified functions in the build
+container (oracle/ref_loader.py -> oracle/gen_golden.py -> tests/golden/*.npz), and directly
+against the live reference whenever /root/reference is present.  The reference's own test-suite
+has no golden vectors for this path.
+
+Each function cites the reference file:line it restates (paths relative to the reference
+root).  The restatement is written independently (vectorised numpy, explicit tie rule); it is
+not a copy of the reference code.
+"""
+import math
+
+import numpy as np
+import torch
+
+MAX_OBJS = 128          # hard-coded slot count, detectron2/data/detection_utils.py:611-616
+BOX_DIVISOR = 4.0       # hard-coded "/ 4", detection_utils.py:618 (not down_ratio)
+
+
+# --------------------------------------------------------------------------------------
+# Target generation
+# --------------------------------------------------------------------------------------
+def gaussian_radius(height, width, min_overlap=0.7):
+    """detection_utils.py:654-680.  Three quadratics, fp64, min of the larger roots
+    (the third divides by 2 rather than 2a -- kept, it is what the reference computes)."""
+    height = float(height)
+    width = float(width)
+    s = height + width
+    area = width * height
+    # case 1: a=1, b=s, c=area*(1-o)/(1+o)
+    c1 = area * (1 - min_overlap) / (1 + min_overlap)
+    r1 = (s + math.sqrt(s * s - 4.0 * c1)) / 2
+    # case 2: a=4, b=2s, c=(1-o)*area
+    b2 = 2 * s
+    c2 = (1 - min_overlap) * width * height       # left-to-right, as the reference
+    r2 = (b2 + math.sqrt(b2 * b2 - 16.0 * c2)) / 2
+    # case 3: a=4o, b=-2o*s, c=(o-1)*area
+    a3 = 4 * min_overlap
+    b3 = -2 * min_overlap * s
+    c3 = (min_overlap - 1) * width * height
+    r3 = (b3 + math.sqrt(b3 * b3 - 4 * a3 * c3)) / 2
+    return min(r1, r2, r3)
+
+
+def _splat(plane, cx, cy, radius):
+    """gaussian2D + draw_umich_gaussian, detection_utils.py:682-705: in-place max of a
+    (2r+1)^2 fp64 Gaussian (sigma = (2r+1)/6), clipped to the map, rounded to fp32."""
+    H, W = plane.shape
+    if not (0 <= cx < W and 0 <= cy < H):
+        # the reference's numpy slicing misbehaves (negative-index wrap / shape error) for
+        # centres outside the map; boxes clipped to the image never produce them.  We skip.
+        return
+    x0, x1 = max(cx - radius, 0), min(cx + radius + 1, W)
+    y0, y1 = max(cy - radius, 0), min(cy + radius + 1, H)
+    sigma = (2 * radius + 1) / 6.0
+    dx = np.arange(x0, x1, dtype=np.float64) - cx
+    dy = np.arange(y0, y1, dtype=np.float64) - cy
+    g = np.exp(-(dx[None, :] ** 2 + dy[:, None] ** 2) / (2 * sigma * sigma))
+    g[g < np.finfo(np.float64).eps * 1.0] = 0     # :687, max of the kernel is exp(0) = 1
+    win = plane[y0:y1, x0:x1]
+    np.maximum(win, g.astype(np.float32), out=win)
+
+
+def gen_heatmap(boxes, classes, H, W, C):
+    """detection_utils.py:600-651 for one image.
+    boxes f32 [n,4] XYXY in input pixels, classes int [n].  Returns dict of numpy arrays:
+    hm f32[C,H,W], reg_mask u8[128], ind i64[128], wh f32[128,2], reg f32[128,2]."""
+    boxes = np.asarray(boxes, dtype=np.float32).reshape(-1, 4)
+    classes = np.asarray(classes, dtype=np.int64).reshape(-1)
+    hm = np.zeros((C, H, W), np.float32)
+    wh = np.zeros((MAX_OBJS, 2), np.float32)
+    reg = np.zeros((MAX_OBJS, 2), np.float32)
+    ind = np.zeros((MAX_OBJS,), np.int64)
+    reg_mask = np.zeros((MAX_OBJS,), np.uint8)
+    n = min(len(classes), MAX_OBJS)
+    for k in range(n):
+        b = boxes[k] / np.float32(BOX_DIVISOR)                 # :618 (fp32)
+        bw = np.float32(b[2] - b[0])
+        bh = np.float32(b[3] - b[1])
+        if not (bh > 0 and bw > 0):                            # :621, slot k stays zero
+            continue
+        r = max(0, int(gaussian_radius(math.ceil(bh), math.ceil(bw))))   # :623-624
+        ctx = np.float32(np.float32(b[0] + b[2]) / np.float32(2))       # :625-626 (fp32)
+        cty = np.float32(np.float32(b[1] + b[3]) / np.float32(2))
+        cxi, cyi = int(np.int32(ctx)), int(np.int32(cty))      # :627 trunc toward zero
+        _splat(hm[int(classes[k])], cxi, cyi, r)               # :628
+        wh[k] = (bw, bh)                                       # :629
+        ind[k] = cyi * W + cxi                                 # :630
+        reg[k] = (ctx - np.float32(cxi), cty - np.float32(cyi))  # :631
+        reg_mask[k] = 1                                        # :632
+    return {"hm": hm, "reg_mask": reg_mask, "ind": ind, "wh": wh, "reg": reg}
+
+
+def gen_heatmap_batch(boxes_list, classes_list, H, W, C):
+    """The torch.cat of per-image targets in CenterNet.losses, meta_arch/centernet.py:197-201."""
+    per = [gen_heatmap(b, c, H, W, C) for b, c in zip(boxes_list, classes_list)]
+    return {k: np.stack([p[k] for p in per]) for k in per[0]}
+
+
+def count_positives(gt):
+    """num_pos of _neg_loss (centernet.py:360): number of cells with gt == 1."""
+    return int((gt["hm"] == 1).sum())
+
+
+# --------------------------------------------------------------------------------------
+# Losses (forward and backward), torch fp32 on CPU
+# --------------------------------------------------------------------------------------
+def _alpha_vector(alpha, C):
+    """alpha handling of _neg_loss, centernet.py:341-349."""
+    if alpha is None:
+        return torch.ones(C)
+    if not isinstance(alpha, (list, tuple)):
+        return torch.full((C,), float(alpha))
+    a = list(alpha)
+    if len(a) == 1:
+        a = a * C
+    elif len(a) != C:
+        a = a + [1] * (C - len(a))
+    return torch.tensor(a, dtype=torch.float32)
+
+
+def focal_loss(pred, gt, alpha=None):
+    """_neg_loss, centernet.py:333-369.  pred = clamp(sigmoid(logits)) fp32 [B,C,H,W]."""
+    a = _alpha_vector(alpha, pred.shape[1]).to(pred.dtype)
+    is_pos = (gt == 1).to(pred.dtype)
+    is_neg = (gt < 1).to(pred.dtype)
+    pos_term = torch.log(pred) * (1 - pred) ** 2 * is_pos
+    neg_term = torch.log(1 - pred) * pred ** 2 * (1 - gt) ** 4 * is_neg
+    n_pos = is_pos.sum()
+    pos_sum = (a[:, None, None] * pos_term.sum(0)).sum()      # alpha on positives only (:361)
+    neg_sum = neg_term.sum()
+    if n_pos == 0:
+        return -neg_sum                                       # :365-366
+    return -(pos_sum + neg_sum) / n_pos                       # :368
+
+
+def gather_feat_nchw(feat, ind):
+    """_transpose_and_gather_feat, centernet.py:383-397: feat[B,Ch,H,W], ind[B,K] ->
+    [B,K,Ch] with out[b,k,c] = feat[b,c,ind[b,k]]  (no NHWC copy needed)."""
+    B, Ch = feat.shape[:2]
+    flat = feat.reshape(B, Ch, -1)
+    idx = ind.long().unsqueeze(1).expand(B, Ch, ind.shape[1])
+    return flat.gather(2, idx).permute(0, 2, 1)
+
+
+def reg_l1_loss(output, mask, ind, target):
+    """RegL1Loss.forward, centernet.py:376-381.  The mask is expanded over both channels
+    before being summed, so the normaliser is 2*sum(mask) + 1e-4."""
+    pred = gather_feat_nchw(output, ind)
+    m = mask.unsqueeze(2).expand_as(pred).to(pred.dtype)
+    return (pred * m - target * m).abs().sum() / (m.sum() + 1e-4)
+
+
+def losses(hm_logits, wh, reg, gt, alpha=(1.0,), weights=(1.0, 0.1, 1.0)):
+    """CenterNet.losses, centernet.py:191-212 (sigmoid + clamp(1e-4, 1-1e-4) then the three
+    criteria and the HM/WH/OFF weights).  gt values may be numpy or torch."""
+    g = {k: torch.as_tensor(v) for k, v in gt.items()}
+    p = torch.clamp(torch.sigmoid(hm_logits), min=1e-4, max=1 - 1e-4)
+    return {"hm_loss": focal_loss(p, g["hm"], list(alpha)) * weights[0],
+            "wh_loss": reg_l1_loss(wh, g["reg_mask"], g["ind"], g["wh"]) * weights[1],
+            "off_loss": reg_l1_loss(reg, g["reg_mask"], g["ind"], g["reg"]) * weights[2]}
+
+
+def losses_and_grads(hm_logits, wh, reg, gt, alpha=(1.0,), weights=(1.0, 0.1, 1.0)):
+    """losses() plus d(sum of the three weighted losses)/d(hm_logits, wh, reg) by autograd."""
+    x = hm_logits.detach().clone().requires_grad_(True)
+    w = wh.detach().clone().requires_grad_(True)
+    r = reg.detach().clone().requires_grad_(True)
+    out = losses(x, w, r, gt, alpha, weights)
+    (out["hm_loss"] + out["wh_loss"] + out["off_loss"]).backward()
+    return {k: v.detach() for k, v in out.items()}, (x.grad, w.grad, r.grad)
+
+
+# --------------------------------------------------------------------------------------
+# Decode
+# --------------------------------------------------------------------------------------
+def peak_mask(heat):
+    """_nms, centernet.py:399-405: cell is kept iff it equals the max of its 3x3
+    neighbourhood (-inf padding; plateaus are all kept)."""
+    h = np.asarray(heat, dtype=np.float32)
+    B, C, H, W = h.shape
+    pad = np.full((B, C, H + 2, W + 2), -np.inf, np.float32)
+    pad[:, :, 1:-1, 1:-1] = h
+    m = h.copy()
+    for dy in range(3):
+        for dx in range(3):
+            np.maximum(m, pad[:, :, dy:dy + H, dx:dx + W], out=m)
+    return m == h
+
+
+def decode(heat, wh, reg=None, down_ratio=1, K=100, cat_spec_wh=False, logits=False):
+    """ctdet_decode, centernet.py:426-458, batched over images (the reference is batch=1).
+
+    heat: f32 [B,C,H,W], probabilities in (0,1] as produced at centernet.py:161, or raw head
+    logits when logits=True (sigmoid is monotone, so peaks and ranking are taken on the
+    logits and score = clamp(sigmoid(x), 1e-4, 1-1e-4) is applied to the K winners).
+
+    Selection: the reference takes a per-class top-K (:411) then a top-K of those C*K (:417);
+    that equals one top-K over all C*H*W cells because no class can hold more than K of the
+    global top K.  TIE RULE (torch.topk's is implementation-defined): higher score first, then
+    lower flat index c*H*W + y*W + x.  Non-peak cells have score 0.0 (heat*keep, :405) and can
+    only be selected when fewer than K peaks exist.
+
+    Returns boxes f32[B,K,4], scores f32[B,K], classes i32[B,K], inds i64[B,K] (spatial)."""
+    h = np.asarray(heat, dtype=np.float32)
+    B, C, H, W = h.shape
+    if H * W < K:
+        raise RuntimeError("selected index k out of range")   # torch.topk at :411
+    keep = peak_mask(h)
+    if logits:
+        rank = np.where(keep, h, -np.inf)
+    else:
+        rank = np.where(keep & (h > 0), h, np.float32(0))
+    flat = rank.reshape(B, -1)
+    order = np.stack([np.lexsort((np.arange(flat.shape[1]), -flat[b].astype(np.float64)))[:K]
+                      for b in range(B)])
+    top = np.take_along_axis(flat, order, 1)
+    if logits:
+        with np.errstate(over="ignore"):
+            s = (np.float32(1) / (np.float32(1) + np.exp(-top.astype(np.float32)))).astype(np.float32)
+        scores = np.where(np.isneginf(top), np.float32(0),
+                          np.clip(s, np.float32(1e-4), np.float32(1 - 1e-4))).astype(np.float32)
+    else:
+        scores = top.astype(np.float32)
+    classes = (order // (H * W)).astype(np.int32)              # :418
+    inds = (order % (H * W)).astype(np.int64)
+    ys = (inds // W).astype(np.float32)                        # :414
+    xs = (inds % W).astype(np.float32)                         # :415
+    whf = np.asarray(wh, np.float32).reshape(B, -1, H * W)
+    if reg is not None:
+        rf = np.asarray(reg, np.float32).reshape(B, 2, H * W)
+        xs = xs + np.take_along_axis(rf[:, 0], inds, 1)        # :436-439
+        ys = ys + np.take_along_axis(rf[:, 1], inds, 1)
+    else:
+        xs = xs + np.float32(0.5)                              # :440-441
+        ys = ys + np.float32(0.5)
+    if cat_spec_wh:                                            # :443-446 (wh has 2C channels)
+        bidx = np.arange(B)[:, None]
+        w_ = whf[bidx, 2 * classes, inds]
+        h_ = whf[bidx, 2 * classes + 1, inds]
+    else:
+        w_ = np.take_along_axis(whf[:, 0], inds, 1)
+        h_ = np.take_along_axis(whf[:, 1], inds, 1)
+    two = np.float32(2)
+    dr = np.float32(down_ratio)
+    boxes = np.stack([(xs - w_ / two) * dr, (ys - h_ / two) * dr,
+                      (xs + w_ / two) * dr, (ys + h_ / two) * dr], axis=2).astype(np.float32)
+    return boxes, scores, classes, inds
+
+
+def postprocess_single(boxes, scores, classes, max_dets=100, score_thresh=0.05):
+    """CenterNet.inference_single_image, centernet.py:251-261: slice to max_dets then keep
+    scores strictly greater than the threshold."""
+    n = min(max_dets, len(scores))
+    b, s, c = boxes[:n], scores[:n], classes[:n]
+    k = s > np.float32(score_thresh)
+    return b[k], s[k], c[k]

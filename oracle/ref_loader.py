@@ -1,0 +1,143 @@
+"""TEST INFRASTRUCTURE ONLY -- never imported by the product path.
+
+Loads the *reference's own* ctdet hot-path functions from the read-only tree at
+/root/reference without importing the detectron2 package (which needs fvcore, yacs,
+pycocotools and a built detectron2._C, none of which exist in this image).
+
+The named FunctionDef / ClassDef nodes are AST-extracted from
+
+  detectron2/data/detection_utils.py        gen_heatmap :600, gaussian_radius :654,
+                                            gaussian2D :682, draw_umich_gaussian :690
+  detectron2/modeling/meta_arch/centernet.py  FocalLoss :323, _neg_loss :333, RegL1Loss :372,
+                                            _transpose_and_gather_feat :383, _gather_feat :389,
+                                            _nms :399, _topk :408, ctdet_decode :426
+
+and exec'd unmodified with {torch, nn, F, np} in scope.  `_neg_loss` calls `.cuda()` on its
+alpha tensor (:342-349); on a CPU-only host `Tensor.cuda` is shimmed to identity while the
+reference function runs.
+
+This only works where /root/reference exists (the build container).  It is used by
+oracle/gen_golden.py to produce tests/golden/*.npz and by the CPU tests (when the tree is
+present) to pin oracle/ctdet_oracle.py against the real reference.  Nothing on the GPU box
+may depend on it.
+"""
+import ast
+import contextlib
+import os
+
+import numpy as np
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+REF_ROOT = os.environ.get("CTDET_REFERENCE_ROOT", "/root/reference")
+
+_WANTED = {
+    "detectron2/data/detection_utils.py": [
+        "gen_heatmap", "gaussian_radius", "gaussian2D", "draw_umich_gaussian"],
+    "detectron2/modeling/meta_arch/centernet.py": [
+        "FocalLoss", "_neg_loss", "RegL1Loss", "_transpose_and_gather_feat",
+        "_gather_feat", "_nms", "_topk", "ctdet_decode"],
+}
+
+
+def available():
+    return all(os.path.isfile(os.path.join(REF_ROOT, p)) for p in _WANTED)
+
+
+def _extract(path, names):
+    with open(os.path.join(REF_ROOT, path), "r") as f:
+        src = f.read()
+    tree = ast.parse(src)
+    picked = [n for n in tree.body
+              if isinstance(n, (ast.FunctionDef, ast.ClassDef)) and n.name in names]
+    missing = set(names) - {n.name for n in picked}
+    if missing:
+        raise RuntimeError("reference symbols not found in %s: %s" % (path, sorted(missing)))
+    return ast.Module(body=picked, type_ignores=[])
+
+
+_CACHE = {}
+
+
+def load():
+    """Returns a dict name -> reference object (functions / nn.Module classes)."""
+    if _CACHE:
+        return _CACHE
+    if not available():
+        raise RuntimeError("reference tree not present at %s" % REF_ROOT)
+    ns = {"torch": torch, "nn": nn, "F": F, "np": np, "__name__": "ctdet_reference"}
+    for path, names in _WANTED.items():
+        mod = _extract(path, names)
+        exec(compile(mod, os.path.join(REF_ROOT, path), "exec"), ns)
+    for names in _WANTED.values():
+        for n in names:
+            _CACHE[n] = ns[n]
+    return _CACHE
+
+
+@contextlib.contextmanager
+def cpu_cuda_shim():
+    """`_neg_loss` does `torch.tensor(alpha).cuda()`; make that a no-op on CPU-only hosts."""
+    if torch.cuda.is_available():
+        yield
+        return
+    orig = torch.Tensor.cuda
+    torch.Tensor.cuda = lambda self, *a, **k: self
+    try:
+        yield
+    finally:
+        torch.Tensor.cuda = orig
+
+
+class _Boxes:
+    def __init__(self, t):
+        self.tensor = t
+
+
+class DuckInstances:
+    """What gen_heatmap reads from an Instances: .gt_boxes.tensor [n,4] f32, .gt_classes [n] i64."""
+
+    def __init__(self, boxes, classes):
+        self.gt_boxes = _Boxes(torch.as_tensor(boxes, dtype=torch.float32))
+        self.gt_classes = torch.as_tensor(classes, dtype=torch.int64)
+
+
+class DuckMeta:
+    def __init__(self, num_classes):
+        self.thing_classes = ["c%d" % i for i in range(num_classes)]
+
+
+def ref_gen_heatmap(boxes, classes, H, W, C):
+    """Runs the reference gen_heatmap (detection_utils.py:600) on CPU tensors."""
+    fn = load()["gen_heatmap"]
+    return fn(DuckInstances(boxes, classes), np.array([H, W]), DuckMeta(C))
+
+
+def ref_losses(hm_logits, wh, reg, gt, alpha=(1.0,), weights=(1.0, 0.1, 1.0)):
+    """Reference CenterNet.losses (centernet.py:191-212) on given head outputs; returns
+    (dict of losses, grads wrt hm_logits/wh/reg)."""
+    R = load()
+    hm = hm_logits.clone().requires_grad_(True)
+    w_ = wh.clone().requires_grad_(True)
+    r_ = reg.clone().requires_grad_(True)
+    with cpu_cuda_shim():
+        crit = R["FocalLoss"](list(alpha))
+        regc = R["RegL1Loss"]()
+        # `outputs['hm'].sigmoid_()` is in-place on the head output (a non-leaf); mirror with x*1
+        hm_loss = crit(torch.clamp((hm * 1).sigmoid_(), min=1e-4, max=1 - 1e-4), gt["hm"])
+        wh_loss = regc(w_, gt["reg_mask"], gt["ind"], gt["wh"])
+        off_loss = regc(r_, gt["reg_mask"], gt["ind"], gt["reg"])
+        out = {"hm_loss": hm_loss * weights[0], "wh_loss": wh_loss * weights[1],
+               "off_loss": off_loss * weights[2]}
+        (out["hm_loss"] + out["wh_loss"] + out["off_loss"]).backward()
+    return out, (hm.grad, w_.grad, r_.grad)
+
+
+def ref_decode(heat, wh, reg, down_ratio=4, K=100):
+    """Reference ctdet_decode (centernet.py:426) looped per image (it is batch=1 only)."""
+    fn = load()["ctdet_decode"]
+    outs = [fn(heat[b:b + 1], wh[b:b + 1], reg=None if reg is None else reg[b:b + 1],
+               down_ratio=down_ratio, K=K) for b in range(heat.shape[0])]
+    return (torch.stack([o[0] for o in outs]), torch.stack([o[1] for o in outs]),
+            torch.stack([o[2] for o in outs]))

@@ -1,0 +1,415 @@
+"""GPU: the CUDA path (through the C ABI) against the oracle and the committed golden vectors.
+
+Bars (BASELINE.json north_star): decode indices/classes and ind/reg_mask targets bit-exact on
+tie-free inputs; heatmap targets within 1e-6 absolute; loss values and gradients within 1e-5
+relative; boxes bit-exact in fp32 (stated tolerance: 0).
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import ctdet_oracle as O
+from oracle import gen_golden as G
+from detectron2_centernet_b200 import synthetic as S
+
+pytestmark = pytest.mark.gpu
+
+CASES = list(G.CASES)
+DEV = "cuda:0"
+
+
+def _cuda(*arrs):
+    return [torch.from_numpy(np.ascontiguousarray(a)).to(DEV) for a in arrs]
+
+
+def _targets(bl, cl, H, W, C):
+    from detectron2_centernet_b200 import target as T
+    boxes, classes, offsets = S.pack_objects(bl, cl)
+    if len(classes) == 0:
+        boxes, classes = np.zeros((1, 4), np.float32), np.zeros((1,), np.int64)
+    b, c, o = _cuda(boxes, classes, offsets)
+    return T.target_gen(b, c, o, len(bl), C, H, W)
+
+
+@pytest.fixture(scope="module")
+def inputs():
+    cache = {}
+
+    def get(case):
+        if case not in cache:
+            cache[case] = G.build_inputs(case)
+        return cache[case]
+    return get
+
+
+# ------------------------------------------------------------------ target generation
+@pytest.mark.parametrize("case", CASES)
+def test_target_gen(case, golden, inputs):
+    bl, cl, hm, wh, reg, (B, C, H, W, K, full) = inputs(case)
+    out = _targets(bl, cl, H, W, C)
+    torch.cuda.synchronize()
+    ref = O.gen_heatmap_batch(bl, cl, H, W, C)
+    for k in ("reg_mask", "ind", "wh", "reg"):
+        got = out[k].cpu().numpy()
+        assert got.dtype == ref[k].dtype
+        assert np.array_equal(got, ref[k]), k                       # bit-exact slots
+        assert np.array_equal(got, golden[case + "/gt_" + k]), k    # and equal to the reference's
+    got_hm = out["hm"].cpu().numpy()
+    assert np.abs(got_hm - ref["hm"]).max() <= 1e-6                 # north_star: 1e-6 absolute
+    assert np.array_equal(got_hm == 1, ref["hm"] == 1)              # positives identical
+    assert np.array_equal(got_hm == 0, ref["hm"] == 0)              # footprints identical
+    npos = out["num_pos"].cpu().numpy()
+    assert npos.sum() == int(golden[case + "/num_pos"])
+    assert np.array_equal(npos, (ref["hm"] == 1).reshape(B, -1).sum(1))
+
+
+def test_target_gen_edge_cases():
+    C, H, W = 3, 40, 52          # W % 4 == 0 (bulk store) but not a power of two
+    bl = [np.array([[0, 0, 4, 4], [200, 150, 208, 160], [10, 10, 10, 50], [-30, -30, 10, 10],
+                    [100, 60, 140, 100], [100, 60, 140, 100], [0, 0, 208, 160]], np.float32),
+          np.zeros((0, 4), np.float32),
+          np.tile(np.array([[40, 40, 80, 90]], np.float32), (200, 1))]      # 200 identical objects
+    cl = [np.array([0, 1, 2, 0, 1, 1, 2]), np.zeros((0,), np.int64), np.arange(200) % C]
+    out = _targets(bl, cl, H, W, C)
+    ref = O.gen_heatmap_batch(bl, cl, H, W, C)
+    for k in ("reg_mask", "ind", "wh", "reg"):
+        assert np.array_equal(out[k].cpu().numpy(), ref[k]), k
+    assert np.abs(out["hm"].cpu().numpy() - ref["hm"]).max() <= 1e-6
+    assert np.array_equal(out["num_pos"].cpu().numpy(), (ref["hm"] == 1).reshape(3, -1).sum(1))
+
+
+def test_target_gen_odd_width_fallback():
+    C, H, W = 2, 9, 7            # W % 4 != 0: plain-store path
+    bl, cl = S.make_batch_objects(5, 2, 28, n_max=5, num_classes=C)
+    out = _targets(bl, cl, H, W, C)
+    ref = O.gen_heatmap_batch(bl, cl, H, W, C)
+    assert np.abs(out["hm"].cpu().numpy() - ref["hm"]).max() <= 1e-6
+    assert np.array_equal(out["ind"].cpu().numpy(), ref["ind"])
+
+
+def test_gen_heatmap_dropin_signature():
+    """gen_heatmap(instances, output_shape, meta) as called at centernet.py:188."""
+    from detectron2_centernet_b200.structures import Boxes, Instances
+    from detectron2_centernet_b200.target import gen_heatmap
+    bl, cl = S.make_batch_objects(9, 1, 512)
+    inst = Instances((512, 512))
+    inst.gt_boxes = Boxes(torch.from_numpy(bl[0]).to(DEV))
+    inst.gt_classes = torch.from_numpy(cl[0]).to(DEV)
+
+    class Meta:
+        thing_classes = ["c%d" % i for i in range(80)]
+    out = gen_heatmap(inst, np.array([128, 128]), Meta())
+    ref = O.gen_heatmap(bl[0], cl[0], 128, 128, 80)
+    assert out["hm"].shape == (80, 128, 128) and out["reg_mask"].dtype == torch.uint8
+    assert out["ind"].dtype == torch.int64 and out["wh"].shape == (128, 2)
+    assert np.abs(out["hm"].cpu().numpy() - ref["hm"]).max() <= 1e-6
+    assert np.array_equal(out["ind"].cpu().numpy(), ref["ind"])
+
+
+# ------------------------------------------------------------------ losses
+def _loss_case(case, inputs, alpha, golden=None, tag=None):
+    from detectron2_centernet_b200 import losses as L
+    bl, cl, hm, wh, reg, (B, C, H, W, K, full) = inputs(case)
+    gt_np = O.gen_heatmap_batch(bl, cl, H, W, C)
+    gt = {k: torch.from_numpy(v).to(DEV) for k, v in gt_np.items()}
+    t_hm, t_wh, t_reg = [t.requires_grad_(True) for t in _cuda(hm, wh, reg)]
+    return (bl, cl, hm, wh, reg, gt_np, gt, t_hm, t_wh, t_reg, L)
+
+
+def _check_grads(got, ref, what):
+    ref = ref.numpy() if isinstance(ref, torch.Tensor) else ref
+    got = got.cpu().numpy()
+    scale = np.abs(ref).max()
+    # 1e-5 relative; the absolute floor (1e-6 of the largest gradient) covers cells whose fp32
+    # reference value is itself dominated by rounding of log(1-p) for p ~ 1e-4
+    np.testing.assert_allclose(got, ref, rtol=1e-5, atol=1e-6 * scale, err_msg=what)
+
+
+@pytest.mark.parametrize("case", CASES)
+@pytest.mark.parametrize("tag", ["a1", "acls"])
+def test_fused_losses(case, tag, golden, inputs):
+    bl, cl, hm, wh, reg, gt_np, gt, t_hm, t_wh, t_reg, L = _loss_case(case, inputs, None)
+    C = hm.shape[1]
+    alpha = [1.0] if tag == "a1" else [0.25 + 0.01 * c for c in range(C)]
+    out = L.ctdet_losses({"hm": t_hm, "wh": t_wh, "reg": t_reg}, gt, alpha=alpha)
+    (out["hm_loss"] + out["wh_loss"] + out["off_loss"]).backward()
+    torch.cuda.synchronize()
+    got = np.array([out[k].item() for k in ("hm_loss", "wh_loss", "off_loss")])
+    np.testing.assert_allclose(got, golden["%s/loss_%s" % (case, tag)], rtol=1e-5)   # vs the reference
+    lo, gr = O.losses_and_grads(torch.from_numpy(hm), torch.from_numpy(wh), torch.from_numpy(reg),
+                                gt_np, alpha=alpha)
+    np.testing.assert_allclose(got, [float(lo[k]) for k in ("hm_loss", "wh_loss", "off_loss")], rtol=1e-5)
+    _check_grads(t_hm.grad, gr[0], "d_hm")
+    _check_grads(t_wh.grad, gr[1], "d_wh")
+    _check_grads(t_reg.grad, gr[2], "d_reg")
+    # hm logits are NOT modified in place (the reference's sigmoid_ at :204 is)
+    assert np.array_equal(t_hm.detach().cpu().numpy(), hm)
+
+
+def test_fused_losses_with_num_pos_from_target_gen(inputs):
+    """num_pos produced by ctdet_target_gen feeds the loss: no counting pre-pass, same numbers."""
+    from detectron2_centernet_b200 import losses as L
+    bl, cl, hm, wh, reg, (B, C, H, W, K, full) = inputs("coco512")
+    gt = _targets(bl, cl, H, W, C)
+    assert "num_pos" in gt
+    t_hm, t_wh, t_reg = [t.requires_grad_(True) for t in _cuda(hm, wh, reg)]
+    out = L.ctdet_losses({"hm": t_hm, "wh": t_wh, "reg": t_reg}, gt, alpha=[1.0])
+    sum(out.values()).backward()
+    gt2 = {k: v for k, v in gt.items() if k != "num_pos"}
+    u_hm, u_wh, u_reg = [t.requires_grad_(True) for t in _cuda(hm, wh, reg)]
+    out2 = L.ctdet_losses({"hm": u_hm, "wh": u_wh, "reg": u_reg}, gt2, alpha=[1.0])
+    sum(out2.values()).backward()
+    for k in out:
+        np.testing.assert_allclose(out[k].item(), out2[k].item(), rtol=1e-6)
+    np.testing.assert_allclose(t_hm.grad.cpu().numpy(), u_hm.grad.cpu().numpy(), rtol=1e-6, atol=0)
+
+
+def test_losses_no_positives_and_upstream_grad(inputs):
+    """num_pos == 0 branch (:365-366) and a non-unit upstream gradient."""
+    from detectron2_centernet_b200 import losses as L
+    B, C, H, W = 2, 3, 16, 16
+    hm, wh, reg = S.make_head_outputs(3, B, C, H, W)
+    gt_np = O.gen_heatmap_batch([np.zeros((0, 4), np.float32)] * B, [np.zeros((0,), np.int64)] * B, H, W, C)
+    gt = {k: torch.from_numpy(v).to(DEV) for k, v in gt_np.items()}
+    t_hm, t_wh, t_reg = [t.requires_grad_(True) for t in _cuda(hm, wh, reg)]
+    out = L.ctdet_losses({"hm": t_hm, "wh": t_wh, "reg": t_reg}, gt, alpha=[1.0])
+    (out["hm_loss"] * 3.0 + out["wh_loss"] * 0.5 + out["off_loss"]).backward()
+    lo, _ = O.losses_and_grads(torch.from_numpy(hm), torch.from_numpy(wh), torch.from_numpy(reg), gt_np)
+    x = torch.from_numpy(hm).requires_grad_(True)
+    w = torch.from_numpy(wh).requires_grad_(True)
+    r = torch.from_numpy(reg).requires_grad_(True)
+    l2 = O.losses(x, w, r, gt_np)
+    (l2["hm_loss"] * 3.0 + l2["wh_loss"] * 0.5 + l2["off_loss"]).backward()
+    np.testing.assert_allclose(out["hm_loss"].item(), float(lo["hm_loss"]), rtol=1e-5)
+    assert out["wh_loss"].item() == 0.0 and out["off_loss"].item() == 0.0
+    _check_grads(t_hm.grad, x.grad, "d_hm (x3)")
+    assert t_wh.grad.abs().max().item() == 0.0
+
+
+def test_focal_and_regl1_dropins(inputs):
+    """FocalLoss(alpha)(pred, gt) on probabilities and RegL1Loss()(output, mask, ind, target)."""
+    from detectron2_centernet_b200 import losses as L
+    bl, cl, hm, wh, reg, (B, C, H, W, K, full) = inputs("dense_small")
+    gt_np = O.gen_heatmap_batch(bl, cl, H, W, C)
+    pred_np = S.sigmoid_clamp(hm)
+    pred = torch.from_numpy(pred_np).to(DEV).requires_grad_(True)
+    loss = L.FocalLoss([0.5])(pred, torch.from_numpy(gt_np["hm"]).to(DEV))
+    loss.backward()
+    p_ref = torch.from_numpy(pred_np).requires_grad_(True)
+    l_ref = O.focal_loss(p_ref, torch.from_numpy(gt_np["hm"]), [0.5])
+    l_ref.backward()
+    np.testing.assert_allclose(loss.item(), l_ref.item(), rtol=1e-5)
+    _check_grads(pred.grad, p_ref.grad, "d_pred")
+    o = torch.from_numpy(wh).to(DEV).requires_grad_(True)
+    l1 = L.RegL1Loss()(o, torch.from_numpy(gt_np["reg_mask"]).to(DEV),
+                       torch.from_numpy(gt_np["ind"]).to(DEV), torch.from_numpy(gt_np["wh"]).to(DEV))
+    l1.backward()
+    o_ref = torch.from_numpy(wh).requires_grad_(True)
+    l1_ref = O.reg_l1_loss(o_ref, torch.from_numpy(gt_np["reg_mask"]), torch.from_numpy(gt_np["ind"]),
+                           torch.from_numpy(gt_np["wh"]))
+    l1_ref.backward()
+    np.testing.assert_allclose(l1.item(), l1_ref.item(), rtol=1e-5)
+    _check_grads(o.grad, o_ref.grad, "d_output")
+
+
+# ------------------------------------------------------------------ decode
+@pytest.mark.parametrize("case", CASES)
+def test_decode(case, golden, inputs):
+    from detectron2_centernet_b200 import decode as D
+    bl, cl, hm, wh, reg, (B, C, H, W, K, full) = inputs(case)
+    heat = S.sigmoid_clamp(hm)
+    t_heat, t_wh, t_reg = _cuda(heat, wh, reg)
+    boxes, scores, classes, inds = D.ctdet_decode_batch(t_heat, t_wh, t_reg, down_ratio=4, K=K)
+    torch.cuda.synchronize()
+    ob, os_, oc, oi = O.decode(heat, wh, reg, 4, K)
+    assert classes.dtype == torch.int32 and inds.dtype == torch.int64
+    assert np.array_equal(classes.cpu().numpy(), oc)
+    assert np.array_equal(inds.cpu().numpy(), oi)
+    assert np.array_equal(scores.cpu().numpy(), os_)
+    assert np.array_equal(boxes.cpu().numpy(), ob)                       # fp32 bit-exact
+    # and identical to what the reference itself produced
+    assert np.array_equal(classes.cpu().numpy(), golden[case + "/dec_classes"])
+    assert np.array_equal(scores.cpu().numpy(), golden[case + "/dec_scores"])
+    assert np.array_equal(boxes.cpu().numpy(), golden[case + "/dec_boxes"])
+    b2, _, _, _ = D.ctdet_decode_batch(t_heat, t_wh, None, down_ratio=4, K=K)
+    assert np.array_equal(b2.cpu().numpy(), golden[case + "/dec_boxes_noreg"])
+    # logits mode: same ranking, scores within 1 ulp of clamp(sigmoid)
+    (t_hm,) = _cuda(hm)
+    b3, s3, c3, i3 = D.ctdet_decode_batch(t_hm, t_wh, t_reg, down_ratio=4, K=K, logits=True)
+    assert np.array_equal(c3.cpu().numpy(), oc) and np.array_equal(i3.cpu().numpy(), oi)
+    assert np.array_equal(b3.cpu().numpy(), ob)
+    np.testing.assert_allclose(s3.cpu().numpy(), os_, rtol=2e-7)
+    # single-image drop-in signature
+    bb, ss, cc = D.ctdet_decode(t_heat[:1], t_wh[:1], reg=t_reg[:1], down_ratio=4, K=K)
+    assert bb.shape == (K, 4) and ss.shape == (K,) and cc.shape == (K,)
+    assert np.array_equal(cc.cpu().numpy(), oc[0])
+
+
+def test_decode_ties_plateaus_and_few_peaks():
+    from detectron2_centernet_b200 import decode as D
+    rng = np.random.default_rng(0)
+    # (1) constant map: every cell is a peak with the same score -> lowest flat indices win
+    heat = np.full((2, 3, 16, 20), 0.25, np.float32)
+    # (2) second image: quantised values -> many exact ties and plateaus
+    heat[1] = (rng.integers(1, 6, (3, 16, 20)) / 8.0).astype(np.float32)
+    wh = rng.uniform(0, 8, (2, 2, 16, 20)).astype(np.float32)
+    reg = rng.uniform(0, 1, (2, 2, 16, 20)).astype(np.float32)
+    out = D.ctdet_decode_batch(*_cuda(heat, wh, reg), down_ratio=4, K=50)
+    ref = O.decode(heat, wh, reg, 4, 50)
+    for g, r in zip(out, ref):
+        assert np.array_equal(g.cpu().numpy(), r)
+    # (3) fewer peaks than K: zeros (heat*keep) fill the tail in flat-index order
+    # a strictly increasing ramp has exactly one peak per plane (its last cell)
+    heat = (np.arange(2 * 64, dtype=np.float32).reshape(1, 2, 8, 8) + 1) / 200.0
+    wh1 = np.ones((1, 2, 8, 8), np.float32)
+    out = D.ctdet_decode_batch(*_cuda(heat, wh1), None, down_ratio=1, K=40)
+    ref = O.decode(heat, wh1, None, 1, 40)
+    for g, r in zip(out, ref):
+        assert np.array_equal(g.cpu().numpy(), r)
+
+
+def test_decode_saturated_logits_tie_rule():
+    """Logits > 9.21 saturate the clamp at 1-1e-4: probabilities tie, the rule picks lower index."""
+    from detectron2_centernet_b200 import decode as D
+    hm = np.full((1, 2, 8, 8), -5.0, np.float32)
+    hm[0, 1, 3, 3] = 12.0
+    hm[0, 0, 5, 5] = 15.0
+    heat = S.sigmoid_clamp(hm)
+    assert heat[0, 1, 3, 3] == heat[0, 0, 5, 5]
+    wh = np.ones((1, 2, 8, 8), np.float32)
+    out = D.ctdet_decode_batch(*_cuda(heat, wh), None, down_ratio=1, K=4)
+    ref = O.decode(heat, wh, None, 1, 4)
+    for g, r in zip(out, ref):
+        assert np.array_equal(g.cpu().numpy(), r)
+    assert out[2][0, 0].item() == 0 and out[3][0, 0].item() == 5 * 8 + 5   # class 0 first (lower flat)
+
+
+def test_decode_wide_map_strips_and_cat_spec_wh():
+    """W = 320 (three 128-column strips incl. a partial one), non-square, cat_spec_wh."""
+    from detectron2_centernet_b200 import decode as D
+    B, C, H, W, K = 2, 3, 24, 320, 64
+    hm, wh, reg = S.make_head_outputs(77, B, C, H, W)
+    heat = S.sigmoid_clamp(hm)
+    rng = np.random.default_rng(1)
+    whc = rng.uniform(0, 32, (B, 2 * C, H, W)).astype(np.float32)
+    out = D.ctdet_decode_batch(*_cuda(heat, whc, reg), down_ratio=4, K=K, cat_spec_wh=True)
+    ref = O.decode(heat, whc, reg, 4, K, cat_spec_wh=True)
+    for g, r in zip(out, ref):
+        assert np.array_equal(g.cpu().numpy(), r)
+
+
+def test_decode_odd_width():
+    from detectron2_centernet_b200 import decode as D
+    B, C, H, W, K = 1, 2, 13, 37, 20
+    hm, wh, reg = S.make_head_outputs(78, B, C, H, W)
+    heat = S.sigmoid_clamp(hm)
+    out = D.ctdet_decode_batch(*_cuda(heat, wh, reg), down_ratio=4, K=K)
+    ref = O.decode(heat, wh, reg, 4, K)
+    for g, r in zip(out, ref):
+        assert np.array_equal(g.cpu().numpy(), r)
+
+
+def test_nms_topk_gather_dropins(inputs):
+    from detectron2_centernet_b200 import decode as D
+    bl, cl, hm, wh, reg, (B, C, H, W, K, full) = inputs("dense_small")
+    heat = S.sigmoid_clamp(hm)
+    (t_heat, t_wh) = _cuda(heat, wh)
+    keep = O.peak_mask(heat)
+    nms = D._nms(t_heat).cpu().numpy()
+    assert np.array_equal(nms, heat * keep)
+    s, inds, cls, ys, xs = D._topk(t_heat, K=K)       # bare top-K: no peak test
+    flat = heat.reshape(B, -1)
+    order = np.argsort(-flat, axis=1, kind="stable")[:, :K]
+    assert np.array_equal(s.cpu().numpy(), np.take_along_axis(flat, order, 1))
+    assert np.array_equal(cls.cpu().numpy(), (order // (H * W)).astype(np.int32))
+    assert np.array_equal(inds.cpu().numpy(), order % (H * W))
+    assert np.array_equal(ys.cpu().numpy(), ((order % (H * W)) // W).astype(np.float32))
+    g = D._transpose_and_gather_feat(t_wh, inds).cpu().numpy()
+    ref = O.gather_feat_nchw(torch.from_numpy(wh), inds.cpu()).numpy()
+    assert np.array_equal(g, ref)
+
+
+def test_cpu_tensors_raise():
+    from detectron2_centernet_b200 import decode as D
+    with pytest.raises(NotImplementedError):
+        D.ctdet_decode_batch(torch.zeros(1, 2, 8, 8), torch.zeros(1, 2, 8, 8))
+    with pytest.raises(RuntimeError):
+        D.ctdet_decode_batch(torch.zeros(1, 2, 4, 4, device=DEV), torch.zeros(1, 2, 4, 4, device=DEV), K=17)
+
+
+# ------------------------------------------------------------------ full-size properties
+def test_full_size_properties():
+    """BASELINE config 2/3 sizes: size-independent checks (no oracle at this size)."""
+    from detectron2_centernet_b200 import decode as D
+    from detectron2_centernet_b200 import losses as L
+    B, C, H, W, K = 32, 80, 128, 128, 100
+    bl, cl = S.make_batch_objects(1236, B, 512)
+    gt = _targets(bl, cl, H, W, C)
+    hm = gt["hm"]
+    assert float(hm.min()) >= 0.0 and float(hm.max()) <= 1.0
+    # idempotence / determinism: a second run gives identical bytes
+    gt2 = _targets(bl, cl, H, W, C)
+    assert torch.equal(hm, gt2["hm"])
+    # positives: exactly one 1.0 per distinct (class, centre) -> equals num_pos
+    assert int((hm == 1).sum()) == int(gt["num_pos"].sum())
+    # image b of the batch equals a batch-of-one run of the same image (image independence)
+    one = _targets(bl[5:6], cl[5:6], H, W, C)
+    assert torch.equal(one["hm"][0], hm[5]) and torch.equal(one["ind"][0], gt["ind"][5])
+    g = torch.Generator(device=DEV).manual_seed(1)
+    logits = torch.randn((B, C, H, W), device=DEV, generator=g) * 1.5 - 2.19
+    wh = torch.rand((B, 2, H, W), device=DEV, generator=g) * 64
+    reg = torch.rand((B, 2, H, W), device=DEV, generator=g)
+    # loss linearity in the weights + gradient equals a finite-difference directional derivative
+    x = logits.clone().requires_grad_(True)
+    o1 = L.ctdet_losses({"hm": x, "wh": wh.clone().requires_grad_(True), "reg": reg.clone().requires_grad_(True)},
+                        gt, alpha=[1.0], weights=(1.0, 0.1, 1.0))
+    sum(o1.values()).backward()
+    o2 = L.ctdet_losses({"hm": logits, "wh": wh, "reg": reg}, gt, alpha=[1.0], weights=(2.0, 0.2, 2.0))
+    for k in o1:
+        np.testing.assert_allclose(2 * o1[k].item(), o2[k].item(), rtol=1e-6)
+    d = torch.randn_like(logits)
+    eps = 1e-2
+    lp = L.ctdet_losses({"hm": logits + eps * d, "wh": wh, "reg": reg}, gt, alpha=[1.0])["hm_loss"].item()
+    lm = L.ctdet_losses({"hm": logits - eps * d, "wh": wh, "reg": reg}, gt, alpha=[1.0])["hm_loss"].item()
+    fd = (lp - lm) / (2 * eps)
+    an = float((x.grad.double() * d.double()).sum())
+    np.testing.assert_allclose(an, fd, rtol=2e-3)
+    # decode: scores sorted, every winner is a 3x3 peak, nothing outside the winners beats the K-th
+    heat = torch.clamp(torch.sigmoid(logits), 1e-4, 1 - 1e-4)
+    boxes, scores, classes, inds = D.ctdet_decode_batch(heat, wh, reg, down_ratio=4, K=K)
+    assert bool((scores[:, :-1] >= scores[:, 1:]).all())
+    pooled = torch.nn.functional.max_pool2d(heat, 3, 1, 1)
+    peaks = torch.where(pooled == heat, heat, torch.zeros_like(heat)).view(B, -1)
+    flat = classes.long() * (H * W) + inds
+    assert torch.equal(peaks.gather(1, flat), scores)
+    ref_s, ref_i = torch.topk(peaks, K, dim=1)                 # tie-free random data
+    assert torch.equal(ref_s, scores) and torch.equal(ref_i, flat)
+    # batch independence: image 7 alone decodes to the same detections
+    b1, s1, c1, i1 = D.ctdet_decode_batch(heat[7:8], wh[7:8], reg[7:8], down_ratio=4, K=K)
+    assert torch.equal(b1[0], boxes[7]) and torch.equal(c1[0], classes[7])
+
+
+def test_postprocess_batch():
+    from detectron2_centernet_b200 import decode as D
+    B, C, H, W, K = 3, 5, 32, 32, 40
+    hm, wh, reg = S.make_head_outputs(5, B, C, H, W)
+    heat = S.sigmoid_clamp(hm)
+    boxes, scores, classes, inds = D.ctdet_decode_batch(*_cuda(heat, wh, reg), down_ratio=4, K=K)
+    rb, rs, rc = boxes.cpu().numpy().copy(), scores.cpu().numpy().copy(), classes.cpu().numpy().copy()
+    sizes = np.array([[128, 128, 256, 192], [128, 128, 128, 128], [100, 120, 50, 60]], np.int32)
+    n_keep = D.postprocess_batch(boxes, scores, classes, torch.from_numpy(sizes).to(DEV),
+                                 max_dets=30, score_thresh=0.3)
+    for b in range(B):
+        bb, ss, cc = O.postprocess_single(rb[b], rs[b], rc[b], 30, 0.3)
+        in_h, in_w, out_h, out_w = [int(v) for v in sizes[b]]
+        t = torch.from_numpy(bb.copy())
+        t[:, 0::2] *= out_w / in_w
+        t[:, 1::2] *= out_h / in_h
+        t[:, 0::2].clamp_(0, out_w)
+        t[:, 1::2].clamp_(0, out_h)
+        ne = ((t[:, 2] - t[:, 0]) > 0) & ((t[:, 3] - t[:, 1]) > 0)
+        n = int(ne.sum())
+        assert int(n_keep[b]) == n
+        assert np.array_equal(boxes[b, :n].cpu().numpy(), t[ne].numpy())
+        assert np.array_equal(scores[b, :n].cpu().numpy(), ss[ne.numpy()])
+        assert np.array_equal(classes[b, :n].cpu().numpy(), cc[ne.numpy()])
