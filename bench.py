@@ -1,0 +1,284 @@
+#!/usr/bin/env python
+"""bench.py -- ctdet heatmap hot path throughput (BASELINE.json metric: images/sec @512^2).
+
+Workload (config.workload = BASELINE.json configs[1] + the decode of the metric): one "step" is
+one pass of the hot path over a batch of 32 synthetic COCO-shaped images at 512^2 (80x128x128
+heatmap): Gaussian target generation -> fused focal/RegL1 loss forward+backward -> top-100 decode.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]           our CUDA path (one rank per GPU)
+  python bench.py --impl reference ...                          the reference's CPU path (oracle port)
+
+One JSON line on stdout (rank 0).  `value` = images/s with inputs resident in HBM; `e2e` = the same
+through the public API from pinned HOST buffers, H2D/D2H inside the timed region; `roofline` =
+the dominant kernel (fused loss) against the measured HBM peak; `cpu_baseline` = the oracle port
+timed on this box's host cores on a bounded sample.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from detectron2_centernet_b200 import synthetic as S   # noqa: E402
+
+B_PER_GPU, C, H, W, K, INPUT = 32, 80, 128, 128, 100, 512
+METRIC = "ctdet target-gen + focal/RegL1 loss fwd+bwd + top-100 decode, images/sec @512^2"
+WORKLOAD = ("ctdet DLA-34 training-step heads, batch=32/GPU @512^2 (80x128x128 heatmap, <=40 objects/image): "
+            "gaussian targets + fused focal/RegL1 loss fwd+bwd + top-100 decode with 3x3 peak NMS")
+BYTES_PER_CELL = {"target_gen": 4, "loss": 12, "decode": 4}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.isfile(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks + throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.proc = index, [], None
+
+    def run(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                self.rows.append([x.strip() for x in line.split(",")])
+        except Exception:
+            pass
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 6 for n, v in zip(names, r[2:6]) if v == "Active"})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch.distributed as dist
+    from detectron2_centernet_b200 import decode as D
+    from detectron2_centernet_b200 import losses as L
+    from detectron2_centernet_b200 import target as T
+    from detectron2_centernet_b200 import _lib
+
+    rank = int(os.environ.get("RANK", 0))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    _lib.load()
+    B = B_PER_GPU                                   # weak scaling: 32 images per GPU per step
+    cells = B * C * H * W
+
+    # per-rank synthetic inputs (seed = 1236 + rank), generated on the host like a data loader would
+    bl, cl = S.make_batch_objects(1236 + rank, B, INPUT)
+    boxes, classes, offsets = S.pack_objects(bl, cl)
+    hm_np, wh_np, reg_np = S.make_head_outputs(2236 + rank, B, C, H, W, bl, tie_free=False)
+    pin = lambda a: torch.from_numpy(a).pin_memory()            # noqa: E731
+    h_boxes, h_classes, h_offsets = pin(boxes), pin(classes), pin(offsets)
+    h_hm, h_wh, h_reg = pin(hm_np), pin(wh_np), pin(reg_np)
+    d_boxes, d_classes, d_offsets = h_boxes.to(dev), h_classes.to(dev), h_offsets.to(dev)
+    d_hm, d_wh, d_reg = h_hm.to(dev), h_wh.to(dev), h_reg.to(dev)
+    alpha = L.alpha_tensor([1.0], C, dev)
+    weights = (1.0, 0.1, 1.0)
+    gt = T.target_gen(d_boxes, d_classes, d_offsets, B, C, H, W)
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)   # > 126 MB L2
+    h_out = torch.empty(3 + B * K * 6, dtype=torch.float32).pin_memory()
+
+    def hot_path(hm, wh, reg, bx, cls_, off):
+        """target-gen -> fused loss fwd+bwd -> decode; 4 kernel launches of ours."""
+        T.target_gen(bx, cls_, off, B, C, H, W, out=gt)
+        losses, g_hm, g_wh, g_reg = L._call(hm, wh, reg, gt["hm"], gt["reg_mask"], gt["ind"], gt["wh"],
+                                            gt["reg"], alpha, gt["num_pos"], None, 0, weights, True)
+        det = D.ctdet_decode_batch(hm, wh, reg, down_ratio=4, K=K, logits=True)
+        return losses, det
+
+    LAUNCHES_PER_STEP = 4      # target_gen, loss, decode_peaks, decode_finalize
+
+    def step_device():
+        return hot_path(d_hm, d_wh, d_reg, d_boxes, d_classes, d_offsets)
+
+    def step_e2e():
+        hm = h_hm.to(dev, non_blocking=True)
+        wh = h_wh.to(dev, non_blocking=True)
+        reg = h_reg.to(dev, non_blocking=True)
+        bx = h_boxes.to(dev, non_blocking=True)
+        cl_ = h_classes.to(dev, non_blocking=True)
+        off = h_offsets.to(dev, non_blocking=True)
+        losses, det = hot_path(hm, wh, reg, bx, cl_, off)
+        packed = torch.cat([losses, det[0].reshape(-1), det[1].reshape(-1), det[2].reshape(-1).float()])
+        h_out.copy_(packed, non_blocking=True)
+        torch.cuda.current_stream().synchronize()            # the result is on the host
+        return h_out
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup, flush_l2):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        evs = []
+        for _ in range(steps):
+            if flush_l2:
+                flush.zero_()                                # evict L2 between timed iterations
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record()
+            fn()
+            e.record()
+            evs.append((s, e))
+        barrier()
+        ms = sum(s.elapsed_time(e) for s, e in evs)          # device time of the K steps
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)         # max over ranks
+        return float(t.item())
+
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    total_ms = timed(step_device, args.steps, args.warmup, True)
+    clocks = sampler.stop() if sampler else None
+
+    # dominant kernel alone (fused loss), CUDA events on the launching stream, L2 flushed
+    def loss_only():
+        L._call(d_hm, d_wh, d_reg, gt["hm"], gt["reg_mask"], gt["ind"], gt["wh"], gt["reg"], alpha,
+                gt["num_pos"], None, 0, weights, True)
+    per_kernel = {}
+    for name, fn in (("loss", loss_only),
+                     ("target_gen", lambda: T.target_gen(d_boxes, d_classes, d_offsets, B, C, H, W, out=gt)),
+                     ("decode", lambda: D.ctdet_decode_batch(d_hm, d_wh, d_reg, down_ratio=4, K=K, logits=True))):
+        ms = timed(fn, max(args.steps, 10), 3, True) / max(args.steps, 10)
+        per_kernel[name] = {"us": round(ms * 1e3, 2),
+                            "GBps": round(cells * BYTES_PER_CELL[name] / (ms * 1e-3) / 1e9, 1)}
+    e2e_ms = timed(step_e2e, args.steps, args.warmup, False)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    peak, peak_src = peaks()
+    ms_per_step = total_ms / args.steps
+    value = world * B / (ms_per_step * 1e-3)
+    e2e_value = world * B / (e2e_ms / args.steps * 1e-3)
+    h2d = sum(t.numel() * t.element_size() for t in (h_hm, h_wh, h_reg, h_boxes, h_classes, h_offsets))
+    ach = per_kernel["loss"]["GBps"]
+    out = {
+        "metric": METRIC, "value": round(value, 1), "unit": "images/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_per_step, 4),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic (seeded COCO-shaped boxes; logits ~N(-2.19,1.5^2) + planted peaks)",
+        "config": {"workload": WORKLOAD, "images_per_gpu": B, "heatmap": [C, H, W], "K": K,
+                   "l2": "flushed (256 MB memset) between timed iterations",
+                   "sharding": "by image, no data-path collective"},
+        "clocks": clocks,
+        "e2e": {"value": round(e2e_value, 1), "unit": "images/s", "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": h_out.numel() * 4,
+                "note": "head outputs (hm/wh/reg, 176 MB/step) copied from pinned host memory every step: PCIe-bound"},
+        "gpu_launches": LAUNCHES_PER_STEP * args.steps,
+        "roofline": {"bound": "hbm", "kernel": "ctdet::loss_kernel (fused focal+RegL1 fwd+bwd)",
+                     "achieved": ach, "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4),
+                     "peak_source": peak_src, "algorithmic_bytes_per_launch": cells * 12, "traffic": None},
+        "kernels": per_kernel,
+    }
+    traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.isfile(traffic_file):
+        out["roofline"]["traffic"] = json.load(open(traffic_file)).get("loss_kernel_bytes_per_launch")
+    if world == 1 and not args.no_cpu_baseline:
+        out["cpu_baseline"] = cpu_baseline(sample_images=2, reps=2)
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# ----------------------------------------------------------------------------------------------
+def cpu_step(bl, cl, hm, wh, reg):
+    """The reference's CPU path for the same step (oracle port of gen_heatmap, CenterNet.losses +
+    backward, ctdet_decode); test infrastructure used here only as the timed CPU baseline."""
+    from oracle import ctdet_oracle as O
+    gt = O.gen_heatmap_batch(bl, cl, H, W, C)
+    O.losses_and_grads(torch.from_numpy(hm), torch.from_numpy(wh), torch.from_numpy(reg), gt)
+    O.decode_torch(S.sigmoid_clamp(hm), wh, reg, 4, K)
+
+
+def cpu_baseline(sample_images=2, reps=2):
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    bl, cl = S.make_batch_objects(1236, sample_images, INPUT)
+    hm, wh, reg = S.make_head_outputs(2236, sample_images, C, H, W, bl, tie_free=False)
+    cpu_step(bl, cl, hm, wh, reg)                                  # warm-up
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        cpu_step(bl, cl, hm, wh, reg)
+    dt = (time.perf_counter() - t0) / reps
+    return {"value": round(sample_images / dt, 2), "unit": "images/s", "cores": cores, "kind": "port",
+            "sample": "%d images of the same workload x %d reps (oracle port of the reference's numpy/torch CPU path)"
+                      % (sample_images, reps)}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    n = 2                                                          # images per bounded step
+    bl, cl = S.make_batch_objects(1236, n, INPUT)
+    hm, wh, reg = S.make_head_outputs(2236, n, C, H, W, bl, tie_free=False)
+    for _ in range(args.warmup):
+        cpu_step(bl, cl, hm, wh, reg)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_step(bl, cl, hm, wh, reg)
+    dt = time.perf_counter() - t0
+    value = n * args.steps / dt
+    sample = "each step = %d images of the workload on the host cores (oracle port; the reference package itself " \
+             "needs fvcore/yacs/pycocotools which are absent)" % n
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": round(value, 2), "unit": "images/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 3),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "images_per_step": n},
+        "cpu_baseline": {"value": round(value, 2), "unit": "images/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": round(value, 2), "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    a = ap.parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

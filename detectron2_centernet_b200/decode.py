@@ -13,16 +13,10 @@ from . import _lib
 
 FLAG_LOGITS, FLAG_CAT_SPEC_WH, FLAG_NO_NMS = 1, 2, 4
 
-_dec_ws = {}
-
-
-def _workspace(nbytes, device):
-    k = (str(device), torch.cuda.current_stream(device).cuda_stream)
-    buf = _dec_ws.get(k)
-    if buf is None or buf.numel() < nbytes:
-        buf = torch.empty(nbytes, dtype=torch.uint8, device=device)
-        _dec_ws[k] = buf
-    return buf
+def _workspace(nbytes, device, B):
+    # zero-initialised once; the finalize kernel leaves the per-image headers zeroed.  The header
+    # size depends on B, so each batch size gets its own buffer.
+    return _lib.zero_workspace("decode%d" % B, nbytes, device)
 
 
 def ctdet_decode_batch(heat, wh, reg=None, down_ratio=1, cat_spec_wh=False, K=100, logits=False,
@@ -53,7 +47,7 @@ def ctdet_decode_batch(heat, wh, reg=None, down_ratio=1, cat_spec_wh=False, K=10
     flags = (FLAG_LOGITS if logits else 0) | (FLAG_CAT_SPEC_WH if cat_spec_wh else 0) | \
             (0 if nms else FLAG_NO_NMS)
     nbytes = lib.ctdet_decode_workspace_bytes(B, C, H, W, K)
-    ws = _workspace(max(nbytes, 8), dev)
+    ws = _workspace(max(nbytes, 8), dev, B)
     with torch.cuda.device(dev):
         rc = lib.ctdet_decode(_lib.ptr(heat), _lib.ptr(wh), _lib.ptr(reg), B, C, H, W, K,
                               float(down_ratio), flags, _lib.ptr(boxes), _lib.ptr(scores),

@@ -261,3 +261,32 @@ def postprocess_single(boxes, scores, classes, max_dets=100, score_thresh=0.05):
     b, s, c = boxes[:n], scores[:n], classes[:n]
     k = s > np.float32(score_thresh)
     return b[k], s[k], c[k]
+
+
+def decode_torch(heat, wh, reg=None, down_ratio=1, K=100):
+    """ctdet_decode restated with the reference's own operator sequence (max_pool2d, two
+    torch.topk, gathers; centernet.py:399-458), batched.  Same results as decode() on tie-free
+    inputs (checked in tests); this is the variant timed as the CPU baseline because it costs
+    what the reference costs, whereas decode() pays for an explicit full sort."""
+    heat = torch.as_tensor(heat)
+    wh = torch.as_tensor(wh)
+    B, C, H, W = heat.shape
+    pooled = torch.nn.functional.max_pool2d(heat, 3, stride=1, padding=1)
+    kept = heat * (pooled == heat).to(heat.dtype)
+    cls_scores, cls_inds = torch.topk(kept.view(B, C, -1), K)            # per class (:411)
+    scores, sel = torch.topk(cls_scores.view(B, -1), K)                  # over C*K (:417)
+    classes = (sel // K).to(torch.int32)
+    inds = cls_inds.view(B, -1).gather(1, sel)
+    ys = (inds // W).to(torch.float32)
+    xs = (inds % W).to(torch.float32)
+    if reg is not None:
+        r = gather_feat_nchw(torch.as_tensor(reg), inds)
+        xs = xs + r[..., 0]
+        ys = ys + r[..., 1]
+    else:
+        xs = xs + 0.5
+        ys = ys + 0.5
+    w = gather_feat_nchw(wh, inds)
+    boxes = torch.stack([xs - w[..., 0] / 2, ys - w[..., 1] / 2,
+                         xs + w[..., 0] / 2, ys + w[..., 1] / 2], dim=2) * down_ratio
+    return boxes.numpy(), scores.numpy(), classes.numpy(), inds.numpy()

@@ -11,7 +11,7 @@ hm=(torch.randn((B,C,H,W),device=dev,generator=g)*1.5-2.19).requires_grad_(True)
 wh=(torch.rand((B,2,H,W),device=dev,generator=g)*64).requires_grad_(True)
 reg=torch.rand((B,2,H,W),device=dev,generator=g).requires_grad_(True)
 flush=torch.empty(512*1024*1024//4,device=dev)
-def timeit(fn,n=20):
+def timeit(fn,n=int(sys.argv[1]) if len(sys.argv)>1 else 20):
     for _ in range(3): fn()
     ts=[]
     for _ in range(n):

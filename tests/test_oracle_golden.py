@@ -84,6 +84,8 @@ def test_decode_matches_reference(case, golden, inputs):
     assert np.array_equal(boxes, golden[case + "/dec_boxes"])            # bit-exact boxes
     b2, _, _, _ = O.decode(heat, wh, None, down_ratio=4, K=K)
     assert np.array_equal(b2, golden[case + "/dec_boxes_noreg"])
+    bt, st, ct, it = O.decode_torch(heat, wh, reg, down_ratio=4, K=K)      # the timed CPU-baseline variant
+    assert np.array_equal(bt, boxes) and np.array_equal(st, scores) and np.array_equal(ct, classes)
     # ranking on raw logits is the same ranking (sigmoid is monotone, inputs are tie-free)
     b3, s3, c3, i3 = O.decode(hm, wh, reg, down_ratio=4, K=K, logits=True)
     assert np.array_equal(c3, classes) and np.array_equal(i3, inds) and np.array_equal(b3, boxes)
