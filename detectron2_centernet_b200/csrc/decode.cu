@@ -10,18 +10,20 @@
 //   shuffle), so the 3x3 peak test needs no shared-memory staging.  Peaks are packed into 64-bit
 //   keys  (ordered(score) << 32) | ~flat_index  -- one integer compare implements the tie rule
 //   "higher score, then lower flat index" -- and appended to a shared-memory candidate buffer.
-//   Every admitted key also bumps a shared-memory histogram over the top bits of its score; the
-//   histogram yields, in one scan, the score bin that holds the CTA's K-th best peak.  Keys below
-//   that bin are dropped and its lower edge becomes the admission threshold (streaming top-K: one
-//   float compare rejects almost every later cell).  CTAs of one image share the best bound found
-//   so far through a global atomicMax, and append their survivors (>= K of them, or everything
-//   above the shared bound) to a per-image list.  Exactness never depends on the thresholds: they
-//   are always lower bounds of the image's K-th best peak.  An exact MSB-first radix select is the
-//   fallback when one bin holds too many ties.
-// Kernel 2 (one CTA per image): histogram threshold + bitonic sort of the survivors = the exact K
-//   best (equivalent to the reference's per-class top-K followed by a top-K over C*K), gather of
-//   wh/reg, boxes, outputs; resets the per-image header.
-// Workspace: per-image header {count, bound} (zero on entry, left zero) + the key lists.
+//   Every admitted key also bumps (fire-and-forget RED) a per-IMAGE histogram in global memory over
+//   the top bits of its score.  All CTAs of an image feed it concurrently, so after each CTA's first
+//   few rows it already holds thousands of verified peaks; the bin where its suffix count reaches
+//   K is a valid lower bound of the image's K-th best peak.  CTAs re-derive that bound (after their
+//   first batch and whenever their buffer fills), publish it with atomicMax and use it as the
+//   admission threshold (streaming top-K: one float compare rejects almost every later cell), so
+//   only a few thousand keys per image ever reach the buffers.  Survivors are appended to a
+//   per-image list.  Exactness never depends on the thresholds: they are always lower bounds.  An
+//   exact MSB-first radix select is the fallback when one bin holds too many near-ties.
+// Kernel 2 (one CTA per image): final bound from the histogram + bitonic sort of the survivors = the
+//   exact K best (equivalent to the reference's per-class top-K followed by a top-K over C*K),
+//   gather of wh/reg, boxes, outputs; resets the per-image header and histogram.
+// Workspace: per-image header {count, bound} + histogram (zero on entry, left zero) + key lists.
+#include <type_traits>
 #include "common.cuh"
 
 namespace ctdet {
@@ -99,20 +101,22 @@ __device__ u64 radix_select_kth(KeyAt keyat, int n, int k, SelectScratch* sc) {
 constexpr int kHistBits = 11;                    // bin = ordered(score) >> 21: sign + exponent + 2 mantissa bits
 constexpr int kHistBins = 1 << kHistBits;
 constexpr int kHistShift = 32 - kHistBits;
-constexpr int kKeepSlack = 512;                  // a CTA keeps / emits at most K + kKeepSlack keys
+constexpr int kKeepSlack = 256;                  // a CTA keeps / emits at most K + kKeepSlack keys
 
-// Finds the highest bin b such that the number of histogram entries in bins >= b reaches `need`.
-// Returns (via smem scratch) b and that count; if the whole histogram holds fewer than `need`
-// entries, b = 0 and the count is the total.  All kThreads threads must call it.
+// Finds the highest bin b such that the number of histogram entries in bins >= b reaches `need`
+// (bin 0 / the total if the histogram holds fewer).  The histogram lives in global memory and may
+// grow while it is read: counts only increase, so the reported bin is still a valid lower bound.
+// All kThreads threads must call it; results land in *bs.
 struct BinScratch { unsigned int warp_tot[32]; int bin; unsigned int cnt_ge; };
 
 template <int kThreads>
 __device__ void find_threshold_bin(const unsigned int* hist, int need, BinScratch* bs) {
   constexpr int PER = kHistBins / kThreads;      // descending slots owned by one thread
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  unsigned int loc[PER];
   unsigned int sum = 0;
-#pragma unroll 8
-  for (int j = 0; j < PER; ++j) sum += hist[kHistBins - 1 - (tid * PER + j)];
+#pragma unroll
+  for (int j = 0; j < PER; ++j) { loc[j] = __ldcg(hist + (kHistBins - 1 - (tid * PER + j))); sum += loc[j]; }
   unsigned int incl = sum;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
@@ -120,7 +124,7 @@ __device__ void find_threshold_bin(const unsigned int* hist, int need, BinScratc
     if (lane >= o) incl += t;
   }
   if (lane == 31) bs->warp_tot[warp] = incl;
-  if (tid == 0) { bs->bin = 0; bs->cnt_ge = 0xffffffffu; }
+  if (tid == 0) { bs->bin = 0; bs->cnt_ge = 0u; }
   __syncthreads();
   unsigned int before = 0, total = 0;
   for (int w = 0; w < kThreads / 32; ++w) {
@@ -132,16 +136,23 @@ __device__ void find_threshold_bin(const unsigned int* hist, int need, BinScratc
   const unsigned int excl = incl - sum;
   if (excl < (unsigned)need && incl >= (unsigned)need) {
     unsigned int run = excl;
+    int b = 0; unsigned int cnt = 0; bool found = false;
+#pragma unroll
     for (int j = 0; j < PER; ++j) {
-      const int b = kHistBins - 1 - (tid * PER + j);
-      run += hist[b];
-      if (run >= (unsigned)need) { bs->bin = b; bs->cnt_ge = run; break; }
+      run += loc[j];
+      if (!found && run >= (unsigned)need) { found = true; b = kHistBins - 1 - (tid * PER + j); cnt = run; }
     }
+    bs->bin = b; bs->cnt_ge = cnt;
+  } else if (tid == 0 && total < (unsigned)need) {
+    bs->cnt_ge = total;
   }
   __syncthreads();
-  if (total < (unsigned)need && tid == 0) { bs->bin = 0; bs->cnt_ge = total; }
-  __syncthreads();
 }
+
+struct DecodeHeader {            // per image, zero on entry, reset by the finalize kernel
+  unsigned int count;            // keys emitted so far
+  unsigned int thr_ord;          // a valid lower bound (ordered score) of the image's K-th best peak
+};
 
 struct DecodeShared {
   SelectScratch sel;
@@ -152,96 +163,101 @@ struct DecodeShared {
   u64 kept_min;
 };
 
-// Exact prune (slow path: many equal / near-equal scores): buf[0..count) -> its K largest keys.
-__device__ void prune_exact(u64* buf, u64* tmp, DecodeShared* sh, unsigned int* hist, int K) {
-  const int tid = threadIdx.x;
-  const int n = sh->count;
-  __syncthreads();
-  if (n <= K) return;
-  const u64 T = radix_select_kth<kDecThreads>([&](int i) { return buf[i]; }, n, K, &sh->sel);
-  if (tid == 0) { sh->kept = 0; sh->kept_min = ~0ull; }
-  for (int i = tid; i < kHistBins; i += kDecThreads) hist[i] = 0u;
-  __syncthreads();
-  for (int i = tid; i < n; i += kDecThreads) {
-    const u64 key = buf[i];
-    if (key >= T) {
-      tmp[atomicAdd(&sh->kept, 1)] = key;
-      atomicMin(&sh->kept_min, key);
-      atomicAdd(&hist[(unsigned)(key >> 32) >> kHistShift], 1u);
-    }
+// Re-derives the image-wide bound from the global histogram, publishes it and raises the local
+// admission threshold.  All threads.
+__device__ void refresh_bound(const unsigned int* ghist, DecodeHeader* hdr, DecodeShared* sh, int K) {
+  find_threshold_bin<kDecThreads>(ghist, K, &sh->bs);
+  if (threadIdx.x == 0) {
+    unsigned int ord = ((unsigned int)sh->bs.bin) << kHistShift;      // lower edge of that bin
+    if (sh->bs.cnt_ge < (unsigned)K) ord = 0u;
+    if (ord) atomicMax(&hdr->thr_ord, ord);
+    const unsigned int g = max(ord, *((volatile unsigned int*)&hdr->thr_ord));
+    if (g) { const u64 t = ((u64)g << 32) - 1ull; if (t > sh->thresh) sh->thresh = t; }
   }
-  __syncthreads();
-  for (int i = tid; i < K; i += kDecThreads) buf[i] = tmp[i];
-  if (tid == 0) { sh->count = K; sh->thresh = sh->kept_min - 1ull; }
   __syncthreads();
 }
 
-// Histogram prune (fast path): keeps every key whose score bin is >= the bin that holds the K-th
-// best (so K <= kept), raises the admission threshold to that bin's lower edge and forgets the
-// bins below.  Falls back to the exact prune when more than K + kKeepSlack keys would survive.
-// `floor_ord` is an externally known lower bound (the image-wide threshold published by other CTAs).
-__device__ void prune(u64* buf, u64* tmp, DecodeShared* sh, unsigned int* hist, int K,
-                      uint32_t floor_ord) {
+// Shrinks buf[0..count): first by the freshest image-wide bound; if more than K + kKeepSlack keys
+// survive (a bin full of near-ties, or no bound yet), by an exact radix select of the K best.
+__device__ void prune(u64* buf, u64* tmp, DecodeShared* sh, const unsigned int* ghist,
+                      DecodeHeader* hdr, int K) {
   const int tid = threadIdx.x;
   __syncthreads();
+  refresh_bound(ghist, hdr, sh, K);
   const int n = sh->count;
-  find_threshold_bin<kDecThreads>(hist, K, &sh->bs);
-  int bin = sh->bs.bin;
-  const int floor_bin = (int)(floor_ord >> kHistShift);
-  if (bin < floor_bin) bin = floor_bin;               // the image already has K better peaks
-  const u64 edge = ((u64)bin << kHistShift) << 32;    // smallest key of that bin
+  const u64 th = sh->thresh;
+  const int keep_max = K + kKeepSlack;
   if (tid == 0) sh->kept = 0;
   __syncthreads();
   for (int i = tid; i < n; i += kDecThreads) {
     const u64 key = buf[i];
-    if (key >= edge) {
+    if (key > th) {
       const int pos = atomicAdd(&sh->kept, 1);
-      if (pos < K + kKeepSlack) tmp[pos] = key;
+      if (pos < keep_max) tmp[pos] = key;
     }
   }
-  for (int i = tid; i < bin; i += kDecThreads) hist[i] = 0u;
   __syncthreads();
   const int kept = sh->kept;
-  if (kept > K + kKeepSlack) {                          // too many ties in the threshold bin
-    prune_exact(buf, tmp, sh, hist, K);
+  if (kept <= keep_max) {
+    for (int i = tid; i < kept; i += kDecThreads) buf[i] = tmp[i];
+    __syncthreads();
+    if (tid == 0) sh->count = kept;
+    __syncthreads();
     return;
   }
-  for (int i = tid; i < kept; i += kDecThreads) buf[i] = tmp[i];
-  if (tid == 0) { sh->count = kept; if (edge > sh->thresh + 1ull) sh->thresh = edge - 1ull; }
+  // slow path: exact K best of buf[0..n)
+  const u64 T = radix_select_kth<kDecThreads>([&](int i) { return buf[i]; }, n, K, &sh->sel);
+  if (tid == 0) { sh->kept = 0; sh->kept_min = ~0ull; }
+  __syncthreads();
+  for (int i = tid; i < n; i += kDecThreads) {
+    const u64 key = buf[i];
+    if (key >= T) { tmp[atomicAdd(&sh->kept, 1)] = key; atomicMin(&sh->kept_min, key); }
+  }
+  __syncthreads();
+  for (int i = tid; i < K; i += kDecThreads) buf[i] = tmp[i];
+  if (tid == 0) {
+    sh->count = K;
+    if (sh->kept_min - 1ull > sh->thresh) sh->thresh = sh->kept_min - 1ull;
+    // this CTA alone holds K peaks >= kept_min: publish the (bin-rounded) bound
+    atomicMax(&hdr->thr_ord, (unsigned int)(sh->kept_min >> 32) >> kHistShift << kHistShift);
+  }
   __syncthreads();
 }
 
-struct DecodeHeader {            // per image, zero on entry, reset by the finalize kernel
-  unsigned int count;            // keys emitted so far
-  unsigned int thr_ord;          // a valid lower bound (ordered score) of the image's K-th best peak
-};
-
-// heat [B,C,H,W]; per image: hdr[b], keys[b][0 .. tiles*(K+kKeepSlack))
-__global__ void __launch_bounds__(kDecThreads)
-decode_peaks_kernel(const float* __restrict__ heat, int C, int H, int W, int K, int band_rows,
-                    int bands, int flags, int cap, DecodeHeader* __restrict__ hdr,
-                    u64* __restrict__ out_keys, size_t keys_per_image) {
+// heat [B,C,H,W]; per image b: hdr[b], ghist[b][kHistBins], keys[b][0 .. tiles*(K+kKeepSlack))
+template <bool kVec>
+__global__ void __launch_bounds__(kDecThreads, 7)
+decode_peaks_kernel(const float* __restrict__ heat, int B, int C, int H, int W, int K, int band_rows,
+                    int bands, int flags, int cap, DecodeHeader* __restrict__ hdrs,
+                    unsigned int* __restrict__ ghists, u64* __restrict__ out_keys,
+                    size_t keys_per_image) {
   extern __shared__ __align__(16) unsigned char s_raw[];
   u64* buf = reinterpret_cast<u64*>(s_raw);             // [cap]
   u64* tmp = buf + cap;                                 // [K + kKeepSlack]
-  unsigned int* hist = reinterpret_cast<unsigned int*>(tmp + K + kKeepSlack);   // [kHistBins]
   __shared__ DecodeShared sh;
   __shared__ unsigned int s_base;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  // CTA order: band fastest, then IMAGE, then class.  CTAs that run concurrently therefore belong
+  // to many images, and most CTAs of an image start after its first CTAs have published a bound.
   const int band = blockIdx.x % bands;
-  const int plane = blockIdx.x / bands;                 // b*C + c
-  const int c = plane % C, b = plane / C;
+  const int b = (blockIdx.x / bands) % B;
+  const int c = blockIdx.x / (bands * B);
+  const int plane = b * C + c;
   const bool logits = flags & CTDET_DECODE_LOGITS;
   const bool no_nms = flags & CTDET_DECODE_NO_NMS;
   const int y_lo = band * band_rows, y_hi = min(H, y_lo + band_rows);
   const float* p = heat + (size_t)plane * H * W;
+  DecodeHeader* hdr = hdrs + b;
+  unsigned int* ghist = ghists + (size_t)b * kHistBins;
   const float NEG = -__int_as_float(0x7f800000);        // -inf: max_pool2d padding (:401)
+  const float POS = __int_as_float(0x7f800000);
+  // probabilities: only cells > 0 are candidates (heat*keep zeros rank last) -> smallest denormal
+  const float floor_f = logits ? NEG : __int_as_float(1);
 
-  for (int i = tid; i < kHistBins; i += kDecThreads) hist[i] = 0u;
   if (tid == 0) {
     sh.count = 0;
-    const unsigned int g = *((volatile unsigned int*)&hdr[b].thr_ord);
+    const unsigned int g = *((volatile unsigned int*)&hdr->thr_ord);
     sh.thresh = g ? (((u64)g << 32) - 1ull) : 0ull;
   }
   __syncthreads();
@@ -252,9 +268,10 @@ decode_peaks_kernel(const float* __restrict__ heat, int C, int H, int W, int K, 
   const int sub_rows = (y_hi - y_lo + subs - 1) / subs;
   const int items = strips * subs;
   const int rounds = (items + kDecWarps - 1) / kDecWarps;
-  const int batches = (sub_rows + kRowsPerBatch - 1) / kRowsPerBatch;
+  // the first batch of an item is a single row: its peaks reach the image histogram early and
+  // give a first bound after 1/32 of the work instead of 1/8
+  const int batches = 1 + (sub_rows - 1 + kRowsPerBatch - 1) / kRowsPerBatch;
   const int limit = cap - kBatchMax;
-  const bool vec = (W % 4) == 0;
 
   for (int rnd = 0; rnd < rounds; ++rnd) {
     const int item = rnd * kDecWarps + warp;
@@ -262,25 +279,30 @@ decode_peaks_kernel(const float* __restrict__ heat, int C, int H, int W, int K, 
     const int strip = active ? item % strips : 0;
     const int sub = active ? item / strips : 0;
     const int r0 = y_lo + sub * sub_rows;
-    const int r1 = active ? min(y_hi, r0 + sub_rows) : r0;      // rows [r0, r1)
+    const int r1 = active ? min(y_hi, r0 + sub_rows) : r0;      // rows [r0, r1) are tested
+    const int last_row = active ? min(r1, H - 1) : -1;          // last row that may be loaded
     const int x0 = strip * 128 + lane * 4;                      // this lane's 4 columns
+    const bool edge_l = (strips > 1) && (lane == 0) && (x0 > 0) && (x0 - 1 < W);
+    const bool edge_r = (strips > 1) && (lane == 31) && (x0 + 4 < W);
+    const bool lane_in = x0 < W;
+    const float* colp = p + x0;
 
-    // loads row y (4 values + left/right neighbours); out-of-map cells read as -inf
+    // loads row y if 0 <= y <= last_row (warp-uniform), else the row reads as -inf
     auto load_row = [&](int y, float (&v)[4], float& lft, float& rgt) {
       v[0] = v[1] = v[2] = v[3] = NEG; lft = NEG; rgt = NEG;
-      if (y < 0 || y >= H) return;
-      const float* row = p + (size_t)y * W;
-      if (vec) {
-        if (x0 < W) { const float4 t = ldg_stream4(row + x0); v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w; }
-      } else {
+      if (y >= 0 && y <= last_row) {
+        const float* row = colp + (size_t)y * W;
+        if (kVec) {
+          if (lane_in) { const float4 t = ldg_stream4(row); v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w; }
+        } else {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) if (x0 + j < W) v[j] = __ldg(row + x0 + j);
+          for (int j = 0; j < 4; ++j) if (x0 + j < W) v[j] = __ldg(row + j);
+        }
+        if (edge_l) lft = __ldg(row - 1);                  // neighbour lives in another strip
+        if (edge_r) rgt = __ldg(row + 4);
       }
-      // neighbours across the strip edge come from memory, inside the strip from the next lane
-      if (lane == 0 && x0 > 0 && x0 - 1 < W) lft = __ldg(row + x0 - 1);
-      if (lane == 31 && x0 + 4 < W) rgt = __ldg(row + x0 + 4);
     };
-    // horizontal 3-max of a row
+    // horizontal 3-max of a row; inside the strip the neighbours come from the adjacent lanes
     auto hmax3 = [&](const float (&v)[4], float lft, float rgt, float (&m)[4]) {
       const float l = __shfl_up_sync(0xffffffffu, v[3], 1);
       const float r = __shfl_down_sync(0xffffffffu, v[0], 1);
@@ -292,84 +314,77 @@ decode_peaks_kernel(const float* __restrict__ heat, int C, int H, int W, int K, 
       m[3] = fmaxf(fmaxf(v[2], v[3]), R);
     };
 
-    float cur[4], hm_prev[4], hm_cur[4];                 // sliding window state
+    float cur[4], hm_prev[4], hm_cur[4];                 // sliding 3-row window
     {
       float t[4], l, r;
-      load_row(active ? r0 - 1 : -1, t, l, r);  hmax3(t, l, r, hm_prev);
-      load_row(active ? r0 : -1, cur, l, r);    hmax3(cur, l, r, hm_cur);
+      load_row(r0 - 1, t, l, r);   hmax3(t, l, r, hm_prev);
+      load_row(r0, cur, l, r);     hmax3(cur, l, r, hm_cur);
     }
 
-    for (int bt = 0; bt < batches; ++bt) {
-      const int yb = r0 + bt * kRowsPerBatch;
-      float nxt[kRowsPerBatch][4], nl[kRowsPerBatch], nr[kRowsPerBatch];
+    // tests rows yb .. yb+NR-1 (NR loads in flight per lane before the first use)
+    auto run_batch = [&](auto nr_tag, int yb) {
+      constexpr int NR = decltype(nr_tag)::value;
+      float nxt[NR][4], nl[NR], nr[NR];
 #pragma unroll
-      for (int q = 0; q < kRowsPerBatch; ++q) {
-        const int y = yb + q;                            // row being tested; needs row y+1
-        load_row((active && y < r1) ? y + 1 : -1, nxt[q], nl[q], nr[q]);
-      }
+      for (int q = 0; q < NR; ++q) load_row(yb + q + 1, nxt[q], nl[q], nr[q]);
+
       bool crossed = false;
       const u64 th = sh.thresh;
-      // threshold in the float domain: one FSETP per cell rejects almost everything early
       const uint32_t th_ord = (uint32_t)(th >> 32);
-      const float th_f = th_ord ? ordered_to_float(th_ord) : NEG;
+      // admission test in the float domain (one FSETP per cell); cells outside the map never pass
+      const float thv = fmaxf(th_ord ? ordered_to_float(th_ord) : NEG, floor_f);
+      float th_f[4];
 #pragma unroll
-      for (int q = 0; q < kRowsPerBatch; ++q) {
-        const int y = yb + q;
+      for (int j = 0; j < 4; ++j) th_f[j] = (x0 + j < W) ? thv : POS;
+      uint32_t flat_row = (uint32_t)((c * H + yb) * W + x0);
+#pragma unroll
+      for (int q = 0; q < NR; ++q) {
         float hm_next[4];
         hmax3(nxt[q], nl[q], nr[q], hm_next);
-        if (active && y < r1) {
-          bool cand[4];
-          bool any = false;
+        if (yb + q < r1) {                                 // warp-uniform
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             const float v = cur[j];
             const float nb = fmaxf(fmaxf(hm_prev[j], hm_cur[j]), hm_next[j]);
-            cand[j] = (no_nms || v >= nb) && (v >= th_f) && (logits || v > 0.f) && (x0 + j < W);
-            any |= cand[j];
-          }
-          if (__any_sync(0xffffffffu, any)) {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              u64 key = 0ull;
-              bool cj = cand[j];
-              if (cj) {
-                const uint32_t flat = (uint32_t)((c * H + y) * W + x0 + j);
-                const uint32_t ord = float_to_ordered(cur[j]);
-                key = ((u64)ord << 32) | (u64)(0xffffffffu - flat);
-                cj = key > th;
-                if (cj) atomicAdd(&hist[ord >> kHistShift], 1u);
-              }
-              const unsigned m = __ballot_sync(0xffffffffu, cj);
-              if (m) {
-                int base = 0;
-                if (lane == 0) {
-                  base = atomicAdd(&sh.count, __popc(m));
-                  crossed |= (base + __popc(m) > limit);
-                }
-                base = __shfl_sync(0xffffffffu, base, 0);
-                if (cj) buf[base + __popc(m & ((1u << lane) - 1u))] = key;
+            if ((no_nms || v >= nb) && v >= th_f[j]) {     // rare once a bound exists
+              const uint32_t ord = float_to_ordered(v);
+              const u64 key = ((u64)ord << 32) | (u64)(0xffffffffu - (flat_row + j));
+              if (key > th) {
+                const int pos = atomicAdd(&sh.count, 1);
+                buf[pos] = key;
+                atomicAdd(ghist + (ord >> kHistShift), 1u);   // image-wide score histogram (RED)
+                crossed |= (pos >= limit);
               }
             }
           }
         }
+        flat_row += (uint32_t)W;
 #pragma unroll
         for (int j = 0; j < 4; ++j) { hm_prev[j] = hm_cur[j]; hm_cur[j] = hm_next[j]; cur[j] = nxt[q][j]; }
       }
-      // CTA-uniform decision: did any warp push the buffer past the safe fill level?
-      if (__syncthreads_or(crossed))
-        prune(buf, tmp, &sh, hist, K, *((volatile unsigned int*)&hdr[b].thr_ord));
+      return crossed;
+    };
+
+    for (int bt = 0; bt < batches; ++bt) {
+      bool crossed;
+      if (bt == 0) crossed = run_batch(std::integral_constant<int, 1>{}, r0);
+      else crossed = run_batch(std::integral_constant<int, kRowsPerBatch>{}, r0 + 1 + (bt - 1) * kRowsPerBatch);
+      // pick up a better image-wide bound published by other CTAs (visible after the barrier)
+      if (tid == 0) {
+        const unsigned int g = *((volatile unsigned int*)&hdr->thr_ord);
+        if (g) { const u64 t = ((u64)g << 32) - 1ull; if (t > sh.thresh) sh.thresh = t; }
+      }
+      // CTA-uniform decision: did any thread push the buffer past the safe fill level?
+      if (__syncthreads_or(crossed)) prune(buf, tmp, &sh, ghist, hdr, K);
+      else if (bt <= 1 && rnd == 0) refresh_bound(ghist, hdr, &sh, K);
     }
   }
 
-  // final: keep the K best (plus ties of the threshold bin), publish the bound, emit
-  const unsigned int g_thr = *((volatile unsigned int*)&hdr[b].thr_ord);
-  prune(buf, tmp, &sh, hist, K, g_thr);
+  // final: drop everything below the freshest bound, append the survivors to the image's list
+  __threadfence();
+  prune(buf, tmp, &sh, ghist, hdr, K);
   const int n = sh.count;
-  if (tid == 0) {
-    s_base = n ? atomicAdd(&hdr[b].count, (unsigned)n) : 0u;
-    // this CTA alone holds >= K peaks at or above thresh+1: a valid bound for the whole image
-    if (n >= K) atomicMax(&hdr[b].thr_ord, (unsigned int)((sh.thresh + 1ull) >> 32));
-  }
+  if (tid == 0) s_base = n ? atomicAdd(&hdr->count, (unsigned)n) : 0u;
   __syncthreads();
   u64* dst = out_keys + (size_t)b * keys_per_image + s_base;
   for (int i = tid; i < n; i += kDecThreads) dst[i] = buf[i];
@@ -380,41 +395,42 @@ decode_peaks_kernel(const float* __restrict__ heat, int C, int H, int W, int K, 
 constexpr int kSelCap = 2048;
 
 __global__ void __launch_bounds__(kFinThreads)
-decode_finalize_kernel(DecodeHeader* __restrict__ hdr, const u64* __restrict__ keys,
-                       size_t keys_per_image, const float* __restrict__ wh,
-                       const float* __restrict__ reg, int C, int H, int W, int K, float down_ratio,
-                       int flags, float* __restrict__ boxes, float* __restrict__ scores,
-                       int32_t* __restrict__ classes, int64_t* __restrict__ inds) {
+decode_finalize_kernel(DecodeHeader* __restrict__ hdrs, unsigned int* __restrict__ ghists,
+                       const u64* __restrict__ keys, size_t keys_per_image,
+                       const float* __restrict__ wh, const float* __restrict__ reg, int C, int H,
+                       int W, int K, float down_ratio, int flags, float* __restrict__ boxes,
+                       float* __restrict__ scores, int32_t* __restrict__ classes,
+                       int64_t* __restrict__ inds) {
   __shared__ SelectScratch sc;
   __shared__ BinScratch bs;
-  __shared__ unsigned int hist[kHistBins];
   __shared__ u64 s_sel[kSelCap];
   __shared__ int s_n;
   const int tid = threadIdx.x;
   const int b = blockIdx.x;
   const u64* kb = keys + (size_t)b * keys_per_image;
-  const int n_keys = (int)hdr[b].count;
+  DecodeHeader* hdr = hdrs + b;
+  unsigned int* ghist = ghists + (size_t)b * kHistBins;
+  const int n_keys = (int)hdr->count;
   const int HW = H * W;
 
-  for (int i = tid; i < kHistBins; i += kFinThreads) hist[i] = 0u;
   if (tid == 0) s_n = 0;
-  __syncthreads();
-  for (int i = tid; i < n_keys; i += kFinThreads)
-    atomicAdd(&hist[(unsigned)(kb[i] >> 32) >> kHistShift], 1u);
-  __syncthreads();
-  find_threshold_bin<kFinThreads>(hist, K, &bs);
+  // every admitted peak of the image was counted once in ghist: its K-th best bin is exact now
+  find_threshold_bin<kFinThreads>(ghist, K, &bs);
   u64 T = ((u64)bs.bin << kHistShift) << 32;
+  if (bs.cnt_ge < (unsigned)K) T = 0ull;                  // fewer than K peaks in the whole image
   if (bs.cnt_ge > (unsigned)kSelCap) {
-    // too many keys share the threshold bin: exact radix select instead
+    // too many keys share the threshold bin: exact radix select over the list instead
     T = radix_select_kth<kFinThreads>([&](int i) { return kb[i]; }, n_keys, K, &sc);
   }
+  __syncthreads();
   for (int i = tid; i < n_keys; i += kFinThreads) {
     const u64 key = kb[i];
-    if (key >= T) s_sel[atomicAdd(&s_n, 1)] = key;
+    if (key >= T) { const int pos = atomicAdd(&s_n, 1); if (pos < kSelCap) s_sel[pos] = key; }
   }
+  for (int i = tid; i < kHistBins; i += kFinThreads) ghist[i] = 0u;     // leave the workspace zeroed
   __syncthreads();
-  if (tid == 0) { hdr[b].count = 0u; hdr[b].thr_ord = 0u; }      // leave the header zeroed
-  int n = s_n;                                            // >= min(n_keys, K), <= kSelCap
+  if (tid == 0) { hdr->count = 0u; hdr->thr_ord = 0u; }
+  int n = min(s_n, kSelCap);                              // >= min(#peaks, K)
   // fewer than K peaks: the reference's heat*keep zeros fill the rest (:405); by the tie rule
   // these are the lowest flat indices that are not selected peaks.
   if (n < K && tid == 0) {
@@ -486,7 +502,7 @@ decode_finalize_kernel(DecodeHeader* __restrict__ hdr, const u64* __restrict__ k
 
 struct DecodePlan {
   int band_rows, bands, tiles_per_image, cap;
-  size_t smem, keys_per_image, header_bytes, total_bytes;
+  size_t smem, keys_per_image, header_bytes, hist_bytes, total_bytes;
 };
 
 static DecodePlan make_plan(int B, int C, int H, int W, int K) {
@@ -500,11 +516,12 @@ static DecodePlan make_plan(int B, int C, int H, int W, int K) {
   p.bands = (H + p.band_rows - 1) / p.band_rows;
   p.tiles_per_image = C * p.bands;
   const int keep_max = K + kKeepSlack;
-  p.cap = keep_max + 256 + kBatchMax;          // prune when count > cap - kBatchMax
-  p.smem = (size_t)(p.cap + keep_max) * sizeof(u64) + (size_t)kHistBins * sizeof(unsigned int);
+  p.cap = keep_max + 128 + kBatchMax;          // prune when count > cap - kBatchMax
+  p.smem = (size_t)(p.cap + keep_max) * sizeof(u64);
   p.keys_per_image = (size_t)p.tiles_per_image * keep_max;
   p.header_bytes = (((size_t)B * sizeof(DecodeHeader)) + 255) / 256 * 256;
-  p.total_bytes = p.header_bytes + (size_t)B * p.keys_per_image * sizeof(u64);
+  p.hist_bytes = (size_t)B * kHistBins * sizeof(unsigned int);
+  p.total_bytes = p.header_bytes + p.hist_bytes + (size_t)B * p.keys_per_image * sizeof(u64);
   return p;
 }
 
@@ -533,18 +550,21 @@ extern "C" int ctdet_decode(const float* heat, const float* wh, const float* reg
   if (workspace_bytes < p.total_bytes) return CTDET_EWORKSPACE;
   if ((long long)B * p.tiles_per_image > 0x7fffffffLL) return CTDET_EINVAL;
   cudaStream_t st = (cudaStream_t)stream;
+  const bool vec = (W % 4) == 0;
+  auto kern = vec ? decode_peaks_kernel<true> : decode_peaks_kernel<false>;
   if (p.smem > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(decode_peaks_kernel,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem);
     if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
   }
-  DecodeHeader* hdr = reinterpret_cast<DecodeHeader*>(workspace);
-  u64* keys = reinterpret_cast<u64*>(reinterpret_cast<unsigned char*>(workspace) + p.header_bytes);
-  decode_peaks_kernel<<<B * p.tiles_per_image, kDecThreads, p.smem, st>>>(
-      heat, C, H, W, K, p.band_rows, p.bands, flags, p.cap, hdr, keys, p.keys_per_image);
+  unsigned char* base = reinterpret_cast<unsigned char*>(workspace);
+  DecodeHeader* hdr = reinterpret_cast<DecodeHeader*>(base);
+  unsigned int* ghist = reinterpret_cast<unsigned int*>(base + p.header_bytes);
+  u64* keys = reinterpret_cast<u64*>(base + p.header_bytes + p.hist_bytes);
+  kern<<<B * p.tiles_per_image, kDecThreads, p.smem, st>>>(
+      heat, B, C, H, W, K, p.band_rows, p.bands, flags, p.cap, hdr, ghist, keys, p.keys_per_image);
   int rc = check_launch();
   if (rc) return rc;
-  decode_finalize_kernel<<<B, kFinThreads, 0, st>>>(hdr, keys, p.keys_per_image, wh, reg, C, H, W, K,
-                                                    down_ratio, flags, boxes, scores, classes, inds);
+  decode_finalize_kernel<<<B, kFinThreads, 0, st>>>(hdr, ghist, keys, p.keys_per_image, wh, reg, C, H, W,
+                                                    K, down_ratio, flags, boxes, scores, classes, inds);
   return check_launch();
 }
