@@ -5,40 +5,37 @@
 // full-map NHWC permutes (:435,:442) and the per-image Python loop of CenterNet.inference (:224).
 //
 // Kernel 1 (HBM-bound, reads every heatmap cell exactly once = 4 B/cell):
-//   one CTA per (image, class plane, row band).  Warps walk down the rows of a 128-column strip
-//   with float4 loads kept in registers (3-row sliding window, horizontal neighbours by warp
-//   shuffle), so the 3x3 peak test needs no shared-memory staging.  Peaks are packed into 64-bit
-//   keys  (ordered(score) << 32) | ~flat_index  -- one integer compare implements the tie rule
-//   "higher score, then lower flat index" -- and appended to a shared-memory candidate buffer.
-//   Every admitted key also bumps (fire-and-forget RED) a per-IMAGE histogram in global memory over
-//   the top bits of its score.  All CTAs of an image feed it concurrently, so after each CTA's first
-//   few rows it already holds thousands of verified peaks; the bin where its suffix count reaches
-//   K is a valid lower bound of the image's K-th best peak.  CTAs re-derive that bound (after their
-//   first batch and whenever their buffer fills), publish it with atomicMax and use it as the
-//   admission threshold (streaming top-K: one float compare rejects almost every later cell), so
-//   only a few thousand keys per image ever reach the buffers.  Survivors are appended to a
-//   per-image list.  Exactness never depends on the thresholds: they are always lower bounds.  An
-//   exact MSB-first radix select is the fallback when one bin holds too many near-ties.
+//   one CTA per (image, class plane, row band).  The band (+ halo rows) is staged into shared
+//   memory by ONE bulk async copy (TMA 1-D, mbarrier completion); several CTAs are resident per SM
+//   so the copies of some overlap the peak tests of others.  Warps walk down the rows of a
+//   128-column strip (float4 per lane per row from shared memory, 3-row sliding window in
+//   registers, horizontal neighbours by warp shuffle) and record the candidate cells -- 3x3 peaks
+//   at or above the current bound -- as a bitmap (4 ballots per row).  No barriers, no atomics in
+//   this sweep.  The few candidates are then collected from the bitmap into 64-bit keys
+//   (ordered(score) << 32) | ~flat_index -- one integer compare implements the tie rule "higher
+//   score, then lower flat index" -- and each bumps (fire-and-forget RED) a per-IMAGE histogram in
+//   global memory over the top bits of its score.  The bin where that histogram's suffix count
+//   reaches K is a valid lower bound of the image's K-th best peak: the first CTAs of an image
+//   derive and publish it (atomicMax), later CTAs start from it, so one float compare rejects
+//   almost every cell and only a few thousand keys per image survive.  Survivors are appended to a
+//   per-image list.  Exactness never depends on the bounds: they are always lower bounds; an exact
+//   MSB-first radix select is the fallback when a tile holds too many near-ties.
 // Kernel 2 (one CTA per image): final bound from the histogram + bitonic sort of the survivors = the
 //   exact K best (equivalent to the reference's per-class top-K followed by a top-K over C*K),
 //   gather of wh/reg, boxes, outputs; resets the per-image header and histogram.
 // Workspace: per-image header {count, bound} + histogram (zero on entry, left zero) + key lists.
-#include <type_traits>
 #include "common.cuh"
 
 namespace ctdet {
 
 constexpr int kDecThreads = 128;                 // kernel 1: 4 warps
 constexpr int kDecWarps = kDecThreads / 32;
-constexpr int kRowsPerBatch = 4;                 // rows a warp loads before a CTA-wide check
-constexpr int kBatchMax = kDecWarps * kRowsPerBatch * 128;   // most keys one batch can append
-constexpr int kFinThreads = 1024;                // kernel 2
+constexpr int kFinThreads = 512;                 // kernel 2
 
 typedef unsigned long long u64;
 
 struct SelectScratch {
   unsigned int hist[256];
-  u64 prefix;       // selected high bits so far
   int need;         // how many still to take from the current bucket
   int bucket_count;
   int digit;
@@ -46,9 +43,10 @@ struct SelectScratch {
 
 // Exact "k-th largest" of n distinct 64-bit keys: returns T such that exactly min(n,k) keys are
 // >= T.  MSB-first radix select, 8 bits per pass; stops as soon as the bucket holding the k-th
-// key must be taken whole.  `keyat(i)` yields key i.  All threads of the CTA must call it.
-template <int kThreads, typename KeyAt>
-__device__ u64 radix_select_kth(KeyAt keyat, int n, int k, SelectScratch* sc) {
+// key must be taken whole.  visit(f) must call f(key) for every key owned by the calling thread
+// (the union over the CTA's threads = the n keys).  All threads of the CTA must call it.
+template <int kThreads, typename Visit>
+__device__ u64 radix_select_kth(Visit visit, int n, int k, SelectScratch* sc) {
   const int tid = threadIdx.x;
   if (n <= k) return 0ull;
   u64 prefix = 0ull, mask = 0ull;
@@ -56,10 +54,9 @@ __device__ u64 radix_select_kth(KeyAt keyat, int n, int k, SelectScratch* sc) {
   for (int shift = 56; shift >= 0; shift -= 8) {
     for (int i = tid; i < 256; i += kThreads) sc->hist[i] = 0u;
     __syncthreads();
-    for (int i = tid; i < n; i += kThreads) {
-      const u64 key = keyat(i);
+    visit([&](u64 key) {
       if ((key & mask) == prefix) atomicAdd(&sc->hist[(unsigned)(key >> shift) & 255u], 1u);
-    }
+    });
     __syncthreads();
     if (tid < 32) {
       // lane l owns digits 255-8l .. 248-8l (descending); find where the running count reaches need
@@ -101,7 +98,7 @@ __device__ u64 radix_select_kth(KeyAt keyat, int n, int k, SelectScratch* sc) {
 constexpr int kHistBits = 11;                    // bin = ordered(score) >> 21: sign + exponent + 2 mantissa bits
 constexpr int kHistBins = 1 << kHistBits;
 constexpr int kHistShift = 32 - kHistBits;
-constexpr int kKeepSlack = 256;                  // a CTA keeps / emits at most K + kKeepSlack keys
+constexpr int kKeepSlack = 384;                  // a CTA collects / emits at most K + kKeepSlack keys
 
 // Finds the highest bin b such that the number of histogram entries in bins >= b reaches `need`
 // (bin 0 / the total if the histogram holds fewer).  The histogram lives in global memory and may
@@ -157,14 +154,13 @@ struct DecodeHeader {            // per image, zero on entry, reset by the final
 struct DecodeShared {
   SelectScratch sel;
   BinScratch bs;
+  int ncand;        // candidate bits set in the bitmap
   int count;        // keys in buf
-  int kept;
-  u64 thresh;       // admit keys > thresh
-  u64 kept_min;
+  u64 thresh;       // candidates must be > thresh
 };
 
 // Re-derives the image-wide bound from the global histogram, publishes it and raises the local
-// admission threshold.  All threads.
+// threshold.  All threads.
 __device__ void refresh_bound(const unsigned int* ghist, DecodeHeader* hdr, DecodeShared* sh, int K) {
   find_threshold_bin<kDecThreads>(ghist, K, &sh->bs);
   if (threadIdx.x == 0) {
@@ -177,65 +173,45 @@ __device__ void refresh_bound(const unsigned int* ghist, DecodeHeader* hdr, Deco
   __syncthreads();
 }
 
-// Shrinks buf[0..count): first by the freshest image-wide bound; if more than K + kKeepSlack keys
-// survive (a bin full of near-ties, or no bound yet), by an exact radix select of the K best.
-__device__ void prune(u64* buf, u64* tmp, DecodeShared* sh, const unsigned int* ghist,
-                      DecodeHeader* hdr, int K) {
-  const int tid = threadIdx.x;
-  __syncthreads();
-  refresh_bound(ghist, hdr, sh, K);
-  const int n = sh->count;
-  const u64 th = sh->thresh;
-  const int keep_max = K + kKeepSlack;
-  if (tid == 0) sh->kept = 0;
-  __syncthreads();
-  for (int i = tid; i < n; i += kDecThreads) {
-    const u64 key = buf[i];
-    if (key > th) {
-      const int pos = atomicAdd(&sh->kept, 1);
-      if (pos < keep_max) tmp[pos] = key;
-    }
-  }
-  __syncthreads();
-  const int kept = sh->kept;
-  if (kept <= keep_max) {
-    for (int i = tid; i < kept; i += kDecThreads) buf[i] = tmp[i];
-    __syncthreads();
-    if (tid == 0) sh->count = kept;
-    __syncthreads();
-    return;
-  }
-  // slow path: exact K best of buf[0..n)
-  const u64 T = radix_select_kth<kDecThreads>([&](int i) { return buf[i]; }, n, K, &sh->sel);
-  if (tid == 0) { sh->kept = 0; sh->kept_min = ~0ull; }
-  __syncthreads();
-  for (int i = tid; i < n; i += kDecThreads) {
-    const u64 key = buf[i];
-    if (key >= T) { tmp[atomicAdd(&sh->kept, 1)] = key; atomicMin(&sh->kept_min, key); }
-  }
-  __syncthreads();
-  for (int i = tid; i < K; i += kDecThreads) buf[i] = tmp[i];
-  if (tid == 0) {
-    sh->count = K;
-    if (sh->kept_min - 1ull > sh->thresh) sh->thresh = sh->kept_min - 1ull;
-    // this CTA alone holds K peaks >= kept_min: publish the (bin-rounded) bound
-    atomicMax(&hdr->thr_ord, (unsigned int)(sh->kept_min >> 32) >> kHistShift << kHistShift);
-  }
-  __syncthreads();
+// ---- mbarrier / bulk-copy helpers (TMA 1-D bulk load: "UBLKCP" in SASS) ---------------------------
+__device__ __forceinline__ void mbar_init(uint64_t* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
+               :: "r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}"
+      :: "r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, unsigned bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               :: "r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc), "r"(bytes),
+                  "r"((uint32_t)__cvta_generic_to_shared(bar)) : "memory");
 }
 
 // heat [B,C,H,W]; per image b: hdr[b], ghist[b][kHistBins], keys[b][0 .. tiles*(K+kKeepSlack))
-template <bool kVec>
-__global__ void __launch_bounds__(kDecThreads, 7)
-decode_peaks_kernel(const float* __restrict__ heat, int B, int C, int H, int W, int K, int band_rows,
-                    int bands, int flags, int cap, DecodeHeader* __restrict__ hdrs,
+__global__ void __launch_bounds__(kDecThreads)
+decode_peaks_kernel(const float* __restrict__ heat, int B, int C, int H, int W, int Wp, int K,
+                    int band_rows, int bands, int flags, DecodeHeader* __restrict__ hdrs,
                     unsigned int* __restrict__ ghists, u64* __restrict__ out_keys,
                     size_t keys_per_image) {
-  extern __shared__ __align__(16) unsigned char s_raw[];
-  u64* buf = reinterpret_cast<u64*>(s_raw);             // [cap]
-  u64* tmp = buf + cap;                                 // [K + kKeepSlack]
+  extern __shared__ __align__(128) unsigned char s_raw[];
+  const int strips = (Wp + 127) / 128;
+  const int cap = (K + kKeepSlack + 1) & ~1;                            // even: keeps the bitmap 16-byte aligned
+  float* tile = reinterpret_cast<float*>(s_raw);                        // [(band_rows+2)][Wp]
+  u64* buf = reinterpret_cast<u64*>(s_raw + (size_t)(band_rows + 2) * Wp * sizeof(float));   // [cap]
+  uint32_t* bitmap = reinterpret_cast<uint32_t*>(buf + cap);            // [band_rows][strips][4]
   __shared__ DecodeShared sh;
   __shared__ unsigned int s_base;
+  __shared__ __align__(8) uint64_t s_bar;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   // CTA order: band fastest, then IMAGE, then class.  CTAs that run concurrently therefore belong
@@ -247,147 +223,211 @@ decode_peaks_kernel(const float* __restrict__ heat, int B, int C, int H, int W, 
   const bool logits = flags & CTDET_DECODE_LOGITS;
   const bool no_nms = flags & CTDET_DECODE_NO_NMS;
   const int y_lo = band * band_rows, y_hi = min(H, y_lo + band_rows);
+  const int nrows = y_hi - y_lo;                                        // tile row t <-> map row y_lo-1+t
   const float* p = heat + (size_t)plane * H * W;
   DecodeHeader* hdr = hdrs + b;
   unsigned int* ghist = ghists + (size_t)b * kHistBins;
-  const float NEG = -__int_as_float(0x7f800000);        // -inf: max_pool2d padding (:401)
+  const float NEG = -__int_as_float(0x7f800000);                        // max_pool2d padding (:401)
   const float POS = __int_as_float(0x7f800000);
-  // probabilities: only cells > 0 are candidates (heat*keep zeros rank last) -> smallest denormal
-  const float floor_f = logits ? NEG : __int_as_float(1);
+  // candidates: probabilities must be > 0 (heat*keep zeros rank last, :405); logits must be finite
+  const float floor_f = logits ? -3.402823466e38f : __int_as_float(1);
 
+  // ---- stage the band (+ halo rows) -------------------------------------------------------------
+  const int g_first = max(y_lo - 1, 0), g_last = min(y_hi, H - 1);      // map rows that exist
+  const bool bulk = (Wp == W);
   if (tid == 0) {
-    sh.count = 0;
+    sh.ncand = 0; sh.count = 0;
     const unsigned int g = *((volatile unsigned int*)&hdr->thr_ord);
     sh.thresh = g ? (((u64)g << 32) - 1ull) : 0ull;
+    mbar_init(&s_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-
-  // work items of this CTA: (128-column strip, sub-band of rows); a warp takes items round-robin
-  const int strips = (W + 127) / 128;
-  int subs = kDecWarps / strips; if (subs < 1) subs = 1;
-  const int sub_rows = (y_hi - y_lo + subs - 1) / subs;
-  const int items = strips * subs;
-  const int rounds = (items + kDecWarps - 1) / kDecWarps;
-  // the first batch of an item is a single row: its peaks reach the image histogram early and
-  // give a first bound after 1/32 of the work instead of 1/8
-  const int batches = 1 + (sub_rows - 1 + kRowsPerBatch - 1) / kRowsPerBatch;
-  const int limit = cap - kBatchMax;
-
-  for (int rnd = 0; rnd < rounds; ++rnd) {
-    const int item = rnd * kDecWarps + warp;
-    const bool active = item < items;
-    const int strip = active ? item % strips : 0;
-    const int sub = active ? item / strips : 0;
-    const int r0 = y_lo + sub * sub_rows;
-    const int r1 = active ? min(y_hi, r0 + sub_rows) : r0;      // rows [r0, r1) are tested
-    const int last_row = active ? min(r1, H - 1) : -1;          // last row that may be loaded
-    const int x0 = strip * 128 + lane * 4;                      // this lane's 4 columns
-    const bool edge_l = (strips > 1) && (lane == 0) && (x0 > 0) && (x0 - 1 < W);
-    const bool edge_r = (strips > 1) && (lane == 31) && (x0 + 4 < W);
-    const bool lane_in = x0 < W;
-    const float* colp = p + x0;
-
-    // loads row y if 0 <= y <= last_row (warp-uniform), else the row reads as -inf
-    auto load_row = [&](int y, float (&v)[4], float& lft, float& rgt) {
-      v[0] = v[1] = v[2] = v[3] = NEG; lft = NEG; rgt = NEG;
-      if (y >= 0 && y <= last_row) {
-        const float* row = colp + (size_t)y * W;
-        if (kVec) {
-          if (lane_in) { const float4 t = ldg_stream4(row); v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w; }
-        } else {
-#pragma unroll
-          for (int j = 0; j < 4; ++j) if (x0 + j < W) v[j] = __ldg(row + j);
-        }
-        if (edge_l) lft = __ldg(row - 1);                  // neighbour lives in another strip
-        if (edge_r) rgt = __ldg(row + 4);
-      }
-    };
-    // horizontal 3-max of a row; inside the strip the neighbours come from the adjacent lanes
-    auto hmax3 = [&](const float (&v)[4], float lft, float rgt, float (&m)[4]) {
-      const float l = __shfl_up_sync(0xffffffffu, v[3], 1);
-      const float r = __shfl_down_sync(0xffffffffu, v[0], 1);
-      const float L = lane == 0 ? lft : l;
-      const float R = lane == 31 ? rgt : r;
-      m[0] = fmaxf(fmaxf(L, v[0]), v[1]);
-      m[1] = fmaxf(fmaxf(v[0], v[1]), v[2]);
-      m[2] = fmaxf(fmaxf(v[1], v[2]), v[3]);
-      m[3] = fmaxf(fmaxf(v[2], v[3]), R);
-    };
-
-    float cur[4], hm_prev[4], hm_cur[4];                 // sliding 3-row window
-    {
-      float t[4], l, r;
-      load_row(r0 - 1, t, l, r);   hmax3(t, l, r, hm_prev);
-      load_row(r0, cur, l, r);     hmax3(cur, l, r, hm_cur);
+  if (bulk) {
+    if (tid == 0) {
+      const unsigned bytes = (unsigned)((g_last - g_first + 1) * W * sizeof(float));
+      mbar_expect_tx(&s_bar, bytes);
+      bulk_g2s(tile + (size_t)(g_first - (y_lo - 1)) * Wp, p + (size_t)g_first * W, bytes, &s_bar);
     }
+  } else {                                              // W % 4 != 0: padded rows, plain copies
+    for (int i = tid; i < (g_last - g_first + 1) * Wp; i += kDecThreads) {
+      const int r = i / Wp, x = i - r * Wp;
+      tile[(size_t)(g_first - (y_lo - 1) + r) * Wp + x] = x < W ? __ldg(p + (size_t)(g_first + r) * W + x) : NEG;
+    }
+  }
+  if (y_lo == 0) for (int x = tid; x < Wp; x += kDecThreads) tile[x] = NEG;
+  if (y_hi == H) for (int x = tid; x < Wp; x += kDecThreads) tile[(size_t)(nrows + 1) * Wp + x] = NEG;
+  const u64 th0 = sh.thresh;
+  const bool had_bound = th0 != 0ull;
+  __syncthreads();
+  if (bulk) mbar_wait(&s_bar, 0);
 
-    // tests rows yb .. yb+NR-1 (NR loads in flight per lane before the first use)
-    auto run_batch = [&](auto nr_tag, int yb) {
-      constexpr int NR = decltype(nr_tag)::value;
-      float nxt[NR][4], nl[NR], nr[NR];
-#pragma unroll
-      for (int q = 0; q < NR; ++q) load_row(yb + q + 1, nxt[q], nl[q], nr[q]);
-
-      bool crossed = false;
-      const u64 th = sh.thresh;
-      const uint32_t th_ord = (uint32_t)(th >> 32);
-      // admission test in the float domain (one FSETP per cell); cells outside the map never pass
-      const float thv = fmaxf(th_ord ? ordered_to_float(th_ord) : NEG, floor_f);
-      float th_f[4];
+  // ---- sweep: candidate bitmap ------------------------------------------------------------------
+  // work items: (128-column strip, sub-band of rows); a warp takes items round-robin
+  {
+    int subs = kDecWarps / strips; if (subs < 1) subs = 1;
+    const int sub_rows = (nrows + subs - 1) / subs;
+    const int items = strips * subs;
+    const uint32_t th_ord = (uint32_t)(th0 >> 32);
+    const float thv = fmaxf(th_ord ? ordered_to_float(th_ord) : NEG, floor_f);
+    int my_count = 0;
+    for (int item = warp; item < items; item += kDecWarps) {
+      const int strip = item % strips, sub = item / strips;
+      const int t0 = 1 + sub * sub_rows;                        // tile rows [t0, t1) are tested
+      const int t1 = min(nrows + 1, t0 + sub_rows);
+      const int x0 = strip * 128 + lane * 4;                    // this lane's 4 columns
+      const bool lane_in = x0 < Wp;
+      const bool has_l = (lane == 0) && (x0 > 0);               // neighbour cell in another strip
+      const bool has_r = (lane == 31) && (x0 + 4 < Wp);
+      const float* colp = tile + (lane_in ? x0 : 0);
+      float th_f[4];                                            // pad cells never pass
 #pragma unroll
       for (int j = 0; j < 4; ++j) th_f[j] = (x0 + j < W) ? thv : POS;
-      uint32_t flat_row = (uint32_t)((c * H + yb) * W + x0);
-#pragma unroll
-      for (int q = 0; q < NR; ++q) {
-        float hm_next[4];
-        hmax3(nxt[q], nl[q], nr[q], hm_next);
-        if (yb + q < r1) {                                 // warp-uniform
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const float v = cur[j];
-            const float nb = fmaxf(fmaxf(hm_prev[j], hm_cur[j]), hm_next[j]);
-            if ((no_nms || v >= nb) && v >= th_f[j]) {     // rare once a bound exists
-              const uint32_t ord = float_to_ordered(v);
-              const u64 key = ((u64)ord << 32) | (u64)(0xffffffffu - (flat_row + j));
-              if (key > th) {
-                const int pos = atomicAdd(&sh.count, 1);
-                buf[pos] = key;
-                atomicAdd(ghist + (ord >> kHistShift), 1u);   // image-wide score histogram (RED)
-                crossed |= (pos >= limit);
-              }
-            }
-          }
-        }
-        flat_row += (uint32_t)W;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) { hm_prev[j] = hm_cur[j]; hm_cur[j] = hm_next[j]; cur[j] = nxt[q][j]; }
-      }
-      return crossed;
-    };
 
-    for (int bt = 0; bt < batches; ++bt) {
-      bool crossed;
-      if (bt == 0) crossed = run_batch(std::integral_constant<int, 1>{}, r0);
-      else crossed = run_batch(std::integral_constant<int, kRowsPerBatch>{}, r0 + 1 + (bt - 1) * kRowsPerBatch);
-      // pick up a better image-wide bound published by other CTAs (visible after the barrier)
-      if (tid == 0) {
-        const unsigned int g = *((volatile unsigned int*)&hdr->thr_ord);
-        if (g) { const u64 t = ((u64)g << 32) - 1ull; if (t > sh.thresh) sh.thresh = t; }
+      auto load_row = [&](int t, float (&v)[4], float& lft, float& rgt) {
+        const float* row = colp + (size_t)t * Wp;
+        const float4 q = *reinterpret_cast<const float4*>(row);
+        v[0] = lane_in ? q.x : NEG; v[1] = lane_in ? q.y : NEG;
+        v[2] = lane_in ? q.z : NEG; v[3] = lane_in ? q.w : NEG;
+        lft = has_l ? row[-1] : NEG;
+        rgt = has_r ? row[4] : NEG;
+      };
+      auto hmax3 = [&](const float (&v)[4], float lft, float rgt, float (&m)[4]) {
+        const float l = __shfl_up_sync(0xffffffffu, v[3], 1);
+        const float r = __shfl_down_sync(0xffffffffu, v[0], 1);
+        const float L = lane == 0 ? lft : l;
+        const float R = lane == 31 ? rgt : r;
+        m[0] = fmaxf(fmaxf(L, v[0]), v[1]);
+        m[1] = fmaxf(fmaxf(v[0], v[1]), v[2]);
+        m[2] = fmaxf(fmaxf(v[1], v[2]), v[3]);
+        m[3] = fmaxf(fmaxf(v[2], v[3]), R);
+      };
+
+      float cur[4], hm_prev[4], hm_cur[4];                      // sliding 3-row window
+      {
+        float t[4], l, r;
+        load_row(t0 - 1, t, l, r);   hmax3(t, l, r, hm_prev);
+        load_row(t0, cur, l, r);     hmax3(cur, l, r, hm_cur);
       }
-      // CTA-uniform decision: did any thread push the buffer past the safe fill level?
-      if (__syncthreads_or(crossed)) prune(buf, tmp, &sh, ghist, hdr, K);
-      else if (bt <= 1 && rnd == 0) refresh_bound(ghist, hdr, &sh, K);
+#pragma unroll 4
+      for (int t = t0; t < t1; ++t) {
+        float nx[4], nl, nr, hm_next[4];
+        load_row(t + 1, nx, nl, nr);
+        hmax3(nx, nl, nr, hm_next);
+        uint32_t m[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float v = cur[j];
+          const float nb = fmaxf(fmaxf(hm_prev[j], hm_cur[j]), hm_next[j]);
+          m[j] = __ballot_sync(0xffffffffu, (no_nms || v >= nb) && v >= th_f[j]);
+        }
+        if (lane == 0) {
+          *reinterpret_cast<uint4*>(bitmap + ((size_t)(t - 1) * strips + strip) * 4) = make_uint4(m[0], m[1], m[2], m[3]);
+          my_count += __popc(m[0]) + __popc(m[1]) + __popc(m[2]) + __popc(m[3]);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { hm_prev[j] = hm_cur[j]; hm_cur[j] = hm_next[j]; cur[j] = nx[j]; }
+      }
+    }
+    if (lane == 0 && my_count) atomicAdd(&sh.ncand, my_count);
+  }
+  __syncthreads();
+
+  // ---- candidates -> keys -----------------------------------------------------------------------
+  const int n_words = nrows * strips * 4;
+  // calls f(key, word index, bit) for every candidate bit owned by this thread
+  auto for_each_candidate = [&](auto f) {
+    for (int w = tid; w < n_words; w += kDecThreads) {
+      uint32_t bits = bitmap[w];
+      const int j = w & 3, strip = (w >> 2) % strips, t = (w >> 2) / strips;     // tile row t+1
+      while (bits) {
+        const int ln = __ffs(bits) - 1;
+        bits &= bits - 1;
+        const int x = strip * 128 + ln * 4 + j;
+        const float v = tile[(size_t)(t + 1) * Wp + x];
+        const uint32_t flat = (uint32_t)((c * H + (y_lo + t)) * W + x);
+        f(((u64)float_to_ordered(v) << 32) | (u64)(0xffffffffu - flat), w, ln);
+      }
+    }
+  };
+
+  bool counted = false;                                  // have this CTA's candidates been RED-ed?
+  if (sh.ncand > cap) {
+    // Slow path (weak or no bound yet, plateaus, ties).  1: count every candidate into the image
+    // histogram and re-derive the bound; 2: drop the candidates below it; 3: if still too many,
+    // keep exactly the tile's K best (exact radix select).  CTA-uniform branch.
+    for_each_candidate([&](u64 key, int, int) { atomicAdd(ghist + ((uint32_t)(key >> 32) >> kHistShift), 1u); });
+    counted = true;
+    __threadfence();
+    __syncthreads();
+    refresh_bound(ghist, hdr, &sh, K);
+    if (tid == 0) sh.ncand = 0;
+    __syncthreads();
+    {
+      const u64 th = sh.thresh;
+      int kept = 0;
+      for_each_candidate([&](u64 key, int w, int ln) {
+        if (key > th) ++kept; else atomicAnd(&bitmap[w], ~(1u << ln));
+      });
+      kept = warp_sum(kept);
+      if (lane == 0 && kept) atomicAdd(&sh.ncand, kept);
+    }
+    __syncthreads();
+    if (sh.ncand > cap) {
+      const int n = sh.ncand;
+      const u64 T = radix_select_kth<kDecThreads>(
+          [&](auto f) { for_each_candidate([&](u64 key, int, int) { f(key); }); }, n, K, &sh.sel);
+      for_each_candidate([&](u64 key, int w, int ln) { if (key < T) atomicAnd(&bitmap[w], ~(1u << ln)); });
+      if (tid == 0 && T - 1ull > sh.thresh) sh.thresh = T - 1ull;
+      __syncthreads();
     }
   }
-
-  // final: drop everything below the freshest bound, append the survivors to the image's list
-  __threadfence();
-  prune(buf, tmp, &sh, ghist, hdr, K);
-  const int n = sh.count;
-  if (tid == 0) s_base = n ? atomicAdd(&hdr->count, (unsigned)n) : 0u;
+  // collect (at most cap keys by construction)
+  {
+    const u64 th = sh.thresh;
+    for_each_candidate([&](u64 key, int, int) {
+      if (key > th) {
+        const int pos = atomicAdd(&sh.count, 1);
+        if (pos < cap) buf[pos] = key;
+        if (!counted) atomicAdd(ghist + ((uint32_t)(key >> 32) >> kHistShift), 1u);
+      }
+    });
+  }
   __syncthreads();
-  u64* dst = out_keys + (size_t)b * keys_per_image + s_base;
-  for (int i = tid; i < n; i += kDecThreads) dst[i] = buf[i];
+  const int n = min(sh.count, cap);
+
+  // ---- publish / pick up the image bound, emit --------------------------------------------------
+  // CTAs that started without a bound (the first of their image) or still hold many keys derive a
+  // new bound from the histogram; the others just read the published one.
+  if (!had_bound || n > K / 2 + 32) {
+    __threadfence();
+    refresh_bound(ghist, hdr, &sh, K);
+  } else {
+    if (tid == 0) {
+      const unsigned int g = *((volatile unsigned int*)&hdr->thr_ord);
+      if (g) { const u64 t = ((u64)g << 32) - 1ull; if (t > sh.thresh) sh.thresh = t; }
+    }
+    __syncthreads();
+  }
+  {
+    const u64 th = sh.thresh;
+    int mine = 0;
+    for (int i = tid; i < n; i += kDecThreads) mine += (buf[i] > th);
+    mine = warp_sum(mine);
+    if (tid == 0) sh.count = 0;
+    __syncthreads();
+    if (lane == 0 && mine) atomicAdd(&sh.count, mine);
+    __syncthreads();
+    if (tid == 0) { const int tot = sh.count; s_base = tot ? atomicAdd(&hdr->count, (unsigned)tot) : 0u; }
+    __syncthreads();
+    if (tid == 0) sh.count = 0;
+    __syncthreads();
+    u64* dst = out_keys + (size_t)b * keys_per_image + s_base;
+    for (int i = tid; i < n; i += kDecThreads) {
+      const u64 key = buf[i];
+      if (key > th) dst[atomicAdd(&sh.count, 1)] = key;
+    }
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -414,13 +454,14 @@ decode_finalize_kernel(DecodeHeader* __restrict__ hdrs, unsigned int* __restrict
   const int HW = H * W;
 
   if (tid == 0) s_n = 0;
-  // every admitted peak of the image was counted once in ghist: its K-th best bin is exact now
+  // every collected peak of the image was counted once in ghist: its K-th best bin is final now
   find_threshold_bin<kFinThreads>(ghist, K, &bs);
   u64 T = ((u64)bs.bin << kHistShift) << 32;
   if (bs.cnt_ge < (unsigned)K) T = 0ull;                  // fewer than K peaks in the whole image
   if (bs.cnt_ge > (unsigned)kSelCap) {
     // too many keys share the threshold bin: exact radix select over the list instead
-    T = radix_select_kth<kFinThreads>([&](int i) { return kb[i]; }, n_keys, K, &sc);
+    T = radix_select_kth<kFinThreads>(
+        [&](auto f) { for (int i = tid; i < n_keys; i += kFinThreads) f(kb[i]); }, n_keys, K, &sc);
   }
   __syncthreads();
   for (int i = tid; i < n_keys; i += kFinThreads) {
@@ -501,24 +542,26 @@ decode_finalize_kernel(DecodeHeader* __restrict__ hdrs, unsigned int* __restrict
 }
 
 struct DecodePlan {
-  int band_rows, bands, tiles_per_image, cap;
+  int band_rows, bands, tiles_per_image, Wp;
   size_t smem, keys_per_image, header_bytes, hist_bytes, total_bytes;
 };
 
 static DecodePlan make_plan(int B, int C, int H, int W, int K) {
   DecodePlan p;
-  // enough CTAs to fill the machine (>= 4 per SM) without shrinking bands below 8 rows
-  int bands = 1;
-  while ((long long)B * C * bands < 4LL * kNumSMs && H / (bands * 2) >= 8) bands *= 2;
-  // a band of more than 128 rows x 512 columns is split further to bound the work per CTA
-  while ((long long)(H / bands) * W > 128 * 512 && H / (bands * 2) >= 8) bands *= 2;
-  p.band_rows = (H + bands - 1) / bands;
-  p.bands = (H + p.band_rows - 1) / p.band_rows;
+  p.Wp = (W + 3) / 4 * 4;                       // shared-memory row stride (floats)
+  // band = as many rows as fit ~32 KB of shared memory, at least 8; enough CTAs to fill the machine
+  int rows = (32 * 1024) / (p.Wp * 4);
+  if (rows < 8) rows = 8;
+  if (rows > H) rows = H;
+  while ((long long)B * C * ((H + rows - 1) / rows) < 4LL * kNumSMs && rows > 8) rows = (rows + 1) / 2;
+  p.band_rows = rows;
+  p.bands = (H + rows - 1) / rows;
   p.tiles_per_image = C * p.bands;
-  const int keep_max = K + kKeepSlack;
-  p.cap = keep_max + 128 + kBatchMax;          // prune when count > cap - kBatchMax
-  p.smem = (size_t)(p.cap + keep_max) * sizeof(u64);
-  p.keys_per_image = (size_t)p.tiles_per_image * keep_max;
+  const int cap = (K + kKeepSlack + 1) & ~1;
+  const int strips = (p.Wp + 127) / 128;
+  p.smem = (size_t)(rows + 2) * p.Wp * sizeof(float) + (size_t)cap * sizeof(u64) +
+           (size_t)rows * strips * 4 * sizeof(uint32_t);
+  p.keys_per_image = (size_t)p.tiles_per_image * cap;
   p.header_bytes = (((size_t)B * sizeof(DecodeHeader)) + 255) / 256 * 256;
   p.hist_bytes = (size_t)B * kHistBins * sizeof(unsigned int);
   p.total_bytes = p.header_bytes + p.hist_bytes + (size_t)B * p.keys_per_image * sizeof(u64);
@@ -544,24 +587,24 @@ extern "C" int ctdet_decode(const float* heat, const float* wh, const float* reg
   if (flags & ~(CTDET_DECODE_LOGITS | CTDET_DECODE_CAT_SPEC_WH | CTDET_DECODE_NO_NMS)) return CTDET_EINVAL;
   if (B == 0) return CTDET_OK;
   if (!heat || !wh || !boxes || !scores || !classes || !workspace) return CTDET_ENULL;
-  if ((W % 4) == 0 && !aligned16(heat)) return CTDET_EALIGN;
+  if ((W % 4) == 0 && !aligned16(heat)) return CTDET_EALIGN;     // bulk copies need 16-byte alignment
   if (reinterpret_cast<uintptr_t>(workspace) & 7u) return CTDET_EALIGN;
   const DecodePlan p = make_plan(B, C, H, W, K);
   if (workspace_bytes < p.total_bytes) return CTDET_EWORKSPACE;
   if ((long long)B * p.tiles_per_image > 0x7fffffffLL) return CTDET_EINVAL;
+  if (p.smem > 200 * 1024) return CTDET_EUNSUPPORTED;          // W > ~5000 columns
   cudaStream_t st = (cudaStream_t)stream;
-  const bool vec = (W % 4) == 0;
-  auto kern = vec ? decode_peaks_kernel<true> : decode_peaks_kernel<false>;
-  if (p.smem > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem);
+  {
+    cudaError_t e = cudaFuncSetAttribute(decode_peaks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)p.smem);
     if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
   }
   unsigned char* base = reinterpret_cast<unsigned char*>(workspace);
   DecodeHeader* hdr = reinterpret_cast<DecodeHeader*>(base);
   unsigned int* ghist = reinterpret_cast<unsigned int*>(base + p.header_bytes);
   u64* keys = reinterpret_cast<u64*>(base + p.header_bytes + p.hist_bytes);
-  kern<<<B * p.tiles_per_image, kDecThreads, p.smem, st>>>(
-      heat, B, C, H, W, K, p.band_rows, p.bands, flags, p.cap, hdr, ghist, keys, p.keys_per_image);
+  decode_peaks_kernel<<<B * p.tiles_per_image, kDecThreads, p.smem, st>>>(
+      heat, B, C, H, W, p.Wp, K, p.band_rows, p.bands, flags, hdr, ghist, keys, p.keys_per_image);
   int rc = check_launch();
   if (rc) return rc;
   decode_finalize_kernel<<<B, kFinThreads, 0, st>>>(hdr, ghist, keys, p.keys_per_image, wh, reg, C, H, W,
