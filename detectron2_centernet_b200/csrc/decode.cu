@@ -24,6 +24,7 @@
 //   exact K best (equivalent to the reference's per-class top-K followed by a top-K over C*K),
 //   gather of wh/reg, boxes, outputs; resets the per-image header and histogram.
 // Workspace: per-image header {count, bound} + histogram (zero on entry, left zero) + key lists.
+#include <cstdlib>
 #include "common.cuh"
 
 namespace ctdet {
@@ -198,13 +199,15 @@ __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, unsig
 }
 
 // heat [B,C,H,W]; per image b: hdr[b], ghist[b][kHistBins], keys[b][0 .. tiles*(K+kKeepSlack))
+// grid = (bands, B, C): band fastest, then IMAGE, then class.  CTAs that run concurrently therefore
+// belong to many images, and most CTAs of an image start after its first CTAs published a bound.
 __global__ void __launch_bounds__(kDecThreads)
-decode_peaks_kernel(const float* __restrict__ heat, int B, int C, int H, int W, int Wp, int K,
-                    int band_rows, int bands, int flags, DecodeHeader* __restrict__ hdrs,
-                    unsigned int* __restrict__ ghists, u64* __restrict__ out_keys,
-                    size_t keys_per_image) {
+decode_peaks_kernel(const float* __restrict__ heat, int C, int H, int W, int Wp, int K,
+                    int band_rows, int sub_rows, FastDiv div_strips, int flags,
+                    DecodeHeader* __restrict__ hdrs, unsigned int* __restrict__ ghists,
+                    u64* __restrict__ out_keys, size_t keys_per_image) {
   extern __shared__ __align__(128) unsigned char s_raw[];
-  const int strips = (Wp + 127) / 128;
+  const int strips = (int)div_strips.d;
   const int cap = (K + kKeepSlack + 1) & ~1;                            // even: keeps the bitmap 16-byte aligned
   float* tile = reinterpret_cast<float*>(s_raw);                        // [(band_rows+2)][Wp]
   u64* buf = reinterpret_cast<u64*>(s_raw + (size_t)(band_rows + 2) * Wp * sizeof(float));   // [cap]
@@ -214,11 +217,7 @@ decode_peaks_kernel(const float* __restrict__ heat, int B, int C, int H, int W, 
   __shared__ __align__(8) uint64_t s_bar;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  // CTA order: band fastest, then IMAGE, then class.  CTAs that run concurrently therefore belong
-  // to many images, and most CTAs of an image start after its first CTAs have published a bound.
-  const int band = blockIdx.x % bands;
-  const int b = (blockIdx.x / bands) % B;
-  const int c = blockIdx.x / (bands * B);
+  const int band = blockIdx.x, b = blockIdx.y, c = blockIdx.z;
   const int plane = b * C + c;
   const bool logits = flags & CTDET_DECODE_LOGITS;
   const bool no_nms = flags & CTDET_DECODE_NO_NMS;
@@ -235,21 +234,20 @@ decode_peaks_kernel(const float* __restrict__ heat, int B, int C, int H, int W, 
   // ---- stage the band (+ halo rows) -------------------------------------------------------------
   const int g_first = max(y_lo - 1, 0), g_last = min(y_hi, H - 1);      // map rows that exist
   const bool bulk = (Wp == W);
+  const int n_words = nrows * strips * 4;
   if (tid == 0) {
-    sh.ncand = 0; sh.count = 0;
-    const unsigned int g = *((volatile unsigned int*)&hdr->thr_ord);
-    sh.thresh = g ? (((u64)g << 32) - 1ull) : 0ull;
     mbar_init(&s_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
-  __syncthreads();
-  if (bulk) {
-    if (tid == 0) {
+    if (bulk) {
       const unsigned bytes = (unsigned)((g_last - g_first + 1) * W * sizeof(float));
       mbar_expect_tx(&s_bar, bytes);
       bulk_g2s(tile + (size_t)(g_first - (y_lo - 1)) * Wp, p + (size_t)g_first * W, bytes, &s_bar);
     }
-  } else {                                              // W % 4 != 0: padded rows, plain copies
+    sh.ncand = 0; sh.count = 0;
+    const unsigned int g = *((volatile unsigned int*)&hdr->thr_ord);   // overlaps the copy
+    sh.thresh = g ? (((u64)g << 32) - 1ull) : 0ull;
+  }
+  if (!bulk) {                                          // W % 4 != 0: padded rows, plain copies
     for (int i = tid; i < (g_last - g_first + 1) * Wp; i += kDecThreads) {
       const int r = i / Wp, x = i - r * Wp;
       tile[(size_t)(g_first - (y_lo - 1) + r) * Wp + x] = x < W ? __ldg(p + (size_t)(g_first + r) * W + x) : NEG;
@@ -257,22 +255,23 @@ decode_peaks_kernel(const float* __restrict__ heat, int B, int C, int H, int W, 
   }
   if (y_lo == 0) for (int x = tid; x < Wp; x += kDecThreads) tile[x] = NEG;
   if (y_hi == H) for (int x = tid; x < Wp; x += kDecThreads) tile[(size_t)(nrows + 1) * Wp + x] = NEG;
+  for (int w = tid; w < n_words; w += kDecThreads) bitmap[w] = 0u;
+  __syncthreads();
   const u64 th0 = sh.thresh;
   const bool had_bound = th0 != 0ull;
-  __syncthreads();
   if (bulk) mbar_wait(&s_bar, 0);
 
   // ---- sweep: candidate bitmap ------------------------------------------------------------------
-  // work items: (128-column strip, sub-band of rows); a warp takes items round-robin
+  // work items: (128-column strip, sub-band of rows); a warp takes items round-robin.  Per row a
+  // lane reads its 4 cells and the warp votes whether ANY of them reaches the bound; with a bound
+  // in place that is false for ~97% of the rows and the row costs ~8 instructions.  Only the other
+  // rows run the 3x3 test (rows t-1, t, t+1 are all in shared memory).
   {
-    int subs = kDecWarps / strips; if (subs < 1) subs = 1;
-    const int sub_rows = (nrows + subs - 1) / subs;
-    const int items = strips * subs;
+    const int items = strips * ((nrows + sub_rows - 1) / sub_rows);
     const uint32_t th_ord = (uint32_t)(th0 >> 32);
     const float thv = fmaxf(th_ord ? ordered_to_float(th_ord) : NEG, floor_f);
-    int my_count = 0;
     for (int item = warp; item < items; item += kDecWarps) {
-      const int strip = item % strips, sub = item / strips;
+      const int sub = (int)div_strips.div((uint32_t)item), strip = item - sub * strips;
       const int t0 = 1 + sub * sub_rows;                        // tile rows [t0, t1) are tested
       const int t1 = min(nrows + 1, t0 + sub_rows);
       const int x0 = strip * 128 + lane * 4;                    // this lane's 4 columns
@@ -280,66 +279,58 @@ decode_peaks_kernel(const float* __restrict__ heat, int B, int C, int H, int W, 
       const bool has_l = (lane == 0) && (x0 > 0);               // neighbour cell in another strip
       const bool has_r = (lane == 31) && (x0 + 4 < Wp);
       const float* colp = tile + (lane_in ? x0 : 0);
-      float th_f[4];                                            // pad cells never pass
+      const float th_lane = lane_in ? thv : POS;
+
+      // the 3x3 test of tile row t for this strip; warp-uniform call
+      auto full_test = [&](int t) {
+        float hm[3][4], v1[4];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) th_f[j] = (x0 + j < W) ? thv : POS;
-
-      auto load_row = [&](int t, float (&v)[4], float& lft, float& rgt) {
-        const float* row = colp + (size_t)t * Wp;
-        const float4 q = *reinterpret_cast<const float4*>(row);
-        v[0] = lane_in ? q.x : NEG; v[1] = lane_in ? q.y : NEG;
-        v[2] = lane_in ? q.z : NEG; v[3] = lane_in ? q.w : NEG;
-        lft = has_l ? row[-1] : NEG;
-        rgt = has_r ? row[4] : NEG;
-      };
-      auto hmax3 = [&](const float (&v)[4], float lft, float rgt, float (&m)[4]) {
-        const float l = __shfl_up_sync(0xffffffffu, v[3], 1);
-        const float r = __shfl_down_sync(0xffffffffu, v[0], 1);
-        const float L = lane == 0 ? lft : l;
-        const float R = lane == 31 ? rgt : r;
-        m[0] = fmaxf(fmaxf(L, v[0]), v[1]);
-        m[1] = fmaxf(fmaxf(v[0], v[1]), v[2]);
-        m[2] = fmaxf(fmaxf(v[1], v[2]), v[3]);
-        m[3] = fmaxf(fmaxf(v[2], v[3]), R);
-      };
-
-      float cur[4], hm_prev[4], hm_cur[4];                      // sliding 3-row window
-      {
-        float t[4], l, r;
-        load_row(t0 - 1, t, l, r);   hmax3(t, l, r, hm_prev);
-        load_row(t0, cur, l, r);     hmax3(cur, l, r, hm_cur);
-      }
-#pragma unroll 4
-      for (int t = t0; t < t1; ++t) {
-        float nx[4], nl, nr, hm_next[4];
-        load_row(t + 1, nx, nl, nr);
-        hmax3(nx, nl, nr, hm_next);
+        for (int r = 0; r < 3; ++r) {
+          const float* row = colp + (size_t)(t - 1 + r) * Wp;
+          const float4 q = *reinterpret_cast<const float4*>(row);
+          const float v[4] = {lane_in ? q.x : NEG, lane_in ? q.y : NEG, lane_in ? q.z : NEG, lane_in ? q.w : NEG};
+          const float lft = has_l ? row[-1] : NEG;
+          const float rgt = has_r ? row[4] : NEG;
+          const float l = __shfl_up_sync(0xffffffffu, v[3], 1);
+          const float rr = __shfl_down_sync(0xffffffffu, v[0], 1);
+          const float L = lane == 0 ? lft : l;
+          const float R = lane == 31 ? rgt : rr;
+          hm[r][0] = fmaxf(fmaxf(L, v[0]), v[1]);
+          hm[r][1] = fmaxf(fmaxf(v[0], v[1]), v[2]);
+          hm[r][2] = fmaxf(fmaxf(v[1], v[2]), v[3]);
+          hm[r][3] = fmaxf(fmaxf(v[2], v[3]), R);
+          if (r == 1) { v1[0] = v[0]; v1[1] = v[1]; v1[2] = v[2]; v1[3] = v[3]; }
+        }
         uint32_t m[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          const float v = cur[j];
-          const float nb = fmaxf(fmaxf(hm_prev[j], hm_cur[j]), hm_next[j]);
-          m[j] = __ballot_sync(0xffffffffu, (no_nms || v >= nb) && v >= th_f[j]);
+          const float nb = fmaxf(fmaxf(hm[0][j], hm[1][j]), hm[2][j]);
+          const float thj = (x0 + j < W) ? thv : POS;          // pad cells never pass
+          m[j] = __ballot_sync(0xffffffffu, (no_nms || v1[j] >= nb) && v1[j] >= thj);
         }
-        if (lane == 0) {
+        if (lane == 0 && (m[0] | m[1] | m[2] | m[3]))
           *reinterpret_cast<uint4*>(bitmap + ((size_t)(t - 1) * strips + strip) * 4) = make_uint4(m[0], m[1], m[2], m[3]);
-          my_count += __popc(m[0]) + __popc(m[1]) + __popc(m[2]) + __popc(m[3]);
-        }
-#pragma unroll
-        for (int j = 0; j < 4; ++j) { hm_prev[j] = hm_cur[j]; hm_cur[j] = hm_next[j]; cur[j] = nx[j]; }
+      };
+
+      const float* rowp = colp + (size_t)t0 * Wp;
+#pragma unroll 4
+      for (int t = t0; t < t1; ++t, rowp += Wp) {
+        const float4 q = *reinterpret_cast<const float4*>(rowp);
+        const float mx = fmaxf(fmaxf(q.x, q.y), fmaxf(q.z, q.w));
+        if (__any_sync(0xffffffffu, mx >= th_lane)) full_test(t);
       }
     }
-    if (lane == 0 && my_count) atomicAdd(&sh.ncand, my_count);
   }
   __syncthreads();
 
   // ---- candidates -> keys -----------------------------------------------------------------------
-  const int n_words = nrows * strips * 4;
   // calls f(key, word index, bit) for every candidate bit owned by this thread
   auto for_each_candidate = [&](auto f) {
     for (int w = tid; w < n_words; w += kDecThreads) {
       uint32_t bits = bitmap[w];
-      const int j = w & 3, strip = (w >> 2) % strips, t = (w >> 2) / strips;     // tile row t+1
+      if (!bits) continue;
+      const int j = w & 3, rs = w >> 2;
+      const int t = (int)div_strips.div((uint32_t)rs), strip = rs - t * strips;   // tile row t+1
       while (bits) {
         const int ln = __ffs(bits) - 1;
         bits &= bits - 1;
@@ -350,6 +341,14 @@ decode_peaks_kernel(const float* __restrict__ heat, int B, int C, int H, int W, 
       }
     }
   };
+  {
+    int cnt = 0;
+    for (int w = tid; w < n_words; w += kDecThreads) cnt += __popc(bitmap[w]);
+    cnt = warp_sum(cnt);
+    if (lane == 0 && cnt) atomicAdd(&sh.ncand, cnt);
+  }
+  __syncthreads();
+  if (sh.ncand == 0) return;                             // CTA-uniform: nothing in this tile
 
   bool counted = false;                                  // have this CTA's candidates been RED-ed?
   if (sh.ncand > cap) {
@@ -398,22 +397,18 @@ decode_peaks_kernel(const float* __restrict__ heat, int B, int C, int H, int W, 
 
   // ---- publish / pick up the image bound, emit --------------------------------------------------
   // CTAs that started without a bound (the first of their image) or still hold many keys derive a
-  // new bound from the histogram; the others just read the published one.
+  // new bound from the histogram; the others just emit.
+  u64 th = sh.thresh;
   if (!had_bound || n > K / 2 + 32) {
     __threadfence();
     refresh_bound(ghist, hdr, &sh, K);
-  } else {
-    if (tid == 0) {
-      const unsigned int g = *((volatile unsigned int*)&hdr->thr_ord);
-      if (g) { const u64 t = ((u64)g << 32) - 1ull; if (t > sh.thresh) sh.thresh = t; }
-    }
-    __syncthreads();
+    th = sh.thresh;
   }
   {
-    const u64 th = sh.thresh;
     int mine = 0;
     for (int i = tid; i < n; i += kDecThreads) mine += (buf[i] > th);
     mine = warp_sum(mine);
+    __syncthreads();
     if (tid == 0) sh.count = 0;
     __syncthreads();
     if (lane == 0 && mine) atomicAdd(&sh.count, mine);
@@ -542,15 +537,17 @@ decode_finalize_kernel(DecodeHeader* __restrict__ hdrs, unsigned int* __restrict
 }
 
 struct DecodePlan {
-  int band_rows, bands, tiles_per_image, Wp;
+  int band_rows, bands, tiles_per_image, Wp, strips, sub_rows;
   size_t smem, keys_per_image, header_bytes, hist_bytes, total_bytes;
 };
 
 static DecodePlan make_plan(int B, int C, int H, int W, int K) {
   DecodePlan p;
   p.Wp = (W + 3) / 4 * 4;                       // shared-memory row stride (floats)
-  // band = as many rows as fit ~32 KB of shared memory, at least 8; enough CTAs to fill the machine
-  int rows = (32 * 1024) / (p.Wp * 4);
+  // band = as many rows as fit ~16 KB of shared memory, at least 8; enough CTAs to fill the machine
+  static int band_kb = 0;                       // tuning knob: CTDET_DECODE_BAND_KB (default 16: measured best of 8/16/32/64 on B200)
+  if (band_kb == 0) { const char* e = getenv("CTDET_DECODE_BAND_KB"); band_kb = e ? atoi(e) : 16; if (band_kb < 1) band_kb = 16; }
+  int rows = (band_kb * 1024) / (p.Wp * 4);
   if (rows < 8) rows = 8;
   if (rows > H) rows = H;
   while ((long long)B * C * ((H + rows - 1) / rows) < 4LL * kNumSMs && rows > 8) rows = (rows + 1) / 2;
@@ -559,6 +556,9 @@ static DecodePlan make_plan(int B, int C, int H, int W, int K) {
   p.tiles_per_image = C * p.bands;
   const int cap = (K + kKeepSlack + 1) & ~1;
   const int strips = (p.Wp + 127) / 128;
+  p.strips = strips;
+  int subs = kDecWarps / strips; if (subs < 1) subs = 1;
+  p.sub_rows = (rows + subs - 1) / subs;           // rows of a band walked by one warp
   p.smem = (size_t)(rows + 2) * p.Wp * sizeof(float) + (size_t)cap * sizeof(u64) +
            (size_t)rows * strips * 4 * sizeof(uint32_t);
   p.keys_per_image = (size_t)p.tiles_per_image * cap;
@@ -603,8 +603,10 @@ extern "C" int ctdet_decode(const float* heat, const float* wh, const float* reg
   DecodeHeader* hdr = reinterpret_cast<DecodeHeader*>(base);
   unsigned int* ghist = reinterpret_cast<unsigned int*>(base + p.header_bytes);
   u64* keys = reinterpret_cast<u64*>(base + p.header_bytes + p.hist_bytes);
-  decode_peaks_kernel<<<B * p.tiles_per_image, kDecThreads, p.smem, st>>>(
-      heat, B, C, H, W, p.Wp, K, p.band_rows, p.bands, flags, hdr, ghist, keys, p.keys_per_image);
+  if (B > 65535 || C > 65535) return CTDET_EINVAL;
+  decode_peaks_kernel<<<dim3(p.bands, B, C), kDecThreads, p.smem, st>>>(
+      heat, C, H, W, p.Wp, K, p.band_rows, p.sub_rows, FastDiv((uint32_t)p.strips), flags, hdr, ghist, keys,
+      p.keys_per_image);
   int rc = check_launch();
   if (rc) return rc;
   decode_finalize_kernel<<<B, kFinThreads, 0, st>>>(hdr, ghist, keys, p.keys_per_image, wh, reg, C, H, W,
