@@ -479,20 +479,35 @@ decode_finalize_kernel(DecodeHeader* __restrict__ hdrs, unsigned int* __restrict
   }
   __syncthreads();
   if (n < K) n = K;
-  // bitonic sort, descending, padded to a power of two with zeros; the first K are the answer
-  int P = 1; while (P < n) P <<= 1;
-  for (int i = n + tid; i < P; i += kFinThreads) s_sel[i] = 0ull;
-  __syncthreads();
-  for (int size = 2; size <= P; size <<= 1) {
-    for (int stride = size >> 1; stride > 0; stride >>= 1) {
-      for (int i = tid; i < P / 2; i += kFinThreads) {
-        const int lo = (i / stride) * 2 * stride + (i % stride);
-        const int hi = lo + stride;
-        const bool desc = ((lo & size) == 0);
-        const u64 a = s_sel[lo], bb = s_sel[hi];
-        if (desc ? (a < bb) : (a > bb)) { s_sel[lo] = bb; s_sel[hi] = a; }
+  if (n <= kFinThreads) {
+    // rank sort: keys are distinct, so rank = number of larger keys; one key per thread, the
+    // compares read shared memory as broadcasts.  No barriers inside (a bitonic network of this
+    // size costs ~36 __syncthreads).
+    u64 mine = 0ull; int rank = K;
+    if (tid < n) {
+      mine = s_sel[tid];
+      rank = 0;
+      for (int j2 = 0; j2 < n; ++j2) rank += (s_sel[j2] > mine);
+    }
+    __syncthreads();
+    if (rank < K) s_sel[rank] = mine;
+    __syncthreads();
+  } else {
+    // bitonic sort, descending, padded to a power of two with zeros; the first K are the answer
+    int P = 1; while (P < n) P <<= 1;
+    for (int i = n + tid; i < P; i += kFinThreads) s_sel[i] = 0ull;
+    __syncthreads();
+    for (int size = 2; size <= P; size <<= 1) {
+      for (int stride = size >> 1; stride > 0; stride >>= 1) {
+        for (int i = tid; i < P / 2; i += kFinThreads) {
+          const int lo = (i / stride) * 2 * stride + (i % stride);
+          const int hi = lo + stride;
+          const bool desc = ((lo & size) == 0);
+          const u64 a = s_sel[lo], bb = s_sel[hi];
+          if (desc ? (a < bb) : (a > bb)) { s_sel[lo] = bb; s_sel[hi] = a; }
+        }
+        __syncthreads();
       }
-      __syncthreads();
     }
   }
   for (int k = tid; k < K; k += kFinThreads) {

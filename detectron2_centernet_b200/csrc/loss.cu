@@ -19,7 +19,7 @@ constexpr int kLossThreads = 256;
 constexpr int kUnroll = 4;         // float4 chunks in flight per thread (x and gt: 8 x LDG.128)
 
 struct LossWs {                    // must be zero on entry; left zero on exit
-  double pos_sum, neg_sum, wh_sum, off_sum;
+  double pos_sum, neg_sum, wh_sum, off_sum;   // pos_sum: weighted focal loss; neg_sum: unused
   unsigned long long npos_count;   // counted positives (pre-pass), when no normaliser is given
   unsigned int done;
   float nmask;                     // sum(reg_mask), published by RegL1 CTA 0 for the finaliser
@@ -37,47 +37,119 @@ count_pos_kernel(const float* __restrict__ gt, size_t n4, LossWs* ws) {
   if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(&ws->npos_count, (unsigned long long)cnt);
 }
 
-// One heatmap cell.  Follows the reference's fp32 evaluation order (:350-357): pred =
-// clamp(sigmoid(x)); log(pred)*(1-pred)^2 for positives, log(1-pred)*pred^2*(1-gt)^4 for
-// negatives.  Returns d(term)/dx (zero where the clamp is active: torch.clamp passes gradient only
-// for 1e-4 <= p <= 1-1e-4) and accumulates the un-normalised loss terms in pos/neg.
-// Instruction budget: the sweep has ~60 issue slots per cell at the HBM roofline, so the sigmoid
-// uses the MUFU paths (ex2.approx / rcp.approx: <= 1e-6 relative on p over the unclamped range
-// |x| <= 9.3, measured against torch in the tests); log(1-p) stays the accurate logf because its
-// value can be as small as 1e-4 and needs relative, not absolute, accuracy.
+// ---- packed fp32 (Blackwell FFMA2 / FMUL2 / FADD2: two IEEE fp32 lanes per issue slot) ----------
+// The sweep is issue-bound, not HBM-bound, when written with scalar fp32 (~70 instructions per
+// cell measured); the arithmetic below runs on float2 pairs so that every add/mul/fma covers two
+// cells.  Rounding per lane is identical to the scalar instructions.
+typedef unsigned long long pk2;                      // two fp32 lanes in one 64-bit register
+__device__ __forceinline__ pk2 pack2(float a, float b) { pk2 r; asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ void unpack2(pk2 v, float& a, float& b) { asm("mov.b64 {%0,%1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+__device__ __forceinline__ pk2 bcast2(float a) { return pack2(a, a); }
+__device__ __forceinline__ pk2 add2(pk2 a, pk2 b) { pk2 r; asm("add.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ pk2 sub2(pk2 a, pk2 b) { pk2 r; asm("sub.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ pk2 mul2(pk2 a, pk2 b) { pk2 r; asm("mul.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ pk2 fma2(pk2 a, pk2 b, pk2 c) { pk2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+
 __device__ __forceinline__ float rcp_approx(float a) {
   float r;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a));
   return r;
 }
+__device__ __forceinline__ float exp2f_approx(float a) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a));
+  return r;
+}
+__device__ __forceinline__ pk2 rcp2(pk2 v) { float a, b; unpack2(v, a, b); return pack2(rcp_approx(a), rcp_approx(b)); }
 
+// ln(a) for a in (0, 1], ~2e-7 relative everywhere (the loss needs RELATIVE accuracy: ln(1-p) is as
+// small as 1e-4).  Near 1 (a >= 0.75): ln(a) = 2 atanh(s), s = (a-1)/(a+1), |s| <= 1/7, odd series
+// to s^7 (truncation 3e-9); a-1 is exact (Sterbenz).  Elsewhere: MUFU lg2 (2^-22 absolute in
+// (0.5,2), 2^-22 relative outside) on |ln a| > 0.28.  Branch-free.
+__device__ __forceinline__ float log_unit(float a) {
+  const float s = (a - 1.f) * rcp_approx(a + 1.f);
+  const float s2 = s * s;
+  float poly = fmaf(s2, 1.f / 7.f, 1.f / 5.f);
+  poly = fmaf(poly, s2, 1.f / 3.f);
+  poly = fmaf(poly, s2, 1.f);
+  const float near1 = (s + s) * poly;
+  const float far = __log2f(a) * 0.693147180559945309f;
+  return a >= 0.75f ? near1 : far;
+}
+__device__ __forceinline__ pk2 log_unit2(pk2 a) {
+  const pk2 one = bcast2(1.f);
+  const pk2 s = mul2(sub2(a, one), rcp2(add2(a, one)));
+  const pk2 s2 = mul2(s, s);
+  pk2 poly = fma2(s2, bcast2(1.f / 7.f), bcast2(1.f / 5.f));
+  poly = fma2(poly, s2, bcast2(1.f / 3.f));
+  poly = fma2(poly, s2, one);
+  const pk2 near1 = mul2(add2(s, s), poly);
+  float a0, a1, n0, n1;
+  unpack2(a, a0, a1);
+  const pk2 far = mul2(pack2(__log2f(a0), __log2f(a1)), bcast2(0.693147180559945309f));
+  float f0, f1;
+  unpack2(near1, n0, n1); unpack2(far, f0, f1);
+  return pack2(a0 >= 0.75f ? n0 : f0, a1 >= 0.75f ? n1 : f1);
+}
+
+// Two heatmap cells.  Follows the reference's fp32 evaluation order (:350-357): pred =
+// clamp(sigmoid(x)); log(1-pred)*pred^2*(1-gt)^4 for negatives, log(pred)*(1-pred)^2*alpha for
+// positives; everything is pre-multiplied by gscale = -w_hm/num_pos (:365-368), so `tot`
+// accumulates the final weighted loss directly and the return value is d(loss)/dx (zero where the
+// clamp is active: torch.clamp passes gradient only for 1e-4 <= p <= 1-1e-4).
+// The packed path evaluates the NEGATIVE formula for both lanes -- for a positive cell
+// (1-gt)^4 = 0 makes it contribute exactly 0 -- and the rare positives (~1 cell in 30,000) add
+// their term in a scalar fix-up branch.
+// The sigmoid uses the MUFU paths (ex2.approx / rcp.approx: <= 1e-6 relative on p over the
+// unclamped range |x| <= 9.3, checked against torch in the tests).
 template <bool kProb>
-__device__ __forceinline__ float cell(float x, float g, float alpha, float& pos, float& neg) {
-  float pc, dsig;
+__device__ __forceinline__ pk2 cell2(float x0, float x1, float g0, float g1, float alpha, float gscale,
+                                     pk2& tot, float& tot_pos) {
+  const pk2 one = bcast2(1.f);
+  float p0, p1, pc0, pc1, ds0, ds1;
+  pk2 pc, om, dsig;
   if (kProb) {                                       // x already is pred (FocalLoss drop-in, :323)
-    pc = x; dsig = 1.f;
+    pc0 = x0; pc1 = x1;
+    pc = pack2(x0, x1);
+    om = sub2(one, pc);
+    dsig = one;
   } else {
-    const float p = rcp_approx(1.f + __expf(-x));    // sigmoid
-    pc = fminf(fmaxf(p, 1e-4f), 1.f - 1e-4f);
-    dsig = (pc == p) ? p * (1.f - p) : 0.f;          // d clamp(sigmoid(x)) / dx
+    float e0, e1;
+    unpack2(mul2(pack2(x0, x1), bcast2(-1.4426950408889634f)), e0, e1);
+    const pk2 den = add2(pack2(exp2f_approx(e0), exp2f_approx(e1)), one);
+    unpack2(rcp2(den), p0, p1);                       // sigmoid
+    pc0 = fminf(fmaxf(p0, 1e-4f), 1.f - 1e-4f);
+    pc1 = fminf(fmaxf(p1, 1e-4f), 1.f - 1e-4f);
+    pc = pack2(pc0, pc1);
+    om = sub2(one, pc);
+    unpack2(mul2(pc, om), ds0, ds1);                  // p(1-p) where the clamp is inactive (pc == p)
+    dsig = pack2(pc0 == p0 ? ds0 : 0.f, pc1 == p1 ? ds1 : 0.f);
   }
-  const float om = 1.f - pc;
-  // Branch-free over the (rare) positives: with A = the factor that is squared and L = the log's
-  // argument, term = coef * log(L) * A^2 and d(term)/dp = sgn * coef * (2 A log(L) - A^2 / L):
-  //   negatives: A = p,   L = 1-p, coef = (1-g)^4, sgn = +1      (:355)
-  //   positives: A = 1-p, L = p,   coef = alpha,   sgn = -1      (:354, :361)
-  const bool is_pos = (g == 1.f);
-  const float w = (1.f - g) * (1.f - g);
-  const float A = is_pos ? om : pc;
-  const float Lg = is_pos ? pc : om;
-  const float coef = is_pos ? alpha : w * w;
-  const float l = logf(Lg);                           // accurate: can be as small as 1e-4
-  const float aa = A * A;
-  const float term = coef * (l * aa);
-  if (is_pos) pos += term; else neg += term;
-  float dterm = coef * ((A + A) * l - aa * rcp_approx(Lg));
-  dterm = is_pos ? -dterm : dterm;
-  return dterm * dsig;
+  const pk2 w = sub2(one, pack2(g0, g1));
+  const pk2 w2 = mul2(w, w);
+  const pk2 coef = mul2(mul2(w2, w2), bcast2(gscale));         // (1-g)^4 * gscale
+  const pk2 l = log_unit2(om);
+  const pk2 aa = mul2(pc, pc);
+  tot = fma2(coef, mul2(l, aa), tot);                          // log(1-p) p^2 (1-g)^4
+  // d/dp [log(1-p) p^2] = 2 p log(1-p) - p^2 / (1-p)
+  const pk2 dterm = sub2(mul2(add2(pc, pc), l), mul2(aa, rcp2(om)));
+  pk2 d = mul2(mul2(coef, dterm), dsig);
+  if (g0 == 1.f || g1 == 1.f) {                                // rare
+    float d0, d1, dsa, dsb, oma, omb;
+    unpack2(d, d0, d1); unpack2(dsig, dsa, dsb); unpack2(om, oma, omb);
+    if (g0 == 1.f) {
+      const float lp = log_unit(pc0);
+      tot_pos += gscale * alpha * (lp * (oma * oma));
+      d0 = gscale * alpha * (oma * oma * rcp_approx(pc0) - 2.f * oma * lp) * dsa;   // d/dp [log p (1-p)^2]
+    }
+    if (g1 == 1.f) {
+      const float lp = log_unit(pc1);
+      tot_pos += gscale * alpha * (lp * (omb * omb));
+      d1 = gscale * alpha * (omb * omb * rcp_approx(pc1) - 2.f * omb * lp) * dsb;
+    }
+    d = pack2(d0, d1);
+  }
+  return d;
 }
 
 template <bool kProb>
@@ -167,23 +239,26 @@ loss_kernel(const float* __restrict__ hm, const float* __restrict__ wh, const fl
         const size_t j = i + u * stride;
         if (j < n4) { x[u] = ldg_stream4(hm + 4 * j); g[u] = ldg_stream4(gt + 4 * j); }
       }
-      float pos = 0.f, neg = 0.f;
+      pk2 tot = bcast2(0.f);
+      float tot_pos = 0.f;
 #pragma unroll
       for (int u = 0; u < kUnroll; ++u) {
         const size_t j = i + u * stride;
         if (j < n4) {
           const uint32_t plane = div_hw4.div((uint32_t)j);           // b*C + c
           const float al = __ldg(alpha + (plane - div_c.div(plane) * (uint32_t)C));
-          float4 d;
-          d.x = gscale * cell<kProb>(x[u].x, g[u].x, al, pos, neg);
-          d.y = gscale * cell<kProb>(x[u].y, g[u].y, al, pos, neg);
-          d.z = gscale * cell<kProb>(x[u].z, g[u].z, al, pos, neg);
-          d.w = gscale * cell<kProb>(x[u].w, g[u].w, al, pos, neg);
-          if (d_hm != nullptr) stg_stream4(d_hm + 4 * j, d);
+          const pk2 d01 = cell2<kProb>(x[u].x, x[u].y, g[u].x, g[u].y, al, gscale, tot, tot_pos);
+          const pk2 d23 = cell2<kProb>(x[u].z, x[u].w, g[u].z, g[u].w, al, gscale, tot, tot_pos);
+          if (d_hm != nullptr) {
+            float4 d;
+            unpack2(d01, d.x, d.y); unpack2(d23, d.z, d.w);
+            stg_stream4(d_hm + 4 * j, d);
+          }
         }
       }
-      acc0 += (double)pos;
-      acc1 += (double)neg;
+      float t0, t1;
+      unpack2(tot, t0, t1);
+      acc0 += (double)(t0 + t1) + (double)tot_pos;   // already scaled by gscale = -w_hm/num_pos
     }
   }
 
@@ -199,8 +274,7 @@ loss_kernel(const float* __restrict__ hm, const float* __restrict__ wh, const fl
       atomicAdd((blockIdx.x & 1) ? &ws->off_sum : &ws->wh_sum, a0);
       if (blockIdx.x == 0) ws->nmask = s_norm[1];
     } else {
-      if (a0 != 0.0) atomicAdd(&ws->pos_sum, a0);
-      atomicAdd(&ws->neg_sum, a1);
+      atomicAdd(&ws->pos_sum, a0);                  // focal: the weighted loss itself
     }
     __threadfence();
     s_last = (atomicAdd(&ws->done, 1u) == gridDim.x - 1);
@@ -208,13 +282,11 @@ loss_kernel(const float* __restrict__ hm, const float* __restrict__ wh, const fl
   __syncthreads();
   if (s_last && tid == 0) {
     __threadfence();
-    const double pos = *((volatile double*)&ws->pos_sum), neg = *((volatile double*)&ws->neg_sum);
+    const double focal = *((volatile double*)&ws->pos_sum);
     const double whs = *((volatile double*)&ws->wh_sum), offs = *((volatile double*)&ws->off_sum);
-    const float npos = s_norm[0];
     const float nmask = *((volatile float*)&ws->nmask);
     const float denom = 2.f * nmask + 1e-4f;
-    const float hm_loss = (npos == 0.f) ? (float)(-neg) : (float)(-(pos + neg) / (double)npos);
-    losses[0] = hm_loss * w_hm;
+    losses[0] = (float)focal;                        // = -(pos+neg)/num_pos * w_hm  (or -neg * w_hm)
     losses[1] = ((float)whs / denom) * w_wh;
     losses[2] = ((float)offs / denom) * w_off;
     ws->pos_sum = 0.0; ws->neg_sum = 0.0; ws->wh_sum = 0.0; ws->off_sum = 0.0;
