@@ -16,7 +16,7 @@
 namespace ctdet {
 
 constexpr int kLossThreads = 256;
-constexpr int kUnroll = 4;         // float4 chunks in flight per thread (x and gt: 8 x LDG.128)
+constexpr int kUnroll = 2;         // float4 chunks per thread per iteration (x and gt), double-buffered
 
 struct LossWs {                    // must be zero on entry; left zero on exit
   double pos_sum, neg_sum, wh_sum, off_sum;   // pos_sum: weighted focal loss; neg_sum: unused
@@ -55,6 +55,11 @@ __device__ __forceinline__ float rcp_approx(float a) {
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a));
   return r;
 }
+__device__ __forceinline__ float lg2_approx(float a) {
+  float r;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a));
+  return r;
+}
 __device__ __forceinline__ float exp2f_approx(float a) {
   float r;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a));
@@ -73,7 +78,7 @@ __device__ __forceinline__ float log_unit(float a) {
   poly = fmaf(poly, s2, 1.f / 3.f);
   poly = fmaf(poly, s2, 1.f);
   const float near1 = (s + s) * poly;
-  const float far = __log2f(a) * 0.693147180559945309f;
+  const float far = lg2_approx(a) * 0.693147180559945309f;
   return a >= 0.75f ? near1 : far;
 }
 __device__ __forceinline__ pk2 log_unit2(pk2 a) {
@@ -86,7 +91,7 @@ __device__ __forceinline__ pk2 log_unit2(pk2 a) {
   const pk2 near1 = mul2(add2(s, s), poly);
   float a0, a1, n0, n1;
   unpack2(a, a0, a1);
-  const pk2 far = mul2(pack2(__log2f(a0), __log2f(a1)), bcast2(0.693147180559945309f));
+  const pk2 far = mul2(pack2(lg2_approx(a0), lg2_approx(a1)), bcast2(0.693147180559945309f));
   float f0, f1;
   unpack2(near1, n0, n1); unpack2(far, f0, f1);
   return pack2(a0 >= 0.75f ? n0 : f0, a1 >= 0.75f ? n1 : f1);
@@ -159,7 +164,7 @@ loss_kernel(const float* __restrict__ hm, const float* __restrict__ wh, const fl
             const int64_t* __restrict__ ind, const float* __restrict__ gt_wh,
             const float* __restrict__ gt_reg, const float* __restrict__ alpha,
             const int32_t* __restrict__ num_pos_img, const float* __restrict__ norm_override,
-            int B, int C, int HW, int M, int n_reg_ctas, FastDiv div_hw4, FastDiv div_c,
+            int B, int C, int HW, int M, int flags, int n_reg_ctas, FastDiv div_hw4, FastDiv div_c,
             float w_hm, float w_wh, float w_off, float* __restrict__ losses, float* __restrict__ d_hm, float* __restrict__ d_wh,
             float* __restrict__ d_reg, LossWs* ws) {
   __shared__ float s_norm[2];
@@ -232,12 +237,21 @@ loss_kernel(const float* __restrict__ hm, const float* __restrict__ wh, const fl
     const size_t n4 = (size_t)B * C * HW / 4;      // < 2^31 (checked on the host)
     const size_t stride = (size_t)(gridDim.x - n_reg_ctas) * kLossThreads;
     size_t i = (size_t)(blockIdx.x - n_reg_ctas) * kLossThreads + tid;
+    const bool uniform_alpha = flags & CTDET_LOSS_ALPHA_UNIFORM;
+    const float alpha0 = __ldg(alpha);
+    // software pipeline: the loads of iteration k+1 are in flight while iteration k computes
+    float4 x[kUnroll], g[kUnroll], xn[kUnroll], gn[kUnroll];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const size_t j = i + u * stride;
+      if (j < n4) { x[u] = ldg_stream4(hm + 4 * j); g[u] = ldg_stream4(gt + 4 * j); }
+    }
     for (; i < n4; i += stride * kUnroll) {
-      float4 x[kUnroll], g[kUnroll];
+      const size_t inext = i + stride * kUnroll;
 #pragma unroll
       for (int u = 0; u < kUnroll; ++u) {
-        const size_t j = i + u * stride;
-        if (j < n4) { x[u] = ldg_stream4(hm + 4 * j); g[u] = ldg_stream4(gt + 4 * j); }
+        const size_t j = inext + u * stride;
+        if (j < n4) { xn[u] = ldg_stream4(hm + 4 * j); gn[u] = ldg_stream4(gt + 4 * j); }
       }
       pk2 tot = bcast2(0.f);
       float tot_pos = 0.f;
@@ -245,8 +259,11 @@ loss_kernel(const float* __restrict__ hm, const float* __restrict__ wh, const fl
       for (int u = 0; u < kUnroll; ++u) {
         const size_t j = i + u * stride;
         if (j < n4) {
-          const uint32_t plane = div_hw4.div((uint32_t)j);           // b*C + c
-          const float al = __ldg(alpha + (plane - div_c.div(plane) * (uint32_t)C));
+          float al = alpha0;
+          if (!uniform_alpha) {
+            const uint32_t plane = div_hw4.div((uint32_t)j);         // b*C + c
+            al = __ldg(alpha + (plane - div_c.div(plane) * (uint32_t)C));
+          }
           const pk2 d01 = cell2<kProb>(x[u].x, x[u].y, g[u].x, g[u].y, al, gscale, tot, tot_pos);
           const pk2 d23 = cell2<kProb>(x[u].z, x[u].w, g[u].z, g[u].w, al, gscale, tot, tot_pos);
           if (d_hm != nullptr) {
@@ -259,6 +276,8 @@ loss_kernel(const float* __restrict__ hm, const float* __restrict__ wh, const fl
       float t0, t1;
       unpack2(tot, t0, t1);
       acc0 += (double)(t0 + t1) + (double)tot_pos;   // already scaled by gscale = -w_hm/num_pos
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) { x[u] = xn[u]; g[u] = gn[u]; }
     }
   }
 
@@ -327,7 +346,7 @@ extern "C" int ctdet_loss_fwd_bwd(const float* hm, const float* wh, const float*
                                   void* workspace, size_t workspace_bytes, ctdet_stream_t stream) {
   using namespace ctdet;
   if (B <= 0 || C <= 0 || H <= 0 || W <= 0 || M <= 0) return CTDET_EINVAL;
-  if (flags & ~CTDET_LOSS_INPUT_PROB) return CTDET_EINVAL;
+  if (flags & ~(CTDET_LOSS_INPUT_PROB | CTDET_LOSS_ALPHA_UNIFORM)) return CTDET_EINVAL;
   if (!losses || !workspace) return CTDET_ENULL;
   if (hm && (!gt_hm || !alpha)) return CTDET_ENULL;
   if ((wh || reg) && (!reg_mask || !ind)) return CTDET_ENULL;
@@ -365,7 +384,7 @@ extern "C" int ctdet_loss_fwd_bwd(const float* hm, const float* wh, const float*
   auto kern = (flags & CTDET_LOSS_INPUT_PROB) ? loss_kernel<true> : loss_kernel<false>;
   kern<<<n_reg + sweep, kLossThreads, 0, st>>>(
       hm, wh, reg, gt_hm, reg_mask, ind, gt_wh, gt_reg, alpha, num_pos_img, norm_override,
-      B, C, (int)HW, M, n_reg, FastDiv((uint32_t)(HW / 4)), FastDiv((uint32_t)C), w_hm, w_wh, w_off,
+      B, C, (int)HW, M, flags, n_reg, FastDiv((uint32_t)(HW / 4)), FastDiv((uint32_t)C), w_hm, w_wh, w_off,
       losses, d_hm, d_wh, d_reg, ws);
   return check_launch();
 }

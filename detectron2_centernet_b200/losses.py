@@ -10,11 +10,36 @@ import torch.nn as nn
 from . import _lib
 
 _FLAG_PROB = 1
+_FLAG_ALPHA_UNIFORM = 2
+
+
+_alpha_cache = {}
+
+
+def alpha_is_uniform(alpha):
+    """True when every class shares one alpha (None, a scalar, or a 1-element list)."""
+    if alpha is None or isinstance(alpha, (int, float)):
+        return True
+    if isinstance(alpha, torch.Tensor):
+        return alpha.numel() == 1
+    return len(alpha) == 1
 
 
 def alpha_tensor(alpha, num_classes, device):
     """alpha handling of _neg_loss (centernet.py:341-349) -> f32[C] on `device`.  Unlike the
-    reference the caller's list is not mutated (`alpha.extend` at :348)."""
+    reference the caller's list is not mutated (`alpha.extend` at :348) and the tensor is built and
+    copied to the device once per distinct value (the reference does an H2D copy every call)."""
+    if not isinstance(alpha, torch.Tensor):
+        key = (None if alpha is None else (tuple(alpha) if isinstance(alpha, (list, tuple)) else float(alpha)),
+               num_classes, str(device))
+        hit = _alpha_cache.get(key)
+        if hit is None:
+            hit = _alpha_cache[key] = _alpha_tensor(alpha, num_classes, device)
+        return hit
+    return _alpha_tensor(alpha, num_classes, device)
+
+
+def _alpha_tensor(alpha, num_classes, device):
     if isinstance(alpha, torch.Tensor):
         a = alpha.to(device=device, dtype=torch.float32).reshape(-1)
         if a.numel() == 1:
@@ -120,7 +145,8 @@ def ctdet_losses(outputs, targets, alpha=None, weights=(1.0, 0.1, 1.0), norm=Non
     a = alpha_tensor(alpha, hm.shape[1], hm.device)
     out = _FusedLoss.apply(hm, wh, reg, gt_hm, targets["reg_mask"].contiguous(),
                            targets["ind"].contiguous(), _prep(targets["wh"], "gt wh"),
-                           _prep(targets["reg"], "gt reg"), a, targets.get("num_pos"), norm, 0,
+                           _prep(targets["reg"], "gt reg"), a, targets.get("num_pos"), norm,
+                           _FLAG_ALPHA_UNIFORM if alpha_is_uniform(alpha) else 0,
                            tuple(float(w) for w in weights))
     return {"hm_loss": out[0], "wh_loss": out[1], "off_loss": out[2]}
 
@@ -131,7 +157,8 @@ def _neg_loss(pred, gt, alpha=None, num_pos=None):
     gt = _prep(gt, "_neg_loss")
     a = alpha_tensor(alpha, pred.shape[1], pred.device)
     out = _FusedLoss.apply(pred, None, None, gt, None, None, None, None, a, num_pos, None,
-                           _FLAG_PROB, (1.0, 0.0, 0.0))
+                           _FLAG_PROB | (_FLAG_ALPHA_UNIFORM if alpha_is_uniform(alpha) else 0),
+                           (1.0, 0.0, 0.0))
     return out[0]
 
 

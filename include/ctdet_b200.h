@@ -87,6 +87,7 @@ int ctdet_target_gen(const float* boxes, const int64_t* classes, const int32_t* 
  * use; every call leaves it zero-filled again.  Not re-entrant on two streams with the same
  * workspace. */
 #define CTDET_LOSS_INPUT_PROB 1
+#define CTDET_LOSS_ALPHA_UNIFORM 2 /* every class uses alpha[0] (skips the per-class lookup) */
 size_t ctdet_loss_workspace_bytes(void);
 int ctdet_loss_fwd_bwd(const float* hm, const float* wh, const float* reg,
                        const float* gt_hm, const uint8_t* reg_mask, const int64_t* ind,

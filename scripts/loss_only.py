@@ -14,7 +14,7 @@ gt = T.target_gen(tb, tc, to, B, C, H, W)
 alpha = L.alpha_tensor([1.0], C, dev)
 flush = torch.empty(512 * 1024 * 1024 // 4, device=dev)
 def run():
-    return L._call(hm, wh, reg, gt["hm"], gt["reg_mask"], gt["ind"], gt["wh"], gt["reg"], alpha, gt["num_pos"], None, 0, (1.0, 0.1, 1.0), True)
+    return L._call(hm, wh, reg, gt["hm"], gt["reg_mask"], gt["ind"], gt["wh"], gt["reg"], alpha, gt["num_pos"], None, 2, (1.0, 0.1, 1.0), True)
 for _ in range(3): run()
 ts = []
 for _ in range(int(sys.argv[1]) if len(sys.argv) > 1 else 20):
