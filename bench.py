@@ -45,33 +45,41 @@ def peaks():
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks + throttle reasons sampled DURING the timed region."""
-    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock + throttle reasons sampled through NVML every 5 ms DURING the timed regions."""
 
     def __init__(self, index):
         super().__init__(daemon=True)
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.sm, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop_evt = threading.Event()
+        self.ready = threading.Event()
 
     def run(self):
         try:
-            self.proc = subprocess.Popen(
-                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
-                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            for line in self.proc.stdout:
-                self.rows.append([x.strip() for x in line.split(",")])
-        except Exception:
-            pass
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            names = {"hw_slowdown": nv.nvmlClocksThrottleReasonHwSlowdown,
+                     "hw_thermal_slowdown": nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+                     "sw_thermal_slowdown": nv.nvmlClocksThrottleReasonSwThermalSlowdown,
+                     "sw_power_cap": nv.nvmlClocksThrottleReasonSwPowerCap}
+            while not self._stop_evt.is_set():
+                self.sm.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                for n, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(n)
+                self.ready.set()
+                time.sleep(0.005)
+        except Exception as e:                                  # NVML missing: report it, do not fake
+            self.reasons.add("nvml_unavailable:%s" % type(e).__name__)
+            self.ready.set()
 
     def stop(self):
-        if self.proc is not None:
-            self.proc.terminate()
-        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({n for r in self.rows if len(r) >= 6 for n, v in zip(names, r[2:6]) if v == "Active"})
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+        self._stop_evt.set()
+        self.join(timeout=2)
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.sm)}
 
 
 # ----------------------------------------------------------------------------------------------
@@ -118,8 +126,25 @@ def run_ours(args):
 
     LAUNCHES_PER_STEP = 4      # target_gen, loss, decode_peaks, decode_finalize
 
+    # The device-resident step is captured ONCE into a CUDA graph (4 kernel nodes) and replayed:
+    # the kernels take 30-100 us each, so per-call Python/ctypes overhead would otherwise show up
+    # as idle gaps on the stream.
+    for _ in range(2):
+        hot_path(d_hm, d_wh, d_reg, d_boxes, d_classes, d_offsets)          # warm caches / workspaces
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    cap_stream = torch.cuda.Stream()
+    with torch.cuda.stream(cap_stream):
+        # workspaces are keyed by stream: create them on the capture stream before capturing
+        hot_path(d_hm, d_wh, d_reg, d_boxes, d_classes, d_offsets)
+        cap_stream.synchronize()
+        with torch.cuda.graph(graph, stream=cap_stream):
+            graph_out = hot_path(d_hm, d_wh, d_reg, d_boxes, d_classes, d_offsets)
+    torch.cuda.synchronize()
+
     def step_device():
-        return hot_path(d_hm, d_wh, d_reg, d_boxes, d_classes, d_offsets)
+        graph.replay()
+        return graph_out
 
     def step_e2e():
         hm = h_hm.to(dev, non_blocking=True)
@@ -162,8 +187,8 @@ def run_ours(args):
     sampler = ClockSampler(local) if rank == 0 else None
     if sampler:
         sampler.start()
+        sampler.ready.wait(timeout=5)
     total_ms = timed(step_device, args.steps, args.warmup, True)
-    clocks = sampler.stop() if sampler else None
 
     # dominant kernel alone (fused loss), CUDA events on the launching stream, L2 flushed
     def loss_only():
@@ -177,6 +202,7 @@ def run_ours(args):
         per_kernel[name] = {"us": round(ms * 1e3, 2),
                             "GBps": round(cells * BYTES_PER_CELL[name] / (ms * 1e-3) / 1e9, 1)}
     e2e_ms = timed(step_e2e, args.steps, args.warmup, False)
+    clocks = sampler.stop() if sampler else None               # covers every timed region above
 
     if rank != 0:
         if world > 1:
@@ -195,6 +221,7 @@ def run_ours(args):
         "data": "synthetic (seeded COCO-shaped boxes; logits ~N(-2.19,1.5^2) + planted peaks)",
         "config": {"workload": WORKLOAD, "images_per_gpu": B, "heatmap": [C, H, W], "K": K,
                    "l2": "flushed (256 MB memset) between timed iterations",
+                   "launch": "device-resident step replayed from a CUDA graph (4 kernel nodes); e2e uses plain calls",
                    "sharding": "by image, no data-path collective"},
         "clocks": clocks,
         "e2e": {"value": round(e2e_value, 1), "unit": "images/s", "h2d_bytes_per_step": h2d,
