@@ -1,0 +1,362 @@
+// DCNv2 (modulated deformable 3x3 convolution) forward as ONE implicit GEMM on the 5th-generation
+// tensor cores (tcgen05.mma, accumulators in TMEM) -- the only dense contraction of the ctdet path.
+//
+// Replaces modulated_deform_conv_cuda_forward (detectron2/layers/csrc/deformable/deform_conv_cuda.cu:
+// 804-927): per IMAGE an im2col kernel (deform_conv_cuda_kernel.cu:786-868) writes fp32
+// columns[Cin*9, H*W] to HBM, an fp32 SGEMM (at::addmm_, :904-909) reads them back, and a separate
+// elementwise pass adds the bias (:924-926).  Here the bilinear-sampled, mask-modulated im2col tile
+// only ever exists in shared memory:
+//
+//   GEMM view per 128-pixel tile:  D[128 pixels, Cout] = A[128 pixels, K = 9*Cin] * Wk[Cout, K]^T
+//   K is ordered tap-major (k = tap*Cin + ci) so a 64-wide K block shares one sampling position.
+//
+//   * pre-pass 1: x NCHW fp32 -> NHWC bf16 (a sampled corner becomes one contiguous channel vector:
+//     16-byte loads, 8 channels each; x is read ~36 times by the sampler, once by this pass)
+//   * pre-pass 2: weight [Cout,Cin,3,3] fp32 -> Wk [Cout, 9*Cin] bf16, tap-major
+//   * main kernel, one CTA (4 warps) per tile, 2-stage shared-memory pipeline:
+//       all 128 threads (thread = pixel) build the A stage: 4 corners x Cin/8 16-byte gathers,
+//       bilinear * mask blend in packed bf16x2 FMAs (or fp32 with DCN_FLAG_FP32_BLEND), 16-byte
+//       stores into the 128B-swizzled K-major layout the UMMA descriptor expects; the Wk block is
+//       copied beside it; fence.proxy.async + barrier; ONE elected thread issues 4 tcgen05.mma
+//       (M=128, N=Cout, K=16, bf16 x bf16 -> fp32 in TMEM) and a tcgen05.commit onto the stage's
+//       mbarrier, so the tensor pipe works on stage s while the SIMT sampler fills stage s^1.
+//     epilogue: tcgen05.ld (32 lanes x 16 columns per warp) -> bias (+ optional per-channel affine
+//     and ReLU: DeformConvV2.actf = BN + ReLU, deform_conv.py:501-504, folded for inference) ->
+//     coalesced NCHW fp32 stores.
+// Border rule identical to the reference: a tap samples iff h_im > -1 && w_im > -1 && h_im < H &&
+// w_im < W (:852); each bilinear corner outside the image contributes 0 (:683-693).
+#include <cuda_bf16.h>
+#include "common.cuh"
+
+namespace ctdet {
+
+constexpr int kDcnThreads = 128;      // = pixels per tile = TMEM lanes = UMMA M
+constexpr int kBK = 64;               // K block: 64 bf16 = one 128-byte swizzle row
+constexpr int kStages = 2;
+
+// ------------------------------------------------------------------------------------------------
+// pre-pass 1: NCHW fp32 -> NHWC bf16, 32x32 tiles through shared memory (coalesced both ways)
+__global__ void dcn_pack_input_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ xh,
+                                      int C, int P) {
+  __shared__ float t[32][33];
+  const int b = blockIdx.z, c0 = blockIdx.y * 32, p0 = blockIdx.x * 32;
+  const float* src = x + (size_t)b * C * P;
+  __nv_bfloat16* dst = xh + (size_t)b * P * C;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int c = c0 + i, p = p0 + threadIdx.x;
+    t[i][threadIdx.x] = (c < C && p < P) ? src[(size_t)c * P + p] : 0.f;
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int p = p0 + i, c = c0 + threadIdx.x;
+    if (p < P && c < C) dst[(size_t)p * C + c] = __float2bfloat16_rn(t[threadIdx.x][i]);
+  }
+}
+
+// pre-pass 2: weight [Cout][Cin][9] fp32 -> Wk [Cout][9][Cin] bf16
+__global__ void dcn_pack_weight_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ wk,
+                                       int Cout, int Cin) {
+  const size_t n = (size_t)Cout * Cin * 9;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int ci = (int)(i % Cin);
+    const int t = (int)((i / Cin) % 9);
+    const int co = (int)(i / ((size_t)Cin * 9));
+    wk[i] = __float2bfloat16_rn(w[((size_t)co * Cin + ci) * 9 + t]);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// tcgen05 / mbarrier plumbing (raw PTX; SASS: UTCHMMA, LDTM, UTCBAR)
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void dcn_mbar_init(uint64_t* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void dcn_mbar_wait(uint64_t* bar, unsigned parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}"
+      :: "r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t* slot, uint32_t ncols) {      // whole warp
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smem_u32(slot)), "r"(ncols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t ncols) {     // whole warp
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(addr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      :: "r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {                      // arrives when all prior MMAs retire
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {     // 32 lanes x 16 columns
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// K-major, 128-byte-swizzled operand tile (rows of 64 bf16 = 128 B, 8-row groups 1024 B apart):
+// start address >> 4 | LBO (unused for swizzled K-major, 1) | SBO = 1024 B | version 1 | SWIZZLE_128B
+__device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr) {
+  return (uint64_t)((smem_addr >> 4) & 0x3fffu) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) |
+         (1ull << 46) | (2ull << 61);
+}
+// kind::f16 instruction descriptor: D = fp32, A = B = bf16, both K-major, N>>3 at [17,23), M>>4 at [24,29)
+__device__ __forceinline__ uint32_t make_idesc_bf16(int M, int N) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// ------------------------------------------------------------------------------------------------
+struct DcnParams {
+  const __nv_bfloat16* xh;     // [B][H*W][Cin]
+  const float* offset;         // [B][18][Ho*Wo]   channel 2t = dh, 2t+1 = dw (deform_conv_cuda_kernel.cu:838-846)
+  const float* mask;           // [B][9][Ho*Wo]
+  const __nv_bfloat16* wk;     // [Cout][9*Cin]
+  const float* bias;           // [Cout] or null
+  const float* scale;          // [Cout] or null   y = (conv + bias) * scale + shift
+  const float* shift;          // [Cout] or null
+  float* y;                    // [B][Cout][Ho*Wo]
+  int Cin, H, W, Ho, Wo, Cout, stride, pad, dil, relu, tiles_per_image;
+  uint32_t tmem_cols;
+};
+
+__device__ __forceinline__ uint32_t blend_bf16x2(uint32_t a, uint32_t b, uint32_t c, uint32_t d,
+                                                 __nv_bfloat162 w1, __nv_bfloat162 w2, __nv_bfloat162 w3, __nv_bfloat162 w4) {
+  __nv_bfloat162 acc = __hmul2(w1, *reinterpret_cast<__nv_bfloat162*>(&a));
+  acc = __hfma2(w2, *reinterpret_cast<__nv_bfloat162*>(&b), acc);
+  acc = __hfma2(w3, *reinterpret_cast<__nv_bfloat162*>(&c), acc);
+  acc = __hfma2(w4, *reinterpret_cast<__nv_bfloat162*>(&d), acc);
+  return *reinterpret_cast<uint32_t*>(&acc);
+}
+__device__ __forceinline__ uint32_t blend_fp32(uint32_t a, uint32_t b, uint32_t c, uint32_t d,
+                                               float w1, float w2, float w3, float w4) {
+  const float lo = w1 * __uint_as_float(a << 16) + w2 * __uint_as_float(b << 16) +
+                   w3 * __uint_as_float(c << 16) + w4 * __uint_as_float(d << 16);
+  const float hi = w1 * __uint_as_float(a & 0xffff0000u) + w2 * __uint_as_float(b & 0xffff0000u) +
+                   w3 * __uint_as_float(c & 0xffff0000u) + w4 * __uint_as_float(d & 0xffff0000u);
+  const __nv_bfloat162 r = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<const uint32_t*>(&r);
+}
+
+template <bool kFp32Blend>
+__global__ void __launch_bounds__(kDcnThreads)
+dcn_forward_kernel(const DcnParams prm) {
+  extern __shared__ __align__(1024) uint8_t dcn_smem[];
+  __shared__ __align__(8) uint64_t s_bar[kStages];
+  __shared__ uint32_t s_tmem;
+
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int Cin = prm.Cin, Cout = prm.Cout, W = prm.W, H = prm.H;
+  const int P = prm.Ho * prm.Wo, Pin = H * W;
+  const int b = blockIdx.x / prm.tiles_per_image;
+  const int p = (blockIdx.x % prm.tiles_per_image) * kDcnThreads + tid;     // this thread's output pixel
+  const bool valid = p < P;
+  const int ho = valid ? p / prm.Wo : 0, wo = valid ? p % prm.Wo : 0;
+  const uint32_t stage_bytes = 128u * kBK * 2u + (uint32_t)Cout * kBK * 2u;  // A tile + Wk tile
+  // dynamic shared memory is only guaranteed 16-byte aligned: round up to the 1024-byte swizzle atom
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(dcn_smem) + 1023) & ~(uintptr_t)1023);
+
+  if (tid == 0) {
+    for (int s = 0; s < kStages; ++s) dcn_mbar_init(&s_bar[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) tmem_alloc(&s_tmem, prm.tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = s_tmem;
+  const uint32_t idesc = make_idesc_bf16(128, Cout);
+
+  const int cpb = Cin / kBK;                     // K blocks per tap
+  const int KB = 9 * cpb;
+  const size_t Ktot = (size_t)9 * Cin;
+  const __nv_bfloat16* xb = prm.xh + (size_t)b * Pin * Cin;
+  const float* offb = prm.offset + (size_t)b * 18 * P;
+  const float* mskb = prm.mask + (size_t)b * 9 * P;
+
+  int o1 = 0, o2 = 0, o3 = 0, o4 = 0;            // corner pixel indices (clamped into the image)
+  float w1 = 0.f, w2 = 0.f, w3 = 0.f, w4 = 0.f;  // bilinear weights * mask, 0 for corners outside
+
+  for (int kb = 0; kb < KB; ++kb) {
+    const int s = kb % kStages, use = kb / kStages;
+    if (kb >= kStages) dcn_mbar_wait(&s_bar[s], (unsigned)((use - 1) & 1));   // MMAs that read stage s retired
+    const int t = kb / cpb, ci0 = (kb - t * cpb) * kBK;
+    if (ci0 == 0) {
+      // ---- sampling geometry of tap t (dmcn_im2col_bilinear, :666-699) -----------------------------
+      w1 = w2 = w3 = w4 = 0.f; o1 = o2 = o3 = o4 = 0;
+      if (valid) {
+        const int i = t / 3, j = t - 3 * i;
+        const float h_im = (float)(ho * prm.stride - prm.pad + i * prm.dil) + offb[(size_t)(2 * t) * P + p];
+        const float w_im = (float)(wo * prm.stride - prm.pad + j * prm.dil) + offb[(size_t)(2 * t + 1) * P + p];
+        const float m = mskb[(size_t)t * P + p];
+        if (h_im > -1.f && w_im > -1.f && h_im < (float)H && w_im < (float)W) {       // :852
+          const int h_low = (int)floorf(h_im), w_low = (int)floorf(w_im);
+          const int h_high = h_low + 1, w_high = w_low + 1;
+          const float lh = h_im - (float)h_low, lw = w_im - (float)w_low;
+          const float hh = 1.f - lh, hw = 1.f - lw;
+          const bool t_ok = h_low >= 0, b_ok = h_high <= H - 1, l_ok = w_low >= 0, r_ok = w_high <= W - 1;
+          const int hl = max(h_low, 0), hh_i = min(h_high, H - 1), wl = max(w_low, 0), wh_i = min(w_high, W - 1);
+          o1 = hl * W + wl;   w1 = (t_ok && l_ok) ? hh * hw * m : 0.f;
+          o2 = hl * W + wh_i; w2 = (t_ok && r_ok) ? hh * lw * m : 0.f;
+          o3 = hh_i * W + wl; w3 = (b_ok && l_ok) ? lh * hw * m : 0.f;
+          o4 = hh_i * W + wh_i; w4 = (b_ok && r_ok) ? lh * lw * m : 0.f;
+        }
+      }
+    }
+    uint8_t* a_tile = smem + (size_t)s * stage_bytes;
+    uint8_t* b_tile = a_tile + 128 * kBK * 2;
+
+    // ---- A row of this pixel: 64 channels = 8 chunks of 16 bytes, swizzled -----------------------
+    {
+      const uint4* c1 = reinterpret_cast<const uint4*>(xb + (size_t)o1 * Cin + ci0);
+      const uint4* c2 = reinterpret_cast<const uint4*>(xb + (size_t)o2 * Cin + ci0);
+      const uint4* c3 = reinterpret_cast<const uint4*>(xb + (size_t)o3 * Cin + ci0);
+      const uint4* c4 = reinterpret_cast<const uint4*>(xb + (size_t)o4 * Cin + ci0);
+      uint8_t* arow = a_tile + tid * 128;
+      const __nv_bfloat162 q1 = __float2bfloat162_rn(w1), q2 = __float2bfloat162_rn(w2),
+                           q3 = __float2bfloat162_rn(w3), q4 = __float2bfloat162_rn(w4);
+#pragma unroll 4
+      for (int c = 0; c < 8; ++c) {
+        const uint4 a = __ldg(c1 + c), bq = __ldg(c2 + c), cq = __ldg(c3 + c), d = __ldg(c4 + c);
+        uint4 r;
+        if (kFp32Blend) {
+          r.x = blend_fp32(a.x, bq.x, cq.x, d.x, w1, w2, w3, w4);
+          r.y = blend_fp32(a.y, bq.y, cq.y, d.y, w1, w2, w3, w4);
+          r.z = blend_fp32(a.z, bq.z, cq.z, d.z, w1, w2, w3, w4);
+          r.w = blend_fp32(a.w, bq.w, cq.w, d.w, w1, w2, w3, w4);
+        } else {
+          r.x = blend_bf16x2(a.x, bq.x, cq.x, d.x, q1, q2, q3, q4);
+          r.y = blend_bf16x2(a.y, bq.y, cq.y, d.y, q1, q2, q3, q4);
+          r.z = blend_bf16x2(a.z, bq.z, cq.z, d.z, q1, q2, q3, q4);
+          r.w = blend_bf16x2(a.w, bq.w, cq.w, d.w, q1, q2, q3, q4);
+        }
+        *reinterpret_cast<uint4*>(arow + ((c ^ (tid & 7)) << 4)) = r;
+      }
+    }
+    // ---- Wk block [Cout][64], same swizzle --------------------------------------------------------
+    {
+      const __nv_bfloat16* wsrc = prm.wk + (size_t)kb * kBK;
+      for (int idx = tid; idx < Cout * 8; idx += kDcnThreads) {
+        const int n = idx >> 3, ch = idx & 7;
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(wsrc + (size_t)n * Ktot) + ch);
+        *reinterpret_cast<uint4*>(b_tile + n * 128 + ((ch ^ (n & 7)) << 4)) = v;
+      }
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> tensor core reads
+    __syncthreads();
+    if (tid == 0) {
+      tc_fence_after();
+      const uint64_t adesc = make_sw128_desc(smem_u32(a_tile));
+      const uint64_t bdesc = make_sw128_desc(smem_u32(b_tile));
+#pragma unroll
+      for (int k4 = 0; k4 < kBK / 16; ++k4)      // +32 bytes (16 bf16) along K inside the swizzle row
+        umma_bf16(tmem, adesc + 2 * k4, bdesc + 2 * k4, idesc, (uint32_t)((kb | k4) != 0));
+      umma_commit(&s_bar[s]);
+    }
+  }
+  // ---- drain: the last commit covers every MMA issued before it --------------------------------
+  {
+    const int last = KB - 1;
+    dcn_mbar_wait(&s_bar[last % kStages], (unsigned)((last / kStages) & 1));
+    tc_fence_after();
+  }
+  // ---- epilogue: TMEM -> registers -> bias / affine / ReLU -> NCHW fp32 ---------------------------
+  float* yb = prm.y + (size_t)b * Cout * P;
+  for (int c0 = 0; c0 < Cout; c0 += 16) {
+    uint32_t v[16];
+    tmem_ld16(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, v);
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      float r = __uint_as_float(v[j]);
+      if (prm.bias) r += __ldg(prm.bias + c0 + j);
+      if (prm.scale) r = r * __ldg(prm.scale + c0 + j) + __ldg(prm.shift + c0 + j);
+      if (prm.relu) r = fmaxf(r, 0.f);
+      if (valid) yb[(size_t)(c0 + j) * P + p] = r;
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, prm.tmem_cols);
+}
+
+}  // namespace ctdet
+
+static inline size_t dcn_align256(size_t v) { return (v + 255) / 256 * 256; }
+
+extern "C" size_t dcnv2_workspace_bytes(int B, int Cin, int H, int W, int Cout) {
+  if (B <= 0 || Cin <= 0 || H <= 0 || W <= 0 || Cout <= 0) return 0;
+  return dcn_align256((size_t)B * H * W * Cin * 2) + dcn_align256((size_t)Cout * Cin * 9 * 2);
+}
+
+extern "C" int dcnv2_forward(const float* input, const float* weight, const float* bias,
+                             const float* offset, const float* mask, float* output,
+                             int B, int Cin, int H, int W, int Cout, int kernel_h, int kernel_w,
+                             int stride_h, int stride_w, int pad_h, int pad_w, int dilation_h,
+                             int dilation_w, int group, int deformable_group,
+                             const float* scale, const float* shift, int flags,
+                             void* workspace, size_t workspace_bytes, ctdet_stream_t stream) {
+  using namespace ctdet;
+  if (B < 0 || Cin <= 0 || H <= 0 || W <= 0 || Cout <= 0) return CTDET_EINVAL;
+  if (flags & ~(DCN_FLAG_RELU | DCN_FLAG_FP32_BLEND)) return CTDET_EINVAL;
+  if ((scale == nullptr) != (shift == nullptr)) return CTDET_EINVAL;
+  // what DLA-34's DeformConvV2 uses (deform_conv.py:505-513): 3x3, one group, one deformable group
+  if (kernel_h != 3 || kernel_w != 3 || group != 1 || deformable_group != 1) return CTDET_EUNSUPPORTED;
+  if (stride_h != stride_w || pad_h != pad_w || dilation_h != dilation_w || stride_h < 1 || dilation_h < 1 || pad_h < 0)
+    return CTDET_EUNSUPPORTED;
+  // tensor-core tiling: K blocks of 64 channels inside one tap, UMMA N = Cout
+  if (Cin % kBK != 0 || Cout % 16 != 0 || Cout < 16 || Cout > 256) return CTDET_EUNSUPPORTED;
+  const int Ho = (H + 2 * pad_h - (dilation_h * 2 + 1)) / stride_h + 1;
+  const int Wo = (W + 2 * pad_w - (dilation_w * 2 + 1)) / stride_w + 1;
+  if (Ho <= 0 || Wo <= 0) return CTDET_EINVAL;
+  if (B == 0) return CTDET_OK;
+  if (!input || !weight || !offset || !mask || !output || !workspace) return CTDET_ENULL;
+  if (workspace_bytes < dcnv2_workspace_bytes(B, Cin, H, W, Cout)) return CTDET_EWORKSPACE;
+  if (reinterpret_cast<uintptr_t>(workspace) & 15u) return CTDET_EALIGN;
+  if ((size_t)H * W >= ((size_t)1 << 31) / (size_t)Cin) return CTDET_EINVAL;
+  cudaStream_t st = (cudaStream_t)stream;
+
+  __nv_bfloat16* xh = reinterpret_cast<__nv_bfloat16*>(workspace);
+  __nv_bfloat16* wk = reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<unsigned char*>(workspace) +
+                                                       dcn_align256((size_t)B * H * W * Cin * 2));
+  const int Pin = H * W;
+  if (B > 65535) return CTDET_EINVAL;
+  dcn_pack_input_kernel<<<dim3((Pin + 31) / 32, (Cin + 31) / 32, B), dim3(32, 8), 0, st>>>(input, xh, Cin, Pin);
+  int rc = check_launch();
+  if (rc) return rc;
+  dcn_pack_weight_kernel<<<kNumSMs, 256, 0, st>>>(weight, wk, Cout, Cin);
+  rc = check_launch();
+  if (rc) return rc;
+
+  DcnParams prm;
+  prm.xh = xh; prm.offset = offset; prm.mask = mask; prm.wk = wk; prm.bias = bias;
+  prm.scale = scale; prm.shift = shift; prm.y = output;
+  prm.Cin = Cin; prm.H = H; prm.W = W; prm.Ho = Ho; prm.Wo = Wo; prm.Cout = Cout;
+  prm.stride = stride_h; prm.pad = pad_h; prm.dil = dilation_h; prm.relu = (flags & DCN_FLAG_RELU) ? 1 : 0;
+  prm.tiles_per_image = (Ho * Wo + kDcnThreads - 1) / kDcnThreads;
+  uint32_t cols = 32;
+  while (cols < (uint32_t)Cout) cols <<= 1;                  // TMEM allocations are powers of two >= 32
+  prm.tmem_cols = cols;
+  const size_t smem = (size_t)kStages * (128 * kBK * 2 + (size_t)Cout * kBK * 2) + 1024;
+  auto kern = (flags & DCN_FLAG_FP32_BLEND) ? dcn_forward_kernel<true> : dcn_forward_kernel<false>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
+  const long long tiles = (long long)B * prm.tiles_per_image;
+  if (tiles > 0x7fffffffLL) return CTDET_EINVAL;
+  kern<<<(unsigned)tiles, kDcnThreads, smem, st>>>(prm);
+  return check_launch();
+}

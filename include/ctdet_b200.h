@@ -139,6 +139,32 @@ int ctdet_postprocess(float* boxes, float* scores, int32_t* classes, const int32
                       int B, int K, int max_dets, float score_thresh, int32_t* n_keep,
                       ctdet_stream_t stream);
 
+/* ---------------------------------------------------------------- DCNv2 forward ----------
+ * Modulated deformable 3x3 convolution, replaces modulated_deform_conv_forward
+ * (detectron2/layers/csrc/deformable/deform_conv.h:262-312; same argument meaning, minus the
+ * `ones`/`columns` scratch tensors: the im2col tile lives in shared memory and feeds tcgen05 MMAs).
+ *   input  f32 [B,Cin,H,W]      weight f32 [Cout,Cin,3,3]    bias f32 [Cout] or NULL (with_bias = 0)
+ *   offset f32 [B,18,Ho,Wo]     (channel 2t = dh, 2t+1 = dw of tap t)   mask f32 [B,9,Ho,Wo]
+ *   output f32 [B,Cout,Ho,Wo]
+ * Optional fused epilogue (DeformConvV2.actf, detectron2/layers/deform_conv.py:501-504, with the
+ * BatchNorm folded for inference): y = (conv + bias) * scale[c] + shift[c], then ReLU with
+ * DCN_FLAG_RELU; scale/shift NULL to skip.
+ * Operands are rounded to bf16, accumulation is fp32 (tolerance: see tests/test_gpu_dcn.py).
+ * DCN_FLAG_FP32_BLEND evaluates the bilinear blend in fp32 before the bf16 rounding (slower).
+ * Supported: kernel 3x3, group = deformable_group = 1, square stride/pad/dilation,
+ * Cin % 64 == 0, Cout % 16 == 0, 16 <= Cout <= 256; anything else returns CTDET_EUNSUPPORTED.
+ * workspace: dcnv2_workspace_bytes() bytes, 16-byte aligned (NHWC bf16 copy of the input + packed
+ * weights), no initialisation needed. */
+#define DCN_FLAG_RELU 1
+#define DCN_FLAG_FP32_BLEND 2
+size_t dcnv2_workspace_bytes(int B, int Cin, int H, int W, int Cout);
+int dcnv2_forward(const float* input, const float* weight, const float* bias,
+                  const float* offset, const float* mask, float* output,
+                  int B, int Cin, int H, int W, int Cout, int kernel_h, int kernel_w,
+                  int stride_h, int stride_w, int pad_h, int pad_w, int dilation_h, int dilation_w,
+                  int group, int deformable_group, const float* scale, const float* shift, int flags,
+                  void* workspace, size_t workspace_bytes, ctdet_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,129 @@
+"""GPU: the tcgen05 DCNv2 forward (through the C ABI) against the C oracle.
+
+Stated tolerance (operands rounded to bf16, fp32 accumulation, K = 9*Cin up to 4608):
+  max |got - ref| <= 2e-2 * max |ref|  and relative L2 error <= 1e-2 with the packed-bf16 blend,
+  relative L2 error <= 6e-3 with DCN_FLAG_FP32_BLEND."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import dcn_oracle as DO
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _case(seed, B, Cin, Cout, H, W, s=1, p=1, d=1, off_range=2.0):
+    rng = np.random.default_rng(seed)
+    Ho = (H + 2 * p - (2 * d + 1)) // s + 1
+    Wo = (W + 2 * p - (2 * d + 1)) // s + 1
+    x = rng.normal(size=(B, Cin, H, W)).astype(np.float32)
+    off = rng.uniform(-off_range, off_range, (B, 18, Ho, Wo)).astype(np.float32)
+    m = (1 / (1 + np.exp(-rng.normal(size=(B, 9, Ho, Wo))))).astype(np.float32)
+    bound = 1 / math.sqrt(9 * Cin)
+    w = rng.uniform(-bound, bound, (Cout, Cin, 3, 3)).astype(np.float32)
+    b = rng.normal(size=(Cout,)).astype(np.float32) * 0.1
+    return x, off, m, w, b
+
+
+def _run(x, off, m, w, b, s=1, p=1, d=1, **kw):
+    from detectron2_centernet_b200 import deform_conv as DC
+    t = [None if a is None else torch.from_numpy(a).to(DEV) for a in (x, off, m, w, b)]
+    out = DC.dcnv2_forward(*t, stride=s, padding=p, dilation=d, **kw)
+    torch.cuda.synchronize()
+    return out.cpu().numpy()
+
+
+def _errs(got, ref):
+    return np.abs(got - ref).max() / np.abs(ref).max(), np.linalg.norm(got - ref) / np.linalg.norm(ref)
+
+
+SHAPES = [
+    (1, 64, 64, 16, 24, 1, 1, 1, 2.0),      # 384 pixels = 3 full tiles
+    (2, 128, 64, 20, 20, 1, 1, 1, 2.0),     # 400 pixels: ragged last tile, 2 K blocks per tap
+    (1, 64, 256, 12, 12, 1, 1, 1, 8.0),     # N = 256, offsets far outside the image
+    (1, 256, 128, 9, 7, 1, 1, 1, 1.0),      # fewer pixels than one tile
+    (1, 64, 64, 17, 15, 2, 1, 1, 2.0),      # stride 2
+    (1, 64, 48, 10, 11, 1, 2, 2, 2.0),      # dilation 2, Cout = 48 (TMEM allocation rounded to 64)
+    (1, 512, 256, 16, 16, 1, 1, 1, 2.0),    # the deepest DLA layer: K = 4608
+]
+
+
+@pytest.mark.parametrize("cfg", SHAPES)
+def test_dcn_matches_oracle(cfg):
+    B, Cin, Cout, H, W, s, p, d, rng_ = cfg
+    x, off, m, w, b = _case(11, B, Cin, Cout, H, W, s, p, d, rng_)
+    ref = DO.dcn_forward(x, off, m, w, b, s, p, d, threads=4)
+    got = _run(x, off, m, w, b, s, p, d)
+    emax, el2 = _errs(got, ref)
+    assert emax <= 2e-2 and el2 <= 1e-2, (emax, el2)
+    got32 = _run(x, off, m, w, b, s, p, d, fp32_blend=True)
+    emax, el2 = _errs(got32, ref)
+    assert emax <= 2e-2 and el2 <= 6e-3, (emax, el2)
+
+
+def test_dcn_zero_offset_is_conv2d_and_no_bias():
+    x, off, m, w, b = _case(3, 2, 64, 64, 24, 24)
+    got = _run(x, np.zeros_like(off), np.ones_like(m), w, None)
+    ref = torch.nn.functional.conv2d(torch.from_numpy(x), torch.from_numpy(w), None, padding=1).numpy()
+    emax, el2 = _errs(got, ref)
+    assert el2 <= 6e-3, (emax, el2)
+
+
+def test_dcn_exact_on_bf16_representable_inputs():
+    """Integer-valued inputs/weights, integer offsets, unit mask: every product and the fp32
+    accumulation are exact, so the kernel must reproduce the oracle bit for bit -- this pins the
+    K ordering, the swizzled shared-memory layout and the UMMA descriptors."""
+    rng = np.random.default_rng(5)
+    B, Cin, Cout, H, W = 1, 64, 64, 16, 16
+    x = rng.integers(-4, 5, (B, Cin, H, W)).astype(np.float32)
+    w = rng.integers(-2, 3, (Cout, Cin, 3, 3)).astype(np.float32)
+    off = rng.integers(-2, 3, (B, 18, H, W)).astype(np.float32)
+    m = np.ones((B, 9, H, W), np.float32)
+    b = rng.integers(-3, 4, (Cout,)).astype(np.float32)
+    ref = DO.dcn_forward(x, off, m, w, b, 1, 1, 1)
+    got = _run(x, off, m, w, b)
+    assert np.array_equal(got, ref)
+
+
+def test_dcn_fused_epilogue_and_module():
+    from detectron2_centernet_b200 import deform_conv as DC
+    torch.manual_seed(0)
+    layer = DC.DeformConvV2(64, 64).to(DEV).eval()
+    # give the zero-initialised offset conv and the BatchNorm statistics non-trivial values
+    with torch.no_grad():
+        layer.conv.conv_offset_mask.weight.normal_(0, 0.05)
+        layer.conv.conv_offset_mask.bias.normal_(0, 0.5)
+        layer.actf[0].running_mean.normal_(0, 0.2)
+        layer.actf[0].running_var.uniform_(0.5, 1.5)
+        layer.actf[0].bias.normal_(0, 0.1)
+    assert set(k for k, _ in layer.named_parameters()) >= {"conv.weight", "conv.bias", "conv.conv_offset_mask.weight",
+                                                           "conv.conv_offset_mask.bias", "actf.0.weight", "actf.0.bias"}
+    x = torch.randn(2, 64, 32, 32, device=DEV)
+    with torch.no_grad():
+        fused = layer(x)                                             # BN + ReLU folded into the epilogue
+        offset, mask = layer.conv.offset_mask(x)
+    ref = DO.dcn_forward(x.cpu().numpy(), offset.cpu().numpy(), mask.cpu().numpy(),
+                         layer.conv.weight.detach().cpu().numpy(), layer.conv.bias.detach().cpu().numpy(), 1, 1, 1, threads=2)
+    bn = layer.actf[0]
+    scale = (bn.weight / torch.sqrt(bn.running_var + bn.eps)).detach().cpu().numpy()
+    shift = (bn.bias - bn.running_mean * bn.weight / torch.sqrt(bn.running_var + bn.eps)).detach().cpu().numpy()
+    ref = np.maximum(ref * scale[None, :, None, None] + shift[None, :, None, None], 0)
+    emax, el2 = _errs(fused.cpu().numpy(), ref)
+    assert el2 <= 1e-2, (emax, el2)
+    # the unfused path (autograd on) computes the same thing
+    unfused = layer(x.requires_grad_(True)).detach()
+    emax, el2 = _errs(unfused.cpu().numpy(), ref)
+    assert el2 <= 1e-2, (emax, el2)
+
+
+def test_dcn_unsupported_and_cpu():
+    from detectron2_centernet_b200 import deform_conv as DC
+    with pytest.raises(NotImplementedError):
+        DC.dcnv2_forward(torch.zeros(1, 64, 8, 8), torch.zeros(1, 18, 8, 8), torch.zeros(1, 9, 8, 8),
+                         torch.zeros(64, 64, 3, 3), None, 1, 1)
+    with pytest.raises(NotImplementedError):                           # Cin not a multiple of 64
+        DC.dcnv2_forward(torch.zeros(1, 32, 8, 8, device=DEV), torch.zeros(1, 18, 8, 8, device=DEV),
+                         torch.zeros(1, 9, 8, 8, device=DEV), torch.zeros(64, 32, 3, 3, device=DEV), None, 1, 1)
