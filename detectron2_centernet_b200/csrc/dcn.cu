@@ -30,7 +30,9 @@
 
 namespace ctdet {
 
-constexpr int kDcnThreads = 128;      // = pixels per tile = TMEM lanes = UMMA M
+constexpr int kDcnThreads = 256;      // 8 warps per CTA
+constexpr int kTileM = 128;           // pixels per tile = TMEM lanes = UMMA M
+constexpr int kTileH = 8, kTileW = 16; // 2-D pixel tile
 constexpr int kBK = 64;               // K block: 64 bf16 = one 128-byte swizzle row
 constexpr int kStages = 2;
 
@@ -131,7 +133,7 @@ struct DcnParams {
   const float* scale;          // [Cout] or null   y = (conv + bias) * scale + shift
   const float* shift;          // [Cout] or null
   float* y;                    // [B][Cout][Ho*Wo]
-  int Cin, H, W, Ho, Wo, Cout, stride, pad, dil, relu, tiles_per_image;
+  int Cin, H, W, Ho, Wo, Cout, stride, pad, dil, relu, tiles_per_image, tiles_x;
   uint32_t tmem_cols;
 };
 
@@ -153,34 +155,62 @@ __device__ __forceinline__ uint32_t blend_fp32(uint32_t a, uint32_t b, uint32_t 
   return *reinterpret_cast<const uint32_t*>(&r);
 }
 
+// Sampling geometry of output pixel (ho, wo) for tap t (dmcn_im2col_bilinear, :666-699): corner
+// pixel indices clamped into the image and bilinear weights * mask (0 for corners outside).
+__device__ __forceinline__ void tap_geometry(const DcnParams& prm, const float* offb, const float* mskb,
+                                             int P, int p, int ho, int wo, bool valid, int t, int4& o, float4& wq) {
+  o = make_int4(0, 0, 0, 0);
+  wq = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (!valid) return;
+  const int H = prm.H, W = prm.W;
+  const int i = t / 3, j = t - 3 * i;
+  const float h_im = (float)(ho * prm.stride - prm.pad + i * prm.dil) + __ldg(offb + (size_t)(2 * t) * P + p);
+  const float w_im = (float)(wo * prm.stride - prm.pad + j * prm.dil) + __ldg(offb + (size_t)(2 * t + 1) * P + p);
+  const float m = __ldg(mskb + (size_t)t * P + p);
+  if (h_im > -1.f && w_im > -1.f && h_im < (float)H && w_im < (float)W) {       // :852
+    const int h_low = (int)floorf(h_im), w_low = (int)floorf(w_im);
+    const int h_high = h_low + 1, w_high = w_low + 1;
+    const float lh = h_im - (float)h_low, lw = w_im - (float)w_low;
+    const float hh = 1.f - lh, hw = 1.f - lw;
+    const bool t_ok = h_low >= 0, b_ok = h_high <= H - 1, l_ok = w_low >= 0, r_ok = w_high <= W - 1;
+    const int hl = max(h_low, 0), hh_i = min(h_high, H - 1), wl = max(w_low, 0), wh_i = min(w_high, W - 1);
+    o.x = hl * W + wl;     wq.x = (t_ok && l_ok) ? hh * hw * m : 0.f;
+    o.y = hl * W + wh_i;   wq.y = (t_ok && r_ok) ? hh * lw * m : 0.f;
+    o.z = hh_i * W + wl;   wq.z = (b_ok && l_ok) ? lh * hw * m : 0.f;
+    o.w = hh_i * W + wh_i; wq.w = (b_ok && r_ok) ? lh * lw * m : 0.f;
+  }
+}
+
+// One CTA = one 8 x 16 tile of output pixels (128 = UMMA M) of one image, 8 warps.
+// 2-D tiles keep the sampled neighbourhood of the 9 taps (~14 x 22 pixels x Cin bf16) resident in
+// L1 between K blocks; a row-of-128 tile touches three times as many lines.
 template <bool kFp32Blend>
 __global__ void __launch_bounds__(kDcnThreads)
 dcn_forward_kernel(const DcnParams prm) {
   extern __shared__ __align__(1024) uint8_t dcn_smem[];
   __shared__ __align__(8) uint64_t s_bar[kStages];
   __shared__ uint32_t s_tmem;
+  // per-pixel geometry of the current / next tap (double buffered by tap parity): the gather is
+  // done by 8 lanes per pixel (one 16-byte chunk each), so one warp-wide load touches 4 full
+  // 128-byte lines instead of 32 partial ones
+  __shared__ int4 s_geo_o[2][kTileM];
+  __shared__ float4 s_geo_w[2][kTileM];
 
-  const int tid = threadIdx.x, warp = tid >> 5;
-  const int Cin = prm.Cin, Cout = prm.Cout, W = prm.W, H = prm.H;
-  const int P = prm.Ho * prm.Wo, Pin = H * W;
-  const int b = blockIdx.x / prm.tiles_per_image;
-  const int p = (blockIdx.x % prm.tiles_per_image) * kDcnThreads + tid;     // this thread's output pixel
-  const bool valid = p < P;
-  const int ho = valid ? p / prm.Wo : 0, wo = valid ? p % prm.Wo : 0;
-  const uint32_t stage_bytes = 128u * kBK * 2u + (uint32_t)Cout * kBK * 2u;  // A tile + Wk tile
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int Cin = prm.Cin, Cout = prm.Cout;
+  const int P = prm.Ho * prm.Wo, Pin = prm.H * prm.W;
+  int tile = blockIdx.x;
+  const int b = tile / prm.tiles_per_image;
+  tile -= b * prm.tiles_per_image;
+  const int tile_y = tile / prm.tiles_x, tile_x = tile - tile_y * prm.tiles_x;
+  // geometry role: thread r and thread r+128 both describe tile row r (pixel ty = r/16, tx = r%16)
+  const int r = tid & (kTileM - 1);
+  const int ho = tile_y * kTileH + (r >> 4), wo = tile_x * kTileW + (r & 15);
+  const bool valid = ho < prm.Ho && wo < prm.Wo;
+  const int p = valid ? ho * prm.Wo + wo : 0;
+  const uint32_t stage_bytes = (uint32_t)kTileM * kBK * 2u + (uint32_t)Cout * kBK * 2u;   // A tile + Wk tile
   // dynamic shared memory is only guaranteed 16-byte aligned: round up to the 1024-byte swizzle atom
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(dcn_smem) + 1023) & ~(uintptr_t)1023);
-
-  if (tid == 0) {
-    for (int s = 0; s < kStages; ++s) dcn_mbar_init(&s_bar[s], 1);
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
-  if (warp == 0) tmem_alloc(&s_tmem, prm.tmem_cols);
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem = s_tmem;
-  const uint32_t idesc = make_idesc_bf16(128, Cout);
 
   const int cpb = Cin / kBK;                     // K blocks per tap
   const int KB = 9 * cpb;
@@ -189,63 +219,65 @@ dcn_forward_kernel(const DcnParams prm) {
   const float* offb = prm.offset + (size_t)b * 18 * P;
   const float* mskb = prm.mask + (size_t)b * 9 * P;
 
-  int o1 = 0, o2 = 0, o3 = 0, o4 = 0;            // corner pixel indices (clamped into the image)
-  float w1 = 0.f, w2 = 0.f, w3 = 0.f, w4 = 0.f;  // bilinear weights * mask, 0 for corners outside
+  if (tid == 0) {
+    for (int s = 0; s < kStages; ++s) dcn_mbar_init(&s_bar[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) tmem_alloc(&s_tmem, prm.tmem_cols);
+  if (tid < kTileM) {                            // tap 0
+    int4 o; float4 wq;
+    tap_geometry(prm, offb, mskb, P, p, ho, wo, valid, 0, o, wq);
+    s_geo_o[0][r] = o; s_geo_w[0][r] = wq;
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = s_tmem;
+  const uint32_t idesc = make_idesc_bf16(kTileM, Cout);
+  const int sub = lane >> 3, chunk = lane & 7;   // 4 pixels x 8 chunks per warp-wide load
 
   for (int kb = 0; kb < KB; ++kb) {
     const int s = kb % kStages, use = kb / kStages;
     if (kb >= kStages) dcn_mbar_wait(&s_bar[s], (unsigned)((use - 1) & 1));   // MMAs that read stage s retired
     const int t = kb / cpb, ci0 = (kb - t * cpb) * kBK;
-    if (ci0 == 0) {
-      // ---- sampling geometry of tap t (dmcn_im2col_bilinear, :666-699) -----------------------------
-      w1 = w2 = w3 = w4 = 0.f; o1 = o2 = o3 = o4 = 0;
-      if (valid) {
-        const int i = t / 3, j = t - 3 * i;
-        const float h_im = (float)(ho * prm.stride - prm.pad + i * prm.dil) + offb[(size_t)(2 * t) * P + p];
-        const float w_im = (float)(wo * prm.stride - prm.pad + j * prm.dil) + offb[(size_t)(2 * t + 1) * P + p];
-        const float m = mskb[(size_t)t * P + p];
-        if (h_im > -1.f && w_im > -1.f && h_im < (float)H && w_im < (float)W) {       // :852
-          const int h_low = (int)floorf(h_im), w_low = (int)floorf(w_im);
-          const int h_high = h_low + 1, w_high = w_low + 1;
-          const float lh = h_im - (float)h_low, lw = w_im - (float)w_low;
-          const float hh = 1.f - lh, hw = 1.f - lw;
-          const bool t_ok = h_low >= 0, b_ok = h_high <= H - 1, l_ok = w_low >= 0, r_ok = w_high <= W - 1;
-          const int hl = max(h_low, 0), hh_i = min(h_high, H - 1), wl = max(w_low, 0), wh_i = min(w_high, W - 1);
-          o1 = hl * W + wl;   w1 = (t_ok && l_ok) ? hh * hw * m : 0.f;
-          o2 = hl * W + wh_i; w2 = (t_ok && r_ok) ? hh * lw * m : 0.f;
-          o3 = hh_i * W + wl; w3 = (b_ok && l_ok) ? lh * hw * m : 0.f;
-          o4 = hh_i * W + wh_i; w4 = (b_ok && r_ok) ? lh * lw * m : 0.f;
-        }
-      }
+    // the upper half of the CTA prepares the next tap's geometry (published by this block's barrier)
+    if (ci0 == 0 && t + 1 < 9 && tid >= kTileM) {
+      int4 o; float4 wq;
+      tap_geometry(prm, offb, mskb, P, p, ho, wo, valid, t + 1, o, wq);
+      s_geo_o[(t + 1) & 1][r] = o; s_geo_w[(t + 1) & 1][r] = wq;
     }
     uint8_t* a_tile = smem + (size_t)s * stage_bytes;
-    uint8_t* b_tile = a_tile + 128 * kBK * 2;
+    uint8_t* b_tile = a_tile + kTileM * kBK * 2;
 
-    // ---- A row of this pixel: 64 channels = 8 chunks of 16 bytes, swizzled -----------------------
+    // ---- A rows: warp w builds tile rows 16w .. 16w+15 in 4 passes of (4 pixels x 8 chunks) ------
     {
-      const uint4* c1 = reinterpret_cast<const uint4*>(xb + (size_t)o1 * Cin + ci0);
-      const uint4* c2 = reinterpret_cast<const uint4*>(xb + (size_t)o2 * Cin + ci0);
-      const uint4* c3 = reinterpret_cast<const uint4*>(xb + (size_t)o3 * Cin + ci0);
-      const uint4* c4 = reinterpret_cast<const uint4*>(xb + (size_t)o4 * Cin + ci0);
-      uint8_t* arow = a_tile + tid * 128;
-      const __nv_bfloat162 q1 = __float2bfloat162_rn(w1), q2 = __float2bfloat162_rn(w2),
-                           q3 = __float2bfloat162_rn(w3), q4 = __float2bfloat162_rn(w4);
-#pragma unroll 4
-      for (int c = 0; c < 8; ++c) {
-        const uint4 a = __ldg(c1 + c), bq = __ldg(c2 + c), cq = __ldg(c3 + c), d = __ldg(c4 + c);
-        uint4 r;
+      const __nv_bfloat16* xc = xb + ci0 + chunk * 8;
+      const int4* go = s_geo_o[t & 1];
+      const float4* gw = s_geo_w[t & 1];
+#pragma unroll
+      for (int it = 0; it < 4; ++it) {
+        const int row = (warp << 4) + (it << 2) + sub;
+        const int4 o = go[row];
+        const float4 wq = gw[row];
+        const uint4 a = __ldg(reinterpret_cast<const uint4*>(xc + (size_t)o.x * Cin));
+        const uint4 bq = __ldg(reinterpret_cast<const uint4*>(xc + (size_t)o.y * Cin));
+        const uint4 cq = __ldg(reinterpret_cast<const uint4*>(xc + (size_t)o.z * Cin));
+        const uint4 d = __ldg(reinterpret_cast<const uint4*>(xc + (size_t)o.w * Cin));
+        uint4 q;
         if (kFp32Blend) {
-          r.x = blend_fp32(a.x, bq.x, cq.x, d.x, w1, w2, w3, w4);
-          r.y = blend_fp32(a.y, bq.y, cq.y, d.y, w1, w2, w3, w4);
-          r.z = blend_fp32(a.z, bq.z, cq.z, d.z, w1, w2, w3, w4);
-          r.w = blend_fp32(a.w, bq.w, cq.w, d.w, w1, w2, w3, w4);
+          q.x = blend_fp32(a.x, bq.x, cq.x, d.x, wq.x, wq.y, wq.z, wq.w);
+          q.y = blend_fp32(a.y, bq.y, cq.y, d.y, wq.x, wq.y, wq.z, wq.w);
+          q.z = blend_fp32(a.z, bq.z, cq.z, d.z, wq.x, wq.y, wq.z, wq.w);
+          q.w = blend_fp32(a.w, bq.w, cq.w, d.w, wq.x, wq.y, wq.z, wq.w);
         } else {
-          r.x = blend_bf16x2(a.x, bq.x, cq.x, d.x, q1, q2, q3, q4);
-          r.y = blend_bf16x2(a.y, bq.y, cq.y, d.y, q1, q2, q3, q4);
-          r.z = blend_bf16x2(a.z, bq.z, cq.z, d.z, q1, q2, q3, q4);
-          r.w = blend_bf16x2(a.w, bq.w, cq.w, d.w, q1, q2, q3, q4);
+          const __nv_bfloat162 q1 = __float2bfloat162_rn(wq.x), q2 = __float2bfloat162_rn(wq.y),
+                               q3 = __float2bfloat162_rn(wq.z), q4 = __float2bfloat162_rn(wq.w);
+          q.x = blend_bf16x2(a.x, bq.x, cq.x, d.x, q1, q2, q3, q4);
+          q.y = blend_bf16x2(a.y, bq.y, cq.y, d.y, q1, q2, q3, q4);
+          q.z = blend_bf16x2(a.z, bq.z, cq.z, d.z, q1, q2, q3, q4);
+          q.w = blend_bf16x2(a.w, bq.w, cq.w, d.w, q1, q2, q3, q4);
         }
-        *reinterpret_cast<uint4*>(arow + ((c ^ (tid & 7)) << 4)) = r;
+        *reinterpret_cast<uint4*>(a_tile + row * 128 + ((chunk ^ (row & 7)) << 4)) = q;
       }
     }
     // ---- Wk block [Cout][64], same swizzle --------------------------------------------------------
@@ -276,17 +308,25 @@ dcn_forward_kernel(const DcnParams prm) {
     tc_fence_after();
   }
   // ---- epilogue: TMEM -> registers -> bias / affine / ReLU -> NCHW fp32 ---------------------------
-  float* yb = prm.y + (size_t)b * Cout * P;
-  for (int c0 = 0; c0 < Cout; c0 += 16) {
-    uint32_t v[16];
-    tmem_ld16(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, v);
+  // warp w may only read TMEM lanes 32*(w%4) .. +31; the two warps of a lane quarter split the
+  // 16-column groups between them
+  {
+    const int quarter = warp & 3, half = warp >> 2;
+    const int er = (quarter << 5) + lane;                       // tile row = TMEM lane of this thread
+    const int eho = tile_y * kTileH + (er >> 4), ewo = tile_x * kTileW + (er & 15);
+    const bool evalid = eho < prm.Ho && ewo < prm.Wo;
+    float* yb = prm.y + (size_t)b * Cout * P + (evalid ? eho * prm.Wo + ewo : 0);
+    for (int c0 = half * 16; c0 < Cout; c0 += 32) {
+      uint32_t v[16];
+      tmem_ld16(tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)c0, v);
 #pragma unroll
-    for (int j = 0; j < 16; ++j) {
-      float r = __uint_as_float(v[j]);
-      if (prm.bias) r += __ldg(prm.bias + c0 + j);
-      if (prm.scale) r = r * __ldg(prm.scale + c0 + j) + __ldg(prm.shift + c0 + j);
-      if (prm.relu) r = fmaxf(r, 0.f);
-      if (valid) yb[(size_t)(c0 + j) * P + p] = r;
+      for (int j = 0; j < 16; ++j) {
+        float q = __uint_as_float(v[j]);
+        if (prm.bias) q += __ldg(prm.bias + c0 + j);
+        if (prm.scale) q = q * __ldg(prm.scale + c0 + j) + __ldg(prm.shift + c0 + j);
+        if (prm.relu) q = fmaxf(q, 0.f);
+        if (evalid) yb[(size_t)(c0 + j) * P] = q;
+      }
     }
   }
   tc_fence_before();
@@ -347,11 +387,12 @@ extern "C" int dcnv2_forward(const float* input, const float* weight, const floa
   prm.scale = scale; prm.shift = shift; prm.y = output;
   prm.Cin = Cin; prm.H = H; prm.W = W; prm.Ho = Ho; prm.Wo = Wo; prm.Cout = Cout;
   prm.stride = stride_h; prm.pad = pad_h; prm.dil = dilation_h; prm.relu = (flags & DCN_FLAG_RELU) ? 1 : 0;
-  prm.tiles_per_image = (Ho * Wo + kDcnThreads - 1) / kDcnThreads;
+  prm.tiles_x = (Wo + kTileW - 1) / kTileW;
+  prm.tiles_per_image = prm.tiles_x * ((Ho + kTileH - 1) / kTileH);
   uint32_t cols = 32;
   while (cols < (uint32_t)Cout) cols <<= 1;                  // TMEM allocations are powers of two >= 32
   prm.tmem_cols = cols;
-  const size_t smem = (size_t)kStages * (128 * kBK * 2 + (size_t)Cout * kBK * 2) + 1024;
+  const size_t smem = (size_t)kStages * (kTileM * kBK * 2 + (size_t)Cout * kBK * 2) + 1024;
   auto kern = (flags & DCN_FLAG_FP32_BLEND) ? dcn_forward_kernel<true> : dcn_forward_kernel<false>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
