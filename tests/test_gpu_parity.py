@@ -413,3 +413,49 @@ def test_postprocess_batch():
         assert np.array_equal(boxes[b, :n].cpu().numpy(), t[ne].numpy())
         assert np.array_equal(scores[b, :n].cpu().numpy(), ss[ne.numpy()])
         assert np.array_equal(classes[b, :n].cpu().numpy(), cc[ne.numpy()])
+
+
+# ------------------------------------------------------------------ meta-arch glue
+def test_centernet_hot_path_losses_and_inference(inputs):
+    """CenterNetHotPath.losses / inference against the oracle's restatement of
+    CenterNet.losses (:191-212) and inference_single_image (:236-266) + detector_postprocess."""
+    import detectron2_centernet_b200 as P
+    bl, cl, hm, wh, reg, (B, C, H, W, K, full) = inputs("coco512")
+    model = P.CenterNetHotPath(P.get_cfg(overrides={"MODEL": {"CENTERNET": {"FOCAL_LOSS_ALPHA": [1]}}}), num_classes=C)
+    insts = []
+    for b in range(B):
+        i = P.Instances((512, 512))
+        i.gt_boxes = P.Boxes(torch.from_numpy(bl[b]).to(DEV))
+        i.gt_classes = torch.from_numpy(cl[b]).to(DEV)
+        insts.append(i)
+    targets = model.targets(insts, (512, 512))
+    t_hm, t_wh, t_reg = [t.requires_grad_(True) for t in _cuda(hm, wh, reg)]
+    out = model.losses({"hm": t_hm, "wh": t_wh, "reg": t_reg}, targets)
+    gt_np = O.gen_heatmap_batch(bl, cl, H, W, C)
+    ref, _ = O.losses_and_grads(torch.from_numpy(hm), torch.from_numpy(wh), torch.from_numpy(reg), gt_np, alpha=[1.0])
+    for k in ("hm_loss", "wh_loss", "off_loss"):
+        np.testing.assert_allclose(out[k].item(), float(ref[k]), rtol=1e-5)
+    # the optional all-reduce path with one process gives the same numbers
+    model_sync = P.CenterNetHotPath(P.get_cfg(overrides={"MODEL": {"CENTERNET": {"FOCAL_LOSS_ALPHA": [1]}}}),
+                                    num_classes=C, sync_num_pos=True)
+    out2 = model_sync.losses({"hm": t_hm, "wh": t_wh, "reg": t_reg}, targets)
+    for k in out:
+        np.testing.assert_allclose(out2[k].item(), out[k].item(), rtol=1e-6)
+    # inference: list of Instances, thresholded (score > 0.05) and resized to the original image size
+    sizes, orig = [(512, 512)] * B, [(1024, 768), (512, 512)][:B]
+    res = model.inference({"hm": t_hm.detach(), "wh": t_wh.detach(), "reg": t_reg.detach()}, sizes, orig)
+    ob, os_, oc, _ = O.decode(S.sigmoid_clamp(hm), wh, reg, 4, model.topk_candidates)
+    for b in range(B):
+        bb, ss, cc = O.postprocess_single(ob[b], os_[b], oc[b], model.max_detections_per_image, model.score_threshold)
+        t = torch.from_numpy(bb.copy())
+        t[:, 0::2] *= orig[b][1] / sizes[b][1]
+        t[:, 1::2] *= orig[b][0] / sizes[b][0]
+        t[:, 0::2].clamp_(0, orig[b][1])
+        t[:, 1::2].clamp_(0, orig[b][0])
+        keep = ((t[:, 2] - t[:, 0]) > 0) & ((t[:, 3] - t[:, 1]) > 0)
+        r = res[b]
+        assert r.image_size == orig[b] and len(r) == int(keep.sum())
+        assert r.pred_classes.dtype == torch.int32
+        assert np.array_equal(r.pred_classes.cpu().numpy(), cc[keep.numpy()])
+        np.testing.assert_allclose(r.scores.cpu().numpy(), ss[keep.numpy()], rtol=2e-7)
+        assert np.array_equal(r.pred_boxes.tensor.cpu().numpy(), t[keep].numpy())
