@@ -26,15 +26,14 @@
 // Border rule identical to the reference: a tap samples iff h_im > -1 && w_im > -1 && h_im < H &&
 // w_im < W (:852); each bilinear corner outside the image contributes 0 (:683-693).
 #include <cuda_bf16.h>
+#include <cstdlib>
 #include "common.cuh"
 
 namespace ctdet {
 
-constexpr int kDcnThreads = 256;      // 8 warps per CTA
 constexpr int kTileM = 128;           // pixels per tile = TMEM lanes = UMMA M
 constexpr int kTileH = 8, kTileW = 16; // 2-D pixel tile
 constexpr int kBK = 64;               // K block: 64 bf16 = one 128-byte swizzle row
-constexpr int kStages = 2;
 
 // ------------------------------------------------------------------------------------------------
 // pre-pass 1: NCHW fp32 -> NHWC bf16.  One CTA transposes a 64-channel x 64-pixel block through
@@ -80,15 +79,22 @@ dcn_pack_input_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ x
   }
 }
 
-// pre-pass 2: weight [Cout][Cin][9] fp32 -> Wk [Cout][9][Cin] bf16
+// pre-pass 2: weight [Cout][Cin][9] fp32 -> bf16 B-operand tiles, one per K block kb = cb*9 + t
+// (cb = 64-channel block, t = tap): tile kb is the [Cout][64] K-major slab in EXACTLY the 128-byte
+// swizzled shared-memory image the UMMA descriptor expects (row n at n*128 B, 16-byte chunk ch at
+// (ch ^ (n & 7)) << 4), so the main kernel moves it with one 1-D bulk async copy.
 __global__ void dcn_pack_weight_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ wk,
                                        int Cout, int Cin) {
-  const size_t n = (size_t)Cout * Cin * 9;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
-    const int ci = (int)(i % Cin);
-    const int t = (int)((i / Cin) % 9);
-    const int co = (int)(i / ((size_t)Cin * 9));
-    wk[i] = __float2bfloat16_rn(w[((size_t)co * Cin + ci) * 9 + t]);
+  const size_t n_el = (size_t)Cout * Cin * 9;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_el; i += (size_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i & 63);                         // channel inside the block
+    const int n = (int)((i >> 6) % Cout);
+    const int kb = (int)(i / ((size_t)Cout * 64));
+    const int cb = kb / 9, t = kb - 9 * cb;
+    const int ci = cb * 64 + c;
+    const int ch = c >> 3, e = c & 7;
+    wk[(size_t)kb * Cout * 64 + (size_t)n * 64 + ((ch ^ (n & 7)) << 3) + e] =
+        __float2bfloat16_rn(w[((size_t)n * Cin + ci) * 9 + t]);
   }
 }
 
@@ -148,26 +154,53 @@ __device__ __forceinline__ uint32_t make_idesc_bf16(int M, int N) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
+// waiters that are idle most of the time back off between polls: every poll is a shared-memory
+// pipe transaction that competes with the producers' A-tile stores
+__device__ __forceinline__ void dcn_mbar_wait_relaxed(uint64_t* bar, unsigned parity, unsigned ns = 64) {
+  const uint32_t addr = smem_u32(bar);
+  for (;;) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(addr), "r"(parity) : "memory");
+    if (ok) break;
+    if (ns) __nanosleep(ns);
+  }
+}
+__device__ __forceinline__ void dcn_mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void dcn_mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+// 1-D bulk async copy global -> shared (TMA engine, no LSU instructions), completion on an mbarrier
+__device__ __forceinline__ void dcn_bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               :: "r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
 // ------------------------------------------------------------------------------------------------
 struct DcnParams {
   const __nv_bfloat16* xh;     // [B][H*W][Cin]
   const float* offset;         // [B][18][Ho*Wo]   channel 2t = dh, 2t+1 = dw (deform_conv_cuda_kernel.cu:838-846)
   const float* mask;           // [B][9][Ho*Wo]
-  const __nv_bfloat16* wk;     // [Cout][9*Cin]
+  const __nv_bfloat16* wk;     // [9*Cin/64][Cout][64] swizzled B tiles
   const float* bias;           // [Cout] or null
   const float* scale;          // [Cout] or null   y = (conv + bias) * scale + shift
   const float* shift;          // [Cout] or null
   float* y;                    // [B][Cout][Ho*Wo]
-  int Cin, H, W, Ho, Wo, Cout, stride, pad, dil, relu, tiles_per_image, tiles_x;
+  int Cin, H, W, Ho, Wo, Cout, stride, pad, dil, relu, tiles_per_image, tiles_x, num_tiles, stages, mma_sleep, ld_sleep;
   uint32_t tmem_cols;
 };
 
 __device__ __forceinline__ uint32_t blend_bf16x2(uint32_t a, uint32_t b, uint32_t c, uint32_t d,
-                                                 __nv_bfloat162 w1, __nv_bfloat162 w2, __nv_bfloat162 w3, __nv_bfloat162 w4) {
-  __nv_bfloat162 acc = __hmul2(w1, *reinterpret_cast<__nv_bfloat162*>(&a));
-  acc = __hfma2(w2, *reinterpret_cast<__nv_bfloat162*>(&b), acc);
-  acc = __hfma2(w3, *reinterpret_cast<__nv_bfloat162*>(&c), acc);
-  acc = __hfma2(w4, *reinterpret_cast<__nv_bfloat162*>(&d), acc);
+                                                 uint32_t w1, uint32_t w2, uint32_t w3, uint32_t w4) {
+  __nv_bfloat162 acc = __hmul2(*reinterpret_cast<__nv_bfloat162*>(&w1), *reinterpret_cast<__nv_bfloat162*>(&a));
+  acc = __hfma2(*reinterpret_cast<__nv_bfloat162*>(&w2), *reinterpret_cast<__nv_bfloat162*>(&b), acc);
+  acc = __hfma2(*reinterpret_cast<__nv_bfloat162*>(&w3), *reinterpret_cast<__nv_bfloat162*>(&c), acc);
+  acc = __hfma2(*reinterpret_cast<__nv_bfloat162*>(&w4), *reinterpret_cast<__nv_bfloat162*>(&d), acc);
   return *reinterpret_cast<uint32_t*>(&acc);
 }
 __device__ __forceinline__ uint32_t blend_fp32(uint32_t a, uint32_t b, uint32_t c, uint32_t d,
@@ -180,184 +213,321 @@ __device__ __forceinline__ uint32_t blend_fp32(uint32_t a, uint32_t b, uint32_t 
   return *reinterpret_cast<const uint32_t*>(&r);
 }
 
-// Sampling geometry of output pixel (ho, wo) for tap t (dmcn_im2col_bilinear, :666-699): corner
-// pixel indices clamped into the image and bilinear weights * mask (0 for corners outside).
-__device__ __forceinline__ void tap_geometry(const DcnParams& prm, const float* offb, const float* mskb,
-                                             int P, int p, int ho, int wo, bool valid, int t, int4& o, float4& wq) {
-  o = make_int4(0, 0, 0, 0);
-  wq = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (!valid) return;
-  const int H = prm.H, W = prm.W;
-  const int i = t / 3, j = t - 3 * i;
-  const float h_im = (float)(ho * prm.stride - prm.pad + i * prm.dil) + __ldg(offb + (size_t)(2 * t) * P + p);
-  const float w_im = (float)(wo * prm.stride - prm.pad + j * prm.dil) + __ldg(offb + (size_t)(2 * t + 1) * P + p);
-  const float m = __ldg(mskb + (size_t)t * P + p);
-  if (h_im > -1.f && w_im > -1.f && h_im < (float)H && w_im < (float)W) {       // :852
-    const int h_low = (int)floorf(h_im), w_low = (int)floorf(w_im);
-    const int h_high = h_low + 1, w_high = w_low + 1;
-    const float lh = h_im - (float)h_low, lw = w_im - (float)w_low;
-    const float hh = 1.f - lh, hw = 1.f - lw;
-    const bool t_ok = h_low >= 0, b_ok = h_high <= H - 1, l_ok = w_low >= 0, r_ok = w_high <= W - 1;
-    const int hl = max(h_low, 0), hh_i = min(h_high, H - 1), wl = max(w_low, 0), wh_i = min(w_high, W - 1);
-    o.x = hl * W + wl;     wq.x = (t_ok && l_ok) ? hh * hw * m : 0.f;
-    o.y = hl * W + wh_i;   wq.y = (t_ok && r_ok) ? hh * lw * m : 0.f;
-    o.z = hh_i * W + wl;   wq.z = (b_ok && l_ok) ? lh * hw * m : 0.f;
-    o.w = hh_i * W + wh_i; wq.w = (b_ok && r_ok) ? lh * lw * m : 0.f;
+// Sampling geometry of output pixel (ho, wo) for tap t (dmcn_im2col_bilinear, :666-699).
+//   g  = element offset of the clamped top-left corner pixel in the NHWC image (pixel * Cin, a
+//        multiple of 64) | bit0: the right corner is a different pixel | bit1: the bottom corner is
+//   wq = the four bilinear weights * mask (0 for corners outside the image); either fp32 or, for
+//        the packed blend, each rounded to bf16 and broadcast into both halves of a bf16x2
+template <bool kFp32Blend>
+__device__ __forceinline__ void tap_geometry(const DcnParams& prm, float off_h, float off_w, float m,
+                                             int ho, int wo, bool valid, int t, uint32_t& g, uint4& wout) {
+  g = 0u;
+  float4 wq = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (valid) {
+    const int H = prm.H, W = prm.W;
+    const int i = t / 3, j = t - 3 * i;
+    const float h_im = (float)(ho * prm.stride - prm.pad + i * prm.dil) + off_h;
+    const float w_im = (float)(wo * prm.stride - prm.pad + j * prm.dil) + off_w;
+    if (h_im > -1.f && w_im > -1.f && h_im < (float)H && w_im < (float)W) {       // :852
+      const int h_low = (int)floorf(h_im), w_low = (int)floorf(w_im);
+      const int h_high = h_low + 1, w_high = w_low + 1;
+      const float lh = h_im - (float)h_low, lw = w_im - (float)w_low;
+      const float hh = 1.f - lh, hw = 1.f - lw;
+      const bool t_ok = h_low >= 0, b_ok = h_high <= H - 1, l_ok = w_low >= 0, r_ok = w_high <= W - 1;
+      const int hl = max(h_low, 0), hh_i = min(h_high, H - 1), wl = max(w_low, 0), wh_i = min(w_high, W - 1);
+      g = (uint32_t)(hl * W + wl) * (uint32_t)prm.Cin | (wh_i != wl ? 1u : 0u) | (hh_i != hl ? 2u : 0u);
+      wq.x = (t_ok && l_ok) ? hh * hw * m : 0.f;
+      wq.y = (t_ok && r_ok) ? hh * lw * m : 0.f;
+      wq.z = (b_ok && l_ok) ? lh * hw * m : 0.f;
+      wq.w = (b_ok && r_ok) ? lh * lw * m : 0.f;
+    }
+  }
+  if (kFp32Blend) {
+    wout = make_uint4(__float_as_uint(wq.x), __float_as_uint(wq.y), __float_as_uint(wq.z), __float_as_uint(wq.w));
+  } else {
+    const __nv_bfloat162 q1 = __float2bfloat162_rn(wq.x), q2 = __float2bfloat162_rn(wq.y),
+                         q3 = __float2bfloat162_rn(wq.z), q4 = __float2bfloat162_rn(wq.w);
+    wout = make_uint4(*reinterpret_cast<const uint32_t*>(&q1), *reinterpret_cast<const uint32_t*>(&q2),
+                      *reinterpret_cast<const uint32_t*>(&q3), *reinterpret_cast<const uint32_t*>(&q4));
   }
 }
 
-// One CTA = one 8 x 16 tile of output pixels (128 = UMMA M) of one image, 8 warps.
-// 2-D tiles keep the sampled neighbourhood of the 9 taps (~14 x 22 pixels x Cin bf16) resident in
-// L1 between K blocks; a row-of-128 tile touches three times as many lines.
-template <bool kFp32Blend>
-__global__ void __launch_bounds__(kDcnThreads)
+// 16-byte gather of 8 bf16 channels through L1 (volatile: keeps every gather of a K block ahead of
+// the blends, so 4 * ITERS loads are in flight per thread)
+__device__ __forceinline__ uint4 ldg_gather16(const __nv_bfloat16* p) {
+  uint4 v;
+  asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+}
+
+__device__ __forceinline__ float ldg_stream1(const float* p) {      // read-once scalar, volatile = kept in order
+  float v;
+  asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(v) : "l"(p));
+  return v;
+}
+
+constexpr int kMaxStages = 8;
+constexpr int kGeoBytes = 2 * 9 * kTileM * (16 + 4);      // double-buffered {uint4 weights, u32 g} per (tap, pixel)
+
+struct DcnBarriers {
+  uint64_t full[kMaxStages];     // A rows written by the producer warps + B tile landed  -> MMA may read stage
+  uint64_t empty[kMaxStages];    // the MMAs that read the stage retired                  -> stage may be refilled
+  uint64_t geo_full[2], geo_empty[2];   // per-tile sampling geometry (all 9 taps) in shared memory
+  uint64_t acc_full[2], acc_empty[2];   // TMEM accumulator buffers
+};
+
+// ------------------------------------------------------------------------------------------------
+// Persistent, warp-specialised main kernel: one CTA per SM loops over 8 x 16 pixel tiles (128 = UMMA
+// M = TMEM lanes).  2-D tiles keep the sampled neighbourhood of the 9 taps (~14 x 22 pixels x 64
+// channels bf16 = 39 KB per channel block) resident in L1; K runs channel-block-major so that
+// working set does not grow with Cin.
+//   warps [0, NP)        producers: gather 4 corners (8 lanes x 16 B per pixel: one warp-wide load
+//                        touches 4 full 128-byte lines), blend, store A rows (swizzled), arrive on
+//                        full[s].  The gathers of K block n+1 are issued while block n is blended
+//                        (register double-buffering across K blocks AND tiles): 16 loads per thread
+//                        stay in flight, the L1/L2 latency is never exposed
+//   warps [NP, NP+4)     epilogue: TMEM -> registers -> affine/ReLU -> NCHW fp32 (lane quarter = warp % 4)
+//   warps [NP+4, NP+8)   sampling geometry of the tiles ahead (thread = pixel, all 9 taps)
+//   warp  NP+8           one lane issues tcgen05.mma / tcgen05.commit
+//   warp  NP+9           one lane streams the pre-swizzled B (weight) tiles with 1-D bulk copies
+// TMEM holds two accumulator buffers, so the epilogue of tile i overlaps the MMAs of tile i+1.
+template <bool kFp32Blend, int NP>
+__global__ void __launch_bounds__((NP + 10) * 32, 1)
 dcn_forward_kernel(const DcnParams prm) {
+  static_assert(NP % 4 == 0 && 32 % NP == 0, "producer warps must tile the 32 row groups and keep warp%4 aligned");
   extern __shared__ __align__(1024) uint8_t dcn_smem[];
-  __shared__ __align__(8) uint64_t s_bar[kStages];
+  __shared__ DcnBarriers bars;
   __shared__ uint32_t s_tmem;
-  // per-pixel geometry of the current / next tap (double buffered by tap parity): the gather is
-  // done by 8 lanes per pixel (one 16-byte chunk each), so one warp-wide load touches 4 full
-  // 128-byte lines instead of 32 partial ones
-  __shared__ int4 s_geo_o[2][kTileM];
-  __shared__ float4 s_geo_w[2][kTileM];
+  __shared__ __align__(16) float s_sc[256], s_sh[256];         // epilogue: y = acc * sc[c] + sh[c]
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int Cin = prm.Cin, Cout = prm.Cout;
+  const int Cin = prm.Cin, Cout = prm.Cout, NS = prm.stages;
   const int P = prm.Ho * prm.Wo, Pin = prm.H * prm.W;
-  int tile = blockIdx.x;
-  const int b = tile / prm.tiles_per_image;
-  tile -= b * prm.tiles_per_image;
-  const int tile_y = tile / prm.tiles_x, tile_x = tile - tile_y * prm.tiles_x;
-  // geometry role: thread r and thread r+128 both describe tile row r (pixel ty = r/16, tx = r%16)
-  const int r = tid & (kTileM - 1);
-  const int ho = tile_y * kTileH + (r >> 4), wo = tile_x * kTileW + (r & 15);
-  const bool valid = ho < prm.Ho && wo < prm.Wo;
-  const int p = valid ? ho * prm.Wo + wo : 0;
-  const uint32_t stage_bytes = (uint32_t)kTileM * kBK * 2u + (uint32_t)Cout * kBK * 2u;   // A tile + Wk tile
+  const uint32_t a_bytes = (uint32_t)kTileM * kBK * 2u, b_bytes = (uint32_t)Cout * kBK * 2u;
+  const uint32_t stage_bytes = a_bytes + b_bytes;
   // dynamic shared memory is only guaranteed 16-byte aligned: round up to the 1024-byte swizzle atom
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(dcn_smem) + 1023) & ~(uintptr_t)1023);
-
-  const int cpb = Cin / kBK;                     // K blocks per tap
+  // (pointer arithmetic on the array itself, so the compiler keeps the shared address space)
+  uint8_t* smem = dcn_smem + ((1024u - (smem_u32(dcn_smem) & 1023u)) & 1023u);
+  uint4* geo_w = reinterpret_cast<uint4*>(smem + (size_t)NS * stage_bytes);          // [2][9][128]
+  uint32_t* geo_g = reinterpret_cast<uint32_t*>(geo_w + 2 * 9 * kTileM);             // [2][9][128]
+  const int cpb = Cin / kBK;                     // channel blocks
   const int KB = 9 * cpb;
-  const size_t Ktot = (size_t)9 * Cin;
-  const __nv_bfloat16* xb = prm.xh + (size_t)b * Pin * Cin;
-  const float* offb = prm.offset + (size_t)b * 18 * P;
-  const float* mskb = prm.mask + (size_t)b * 9 * P;
+  // each CTA owns a contiguous run of tiles (row-major inside an image): consecutive tiles share
+  // their halo columns in L1
+  const int tile_first = (int)(((long long)blockIdx.x * prm.num_tiles) / gridDim.x);
+  const int my_tiles = (int)(((long long)(blockIdx.x + 1) * prm.num_tiles) / gridDim.x) - tile_first;
+  const int tile_step = 1, tile_base = tile_first;
 
   if (tid == 0) {
-    for (int s = 0; s < kStages; ++s) dcn_mbar_init(&s_bar[s], 1);
+    for (int s = 0; s < NS; ++s) { dcn_mbar_init(&bars.full[s], NP + 1); dcn_mbar_init(&bars.empty[s], 1); }
+    for (int i = 0; i < 2; ++i) {
+      dcn_mbar_init(&bars.geo_full[i], 4);  dcn_mbar_init(&bars.geo_empty[i], NP);
+      dcn_mbar_init(&bars.acc_full[i], 1);  dcn_mbar_init(&bars.acc_empty[i], 4);
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 0) tmem_alloc(&s_tmem, prm.tmem_cols);
-  if (tid < kTileM) {                            // tap 0
-    int4 o; float4 wq;
-    tap_geometry(prm, offb, mskb, P, p, ho, wo, valid, 0, o, wq);
-    s_geo_o[0][r] = o; s_geo_w[0][r] = wq;
+  for (int c = tid; c < Cout; c += blockDim.x) {
+    const float sc = prm.scale ? __ldg(prm.scale + c) : 1.f;
+    const float bi = prm.bias ? __ldg(prm.bias + c) : 0.f;
+    s_sc[c] = sc;
+    s_sh[c] = prm.scale ? bi * sc + __ldg(prm.shift + c) : bi;
   }
+  if (warp == NP + 8) tmem_alloc(&s_tmem, prm.tmem_cols);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = s_tmem;
-  const uint32_t idesc = make_idesc_bf16(kTileM, Cout);
-  const int sub = lane >> 3, chunk = lane & 7;   // 4 pixels x 8 chunks per warp-wide load
+  const uint32_t acc_stride = prm.tmem_cols >> 1;              // columns between the two accumulators
 
-  int t = 0, ci0 = 0;                            // tap and first channel of the current K block
-  for (int kb = 0; kb < KB; ++kb, ci0 += kBK) {
-    if (ci0 == Cin) { ci0 = 0; ++t; }
-    const int s = kb & (kStages - 1), use = kb / kStages;
-    if (kb >= kStages) dcn_mbar_wait(&s_bar[s], (unsigned)((use - 1) & 1));   // MMAs that read stage s retired
-    // the upper half of the CTA prepares the next tap's geometry (published by this block's barrier)
-    if (ci0 == 0 && t + 1 < 9 && tid >= kTileM) {
-      int4 o; float4 wq;
-      tap_geometry(prm, offb, mskb, P, p, ho, wo, valid, t + 1, o, wq);
-      s_geo_o[(t + 1) & 1][r] = o; s_geo_w[(t + 1) & 1][r] = wq;
-    }
-    uint8_t* a_tile = smem + (size_t)s * stage_bytes;
-    uint8_t* b_tile = a_tile + kTileM * kBK * 2;
-
-    // ---- A rows: warp w builds tile rows 16w .. 16w+15 in 4 passes of (4 pixels x 8 chunks) ------
-    {
-      const __nv_bfloat16* xc = xb + ci0 + chunk * 8;
-      const int4* go = s_geo_o[t & 1];
-      const float4* gw = s_geo_w[t & 1];
+  if (warp < NP) {
+    // ===================================== producers ==============================================
+    constexpr int ITERS = 32 / NP;               // 4-row groups per warp per K block
+    const int sub = lane >> 3, chunk = lane & 7;
+    const uint32_t swz = (uint32_t)((chunk ^ (((warp & 1) << 2) + sub)) << 4);      // row & 7 is fixed per thread
+    const uint32_t row0 = (uint32_t)(warp << 2) + sub;
+    const uint32_t ex = (uint32_t)Cin, ey = (uint32_t)prm.W * (uint32_t)Cin;
+    auto tile_x = [&](int it) {
+      const int tile = tile_base + it * tile_step;
+      return prm.xh + (size_t)(tile / prm.tiles_per_image) * Pin * Cin + chunk * 8;
+    };
+    uint4 va[ITERS], vb[ITERS], vc[ITERS], vd[ITERS];
+    auto gather = [&](int i, const __nv_bfloat16* xc, uint32_t g) {
+      const uint32_t e0 = g & ~3u;
+      const uint32_t dx = (g & 1u) ? ex : 0u;
+      const uint32_t e2 = e0 + ((g & 2u) ? ey : 0u);
+      va[i] = ldg_gather16(xc + e0);
+      vb[i] = ldg_gather16(xc + e0 + dx);
+      vc[i] = ldg_gather16(xc + e2);
+      vd[i] = ldg_gather16(xc + e2 + dx);
+    };
+    const int total = my_tiles * KB;
+    int l_it = 0, l_cb = 0, l_t = 0;             // load cursor: the K block whose gathers are in flight
+    const __nv_bfloat16* l_x = tile_x(0);
+    if (total > 0) {
+      dcn_mbar_wait(&bars.geo_full[0], 0u);
 #pragma unroll
-      for (int it = 0; it < 4; ++it) {
-        const int row = (warp << 4) + (it << 2) + sub;
-        const int4 o = go[row];
-        const float4 wq = gw[row];
-        const uint4 a = __ldg(reinterpret_cast<const uint4*>(xc + (size_t)o.x * Cin));
-        const uint4 bq = __ldg(reinterpret_cast<const uint4*>(xc + (size_t)o.y * Cin));
-        const uint4 cq = __ldg(reinterpret_cast<const uint4*>(xc + (size_t)o.z * Cin));
-        const uint4 d = __ldg(reinterpret_cast<const uint4*>(xc + (size_t)o.w * Cin));
+      for (int i = 0; i < ITERS; ++i) gather(i, l_x, geo_g[row0 + i * NP * 4]);
+    }
+    int s = 0; unsigned ph = 0;
+    for (int n = 0; n < total; ++n) {
+      const int c_it = l_it, c_t = l_t;          // consume cursor = the block that is in flight now
+      const bool have_next = n + 1 < total;
+      if (++l_t == 9) {
+        l_t = 0;
+        if (++l_cb == cpb) {
+          l_cb = 0; ++l_it;
+          if (have_next) {
+            l_x = tile_x(l_it);
+            dcn_mbar_wait(&bars.geo_full[l_it & 1], (unsigned)((l_it >> 1) & 1));
+          }
+        }
+      }
+      const __nv_bfloat16* l_xc = l_x + l_cb * kBK;
+      const uint32_t* gg = geo_g + ((l_it & 1) * 9 + l_t) * kTileM + row0;
+      const uint4* gw = geo_w + ((c_it & 1) * 9 + c_t) * kTileM + row0;
+      dcn_mbar_wait(&bars.empty[s], ph ^ 1u);
+      uint8_t* a_tile = smem + (size_t)s * stage_bytes;
+#pragma unroll
+      for (int i = 0; i < ITERS; ++i) {
+        const uint4 wq = gw[i * NP * 4];
         uint4 q;
         if (kFp32Blend) {
-          q.x = blend_fp32(a.x, bq.x, cq.x, d.x, wq.x, wq.y, wq.z, wq.w);
-          q.y = blend_fp32(a.y, bq.y, cq.y, d.y, wq.x, wq.y, wq.z, wq.w);
-          q.z = blend_fp32(a.z, bq.z, cq.z, d.z, wq.x, wq.y, wq.z, wq.w);
-          q.w = blend_fp32(a.w, bq.w, cq.w, d.w, wq.x, wq.y, wq.z, wq.w);
+          const float w1 = __uint_as_float(wq.x), w2 = __uint_as_float(wq.y),
+                      w3 = __uint_as_float(wq.z), w4 = __uint_as_float(wq.w);
+          q.x = blend_fp32(va[i].x, vb[i].x, vc[i].x, vd[i].x, w1, w2, w3, w4);
+          q.y = blend_fp32(va[i].y, vb[i].y, vc[i].y, vd[i].y, w1, w2, w3, w4);
+          q.z = blend_fp32(va[i].z, vb[i].z, vc[i].z, vd[i].z, w1, w2, w3, w4);
+          q.w = blend_fp32(va[i].w, vb[i].w, vc[i].w, vd[i].w, w1, w2, w3, w4);
         } else {
-          const __nv_bfloat162 q1 = __float2bfloat162_rn(wq.x), q2 = __float2bfloat162_rn(wq.y),
-                               q3 = __float2bfloat162_rn(wq.z), q4 = __float2bfloat162_rn(wq.w);
-          q.x = blend_bf16x2(a.x, bq.x, cq.x, d.x, q1, q2, q3, q4);
-          q.y = blend_bf16x2(a.y, bq.y, cq.y, d.y, q1, q2, q3, q4);
-          q.z = blend_bf16x2(a.z, bq.z, cq.z, d.z, q1, q2, q3, q4);
-          q.w = blend_bf16x2(a.w, bq.w, cq.w, d.w, q1, q2, q3, q4);
+          q.x = blend_bf16x2(va[i].x, vb[i].x, vc[i].x, vd[i].x, wq.x, wq.y, wq.z, wq.w);
+          q.y = blend_bf16x2(va[i].y, vb[i].y, vc[i].y, vd[i].y, wq.x, wq.y, wq.z, wq.w);
+          q.z = blend_bf16x2(va[i].z, vb[i].z, vc[i].z, vd[i].z, wq.x, wq.y, wq.z, wq.w);
+          q.w = blend_bf16x2(va[i].w, vb[i].w, vc[i].w, vd[i].w, wq.x, wq.y, wq.z, wq.w);
         }
-        *reinterpret_cast<uint4*>(a_tile + row * 128 + ((chunk ^ (row & 7)) << 4)) = q;
+        *reinterpret_cast<uint4*>(a_tile + (row0 + (uint32_t)(i * NP * 4)) * 128u + swz) = q;
+        if (have_next) gather(i, l_xc, gg[i * NP * 4]);        // refill the slot: K block n+1, same row group
       }
-    }
-    // ---- Wk block [Cout][64], same swizzle --------------------------------------------------------
-    {
-      const __nv_bfloat16* wsrc = prm.wk + (size_t)kb * kBK;
-      for (int idx = tid; idx < Cout * 8; idx += kDcnThreads) {
-        const int n = idx >> 3, ch = idx & 7;
-        const uint4 v = __ldg(reinterpret_cast<const uint4*>(wsrc + (size_t)n * Ktot) + ch);
-        *reinterpret_cast<uint4*>(b_tile + n * 128 + ((ch ^ (n & 7)) << 4)) = v;
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> tensor-core reads
+      __syncwarp();
+      if (lane == 0) {
+        dcn_mbar_arrive(&bars.full[s]);
+        if (l_it != c_it) dcn_mbar_arrive(&bars.geo_empty[c_it & 1]);   // tile c_it fully consumed by this warp
       }
+      if (++s == NS) { s = 0; ph ^= 1u; }
     }
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> tensor core reads
-    __syncthreads();
-    if (tid == 0) {
+  } else if (warp < NP + 4) {
+    // ===================================== epilogue ===============================================
+    const int quarter = warp - NP;                                        // == warp % 4: TMEM lane quarter
+    const int r = (quarter << 5) + lane;                                  // tile row = TMEM lane
+    const int relu = prm.relu;
+    for (int j = 0; j < my_tiles; ++j) {
+      const int ab = j & 1;
+      int tile = tile_base + j * tile_step;
+      const int b = tile / prm.tiles_per_image;
+      tile -= b * prm.tiles_per_image;
+      const int tile_y = tile / prm.tiles_x, tile_x = tile - tile_y * prm.tiles_x;
+      const int eho = tile_y * kTileH + (r >> 4), ewo = tile_x * kTileW + (r & 15);
+      const bool evalid = eho < prm.Ho && ewo < prm.Wo;
+      float* yp = prm.y + (size_t)b * Cout * P + (evalid ? eho * prm.Wo + ewo : 0);
+      dcn_mbar_wait_relaxed(&bars.acc_full[ab], (unsigned)((j >> 1) & 1));
       tc_fence_after();
-      const uint64_t adesc = make_sw128_desc(smem_u32(a_tile));
-      const uint64_t bdesc = make_sw128_desc(smem_u32(b_tile));
+      const uint32_t tbase = tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)ab * acc_stride;
+      for (int c0 = 0; c0 < Cout; c0 += 16) {
+        uint32_t v[16];
+        tmem_ld16(tbase + (uint32_t)c0, v);
+        float sc[16], sh[16];
 #pragma unroll
-      for (int k4 = 0; k4 < kBK / 16; ++k4)      // +32 bytes (16 bf16) along K inside the swizzle row
-        umma_bf16(tmem, adesc + 2 * k4, bdesc + 2 * k4, idesc, (uint32_t)((kb | k4) != 0));
-      umma_commit(&s_bar[s]);
+        for (int k = 0; k < 4; ++k) {
+          *reinterpret_cast<float4*>(&sc[4 * k]) = *reinterpret_cast<const float4*>(&s_sc[c0 + 4 * k]);
+          *reinterpret_cast<float4*>(&sh[4 * k]) = *reinterpret_cast<const float4*>(&s_sh[c0 + 4 * k]);
+        }
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+          float q = fmaf(__uint_as_float(v[k]), sc[k], sh[k]);
+          if (relu) q = fmaxf(q, 0.f);
+          if (evalid) *yp = q;
+          yp += P;
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) dcn_mbar_arrive(&bars.acc_empty[ab]);
     }
-  }
-  // ---- drain: the last commit covers every MMA issued before it --------------------------------
-  {
-    const int last = KB - 1;
-    dcn_mbar_wait(&s_bar[last % kStages], (unsigned)((last / kStages) & 1));
-    tc_fence_after();
-  }
-  // ---- epilogue: TMEM -> registers -> bias / affine / ReLU -> NCHW fp32 ---------------------------
-  // warp w may only read TMEM lanes 32*(w%4) .. +31; the two warps of a lane quarter split the
-  // 16-column groups between them
-  {
-    const int quarter = warp & 3, half = warp >> 2;
-    const int er = (quarter << 5) + lane;                       // tile row = TMEM lane of this thread
-    const int eho = tile_y * kTileH + (er >> 4), ewo = tile_x * kTileW + (er & 15);
-    const bool evalid = eho < prm.Ho && ewo < prm.Wo;
-    float* yb = prm.y + (size_t)b * Cout * P + (evalid ? eho * prm.Wo + ewo : 0);
-    for (int c0 = half * 16; c0 < Cout; c0 += 32) {
-      uint32_t v[16];
-      tmem_ld16(tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)c0, v);
+  } else if (warp < NP + 8) {
+    // ===================================== geometry ===============================================
+    const int r = ((warp - NP - 4) << 5) + lane;                          // tile row = pixel of the tile
+    for (int it = 0; it < my_tiles; ++it) {
+      int tile = tile_base + it * tile_step;
+      const int b = tile / prm.tiles_per_image;
+      tile -= b * prm.tiles_per_image;
+      const int tile_y = tile / prm.tiles_x, tile_x = tile - tile_y * prm.tiles_x;
+      const int ho = tile_y * kTileH + (r >> 4), wo = tile_x * kTileW + (r & 15);
+      const bool valid = ho < prm.Ho && wo < prm.Wo;
+      const int p = valid ? ho * prm.Wo + wo : 0;
+      const float* offb = prm.offset + (size_t)b * 18 * P + p;
+      const float* mskb = prm.mask + (size_t)b * 9 * P + p;
+      const int buf = it & 1;
+      // all 27 loads first (one DRAM round trip, issued before the buffer is even free)
+      float ov[18], mv[9];
 #pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        float q = __uint_as_float(v[j]);
-        if (prm.bias) q += __ldg(prm.bias + c0 + j);
-        if (prm.scale) q = q * __ldg(prm.scale + c0 + j) + __ldg(prm.shift + c0 + j);
-        if (prm.relu) q = fmaxf(q, 0.f);
-        if (evalid) yb[(size_t)(c0 + j) * P] = q;
+      for (int k = 0; k < 18; ++k) ov[k] = ldg_stream1(offb + (size_t)k * P);
+#pragma unroll
+      for (int k = 0; k < 9; ++k) mv[k] = ldg_stream1(mskb + (size_t)k * P);
+      dcn_mbar_wait_relaxed(&bars.geo_empty[buf], (unsigned)(((it >> 1) & 1) ^ 1));
+#pragma unroll
+      for (int t = 0; t < 9; ++t) {
+        uint32_t g; uint4 wq;
+        tap_geometry<kFp32Blend>(prm, ov[2 * t], ov[2 * t + 1], mv[t], ho, wo, valid, t, g, wq);
+        geo_w[(buf * 9 + t) * kTileM + r] = wq;
+        geo_g[(buf * 9 + t) * kTileM + r] = g;
+      }
+      __syncwarp();
+      if (lane == 0) dcn_mbar_arrive(&bars.geo_full[buf]);
+    }
+  } else if (warp == NP + 8) {
+    // ===================================== MMA issuer =============================================
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_bf16(kTileM, Cout);
+      int s = 0; unsigned ph = 0;
+      for (int it = 0; it < my_tiles; ++it) {
+        const int ab = it & 1;
+        dcn_mbar_wait(&bars.acc_empty[ab], (unsigned)(((it >> 1) & 1) ^ 1));   // epilogue drained this buffer
+        tc_fence_after();
+        const uint32_t d_tmem = tmem + (uint32_t)ab * acc_stride;
+        for (int kb = 0; kb < KB; ++kb) {
+          dcn_mbar_wait_relaxed(&bars.full[s], ph, (unsigned)prm.mma_sleep);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smem + (size_t)s * stage_bytes);
+          const uint64_t adesc = make_sw128_desc(a_addr);
+          const uint64_t bdesc = make_sw128_desc(a_addr + a_bytes);
+#pragma unroll
+          for (int k4 = 0; k4 < kBK / 16; ++k4)      // +32 bytes (16 bf16) along K inside the swizzle row
+            umma_bf16(d_tmem, adesc + 2 * k4, bdesc + 2 * k4, idesc, (uint32_t)((kb | k4) != 0));
+          umma_commit(&bars.empty[s]);               // arrives when the MMAs above have read the stage
+          if (++s == NS) { s = 0; ph ^= 1u; }
+        }
+        umma_commit(&bars.acc_full[ab]);             // accumulator of tile it complete
       }
     }
+    __syncwarp();
+  } else {
+    // ===================================== B-tile loader ==========================================
+    if (lane == 0) {
+      int s = 0; unsigned ph = 0;
+      for (int it = 0; it < my_tiles; ++it) {
+        for (int kb = 0; kb < KB; ++kb) {
+          dcn_mbar_wait_relaxed(&bars.empty[s], ph ^ 1u, (unsigned)prm.ld_sleep);
+          dcn_mbar_arrive_expect_tx(&bars.full[s], b_bytes);
+          dcn_bulk_g2s(smem + (size_t)s * stage_bytes + a_bytes, prm.wk + (size_t)kb * Cout * kBK, b_bytes, &bars.full[s]);
+          if (++s == NS) { s = 0; ph ^= 1u; }
+        }
+      }
+    }
+    __syncwarp();
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem, prm.tmem_cols);
+  if (warp == NP + 8) tmem_dealloc(tmem, prm.tmem_cols);
 }
 
 }  // namespace ctdet
@@ -367,6 +537,11 @@ static inline size_t dcn_align256(size_t v) { return (v + 255) / 256 * 256; }
 extern "C" size_t dcnv2_workspace_bytes(int B, int Cin, int H, int W, int Cout) {
   if (B <= 0 || Cin <= 0 || H <= 0 || W <= 0 || Cout <= 0) return 0;
   return dcn_align256((size_t)B * H * W * Cin * 2) + dcn_align256((size_t)Cout * Cin * 9 * 2);
+}
+
+static int dcn_env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return (v && *v) ? atoi(v) : dflt;
 }
 
 extern "C" int dcnv2_forward(const float* input, const float* weight, const float* bias,
@@ -393,7 +568,7 @@ extern "C" int dcnv2_forward(const float* input, const float* weight, const floa
   if (!input || !weight || !offset || !mask || !output || !workspace) return CTDET_ENULL;
   if (workspace_bytes < dcnv2_workspace_bytes(B, Cin, H, W, Cout)) return CTDET_EWORKSPACE;
   if (reinterpret_cast<uintptr_t>(workspace) & 15u) return CTDET_EALIGN;
-  if ((size_t)H * W >= ((size_t)1 << 31) / (size_t)Cin) return CTDET_EINVAL;
+  if ((size_t)H * W >= ((size_t)1 << 31) / (size_t)Cin) return CTDET_EINVAL;     // 32-bit element offsets per image
   cudaStream_t st = (cudaStream_t)stream;
 
   __nv_bfloat16* xh = reinterpret_cast<__nv_bfloat16*>(workspace);
@@ -416,15 +591,34 @@ extern "C" int dcnv2_forward(const float* input, const float* weight, const floa
   prm.stride = stride_h; prm.pad = pad_h; prm.dil = dilation_h; prm.relu = (flags & DCN_FLAG_RELU) ? 1 : 0;
   prm.tiles_x = (Wo + kTileW - 1) / kTileW;
   prm.tiles_per_image = prm.tiles_x * ((Ho + kTileH - 1) / kTileH);
-  uint32_t cols = 32;
-  while (cols < (uint32_t)Cout) cols <<= 1;                  // TMEM allocations are powers of two >= 32
-  prm.tmem_cols = cols;
-  const size_t smem = (size_t)kStages * (kTileM * kBK * 2 + (size_t)Cout * kBK * 2) + 1024;
-  auto kern = (flags & DCN_FLAG_FP32_BLEND) ? dcn_forward_kernel<true> : dcn_forward_kernel<false>;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
   const long long tiles = (long long)B * prm.tiles_per_image;
   if (tiles > 0x7fffffffLL) return CTDET_EINVAL;
-  kern<<<(unsigned)tiles, kDcnThreads, smem, st>>>(prm);
+  prm.num_tiles = (int)tiles;
+  uint32_t cols = 32;
+  while (cols < 2u * (uint32_t)Cout) cols <<= 1;             // two accumulators; TMEM allocations are powers of two >= 32
+  prm.tmem_cols = cols;
+  // pipeline depth: as many stages as fit beside the geometry buffers, capped -- every KB of shared
+  // memory is a KB less L1 for the gathers
+  const size_t stage_bytes = (size_t)kTileM * kBK * 2 + (size_t)Cout * kBK * 2;
+  const size_t budget = 230 * 1024 - 1024 - kGeoBytes;
+  int stages = (int)(budget / stage_bytes);
+  const int cap = dcn_env_int("CTDET_DCN_STAGES", 4);
+  if (stages > cap) stages = cap;
+  if (stages > kMaxStages) stages = kMaxStages;
+  if (stages < 2) return CTDET_EUNSUPPORTED;
+  prm.stages = stages;
+  prm.mma_sleep = dcn_env_int("CTDET_DCN_MMA_SLEEP", 0);
+  prm.ld_sleep = dcn_env_int("CTDET_DCN_LD_SLEEP", 20);
+  const size_t smem = (size_t)stages * stage_bytes + kGeoBytes + 1024;
+  const int np = dcn_env_int("CTDET_DCN_PRODUCER_WARPS", 16);
+  const bool f32 = (flags & DCN_FLAG_FP32_BLEND) != 0;
+  void (*kern)(const DcnParams) = nullptr;
+  if (np == 16) kern = f32 ? dcn_forward_kernel<true, 16> : dcn_forward_kernel<false, 16>;
+  else          kern = f32 ? dcn_forward_kernel<true, 8> : dcn_forward_kernel<false, 8>;
+  const int threads = ((np == 16 ? 16 : 8) + 10) * 32;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
+  const unsigned grid = (unsigned)(tiles < kNumSMs ? tiles : kNumSMs);
+  kern<<<grid, threads, smem, st>>>(prm);
   return check_launch();
 }
