@@ -11,7 +11,7 @@ from .target import gen_heatmap, gen_heatmap_batch                              
 from .losses import FocalLoss, RegL1Loss, _neg_loss, ctdet_losses                      # noqa: F401
 from .decode import (ctdet_decode, ctdet_decode_batch, _nms, _topk, _transpose_and_gather_feat,   # noqa: F401
                      postprocess_batch)
-from .deform_conv import DCN, DeformConvV2, ModulatedDeformConv, modulated_deform_conv, dcnv2_forward   # noqa: F401
+from .deform_conv import DCN, DeformConvV2, ModulatedDeformConv, modulated_deform_conv, dcnv2_forward, dcnv2_backward   # noqa: F401
 from .structures import Boxes, Instances                                               # noqa: F401
 from .centernet import CenterNetHotPath                                                # noqa: F401
 from .config import get_cfg                                                            # noqa: F401

@@ -25,22 +25,18 @@
 //     coalesced NCHW fp32 stores.
 // Border rule identical to the reference: a tap samples iff h_im > -1 && w_im > -1 && h_im < H &&
 // w_im < W (:852); each bilinear corner outside the image contributes 0 (:683-693).
-#include <cuda_bf16.h>
-#include <cstdlib>
-#include "common.cuh"
+#include "dcn_common.cuh"
 
 namespace ctdet {
 
-constexpr int kTileM = 128;           // pixels per tile = TMEM lanes = UMMA M
-constexpr int kTileH = 8, kTileW = 16; // 2-D pixel tile
-constexpr int kBK = 64;               // K block: 64 bf16 = one 128-byte swizzle row
 
 // ------------------------------------------------------------------------------------------------
 // pre-pass 1: NCHW fp32 -> NHWC bf16.  One CTA transposes a 64-channel x 64-pixel block through
 // shared memory: float4 loads along the pixel axis, 16-byte (8-channel) stores along the channel
-// axis (C % 64 == 0 on this path).
+// axis (C % 64 == 0 on this path).  Optionally accumulates per-channel sums over (batch, pixels).
 __global__ void __launch_bounds__(256)
-dcn_pack_input_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ xh, int C, int P, int vec) {
+dcn_pack_input_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ xh, int C, int P, int vec,
+                      float* __restrict__ chan_sum) {
   __shared__ __nv_bfloat16 t[64][64 + 8];                 // [pixel][channel], padded rows (144 B)
   const int b = blockIdx.z, c0 = blockIdx.y * 64, p0 = blockIdx.x * 64;
   const float* src = x + (size_t)b * C * P;
@@ -62,6 +58,12 @@ dcn_pack_input_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ x
         if (p + 2 < P) v.z = __ldg(sp + 2);
         if (p + 3 < P) v.w = __ldg(sp + 3);
       }
+    }
+    if (chan_sum) {                                       // per-channel sums (grad_bias of the backward):
+      float sum = (v.x + v.y) + (v.z + v.w);              // 16 consecutive lanes share one channel
+#pragma unroll
+      for (int o = 8; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+      if (q == 0 && c0 + c < C) atomicAdd(chan_sum + c0 + c, sum);
     }
     t[q * 4 + 0][c] = __float2bfloat16_rn(v.x);
     t[q * 4 + 1][c] = __float2bfloat16_rn(v.y);
@@ -97,184 +99,6 @@ __global__ void dcn_pack_weight_kernel(const float* __restrict__ w, __nv_bfloat1
         __float2bfloat16_rn(w[((size_t)n * Cin + ci) * 9 + t]);
   }
 }
-
-// ------------------------------------------------------------------------------------------------
-// tcgen05 / mbarrier plumbing (raw PTX; SASS: UTCHMMA, LDTM, UTCBAR)
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void dcn_mbar_init(uint64_t* bar, unsigned count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void dcn_mbar_wait(uint64_t* bar, unsigned parity) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "WAIT_%=:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-      "@p bra DONE_%=;\n\t"
-      "bra WAIT_%=;\n\t"
-      "DONE_%=:\n\t}"
-      :: "r"(smem_u32(bar)), "r"(parity) : "memory");
-}
-__device__ __forceinline__ void tmem_alloc(uint32_t* slot, uint32_t ncols) {      // whole warp
-  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smem_u32(slot)), "r"(ncols) : "memory");
-  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t ncols) {     // whole warp
-  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(addr), "r"(ncols) : "memory");
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-      :: "r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
-}
-__device__ __forceinline__ void umma_commit(uint64_t* bar) {                      // arrives when all prior MMAs retire
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {     // 32 lanes x 16 columns
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
-      : "r"(taddr));
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-}
-
-// K-major, 128-byte-swizzled operand tile (rows of 64 bf16 = 128 B, 8-row groups 1024 B apart):
-// start address >> 4 | LBO (unused for swizzled K-major, 1) | SBO = 1024 B | version 1 | SWIZZLE_128B
-__device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr) {
-  return (uint64_t)((smem_addr >> 4) & 0x3fffu) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) |
-         (1ull << 46) | (2ull << 61);
-}
-// kind::f16 instruction descriptor: D = fp32, A = B = bf16, both K-major, N>>3 at [17,23), M>>4 at [24,29)
-__device__ __forceinline__ uint32_t make_idesc_bf16(int M, int N) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
-}
-
-// waiters that are idle most of the time back off between polls: every poll is a shared-memory
-// pipe transaction that competes with the producers' A-tile stores
-__device__ __forceinline__ void dcn_mbar_wait_relaxed(uint64_t* bar, unsigned parity, unsigned ns = 64) {
-  const uint32_t addr = smem_u32(bar);
-  for (;;) {
-    uint32_t ok;
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(ok) : "r"(addr), "r"(parity) : "memory");
-    if (ok) break;
-    if (ns) __nanosleep(ns);
-  }
-}
-__device__ __forceinline__ void dcn_mbar_arrive(uint64_t* bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void dcn_mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-// 1-D bulk async copy global -> shared (TMA engine, no LSU instructions), completion on an mbarrier
-__device__ __forceinline__ void dcn_bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-               :: "r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
-}
-
-// ------------------------------------------------------------------------------------------------
-struct DcnParams {
-  const __nv_bfloat16* xh;     // [B][H*W][Cin]
-  const float* offset;         // [B][18][Ho*Wo]   channel 2t = dh, 2t+1 = dw (deform_conv_cuda_kernel.cu:838-846)
-  const float* mask;           // [B][9][Ho*Wo]
-  const __nv_bfloat16* wk;     // [9*Cin/64][Cout][64] swizzled B tiles
-  const float* bias;           // [Cout] or null
-  const float* scale;          // [Cout] or null   y = (conv + bias) * scale + shift
-  const float* shift;          // [Cout] or null
-  float* y;                    // [B][Cout][Ho*Wo]
-  int Cin, H, W, Ho, Wo, Cout, stride, pad, dil, relu, tiles_per_image, tiles_x, num_tiles, stages, mma_sleep, ld_sleep;
-  uint32_t tmem_cols;
-};
-
-__device__ __forceinline__ uint32_t blend_bf16x2(uint32_t a, uint32_t b, uint32_t c, uint32_t d,
-                                                 uint32_t w1, uint32_t w2, uint32_t w3, uint32_t w4) {
-  __nv_bfloat162 acc = __hmul2(*reinterpret_cast<__nv_bfloat162*>(&w1), *reinterpret_cast<__nv_bfloat162*>(&a));
-  acc = __hfma2(*reinterpret_cast<__nv_bfloat162*>(&w2), *reinterpret_cast<__nv_bfloat162*>(&b), acc);
-  acc = __hfma2(*reinterpret_cast<__nv_bfloat162*>(&w3), *reinterpret_cast<__nv_bfloat162*>(&c), acc);
-  acc = __hfma2(*reinterpret_cast<__nv_bfloat162*>(&w4), *reinterpret_cast<__nv_bfloat162*>(&d), acc);
-  return *reinterpret_cast<uint32_t*>(&acc);
-}
-__device__ __forceinline__ uint32_t blend_fp32(uint32_t a, uint32_t b, uint32_t c, uint32_t d,
-                                               float w1, float w2, float w3, float w4) {
-  const float lo = w1 * __uint_as_float(a << 16) + w2 * __uint_as_float(b << 16) +
-                   w3 * __uint_as_float(c << 16) + w4 * __uint_as_float(d << 16);
-  const float hi = w1 * __uint_as_float(a & 0xffff0000u) + w2 * __uint_as_float(b & 0xffff0000u) +
-                   w3 * __uint_as_float(c & 0xffff0000u) + w4 * __uint_as_float(d & 0xffff0000u);
-  const __nv_bfloat162 r = __floats2bfloat162_rn(lo, hi);
-  return *reinterpret_cast<const uint32_t*>(&r);
-}
-
-// Sampling geometry of output pixel (ho, wo) for tap t (dmcn_im2col_bilinear, :666-699).
-//   g  = element offset of the clamped top-left corner pixel in the NHWC image (pixel * Cin, a
-//        multiple of 64) | bit0: the right corner is a different pixel | bit1: the bottom corner is
-//   wq = the four bilinear weights * mask (0 for corners outside the image); either fp32 or, for
-//        the packed blend, each rounded to bf16 and broadcast into both halves of a bf16x2
-template <bool kFp32Blend>
-__device__ __forceinline__ void tap_geometry(const DcnParams& prm, float off_h, float off_w, float m,
-                                             int ho, int wo, bool valid, int t, uint32_t& g, uint4& wout) {
-  g = 0u;
-  float4 wq = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (valid) {
-    const int H = prm.H, W = prm.W;
-    const int i = t / 3, j = t - 3 * i;
-    const float h_im = (float)(ho * prm.stride - prm.pad + i * prm.dil) + off_h;
-    const float w_im = (float)(wo * prm.stride - prm.pad + j * prm.dil) + off_w;
-    if (h_im > -1.f && w_im > -1.f && h_im < (float)H && w_im < (float)W) {       // :852
-      const int h_low = (int)floorf(h_im), w_low = (int)floorf(w_im);
-      const int h_high = h_low + 1, w_high = w_low + 1;
-      const float lh = h_im - (float)h_low, lw = w_im - (float)w_low;
-      const float hh = 1.f - lh, hw = 1.f - lw;
-      const bool t_ok = h_low >= 0, b_ok = h_high <= H - 1, l_ok = w_low >= 0, r_ok = w_high <= W - 1;
-      const int hl = max(h_low, 0), hh_i = min(h_high, H - 1), wl = max(w_low, 0), wh_i = min(w_high, W - 1);
-      g = (uint32_t)(hl * W + wl) * (uint32_t)prm.Cin | (wh_i != wl ? 1u : 0u) | (hh_i != hl ? 2u : 0u);
-      wq.x = (t_ok && l_ok) ? hh * hw * m : 0.f;
-      wq.y = (t_ok && r_ok) ? hh * lw * m : 0.f;
-      wq.z = (b_ok && l_ok) ? lh * hw * m : 0.f;
-      wq.w = (b_ok && r_ok) ? lh * lw * m : 0.f;
-    }
-  }
-  if (kFp32Blend) {
-    wout = make_uint4(__float_as_uint(wq.x), __float_as_uint(wq.y), __float_as_uint(wq.z), __float_as_uint(wq.w));
-  } else {
-    const __nv_bfloat162 q1 = __float2bfloat162_rn(wq.x), q2 = __float2bfloat162_rn(wq.y),
-                         q3 = __float2bfloat162_rn(wq.z), q4 = __float2bfloat162_rn(wq.w);
-    wout = make_uint4(*reinterpret_cast<const uint32_t*>(&q1), *reinterpret_cast<const uint32_t*>(&q2),
-                      *reinterpret_cast<const uint32_t*>(&q3), *reinterpret_cast<const uint32_t*>(&q4));
-  }
-}
-
-// 16-byte gather of 8 bf16 channels through L1 (volatile: keeps every gather of a K block ahead of
-// the blends, so 4 * ITERS loads are in flight per thread)
-__device__ __forceinline__ uint4 ldg_gather16(const __nv_bfloat16* p) {
-  uint4 v;
-  asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
-  return v;
-}
-
-__device__ __forceinline__ float ldg_stream1(const float* p) {      // read-once scalar, volatile = kept in order
-  float v;
-  asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(v) : "l"(p));
-  return v;
-}
-
-constexpr int kMaxStages = 8;
-constexpr int kGeoBytes = 2 * 9 * kTileM * (16 + 4);      // double-buffered {uint4 weights, u32 g} per (tap, pixel)
-
-struct DcnBarriers {
-  uint64_t full[kMaxStages];     // A rows written by the producer warps + B tile landed  -> MMA may read stage
-  uint64_t empty[kMaxStages];    // the MMAs that read the stage retired                  -> stage may be refilled
-  uint64_t geo_full[2], geo_empty[2];   // per-tile sampling geometry (all 9 taps) in shared memory
-  uint64_t acc_full[2], acc_empty[2];   // TMEM accumulator buffers
-};
 
 // ------------------------------------------------------------------------------------------------
 // Persistent, warp-specialised main kernel: one CTA per SM loops over 8 x 16 pixel tiles (128 = UMMA
@@ -341,80 +165,8 @@ dcn_forward_kernel(const DcnParams prm) {
 
   if (warp < NP) {
     // ===================================== producers ==============================================
-    constexpr int ITERS = 32 / NP;               // 4-row groups per warp per K block
-    const int sub = lane >> 3, chunk = lane & 7;
-    const uint32_t swz = (uint32_t)((chunk ^ (((warp & 1) << 2) + sub)) << 4);      // row & 7 is fixed per thread
-    const uint32_t row0 = (uint32_t)(warp << 2) + sub;
-    const uint32_t ex = (uint32_t)Cin, ey = (uint32_t)prm.W * (uint32_t)Cin;
-    auto tile_x = [&](int it) {
-      const int tile = tile_base + it * tile_step;
-      return prm.xh + (size_t)(tile / prm.tiles_per_image) * Pin * Cin + chunk * 8;
-    };
-    uint4 va[ITERS], vb[ITERS], vc[ITERS], vd[ITERS];
-    auto gather = [&](int i, const __nv_bfloat16* xc, uint32_t g) {
-      const uint32_t e0 = g & ~3u;
-      const uint32_t dx = (g & 1u) ? ex : 0u;
-      const uint32_t e2 = e0 + ((g & 2u) ? ey : 0u);
-      va[i] = ldg_gather16(xc + e0);
-      vb[i] = ldg_gather16(xc + e0 + dx);
-      vc[i] = ldg_gather16(xc + e2);
-      vd[i] = ldg_gather16(xc + e2 + dx);
-    };
-    const int total = my_tiles * KB;
-    int l_it = 0, l_cb = 0, l_t = 0;             // load cursor: the K block whose gathers are in flight
-    const __nv_bfloat16* l_x = tile_x(0);
-    if (total > 0) {
-      dcn_mbar_wait(&bars.geo_full[0], 0u);
-#pragma unroll
-      for (int i = 0; i < ITERS; ++i) gather(i, l_x, geo_g[row0 + i * NP * 4]);
-    }
-    int s = 0; unsigned ph = 0;
-    for (int n = 0; n < total; ++n) {
-      const int c_it = l_it, c_t = l_t;          // consume cursor = the block that is in flight now
-      const bool have_next = n + 1 < total;
-      if (++l_t == 9) {
-        l_t = 0;
-        if (++l_cb == cpb) {
-          l_cb = 0; ++l_it;
-          if (have_next) {
-            l_x = tile_x(l_it);
-            dcn_mbar_wait(&bars.geo_full[l_it & 1], (unsigned)((l_it >> 1) & 1));
-          }
-        }
-      }
-      const __nv_bfloat16* l_xc = l_x + l_cb * kBK;
-      const uint32_t* gg = geo_g + ((l_it & 1) * 9 + l_t) * kTileM + row0;
-      const uint4* gw = geo_w + ((c_it & 1) * 9 + c_t) * kTileM + row0;
-      dcn_mbar_wait(&bars.empty[s], ph ^ 1u);
-      uint8_t* a_tile = smem + (size_t)s * stage_bytes;
-#pragma unroll
-      for (int i = 0; i < ITERS; ++i) {
-        const uint4 wq = gw[i * NP * 4];
-        uint4 q;
-        if (kFp32Blend) {
-          const float w1 = __uint_as_float(wq.x), w2 = __uint_as_float(wq.y),
-                      w3 = __uint_as_float(wq.z), w4 = __uint_as_float(wq.w);
-          q.x = blend_fp32(va[i].x, vb[i].x, vc[i].x, vd[i].x, w1, w2, w3, w4);
-          q.y = blend_fp32(va[i].y, vb[i].y, vc[i].y, vd[i].y, w1, w2, w3, w4);
-          q.z = blend_fp32(va[i].z, vb[i].z, vc[i].z, vd[i].z, w1, w2, w3, w4);
-          q.w = blend_fp32(va[i].w, vb[i].w, vc[i].w, vd[i].w, w1, w2, w3, w4);
-        } else {
-          q.x = blend_bf16x2(va[i].x, vb[i].x, vc[i].x, vd[i].x, wq.x, wq.y, wq.z, wq.w);
-          q.y = blend_bf16x2(va[i].y, vb[i].y, vc[i].y, vd[i].y, wq.x, wq.y, wq.z, wq.w);
-          q.z = blend_bf16x2(va[i].z, vb[i].z, vc[i].z, vd[i].z, wq.x, wq.y, wq.z, wq.w);
-          q.w = blend_bf16x2(va[i].w, vb[i].w, vc[i].w, vd[i].w, wq.x, wq.y, wq.z, wq.w);
-        }
-        *reinterpret_cast<uint4*>(a_tile + (row0 + (uint32_t)(i * NP * 4)) * 128u + swz) = q;
-        if (have_next) gather(i, l_xc, gg[i * NP * 4]);        // refill the slot: K block n+1, same row group
-      }
-      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> tensor-core reads
-      __syncwarp();
-      if (lane == 0) {
-        dcn_mbar_arrive(&bars.full[s]);
-        if (l_it != c_it) dcn_mbar_arrive(&bars.geo_empty[c_it & 1]);   // tile c_it fully consumed by this warp
-      }
-      if (++s == NS) { s = 0; ph ^= 1u; }
-    }
+    dcn_producer_loop<kFp32Blend, NP>(prm, smem, stage_bytes, NS, geo_w, geo_g, bars, warp, lane,
+                                      tile_first, my_tiles, 0, KB);
   } else if (warp < NP + 4) {
     // ===================================== epilogue ===============================================
     const int quarter = warp - NP;                                        // == warp % 4: TMEM lane quarter
@@ -457,32 +209,9 @@ dcn_forward_kernel(const DcnParams prm) {
     // ===================================== geometry ===============================================
     const int r = ((warp - NP - 4) << 5) + lane;                          // tile row = pixel of the tile
     for (int it = 0; it < my_tiles; ++it) {
-      int tile = tile_base + it * tile_step;
-      const int b = tile / prm.tiles_per_image;
-      tile -= b * prm.tiles_per_image;
-      const int tile_y = tile / prm.tiles_x, tile_x = tile - tile_y * prm.tiles_x;
-      const int ho = tile_y * kTileH + (r >> 4), wo = tile_x * kTileW + (r & 15);
-      const bool valid = ho < prm.Ho && wo < prm.Wo;
-      const int p = valid ? ho * prm.Wo + wo : 0;
-      const float* offb = prm.offset + (size_t)b * 18 * P + p;
-      const float* mskb = prm.mask + (size_t)b * 9 * P + p;
-      const int buf = it & 1;
-      // all 27 loads first (one DRAM round trip, issued before the buffer is even free)
-      float ov[18], mv[9];
-#pragma unroll
-      for (int k = 0; k < 18; ++k) ov[k] = ldg_stream1(offb + (size_t)k * P);
-#pragma unroll
-      for (int k = 0; k < 9; ++k) mv[k] = ldg_stream1(mskb + (size_t)k * P);
-      dcn_mbar_wait_relaxed(&bars.geo_empty[buf], (unsigned)(((it >> 1) & 1) ^ 1));
-#pragma unroll
-      for (int t = 0; t < 9; ++t) {
-        uint32_t g; uint4 wq;
-        tap_geometry<kFp32Blend>(prm, ov[2 * t], ov[2 * t + 1], mv[t], ho, wo, valid, t, g, wq);
-        geo_w[(buf * 9 + t) * kTileM + r] = wq;
-        geo_g[(buf * 9 + t) * kTileM + r] = g;
-      }
+      dcn_geometry_tile<kFp32Blend>(prm, tile_first + it, it, r, geo_w, geo_g, bars);
       __syncwarp();
-      if (lane == 0) dcn_mbar_arrive(&bars.geo_full[buf]);
+      if (lane == 0) dcn_mbar_arrive(&bars.geo_full[it & 1]);
     }
   } else if (warp == NP + 8) {
     // ===================================== MMA issuer =============================================
@@ -539,10 +268,7 @@ extern "C" size_t dcnv2_workspace_bytes(int B, int Cin, int H, int W, int Cout) 
   return dcn_align256((size_t)B * H * W * Cin * 2) + dcn_align256((size_t)Cout * Cin * 9 * 2);
 }
 
-static int dcn_env_int(const char* name, int dflt) {
-  const char* v = getenv(name);
-  return (v && *v) ? atoi(v) : dflt;
-}
+using ctdet::dcn_env_int;
 
 extern "C" int dcnv2_forward(const float* input, const float* weight, const float* bias,
                              const float* offset, const float* mask, float* output,
@@ -577,7 +303,7 @@ extern "C" int dcnv2_forward(const float* input, const float* weight, const floa
   const int Pin = H * W;
   if (B > 65535) return CTDET_EINVAL;
   const int vec = (Pin % 4 == 0 && aligned16(input)) ? 1 : 0;          // float4 loads of the NCHW input
-  dcn_pack_input_kernel<<<dim3((Pin + 63) / 64, (Cin + 63) / 64, B), 256, 0, st>>>(input, xh, Cin, Pin, vec);
+  dcn_pack_input_kernel<<<dim3((Pin + 63) / 64, (Cin + 63) / 64, B), 256, 0, st>>>(input, xh, Cin, Pin, vec, nullptr);
   int rc = check_launch();
   if (rc) return rc;
   dcn_pack_weight_kernel<<<kNumSMs, 256, 0, st>>>(weight, wk, Cout, Cin);

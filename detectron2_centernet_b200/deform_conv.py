@@ -6,7 +6,7 @@
 
 Parameter names match the reference so state_dicts stay loadable: `conv.weight`, `conv.bias`,
 `conv.conv_offset_mask.{weight,bias}`, `actf.0.*`.
-Forward only in this round: the backward raises.
+The backward (`dcnv2_backward`) runs on the tensor cores as well.
 """
 import ctypes
 import math
@@ -70,17 +70,62 @@ def dcnv2_forward(input, offset, mask, weight, bias=None, stride=1, padding=0, d
     return out
 
 
+def dcnv2_backward(input, offset, mask, weight, grad_output, stride=1, padding=0, dilation=1, groups=1,
+                   deformable_groups=1, with_bias=True, need_input_grads=True, need_weight_grad=True):
+    """Low-level call: returns (grad_input, grad_offset, grad_mask, grad_weight, grad_bias); entries that were
+    not requested are None.  Mirrors `_ModulatedDeformConv.backward` (deform_conv.py:225-262)."""
+    if not grad_output.is_cuda:
+        raise NotImplementedError("Deformable Conv is not supported on CPUs!")
+    lib = _lib.load()
+    input, weight = _lib.f32c(input, "input"), _lib.f32c(weight, "weight")
+    offset, mask = _lib.f32c(offset, "offset"), _lib.f32c(mask, "mask")
+    grad_output = _lib.f32c(grad_output, "grad_output")
+    s, p, d = _pair(stride), _pair(padding), _pair(dilation)
+    B, Cin, H, W = input.shape
+    Cout, _, kh, kw = weight.shape
+    Ho, Wo = grad_output.shape[2], grad_output.shape[3]
+    if tuple(grad_output.shape) != (B, Cout, offset.shape[2], offset.shape[3]):
+        raise RuntimeError("grad_output shape %s does not match the forward output" % (tuple(grad_output.shape),))
+    dev = input.device
+    gi = go = gm = gw = gb = None
+    if need_input_grads:
+        gi, go, gm = torch.empty_like(input), torch.empty_like(offset), torch.empty_like(mask)
+    if need_weight_grad:
+        gw = torch.empty_like(weight)
+        gb = torch.empty(Cout, dtype=torch.float32, device=dev) if with_bias else None
+    if B == 0 or grad_output.numel() == 0:
+        return tuple(None if t is None else t.zero_() for t in (gi, go, gm, gw, gb))
+    nbytes = lib.dcnv2_backward_workspace_bytes(B, Cin, H, W, Cout, Ho, Wo)
+    ws = _workspace(max(nbytes, 16), dev)
+    with torch.cuda.device(dev):
+        rc = lib.dcnv2_backward(_lib.ptr(input), _lib.ptr(weight), _lib.ptr(offset), _lib.ptr(mask), _lib.ptr(grad_output),
+                                _lib.ptr(gi), _lib.ptr(gw), _lib.ptr(gb), _lib.ptr(go), _lib.ptr(gm),
+                                B, Cin, H, W, Cout, kh, kw, s[0], s[1], p[0], p[1], d[0], d[1], groups, deformable_groups, 0,
+                                _lib.ptr(ws), ctypes.c_size_t(ws.numel()), _lib.stream_ptr(dev))
+    _lib.check(rc, "dcnv2_backward")
+    return gi, go, gm, gw, gb
+
+
 class _ModulatedDeformConv(torch.autograd.Function):
     @staticmethod
     def forward(ctx, input, offset, mask, weight, bias=None, stride=1, padding=0, dilation=1, groups=1,
                 deformable_groups=1):
+        ctx.cfg = (stride, padding, dilation, groups, deformable_groups)
+        ctx.with_bias = bias is not None
+        if weight.requires_grad or mask.requires_grad or offset.requires_grad or input.requires_grad:
+            ctx.save_for_backward(input, offset, mask, weight)               # deform_conv.py:211
         return dcnv2_forward(input, offset, mask, weight, bias, stride, padding, dilation, groups, deformable_groups)
 
     @staticmethod
+    @torch.autograd.function.once_differentiable
     def backward(ctx, grad_output):
-        raise NotImplementedError(
-            "DCNv2 backward (modulated_deform_conv_cuda_backward, deform_conv_cuda.cu:929) is the next row of the "
-            "hot-path plan and is not built yet; use the forward under torch.no_grad()")
+        input, offset, mask, weight = ctx.saved_tensors
+        stride, padding, dilation, groups, dg = ctx.cfg
+        need_in = any(ctx.needs_input_grad[:3])
+        need_w = ctx.needs_input_grad[3] or (ctx.with_bias and ctx.needs_input_grad[4])
+        gi, go, gm, gw, gb = dcnv2_backward(input, offset, mask, weight, grad_output, stride, padding, dilation, groups,
+                                            dg, ctx.with_bias, need_in, need_w)
+        return gi, go, gm, gw, gb, None, None, None, None, None
 
 
 modulated_deform_conv = _ModulatedDeformConv.apply

@@ -22,6 +22,9 @@
  *   dcnv2_forward        detectron2/layers/csrc/deformable/deform_conv.h:262 modulated_deform_conv_forward
  *                        -> deform_conv_cuda.cu:804 modulated_deform_conv_cuda_forward
  *                        (im2col kernel deform_conv_cuda_kernel.cu:786 + addmm_ :904 + bias :924)
+ *   dcnv2_backward       deform_conv.h:314 modulated_deform_conv_backward
+ *                        -> deform_conv_cuda.cu:929 modulated_deform_conv_cuda_backward
+ *                        (col2im_coord deform_conv_cuda_kernel.cu:952, col2im :871, im2col :786, 3 GEMMs)
  */
 #ifndef CTDET_B200_H_
 #define CTDET_B200_H_
@@ -164,6 +167,29 @@ int dcnv2_forward(const float* input, const float* weight, const float* bias,
                   int stride_h, int stride_w, int pad_h, int pad_w, int dilation_h, int dilation_w,
                   int group, int deformable_group, const float* scale, const float* shift, int flags,
                   void* workspace, size_t workspace_bytes, ctdet_stream_t stream);
+
+/* ---------------------------------------------------------------- DCNv2 backward ---------
+ * Replaces modulated_deform_conv_backward (deform_conv.h:314-338; same argument meaning, minus the
+ * `ones`/`columns` scratch tensors and the unused `bias`).  All gradient outputs are OVERWRITTEN
+ * (the reference accumulates into caller-zeroed tensors, deform_conv.py:230-234 -- same result).
+ *   grad_output f32 [B,Cout,Ho,Wo]
+ *   grad_input  f32 [B,Cin,H,W]   grad_offset f32 [B,18,Ho,Wo]   grad_mask f32 [B,9,Ho,Wo]
+ *       -- produced together: pass all three or none (NULL)
+ *   grad_weight f32 [Cout,Cin,3,3] or NULL     grad_bias f32 [Cout] or NULL
+ * Operands (input, weight, grad_output and the column gradient) are rounded to bf16, accumulation
+ * is fp32 (tolerance: tests/test_gpu_dcn_bwd.py).  grad_input / grad_weight are accumulated with
+ * fp32 atomics, so their low bits vary from run to run -- exactly like the reference's col2im
+ * (deform_conv_cuda_kernel.cu:944).
+ * Supported: as dcnv2_forward, and Cout % 64 == 0.  flags must be 0.
+ * workspace: dcnv2_backward_workspace_bytes() bytes, 16-byte aligned, no initialisation needed. */
+size_t dcnv2_backward_workspace_bytes(int B, int Cin, int H, int W, int Cout, int Ho, int Wo);
+int dcnv2_backward(const float* input, const float* weight, const float* offset, const float* mask,
+                   const float* grad_output, float* grad_input, float* grad_weight, float* grad_bias,
+                   float* grad_offset, float* grad_mask,
+                   int B, int Cin, int H, int W, int Cout, int kernel_h, int kernel_w,
+                   int stride_h, int stride_w, int pad_h, int pad_w, int dilation_h, int dilation_w,
+                   int group, int deformable_group, int flags,
+                   void* workspace, size_t workspace_bytes, ctdet_stream_t stream);
 
 #ifdef __cplusplus
 }
