@@ -187,7 +187,386 @@ dcn_wgrad_kernel(const DcnParams prm, const DcnBwdParams bw) {
 }
 
 
-// HOST_PLACEHOLDER_DGRAD
+// ================================================================================================
+// dgrad: grad_input, grad_offset, grad_mask
+// ================================================================================================
+// weight [Cout][Cin][9] fp32 -> per K block kb = cb*9 + t, Cout/64 slabs of [64 ci][64 co] bf16
+// (K-major over co) in the 128-byte swizzled shared-memory image, moved by 1-D bulk copies.
+__global__ void dcn_pack_weight_t_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ wt,
+                                         int Cout, int Cin) {
+  const size_t n_el = (size_t)Cout * Cin * 9;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_el; i += (size_t)gridDim.x * blockDim.x) {
+    const int k = (int)(i & 63);                          // co inside the slab
+    const int n = (int)((i >> 6) & 63);                   // ci inside the block
+    const int j = (int)((i >> 12) % (Cout / 64));         // slab = 64-channel block of co
+    const int kb = (int)(i / ((size_t)Cout * 64));
+    const int cb = kb / 9, t = kb - 9 * cb;
+    wt[(size_t)kb * Cout * 64 + (size_t)j * 4096 + n * 64 + (((k >> 3) ^ (n & 7)) << 3) + (k & 7)] =
+        __float2bfloat16_rn(w[((size_t)(64 * j + k) * Cin + cb * 64 + n) * 9 + t]);
+  }
+}
+
+// grad_input NHWC fp32 -> NCHW fp32 (64 x 64 blocks through shared memory)
+__global__ void __launch_bounds__(256)
+dcn_unpack_grad_input_kernel(const float* __restrict__ gx, float* __restrict__ out, int C, int P) {
+  __shared__ float t[64][65];                             // [pixel][channel]
+  const int b = blockIdx.z, c0 = blockIdx.y * 64, p0 = blockIdx.x * 64;
+  const float* src = gx + (size_t)b * P * C;
+  float* dst = out + (size_t)b * C * P;
+  const int tid = threadIdx.x;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int idx = tid + k * 256;                        // 64 pixels x 16 float4 of channels
+    const int pp = idx >> 4, q = idx & 15;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (p0 + pp < P) v = *reinterpret_cast<const float4*>(src + (size_t)(p0 + pp) * C + c0 + q * 4);
+    t[pp][q * 4 + 0] = v.x; t[pp][q * 4 + 1] = v.y; t[pp][q * 4 + 2] = v.z; t[pp][q * 4 + 3] = v.w;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    const int idx = tid + k * 256;                        // 64 channels x 64 pixels
+    const int c = idx >> 6, pp = idx & 63;
+    if (p0 + pp < P) dst[(size_t)(c0 + c) * P + p0 + pp] = t[pp][c];
+  }
+}
+
+// Raw sampling geometry for the backward: {g, lh, lw, mask} with
+//   g = element offset of the clamped top-left corner (pixel * Cin, multiple of 64)
+//       | bit0: right corner is another pixel | bit1: bottom corner is another pixel
+//       | bit2: top row inside | bit3: bottom row inside | bit4: left column inside | bit5: right column inside
+// all zero when the tap falls outside (h_im <= -1 ... , dmcn_get_coordinate_weight :738-742).
+__device__ __forceinline__ uint4 tap_geometry_raw(const DcnParams& prm, float off_h, float off_w, float m,
+                                                  int ho, int wo, bool valid, int t) {
+  uint4 o = make_uint4(0u, 0u, 0u, 0u);
+  if (valid) {
+    const int H = prm.H, W = prm.W;
+    const int i = t / 3, j = t - 3 * i;
+    const float h_im = (float)(ho * prm.stride - prm.pad + i * prm.dil) + off_h;
+    const float w_im = (float)(wo * prm.stride - prm.pad + j * prm.dil) + off_w;
+    if (h_im > -1.f && w_im > -1.f && h_im < (float)H && w_im < (float)W) {
+      const int h_low = (int)floorf(h_im), w_low = (int)floorf(w_im);
+      const int h_high = h_low + 1, w_high = w_low + 1;
+      const bool t_ok = h_low >= 0, b_ok = h_high <= H - 1, l_ok = w_low >= 0, r_ok = w_high <= W - 1;
+      const int hl = max(h_low, 0), hh_i = min(h_high, H - 1), wl = max(w_low, 0), wh_i = min(w_high, W - 1);
+      o.x = (uint32_t)(hl * W + wl) * (uint32_t)prm.Cin | (wh_i != wl ? 1u : 0u) | (hh_i != hl ? 2u : 0u) |
+            (t_ok ? 4u : 0u) | (b_ok ? 8u : 0u) | (l_ok ? 16u : 0u) | (r_ok ? 32u : 0u);
+      o.y = __float_as_uint(h_im - (float)h_low);
+      o.z = __float_as_uint(w_im - (float)w_low);
+      o.w = __float_as_uint(m);
+    }
+  }
+  return o;
+}
+
+__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" :: "l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+__device__ __forceinline__ float bf_lo(uint32_t u) { return __uint_as_float(u << 16); }
+__device__ __forceinline__ float bf_hi(uint32_t u) { return __uint_as_float(u & 0xffff0000u); }
+__device__ __forceinline__ float dot8(const float (&g)[8], uint4 v) {
+  float d = g[0] * bf_lo(v.x);
+  d = fmaf(g[1], bf_hi(v.x), d); d = fmaf(g[2], bf_lo(v.y), d); d = fmaf(g[3], bf_hi(v.y), d);
+  d = fmaf(g[4], bf_lo(v.z), d); d = fmaf(g[5], bf_hi(v.z), d); d = fmaf(g[6], bf_lo(v.w), d);
+  return fmaf(g[7], bf_hi(v.w), d);
+}
+
+constexpr int kDgMaxRing = 4;
+struct DgradBarriers {
+  uint64_t geo_full[2], geo_empty[2];       // raw geometry of a tile               (geometry warps -> consumers)
+  uint64_t gout_full[2], gout_empty[2];     // grad_output tile                      (geometry warps -> MMA)
+  uint64_t wt_full[kDgMaxRing], wt_empty[kDgMaxRing];   // transposed weight tiles   (bulk copies   -> MMA)
+  uint64_t acc_full[2], acc_empty[2];       // TMEM column-gradient accumulators     (MMA -> transfer warps)
+  uint64_t g_full[kDgMaxRing], g_empty[kDgMaxRing];     // bf16 column-gradient tile (transfer -> consumers)
+};
+constexpr int kDgGeoBytes = 2 * 9 * kTileM * 16;
+constexpr int kDgAccBytes = 27 * kTileM * 4;
+
+// Persistent, warp-specialised dgrad kernel, one CTA per SM over 8 x 16 pixel tiles:
+//   warps [0, NP)        consumers: per K block read the bf16 column gradient G[128 px][64 ci] from shared
+//                        memory and the four corner vectors of x (8 lanes x 16 B per pixel, prefetched one
+//                        K block ahead like the forward's producer): 4 dot products -> grad_mask /
+//                        grad_offset (8-lane shuffle reduce), G * mask * corner weight -> grad_input (RED.v4)
+//   warps [NP, NP+4)     transfer: TMEM accumulator -> bf16 -> swizzled shared-memory G tile
+//   warps [NP+4, NP+8)   grad_output tile + raw sampling geometry of the tiles ahead (thread = pixel)
+//   warp  NP+8           one lane issues tcgen05.mma: G = gout[128 px, Cout] * Wt_kb[Cout, 64 ci]
+//   warp  NP+9           one lane streams the transposed weight tiles with 1-D bulk copies
+template <int NP>
+__global__ void __launch_bounds__((NP + 10) * 32, 1)
+dcn_dgrad_kernel(const DcnParams prm, const DcnBwdParams bw) {
+  static_assert(NP % 4 == 0 && 32 % NP == 0, "consumer warps must tile the 32 row groups");
+  extern __shared__ __align__(1024) uint8_t dcn_smem[];
+  __shared__ DgradBarriers bars;
+  __shared__ uint32_t s_tmem;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int Cin = prm.Cin, Cout = prm.Cout;
+  const int P = prm.Ho * prm.Wo, Pin = prm.H * prm.W;
+  const int NG = bw.g_stages, NW = bw.w_stages, GB = bw.gout_bufs;
+  const uint32_t gout_bytes = (uint32_t)(Cout / 64) * kTileM * 128u, wt_bytes = (uint32_t)Cout * 128u;
+  const uint32_t g_bytes = (uint32_t)kTileM * 128u;
+  uint8_t* smem = dcn_smem + ((1024u - (smem_u32(dcn_smem) & 1023u)) & 1023u);
+  uint8_t* gout = smem;                                               // [GB][Cout/64][128][128 B]
+  uint8_t* wtr = gout + (size_t)GB * gout_bytes;                      // [NW][Cout/64][64][128 B]
+  uint8_t* gring = wtr + (size_t)NW * wt_bytes;                       // [NG][128][128 B]
+  uint4* geo = reinterpret_cast<uint4*>(gring + (size_t)NG * g_bytes);   // [2][9][128] {g, lh, lw, mask}
+  float* acc = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(geo) + kDgGeoBytes);   // [27][128]
+  const int cpb = Cin / kBK, KB = 9 * cpb;
+  const int tile_first = (int)(((long long)blockIdx.x * prm.num_tiles) / gridDim.x);
+  const int my_tiles = (int)(((long long)(blockIdx.x + 1) * prm.num_tiles) / gridDim.x) - tile_first;
+  const int total = my_tiles * KB;
+
+  if (tid == 0) {
+    for (int i = 0; i < 2; ++i) {
+      dcn_mbar_init(&bars.geo_full[i], 4);   dcn_mbar_init(&bars.geo_empty[i], NP);
+      dcn_mbar_init(&bars.gout_full[i], 4);  dcn_mbar_init(&bars.gout_empty[i], 1);
+      dcn_mbar_init(&bars.acc_full[i], 1);   dcn_mbar_init(&bars.acc_empty[i], 4);
+    }
+    for (int i = 0; i < kDgMaxRing; ++i) {
+      dcn_mbar_init(&bars.wt_full[i], 1);    dcn_mbar_init(&bars.wt_empty[i], 1);
+      dcn_mbar_init(&bars.g_full[i], 4);     dcn_mbar_init(&bars.g_empty[i], NP);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == NP + 8) tmem_alloc(&s_tmem, 128);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = s_tmem;
+
+  if (warp < NP) {
+    // ===================================== consumers ==============================================
+    constexpr int ITERS = 32 / NP;
+    const int sub = lane >> 3, chunk = lane & 7;
+    const uint32_t swz = (uint32_t)((chunk ^ (((warp & 1) << 2) + sub)) << 4);
+    const uint32_t row0 = (uint32_t)(warp << 2) + sub;
+    const uint32_t ex = (uint32_t)Cin, ey = (uint32_t)prm.W * (uint32_t)Cin;
+    uint4 va[ITERS], vb[ITERS], vc[ITERS], vd[ITERS];
+    auto gather = [&](int i, const __nv_bfloat16* xc, uint32_t g) {
+      const uint32_t e0 = g & ~63u;
+      const uint32_t dx = (g & 1u) ? ex : 0u;
+      const uint32_t e2 = e0 + ((g & 2u) ? ey : 0u);
+      va[i] = ldg_gather16(xc + e0);
+      vb[i] = ldg_gather16(xc + e0 + dx);
+      vc[i] = ldg_gather16(xc + e2);
+      vd[i] = ldg_gather16(xc + e2 + dx);
+    };
+    int c_img = 0, c_pix[ITERS];                 // image and output pixel (or -1) of this thread's rows
+    auto set_tile = [&](int it) {
+      int tile = tile_first + it;
+      c_img = tile / prm.tiles_per_image;
+      tile -= c_img * prm.tiles_per_image;
+      const int tile_y = tile / prm.tiles_x, tile_x = tile - tile_y * prm.tiles_x;
+#pragma unroll
+      for (int i = 0; i < ITERS; ++i) {
+        const int r = (int)row0 + i * NP * 4;
+        const int ho = tile_y * kTileH + (r >> 4), wo = tile_x * kTileW + (r & 15);
+        c_pix[i] = (ho < prm.Ho && wo < prm.Wo) ? ho * prm.Wo + wo : -1;
+      }
+    };
+    int l_it = 0, l_cb = 0, l_t = 0;             // load cursor: the K block whose gathers are in flight
+    const __nv_bfloat16* l_x = prm.xh + chunk * 8;
+    if (total > 0) {
+      set_tile(0);
+      l_x = prm.xh + (size_t)c_img * Pin * Cin + chunk * 8;
+      dcn_mbar_wait(&bars.geo_full[0], 0u);
+#pragma unroll
+      for (int i = 0; i < ITERS; ++i) gather(i, l_x, geo[row0 + i * NP * 4].x);
+    }
+    int gs = 0; unsigned gph = 0;
+    for (int n = 0; n < total; ++n) {
+      const int c_it = l_it, c_cb = l_cb, c_t = l_t;
+      const bool have_next = n + 1 < total;
+      if (++l_t == 9) {
+        l_t = 0;
+        if (++l_cb == cpb) {
+          l_cb = 0; ++l_it;
+          if (have_next) {
+            const int tile = tile_first + l_it;
+            l_x = prm.xh + (size_t)(tile / prm.tiles_per_image) * Pin * Cin + chunk * 8;
+            dcn_mbar_wait(&bars.geo_full[l_it & 1], (unsigned)((l_it >> 1) & 1));
+          }
+        }
+      }
+      const __nv_bfloat16* l_xc = l_x + l_cb * kBK;
+      const uint4* geo_n = geo + ((l_it & 1) * 9 + l_t) * kTileM + row0;
+      const uint4* geo_c = geo + ((c_it & 1) * 9 + c_t) * kTileM + row0;
+      float* gxp = bw.gx + (size_t)c_img * Pin * Cin + c_cb * kBK + chunk * 8;
+      dcn_mbar_wait(&bars.g_full[gs], gph);
+      const uint8_t* g_tile = gring + (size_t)gs * g_bytes;
+#pragma unroll
+      for (int i = 0; i < ITERS; ++i) {
+        const uint4 q4 = geo_c[i * NP * 4];
+        const uint4 gq = *reinterpret_cast<const uint4*>(g_tile + (row0 + (uint32_t)(i * NP * 4)) * 128u + swz);
+        const uint32_t g = q4.x;
+        const float lh = __uint_as_float(q4.y), lw = __uint_as_float(q4.z), m = __uint_as_float(q4.w);
+        const float g8[8] = {bf_lo(gq.x), bf_hi(gq.x), bf_lo(gq.y), bf_hi(gq.y),
+                             bf_lo(gq.z), bf_hi(gq.z), bf_lo(gq.w), bf_hi(gq.w)};
+        const float o1 = ((g & 20u) == 20u) ? 1.f : 0.f, o2 = ((g & 36u) == 36u) ? 1.f : 0.f;   // top&left, top&right
+        const float o3 = ((g & 24u) == 24u) ? 1.f : 0.f, o4 = ((g & 40u) == 40u) ? 1.f : 0.f;   // bottom&left, bottom&right
+        float d1 = dot8(g8, va[i]) * o1, d2 = dot8(g8, vb[i]) * o2;
+        float d3 = dot8(g8, vc[i]) * o3, d4 = dot8(g8, vd[i]) * o4;
+        const float hh = 1.f - lh, hw = 1.f - lw;
+        const float w1 = hh * hw * o1, w2 = hh * lw * o2, w3 = lh * hw * o3, w4 = lh * lw * o4;
+        {                                        // grad_input: G * mask * corner weight (deform_conv_cuda_kernel.cu:944)
+          const uint32_t e0 = g & ~63u;
+          const uint32_t dx = (g & 1u) ? ex : 0u;
+          const uint32_t e2 = e0 + ((g & 2u) ? ey : 0u);
+          auto scat = [&](uint32_t e, float c) {
+            if (c != 0.f) {
+              red_add_v4(gxp + e, g8[0] * c, g8[1] * c, g8[2] * c, g8[3] * c);
+              red_add_v4(gxp + e + 4, g8[4] * c, g8[5] * c, g8[6] * c, g8[7] * c);
+            }
+          };
+          scat(e0, m * w1); scat(e0 + dx, m * w2); scat(e2, m * w3); scat(e2 + dx, m * w4);
+        }
+        if (have_next) gather(i, l_xc, geo_n[i * NP * 4].x);   // refill the slot: K block n+1, same row group
+#pragma unroll
+        for (int o = 1; o < 8; o <<= 1) {
+          d1 += __shfl_xor_sync(0xffffffffu, d1, o); d2 += __shfl_xor_sync(0xffffffffu, d2, o);
+          d3 += __shfl_xor_sync(0xffffffffu, d3, o); d4 += __shfl_xor_sync(0xffffffffu, d4, o);
+        }
+        if (chunk == 0) {
+          float vm = w1 * d1 + w2 * d2 + w3 * d3 + w4 * d4;             // :1019-1030
+          float vh = m * (hw * (d3 - d1) + lw * (d4 - d2));             // dmcn_get_coordinate_weight, bp_dir 0
+          float vw = m * (hh * (d2 - d1) + lh * (d4 - d3));             // bp_dir 1
+          float* a = acc + (3 * c_t) * kTileM + row0 + i * NP * 4;      // partial sums over channel blocks
+          if (c_cb > 0) { vm += a[0]; vh += a[kTileM]; vw += a[2 * kTileM]; }
+          if (c_cb == cpb - 1) {
+            if (c_pix[i] >= 0) {
+              bw.goff[((size_t)c_img * 18 + 2 * c_t) * P + c_pix[i]] = vh;
+              bw.goff[((size_t)c_img * 18 + 2 * c_t + 1) * P + c_pix[i]] = vw;
+              bw.gmask[((size_t)c_img * 9 + c_t) * P + c_pix[i]] = vm;
+            }
+          } else {
+            a[0] = vm; a[kTileM] = vh; a[2 * kTileM] = vw;
+          }
+        }
+      }
+      __syncwarp();
+      if (lane == 0) {
+        dcn_mbar_arrive(&bars.g_empty[gs]);
+        if (l_it != c_it) dcn_mbar_arrive(&bars.geo_empty[c_it & 1]);
+      }
+      if (++gs == NG) { gs = 0; gph ^= 1u; }
+      if (l_it != c_it && have_next) set_tile(l_it);
+    }
+  } else if (warp < NP + 4) {
+    // ===================================== transfer: TMEM -> bf16 G tile ==========================
+    const int quarter = warp - NP;
+    const int r = (quarter << 5) + lane;
+    int gs = 0; unsigned gph = 0;
+    for (int n = 0; n < total; ++n) {
+      const int ab = n & 1;
+      dcn_mbar_wait(&bars.acc_full[ab], (unsigned)((n >> 1) & 1));
+      tc_fence_after();
+      uint32_t pk[32];
+#pragma unroll
+      for (int c0 = 0; c0 < kBK; c0 += 16) {
+        uint32_t v[16];
+        tmem_ld16(tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(ab * kBK + c0), v);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(v[2 * k]), __uint_as_float(v[2 * k + 1]));
+          pk[c0 / 2 + k] = *reinterpret_cast<const uint32_t*>(&h);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) dcn_mbar_arrive(&bars.acc_empty[ab]);            // TMEM buffer may be overwritten
+      dcn_mbar_wait(&bars.g_empty[gs], gph ^ 1u);
+      uint8_t* dst = gring + (size_t)gs * g_bytes + r * 128;
+#pragma unroll
+      for (int c = 0; c < 8; ++c)
+        *reinterpret_cast<uint4*>(dst + ((c ^ (r & 7)) << 4)) = make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+      __syncwarp();
+      if (lane == 0) dcn_mbar_arrive(&bars.g_full[gs]);
+      if (++gs == NG) { gs = 0; gph ^= 1u; }
+    }
+  } else if (warp < NP + 8) {
+    // ===================================== grad_output tile + geometry ============================
+    const int r = ((warp - NP - 4) << 5) + lane;
+    for (int it = 0; it < my_tiles; ++it) {
+      int tile = tile_first + it;
+      const int gb = it % GB;
+      dcn_mbar_wait_relaxed(&bars.gout_empty[gb], (unsigned)(((it / GB) & 1) ^ 1));
+      dcn_load_gout_tile(prm, bw.gh, tile, r, gout + (size_t)gb * gout_bytes);
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) dcn_mbar_arrive(&bars.gout_full[gb]);
+
+      const int b = tile / prm.tiles_per_image;
+      tile -= b * prm.tiles_per_image;
+      const int tile_y = tile / prm.tiles_x, tile_x = tile - tile_y * prm.tiles_x;
+      const int ho = tile_y * kTileH + (r >> 4), wo = tile_x * kTileW + (r & 15);
+      const bool valid = ho < prm.Ho && wo < prm.Wo;
+      const int p = valid ? ho * prm.Wo + wo : 0;
+      const float* offb = prm.offset + (size_t)b * 18 * P + p;
+      const float* mskb = prm.mask + (size_t)b * 9 * P + p;
+      float ov[18], mv[9];
+#pragma unroll
+      for (int k = 0; k < 18; ++k) ov[k] = ldg_stream1(offb + (size_t)k * P);
+#pragma unroll
+      for (int k = 0; k < 9; ++k) mv[k] = ldg_stream1(mskb + (size_t)k * P);
+      const int buf = it & 1;
+      dcn_mbar_wait_relaxed(&bars.geo_empty[buf], (unsigned)(((it >> 1) & 1) ^ 1));
+#pragma unroll
+      for (int t = 0; t < 9; ++t)
+        geo[(buf * 9 + t) * kTileM + r] = tap_geometry_raw(prm, ov[2 * t], ov[2 * t + 1], mv[t], ho, wo, valid, t);
+      __syncwarp();
+      if (lane == 0) dcn_mbar_arrive(&bars.geo_full[buf]);
+    }
+  } else if (warp == NP + 8) {
+    // ===================================== MMA issuer =============================================
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_bf16(kTileM, kBK);
+      int ws = 0; unsigned wph = 0;
+      int n = 0;
+      for (int it = 0; it < my_tiles; ++it) {
+        const int gb = it % GB;
+        dcn_mbar_wait_relaxed(&bars.gout_full[gb], (unsigned)((it / GB) & 1), 0u);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(gout + (size_t)gb * gout_bytes);
+        for (int kb = 0; kb < KB; ++kb, ++n) {
+          const int ab = n & 1;
+          dcn_mbar_wait_relaxed(&bars.acc_empty[ab], (unsigned)(((n >> 1) & 1) ^ 1), 0u);
+          dcn_mbar_wait_relaxed(&bars.wt_full[ws], wph, 0u);
+          tc_fence_after();
+          const uint32_t b_addr = smem_u32(wtr + (size_t)ws * wt_bytes);
+          for (int j = 0; j < Cout / 64; ++j) {
+            const uint64_t adesc = make_sw128_desc(a_addr + (uint32_t)j * kTileM * 128u);
+            const uint64_t bdesc = make_sw128_desc(b_addr + (uint32_t)j * 64u * 128u);
+#pragma unroll
+            for (int k4 = 0; k4 < 4; ++k4)
+              umma_bf16(tmem + (uint32_t)(ab * kBK), adesc + 2 * k4, bdesc + 2 * k4, idesc, (uint32_t)((j | k4) != 0));
+          }
+          umma_commit(&bars.wt_empty[ws]);
+          umma_commit(&bars.acc_full[ab]);
+          if (++ws == NW) { ws = 0; wph ^= 1u; }
+        }
+        umma_commit(&bars.gout_empty[gb]);
+      }
+    }
+    __syncwarp();
+  } else {
+    // ===================================== transposed-weight tile loader ==========================
+    if (lane == 0) {
+      int ws = 0; unsigned wph = 0;
+      for (int it = 0; it < my_tiles; ++it) {
+        for (int kb = 0; kb < KB; ++kb) {
+          dcn_mbar_wait_relaxed(&bars.wt_empty[ws], wph ^ 1u, 20u);
+          dcn_mbar_arrive_expect_tx(&bars.wt_full[ws], wt_bytes);
+          dcn_bulk_g2s(wtr + (size_t)ws * wt_bytes, bw.wt + (size_t)kb * Cout * kBK, wt_bytes, &bars.wt_full[ws]);
+          if (++ws == NW) { ws = 0; wph ^= 1u; }
+        }
+      }
+    }
+    __syncwarp();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == NP + 8) tmem_dealloc(tmem, 128);
+}
 }  // namespace ctdet
 
 static inline size_t dcnb_align256(size_t v) { return (v + 255) / 256 * 256; }
@@ -291,8 +670,30 @@ extern "C" int dcnv2_backward(const float* input, const float* weight, const flo
     if (rc) return rc;
   }
   if (want_d) {
-    // DGRAD_LAUNCH_PLACEHOLDER
-    return CTDET_EUNSUPPORTED;
+    e = cudaMemsetAsync(gx, 0, (size_t)B * Pin * Cin * 4, st);
+    if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
+    dcn_pack_weight_t_kernel<<<kNumSMs, 256, 0, st>>>(weight, wt, Cout, Cin);
+    rc = check_launch();
+    if (rc) return rc;
+    const size_t gout_bytes = (size_t)(Cout / 64) * kTileM * 128;
+    bw.gout_bufs = Cout <= 128 ? 2 : 1;
+    const size_t fixed = 1024 + (size_t)bw.gout_bufs * gout_bytes + kDgGeoBytes + kDgAccBytes;
+    const size_t unit = (size_t)Cout * 128 + (size_t)kTileM * 128;
+    int ring = (int)((226 * 1024 - fixed) / unit);
+    if (ring > kDgMaxRing) ring = kDgMaxRing;
+    if (ring < 2) return CTDET_EUNSUPPORTED;
+    bw.g_stages = bw.w_stages = ring;
+    const size_t smem = fixed + (size_t)ring * unit;
+    auto kern = dcn_dgrad_kernel<NP>;
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
+    const unsigned grid = (unsigned)(tiles < kNumSMs ? tiles : kNumSMs);
+    kern<<<grid, (NP + 10) * 32, smem, st>>>(prm, bw);
+    rc = check_launch();
+    if (rc) return rc;
+    dcn_unpack_grad_input_kernel<<<dim3((Pin + 63) / 64, Cin / 64, B), 256, 0, st>>>(gx, grad_input, Cin, Pin);
+    rc = check_launch();
+    if (rc) return rc;
   }
   return CTDET_OK;
 }
