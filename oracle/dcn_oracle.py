@@ -18,6 +18,8 @@ def _load():
         _lib = ctypes.CDLL(_SO)
         _lib.dcn_oracle_forward.restype = ctypes.c_int
         _lib.dcn_oracle_forward.argtypes = [ctypes.c_void_p] * 5 + [ctypes.c_int] * 8 + [ctypes.c_void_p]
+        _lib.dcn_oracle_backward.restype = ctypes.c_int
+        _lib.dcn_oracle_backward.argtypes = [ctypes.c_void_p] * 5 + [ctypes.c_int] * 8 + [ctypes.c_void_p] * 5
     return _lib
 
 
@@ -50,3 +52,22 @@ def dcn_forward(x, offset, mask, weight, bias=None, stride=1, pad=1, dil=1, thre
     if any(rcs):
         raise MemoryError("dcn oracle scratch allocation failed")
     return out
+
+
+def dcn_backward(x, offset, mask, weight, grad_out, stride=1, pad=1, dil=1):
+    """-> (grad_input, grad_offset, grad_mask, grad_weight, grad_bias), the five outputs of
+    modulated_deform_conv_cuda_backward (deform_conv_cuda.cu:929)."""
+    x, offset, mask, weight, grad_out = [np.ascontiguousarray(a, np.float32) for a in (x, offset, mask, weight, grad_out)]
+    B, Cin, H, W = x.shape
+    Cout = weight.shape[0]
+    Ho = (H + 2 * pad - (dil * 2 + 1)) // stride + 1
+    Wo = (W + 2 * pad - (dil * 2 + 1)) // stride + 1
+    assert offset.shape == (B, 18, Ho, Wo) and mask.shape == (B, 9, Ho, Wo) and grad_out.shape == (B, Cout, Ho, Wo)
+    gx, go, gm = np.empty_like(x), np.empty_like(offset), np.empty_like(mask)
+    gw, gb = np.empty_like(weight), np.empty((Cout,), np.float32)
+    rc = _load().dcn_oracle_backward(x.ctypes.data, offset.ctypes.data, mask.ctypes.data, weight.ctypes.data,
+                                     grad_out.ctypes.data, B, Cin, H, W, Cout, stride, pad, dil,
+                                     gx.ctypes.data, go.ctypes.data, gm.ctypes.data, gw.ctypes.data, gb.ctypes.data)
+    if rc:
+        raise MemoryError("dcn oracle scratch allocation failed")
+    return gx, go, gm, gw, gb

@@ -53,3 +53,19 @@ def test_border_rule():
     off[0, 8] = -0.75                                     # row 0 samples h_im = -0.75: 0.25 * row 0
     out = DO.dcn_forward(x, off, m, w, None, 1, 1, 1)
     np.testing.assert_allclose(out[0, 0, 0], 0.25, rtol=1e-6)
+
+
+@pytest.mark.parametrize("cfg", [(2, 8, 16, 12, 10, 1, 1, 1), (1, 4, 8, 9, 11, 2, 1, 1), (1, 4, 8, 9, 11, 1, 2, 2)])
+def test_oracle_backward_matches_torchvision_autograd(cfg):
+    """The backward restatement (col2im_coord / col2im / im2col + GEMMs) against autograd through
+    torchvision's op; offsets reach far outside the image so the border rules are exercised."""
+    B, Cin, Cout, H, W, s, p, d = cfg
+    x, off, m, w, b = _case(5, B, Cin, Cout, H, W, s, p, d, off_range=5.0)
+    rng = np.random.default_rng(9)
+    Ho, Wo = off.shape[2], off.shape[3]
+    gy = rng.normal(size=(B, Cout, Ho, Wo)).astype(np.float32)
+    t = [torch.from_numpy(a).double().requires_grad_(True) for a in (x, off, m, w, b)]
+    tv.deform_conv2d(t[0], t[1], t[3], t[4], stride=s, padding=p, dilation=d, mask=t[2]).backward(torch.from_numpy(gy).double())
+    got = DO.dcn_backward(x, off, m, w, gy, s, p, d)
+    for g, r, name in zip(got, (t[0], t[1], t[2], t[3], t[4]), ("input", "offset", "mask", "weight", "bias")):
+        np.testing.assert_allclose(g, r.grad.numpy(), rtol=2e-3, atol=2e-3 * float(r.grad.abs().max()), err_msg=name)

@@ -1,5 +1,6 @@
-"""GPU: the tcgen05 DCNv2 backward (through the C ABI) against autograd through
-torchvision.ops.deform_conv2d on the CPU in fp64 (the same reference the C oracle is pinned on).
+"""GPU: the tcgen05 DCNv2 backward (through the C ABI) against the C oracle's restatement of
+modulated_deform_conv_cuda_backward (oracle/dcn_oracle.c, pinned on torchvision autograd by
+tests/test_dcn_oracle.py).
 
 Stated tolerance (input, weight, grad_output and the column gradient are rounded to bf16, fp32
 accumulation): relative L2 error <= 1.5e-2 per gradient tensor, max-abs error <= 4e-2 of the
@@ -28,12 +29,8 @@ def _case(seed, B, Cin, Cout, H, W, s=1, p=1, d=1, off_range=2.0):
 
 
 def _reference(x, off, m, w, gy, s, p, d):
-    import torchvision
-    t = [torch.from_numpy(a).double().requires_grad_(True) for a in (x, off, m, w)]
-    b = torch.zeros(w.shape[0], dtype=torch.float64, requires_grad=True)
-    y = torchvision.ops.deform_conv2d(t[0], t[1], t[3], b, stride=s, padding=p, dilation=d, mask=t[2])
-    y.backward(torch.from_numpy(gy).double())
-    return [g.grad.numpy() for g in (t[0], t[1], t[2], t[3], b)]
+    from oracle import dcn_oracle as DO
+    return DO.dcn_backward(x, off, m, w, gy, s, p, d)      # (grad_input, grad_offset, grad_mask, grad_weight, grad_bias)
 
 
 def _errs(got, ref):
