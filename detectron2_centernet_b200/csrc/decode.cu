@@ -341,26 +341,26 @@ decode_peaks_kernel(const float* __restrict__ heat, int C, int H, int W, int Wp,
       }
     }
   };
+  // Fast path (the common case once the image has a bound): append the candidates above the
+  // threshold straight into the key buffer -- no counting pass, one barrier.
   {
-    int cnt = 0;
-    for (int w = tid; w < n_words; w += kDecThreads) cnt += __popc(bitmap[w]);
-    cnt = warp_sum(cnt);
-    if (lane == 0 && cnt) atomicAdd(&sh.ncand, cnt);
+    const u64 th = sh.thresh;
+    for_each_candidate([&](u64 key, int, int) {
+      if (key > th) { const int pos = atomicAdd(&sh.count, 1); if (pos < cap) buf[pos] = key; }
+    });
   }
   __syncthreads();
-  if (sh.ncand == 0) return;                             // CTA-uniform: nothing in this tile
-
-  bool counted = false;                                  // have this CTA's candidates been RED-ed?
-  if (sh.ncand > cap) {
+  int n = sh.count;
+  if (n == 0) return;                                    // CTA-uniform: nothing in this tile
+  if (n > cap) {
     // Slow path (weak or no bound yet, plateaus, ties).  1: count every candidate into the image
     // histogram and re-derive the bound; 2: drop the candidates below it; 3: if still too many,
-    // keep exactly the tile's K best (exact radix select).  CTA-uniform branch.
+    // keep exactly the tile's K best (exact radix select); 4: collect again.  CTA-uniform branch.
     for_each_candidate([&](u64 key, int, int) { atomicAdd(ghist + ((uint32_t)(key >> 32) >> kHistShift), 1u); });
-    counted = true;
     __threadfence();
     __syncthreads();
     refresh_bound(ghist, hdr, &sh, K);
-    if (tid == 0) sh.ncand = 0;
+    if (tid == 0) { sh.ncand = 0; sh.count = 0; }
     __syncthreads();
     {
       const u64 th = sh.thresh;
@@ -373,27 +373,25 @@ decode_peaks_kernel(const float* __restrict__ heat, int C, int H, int W, int Wp,
     }
     __syncthreads();
     if (sh.ncand > cap) {
-      const int n = sh.ncand;
+      const int nc = sh.ncand;
       const u64 T = radix_select_kth<kDecThreads>(
-          [&](auto f) { for_each_candidate([&](u64 key, int, int) { f(key); }); }, n, K, &sh.sel);
+          [&](auto f) { for_each_candidate([&](u64 key, int, int) { f(key); }); }, nc, K, &sh.sel);
       for_each_candidate([&](u64 key, int w, int ln) { if (key < T) atomicAnd(&bitmap[w], ~(1u << ln)); });
       if (tid == 0 && T - 1ull > sh.thresh) sh.thresh = T - 1ull;
       __syncthreads();
     }
+    {                                                    // at most cap keys by construction
+      const u64 th = sh.thresh;
+      for_each_candidate([&](u64 key, int, int) {
+        if (key > th) { const int pos = atomicAdd(&sh.count, 1); if (pos < cap) buf[pos] = key; }
+      });
+    }
+    __syncthreads();
+    n = min(sh.count, cap);
+  } else {
+    // every collected key is counted exactly once in the image histogram
+    for (int i = tid; i < n; i += kDecThreads) atomicAdd(ghist + ((uint32_t)(buf[i] >> 32) >> kHistShift), 1u);
   }
-  // collect (at most cap keys by construction)
-  {
-    const u64 th = sh.thresh;
-    for_each_candidate([&](u64 key, int, int) {
-      if (key > th) {
-        const int pos = atomicAdd(&sh.count, 1);
-        if (pos < cap) buf[pos] = key;
-        if (!counted) atomicAdd(ghist + ((uint32_t)(key >> 32) >> kHistShift), 1u);
-      }
-    });
-  }
-  __syncthreads();
-  const int n = min(sh.count, cap);
 
   // ---- publish / pick up the image bound, emit --------------------------------------------------
   // CTAs that started without a bound (the first of their image) or still hold many keys derive a
@@ -403,12 +401,10 @@ decode_peaks_kernel(const float* __restrict__ heat, int C, int H, int W, int Wp,
     __threadfence();
     refresh_bound(ghist, hdr, &sh, K);
     th = sh.thresh;
-  }
-  {
+    // the bound may have risen: count, reserve and compact the keys that still pass
     int mine = 0;
     for (int i = tid; i < n; i += kDecThreads) mine += (buf[i] > th);
     mine = warp_sum(mine);
-    __syncthreads();
     if (tid == 0) sh.count = 0;
     __syncthreads();
     if (lane == 0 && mine) atomicAdd(&sh.count, mine);
@@ -422,6 +418,12 @@ decode_peaks_kernel(const float* __restrict__ heat, int C, int H, int W, int Wp,
       const u64 key = buf[i];
       if (key > th) dst[atomicAdd(&sh.count, 1)] = key;
     }
+  } else {
+    // threshold unchanged since the collect: all n keys pass
+    if (tid == 0) s_base = atomicAdd(&hdr->count, (unsigned)n);
+    __syncthreads();
+    u64* dst = out_keys + (size_t)b * keys_per_image + s_base;
+    for (int i = tid; i < n; i += kDecThreads) dst[i] = buf[i];
   }
 }
 
