@@ -44,6 +44,65 @@ def peaks():
     return 6650.0, "fallback"
 
 
+def tensor_peak():
+    """Sustained dense bf16 TFLOP/s (the DCN stack is timed inside a long loop)."""
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.isfile(p):
+        d = json.load(open(p))
+        return float(d.get("bf16_tflops_sustained", d.get("bf16_tflops", 1389.0))), "measured (sustained)"
+    return 1389.0, "fallback"
+
+
+# the 16 DeformConvV2 layers of the DLA-34 neck at 512^2 (SURVEY.md section 8 a12): (Cin, Cout, H=W, count)
+DCN_LAYERS = [(512, 256, 16, 1), (256, 256, 32, 1), (256, 128, 32, 2), (128, 128, 64, 2), (128, 64, 64, 4),
+              (64, 64, 128, 5), (256, 64, 32, 1)]
+
+
+def dcn_stack(dev, B, reps=5):
+    """BASELINE.json configs[4] (kernel part): forward and backward of the 16 DCNv2 layers of the
+    DLA-34 IDAUp/DLAUp neck, random offsets in (-2, 2), sigmoid masks; CUDA events, device-resident."""
+    import math
+    from detectron2_centernet_b200 import deform_conv as DC
+    g = torch.Generator(device=dev).manual_seed(0)
+    fwd_ms = bwd_ms = flops = 0.0
+    for Cin, Cout, S_, cnt in DCN_LAYERS:
+        x = torch.randn((B, Cin, S_, S_), device=dev, generator=g)
+        off = (torch.rand((B, 18, S_, S_), device=dev, generator=g) - 0.5) * 4
+        m = torch.sigmoid(torch.randn((B, 9, S_, S_), device=dev, generator=g))
+        w = (torch.rand((Cout, Cin, 3, 3), device=dev, generator=g) - 0.5) * 2 / math.sqrt(9 * Cin)
+        bias = torch.zeros(Cout, device=dev)
+        gy = torch.randn((B, Cout, S_, S_), device=dev, generator=g)
+        for which in ("fwd", "bwd"):
+            if which == "fwd":
+                fn = lambda: DC.dcnv2_forward(x, off, m, w, bias, 1, 1, 1)          # noqa: E731
+            else:
+                fn = lambda: DC.dcnv2_backward(x, off, m, w, gy, 1, 1, 1)           # noqa: E731
+            for _ in range(2):
+                fn()
+            torch.cuda.synchronize()
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record()
+            for _ in range(reps):
+                fn()
+            e.record()
+            torch.cuda.synchronize()
+            ms = s.elapsed_time(e) / reps
+            if which == "fwd":
+                fwd_ms += ms * cnt
+            else:
+                bwd_ms += ms * cnt
+        flops += 2.0 * Cout * Cin * 9 * S_ * S_ * B * cnt
+    peak, src = tensor_peak()
+    tf = flops / fwd_ms / 1e9
+    return {"workload": "16 DCNv2 layers of the DLA-34 neck @512^2, batch %d, fp32 NCHW in/out, bf16 operands" % B,
+            "fwd_ms": round(fwd_ms, 3), "fwd_images_per_s": round(B / fwd_ms * 1e3, 1), "fwd_tflops": round(tf, 1),
+            "bwd_ms": round(bwd_ms, 3), "bwd_tflops": round(2 * flops / bwd_ms / 1e9, 1),
+            "gflop_per_image_fwd": round(flops / B / 1e9, 2),
+            "roofline": {"bound": "tensor", "achieved": round(tf, 1), "peak": peak, "unit": "TFLOP/s",
+                         "frac": round(tf / peak, 4), "peak_source": src,
+                         "note": "the sampler is L1-bandwidth-bound (8 B of L1 reads per im2col element), see DESIGN.md section 5"}}
+
+
 class ClockSampler(threading.Thread):
     """SM clock + throttle reasons sampled through NVML every 5 ms DURING the timed regions."""
 
@@ -236,6 +295,8 @@ def run_ours(args):
     traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.isfile(traffic_file):
         out["roofline"]["traffic"] = json.load(open(traffic_file)).get("loss_kernel_bytes_per_launch")
+    if not args.no_dcn:
+        out["dcn_stack"] = dcn_stack(dev, B)
     if world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline(sample_images=2, reps=2)
     print(json.dumps(out))
@@ -304,6 +365,7 @@ if __name__ == "__main__":
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-dcn", action="store_true", help="skip the DCNv2 stack timing (extra key dcn_stack)")
     a = ap.parse_args()
     if a.impl == "reference":
         run_reference(a)
