@@ -336,6 +336,9 @@ dcn_dgrad_kernel(const DcnParams prm, const DcnBwdParams bw) {
 
   if (warp < NP) {
     // ===================================== consumers ==============================================
+    // the consumers are the register-hungry role: take the registers the 4 geometry warps give back
+    // (CTA-local pool: 4 warps x 32 released = 16 warps x 8 acquired, or the inc would block forever)
+    if (NP == 16) asm volatile("setmaxnreg.inc.sync.aligned.u32 80;");
     constexpr int ITERS = 32 / NP;
     const int sub = lane >> 3, chunk = lane & 7;
     const uint32_t swz = (uint32_t)((chunk ^ (((warp & 1) << 2) + sub)) << 4);
@@ -485,6 +488,7 @@ dcn_dgrad_kernel(const DcnParams prm, const DcnBwdParams bw) {
     }
   } else if (warp < NP + 8) {
     // ===================================== grad_output tile + geometry ============================
+    if (NP == 16) asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
     const int r = ((warp - NP - 4) << 5) + lane;
     for (int it = 0; it < my_tiles; ++it) {
       int tile = tile_first + it;
@@ -684,11 +688,12 @@ extern "C" int dcnv2_backward(const float* input, const float* weight, const flo
     if (ring < 2) return CTDET_EUNSUPPORTED;
     bw.g_stages = bw.w_stages = ring;
     const size_t smem = fixed + (size_t)ring * unit;
-    auto kern = dcn_dgrad_kernel<NP>;
+    const int npd = dcn_env_int("CTDET_DCN_DGRAD_WARPS", 16) == 8 ? 8 : 16;
+    void (*kern)(const DcnParams, const DcnBwdParams) = npd == 8 ? dcn_dgrad_kernel<8> : dcn_dgrad_kernel<16>;
     e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
     const unsigned grid = (unsigned)(tiles < kNumSMs ? tiles : kNumSMs);
-    kern<<<grid, (NP + 10) * 32, smem, st>>>(prm, bw);
+    kern<<<grid, (npd + 10) * 32, smem, st>>>(prm, bw);
     rc = check_launch();
     if (rc) return rc;
     dcn_unpack_grad_input_kernel<<<dim3((Pin + 63) / 64, Cin / 64, B), 256, 0, st>>>(gx, grad_input, Cin, Pin);
