@@ -271,6 +271,16 @@ __device__ __forceinline__ float dot8(const float (&g)[8], uint4 v) {
   return fmaf(g[7], bf_hi(v.w), d);
 }
 
+// dgrad lane layout: lane `chunk` (0..7) of a pixel owns channels [4c, 4c+4) and [32+4c, 32+4c+4) of the
+// 64-channel block, so that the 8 lanes' vector REDs into the fp32 NHWC gradient cover whole 32-byte sectors
+// (8 x 16 B contiguous) -- with 8 consecutive channels per lane every RED would touch half a sector.
+__device__ __forceinline__ uint4 ldg_gather8x2(const __nv_bfloat16* p) {
+  uint4 v;
+  asm volatile("ld.global.nc.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
+  asm volatile("ld.global.nc.v2.u32 {%0,%1}, [%2];" : "=r"(v.z), "=r"(v.w) : "l"(p + 32));
+  return v;
+}
+
 constexpr int kDgMaxRing = 4;
 struct DgradBarriers {
   uint64_t geo_full[2], geo_empty[2];       // raw geometry of a tile               (geometry warps -> consumers)
@@ -341,7 +351,9 @@ dcn_dgrad_kernel(const DcnParams prm, const DcnBwdParams bw) {
     if (NP == 16) asm volatile("setmaxnreg.inc.sync.aligned.u32 80;");
     constexpr int ITERS = 32 / NP;
     const int sub = lane >> 3, chunk = lane & 7;
-    const uint32_t swz = (uint32_t)((chunk ^ (((warp & 1) << 2) + sub)) << 4);
+    const uint32_t r7 = (uint32_t)(((warp & 1) << 2) + sub);                       // row & 7 is fixed per thread
+    const uint32_t g_half = (uint32_t)(chunk & 1) * 8u;                             // 8-byte half of a 16-byte chunk
+    const uint32_t g_sw_lo = (((uint32_t)(chunk >> 1)) ^ r7) << 4, g_sw_hi = ((4u + (uint32_t)(chunk >> 1)) ^ r7) << 4;
     const uint32_t row0 = (uint32_t)(warp << 2) + sub;
     const uint32_t ex = (uint32_t)Cin, ey = (uint32_t)prm.W * (uint32_t)Cin;
     uint4 va[ITERS], vb[ITERS], vc[ITERS], vd[ITERS];
@@ -349,10 +361,10 @@ dcn_dgrad_kernel(const DcnParams prm, const DcnBwdParams bw) {
       const uint32_t e0 = g & ~63u;
       const uint32_t dx = (g & 1u) ? ex : 0u;
       const uint32_t e2 = e0 + ((g & 2u) ? ey : 0u);
-      va[i] = ldg_gather16(xc + e0);
-      vb[i] = ldg_gather16(xc + e0 + dx);
-      vc[i] = ldg_gather16(xc + e2);
-      vd[i] = ldg_gather16(xc + e2 + dx);
+      va[i] = ldg_gather8x2(xc + e0);
+      vb[i] = ldg_gather8x2(xc + e0 + dx);
+      vc[i] = ldg_gather8x2(xc + e2);
+      vd[i] = ldg_gather8x2(xc + e2 + dx);
     };
     int c_img = 0, c_pix[ITERS];                 // image and output pixel (or -1) of this thread's rows
     auto set_tile = [&](int it) {
@@ -368,10 +380,10 @@ dcn_dgrad_kernel(const DcnParams prm, const DcnBwdParams bw) {
       }
     };
     int l_it = 0, l_cb = 0, l_t = 0;             // load cursor: the K block whose gathers are in flight
-    const __nv_bfloat16* l_x = prm.xh + chunk * 8;
+    const __nv_bfloat16* l_x = prm.xh + chunk * 4;
     if (total > 0) {
       set_tile(0);
-      l_x = prm.xh + (size_t)c_img * Pin * Cin + chunk * 8;
+      l_x = prm.xh + (size_t)c_img * Pin * Cin + chunk * 4;
       dcn_mbar_wait(&bars.geo_full[0], 0u);
 #pragma unroll
       for (int i = 0; i < ITERS; ++i) gather(i, l_x, geo[row0 + i * NP * 4].x);
@@ -386,7 +398,7 @@ dcn_dgrad_kernel(const DcnParams prm, const DcnBwdParams bw) {
           l_cb = 0; ++l_it;
           if (have_next) {
             const int tile = tile_first + l_it;
-            l_x = prm.xh + (size_t)(tile / prm.tiles_per_image) * Pin * Cin + chunk * 8;
+            l_x = prm.xh + (size_t)(tile / prm.tiles_per_image) * Pin * Cin + chunk * 4;
             dcn_mbar_wait(&bars.geo_full[l_it & 1], (unsigned)((l_it >> 1) & 1));
           }
         }
@@ -394,13 +406,19 @@ dcn_dgrad_kernel(const DcnParams prm, const DcnBwdParams bw) {
       const __nv_bfloat16* l_xc = l_x + l_cb * kBK;
       const uint4* geo_n = geo + ((l_it & 1) * 9 + l_t) * kTileM + row0;
       const uint4* geo_c = geo + ((c_it & 1) * 9 + c_t) * kTileM + row0;
-      float* gxp = bw.gx + (size_t)c_img * Pin * Cin + c_cb * kBK + chunk * 8;
+      float* gxp = bw.gx + (size_t)c_img * Pin * Cin + c_cb * kBK + chunk * 4;
       dcn_mbar_wait(&bars.g_full[gs], gph);
       const uint8_t* g_tile = gring + (size_t)gs * g_bytes;
 #pragma unroll
       for (int i = 0; i < ITERS; ++i) {
         const uint4 q4 = geo_c[i * NP * 4];
-        const uint4 gq = *reinterpret_cast<const uint4*>(g_tile + (row0 + (uint32_t)(i * NP * 4)) * 128u + swz);
+        uint4 gq;                                  // G channels [4c,4c+4) and [32+4c,32+4c+4) of this row
+        {
+          const uint8_t* grow = g_tile + (row0 + (uint32_t)(i * NP * 4)) * 128u + g_half;
+          const uint2 lo = *reinterpret_cast<const uint2*>(grow + g_sw_lo);
+          const uint2 hi = *reinterpret_cast<const uint2*>(grow + g_sw_hi);
+          gq = make_uint4(lo.x, lo.y, hi.x, hi.y);
+        }
         const uint32_t g = q4.x;
         const float lh = __uint_as_float(q4.y), lw = __uint_as_float(q4.z), m = __uint_as_float(q4.w);
         const float g8[8] = {bf_lo(gq.x), bf_hi(gq.x), bf_lo(gq.y), bf_hi(gq.y),
@@ -418,7 +436,7 @@ dcn_dgrad_kernel(const DcnParams prm, const DcnBwdParams bw) {
           auto scat = [&](uint32_t e, float c) {
             if (c != 0.f) {
               red_add_v4(gxp + e, g8[0] * c, g8[1] * c, g8[2] * c, g8[3] * c);
-              red_add_v4(gxp + e + 4, g8[4] * c, g8[5] * c, g8[6] * c, g8[7] * c);
+              red_add_v4(gxp + e + 32, g8[4] * c, g8[5] * c, g8[6] * c, g8[7] * c);
             }
           };
           scat(e0, m * w1); scat(e0 + dx, m * w2); scat(e2, m * w3); scat(e2 + dx, m * w4);
