@@ -440,7 +440,7 @@ decode_finalize_kernel(DecodeHeader* __restrict__ hdrs, unsigned int* __restrict
                        int64_t* __restrict__ inds) {
   __shared__ SelectScratch sc;
   __shared__ BinScratch bs;
-  __shared__ u64 s_sel[kSelCap];
+  __shared__ __align__(16) u64 s_sel[kSelCap];
   __shared__ int s_n;
   const int tid = threadIdx.x;
   const int b = blockIdx.x;
@@ -482,15 +482,33 @@ decode_finalize_kernel(DecodeHeader* __restrict__ hdrs, unsigned int* __restrict
   __syncthreads();
   if (n < K) n = K;
   if (n <= kFinThreads) {
-    // rank sort: keys are distinct, so rank = number of larger keys; one key per thread, the
-    // compares read shared memory as broadcasts.  No barriers inside (a bitonic network of this
+    // rank sort: keys are distinct, so rank = number of larger keys.  All 512 threads work: with
+    // P2 = next power of two >= n, thread t owns key t % P2 and compares it against slice t / P2
+    // of the list (two keys per 16-byte shared-memory broadcast load); partial ranks are combined
+    // with shared-memory atomics.  No barriers inside the compare loop (a bitonic network of this
     // size costs ~36 __syncthreads).
-    u64 mine = 0ull; int rank = K;
-    if (tid < n) {
-      mine = s_sel[tid];
-      rank = 0;
-      for (int j2 = 0; j2 < n; ++j2) rank += (s_sel[j2] > mine);
+    __shared__ int s_rank[kFinThreads];
+    int P2 = 32; while (P2 < n) P2 <<= 1;
+    const int parts = kFinThreads / P2, idx = tid & (P2 - 1), part = tid / P2;
+    s_rank[tid] = 0;
+    if (n & 1) { if (tid == 0) s_sel[n] = 0ull; }          // pad to an even count for the paired loads
+    __syncthreads();
+    const int npair = (n + 1) >> 1;
+    const int j_lo = (int)(((long long)part * npair) / parts), j_hi = (int)(((long long)(part + 1) * npair) / parts);
+    u64 mine = 0ull;
+    if (idx < n) {
+      mine = s_sel[idx];
+      int rank = 0;
+      const ulonglong2* pairs = reinterpret_cast<const ulonglong2*>(s_sel);
+#pragma unroll 4
+      for (int j2 = j_lo; j2 < j_hi; ++j2) {
+        const ulonglong2 kk = pairs[j2];
+        rank += (kk.x > mine) + (kk.y > mine);
+      }
+      if (rank) atomicAdd(&s_rank[idx], rank);
     }
+    __syncthreads();
+    const int rank = (part == 0 && idx < n) ? s_rank[idx] : K;
     __syncthreads();
     if (rank < K) s_sel[rank] = mine;
     __syncthreads();

@@ -222,3 +222,9 @@ def _smoke():
     got = dcnv2_forward(*[torch.from_numpy(a).to(dev) for a in (x, off, m, w, b)], stride=1, padding=1).cpu().numpy()
     err = np.abs(got - ref).max() / np.abs(ref).max()
     assert err < 2e-2, "DCN smoke mismatch: %g" % err
+    gy = rng.normal(size=ref.shape).astype(np.float32)
+    ref_g = DO.dcn_backward(x, off, m, w, gy, 1, 1, 1)
+    got_g = dcnv2_backward(*[torch.from_numpy(a).to(dev) for a in (x, off, m, w, gy)], stride=1, padding=1)
+    for name, g, r in zip(("grad_input", "grad_offset", "grad_mask", "grad_weight", "grad_bias"), got_g, ref_g):
+        e = np.linalg.norm(g.cpu().numpy() - r) / np.linalg.norm(r)
+        assert e < 1.5e-2, "DCN backward smoke mismatch (%s): %g" % (name, e)
