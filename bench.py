@@ -33,7 +33,7 @@ B_PER_GPU, C, H, W, K, INPUT = 32, 80, 128, 128, 100, 512
 METRIC = "ctdet target-gen + focal/RegL1 loss fwd+bwd + top-100 decode, images/sec @512^2"
 WORKLOAD = ("ctdet DLA-34 training-step heads, batch=32/GPU @512^2 (80x128x128 heatmap, <=40 objects/image): "
             "gaussian targets + fused focal/RegL1 loss fwd+bwd + top-100 decode with 3x3 peak NMS")
-BYTES_PER_CELL = {"target_gen": 4, "loss": 12, "decode": 4}
+BYTES_PER_CELL = {"target_gen": 4, "loss": 12, "decode": 4, "fused_target_loss": 8}
 
 
 def peaks():
@@ -205,6 +205,25 @@ def run_ours(args):
         graph.replay()
         return graph_out
 
+    # Separate variant: targets generated inside the loss kernel, the
+    # heatmap target never reaches HBM (8 B/cell on the training side instead of 16).
+    slots = {k: v for k, v in gt.items() if k != "hm"}
+
+    def hot_path_fused(hm, wh, reg, bx, cls_, off):
+        L._FusedTargetLoss.apply(hm, wh, reg, bx, cls_, off, alpha, None, 2, weights, slots)
+        return D.ctdet_decode_batch(hm, wh, reg, down_ratio=4, K=K, logits=True)
+
+    for _ in range(2):
+        hot_path_fused(d_hm, d_wh, d_reg, d_boxes, d_classes, d_offsets)
+    torch.cuda.synchronize()
+    graph_f = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(cap_stream):
+        hot_path_fused(d_hm, d_wh, d_reg, d_boxes, d_classes, d_offsets)
+        cap_stream.synchronize()
+        with torch.cuda.graph(graph_f, stream=cap_stream):
+            hot_path_fused(d_hm, d_wh, d_reg, d_boxes, d_classes, d_offsets)
+    torch.cuda.synchronize()
+
     def step_e2e():
         hm = h_hm.to(dev, non_blocking=True)
         wh = h_wh.to(dev, non_blocking=True)
@@ -248,6 +267,7 @@ def run_ours(args):
         sampler.start()
         sampler.ready.wait(timeout=5)
     total_ms = timed(step_device, args.steps, args.warmup, True)
+    fused_ms = timed(graph_f.replay, args.steps, args.warmup, True)
 
     # dominant kernel alone (fused loss), CUDA events on the launching stream, L2 flushed
     def loss_only():
@@ -256,7 +276,9 @@ def run_ours(args):
     per_kernel = {}
     for name, fn in (("loss", loss_only),
                      ("target_gen", lambda: T.target_gen(d_boxes, d_classes, d_offsets, B, C, H, W, out=gt)),
-                     ("decode", lambda: D.ctdet_decode_batch(d_hm, d_wh, d_reg, down_ratio=4, K=K, logits=True))):
+                     ("decode", lambda: D.ctdet_decode_batch(d_hm, d_wh, d_reg, down_ratio=4, K=K, logits=True)),
+                     ("fused_target_loss", lambda: L._FusedTargetLoss.apply(d_hm, d_wh, d_reg, d_boxes, d_classes, d_offsets,
+                                                                             alpha, None, 2, weights, slots))):
         ms = timed(fn, max(args.steps, 10), 3, True) / max(args.steps, 10)
         per_kernel[name] = {"us": round(ms * 1e3, 2),
                             "GBps": round(cells * BYTES_PER_CELL[name] / (ms * 1e-3) / 1e9, 1)}
@@ -291,6 +313,11 @@ def run_ours(args):
                      "achieved": ach, "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4),
                      "peak_source": peak_src, "algorithmic_bytes_per_launch": cells * 12, "traffic": None},
         "kernels": per_kernel,
+        "fused_variant": {
+            "what": "same step with ctdet_target_loss_fused: the Gaussian target is built in shared memory inside the loss "
+                    "sweep and never written to HBM (SURVEY.md section 8 f2; 12 B/cell per step instead of 20)",
+            "value": round(world * B / (fused_ms / args.steps * 1e-3), 1), "unit": "images/s",
+            "ms_per_step": round(fused_ms / args.steps, 4), "gpu_launches_per_step": 4},
     }
     traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.isfile(traffic_file):

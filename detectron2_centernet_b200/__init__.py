@@ -8,7 +8,7 @@ Importing the package does not load the CUDA library; the first op call does, an
 libctdet_b200.so is missing (there is no CPU / PyTorch fallback).
 """
 from .target import gen_heatmap, gen_heatmap_batch                                    # noqa: F401
-from .losses import FocalLoss, RegL1Loss, _neg_loss, ctdet_losses                      # noqa: F401
+from .losses import FocalLoss, RegL1Loss, _neg_loss, ctdet_losses, ctdet_losses_from_objects                      # noqa: F401
 from .decode import (ctdet_decode, ctdet_decode_batch, _nms, _topk, _transpose_and_gather_feat,   # noqa: F401
                      postprocess_batch)
 from .deform_conv import DCN, DeformConvV2, ModulatedDeformConv, modulated_deform_conv, dcnv2_forward, dcnv2_backward   # noqa: F401

@@ -11,7 +11,7 @@
 //                                 |.| sum, scatter-add the gradient (duplicates accumulate)
 //              CTAs [2B, grid) -> grid-stride float4 streaming sweep of the heatmap
 //              last CTA to finish -> the three loss scalars; resets the workspace to zero.
-#include "common.cuh"
+#include "target_common.cuh"
 
 namespace ctdet {
 
@@ -157,6 +157,110 @@ __device__ __forceinline__ pk2 cell2(float x0, float x1, float g0, float g1, flo
   return d;
 }
 
+// ---- pieces shared by loss_kernel and target_loss_fused_kernel ------------------------------------
+// normalisers: num_pos (focal) and sum(reg_mask) (RegL1), identical in every CTA; ends with a barrier
+__device__ __forceinline__ void loss_norms(const int32_t* __restrict__ num_pos_img, const float* __restrict__ norm_override,
+                                           const uint8_t* __restrict__ reg_mask, int B, int M, bool is_reg,
+                                           LossWs* ws, float* s_norm) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  float npos = 0.f, nmask = 0.f;
+  if (norm_override != nullptr) {
+    if (tid == 0) { npos = norm_override[0]; nmask = norm_override[1]; }
+  } else {
+    if (warp == 0) {
+      if (num_pos_img != nullptr) {
+        int a = 0;
+        for (int i = lane; i < B; i += 32) a += num_pos_img[i];
+        npos = (float)warp_sum(a);
+      } else {
+        npos = (float)ws->npos_count;     // written by count_pos_kernel (stream order)
+      }
+    }
+    if (is_reg && warp == 1) {
+      int a = 0;
+      for (int i = lane; i < B * M; i += 32) a += reg_mask[i];
+      nmask = (float)warp_sum(a);
+      if (lane == 0) s_norm[1] = nmask;
+    }
+  }
+  if (tid == 0) { s_norm[0] = npos; if (norm_override != nullptr) s_norm[1] = nmask; }
+  __syncthreads();
+}
+
+// RegL1 (:376-381) for image blockIdx.x >> 1, head blockIdx.x & 1 (0 = wh, 1 = reg/offset): returns
+// this thread's share of sum |pred*m - tgt*m|; zero-fills and scatters the dense gradient.
+__device__ __forceinline__ double regl1_block(const float* __restrict__ wh, const float* __restrict__ reg,
+                                              const uint8_t* __restrict__ reg_mask, const int64_t* __restrict__ ind,
+                                              const float* __restrict__ gt_wh, const float* __restrict__ gt_reg,
+                                              float* __restrict__ d_wh, float* __restrict__ d_reg,
+                                              int HW, int M, float w_wh, float w_off, float nmask) {
+  const int tid = threadIdx.x;
+  const int b = blockIdx.x >> 1, h = blockIdx.x & 1;
+  const float* out = (h == 0 ? wh : reg);
+  const float* tgt = (h == 0 ? gt_wh : gt_reg) + (size_t)b * M * 2;
+  float* dout = (h == 0 ? d_wh : d_reg);
+  const int Mh = (out != nullptr) ? M : 0;                  // head absent: contributes nothing
+  if (out != nullptr) out += (size_t)b * 2 * HW; else dout = nullptr;
+  const float denom = 2.f * nmask + 1e-4f;                  // mask expanded to 2 channels (:378-380)
+  const float gscale = (h == 0 ? w_wh : w_off) / denom;
+  if (dout != nullptr) {
+    dout += (size_t)b * 2 * HW;
+    for (int i = tid; i < 2 * HW; i += kLossThreads) dout[i] = 0.f;
+    __syncthreads();
+  }
+  float a = 0.f;
+  for (int k = tid; k < Mh; k += kLossThreads) {
+    const float m = (float)reg_mask[(size_t)b * M + k];
+    const int64_t i = ind[(size_t)b * M + k];
+    if (i < 0 || i >= HW) continue;                         // the reference's gather would raise
+#pragma unroll
+    for (int ch = 0; ch < 2; ++ch) {
+      const float diff = out[(size_t)ch * HW + i] * m - tgt[2 * k + ch] * m;
+      a += fabsf(diff);
+      if (dout != nullptr && m != 0.f && diff != 0.f)       // sign(0) = 0
+        atomicAdd(dout + (size_t)ch * HW + i, (diff > 0.f ? gscale : -gscale) * m);
+    }
+  }
+  return (double)a;
+}
+
+// CTA reduction -> fp64 atomics; the last CTA to finish writes the three loss scalars and re-zeroes
+// the workspace.
+__device__ __forceinline__ void loss_tail(double acc0, double acc1, bool is_reg, float nmask_cta, float w_wh, float w_off,
+                                          float* __restrict__ losses, LossWs* ws, double (*s_red)[kLossThreads / 32],
+                                          bool* s_last) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  acc0 = warp_sum(acc0);
+  acc1 = warp_sum(acc1);
+  if (lane == 0) { s_red[0][warp] = acc0; s_red[1][warp] = acc1; }
+  __syncthreads();
+  if (tid == 0) {
+    double a0 = 0.0, a1 = 0.0;
+    for (int w = 0; w < kLossThreads / 32; ++w) { a0 += s_red[0][w]; a1 += s_red[1][w]; }
+    if (is_reg) {
+      atomicAdd((blockIdx.x & 1) ? &ws->off_sum : &ws->wh_sum, a0);
+      if (blockIdx.x == 0) ws->nmask = nmask_cta;
+    } else {
+      atomicAdd(&ws->pos_sum, a0);                  // focal: the weighted loss itself
+    }
+    __threadfence();
+    *s_last = (atomicAdd(&ws->done, 1u) == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (*s_last && tid == 0) {
+    __threadfence();
+    const double focal = *((volatile double*)&ws->pos_sum);
+    const double whs = *((volatile double*)&ws->wh_sum), offs = *((volatile double*)&ws->off_sum);
+    const float nmask = *((volatile float*)&ws->nmask);
+    const float denom = 2.f * nmask + 1e-4f;
+    losses[0] = (float)focal;                        // = -(pos+neg)/num_pos * w_hm  (or -neg * w_hm)
+    losses[1] = ((float)whs / denom) * w_wh;
+    losses[2] = ((float)offs / denom) * w_off;
+    ws->pos_sum = 0.0; ws->neg_sum = 0.0; ws->wh_sum = 0.0; ws->off_sum = 0.0;
+    ws->npos_count = 0ull; ws->done = 0u; ws->nmask = 0.f;
+  }
+}
+
 template <bool kProb>
 __global__ void __launch_bounds__(kLossThreads)
 loss_kernel(const float* __restrict__ hm, const float* __restrict__ wh, const float* __restrict__ reg,
@@ -173,63 +277,12 @@ loss_kernel(const float* __restrict__ hm, const float* __restrict__ wh, const fl
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const bool is_reg = (int)blockIdx.x < n_reg_ctas;
 
-  // ---- normalisers: num_pos (focal) and sum(reg_mask) (RegL1), identical in every CTA ------
-  {
-    float npos = 0.f, nmask = 0.f;
-    if (norm_override != nullptr) {
-      if (tid == 0) { npos = norm_override[0]; nmask = norm_override[1]; }
-    } else {
-      if (warp == 0) {
-        if (num_pos_img != nullptr) {
-          int a = 0;
-          for (int i = lane; i < B; i += 32) a += num_pos_img[i];
-          npos = (float)warp_sum(a);
-        } else {
-          npos = (float)ws->npos_count;     // written by count_pos_kernel (stream order)
-        }
-      }
-      if (is_reg && warp == 1) {
-        int a = 0;
-        for (int i = lane; i < B * M; i += 32) a += reg_mask[i];
-        nmask = (float)warp_sum(a);
-        if (lane == 0) s_norm[1] = nmask;
-      }
-    }
-    if (tid == 0) { s_norm[0] = npos; if (norm_override != nullptr) s_norm[1] = nmask; }
-    __syncthreads();
-  }
+  loss_norms(num_pos_img, norm_override, reg_mask, B, M, is_reg, ws, s_norm);
 
   double acc0 = 0.0, acc1 = 0.0;   // focal: (pos, neg)   RegL1: (abs-sum, unused)
 
   if (is_reg) {
-    // ---- RegL1 (:376-381) for image b, head h (0 = wh, 1 = reg/offset) ----------------------
-    const int b = blockIdx.x >> 1, h = blockIdx.x & 1;
-    const float* out = (h == 0 ? wh : reg);
-    const float* tgt = (h == 0 ? gt_wh : gt_reg) + (size_t)b * M * 2;
-    float* dout = (h == 0 ? d_wh : d_reg);
-    const int Mh = (out != nullptr) ? M : 0;                  // head absent: contributes nothing
-    if (out != nullptr) out += (size_t)b * 2 * HW; else dout = nullptr;
-    const float denom = 2.f * s_norm[1] + 1e-4f;             // mask expanded to 2 channels (:378-380)
-    const float gscale = (h == 0 ? w_wh : w_off) / denom;
-    if (dout != nullptr) {
-      dout += (size_t)b * 2 * HW;
-      for (int i = tid; i < 2 * HW; i += kLossThreads) dout[i] = 0.f;
-      __syncthreads();
-    }
-    float a = 0.f;
-    for (int k = tid; k < Mh; k += kLossThreads) {
-      const float m = (float)reg_mask[(size_t)b * M + k];
-      const int64_t i = ind[(size_t)b * M + k];
-      if (i < 0 || i >= HW) continue;                         // the reference's gather would raise
-#pragma unroll
-      for (int ch = 0; ch < 2; ++ch) {
-        const float diff = out[(size_t)ch * HW + i] * m - tgt[2 * k + ch] * m;
-        a += fabsf(diff);
-        if (dout != nullptr && m != 0.f && diff != 0.f)       // sign(0) = 0
-          atomicAdd(dout + (size_t)ch * HW + i, (diff > 0.f ? gscale : -gscale) * m);
-      }
-    }
-    acc0 = (double)a;
+    acc0 = regl1_block(wh, reg, reg_mask, ind, gt_wh, gt_reg, d_wh, d_reg, HW, M, w_wh, w_off, s_norm[1]);
   } else {
     // ---- focal loss sweep ---------------------------------------------------------------------
     const float npos = s_norm[0];
@@ -281,36 +334,149 @@ loss_kernel(const float* __restrict__ hm, const float* __restrict__ wh, const fl
     }
   }
 
-  // ---- CTA reduction -> fp64 atomics ----------------------------------------------------------
-  acc0 = warp_sum(acc0);
-  acc1 = warp_sum(acc1);
-  if (lane == 0) { s_red[0][warp] = acc0; s_red[1][warp] = acc1; }
-  __syncthreads();
-  if (tid == 0) {
-    double a0 = 0.0, a1 = 0.0;
-    for (int w = 0; w < kLossThreads / 32; ++w) { a0 += s_red[0][w]; a1 += s_red[1][w]; }
-    if (is_reg) {
-      atomicAdd((blockIdx.x & 1) ? &ws->off_sum : &ws->wh_sum, a0);
-      if (blockIdx.x == 0) ws->nmask = s_norm[1];
-    } else {
-      atomicAdd(&ws->pos_sum, a0);                  // focal: the weighted loss itself
+  loss_tail(acc0, acc1, is_reg, s_norm[1], w_wh, w_off, losses, ws, s_red, &s_last);
+}
+
+// ================================================================================================
+// Fused target generation + losses: the Gaussian heatmap target is built
+// per 16 KB band in SHARED memory (same binning / fp64 radius / max-reduce splat as
+// target_gen_kernel) and consumed on the spot by the focal-loss sweep, so it never exists in HBM:
+// read logits 4 + write d_logits 4 = 8 B per heatmap cell instead of 4 (target write) + 12.
+// Persistent CTAs loop over (band, class, image) items; the logits of item i+1 are prefetched into
+// registers while item i is computed.  Bands without an object of that class (most of them) skip the
+// shared-memory band entirely (gt == 0).  CTAs [0, 2B) do the RegL1 heads as in loss_kernel.  The
+// slot targets (wh / reg / ind / reg_mask) and num_pos come from target_slots_kernel, launched first.
+constexpr int kFusedCells = 4096;                 // heatmap cells per band: 16 KB of fp32, 4 float4 per thread
+constexpr int kFusedQ = kFusedCells / 4 / kLossThreads;
+
+__global__ void __launch_bounds__(kLossThreads)
+target_loss_fused_kernel(const int4* __restrict__ obj_geo, const double* __restrict__ obj_ninv,
+                         const int32_t* __restrict__ cls_count,
+                         const float* __restrict__ hm, const float* __restrict__ wh, const float* __restrict__ reg,
+                         const uint8_t* __restrict__ reg_mask, const int64_t* __restrict__ ind,
+                         const float* __restrict__ gt_wh, const float* __restrict__ gt_reg,
+                         const float* __restrict__ alpha, const int32_t* __restrict__ num_pos_img,
+                         const float* __restrict__ norm_override,
+                         int B, int C, int H, int W, int M, int band_rows, int bands, int flags, int n_reg_ctas,
+                         float w_hm, float w_wh, float w_off, float* __restrict__ losses,
+                         float* __restrict__ d_hm, float* __restrict__ d_wh, float* __restrict__ d_reg, LossWs* ws) {
+  __shared__ __align__(16) float s_band[kFusedCells];
+  __shared__ int s_cx[CTDET_MAX_OBJS], s_cy[CTDET_MAX_OBJS], s_r[CTDET_MAX_OBJS];
+  __shared__ double s_ninv[CTDET_MAX_OBJS];
+  __shared__ int s_nbin[2];
+  __shared__ float s_norm[2];
+  __shared__ double s_red[2][kLossThreads / 32];
+  __shared__ bool s_last;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const bool is_reg = (int)blockIdx.x < n_reg_ctas;
+  const int HW = H * W;
+
+  loss_norms(num_pos_img, norm_override, reg_mask, B, M, is_reg, ws, s_norm);   // ends with a barrier
+
+  double acc0 = 0.0, acc1 = 0.0;
+  if (is_reg) {
+    acc0 = regl1_block(wh, reg, reg_mask, ind, gt_wh, gt_reg, d_wh, d_reg, HW, M, w_wh, w_off, s_norm[1]);
+  } else {
+    const float npos = s_norm[0];
+    const float gscale = -(npos == 0.f ? w_hm : w_hm / npos);  // :365-368
+    const bool uniform_alpha = flags & CTDET_LOSS_ALPHA_UNIFORM;
+    const int items = bands * C * B;
+    const int stride = (int)gridDim.x - n_reg_ctas;
+    int it = (int)blockIdx.x - n_reg_ctas;
+    // item -> (band, class, image), band fastest; returns the band's first row and cell count
+    auto item_base = [&](int i, int& band, int& c, int& b, int& y0, int& cells) {
+      band = i % bands;
+      const int pc = i / bands;
+      c = pc % C; b = pc / C;
+      y0 = band * band_rows;
+      cells = (min(H, y0 + band_rows) - y0) * W;
+    };
+    float4 x[kFusedQ], xn[kFusedQ];
+    {
+      int band, c, b, y0, cells;
+      if (it < items) {
+        item_base(it, band, c, b, y0, cells);
+        const float* p = hm + ((size_t)(b * C + c) * H + y0) * W;
+#pragma unroll
+        for (int u = 0; u < kFusedQ; ++u) { const int j = tid + u * kLossThreads; if (4 * j < cells) x[u] = ldg_stream4(p + 4 * j); }
+      }
     }
-    __threadfence();
-    s_last = (atomicAdd(&ws->done, 1u) == gridDim.x - 1);
+    for (; it < items; it += stride) {
+      int band, c, b, y0, cells;
+      item_base(it, band, c, b, y0, cells);
+      const int y1 = y0 + cells / W;
+      if (it + stride < items) {                       // prefetch the next item's logits
+        int band2, c2, b2, y02, cells2;
+        item_base(it + stride, band2, c2, b2, y02, cells2);
+        const float* p2 = hm + ((size_t)(b2 * C + c2) * H + y02) * W;
+#pragma unroll
+        for (int u = 0; u < kFusedQ; ++u) { const int j = tid + u * kLossThreads; if (4 * j < cells2) xn[u] = ldg_stream4(p2 + 4 * j); }
+      }
+      // ---- objects of class c in this image (table written by target_slots_kernel) -----------------
+      const int cnt = __ldg(cls_count + (size_t)b * C + c);     // CTA-uniform; 0 for most (image, class) pairs
+      int nbin = 0;
+      if (cnt > 0) {
+        __syncthreads();                               // previous user of s_band / s_c* / s_nbin is done
+        if (tid == 0) s_nbin[0] = 0;
+        __syncthreads();
+        if (tid < CTDET_MAX_OBJS) {
+          const int4 q = __ldg(obj_geo + (size_t)b * CTDET_MAX_OBJS + tid);
+          if (q.w == c && q.y + q.z >= y0 && q.y - q.z < y1) {      // window touches this band
+            const int slot = atomicAdd(&s_nbin[0], 1);
+            s_cx[slot] = q.x; s_cy[slot] = q.y; s_r[slot] = q.z;
+            s_ninv[slot] = obj_ninv[(size_t)b * CTDET_MAX_OBJS + tid];
+          }
+        }
+        __syncthreads();
+        nbin = s_nbin[0];
+      }
+      if (nbin > 0) {                                  // CTA-uniform
+        for (int i = tid * 4; i < cells; i += kLossThreads * 4) *reinterpret_cast<float4*>(s_band + i) = make_float4(0.f, 0.f, 0.f, 0.f);
+        __syncthreads();
+        for (int o = warp; o < nbin; o += kLossThreads / 32) {
+          const int cx = s_cx[o], cy = s_cy[o], r = s_r[o];
+          const double ninv = s_ninv[o];
+          const int wx0 = max(cx - r, 0), wx1 = min(cx + r, W - 1);     // :698
+          const int wy0 = max(cy - r, y0), wy1 = min(cy + r, y1 - 1);   // :699, clipped to the band
+          const int ncols = wx1 - wx0 + 1;
+          const int total = ncols * (wy1 - wy0 + 1);
+          for (int i = lane; i < total; i += 32) {
+            const int yy = wy0 + i / ncols, xx = wx0 + i % ncols;
+            const int dx = xx - cx, dy = yy - cy;
+            const float t = (float)((double)(dx * dx + dy * dy) * ninv);   // :686, exponent in fp64
+            atomicMax(reinterpret_cast<int*>(s_band + (yy - y0) * W + xx), __float_as_int(expf(t)));  // :704
+          }
+        }
+        __syncthreads();
+      }
+      // ---- focal loss + gradient for the band ----------------------------------------------------
+      const float al = uniform_alpha ? __ldg(alpha) : __ldg(alpha + c);
+      float* dp = d_hm ? d_hm + ((size_t)(b * C + c) * H + y0) * W : nullptr;
+      pk2 tot = bcast2(0.f);
+      float tot_pos = 0.f;
+#pragma unroll
+      for (int u = 0; u < kFusedQ; ++u) {
+        const int j = tid + u * kLossThreads;
+        if (4 * j < cells) {
+          float4 g4 = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (nbin > 0) g4 = *reinterpret_cast<const float4*>(s_band + 4 * j);
+          const pk2 d01 = cell2<false>(x[u].x, x[u].y, g4.x, g4.y, al, gscale, tot, tot_pos);
+          const pk2 d23 = cell2<false>(x[u].z, x[u].w, g4.z, g4.w, al, gscale, tot, tot_pos);
+          if (dp != nullptr) {
+            float4 d;
+            unpack2(d01, d.x, d.y); unpack2(d23, d.z, d.w);
+            stg_stream4(dp + 4 * j, d);
+          }
+        }
+      }
+      float t0, t1;
+      unpack2(tot, t0, t1);
+      acc0 += (double)(t0 + t1) + (double)tot_pos;
+#pragma unroll
+      for (int u = 0; u < kFusedQ; ++u) x[u] = xn[u];
+    }
   }
-  __syncthreads();
-  if (s_last && tid == 0) {
-    __threadfence();
-    const double focal = *((volatile double*)&ws->pos_sum);
-    const double whs = *((volatile double*)&ws->wh_sum), offs = *((volatile double*)&ws->off_sum);
-    const float nmask = *((volatile float*)&ws->nmask);
-    const float denom = 2.f * nmask + 1e-4f;
-    losses[0] = (float)focal;                        // = -(pos+neg)/num_pos * w_hm  (or -neg * w_hm)
-    losses[1] = ((float)whs / denom) * w_wh;
-    losses[2] = ((float)offs / denom) * w_off;
-    ws->pos_sum = 0.0; ws->neg_sum = 0.0; ws->wh_sum = 0.0; ws->off_sum = 0.0;
-    ws->npos_count = 0ull; ws->done = 0u; ws->nmask = 0.f;
-  }
+  loss_tail(acc0, acc1, is_reg, s_norm[1], w_wh, w_off, losses, ws, s_red, &s_last);
 }
 
 }  // namespace ctdet
@@ -386,5 +552,60 @@ extern "C" int ctdet_loss_fwd_bwd(const float* hm, const float* wh, const float*
       hm, wh, reg, gt_hm, reg_mask, ind, gt_wh, gt_reg, alpha, num_pos_img, norm_override,
       B, C, (int)HW, M, flags, n_reg, FastDiv((uint32_t)(HW / 4)), FastDiv((uint32_t)C), w_hm, w_wh, w_off,
       losses, d_hm, d_wh, d_reg, ws);
+  return check_launch();
+}
+
+extern "C" size_t ctdet_fused_workspace_bytes(int B, int C) {
+  if (B <= 0 || C <= 0) return 0;
+  static_assert(sizeof(ctdet::LossWs) <= 256, "LossWs must fit the first 256 bytes");
+  return 256 + (size_t)B * CTDET_MAX_OBJS * (sizeof(int4) + sizeof(double)) + (size_t)B * C * sizeof(int32_t);
+}
+
+extern "C" int ctdet_target_loss_fused(const float* boxes, const int64_t* classes, const int32_t* offsets,
+                                       const float* hm, const float* wh, const float* reg,
+                                       const float* alpha, const float* norm_override,
+                                       int B, int C, int H, int W, int flags,
+                                       float w_hm, float w_wh, float w_off,
+                                       uint8_t* reg_mask, int64_t* ind, float* gt_wh, float* gt_reg, int32_t* num_pos,
+                                       float* losses, float* d_hm, float* d_wh, float* d_reg,
+                                       void* workspace, size_t workspace_bytes, ctdet_stream_t stream) {
+  using namespace ctdet;
+  if (B <= 0 || C <= 0 || H <= 0 || W <= 0) return CTDET_EINVAL;
+  if (flags & ~CTDET_LOSS_ALPHA_UNIFORM) return CTDET_EINVAL;
+  if (!offsets || !hm || !wh || !reg || !alpha || !reg_mask || !ind || !gt_wh || !gt_reg || !num_pos || !losses || !workspace)
+    return CTDET_ENULL;
+  if (workspace_bytes < ctdet_fused_workspace_bytes(B, C)) return CTDET_EWORKSPACE;
+  if (W % 4 != 0 || W > kFusedCells) return CTDET_EUNSUPPORTED;          // float4 rows, one row must fit a band
+  if ((int64_t)C * H * W >= ((int64_t)1 << 31) || B > 65535) return CTDET_EINVAL;
+  if (!aligned16(hm) || (d_hm && !aligned16(d_hm)) || (reinterpret_cast<uintptr_t>(workspace) & 15u)) return CTDET_EALIGN;
+  cudaStream_t st = (cudaStream_t)stream;
+  unsigned char* wsp = reinterpret_cast<unsigned char*>(workspace) + 256;          // [0,256): LossWs
+  int4* obj_geo = reinterpret_cast<int4*>(wsp);
+  wsp += (size_t)B * CTDET_MAX_OBJS * sizeof(int4);
+  double* obj_ninv = reinterpret_cast<double*>(wsp);
+  wsp += (size_t)B * CTDET_MAX_OBJS * sizeof(double);
+  int32_t* cls_count = reinterpret_cast<int32_t*>(wsp);
+  target_slots_kernel<<<B, CTDET_MAX_OBJS, 0, st>>>(boxes, classes, offsets, C, H, W, reg_mask, ind, gt_wh, gt_reg, num_pos,
+                                                    obj_geo, obj_ninv, cls_count);
+  int rc = check_launch();
+  if (rc) return rc;
+  int band_rows = kFusedCells / W;
+  if (band_rows > H) band_rows = H;
+  const int bands = (H + band_rows - 1) / band_rows;
+  const long long items = (long long)bands * C * B;
+  if (items >= ((long long)1 << 30)) return CTDET_EINVAL;
+  static int occ = 0;
+  if (occ == 0) {
+    int o = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, target_loss_fused_kernel, kLossThreads, 0) != cudaSuccess || o < 1) o = 2;
+    occ = o;
+  }
+  long long sweep = (long long)kNumSMs * occ;
+  if (sweep > items) sweep = items;
+  const int n_reg = 2 * B;
+  target_loss_fused_kernel<<<(unsigned)(n_reg + sweep), kLossThreads, 0, st>>>(
+      obj_geo, obj_ninv, cls_count, hm, wh, reg, reg_mask, ind, gt_wh, gt_reg, alpha, num_pos,
+      norm_override, B, C, H, W, CTDET_MAX_OBJS, band_rows, bands, flags, n_reg, w_hm, w_wh, w_off,
+      losses, d_hm, d_wh, d_reg, reinterpret_cast<LossWs*>(workspace));
   return check_launch();
 }

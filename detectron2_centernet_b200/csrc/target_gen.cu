@@ -9,58 +9,12 @@
 // every binned Gaussian with a max-reduce (atomicMax on the int view: all values are >= 0),
 // and writes the band to HBM exactly once with a single bulk async copy (cp.async.bulk
 // shared -> global, "UBLKCP" in SASS).  Algorithmic traffic: 4 B per heatmap cell.
-#include "common.cuh"
+#include "target_common.cuh"
 
 namespace ctdet {
 
 constexpr int kTgThreads = 256;
 constexpr int kBandBytes = 32 * 1024;
-
-// gaussian_radius (detection_utils.py:654-680) in fp64 with the reference's exact operation
-// order; every product/sum that is not exact is an explicit round-to-nearest op so that ptxas
-// cannot contract it into an FMA.  height/width are the math.ceil'ed box sides (:623).
-__device__ int gaussian_radius_int(int hh, int ww) {
-  const double mo = 0.7;
-  const double height = (double)hh, width = (double)ww;
-  const double s = height + width;                       // exact (integers)
-  const double area = width * height;                    // exact (integers)
-  const double c1 = __ddiv_rn(__dmul_rn(area, 1 - mo), 1 + mo);
-  const double sq1 = __dsqrt_rn(__dsub_rn(s * s, 4.0 * c1));
-  const double r1 = __dadd_rn(s, sq1) * 0.5;
-  const double b2 = 2.0 * s;
-  const double c2 = __dmul_rn(__dmul_rn(1 - mo, width), height);
-  const double sq2 = __dsqrt_rn(__dsub_rn(b2 * b2, 16.0 * c2));
-  const double r2 = __dadd_rn(b2, sq2) * 0.5;
-  const double a3 = 4 * mo;
-  const double b3 = __dmul_rn(-2 * mo, s);
-  const double c3 = __dmul_rn(__dmul_rn(mo - 1, width), height);
-  const double sq3 = __dsqrt_rn(__dsub_rn(__dmul_rn(b3, b3), __dmul_rn(4 * a3, c3)));
-  const double r3 = __dadd_rn(b3, sq3) * 0.5;
-  const double r = fmin(r1, fmin(r2, r3));
-  const int ri = (int)r;                                 // int(): truncate toward zero (:624)
-  return ri > 0 ? ri : 0;
-}
-
-struct ObjGeom {
-  float bw, bh, ctx, cty;
-  int cxi, cyi;
-  bool valid;
-};
-
-// fp32 box arithmetic exactly as torch evaluates detection_utils.py:618-627.
-__device__ __forceinline__ ObjGeom object_geometry(const float* __restrict__ box) {
-  ObjGeom g;
-  const float x1 = box[0] * 0.25f, y1 = box[1] * 0.25f;   // "/ 4" (:618), exact
-  const float x2 = box[2] * 0.25f, y2 = box[3] * 0.25f;
-  g.bw = __fsub_rn(x2, x1);
-  g.bh = __fsub_rn(y2, y1);
-  g.valid = (g.bh > 0.f) && (g.bw > 0.f);                 // :621
-  g.ctx = __fadd_rn(x1, x2) * 0.5f;                       // :625-626
-  g.cty = __fadd_rn(y1, y2) * 0.5f;
-  g.cxi = (int)g.ctx;                                     // astype(int32): truncation (:627)
-  g.cyi = (int)g.cty;
-  return g;
-}
 
 __global__ void __launch_bounds__(kTgThreads)
 target_gen_kernel(const float* __restrict__ boxes, const int64_t* __restrict__ classes,
@@ -175,6 +129,62 @@ target_gen_kernel(const float* __restrict__ boxes, const int64_t* __restrict__ c
     for (int i = tid; i < band_elems; i += kTgThreads) dst[i] = s_band[i];
     if (tid == 0 && slot_cta && num_pos != nullptr) num_pos[b] = s_npos;
   }
+}
+
+// Slot outputs and num_pos only (one CTA of 128 threads per image): the part of gen_heatmap that
+// the fused target + loss kernel needs before it starts (it never materialises the heatmap).
+__global__ void __launch_bounds__(CTDET_MAX_OBJS)
+target_slots_kernel(const float* __restrict__ boxes, const int64_t* __restrict__ classes,
+                    const int32_t* __restrict__ offsets, int C, int H, int W,
+                    uint8_t* __restrict__ reg_mask, int64_t* __restrict__ ind,
+                    float* __restrict__ wh, float* __restrict__ reg, int32_t* __restrict__ num_pos,
+                    int4* __restrict__ obj_geo, double* __restrict__ obj_ninv, int32_t* __restrict__ cls_count) {
+  __shared__ uint32_t s_key[CTDET_MAX_OBJS];
+  __shared__ int s_npos;
+  const int b = blockIdx.x, k = threadIdx.x;
+  const int o0 = offsets[b];
+  const int n = min(offsets[b + 1] - o0, CTDET_MAX_OBJS);
+  if (k == 0) s_npos = 0;
+  if (cls_count != nullptr) {
+    for (int c = k; c < C; c += CTDET_MAX_OBJS) cls_count[(size_t)b * C + c] = 0;
+    __syncthreads();
+  }
+  const bool have = k < n;
+  const int64_t cls = have ? classes[o0 + k] : -1;
+  ObjGeom g;
+  g.valid = false;
+  if (have) g = object_geometry(boxes + 4 * (size_t)(o0 + k));
+  const bool inside = g.valid && g.cxi >= 0 && g.cxi < W && g.cyi >= 0 && g.cyi < H;
+  const size_t o = (size_t)b * CTDET_MAX_OBJS + k;
+  const bool v = g.valid;
+  wh[2 * o] = v ? g.bw : 0.f;
+  wh[2 * o + 1] = v ? g.bh : 0.f;
+  reg[2 * o] = v ? __fsub_rn(g.ctx, (float)g.cxi) : 0.f;
+  reg[2 * o + 1] = v ? __fsub_rn(g.cty, (float)g.cyi) : 0.f;
+  ind[o] = v ? (int64_t)g.cyi * W + g.cxi : 0;
+  reg_mask[o] = v ? 1 : 0;
+  s_key[k] = (inside && cls >= 0 && cls < C) ? (uint32_t)((int)cls * H * W + g.cyi * W + g.cxi) : 0xffffffffu;
+  if (obj_geo != nullptr) {
+    // splat table of the fused target + loss kernel: centre, radius, class (-1 = not splatted), -1/(2 sigma^2)
+    int4 q = make_int4(0, 0, 0, -1);
+    double ninv = 0.0;
+    if (inside && cls >= 0 && cls < C) {
+      const int r = gaussian_radius_int((int)ceilf(g.bh), (int)ceilf(g.bw));
+      const double sigma = (double)(2 * r + 1) / 6.0;        // :692
+      q = make_int4(g.cxi, g.cyi, r, (int)cls);
+      ninv = -1.0 / (2.0 * sigma * sigma);
+      atomicAdd(&cls_count[(size_t)b * C + (int)cls], 1);
+    }
+    obj_geo[o] = q;
+    obj_ninv[o] = ninv;
+  }
+  __syncthreads();
+  const uint32_t key = s_key[k];
+  bool first = key != 0xffffffffu;
+  for (int j = 0; j < k && first; ++j) first = s_key[j] != key;
+  if (first) atomicAdd(&s_npos, 1);
+  __syncthreads();
+  if (k == 0 && num_pos != nullptr) num_pos[b] = s_npos;
 }
 
 }  // namespace ctdet

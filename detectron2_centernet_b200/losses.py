@@ -151,6 +151,70 @@ def ctdet_losses(outputs, targets, alpha=None, weights=(1.0, 0.1, 1.0), norm=Non
     return {"hm_loss": out[0], "wh_loss": out[1], "off_loss": out[2]}
 
 
+class _FusedTargetLoss(torch.autograd.Function):
+    """ctdet_target_loss_fused: targets from the objects and the three losses in one pass; the
+    gradients come out of the same sweep (see _FusedLoss)."""
+
+    @staticmethod
+    def forward(ctx, hm, wh, reg, boxes, classes, offsets, alpha, norm, flags, weights, slots):
+        lib = _lib.load()
+        dev = hm.device
+        B, C, H, W = hm.shape
+        need = any(t.requires_grad for t in (hm, wh, reg))
+        losses = torch.empty(3, dtype=torch.float32, device=dev)
+        d_hm = torch.empty_like(hm) if need else None
+        d_wh = torch.empty_like(wh) if need else None
+        d_reg = torch.empty_like(reg) if need else None
+        ws = _lib.zero_workspace("loss_fused", lib.ctdet_fused_workspace_bytes(B, C), dev)
+        with torch.cuda.device(dev):
+            rc = lib.ctdet_target_loss_fused(
+                _lib.ptr(boxes), _lib.ptr(classes), _lib.ptr(offsets), _lib.ptr(hm), _lib.ptr(wh), _lib.ptr(reg),
+                _lib.ptr(alpha), _lib.ptr(norm), B, C, H, W, flags, weights[0], weights[1], weights[2],
+                _lib.ptr(slots["reg_mask"]), _lib.ptr(slots["ind"]), _lib.ptr(slots["wh"]), _lib.ptr(slots["reg"]),
+                _lib.ptr(slots["num_pos"]), _lib.ptr(losses), _lib.ptr(d_hm), _lib.ptr(d_wh), _lib.ptr(d_reg),
+                _lib.ptr(ws), ctypes.c_size_t(ws.numel()), _lib.stream_ptr(dev))
+        _lib.check(rc, "ctdet_target_loss_fused")
+        ctx.grads = (d_hm, d_wh, d_reg)
+        return losses
+
+    @staticmethod
+    def backward(ctx, g):
+        d_hm, d_wh, d_reg = ctx.grads
+        ctx.grads = None
+        g = g.contiguous()
+        return (_scaled(d_hm, g[0:1]), _scaled(d_wh, g[1:2]), _scaled(d_reg, g[2:3]),
+                None, None, None, None, None, None, None, None)
+
+
+def ctdet_losses_from_objects(outputs, boxes, classes, offsets, alpha=None, weights=(1.0, 0.1, 1.0), norm=None,
+                              slots=None):
+    """gen_heatmap for the batch (detection_utils.py:600, called at centernet.py:188) fused with
+    CenterNet.losses (:191-212): the heatmap target is generated band by band in shared memory and
+    never written to HBM.  Objects in the CSR form of `target.pack_instances` / ctdet_target_gen:
+    boxes f32 [total,4] XYXY input pixels, classes i64 [total], offsets i32 [B+1] (device tensors).
+    Returns (loss dict, slot targets dict {reg_mask, ind, wh, reg, num_pos}); `slots` lets the
+    caller reuse the slot buffers between steps."""
+    hm = _prep(outputs["hm"], "ctdet losses")
+    wh = _prep(outputs["wh"], "ctdet losses")
+    reg = _prep(outputs["reg"], "ctdet losses")
+    _lib.require_cuda("ctdet losses", boxes, classes, offsets)
+    B, C = hm.shape[0], hm.shape[1]
+    dev = hm.device
+    if offsets.numel() != B + 1:
+        raise RuntimeError("offsets must have B + 1 = %d entries, got %d" % (B + 1, offsets.numel()))
+    if slots is None:
+        slots = {"reg_mask": torch.empty((B, 128), dtype=torch.uint8, device=dev),
+                 "ind": torch.empty((B, 128), dtype=torch.int64, device=dev),
+                 "wh": torch.empty((B, 128, 2), dtype=torch.float32, device=dev),
+                 "reg": torch.empty((B, 128, 2), dtype=torch.float32, device=dev),
+                 "num_pos": torch.empty((B,), dtype=torch.int32, device=dev)}
+    a = alpha_tensor(alpha, C, dev)
+    out = _FusedTargetLoss.apply(hm, wh, reg, boxes.contiguous(), classes.contiguous(), offsets.contiguous(), a, norm,
+                                 _FLAG_ALPHA_UNIFORM if alpha_is_uniform(alpha) else 0,
+                                 tuple(float(w) for w in weights), slots)
+    return {"hm_loss": out[0], "wh_loss": out[1], "off_loss": out[2]}, slots
+
+
 def _neg_loss(pred, gt, alpha=None, num_pos=None):
     """Drop-in for centernet.py:333: pred = clamp(sigmoid(.)) probabilities [B,C,H,W]."""
     pred = _prep(pred, "_neg_loss")

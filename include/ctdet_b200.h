@@ -15,6 +15,7 @@
  *   ctdet_loss_fwd_bwd   centernet.py:191-212 CenterNet.losses = :204 sigmoid_+clamp, :323-369
  *                        FocalLoss/_neg_loss, :372-381 RegL1Loss (+ :383 _transpose_and_gather_feat)
  *                        and their autograd backward
+ *   ctdet_target_loss_fused  the two rows above in one pass (gen_heatmap at centernet.py:188 + losses :191-212)
  *   ctdet_decode         centernet.py:426 ctdet_decode = :399 _nms, :408 _topk, :383 gather, boxes
  *   ctdet_nms / ctdet_gather_feat   centernet.py:399 _nms / :383 _transpose_and_gather_feat
  *   ctdet_postprocess    centernet.py:236-266 inference_single_image (slice + score threshold) and
@@ -100,6 +101,27 @@ int ctdet_loss_fwd_bwd(const float* hm, const float* wh, const float* reg,
                        float w_hm, float w_wh, float w_off,
                        float* losses, float* d_hm, float* d_wh, float* d_reg,
                        void* workspace, size_t workspace_bytes, ctdet_stream_t stream);
+
+/* ---------------------------------------------------------------- fused targets + losses -
+ * gen_heatmap for the whole batch AND CenterNet.losses in one pass: the
+ * Gaussian heatmap target is built per band in shared memory and consumed by the focal-loss sweep,
+ * it never exists in HBM (8 B per heatmap cell instead of 4 + 12).  Objects as in ctdet_target_gen,
+ * head outputs / alpha / norm_override / weights / losses / gradients as in ctdet_loss_fwd_bwd
+ * (hm holds raw logits; CTDET_LOSS_ALPHA_UNIFORM is the only flag).  The slot targets
+ * reg_mask u8 [B,128], ind i64 [B,128], gt_wh / gt_reg f32 [B,128,2] and num_pos i32 [B] are
+ * OUTPUTS (written by a small pre-pass) and remain valid for the caller.
+ * Requires W % 4 == 0 and W <= 4096.  workspace: ctdet_fused_workspace_bytes(B, C) bytes, 16-byte
+ * aligned; its first 256 bytes follow the ctdet_loss_fwd_bwd workspace contract (zero-filled once
+ * by the caller, left zeroed), the rest needs no initialisation. */
+size_t ctdet_fused_workspace_bytes(int B, int C);
+int ctdet_target_loss_fused(const float* boxes, const int64_t* classes, const int32_t* offsets,
+                            const float* hm, const float* wh, const float* reg,
+                            const float* alpha, const float* norm_override,
+                            int B, int C, int H, int W, int flags,
+                            float w_hm, float w_wh, float w_off,
+                            uint8_t* reg_mask, int64_t* ind, float* gt_wh, float* gt_reg, int32_t* num_pos,
+                            float* losses, float* d_hm, float* d_wh, float* d_reg,
+                            void* workspace, size_t workspace_bytes, ctdet_stream_t stream);
 
 /* d[i] *= *g for i < n, entirely skipped on the device when *g == 1 (autograd upstream gradient,
  * no host sync).  g: f32 device scalar. */

@@ -25,6 +25,9 @@ t=timeit(lambda: T.target_gen(tb,tc,to,B,C,H,W,out=gt)); print('target_gen us',t
 def loss():
     o=L.ctdet_losses({'hm':hm,'wh':wh,'reg':reg},gt,alpha=[1.0]); return o
 t=timeit(loss); print('loss fwd(+grad) us',t,'GB/s',el*12/t[0]/1e3)
+def fused():
+    return L.ctdet_losses_from_objects({'hm':hm,'wh':wh,'reg':reg},tb,tc,to,alpha=[1.0])
+t=timeit(fused); print('fused target+loss fwd(+grad) us',t,'GB/s (8 B/cell)',el*8/t[0]/1e3)
 def lossb():
     o=L.ctdet_losses({'hm':hm,'wh':wh,'reg':reg},gt,alpha=[1.0]); (o['hm_loss']+o['wh_loss']+o['off_loss']).backward(); hm.grad=None;wh.grad=None;reg.grad=None
 t=timeit(lossb); print('loss fwd+autograd bwd us',t)

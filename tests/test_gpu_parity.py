@@ -146,6 +146,34 @@ def test_fused_losses(case, tag, golden, inputs):
     assert np.array_equal(t_hm.detach().cpu().numpy(), hm)
 
 
+@pytest.mark.parametrize("case", CASES)
+@pytest.mark.parametrize("tag", ["a1", "acls"])
+def test_fused_targets_and_losses_from_objects(case, tag, golden, inputs):
+    """ctdet_target_loss_fused (gen_heatmap + CenterNet.losses in one pass, the heatmap target never
+    written to HBM): same losses / gradients / slot targets as the reference chain."""
+    from detectron2_centernet_b200 import losses as L
+    bl, cl, hm, wh, reg, (B, C, H, W, K, full) = inputs(case)
+    alpha = [1.0] if tag == "a1" else [0.25 + 0.01 * c for c in range(C)]
+    boxes, classes, offsets = S.pack_objects(bl, cl)
+    if len(classes) == 0:
+        boxes, classes = np.zeros((1, 4), np.float32), np.zeros((1,), np.int64)
+    t_b, t_c, t_o = _cuda(boxes, classes, offsets)
+    t_hm, t_wh, t_reg = [t.requires_grad_(True) for t in _cuda(hm, wh, reg)]
+    out, slots = L.ctdet_losses_from_objects({"hm": t_hm, "wh": t_wh, "reg": t_reg}, t_b, t_c, t_o, alpha=alpha)
+    (out["hm_loss"] + out["wh_loss"] + out["off_loss"]).backward()
+    torch.cuda.synchronize()
+    got = np.array([out[k].item() for k in ("hm_loss", "wh_loss", "off_loss")])
+    np.testing.assert_allclose(got, golden["%s/loss_%s" % (case, tag)], rtol=1e-5)   # vs the reference
+    gt_np = O.gen_heatmap_batch(bl, cl, H, W, C)
+    lo, gr = O.losses_and_grads(torch.from_numpy(hm), torch.from_numpy(wh), torch.from_numpy(reg), gt_np, alpha=alpha)
+    _check_grads(t_hm.grad, gr[0], "d_hm")
+    _check_grads(t_wh.grad, gr[1], "d_wh")
+    _check_grads(t_reg.grad, gr[2], "d_reg")
+    for k in ("reg_mask", "ind", "wh", "reg"):
+        assert np.array_equal(slots[k].cpu().numpy(), gt_np[k]), k
+    assert int(slots["num_pos"].sum().item()) == int((gt_np["hm"] == 1).sum())
+
+
 def test_fused_losses_with_num_pos_from_target_gen(inputs):
     """num_pos produced by ctdet_target_gen feeds the loss: no counting pre-pass, same numbers."""
     from detectron2_centernet_b200 import losses as L
