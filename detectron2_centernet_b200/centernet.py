@@ -41,6 +41,18 @@ class CenterNetHotPath:
         return L.ctdet_losses(outputs, targets, alpha=self.focal_loss_alpha,
                               weights=(self.hm_weight, self.wh_weight, self.off_weight), norm=norm)
 
+    def losses_from_instances(self, outputs, instances):
+        """`preprocess targets` (:188) + `losses` (:191-212) in ONE pass: the Gaussian heatmap target is
+        generated inside the focal-loss sweep and never written to HBM.  Returns (loss dict, slot targets)."""
+        if self.sync_num_pos:
+            # global normalisers need the slot targets of every rank before the sweep: two-pass path
+            hm = outputs["hm"]
+            targets = T.gen_heatmap_batch(instances, (hm.shape[2], hm.shape[3]), self.num_classes, hm.device)
+            return self.losses(outputs, targets), {k: v for k, v in targets.items() if k != "hm"}
+        boxes, classes, offsets = T.pack_instances(instances, outputs["hm"].device)
+        return L.ctdet_losses_from_objects(outputs, boxes, classes, offsets, alpha=self.focal_loss_alpha,
+                                           weights=(self.hm_weight, self.wh_weight, self.off_weight))
+
     # ---- inference -----------------------------------------------------------------------------
     def decode(self, outputs):
         """Whole batch: sigmoid+clamp (:161) folded in (ranking on logits), top-K, boxes."""

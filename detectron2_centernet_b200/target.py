@@ -46,12 +46,9 @@ def _num_classes(meta):
     return len(meta.thing_classes) if hasattr(meta, "thing_classes") else int(meta)
 
 
-def gen_heatmap_batch(instances, output_shape, meta, device=None):
-    """Batched gen_heatmap: `instances` is a list of per-image Instances (fields gt_boxes.tensor,
-    gt_classes).  One launch for the whole batch; returns the five tensors already concatenated as
-    CenterNet.losses builds them (centernet.py:197-201), plus num_pos i32[B]."""
-    H, W = int(output_shape[0]), int(output_shape[1])
-    C = _num_classes(meta)
+def pack_instances(instances, device=None):
+    """list of per-image Instances (fields gt_boxes.tensor, gt_classes) -> CSR device tensors
+    (boxes f32 [total,4], classes i64 [total], offsets i32 [B+1]) as the C ABI takes them."""
     B = len(instances)
     boxes = [x.gt_boxes.tensor for x in instances]
     classes = [x.gt_classes for x in instances]
@@ -69,7 +66,16 @@ def gen_heatmap_batch(instances, output_shape, meta, device=None):
     else:
         fb = torch.cat([b.reshape(-1, 4) for b in boxes]).to(device=device, dtype=torch.float32)
         fc = torch.cat([c.reshape(-1) for c in classes]).to(device=device, dtype=torch.int64)
-    return target_gen(fb, fc, offsets, B, C, H, W)
+    return fb, fc, offsets
+
+
+def gen_heatmap_batch(instances, output_shape, meta, device=None):
+    """Batched gen_heatmap: `instances` is a list of per-image Instances (fields gt_boxes.tensor,
+    gt_classes).  One launch for the whole batch; returns the five tensors already concatenated as
+    CenterNet.losses builds them (centernet.py:197-201), plus num_pos i32[B]."""
+    H, W = int(output_shape[0]), int(output_shape[1])
+    fb, fc, offsets = pack_instances(instances, device)
+    return target_gen(fb, fc, offsets, len(instances), _num_classes(meta), H, W)
 
 
 def gen_heatmap(instances, output_shape, meta):

@@ -469,6 +469,13 @@ def test_centernet_hot_path_losses_and_inference(inputs):
     out2 = model_sync.losses({"hm": t_hm, "wh": t_wh, "reg": t_reg}, targets)
     for k in out:
         np.testing.assert_allclose(out2[k].item(), out[k].item(), rtol=1e-6)
+    # one-pass variant: targets generated inside the loss sweep (no heatmap target in HBM)
+    out3, slots3 = model.losses_from_instances({"hm": t_hm, "wh": t_wh, "reg": t_reg}, insts)
+    out4, _ = model_sync.losses_from_instances({"hm": t_hm, "wh": t_wh, "reg": t_reg}, insts)
+    for k in out:
+        np.testing.assert_allclose(out3[k].item(), float(ref[k]), rtol=1e-5)
+        np.testing.assert_allclose(out4[k].item(), float(ref[k]), rtol=1e-5)
+    assert np.array_equal(slots3["ind"].cpu().numpy(), gt_np["ind"])
     # inference: list of Instances, thresholded (score > 0.05) and resized to the original image size
     sizes, orig = [(512, 512)] * B, [(1024, 768), (512, 512)][:B]
     res = model.inference({"hm": t_hm.detach(), "wh": t_wh.detach(), "reg": t_reg.detach()}, sizes, orig)
