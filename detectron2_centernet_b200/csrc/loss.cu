@@ -262,7 +262,7 @@ __device__ __forceinline__ void loss_tail(double acc0, double acc1, bool is_reg,
 }
 
 template <bool kProb>
-__global__ void __launch_bounds__(kLossThreads)
+__global__ void __launch_bounds__(kLossThreads, 3)
 loss_kernel(const float* __restrict__ hm, const float* __restrict__ wh, const float* __restrict__ reg,
             const float* __restrict__ gt, const uint8_t* __restrict__ reg_mask,
             const int64_t* __restrict__ ind, const float* __restrict__ gt_wh,
@@ -392,10 +392,12 @@ target_loss_fused_kernel(const int4* __restrict__ obj_geo, const double* __restr
       cells = (min(H, y0 + band_rows) - y0) * W;
     };
     float4 x[kFusedQ], xn[kFusedQ];
+    int cnt = 0, cnt_next = 0;                       // objects of the item's class in its image (prefetched with the logits)
     {
       int band, c, b, y0, cells;
       if (it < items) {
         item_base(it, band, c, b, y0, cells);
+        cnt = __ldg(cls_count + (size_t)b * C + c);
         const float* p = hm + ((size_t)(b * C + c) * H + y0) * W;
 #pragma unroll
         for (int u = 0; u < kFusedQ; ++u) { const int j = tid + u * kLossThreads; if (4 * j < cells) x[u] = ldg_stream4(p + 4 * j); }
@@ -408,12 +410,13 @@ target_loss_fused_kernel(const int4* __restrict__ obj_geo, const double* __restr
       if (it + stride < items) {                       // prefetch the next item's logits
         int band2, c2, b2, y02, cells2;
         item_base(it + stride, band2, c2, b2, y02, cells2);
+        cnt_next = __ldg(cls_count + (size_t)b2 * C + c2);
         const float* p2 = hm + ((size_t)(b2 * C + c2) * H + y02) * W;
 #pragma unroll
         for (int u = 0; u < kFusedQ; ++u) { const int j = tid + u * kLossThreads; if (4 * j < cells2) xn[u] = ldg_stream4(p2 + 4 * j); }
       }
       // ---- objects of class c in this image (table written by target_slots_kernel) -----------------
-      const int cnt = __ldg(cls_count + (size_t)b * C + c);     // CTA-uniform; 0 for most (image, class) pairs
+      // cnt is CTA-uniform; 0 for most (image, class) pairs
       int nbin = 0;
       if (cnt > 0) {
         __syncthreads();                               // previous user of s_band / s_c* / s_nbin is done
@@ -474,6 +477,7 @@ target_loss_fused_kernel(const int4* __restrict__ obj_geo, const double* __restr
       acc0 += (double)(t0 + t1) + (double)tot_pos;
 #pragma unroll
       for (int u = 0; u < kFusedQ; ++u) x[u] = xn[u];
+      cnt = cnt_next;
     }
   }
   loss_tail(acc0, acc1, is_reg, s_norm[1], w_wh, w_off, losses, ws, s_red, &s_last);
