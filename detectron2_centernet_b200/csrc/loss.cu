@@ -16,7 +16,13 @@
 namespace ctdet {
 
 constexpr int kLossThreads = 256;
-constexpr int kUnroll = 2;         // float4 chunks per thread per iteration (x and gt), double-buffered
+#ifndef CTDET_LOSS_UNROLL
+#define CTDET_LOSS_UNROLL 2
+#endif
+#ifndef CTDET_LOSS_MINB
+#define CTDET_LOSS_MINB 4
+#endif
+constexpr int kUnroll = CTDET_LOSS_UNROLL;         // float4 chunks per thread per iteration (x and gt), double-buffered
 
 struct LossWs {                    // must be zero on entry; left zero on exit
   double pos_sum, neg_sum, wh_sum, off_sum;   // pos_sum: weighted focal loss; neg_sum: unused
@@ -68,27 +74,37 @@ __device__ __forceinline__ float exp2f_approx(float a) {
 __device__ __forceinline__ pk2 rcp2(pk2 v) { float a, b; unpack2(v, a, b); return pack2(rcp_approx(a), rcp_approx(b)); }
 
 // ln(a) for a in (0, 1], ~2e-7 relative everywhere (the loss needs RELATIVE accuracy: ln(1-p) is as
-// small as 1e-4).  Near 1 (a >= 0.75): ln(a) = 2 atanh(s), s = (a-1)/(a+1), |s| <= 1/7, odd series
-// to s^7 (truncation 3e-9); a-1 is exact (Sterbenz).  Elsewhere: MUFU lg2 (2^-22 absolute in
-// (0.5,2), 2^-22 relative outside) on |ln a| > 0.28.  Branch-free.
+// small as 1e-4).  Near 1 (a >= 0.75): t = a - 1 is exact (Sterbenz) and ln(1+t) = t*Q(t) with a
+// degree-6 fit of ln(1+t)/t on [-0.25, 0] (fit error 2.7e-9, 1.2e-7 relative evaluated in fp32).
+// Elsewhere: MUFU lg2 (2^-22 absolute in (0.5,2), 2^-22 relative outside) on |ln a| > 0.28.
+// Branch-free; one MUFU per cell.
+#define CTDET_LOGQ0 1.0000000023e+00f
+#define CTDET_LOGQ1 -4.9999909689e-01f
+#define CTDET_LOGQ2 3.3338975475e-01f
+#define CTDET_LOGQ3 -2.4869018849e-01f
+#define CTDET_LOGQ4 2.1425246244e-01f
+#define CTDET_LOGQ5 -8.9520387982e-02f
+#define CTDET_LOGQ6 3.3390907240e-01f
 __device__ __forceinline__ float log_unit(float a) {
-  const float s = (a - 1.f) * rcp_approx(a + 1.f);
-  const float s2 = s * s;
-  float poly = fmaf(s2, 1.f / 7.f, 1.f / 5.f);
-  poly = fmaf(poly, s2, 1.f / 3.f);
-  poly = fmaf(poly, s2, 1.f);
-  const float near1 = (s + s) * poly;
+  const float t = a - 1.f;
+  float q = fmaf(CTDET_LOGQ6, t, CTDET_LOGQ5);
+  q = fmaf(q, t, CTDET_LOGQ4);
+  q = fmaf(q, t, CTDET_LOGQ3);
+  q = fmaf(q, t, CTDET_LOGQ2);
+  q = fmaf(q, t, CTDET_LOGQ1);
+  q = fmaf(q, t, CTDET_LOGQ0);
   const float far = lg2_approx(a) * 0.693147180559945309f;
-  return a >= 0.75f ? near1 : far;
+  return a >= 0.75f ? t * q : far;
 }
 __device__ __forceinline__ pk2 log_unit2(pk2 a) {
-  const pk2 one = bcast2(1.f);
-  const pk2 s = mul2(sub2(a, one), rcp2(add2(a, one)));
-  const pk2 s2 = mul2(s, s);
-  pk2 poly = fma2(s2, bcast2(1.f / 7.f), bcast2(1.f / 5.f));
-  poly = fma2(poly, s2, bcast2(1.f / 3.f));
-  poly = fma2(poly, s2, one);
-  const pk2 near1 = mul2(add2(s, s), poly);
+  const pk2 t = sub2(a, bcast2(1.f));
+  pk2 q = fma2(bcast2(CTDET_LOGQ6), t, bcast2(CTDET_LOGQ5));
+  q = fma2(q, t, bcast2(CTDET_LOGQ4));
+  q = fma2(q, t, bcast2(CTDET_LOGQ3));
+  q = fma2(q, t, bcast2(CTDET_LOGQ2));
+  q = fma2(q, t, bcast2(CTDET_LOGQ1));
+  q = fma2(q, t, bcast2(CTDET_LOGQ0));
+  const pk2 near1 = mul2(t, q);
   float a0, a1, n0, n1;
   unpack2(a, a0, a1);
   const pk2 far = mul2(pack2(lg2_approx(a0), lg2_approx(a1)), bcast2(0.693147180559945309f));
@@ -106,20 +122,35 @@ __device__ __forceinline__ pk2 log_unit2(pk2 a) {
 // (1-gt)^4 = 0 makes it contribute exactly 0 -- and the rare positives (~1 cell in 30,000) add
 // their term in a scalar fix-up branch.
 // The sigmoid uses the MUFU paths (ex2.approx / rcp.approx: <= 1e-6 relative on p over the
-// unclamped range |x| <= 9.3, checked against torch in the tests).
-template <bool kProb>
+// unclamped range |x| <= 9.3, checked against torch in the tests).  With logits the chain rule is
+// folded analytically, d/dx [log(1-p) p^2] = (2 p log(1-p) - p^2/(1-p)) * p(1-p)
+//                                          = 2 p^2 (1-p) log(1-p) - p^3,
+// which needs no reciprocal: 3 MUFU per cell in all (ex2, rcp, lg2).
+// kZeroGt: the caller knows gt == 0 for both cells (a band no Gaussian touches): (1-gt)^4 = 1 and
+// there is no positive to fix up.
+template <bool kProb, bool kZeroGt = false>
 __device__ __forceinline__ pk2 cell2(float x0, float x1, float g0, float g1, float alpha, float gscale,
                                      pk2& tot, float& tot_pos) {
   const pk2 one = bcast2(1.f);
-  float p0, p1, pc0, pc1, ds0, ds1;
-  pk2 pc, om, dsig;
+  pk2 coef = bcast2(gscale);
+  if (!kZeroGt) {
+    const pk2 w = sub2(one, pack2(g0, g1));
+    const pk2 w2 = mul2(w, w);
+    coef = mul2(mul2(w2, w2), coef);                           // (1-g)^4 * gscale
+  }
+  float p0, p1, pc0, pc1;
+  pk2 pc, om, d;
   if (kProb) {                                       // x already is pred (FocalLoss drop-in, :323)
-    pc0 = x0; pc1 = x1;
+    pc0 = p0 = x0; pc1 = p1 = x1;
     pc = pack2(x0, x1);
     om = sub2(one, pc);
-    dsig = one;
+    const pk2 l = log_unit2(om);
+    const pk2 aa = mul2(pc, pc);
+    tot = fma2(coef, mul2(l, aa), tot);                        // log(1-p) p^2 (1-g)^4
+    // d/dp [log(1-p) p^2] = 2 p log(1-p) - p^2 / (1-p)
+    d = mul2(coef, sub2(mul2(add2(pc, pc), l), mul2(aa, rcp2(om))));
   } else {
-    float e0, e1;
+    float e0, e1, d0, d1;
     unpack2(mul2(pack2(x0, x1), bcast2(-1.4426950408889634f)), e0, e1);
     const pk2 den = add2(pack2(exp2f_approx(e0), exp2f_approx(e1)), one);
     unpack2(rcp2(den), p0, p1);                       // sigmoid
@@ -127,28 +158,25 @@ __device__ __forceinline__ pk2 cell2(float x0, float x1, float g0, float g1, flo
     pc1 = fminf(fmaxf(p1, 1e-4f), 1.f - 1e-4f);
     pc = pack2(pc0, pc1);
     om = sub2(one, pc);
-    unpack2(mul2(pc, om), ds0, ds1);                  // p(1-p) where the clamp is inactive (pc == p)
-    dsig = pack2(pc0 == p0 ? ds0 : 0.f, pc1 == p1 ? ds1 : 0.f);
+    const pk2 l = log_unit2(om);
+    const pk2 aa = mul2(pc, pc);
+    const pk2 la = mul2(l, aa);
+    tot = fma2(coef, la, tot);                                 // log(1-p) p^2 (1-g)^4
+    unpack2(mul2(coef, sub2(mul2(add2(la, la), om), mul2(aa, pc))), d0, d1);
+    d = pack2(pc0 == p0 ? d0 : 0.f, pc1 == p1 ? d1 : 0.f);     // clamp active: no gradient
   }
-  const pk2 w = sub2(one, pack2(g0, g1));
-  const pk2 w2 = mul2(w, w);
-  const pk2 coef = mul2(mul2(w2, w2), bcast2(gscale));         // (1-g)^4 * gscale
-  const pk2 l = log_unit2(om);
-  const pk2 aa = mul2(pc, pc);
-  tot = fma2(coef, mul2(l, aa), tot);                          // log(1-p) p^2 (1-g)^4
-  // d/dp [log(1-p) p^2] = 2 p log(1-p) - p^2 / (1-p)
-  const pk2 dterm = sub2(mul2(add2(pc, pc), l), mul2(aa, rcp2(om)));
-  pk2 d = mul2(mul2(coef, dterm), dsig);
-  if (g0 == 1.f || g1 == 1.f) {                                // rare
-    float d0, d1, dsa, dsb, oma, omb;
-    unpack2(d, d0, d1); unpack2(dsig, dsa, dsb); unpack2(om, oma, omb);
+  if (!kZeroGt && (g0 == 1.f || g1 == 1.f)) {                  // rare
+    float d0, d1, oma, omb;
+    unpack2(d, d0, d1); unpack2(om, oma, omb);
     if (g0 == 1.f) {
       const float lp = log_unit(pc0);
+      const float dsa = kProb ? 1.f : (pc0 == p0 ? pc0 * oma : 0.f);   // d pred / dx
       tot_pos += gscale * alpha * (lp * (oma * oma));
       d0 = gscale * alpha * (oma * oma * rcp_approx(pc0) - 2.f * oma * lp) * dsa;   // d/dp [log p (1-p)^2]
     }
     if (g1 == 1.f) {
       const float lp = log_unit(pc1);
+      const float dsb = kProb ? 1.f : (pc1 == p1 ? pc1 * omb : 0.f);
       tot_pos += gscale * alpha * (lp * (omb * omb));
       d1 = gscale * alpha * (omb * omb * rcp_approx(pc1) - 2.f * omb * lp) * dsb;
     }
@@ -262,7 +290,7 @@ __device__ __forceinline__ void loss_tail(double acc0, double acc1, bool is_reg,
 }
 
 template <bool kProb>
-__global__ void __launch_bounds__(kLossThreads, 3)
+__global__ void __launch_bounds__(kLossThreads, CTDET_LOSS_MINB)
 loss_kernel(const float* __restrict__ hm, const float* __restrict__ wh, const float* __restrict__ reg,
             const float* __restrict__ gt, const uint8_t* __restrict__ reg_mask,
             const int64_t* __restrict__ ind, const float* __restrict__ gt_wh,
@@ -349,7 +377,7 @@ loss_kernel(const float* __restrict__ hm, const float* __restrict__ wh, const fl
 constexpr int kFusedCells = 4096;                 // heatmap cells per band: 16 KB of fp32, 4 float4 per thread
 constexpr int kFusedQ = kFusedCells / 4 / kLossThreads;
 
-__global__ void __launch_bounds__(kLossThreads)
+__global__ void __launch_bounds__(kLossThreads, 4)
 target_loss_fused_kernel(const int4* __restrict__ obj_geo, const double* __restrict__ obj_ninv,
                          const int32_t* __restrict__ cls_count,
                          const float* __restrict__ hm, const float* __restrict__ wh, const float* __restrict__ reg,
@@ -357,8 +385,8 @@ target_loss_fused_kernel(const int4* __restrict__ obj_geo, const double* __restr
                          const float* __restrict__ gt_wh, const float* __restrict__ gt_reg,
                          const float* __restrict__ alpha, const int32_t* __restrict__ num_pos_img,
                          const float* __restrict__ norm_override,
-                         int B, int C, int H, int W, int M, int band_rows, int bands, int flags, int n_reg_ctas,
-                         float w_hm, float w_wh, float w_off, float* __restrict__ losses,
+                         int B, int C, int H, int W, int M, int band_rows, int bands, FastDiv div_bands, FastDiv div_c,
+                         int flags, int n_reg_ctas, float w_hm, float w_wh, float w_off, float* __restrict__ losses,
                          float* __restrict__ d_hm, float* __restrict__ d_wh, float* __restrict__ d_reg, LossWs* ws) {
   __shared__ __align__(16) float s_band[kFusedCells];
   __shared__ int s_cx[CTDET_MAX_OBJS], s_cy[CTDET_MAX_OBJS], s_r[CTDET_MAX_OBJS];
@@ -383,51 +411,50 @@ target_loss_fused_kernel(const int4* __restrict__ obj_geo, const double* __restr
     const int items = bands * C * B;
     const int stride = (int)gridDim.x - n_reg_ctas;
     int it = (int)blockIdx.x - n_reg_ctas;
-    // item -> (band, class, image), band fastest; returns the band's first row and cell count
-    auto item_base = [&](int i, int& band, int& c, int& b, int& y0, int& cells) {
-      band = i % bands;
-      const int pc = i / bands;
-      c = pc % C; b = pc / C;
-      y0 = band * band_rows;
-      cells = (min(H, y0 + band_rows) - y0) * W;
+    // item -> (band, class, image), band fastest; the band's first row, cell count and plane index
+    struct Item { int c, y0, cells, plane; };
+    auto item_base = [&](int i, Item& q) {
+      const int pc = (int)div_bands.div((uint32_t)i);            // b*C + c
+      const int band = i - pc * bands;
+      q.plane = pc;
+      q.c = pc - (int)div_c.div((uint32_t)pc) * C;
+      q.y0 = band * band_rows;
+      q.cells = (min(H, q.y0 + band_rows) - q.y0) * W;
     };
     float4 x[kFusedQ], xn[kFusedQ];
     int cnt = 0, cnt_next = 0;                       // objects of the item's class in its image (prefetched with the logits)
-    {
-      int band, c, b, y0, cells;
-      if (it < items) {
-        item_base(it, band, c, b, y0, cells);
-        cnt = __ldg(cls_count + (size_t)b * C + c);
-        const float* p = hm + ((size_t)(b * C + c) * H + y0) * W;
+    Item cur = {0, 0, 0, 0}, nxt = {0, 0, 0, 0};
+    if (it < items) {
+      item_base(it, cur);
+      cnt = __ldg(cls_count + cur.plane);
+      const float* p = hm + ((size_t)cur.plane * H + cur.y0) * W;
 #pragma unroll
-        for (int u = 0; u < kFusedQ; ++u) { const int j = tid + u * kLossThreads; if (4 * j < cells) x[u] = ldg_stream4(p + 4 * j); }
-      }
+      for (int u = 0; u < kFusedQ; ++u) { const int j = tid + u * kLossThreads; if (4 * j < cur.cells) x[u] = ldg_stream4(p + 4 * j); }
     }
     for (; it < items; it += stride) {
-      int band, c, b, y0, cells;
-      item_base(it, band, c, b, y0, cells);
+      const int c = cur.c, y0 = cur.y0, cells = cur.cells;
       const int y1 = y0 + cells / W;
       if (it + stride < items) {                       // prefetch the next item's logits
-        int band2, c2, b2, y02, cells2;
-        item_base(it + stride, band2, c2, b2, y02, cells2);
-        cnt_next = __ldg(cls_count + (size_t)b2 * C + c2);
-        const float* p2 = hm + ((size_t)(b2 * C + c2) * H + y02) * W;
+        item_base(it + stride, nxt);
+        cnt_next = __ldg(cls_count + nxt.plane);
+        const float* p2 = hm + ((size_t)nxt.plane * H + nxt.y0) * W;
 #pragma unroll
-        for (int u = 0; u < kFusedQ; ++u) { const int j = tid + u * kLossThreads; if (4 * j < cells2) xn[u] = ldg_stream4(p2 + 4 * j); }
+        for (int u = 0; u < kFusedQ; ++u) { const int j = tid + u * kLossThreads; if (4 * j < nxt.cells) xn[u] = ldg_stream4(p2 + 4 * j); }
       }
       // ---- objects of class c in this image (table written by target_slots_kernel) -----------------
       // cnt is CTA-uniform; 0 for most (image, class) pairs
       int nbin = 0;
       if (cnt > 0) {
+        const int img = (int)div_c.div((uint32_t)cur.plane);
         __syncthreads();                               // previous user of s_band / s_c* / s_nbin is done
         if (tid == 0) s_nbin[0] = 0;
         __syncthreads();
         if (tid < CTDET_MAX_OBJS) {
-          const int4 q = __ldg(obj_geo + (size_t)b * CTDET_MAX_OBJS + tid);
+          const int4 q = __ldg(obj_geo + (size_t)img * CTDET_MAX_OBJS + tid);
           if (q.w == c && q.y + q.z >= y0 && q.y - q.z < y1) {      // window touches this band
             const int slot = atomicAdd(&s_nbin[0], 1);
             s_cx[slot] = q.x; s_cy[slot] = q.y; s_r[slot] = q.z;
-            s_ninv[slot] = obj_ninv[(size_t)b * CTDET_MAX_OBJS + tid];
+            s_ninv[slot] = obj_ninv[(size_t)img * CTDET_MAX_OBJS + tid];
           }
         }
         __syncthreads();
@@ -454,21 +481,36 @@ target_loss_fused_kernel(const int4* __restrict__ obj_geo, const double* __restr
       }
       // ---- focal loss + gradient for the band ----------------------------------------------------
       const float al = uniform_alpha ? __ldg(alpha) : __ldg(alpha + c);
-      float* dp = d_hm ? d_hm + ((size_t)(b * C + c) * H + y0) * W : nullptr;
+      float* dp = d_hm ? d_hm + ((size_t)cur.plane * H + y0) * W : nullptr;
       pk2 tot = bcast2(0.f);
       float tot_pos = 0.f;
+      if (nbin > 0) {
 #pragma unroll
-      for (int u = 0; u < kFusedQ; ++u) {
-        const int j = tid + u * kLossThreads;
-        if (4 * j < cells) {
-          float4 g4 = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (nbin > 0) g4 = *reinterpret_cast<const float4*>(s_band + 4 * j);
-          const pk2 d01 = cell2<false>(x[u].x, x[u].y, g4.x, g4.y, al, gscale, tot, tot_pos);
-          const pk2 d23 = cell2<false>(x[u].z, x[u].w, g4.z, g4.w, al, gscale, tot, tot_pos);
-          if (dp != nullptr) {
-            float4 d;
-            unpack2(d01, d.x, d.y); unpack2(d23, d.z, d.w);
-            stg_stream4(dp + 4 * j, d);
+        for (int u = 0; u < kFusedQ; ++u) {
+          const int j = tid + u * kLossThreads;
+          if (4 * j < cells) {
+            const float4 g4 = *reinterpret_cast<const float4*>(s_band + 4 * j);
+            const pk2 d01 = cell2<false>(x[u].x, x[u].y, g4.x, g4.y, al, gscale, tot, tot_pos);
+            const pk2 d23 = cell2<false>(x[u].z, x[u].w, g4.z, g4.w, al, gscale, tot, tot_pos);
+            if (dp != nullptr) {
+              float4 d;
+              unpack2(d01, d.x, d.y); unpack2(d23, d.z, d.w);
+              stg_stream4(dp + 4 * j, d);
+            }
+          }
+        }
+      } else {                                         // no Gaussian touches the band: gt == 0
+#pragma unroll
+        for (int u = 0; u < kFusedQ; ++u) {
+          const int j = tid + u * kLossThreads;
+          if (4 * j < cells) {
+            const pk2 d01 = cell2<false, true>(x[u].x, x[u].y, 0.f, 0.f, al, gscale, tot, tot_pos);
+            const pk2 d23 = cell2<false, true>(x[u].z, x[u].w, 0.f, 0.f, al, gscale, tot, tot_pos);
+            if (dp != nullptr) {
+              float4 d;
+              unpack2(d01, d.x, d.y); unpack2(d23, d.z, d.w);
+              stg_stream4(dp + 4 * j, d);
+            }
           }
         }
       }
@@ -478,6 +520,7 @@ target_loss_fused_kernel(const int4* __restrict__ obj_geo, const double* __restr
 #pragma unroll
       for (int u = 0; u < kFusedQ; ++u) x[u] = xn[u];
       cnt = cnt_next;
+      cur = nxt;
     }
   }
   loss_tail(acc0, acc1, is_reg, s_norm[1], w_wh, w_off, losses, ws, s_red, &s_last);
@@ -609,7 +652,8 @@ extern "C" int ctdet_target_loss_fused(const float* boxes, const int64_t* classe
   const int n_reg = 2 * B;
   target_loss_fused_kernel<<<(unsigned)(n_reg + sweep), kLossThreads, 0, st>>>(
       obj_geo, obj_ninv, cls_count, hm, wh, reg, reg_mask, ind, gt_wh, gt_reg, alpha, num_pos,
-      norm_override, B, C, H, W, CTDET_MAX_OBJS, band_rows, bands, flags, n_reg, w_hm, w_wh, w_off,
+      norm_override, B, C, H, W, CTDET_MAX_OBJS, band_rows, bands, FastDiv((uint32_t)bands), FastDiv((uint32_t)C),
+      flags, n_reg, w_hm, w_wh, w_off,
       losses, d_hm, d_wh, d_reg, reinterpret_cast<LossWs*>(workspace));
   return check_launch();
 }

@@ -180,9 +180,14 @@ target_slots_kernel(const float* __restrict__ boxes, const int64_t* __restrict__
   }
   __syncthreads();
   const uint32_t key = s_key[k];
-  bool first = key != 0xffffffffu;
-  for (int j = 0; j < k && first; ++j) first = s_key[j] != key;
-  if (first) atomicAdd(&s_npos, 1);
+  // distinct (class, centre) cells: an object counts when no earlier slot has its key.  No early exit:
+  // the broadcast LDS pipeline instead of forming a dependent chain of up to 127 compares.
+  bool dup = false;
+#pragma unroll 8
+  for (int j = 0; j < CTDET_MAX_OBJS; ++j) dup |= (j < k) & (s_key[j] == key);
+  const bool first = key != 0xffffffffu && !dup;
+  const unsigned bal = __ballot_sync(0xffffffffu, first);
+  if ((k & 31) == 0 && bal) atomicAdd(&s_npos, __popc(bal));
   __syncthreads();
   if (k == 0 && num_pos != nullptr) num_pos[b] = s_npos;
 }

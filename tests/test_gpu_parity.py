@@ -395,13 +395,16 @@ def test_full_size_properties():
     o2 = L.ctdet_losses({"hm": logits, "wh": wh, "reg": reg}, gt, alpha=[1.0], weights=(2.0, 0.2, 2.0))
     for k in o1:
         np.testing.assert_allclose(2 * o1[k].item(), o2[k].item(), rtol=1e-6)
-    d = torch.randn_like(logits)
+    # direction = sign of the gradient: the directional derivative is sum|grad| (large), so the fp32
+    # rounding of the two loss values (~2.4e-4 each) stays far below the tolerance and the check is
+    # deterministic (a random direction gives a derivative of the size of that noise)
+    d = torch.sign(x.grad)
     eps = 1e-2
     lp = L.ctdet_losses({"hm": logits + eps * d, "wh": wh, "reg": reg}, gt, alpha=[1.0])["hm_loss"].item()
     lm = L.ctdet_losses({"hm": logits - eps * d, "wh": wh, "reg": reg}, gt, alpha=[1.0])["hm_loss"].item()
     fd = (lp - lm) / (2 * eps)
     an = float((x.grad.double() * d.double()).sum())
-    np.testing.assert_allclose(an, fd, rtol=2e-2)   # fp32 loss values ~3e3: FD noise ~1e-2
+    np.testing.assert_allclose(an, fd, rtol=5e-3)   # central difference: truncation ~eps^2
     # decode: scores sorted, every winner is a 3x3 peak, nothing outside the winners beats the K-th
     heat = torch.clamp(torch.sigmoid(logits), 1e-4, 1 - 1e-4)
     boxes, scores, classes, inds = D.ctdet_decode_batch(heat, wh, reg, down_ratio=4, K=K)
