@@ -52,7 +52,7 @@ __device__ __forceinline__ float ordered_to_float(uint32_t o) {
 // Division of a uint32 < 2^31 by a runtime constant: one multiply-high and a shift.
 struct FastDiv {
   uint32_t mul, shr, d;
-  FastDiv() : mul(0), shr(0), d(1) {}
+  __host__ __device__ FastDiv() : mul(0), shr(0), d(1) {}
   explicit FastDiv(uint32_t div) : mul(0), shr(0), d(div) {
     if (div > 1) {
       uint32_t lg = 0;
