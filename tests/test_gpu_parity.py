@@ -174,6 +174,60 @@ def test_fused_targets_and_losses_from_objects(case, tag, golden, inputs):
     assert int(slots["num_pos"].sum().item()) == int((gt_np["hm"] == 1).sum())
 
 
+@pytest.mark.parametrize("shape", [(2, 3, 40, 36), (1, 5, 129, 132), (3, 2, 8, 4), (2, 4, 33, 256)])
+def test_fused_from_objects_edge_shapes(shape):
+    """ctdet_target_loss_fused on ragged / awkward inputs: maps that are not a multiple of the band
+    height, a partial last band, several bands per plane, images without objects, objects stacked
+    on one centre, boxes hanging over the border, saturated logits (clamp active -> zero gradient).
+    Checked against the oracle chain gen_heatmap -> CenterNet.losses on the same inputs."""
+    from detectron2_centernet_b200 import losses as L
+    B, C, H, W = shape
+    rng = np.random.default_rng(H * 1000 + W)
+    size_y, size_x = 4 * H, 4 * W
+    bl, cl = [], []
+    for b in range(B):
+        n = 0 if b == B - 1 and B > 1 else int(rng.integers(1, 12))
+        # centres inside the map (the reference's gather raises otherwise), boxes may hang over the border
+        cx = rng.uniform(0.5, size_x - 0.5, n); cy = rng.uniform(0.5, size_y - 0.5, n)
+        bw = rng.uniform(2, size_x / 2, n); bh = rng.uniform(2, size_y / 2, n)
+        boxes = np.stack([cx - bw / 2, cy - bh / 2, cx + bw / 2, cy + bh / 2], 1).astype(np.float32)
+        classes = rng.integers(0, C, n).astype(np.int64)
+        if n >= 3:                                   # two objects of one class on the same centre, different sizes
+            boxes[1] = boxes[0] + np.array([-6, -4, 6, 4], np.float32)
+            classes[1] = classes[0]
+        bl.append(boxes); cl.append(classes)
+    hm = rng.normal(-2.19, 1.5, (B, C, H, W)).astype(np.float32)
+    hm.reshape(-1)[:: max(1, hm.size // 37)] = 14.0     # clamp active at 1-1e-4
+    hm.reshape(-1)[1:: max(1, hm.size // 31)] = -15.0   # clamp active at 1e-4
+    wh = rng.uniform(0, 64, (B, 2, H, W)).astype(np.float32)
+    reg = rng.uniform(0, 1, (B, 2, H, W)).astype(np.float32)
+    alpha = [0.3 + 0.05 * c for c in range(C)]
+    boxes, classes, offsets = S.pack_objects(bl, cl)
+    t_b, t_c, t_o = _cuda(boxes, classes, offsets)
+    t_hm, t_wh, t_reg = [t.requires_grad_(True) for t in _cuda(hm, wh, reg)]
+    out, slots = L.ctdet_losses_from_objects({"hm": t_hm, "wh": t_wh, "reg": t_reg}, t_b, t_c, t_o, alpha=alpha)
+    (out["hm_loss"] + out["wh_loss"] + out["off_loss"]).backward()
+    torch.cuda.synchronize()
+    gt_np = O.gen_heatmap_batch(bl, cl, H, W, C)
+    lo, gr = O.losses_and_grads(torch.from_numpy(hm), torch.from_numpy(wh), torch.from_numpy(reg), gt_np, alpha=alpha)
+    got = np.array([out[k].item() for k in ("hm_loss", "wh_loss", "off_loss")])
+    np.testing.assert_allclose(got, [float(lo[k]) for k in ("hm_loss", "wh_loss", "off_loss")], rtol=1e-5)
+    _check_grads(t_hm.grad, gr[0], "d_hm")
+    _check_grads(t_wh.grad, gr[1], "d_wh")
+    _check_grads(t_reg.grad, gr[2], "d_reg")
+    sat = (hm == 14.0) | (hm == -15.0)
+    assert float(np.abs(t_hm.grad.cpu().numpy()[sat & (gt_np["hm"] < 1)]).max()) == 0.0     # torch.clamp passes no gradient
+    for k in ("reg_mask", "ind", "wh", "reg"):
+        assert np.array_equal(slots[k].cpu().numpy(), gt_np[k]), k
+    # and the two-pass form gives the same numbers (same device functions)
+    gt = _targets(bl, cl, H, W, C)
+    u_hm = torch.from_numpy(hm).to(DEV).requires_grad_(True)
+    out2 = L.ctdet_losses({"hm": u_hm, "wh": torch.from_numpy(wh).to(DEV), "reg": torch.from_numpy(reg).to(DEV)}, gt, alpha=alpha)
+    out2["hm_loss"].backward()
+    np.testing.assert_allclose(out["hm_loss"].item(), out2["hm_loss"].item(), rtol=1e-6)
+    np.testing.assert_allclose(t_hm.grad.cpu().numpy(), u_hm.grad.cpu().numpy(), rtol=1e-6, atol=0)
+
+
 def test_fused_losses_with_num_pos_from_target_gen(inputs):
     """num_pos produced by ctdet_target_gen feeds the loss: no counting pre-pass, same numbers."""
     from detectron2_centernet_b200 import losses as L
