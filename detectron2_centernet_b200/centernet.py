@@ -9,6 +9,7 @@ import torch
 from . import decode as D
 from . import dist as ctdist
 from . import losses as L
+from . import preprocess as P
 from . import target as T
 from .config import get_cfg
 from .structures import Boxes, Instances
@@ -27,6 +28,15 @@ class CenterNetHotPath:
         self.topk_candidates = int(c["TOPK_CANDIDATES_TEST"])
         self.max_detections_per_image = int(cfg["TEST"]["DETECTIONS_PER_IMAGE"])
         self.sync_num_pos = bool(sync_num_pos)
+        self.pixel_mean = list(cfg["MODEL"]["PIXEL_MEAN"])                      # :64-65
+        self.pixel_std = list(cfg["MODEL"]["PIXEL_STD"])
+        self.size_divisibility = int(c["SIZE_DIVISIBILITY"])                  # :72 / :111
+
+    # ---- input ---------------------------------------------------------------------------------
+    def preprocess_image(self, batched_inputs, device=None):
+        """:173-184: `x["image"] / 255`, normalise, pad and batch -> ImageList.  One launch for the batch."""
+        images = [x["image"] if device is None else x["image"].to(device, non_blocking=True) for x in batched_inputs]
+        return P.preprocess_image(images, self.pixel_mean, self.pixel_std, self.size_divisibility)
 
     # ---- training ------------------------------------------------------------------------------
     def targets(self, instances, input_shape):

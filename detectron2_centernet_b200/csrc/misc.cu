@@ -99,6 +99,55 @@ __global__ void postprocess_kernel(float* __restrict__ boxes, float* __restrict_
   }
 }
 
+// CenterNet.preprocess_image (meta_arch/centernet.py:177-184) + ImageList.from_tensors
+// (structures/image_list.py:58-130) for the whole batch in one pass: x / 255, (x - mean) / std per
+// channel in the reference's fp32 operation order (IEEE division, no FMA contraction), written into
+// the zero-padded batch tensor.  HBM-bound: 1 or 4 B read + 4 B written per pixel and channel; the
+// padding is written by the same launch (no separate fill).  One thread = 4 consecutive x of one
+// (image, channel) plane: grid = (plane chunks, C, B).
+template <typename T>
+__global__ void preprocess_kernel(const T* const* __restrict__ images, const int32_t* __restrict__ sizes_hw,
+                                  int C, int Hp, int Wp4, FastDiv div_wp4, const float* __restrict__ mean,
+                                  const float* __restrict__ stdv, float* __restrict__ out) {
+  const int c = blockIdx.y, b = blockIdx.z;
+  // uint8 input: a pixel can take 256 values, so the CTA (256 threads, one channel) tabulates the
+  // whole expression once with the IEEE operations and the per-pixel work is one shared-memory lookup
+  __shared__ float lut[256];
+  if (sizeof(T) == 1) {
+    lut[threadIdx.x] = __fdiv_rn(__fsub_rn(__fdiv_rn((float)threadIdx.x, 255.f), __ldg(mean + c)), __ldg(stdv + c));
+    __syncthreads();
+  }
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;                // float4 index inside the padded plane
+  if (idx >= Hp * Wp4) return;
+  const int y = (int)div_wp4.div((uint32_t)idx), x4 = idx - y * Wp4;
+  const int h = __ldg(sizes_hw + 2 * b), w = __ldg(sizes_hw + 2 * b + 1);
+  float v[4] = {0.f, 0.f, 0.f, 0.f};                         // pad_value of from_tensors
+  const int x = x4 * 4;
+  if (y < h && x < w) {
+    const T* src = images[b] + ((size_t)c * h + y) * w + x;
+    const float m = __ldg(mean + c), sd = __ldg(stdv + c);
+    float r[4] = {0.f, 0.f, 0.f, 0.f};
+    if (x + 4 <= w && (reinterpret_cast<uintptr_t>(src) & (4 * sizeof(T) - 1)) == 0) {        // one aligned 4-pixel load
+      if (sizeof(T) == 1) {
+        const uchar4 q = *reinterpret_cast<const uchar4*>(src);
+        v[0] = lut[q.x]; v[1] = lut[q.y]; v[2] = lut[q.z]; v[3] = lut[q.w];
+      } else {
+        const float4 q = *reinterpret_cast<const float4*>(src);
+        r[0] = q.x; r[1] = q.y; r[2] = q.z; r[3] = q.w;
+      }
+      if (sizeof(T) != 1) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) v[k] = __fdiv_rn(__fsub_rn(__fdiv_rn(r[k], 255.f), m), sd);
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (x + k < w) v[k] = sizeof(T) == 1 ? lut[(int)src[k]] : __fdiv_rn(__fsub_rn(__fdiv_rn((float)src[k], 255.f), m), sd);
+    }
+  }
+  *reinterpret_cast<float4*>(out + (((size_t)b * C + c) * Hp + y) * (size_t)(Wp4 * 4) + x) = make_float4(v[0], v[1], v[2], v[3]);
+}
+
 }  // namespace ctdet
 
 extern "C" int ctdet_abi_version(void) { return CTDET_ABI_VERSION; }
@@ -153,5 +202,27 @@ extern "C" int ctdet_postprocess(float* boxes, float* scores, int32_t* classes, 
   if (!boxes || !scores || !classes || !sizes || !n_keep) return CTDET_ENULL;
   postprocess_kernel<<<B, 128, (size_t)K * 4 * sizeof(float), (cudaStream_t)stream>>>(
       boxes, scores, classes, sizes, K, max_dets, score_thresh, n_keep);
+  return check_launch();
+}
+
+extern "C" int ctdet_preprocess(const void* const* images, const int32_t* sizes_hw, int dtype,
+                                int B, int C, int Hp, int Wp, const float* mean, const float* stdv,
+                                float* out, ctdet_stream_t stream) {
+  using namespace ctdet;
+  if (B < 0 || C <= 0 || Hp <= 0 || Wp <= 0 || (dtype != CTDET_IMAGE_U8 && dtype != CTDET_IMAGE_F32)) return CTDET_EINVAL;
+  if (B == 0) return CTDET_OK;
+  if (!images || !sizes_hw || !mean || !stdv || !out) return CTDET_ENULL;
+  if (Wp % 4 != 0) return CTDET_EUNSUPPORTED;              // size_divisibility is 16 / 32 in every config
+  if (!aligned16(out)) return CTDET_EALIGN;
+  if (B > 65535 || C > 65535 || (long long)Hp * (Wp / 4) >= (1ll << 31)) return CTDET_EINVAL;
+  const int Wp4 = Wp / 4;
+  const dim3 grid((unsigned)((Hp * Wp4 + 255) / 256), (unsigned)C, (unsigned)B);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == CTDET_IMAGE_U8)
+    preprocess_kernel<uint8_t><<<grid, 256, 0, st>>>(reinterpret_cast<const uint8_t* const*>(images), sizes_hw, C, Hp, Wp4,
+                                                    FastDiv((uint32_t)Wp4), mean, stdv, out);
+  else
+    preprocess_kernel<float><<<grid, 256, 0, st>>>(reinterpret_cast<const float* const*>(images), sizes_hw, C, Hp, Wp4,
+                                                  FastDiv((uint32_t)Wp4), mean, stdv, out);
   return check_launch();
 }

@@ -127,3 +127,26 @@ class Instances:
         return "Instances(num_instances={}, image_size={}, fields=[{}])".format(
             len(self) if self._fields else 0, self._image_size,
             ", ".join("{}: {}".format(k, v) for k, v in self._fields.items()))
+
+
+class ImageList:
+    """The slice of detectron2/structures/image_list.py:9 the ctdet path uses: the padded batch
+    tensor [N,C,H,W] plus the original (h, w) of every image."""
+
+    def __init__(self, tensor, image_sizes):
+        self.tensor = tensor
+        self.image_sizes = [tuple(int(v) for v in s) for s in image_sizes]
+
+    def __len__(self):
+        return len(self.image_sizes)
+
+    def __getitem__(self, idx):
+        h, w = self.image_sizes[idx]
+        return self.tensor[idx, ..., :h, :w]          # image_list.py:43-54
+
+    def to(self, *args, **kwargs):
+        return ImageList(self.tensor.to(*args, **kwargs), self.image_sizes)
+
+    @property
+    def device(self):
+        return self.tensor.device

@@ -20,6 +20,8 @@
  *   ctdet_nms / ctdet_gather_feat   centernet.py:399 _nms / :383 _transpose_and_gather_feat
  *   ctdet_postprocess    centernet.py:236-266 inference_single_image (slice + score threshold) and
  *                        detectron2/modeling/postprocessing.py:10-74 detector_postprocess (scale, clip, nonempty)
+ *   ctdet_preprocess     centernet.py:173-184 CenterNet.preprocess_image (x/255, normalise) and
+ *                        detectron2/structures/image_list.py:58-130 ImageList.from_tensors (pad + batch)
  *   dcnv2_forward        detectron2/layers/csrc/deformable/deform_conv.h:262 modulated_deform_conv_forward
  *                        -> deform_conv_cuda.cu:804 modulated_deform_conv_cuda_forward
  *                        (im2col kernel deform_conv_cuda_kernel.cu:786 + addmm_ :904 + bias :924)
@@ -163,6 +165,19 @@ int ctdet_gather_feat(const float* feat, const int64_t* ind, int B, int Ch, int 
 int ctdet_postprocess(float* boxes, float* scores, int32_t* classes, const int32_t* sizes,
                       int B, int K, int max_dets, float score_thresh, int32_t* n_keep,
                       ctdet_stream_t stream);
+
+/* CenterNet.preprocess_image (meta_arch/centernet.py:177-184) + ImageList.from_tensors
+ * (structures/image_list.py:58-130), batched: out[b,c,y,x] = ((img_b[c,y,x] / 255) - mean[c]) / std[c]
+ * inside image b, 0 (pad_value) outside; fp32, the reference's operation order.
+ *   images   DEVICE array of B device pointers, image b = [C,h_b,w_b]
+ *            contiguous, uint8 (CTDET_IMAGE_U8, what the dataset mapper yields) or f32 (CTDET_IMAGE_F32)
+ *   sizes_hw i32 [B,2] = {h_b, w_b}   mean, std f32 [C]   out f32 [B,C,Hp,Wp], Wp % 4 == 0
+ * Hp / Wp are the batch maxima rounded up to the backbone's size_divisibility (host side). */
+#define CTDET_IMAGE_U8 0
+#define CTDET_IMAGE_F32 1
+int ctdet_preprocess(const void* const* images, const int32_t* sizes_hw, int dtype,
+                     int B, int C, int Hp, int Wp, const float* mean, const float* std,
+                     float* out, ctdet_stream_t stream);
 
 /* ---------------------------------------------------------------- DCNv2 forward ----------
  * Modulated deformable 3x3 convolution, replaces modulated_deform_conv_forward

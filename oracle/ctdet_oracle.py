@@ -290,3 +290,26 @@ def decode_torch(heat, wh, reg=None, down_ratio=1, K=100):
     boxes = torch.stack([xs - w[..., 0] / 2, ys - w[..., 1] / 2,
                          xs + w[..., 0] / 2, ys + w[..., 1] / 2], dim=2) * down_ratio
     return boxes.numpy(), scores.numpy(), classes.numpy(), inds.numpy()
+
+
+# --------------------------------------------------------------------------------------
+# Input pre-processing
+def preprocess_image(images, pixel_mean, pixel_std, size_divisibility=0):
+    """CenterNet.preprocess_image, meta_arch/centernet.py:177-184: x / 255., (x - mean) / std, then
+    ImageList.from_tensors (structures/image_list.py:58-130): zero padding (pad_value 0.0) at the
+    bottom / right up to the batch maximum rounded up to size_divisibility.
+    images: list of torch CPU tensors [C,h,w] (uint8 or float32).  Returns (tensor f32 [N,C,Hp,Wp],
+    [(h, w), ...])."""
+    mean = torch.tensor(list(pixel_mean), dtype=torch.float32).view(-1, 1, 1)       # :64
+    std = torch.tensor(list(pixel_std), dtype=torch.float32).view(-1, 1, 1)         # :65
+    xs = [x / 255. for x in images]                                                   # :177
+    xs = [(x - mean) / std for x in xs]                                               # :183
+    sizes = [tuple(int(v) for v in x.shape[-2:]) for x in xs]                         # image_list.py:111
+    Hp, Wp = max(s[0] for s in sizes), max(s[1] for s in sizes)                       # :83-97
+    if size_divisibility > 1:                                                         # :99-102
+        Hp = (Hp + size_divisibility - 1) // size_divisibility * size_divisibility
+        Wp = (Wp + size_divisibility - 1) // size_divisibility * size_divisibility
+    out = xs[0].new_full((len(xs), xs[0].shape[0], Hp, Wp), 0.0)                      # :124-125
+    for x, dst in zip(xs, out):
+        dst[..., :x.shape[-2], :x.shape[-1]].copy_(x)                                 # :126-127
+    return out, sizes

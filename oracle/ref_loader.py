@@ -76,6 +76,29 @@ def load():
     return _CACHE
 
 
+def load_image_list():
+    """The reference's own ImageList class (detectron2/structures/image_list.py imports nothing but
+    torch, so the whole file is exec'd unmodified)."""
+    if "ImageList" not in _CACHE:
+        path = os.path.join(REF_ROOT, "detectron2/structures/image_list.py")
+        ns = {"__name__": "ctdet_reference_image_list"}
+        with open(path, "r") as f:
+            exec(compile(f.read(), path, "exec"), ns)
+        _CACHE["ImageList"] = ns["ImageList"]
+    return _CACHE["ImageList"]
+
+
+def reference_preprocess(images, pixel_mean, pixel_std, size_divisibility):
+    """preprocess_image of the reference, centernet.py:177-184, with its own ImageList."""
+    ImageList = load_image_list()
+    mean = torch.Tensor(list(pixel_mean)).view(-1, 1, 1)                 # :64
+    std = torch.Tensor(list(pixel_std)).view(-1, 1, 1)                   # :65
+    xs = [x / 255. for x in images]                                      # :177
+    xs = [(x - mean) / std for x in xs]                                  # :183
+    il = ImageList.from_tensors(xs, size_divisibility)                   # :184
+    return il.tensor, [tuple(int(v) for v in s) for s in il.image_sizes]
+
+
 @contextlib.contextmanager
 def cpu_cuda_shim():
     """`_neg_loss` does `torch.tensor(alpha).cuda()`; make that a no-op on CPU-only hosts."""
