@@ -289,7 +289,7 @@ __device__ __forceinline__ void loss_tail(double acc0, double acc1, bool is_reg,
   }
 }
 
-template <bool kProb>
+template <bool kProb, bool kV8>
 __global__ void __launch_bounds__(kLossThreads, CTDET_LOSS_MINB)
 loss_kernel(const float* __restrict__ hm, const float* __restrict__ wh, const float* __restrict__ reg,
             const float* __restrict__ gt, const uint8_t* __restrict__ reg_mask,
@@ -321,24 +321,32 @@ loss_kernel(const float* __restrict__ hm, const float* __restrict__ wh, const fl
     const bool uniform_alpha = flags & CTDET_LOSS_ALPHA_UNIFORM;
     const float alpha0 = __ldg(alpha);
     // software pipeline: the loads of iteration k+1 are in flight while iteration k computes
-    float4 x[kUnroll], g[kUnroll], xn[kUnroll], gn[kUnroll];
+    // kV8 (HW % 8 == 0, 32-byte aligned tensors): a thread's two float4 chunks are adjacent and move
+    // as ONE 256-bit load / store per tensor; otherwise they lie `stride` apart (128-bit accesses)
+    static_assert(!kV8 || kUnroll == 2, "the 256-bit path pairs two float4 chunks");
+    auto chunk = [&](size_t base, int u) { return kV8 ? 2 * base + u : base + u * stride; };
+    auto load = [&](size_t base, float4* xs, float4* gs) {
+      if (kV8) {
+        if (2 * base < n4) { ldg_stream8(hm + 8 * base, xs[0], xs[1]); ldg_stream8(gt + 8 * base, gs[0], gs[1]); }
+      } else {
 #pragma unroll
-    for (int u = 0; u < kUnroll; ++u) {
-      const size_t j = i + u * stride;
-      if (j < n4) { x[u] = ldg_stream4(hm + 4 * j); g[u] = ldg_stream4(gt + 4 * j); }
-    }
-    for (; i < n4; i += stride * kUnroll) {
-      const size_t inext = i + stride * kUnroll;
-#pragma unroll
-      for (int u = 0; u < kUnroll; ++u) {
-        const size_t j = inext + u * stride;
-        if (j < n4) { xn[u] = ldg_stream4(hm + 4 * j); gn[u] = ldg_stream4(gt + 4 * j); }
+        for (int u = 0; u < kUnroll; ++u) {
+          const size_t j = base + u * stride;
+          if (j < n4) { xs[u] = ldg_stream4(hm + 4 * j); gs[u] = ldg_stream4(gt + 4 * j); }
+        }
       }
+    };
+    float4 x[kUnroll], g[kUnroll], xn[kUnroll], gn[kUnroll], dd[kUnroll];
+    const size_t step = kV8 ? stride : stride * kUnroll;     // advance of `i` per iteration
+    const size_t n_it = kV8 ? n4 / 2 : n4;                   // range of `i`
+    load(i, x, g);
+    for (; i < n_it; i += step) {
+      load(i + step, xn, gn);
       pk2 tot = bcast2(0.f);
       float tot_pos = 0.f;
 #pragma unroll
       for (int u = 0; u < kUnroll; ++u) {
-        const size_t j = i + u * stride;
+        const size_t j = chunk(i, u);
         if (j < n4) {
           float al = alpha0;
           if (!uniform_alpha) {
@@ -347,13 +355,11 @@ loss_kernel(const float* __restrict__ hm, const float* __restrict__ wh, const fl
           }
           const pk2 d01 = cell2<kProb>(x[u].x, x[u].y, g[u].x, g[u].y, al, gscale, tot, tot_pos);
           const pk2 d23 = cell2<kProb>(x[u].z, x[u].w, g[u].z, g[u].w, al, gscale, tot, tot_pos);
-          if (d_hm != nullptr) {
-            float4 d;
-            unpack2(d01, d.x, d.y); unpack2(d23, d.z, d.w);
-            stg_stream4(d_hm + 4 * j, d);
-          }
+          unpack2(d01, dd[u].x, dd[u].y); unpack2(d23, dd[u].z, dd[u].w);
+          if (!kV8 && d_hm != nullptr) stg_stream4(d_hm + 4 * j, dd[u]);
         }
       }
+      if (kV8 && d_hm != nullptr) stg_stream8(d_hm + 8 * i, dd[0], dd[1]);
       float t0, t1;
       unpack2(tot, t0, t1);
       acc0 += (double)(t0 + t1) + (double)tot_pos;   // already scaled by gscale = -w_hm/num_pos
@@ -586,7 +592,7 @@ extern "C" int ctdet_loss_fwd_bwd(const float* hm, const float* wh, const float*
   static int occ = 0;
   if (occ == 0) {
     int o = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, loss_kernel<false>, kLossThreads, 0) != cudaSuccess || o < 1) o = 3;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, loss_kernel<false, true>, kLossThreads, 0) != cudaSuccess || o < 1) o = 3;
     occ = o;
   }
   size_t want = (n4 + (size_t)kLossThreads * kUnroll - 1) / ((size_t)kLossThreads * kUnroll);
@@ -594,7 +600,13 @@ extern "C" int ctdet_loss_fwd_bwd(const float* hm, const float* wh, const float*
   int sweep = (int)(want < cap ? want : cap);
   const int n_reg = (wh || reg) ? 2 * B : 0;
   if (n_reg + sweep < 1) return CTDET_EINVAL;
-  auto kern = (flags & CTDET_LOSS_INPUT_PROB) ? loss_kernel<true> : loss_kernel<false>;
+  static int use_v8 = -1;                       // CTDET_LOSS_V8=0 forces the 128-bit accesses
+  if (use_v8 < 0) { const char* e = getenv("CTDET_LOSS_V8"); use_v8 = e ? atoi(e) : 1; }
+  const bool v8 = use_v8 && hm && (HW % 8 == 0) && ((reinterpret_cast<uintptr_t>(hm) | reinterpret_cast<uintptr_t>(gt_hm) |
+                                                       reinterpret_cast<uintptr_t>(d_hm)) & 31u) == 0;
+  const bool prob = flags & CTDET_LOSS_INPUT_PROB;
+  auto kern = prob ? (v8 ? loss_kernel<true, true> : loss_kernel<true, false>)
+                   : (v8 ? loss_kernel<false, true> : loss_kernel<false, false>);
   kern<<<n_reg + sweep, kLossThreads, 0, st>>>(
       hm, wh, reg, gt_hm, reg_mask, ind, gt_wh, gt_reg, alpha, num_pos_img, norm_override,
       B, C, (int)HW, M, flags, n_reg, FastDiv((uint32_t)(HW / 4)), FastDiv((uint32_t)C), w_hm, w_wh, w_off,
