@@ -12,6 +12,7 @@ from .losses import FocalLoss, RegL1Loss, _neg_loss, ctdet_losses, ctdet_losses_
 from .decode import (ctdet_decode, ctdet_decode_batch, _nms, _topk, _transpose_and_gather_feat,   # noqa: F401
                      postprocess_batch)
 from .deform_conv import DCN, DeformConvV2, ModulatedDeformConv, modulated_deform_conv, dcnv2_forward, dcnv2_backward   # noqa: F401
+from .neck import CtdetHead, DLA34Neck, DLAUp, IDAUp, fill_up_weights                 # noqa: F401
 from .structures import Boxes, ImageList, Instances                                    # noqa: F401
 from .preprocess import preprocess_image                                               # noqa: F401
 from .centernet import CenterNetHotPath                                                # noqa: F401

@@ -1,0 +1,127 @@
+"""The callers around the DCNv2 contraction: the DLA-34 up-sampling neck and the ctdet heads, as a
+host-side mirror of detectron2/modeling/backbone/dla.py (`fill_up_weights` :33, `IDAUp` :152,
+`DLAUp` :180, the neck half of `DLA34` :287-315) and of the head construction in
+detectron2/modeling/meta_arch/centernet.py:112-134.  Sub-module and parameter names are the reference's
+(`proj_i` / `up_i` / `node_i`, `ida_i`, `dla_up`, `ida_up`, `hm` / `wh` / `reg`), so a reference
+state_dict loads unchanged; every `DeformConvV2` is the B200 one (tcgen05 kernels, BN + ReLU folded
+into the epilogue in eval mode).  The DLA base network (plain cuDNN convolutions) is not part of the
+hot path and stays whatever torch module the caller has: this neck takes its six feature maps.
+"""
+import math
+
+import torch
+from torch import nn
+
+from .deform_conv import DeformConvV2
+
+
+def fill_up_weights(up):
+    """dla.py:33-42: the fixed bilinear kernel of the depth-wise transposed convolution."""
+    w = up.weight.data
+    k = w.size(2)
+    f = math.ceil(k / 2)
+    c = (2 * f - 1 - f % 2) / (2.0 * f)
+    for i in range(k):
+        for j in range(w.size(3)):
+            w[0, 0, i, j] = (1 - math.fabs(i / f - c)) * (1 - math.fabs(j / f - c))
+    w[1:, 0] = w[0, 0]
+
+
+class IDAUp(nn.Module):
+    """dla.py:152-177.  For every level after the first: project to `o` channels (DCN), up-sample by
+    `up_f[i]` (depth-wise ConvTranspose2d with the bilinear kernel), add the previous level, and mix
+    (`node`, another DCN).  `dcn` lets tests swap in another DeformConvV2 implementation."""
+
+    def __init__(self, o, channels, up_f, dcn=DeformConvV2):
+        super().__init__()
+        for i in range(1, len(channels)):
+            f = int(up_f[i])
+            setattr(self, "proj_%d" % i, dcn(channels[i], o))
+            up = nn.ConvTranspose2d(o, o, f * 2, stride=f, padding=f // 2, output_padding=0, groups=o, bias=False)
+            fill_up_weights(up)
+            setattr(self, "up_%d" % i, up)
+            setattr(self, "node_%d" % i, dcn(o, o))
+
+    def forward(self, layers, startp, endp):
+        for i in range(startp + 1, endp):
+            k = i - startp
+            x = getattr(self, "up_%d" % k)(getattr(self, "proj_%d" % k)(layers[i]))
+            layers[i] = getattr(self, "node_%d" % k)(x + layers[i - 1])
+
+
+class DLAUp(nn.Module):
+    """dla.py:180-203: one IDAUp per resolution, deepest first; returns the fused maps, finest first."""
+
+    def __init__(self, startp, channels, scales, in_channels=None, dcn=DeformConvV2):
+        super().__init__()
+        self.startp = startp
+        channels = list(channels)
+        in_channels = list(channels if in_channels is None else in_channels)
+        self.channels = channels
+        scales = [int(s) for s in scales]
+        for i in range(len(channels) - 1):
+            j = -i - 2
+            setattr(self, "ida_%d" % i, IDAUp(channels[j], in_channels[j:], [s // scales[j] for s in scales[j:]], dcn=dcn))
+            scales[j + 1:] = [scales[j]] * len(scales[j + 1:])
+            in_channels[j + 1:] = [channels[j]] * len(in_channels[j + 1:])
+
+    def forward(self, layers):
+        layers = list(layers)
+        out = [layers[-1]]
+        for i in range(len(layers) - self.startp - 1):
+            getattr(self, "ida_%d" % i)(layers, len(layers) - i - 2, len(layers))
+            out.insert(0, layers[-1])
+        return out
+
+
+class DLA34Neck(nn.Module):
+    """The `dla_up` + `ida_up` half of DLA34 (dla.py:287-315) over the base network's feature maps
+    (channels 16, 32, 64, 128, 256, 512 at strides 1 .. 32): 16 DeformConvV2 layers, output = the
+    stride-`down_ratio` map with `channels[first_level]` channels (last element of the returned list)."""
+
+    def __init__(self, channels=(16, 32, 64, 128, 256, 512), down_ratio=4, last_level=5, dcn=DeformConvV2):
+        super().__init__()
+        assert down_ratio in (2, 4, 8, 16)
+        self.channels = list(channels)
+        self.first_level = int(math.log2(down_ratio))
+        self.last_level = last_level
+        up_channels = self.channels[self.first_level:]
+        self.dla_up = DLAUp(self.first_level, up_channels, [2 ** i for i in range(len(up_channels))], dcn=dcn)
+        self.ida_up = IDAUp(self.channels[self.first_level], self.channels[self.first_level:self.last_level],
+                            [2 ** i for i in range(self.last_level - self.first_level)], dcn=dcn)
+
+    def forward(self, base_features):
+        x = self.dla_up(base_features)
+        y = [x[i].clone() for i in range(self.last_level - self.first_level)]
+        self.ida_up(y, 0, len(y))
+        return y
+
+
+class CtdetHead(nn.Module):
+    """centernet.py:112-134: per head `Conv3x3(in, head_conv) + ReLU + Conv(final_kernel)(head_conv, n)`;
+    the `hm` bias starts at -2.19 (:122-123), the other heads' biases at 0 (`fill_fc_weights`).
+    Returns {'hm', 'wh', 'reg'} (names pinned by export/meta_modeling.py:200)."""
+
+    def __init__(self, in_channels=64, num_classes=80, head_conv=256, final_kernel=1, heads=None):
+        super().__init__()
+        self.heads = dict(heads) if heads is not None else {"hm": num_classes, "wh": 2, "reg": 2}
+        for name, n in self.heads.items():
+            if head_conv > 0:
+                fc = nn.Sequential(nn.Conv2d(in_channels, head_conv, kernel_size=3, padding=1, bias=True),
+                                   nn.ReLU(inplace=True),
+                                   nn.Conv2d(head_conv, n, kernel_size=final_kernel, stride=1,
+                                             padding=final_kernel // 2, bias=True))
+                last = fc[-1]
+            else:
+                fc = nn.Conv2d(in_channels, n, kernel_size=final_kernel, stride=1, padding=final_kernel // 2, bias=True)
+                last = fc
+            if "hm" in name.lower():
+                last.bias.data.fill_(-2.19)
+            else:
+                for m in fc.modules():
+                    if isinstance(m, nn.Conv2d) and m.bias is not None:
+                        nn.init.constant_(m.bias, 0)
+            setattr(self, name.lower(), fc)
+
+    def forward(self, x):
+        return {name: getattr(self, name.lower())(x) for name in self.heads}
