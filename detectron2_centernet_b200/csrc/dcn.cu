@@ -36,48 +36,67 @@ namespace ctdet {
 // axis (C % 64 == 0 on this path).  Optionally accumulates per-channel sums over (batch, pixels).
 __global__ void __launch_bounds__(256)
 dcn_pack_input_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ xh, int C, int P, int vec,
-                      float* __restrict__ chan_sum) {
+                      float* __restrict__ chan_sum, int chunks, int border_w) {
   __shared__ __nv_bfloat16 t[64][64 + 8];                 // [pixel][channel], padded rows (144 B)
-  const int b = blockIdx.z, c0 = blockIdx.y * 64, p0 = blockIdx.x * 64;
+  const int b = blockIdx.z, c0 = blockIdx.y * 64;
   const float* src = x + (size_t)b * C * P;
-  __nv_bfloat16* dst = xh + (size_t)b * P * C;
+  // border_w = W > 0: the image is written inside a one-pixel border (rows of W + 2 pixels, pixel (y, x) at
+  // (y + 1, x + 1)); the border itself is zeroed by the caller
+  const size_t img_pixels = border_w ? (size_t)(P / border_w + 2) * (border_w + 2) : (size_t)P;
+  __nv_bfloat16* dst = xh + (size_t)b * img_pixels * C;
   const int tid = threadIdx.x;
+  // with channel sums a CTA walks `chunks` 64-pixel blocks and keeps the sums in registers: one
+  // atomic per channel per CTA instead of one per 64 pixels (8192 same-address atomics per channel
+  // on a 64-channel 128^2 x 32 tensor cost 4x the pack itself)
+  float csum[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int it = 0; it < chunks; ++it) {
+    const int p0 = (blockIdx.x * chunks + it) * 64;
+    if (p0 >= P) break;
+    if (it) __syncthreads();                              // the previous block's stores are done with t
 #pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    const int idx = tid + k * 256;                        // 64 channels x 16 float4
-    const int c = idx >> 4, q = idx & 15;
-    const int p = p0 + q * 4;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (c0 + c < C && p < P) {
-      const float* sp = src + (size_t)(c0 + c) * P + p;
-      if (vec) {
-        v = ldg_stream4(sp);
-      } else {                                            // P % 4 != 0 or unaligned base: scalar loads
-        v.x = __ldg(sp);
-        if (p + 1 < P) v.y = __ldg(sp + 1);
-        if (p + 2 < P) v.z = __ldg(sp + 2);
-        if (p + 3 < P) v.w = __ldg(sp + 3);
+    for (int k = 0; k < 4; ++k) {
+      const int idx = tid + k * 256;                      // 64 channels x 16 float4
+      const int c = idx >> 4, q = idx & 15;
+      const int p = p0 + q * 4;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (c0 + c < C && p < P) {
+        const float* sp = src + (size_t)(c0 + c) * P + p;
+        if (vec) {
+          v = ldg_stream4(sp);
+        } else {                                          // P % 4 != 0 or unaligned base: scalar loads
+          v.x = __ldg(sp);
+          if (p + 1 < P) v.y = __ldg(sp + 1);
+          if (p + 2 < P) v.z = __ldg(sp + 2);
+          if (p + 3 < P) v.w = __ldg(sp + 3);
+        }
+      }
+      csum[k] += (v.x + v.y) + (v.z + v.w);
+      t[q * 4 + 0][c] = __float2bfloat16_rn(v.x);
+      t[q * 4 + 1][c] = __float2bfloat16_rn(v.y);
+      t[q * 4 + 2][c] = __float2bfloat16_rn(v.z);
+      t[q * 4 + 3][c] = __float2bfloat16_rn(v.w);
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const int idx = tid + k * 256;                      // 64 pixels x 8 chunks of 8 channels
+      const int pp = idx >> 3, ch = idx & 7;
+      if (p0 + pp < P && c0 + ch * 8 < C) {
+        int q = p0 + pp;
+        if (border_w) { const int y = q / border_w; q += (y + 1) * 2 + border_w + 1; }   // (y+1)*(W+2) + x+1
+        *reinterpret_cast<uint4*>(dst + (size_t)q * C + c0 + ch * 8) = *reinterpret_cast<const uint4*>(&t[pp][ch * 8]);
       }
     }
-    if (chan_sum) {                                       // per-channel sums (grad_bias of the backward):
-      float sum = (v.x + v.y) + (v.z + v.w);              // 16 consecutive lanes share one channel
+  }
+  if (chan_sum) {                                         // per-channel sums (grad_bias of the backward):
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {                         // 16 consecutive lanes share one channel
+      float sum = csum[k];
 #pragma unroll
       for (int o = 8; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-      if (q == 0 && c0 + c < C) atomicAdd(chan_sum + c0 + c, sum);
+      const int c = (tid + k * 256) >> 4;
+      if ((tid & 15) == 0 && c0 + c < C) atomicAdd(chan_sum + c0 + c, sum);
     }
-    t[q * 4 + 0][c] = __float2bfloat16_rn(v.x);
-    t[q * 4 + 1][c] = __float2bfloat16_rn(v.y);
-    t[q * 4 + 2][c] = __float2bfloat16_rn(v.z);
-    t[q * 4 + 3][c] = __float2bfloat16_rn(v.w);
-  }
-  __syncthreads();
-#pragma unroll
-  for (int k = 0; k < 2; ++k) {
-    const int idx = tid + k * 256;                        // 64 pixels x 8 chunks of 8 channels
-    const int pp = idx >> 3, ch = idx & 7;
-    if (p0 + pp < P && c0 + ch * 8 < C)
-      *reinterpret_cast<uint4*>(dst + (size_t)(p0 + pp) * C + c0 + ch * 8) =
-          *reinterpret_cast<const uint4*>(&t[pp][ch * 8]);
   }
 }
 
@@ -303,7 +322,7 @@ extern "C" int dcnv2_forward(const float* input, const float* weight, const floa
   const int Pin = H * W;
   if (B > 65535) return CTDET_EINVAL;
   const int vec = (Pin % 4 == 0 && aligned16(input)) ? 1 : 0;          // float4 loads of the NCHW input
-  dcn_pack_input_kernel<<<dim3((Pin + 63) / 64, (Cin + 63) / 64, B), 256, 0, st>>>(input, xh, Cin, Pin, vec, nullptr);
+  dcn_pack_input_kernel<<<dim3((Pin + 63) / 64, (Cin + 63) / 64, B), 256, 0, st>>>(input, xh, Cin, Pin, vec, nullptr, 1, 0);
   int rc = check_launch();
   if (rc) return rc;
   dcn_pack_weight_kernel<<<kNumSMs, 256, 0, st>>>(weight, wk, Cout, Cin);
@@ -315,6 +334,7 @@ extern "C" int dcnv2_forward(const float* input, const float* weight, const floa
   prm.scale = scale; prm.shift = shift; prm.y = output;
   prm.Cin = Cin; prm.H = H; prm.W = W; prm.Ho = Ho; prm.Wo = Wo; prm.Cout = Cout;
   prm.stride = stride_h; prm.pad = pad_h; prm.dil = dilation_h; prm.relu = (flags & DCN_FLAG_RELU) ? 1 : 0;
+  prm.xw = W; prm.ximg = Pin * Cin; prm.xorg = 0;
   prm.tiles_x = (Wo + kTileW - 1) / kTileW;
   prm.tiles_per_image = prm.tiles_x * ((Ho + kTileH - 1) / kTileH);
   const long long tiles = (long long)B * prm.tiles_per_image;

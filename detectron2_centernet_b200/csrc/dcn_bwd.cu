@@ -28,7 +28,7 @@ struct DcnBwdParams {
   const __nv_bfloat16* gh;     // grad_output NHWC bf16 [B][Ho*Wo][Cout]
   const __nv_bfloat16* wt;     // dgrad B tiles: per K block kb, Cout/64 slabs of [64 ci][64 co] (swizzled)
   float* gw;                   // grad_weight [Cout][Cin][3][3] fp32 (zeroed before the launch)
-  float* gx;                   // grad_input NHWC fp32 [B][H*W][Cin] (zeroed before the launch)
+  float* gx;                   // grad_input NHWC fp32 [B][(H+2)*(W+2)][Cin], bordered like xh (zeroed before the launch)
   float* goff;                 // grad_offset [B][18][Ho*Wo]
   float* gmask;                // grad_mask   [B][9][Ho*Wo]
   int n_groups, kb_per_group;  // wgrad: K blocks are split into groups that fit TMEM
@@ -206,12 +206,12 @@ __global__ void dcn_pack_weight_t_kernel(const float* __restrict__ w, __nv_bfloa
   }
 }
 
-// grad_input NHWC fp32 -> NCHW fp32 (64 x 64 blocks through shared memory)
+// grad_input bordered NHWC fp32 (pixel (y, x) at (y+1)*(W+2) + x+1) -> NCHW fp32, 64 x 64 blocks through shared memory
 __global__ void __launch_bounds__(256)
-dcn_unpack_grad_input_kernel(const float* __restrict__ gx, float* __restrict__ out, int C, int P) {
+dcn_unpack_grad_input_kernel(const float* __restrict__ gx, float* __restrict__ out, int C, int P, int W) {
   __shared__ float t[64][65];                             // [pixel][channel]
   const int b = blockIdx.z, c0 = blockIdx.y * 64, p0 = blockIdx.x * 64;
-  const float* src = gx + (size_t)b * P * C;
+  const float* src = gx + (size_t)b * (size_t)(P / W + 2) * (W + 2) * C;   // bordered rows of W + 2 pixels
   float* dst = out + (size_t)b * C * P;
   const int tid = threadIdx.x;
 #pragma unroll
@@ -219,7 +219,10 @@ dcn_unpack_grad_input_kernel(const float* __restrict__ gx, float* __restrict__ o
     const int idx = tid + k * 256;                        // 64 pixels x 16 float4 of channels
     const int pp = idx >> 4, q = idx & 15;
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (p0 + pp < P) v = *reinterpret_cast<const float4*>(src + (size_t)(p0 + pp) * C + c0 + q * 4);
+    if (p0 + pp < P) {
+      const int p = p0 + pp, y = p / W;
+      v = *reinterpret_cast<const float4*>(src + (size_t)(p + 2 * y + W + 3) * C + c0 + q * 4);
+    }
     t[pp][q * 4 + 0] = v.x; t[pp][q * 4 + 1] = v.y; t[pp][q * 4 + 2] = v.z; t[pp][q * 4 + 3] = v.w;
   }
   __syncthreads();
@@ -231,26 +234,23 @@ dcn_unpack_grad_input_kernel(const float* __restrict__ gx, float* __restrict__ o
   }
 }
 
-// Raw sampling geometry for the backward: {g, lh, lw, mask} with
-//   g = element offset of the clamped top-left corner (pixel * Cin, multiple of 64)
-//       | bit0: right corner is another pixel | bit1: bottom corner is another pixel
-//       | bit2: top row inside | bit3: bottom row inside | bit4: left column inside | bit5: right column inside
-// all zero when the tap falls outside (h_im <= -1 ... , dmcn_get_coordinate_weight :738-742).
+// Sampling geometry for dgrad: {e, lh, lw, mask}.  The backward's copies of x and of grad_input carry a
+// one-pixel zero border (rows of W + 2 pixels), so the four corners of any tap that the reference samples
+// (h_im in (-1, H), w_im in (-1, W), deform_conv_cuda_kernel.cu:852) are always addressable and the corners
+// outside the image read zeros / collect gradients nobody reads: no clamping, no validity flags.
+//   e = element offset of the top-left corner inside the bordered image ((h_low+1)*(W+2) + w_low+1) * Cin;
+// the other corners are at +Cin, +(W+2)*Cin, +(W+3)*Cin.  A tap that falls outside altogether has all four
+// fields zero (mask 0 -> no gradient, e = 0 -> border pixels).
 __device__ __forceinline__ uint4 tap_geometry_raw(const DcnParams& prm, float off_h, float off_w, float m,
                                                   int ho, int wo, bool valid, int t) {
   uint4 o = make_uint4(0u, 0u, 0u, 0u);
   if (valid) {
-    const int H = prm.H, W = prm.W;
     const int i = t / 3, j = t - 3 * i;
     const float h_im = (float)(ho * prm.stride - prm.pad + i * prm.dil) + off_h;
     const float w_im = (float)(wo * prm.stride - prm.pad + j * prm.dil) + off_w;
-    if (h_im > -1.f && w_im > -1.f && h_im < (float)H && w_im < (float)W) {
+    if (h_im > -1.f && w_im > -1.f && h_im < (float)prm.H && w_im < (float)prm.W) {
       const int h_low = (int)floorf(h_im), w_low = (int)floorf(w_im);
-      const int h_high = h_low + 1, w_high = w_low + 1;
-      const bool t_ok = h_low >= 0, b_ok = h_high <= H - 1, l_ok = w_low >= 0, r_ok = w_high <= W - 1;
-      const int hl = max(h_low, 0), hh_i = min(h_high, H - 1), wl = max(w_low, 0), wh_i = min(w_high, W - 1);
-      o.x = (uint32_t)(hl * W + wl) * (uint32_t)prm.Cin | (wh_i != wl ? 1u : 0u) | (hh_i != hl ? 2u : 0u) |
-            (t_ok ? 4u : 0u) | (b_ok ? 8u : 0u) | (l_ok ? 16u : 0u) | (r_ok ? 32u : 0u);
+      o.x = (uint32_t)((h_low + 1) * prm.xw + w_low + 1) * (uint32_t)prm.Cin;
       o.y = __float_as_uint(h_im - (float)h_low);
       o.z = __float_as_uint(w_im - (float)w_low);
       o.w = __float_as_uint(m);
@@ -264,11 +264,19 @@ __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, 
 }
 __device__ __forceinline__ float bf_lo(uint32_t u) { return __uint_as_float(u << 16); }
 __device__ __forceinline__ float bf_hi(uint32_t u) { return __uint_as_float(u & 0xffff0000u); }
-__device__ __forceinline__ float dot8(const float (&g)[8], uint4 v) {
-  float d = g[0] * bf_lo(v.x);
-  d = fmaf(g[1], bf_hi(v.x), d); d = fmaf(g[2], bf_lo(v.y), d); d = fmaf(g[3], bf_hi(v.y), d);
-  d = fmaf(g[4], bf_lo(v.z), d); d = fmaf(g[5], bf_hi(v.z), d); d = fmaf(g[6], bf_lo(v.w), d);
-  return fmaf(g[7], bf_hi(v.w), d);
+// packed fp32 pairs (fma.rn.f32x2): the consumers are issue-bound, one instruction per two channels
+typedef unsigned long long pk2;
+__device__ __forceinline__ pk2 pk(float lo, float hi) { pk2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void upk(pk2 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ pk2 mul2(pk2 a, pk2 b) { pk2 r; asm("mul.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ pk2 fma2(pk2 a, pk2 b, pk2 c) { pk2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+__device__ __forceinline__ pk2 bf2(uint32_t u) { return pk(bf_lo(u), bf_hi(u)); }      // a bf16 pair as two fp32
+__device__ __forceinline__ float dot8(const pk2 (&g)[4], uint4 v) {
+  pk2 a = mul2(g[0], bf2(v.x));
+  a = fma2(g[1], bf2(v.y), a); a = fma2(g[2], bf2(v.z), a); a = fma2(g[3], bf2(v.w), a);
+  float lo, hi;
+  upk(a, lo, hi);
+  return lo + hi;
 }
 
 // dgrad lane layout: lane `chunk` (0..7) of a pixel owns channels [4c, 4c+4) and [32+4c, 32+4c+4) of the
@@ -311,7 +319,7 @@ dcn_dgrad_kernel(const DcnParams prm, const DcnBwdParams bw) {
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int Cin = prm.Cin, Cout = prm.Cout;
-  const int P = prm.Ho * prm.Wo, Pin = prm.H * prm.W;
+  const int P = prm.Ho * prm.Wo;
   const int NG = bw.g_stages, NW = bw.w_stages, GB = bw.gout_bufs;
   const uint32_t gout_bytes = (uint32_t)(Cout / 64) * kTileM * 128u, wt_bytes = (uint32_t)Cout * 128u;
   const uint32_t g_bytes = (uint32_t)kTileM * 128u;
@@ -355,16 +363,14 @@ dcn_dgrad_kernel(const DcnParams prm, const DcnBwdParams bw) {
     const uint32_t g_half = (uint32_t)(chunk & 1) * 8u;                             // 8-byte half of a 16-byte chunk
     const uint32_t g_sw_lo = (((uint32_t)(chunk >> 1)) ^ r7) << 4, g_sw_hi = ((4u + (uint32_t)(chunk >> 1)) ^ r7) << 4;
     const uint32_t row0 = (uint32_t)(warp << 2) + sub;
-    const uint32_t ex = (uint32_t)Cin, ey = (uint32_t)prm.W * (uint32_t)Cin;
+    const ptrdiff_t ex = Cin, ey = (ptrdiff_t)prm.xw * Cin;                        // bordered rows
     uint4 va[ITERS], vb[ITERS], vc[ITERS], vd[ITERS];
-    auto gather = [&](int i, const __nv_bfloat16* xc, uint32_t g) {
-      const uint32_t e0 = g & ~63u;
-      const uint32_t dx = (g & 1u) ? ex : 0u;
-      const uint32_t e2 = e0 + ((g & 2u) ? ey : 0u);
-      va[i] = ldg_gather8x2(xc + e0);
-      vb[i] = ldg_gather8x2(xc + e0 + dx);
-      vc[i] = ldg_gather8x2(xc + e2);
-      vd[i] = ldg_gather8x2(xc + e2 + dx);
+    auto gather = [&](int i, const __nv_bfloat16* xc, uint32_t e0) {
+      const __nv_bfloat16* p = xc + e0;            // one 64-bit multiply-add, the other corners are adds
+      va[i] = ldg_gather8x2(p);
+      vb[i] = ldg_gather8x2(p + ex);
+      vc[i] = ldg_gather8x2(p + ey);
+      vd[i] = ldg_gather8x2(p + ey + ex);
     };
     int c_img = 0, c_pix[ITERS];                 // image and output pixel (or -1) of this thread's rows
     auto set_tile = [&](int it) {
@@ -383,7 +389,7 @@ dcn_dgrad_kernel(const DcnParams prm, const DcnBwdParams bw) {
     const __nv_bfloat16* l_x = prm.xh + chunk * 4;
     if (total > 0) {
       set_tile(0);
-      l_x = prm.xh + (size_t)c_img * Pin * Cin + chunk * 4;
+      l_x = prm.xh + (size_t)c_img * prm.ximg + chunk * 4;
       dcn_mbar_wait(&bars.geo_full[0], 0u);
 #pragma unroll
       for (int i = 0; i < ITERS; ++i) gather(i, l_x, geo[row0 + i * NP * 4].x);
@@ -398,7 +404,7 @@ dcn_dgrad_kernel(const DcnParams prm, const DcnBwdParams bw) {
           l_cb = 0; ++l_it;
           if (have_next) {
             const int tile = tile_first + l_it;
-            l_x = prm.xh + (size_t)(tile / prm.tiles_per_image) * Pin * Cin + chunk * 4;
+            l_x = prm.xh + (size_t)(tile / prm.tiles_per_image) * prm.ximg + chunk * 4;
             dcn_mbar_wait(&bars.geo_full[l_it & 1], (unsigned)((l_it >> 1) & 1));
           }
         }
@@ -406,7 +412,8 @@ dcn_dgrad_kernel(const DcnParams prm, const DcnBwdParams bw) {
       const __nv_bfloat16* l_xc = l_x + l_cb * kBK;
       const uint4* geo_n = geo + ((l_it & 1) * 9 + l_t) * kTileM + row0;
       const uint4* geo_c = geo + ((c_it & 1) * 9 + c_t) * kTileM + row0;
-      float* gxp = bw.gx + (size_t)c_img * Pin * Cin + c_cb * kBK + chunk * 4;
+      float* gxp = bw.gx + (size_t)c_img * prm.ximg + c_cb * kBK + chunk * 4;
+      asm volatile("" : "+l"(gxp));                // keep the base in registers (else it is re-derived per corner)
       dcn_mbar_wait(&bars.g_full[gs], gph);
       const uint8_t* g_tile = gring + (size_t)gs * g_bytes;
 #pragma unroll
@@ -419,38 +426,40 @@ dcn_dgrad_kernel(const DcnParams prm, const DcnBwdParams bw) {
           const uint2 hi = *reinterpret_cast<const uint2*>(grow + g_sw_hi);
           gq = make_uint4(lo.x, lo.y, hi.x, hi.y);
         }
-        const uint32_t g = q4.x;
+        const uint32_t e0 = q4.x;
         const float lh = __uint_as_float(q4.y), lw = __uint_as_float(q4.z), m = __uint_as_float(q4.w);
-        const float g8[8] = {bf_lo(gq.x), bf_hi(gq.x), bf_lo(gq.y), bf_hi(gq.y),
-                             bf_lo(gq.z), bf_hi(gq.z), bf_lo(gq.w), bf_hi(gq.w)};
-        const float o1 = ((g & 20u) == 20u) ? 1.f : 0.f, o2 = ((g & 36u) == 36u) ? 1.f : 0.f;   // top&left, top&right
-        const float o3 = ((g & 24u) == 24u) ? 1.f : 0.f, o4 = ((g & 40u) == 40u) ? 1.f : 0.f;   // bottom&left, bottom&right
-        float d1 = dot8(g8, va[i]) * o1, d2 = dot8(g8, vb[i]) * o2;
-        float d3 = dot8(g8, vc[i]) * o3, d4 = dot8(g8, vd[i]) * o4;
+        const pk2 g2[4] = {bf2(gq.x), bf2(gq.y), bf2(gq.z), bf2(gq.w)};
+        const float d1 = dot8(g2, va[i]), d2 = dot8(g2, vb[i]), d3 = dot8(g2, vc[i]), d4 = dot8(g2, vd[i]);
         const float hh = 1.f - lh, hw = 1.f - lw;
-        const float w1 = hh * hw * o1, w2 = hh * lw * o2, w3 = lh * hw * o3, w4 = lh * lw * o4;
+        const float w1 = hh * hw, w2 = hh * lw, w3 = lh * hw, w4 = lh * lw;
         {                                        // grad_input: G * mask * corner weight (deform_conv_cuda_kernel.cu:944)
-          const uint32_t e0 = g & ~63u;
-          const uint32_t dx = (g & 1u) ? ex : 0u;
-          const uint32_t e2 = e0 + ((g & 2u) ? ey : 0u);
-          auto scat = [&](uint32_t e, float c) {
+          float* gp = gxp + e0;
+          asm volatile("" : "+l"(gp));
+          auto scat = [&](float* q, float c) {
             if (c != 0.f) {
-              red_add_v4(gxp + e, g8[0] * c, g8[1] * c, g8[2] * c, g8[3] * c);
-              red_add_v4(gxp + e + 32, g8[4] * c, g8[5] * c, g8[6] * c, g8[7] * c);
+              const pk2 cc = pk(c, c);
+              float a0, a1, a2, a3;
+              upk(mul2(g2[0], cc), a0, a1); upk(mul2(g2[1], cc), a2, a3);
+              red_add_v4(q, a0, a1, a2, a3);
+              upk(mul2(g2[2], cc), a0, a1); upk(mul2(g2[3], cc), a2, a3);
+              red_add_v4(q + 32, a0, a1, a2, a3);
             }
           };
-          scat(e0, m * w1); scat(e0 + dx, m * w2); scat(e2, m * w3); scat(e2 + dx, m * w4);
+          scat(gp, m * w1); scat(gp + ex, m * w2); scat(gp + ey, m * w3); scat(gp + ey + ex, m * w4);
         }
         if (have_next) gather(i, l_xc, geo_n[i * NP * 4].x);   // refill the slot: K block n+1, same row group
+        // this lane's share of the three per-(pixel, tap) sums, then one 8-lane reduction each
+        float vm = w1 * d1 + w2 * d2 + w3 * d3 + w4 * d4;             // :1019-1030
+        float vh = hw * (d3 - d1) + lw * (d4 - d2);                   // dmcn_get_coordinate_weight, bp_dir 0 (x mask below)
+        float vw = hh * (d2 - d1) + lh * (d4 - d3);                   // bp_dir 1
 #pragma unroll
         for (int o = 1; o < 8; o <<= 1) {
-          d1 += __shfl_xor_sync(0xffffffffu, d1, o); d2 += __shfl_xor_sync(0xffffffffu, d2, o);
-          d3 += __shfl_xor_sync(0xffffffffu, d3, o); d4 += __shfl_xor_sync(0xffffffffu, d4, o);
+          vm += __shfl_xor_sync(0xffffffffu, vm, o);
+          vh += __shfl_xor_sync(0xffffffffu, vh, o);
+          vw += __shfl_xor_sync(0xffffffffu, vw, o);
         }
         if (chunk == 0) {
-          float vm = w1 * d1 + w2 * d2 + w3 * d3 + w4 * d4;             // :1019-1030
-          float vh = m * (hw * (d3 - d1) + lw * (d4 - d2));             // dmcn_get_coordinate_weight, bp_dir 0
-          float vw = m * (hh * (d2 - d1) + lh * (d4 - d3));             // bp_dir 1
+          vh *= m; vw *= m;
           float* a = acc + (3 * c_t) * kTileM + row0 + i * NP * 4;      // partial sums over channel blocks
           if (c_cb > 0) { vm += a[0]; vh += a[kTileM]; vw += a[2 * kTileM]; }
           if (c_cb == cpb - 1) {
@@ -595,8 +604,9 @@ static inline size_t dcnb_align256(size_t v) { return (v + 255) / 256 * 256; }
 
 extern "C" size_t dcnv2_backward_workspace_bytes(int B, int Cin, int H, int W, int Cout, int Ho, int Wo) {
   if (B <= 0 || Cin <= 0 || H <= 0 || W <= 0 || Cout <= 0 || Ho <= 0 || Wo <= 0) return 0;
-  return dcnb_align256((size_t)B * H * W * Cin * 2) + dcnb_align256((size_t)B * Ho * Wo * Cout * 2) +
-         dcnb_align256((size_t)Cout * Cin * 9 * 2) + dcnb_align256((size_t)B * H * W * Cin * 4);
+  const size_t bordered = (size_t)B * (H + 2) * (W + 2) * Cin;       // x (bf16) and grad_input (fp32) with a zero border
+  return dcnb_align256(bordered * 2) + dcnb_align256((size_t)B * Ho * Wo * Cout * 2) +
+         dcnb_align256((size_t)Cout * Cin * 9 * 2) + dcnb_align256(bordered * 4);
 }
 
 extern "C" int dcnv2_backward(const float* input, const float* weight, const float* offset, const float* mask,
@@ -621,13 +631,14 @@ extern "C" int dcnv2_backward(const float* input, const float* weight, const flo
   if (!input || !weight || !offset || !mask || !grad_output || !workspace) return CTDET_ENULL;
   if (workspace_bytes < dcnv2_backward_workspace_bytes(B, Cin, H, W, Cout, Ho, Wo)) return CTDET_EWORKSPACE;
   if (reinterpret_cast<uintptr_t>(workspace) & 15u) return CTDET_EALIGN;
-  if ((size_t)H * W >= ((size_t)1 << 31) / (size_t)Cin || B > 65535) return CTDET_EINVAL;
+  if ((size_t)(H + 2) * (W + 2) >= ((size_t)1 << 31) / (size_t)Cin || B > 65535) return CTDET_EINVAL;
   cudaStream_t st = (cudaStream_t)stream;
   const int Pin = H * W, P = Ho * Wo;
+  const size_t ximg = (size_t)(H + 2) * (W + 2) * Cin;                // elements of one bordered image
 
   unsigned char* wsp = reinterpret_cast<unsigned char*>(workspace);
   __nv_bfloat16* xh = reinterpret_cast<__nv_bfloat16*>(wsp);
-  wsp += dcnb_align256((size_t)B * Pin * Cin * 2);
+  wsp += dcnb_align256((size_t)B * ximg * 2);
   __nv_bfloat16* gh = reinterpret_cast<__nv_bfloat16*>(wsp);
   wsp += dcnb_align256((size_t)B * P * Cout * 2);
   __nv_bfloat16* wt = reinterpret_cast<__nv_bfloat16*>(wsp);
@@ -639,12 +650,23 @@ extern "C" int dcnv2_backward(const float* input, const float* weight, const flo
     e = cudaMemsetAsync(grad_bias, 0, (size_t)Cout * 4, st);
     if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
   }
+  e = cudaMemsetAsync(xh, 0, (size_t)B * ximg * 2, st);               // the border (the pack fills the interior)
+  if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
   int vec = (Pin % 4 == 0 && aligned16(input)) ? 1 : 0;
-  dcn_pack_input_kernel<<<dim3((Pin + 63) / 64, (Cin + 63) / 64, B), 256, 0, st>>>(input, xh, Cin, Pin, vec, nullptr);
+  dcn_pack_input_kernel<<<dim3((Pin + 63) / 64, (Cin + 63) / 64, B), 256, 0, st>>>(input, xh, Cin, Pin, vec, nullptr, 1, W);
   int rc = check_launch();
   if (rc) return rc;
   vec = (P % 4 == 0 && aligned16(grad_output)) ? 1 : 0;     // grad_bias = per-channel sums, same pass
-  dcn_pack_input_kernel<<<dim3((P + 63) / 64, (Cout + 63) / 64, B), 256, 0, st>>>(grad_output, gh, Cout, P, vec, grad_bias);
+  {
+    // with grad_bias a CTA covers several 64-pixel blocks (fewer same-address atomics), but the grid
+    // keeps at least ~4 CTAs per SM
+    const int blocks = (P + 63) / 64;
+    int chunks = 1;
+    if (grad_bias)
+      while (chunks < 16 && (long long)(blocks / (chunks * 2)) * ((Cout + 63) / 64) * B >= 4LL * kNumSMs) chunks *= 2;
+    dcn_pack_input_kernel<<<dim3((blocks + chunks - 1) / chunks, (Cout + 63) / 64, B), 256, 0, st>>>(grad_output, gh, Cout, P, vec,
+                                                                                                    grad_bias, chunks, 0);
+  }
   rc = check_launch();
   if (rc) return rc;
 
@@ -653,6 +675,7 @@ extern "C" int dcnv2_backward(const float* input, const float* weight, const flo
   prm.scale = nullptr; prm.shift = nullptr; prm.y = nullptr;
   prm.Cin = Cin; prm.H = H; prm.W = W; prm.Ho = Ho; prm.Wo = Wo; prm.Cout = Cout;
   prm.stride = stride_h; prm.pad = pad_h; prm.dil = dilation_h; prm.relu = 0;
+  prm.xw = W + 2; prm.ximg = (int)ximg; prm.xorg = (W + 3) * Cin;
   prm.tiles_x = (Wo + kTileW - 1) / kTileW;
   prm.tiles_per_image = prm.tiles_x * ((Ho + kTileH - 1) / kTileH);
   const long long tiles = (long long)B * prm.tiles_per_image;
@@ -692,7 +715,7 @@ extern "C" int dcnv2_backward(const float* input, const float* weight, const flo
     if (rc) return rc;
   }
   if (want_d) {
-    e = cudaMemsetAsync(gx, 0, (size_t)B * Pin * Cin * 4, st);
+    e = cudaMemsetAsync(gx, 0, (size_t)B * ximg * 4, st);
     if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
     dcn_pack_weight_t_kernel<<<kNumSMs, 256, 0, st>>>(weight, wt, Cout, Cin);
     rc = check_launch();
@@ -714,7 +737,7 @@ extern "C" int dcnv2_backward(const float* input, const float* weight, const flo
     kern<<<grid, (npd + 10) * 32, smem, st>>>(prm, bw);
     rc = check_launch();
     if (rc) return rc;
-    dcn_unpack_grad_input_kernel<<<dim3((Pin + 63) / 64, Cin / 64, B), 256, 0, st>>>(gx, grad_input, Cin, Pin);
+    dcn_unpack_grad_input_kernel<<<dim3((Pin + 63) / 64, Cin / 64, B), 256, 0, st>>>(gx, grad_input, Cin, Pin, W);
     rc = check_launch();
     if (rc) return rc;
   }

@@ -130,7 +130,8 @@ __device__ __forceinline__ float ldg_stream1(const float* p) {      // read-once
 
 // ------------------------------------------------------------------------------------------------
 struct DcnParams {
-  const __nv_bfloat16* xh;     // [B][H*W][Cin]
+  const __nv_bfloat16* xh;     // [B][ximg / Cin pixels][Cin]: rows of xw pixels, image pixel (0,0) at element xorg
+                               // (forward: xw = W, xorg = 0; backward: a zero border of one pixel, xw = W + 2)
   const float* offset;         // [B][18][Ho*Wo]   channel 2t = dh, 2t+1 = dw (deform_conv_cuda_kernel.cu:838-846)
   const float* mask;           // [B][9][Ho*Wo]
   const __nv_bfloat16* wk;     // [9*Cin/64][Cout][64] swizzled B tiles
@@ -139,6 +140,7 @@ struct DcnParams {
   const float* shift;          // [Cout] or null
   float* y;                    // [B][Cout][Ho*Wo]
   int Cin, H, W, Ho, Wo, Cout, stride, pad, dil, relu, tiles_per_image, tiles_x, num_tiles, stages, mma_sleep, ld_sleep;
+  int xw, ximg, xorg;
   uint32_t tmem_cols;
 };
 
@@ -165,7 +167,7 @@ __device__ __forceinline__ void tap_geometry(const DcnParams& prm, float off_h, 
       const float hh = 1.f - lh, hw = 1.f - lw;
       const bool t_ok = h_low >= 0, b_ok = h_high <= H - 1, l_ok = w_low >= 0, r_ok = w_high <= W - 1;
       const int hl = max(h_low, 0), hh_i = min(h_high, H - 1), wl = max(w_low, 0), wh_i = min(w_high, W - 1);
-      g = (uint32_t)(hl * W + wl) * (uint32_t)prm.Cin | (wh_i != wl ? 1u : 0u) | (hh_i != hl ? 2u : 0u);
+      g = (uint32_t)(hl * prm.xw + wl) * (uint32_t)prm.Cin | (wh_i != wl ? 1u : 0u) | (hh_i != hl ? 2u : 0u);
       wq.x = (t_ok && l_ok) ? hh * hw * m : 0.f;
       wq.y = (t_ok && r_ok) ? hh * lw * m : 0.f;
       wq.z = (b_ok && l_ok) ? lh * hw * m : 0.f;
@@ -206,14 +208,14 @@ __device__ __forceinline__ void dcn_producer_loop(const DcnParams& prm, uint8_t*
                                                   const uint4* geo_w, const uint32_t* geo_g, DcnBarriers& bars,
                                                   int warp, int lane, int tile_first, int my_tiles, int kb0, int kb1) {
   constexpr int ITERS = 32 / NP;               // 4-row groups per warp per K block
-  const int Cin = prm.Cin, Pin = prm.H * prm.W;
+  const int Cin = prm.Cin;
   const int sub = lane >> 3, chunk = lane & 7;
   const uint32_t swz = (uint32_t)((chunk ^ (((warp & 1) << 2) + sub)) << 4);      // row & 7 is fixed per thread
   const uint32_t row0 = (uint32_t)(warp << 2) + sub;
-  const uint32_t ex = (uint32_t)Cin, ey = (uint32_t)prm.W * (uint32_t)Cin;
+  const uint32_t ex = (uint32_t)Cin, ey = (uint32_t)prm.xw * (uint32_t)Cin;
   auto tile_x = [&](int it) {
     const int tile = tile_first + it;
-    return prm.xh + (size_t)(tile / prm.tiles_per_image) * Pin * Cin + chunk * 8;
+    return prm.xh + (size_t)(tile / prm.tiles_per_image) * prm.ximg + prm.xorg + chunk * 8;
   };
   uint4 va[ITERS], vb[ITERS], vc[ITERS], vd[ITERS];
   auto gather = [&](int i, const __nv_bfloat16* xc, uint32_t g) {
@@ -315,7 +317,7 @@ __device__ __forceinline__ void dcn_geometry_tile(const DcnParams& prm, int tile
 
 // pre-passes defined in dcn.cu
 __global__ void dcn_pack_input_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ xh, int C, int P, int vec,
-                                      float* __restrict__ chan_sum);
+                                      float* __restrict__ chan_sum, int chunks, int border_w);
 
 static inline int dcn_env_int(const char* name, int dflt) {
   const char* v = getenv(name);
