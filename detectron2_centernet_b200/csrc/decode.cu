@@ -107,14 +107,18 @@ constexpr int kKeepSlack = 384;                  // a CTA collects / emits at mo
 // All kThreads threads must call it; results land in *bs.
 struct BinScratch { unsigned int warp_tot[32]; int bin; unsigned int cnt_ge; };
 
-template <int kThreads>
+template <int kThreads, bool kSharedHist = false>
 __device__ void find_threshold_bin(const unsigned int* hist, int need, BinScratch* bs) {
   constexpr int PER = kHistBins / kThreads;      // descending slots owned by one thread
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   unsigned int loc[PER];
   unsigned int sum = 0;
 #pragma unroll
-  for (int j = 0; j < PER; ++j) { loc[j] = __ldcg(hist + (kHistBins - 1 - (tid * PER + j))); sum += loc[j]; }
+  for (int j = 0; j < PER; ++j) {
+    const unsigned int* q = hist + (kHistBins - 1 - (tid * PER + j));
+    loc[j] = kSharedHist ? *q : __ldcg(q);
+    sum += loc[j];
+  }
   unsigned int incl = sum;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
@@ -451,20 +455,59 @@ decode_finalize_kernel(DecodeHeader* __restrict__ hdrs, unsigned int* __restrict
   const int HW = H * W;
 
   if (tid == 0) s_n = 0;
+  // The list is read by ONE CTA: every pass keeps 8 loads per thread in flight (a plain loop exposes
+  // one L2 round trip per 512 keys).  f is called for every key of the list; 0 = no key.
+  auto scan_keys = [&](auto f) {
+    for (int i0 = 0; i0 < n_keys; i0 += 8 * kFinThreads) {
+      u64 kk[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int i = i0 + u * kFinThreads + tid;
+        kk[u] = i < n_keys ? __ldcg(kb + i) : 0ull;       // real keys are never 0 (low word = ~flat index)
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) f(kk[u]);
+    }
+  };
   // every collected peak of the image was counted once in ghist: its K-th best bin is final now
   find_threshold_bin<kFinThreads>(ghist, K, &bs);
   u64 T = ((u64)bs.bin << kHistShift) << 32;
   if (bs.cnt_ge < (unsigned)K) T = 0ull;                  // fewer than K peaks in the whole image
-  if (bs.cnt_ge > (unsigned)kSelCap) {
-    // too many keys share the threshold bin: exact radix select over the list instead
-    T = radix_select_kth<kFinThreads>(
-        [&](auto f) { for (int i = tid; i < n_keys; i += kFinThreads) f(kb[i]); }, n_keys, K, &sc);
+  if (T != 0ull && bs.cnt_ge > (unsigned)kFinThreads) {
+    // The 11-bit bins are coarse near the top (sign + exponent + 2 mantissa bits: all of [0.875, 1) is one
+    // bin, ~3800 peaks of a 512^2 image).  Refine once: histogram the NEXT 11 bits of the keys inside the
+    // threshold bin (shared memory), find the sub-bin of the K-th best and collect from there up --
+    // K plus a handful of keys, which the rank sort below takes.  Two passes over the list instead of
+    // the 8 of an exact radix select, which remains the fall-back when ties keep the count too high.
+    __shared__ unsigned int s_h2[kHistBins];
+    __shared__ int s_above;
+    const uint32_t tbin = (uint32_t)bs.bin;
+    for (int i = tid; i < kHistBins; i += kFinThreads) s_h2[i] = 0u;
+    if (tid == 0) s_above = 0;
+    __syncthreads();
+    int above = 0;
+    scan_keys([&](u64 key) {
+      const uint32_t ord = (uint32_t)(key >> 32), ob = ord >> kHistShift;
+      if (key == 0ull || ob < tbin) return;
+      if (ob > tbin) ++above;
+      else atomicAdd(&s_h2[(ord >> (kHistShift - kHistBits)) & (kHistBins - 1)], 1u);
+    });
+    above = warp_sum(above);
+    if ((tid & 31) == 0 && above) atomicAdd(&s_above, above);
+    __syncthreads();
+    const int hi = s_above;                               // < K: that is what made tbin the threshold bin
+    find_threshold_bin<kFinThreads, true>(s_h2, K - hi, &bs);
+    if ((unsigned)hi + bs.cnt_ge <= (unsigned)kSelCap) {
+      T = (u64)((tbin << kHistShift) | ((uint32_t)bs.bin << (kHistShift - kHistBits))) << 32;
+    } else {
+      T = radix_select_kth<kFinThreads>(
+          [&](auto f) { for (int i = tid; i < n_keys; i += kFinThreads) f(kb[i]); }, n_keys, K, &sc);
+    }
   }
   __syncthreads();
-  for (int i = tid; i < n_keys; i += kFinThreads) {
-    const u64 key = kb[i];
-    if (key >= T) { const int pos = atomicAdd(&s_n, 1); if (pos < kSelCap) s_sel[pos] = key; }
-  }
+  scan_keys([&](u64 key) {
+    if (key != 0ull && key >= T) { const int pos = atomicAdd(&s_n, 1); if (pos < kSelCap) s_sel[pos] = key; }
+  });
   for (int i = tid; i < kHistBins; i += kFinThreads) ghist[i] = 0u;     // leave the workspace zeroed
   __syncthreads();
   if (tid == 0) { hdr->count = 0u; hdr->thr_ord = 0u; }

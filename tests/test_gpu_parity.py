@@ -474,6 +474,63 @@ def test_full_size_properties():
     assert torch.equal(b1[0], boxes[7]) and torch.equal(c1[0], classes[7])
 
 
+def test_config4_1024_targets_and_decode():
+    """BASELINE config 4: B = 8 at 1024^2 -> [8, 80, 256, 256] maps, 128 objects per image (the MAXOBJ
+    limit of detection_utils.py:606).  Two images are checked against the oracle outright (the oracle
+    needs ~50 ms per image at this size), the whole batch through size-independent properties."""
+    from detectron2_centernet_b200 import decode as D
+    B, C, H, W, K = 8, 80, 256, 256, 100
+    bl, cl = S.make_batch_objects(1238, B, 1024, n=128)
+    out = _targets(bl, cl, H, W, C)
+    ref = O.gen_heatmap_batch(bl[:2], cl[:2], H, W, C)
+    for k in ("reg_mask", "ind", "wh", "reg"):
+        assert np.array_equal(out[k][:2].cpu().numpy(), ref[k]), k
+    got = out["hm"][:2].cpu().numpy()
+    assert np.abs(got - ref["hm"]).max() <= 1e-6
+    assert np.array_equal(got == 1, ref["hm"] == 1) and np.array_equal(got == 0, ref["hm"] == 0)
+    assert int((out["hm"] == 1).sum()) == int(out["num_pos"].sum())
+    assert int(out["reg_mask"].sum()) == sum(int(((b[:, 2] > b[:, 0]) & (b[:, 3] > b[:, 1])).sum()) for b in bl)
+    hm, wh, reg = S.make_head_outputs(1238, B, C, H, W, boxes_list=bl)
+    heat = S.sigmoid_clamp(hm)
+    heat_t, wh_t, reg_t = _cuda(heat, wh, reg)
+    boxes, scores, classes, inds = D.ctdet_decode_batch(heat_t, wh_t, reg_t, down_ratio=4, K=K)
+    for b in range(2):                                              # oracle, image by image like the reference
+        rb, rs, rc, ri = O.decode(heat[b:b + 1], wh[b:b + 1], reg[b:b + 1], 4, K)
+        assert np.array_equal(scores[b].cpu().numpy(), rs[0]) and np.array_equal(classes[b].cpu().numpy(), rc[0])
+        assert np.array_equal(inds[b].cpu().numpy(), ri[0]) and np.array_equal(boxes[b].cpu().numpy(), rb[0])
+    pooled = torch.nn.functional.max_pool2d(heat_t, 3, 1, 1)
+    peaks = torch.where(pooled == heat_t, heat_t, torch.zeros_like(heat_t)).view(B, -1)
+    ref_s, ref_i = torch.topk(peaks, K, dim=1)
+    assert torch.equal(ref_s, scores) and torch.equal(ref_i, classes.long() * (H * W) + inds)
+
+
+def test_config3_b64_decode():
+    """BASELINE config 3: B = 64 decode, K = 100, 3x3 NMS over [64, 80, 128, 128]."""
+    from detectron2_centernet_b200 import decode as D
+    B, C, H, W, K = 64, 80, 128, 128, 100
+    g = torch.Generator(device=DEV).manual_seed(3)
+    logits = torch.randn((B, C, H, W), device=DEV, generator=g) * 1.5 - 2.19
+    wh = torch.rand((B, 2, H, W), device=DEV, generator=g) * 64
+    reg = torch.rand((B, 2, H, W), device=DEV, generator=g)
+    heat = torch.clamp(torch.sigmoid(logits), 1e-4, 1 - 1e-4)
+    boxes, scores, classes, inds = D.ctdet_decode_batch(heat, wh, reg, down_ratio=4, K=K)
+    pooled = torch.nn.functional.max_pool2d(heat, 3, 1, 1)
+    peaks = torch.where(pooled == heat, heat, torch.zeros_like(heat)).view(B, -1)
+    ref_s, ref_i = torch.topk(peaks, K, dim=1)
+    assert torch.equal(ref_s, scores) and torch.equal(ref_i, classes.long() * (H * W) + inds)
+    # boxes from the gathered wh / reg, in the reference's operation order (centernet.py:436-455)
+    xs = (inds % W).float() + reg[:, 0].reshape(B, -1).gather(1, inds)
+    ys = (inds // W).float() + reg[:, 1].reshape(B, -1).gather(1, inds)
+    w2 = wh[:, 0].reshape(B, -1).gather(1, inds) / 2
+    h2 = wh[:, 1].reshape(B, -1).gather(1, inds) / 2
+    want = torch.stack([xs - w2, ys - h2, xs + w2, ys + h2], dim=2) * 4
+    assert torch.equal(boxes, want)
+    # one image through the oracle
+    rb, rs, rc, ri = O.decode(heat[63:64].cpu().numpy(), wh[63:64].cpu().numpy(), reg[63:64].cpu().numpy(), 4, K)
+    assert np.array_equal(scores[63].cpu().numpy(), rs[0]) and np.array_equal(classes[63].cpu().numpy(), rc[0])
+    assert np.array_equal(boxes[63].cpu().numpy(), rb[0])
+
+
 def test_postprocess_batch():
     from detectron2_centernet_b200 import decode as D
     B, C, H, W, K = 3, 5, 32, 32, 40
