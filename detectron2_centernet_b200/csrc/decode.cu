@@ -35,6 +35,24 @@ constexpr int kFinThreads = 512;                 // kernel 2
 
 typedef unsigned long long u64;
 
+// Programmatic dependent launch (PDL): a kernel launched with the programmatic-serialization attribute may
+// start while its predecessor in the stream drains; everything that depends on the predecessor's results
+// comes after pdl_wait() (= the predecessor grid has completed and its writes are visible).  Both are
+// no-ops in a kernel launched without the attribute.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
 struct SelectScratch {
   unsigned int hist[256];
   int need;         // how many still to take from the current bucket
@@ -152,8 +170,13 @@ __device__ void find_threshold_bin(const unsigned int* hist, int need, BinScratc
 }
 
 struct DecodeHeader {            // per image, zero on entry, reset by the finalize kernel
-  unsigned int count;            // keys emitted so far
+  unsigned int count;            // keys emitted so far by decode_peaks_kernel (the staged path)
   unsigned int thr_ord;          // a valid lower bound (ordered score) of the image's K-th best peak
+  unsigned int s_count;          // keys emitted by decode_stream_kernel
+  unsigned int staged;           // 1: the image is decoded by decode_peaks_kernel (no seed bound, or the
+                                 //    streaming list overflowed); finalize then reads that path's list
+  unsigned int ticket;           // decode_seed_kernel: CTAs of the image that have flushed their histogram
+  unsigned int pad[3];
 };
 
 struct DecodeShared {
@@ -205,12 +228,12 @@ __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, unsig
 // heat [B,C,H,W]; per image b: hdr[b], ghist[b][kHistBins], keys[b][0 .. tiles*(K+kKeepSlack))
 // grid = (bands, B, C): band fastest, then IMAGE, then class.  CTAs that run concurrently therefore
 // belong to many images, and most CTAs of an image start after its first CTAs published a bound.
-__global__ void __launch_bounds__(kDecThreads)
-decode_peaks_kernel(const float* __restrict__ heat, int C, int H, int W, int Wp, int K,
-                    int band_rows, int sub_rows, FastDiv div_strips, int flags,
-                    DecodeHeader* __restrict__ hdrs, unsigned int* __restrict__ ghists,
-                    u64* __restrict__ out_keys, size_t keys_per_image) {
-  extern __shared__ __align__(128) unsigned char s_raw[];
+__device__ __forceinline__ void
+decode_peaks_tile(const float* __restrict__ heat, int C, int H, int W, int Wp, int K,
+                  int band_rows, int sub_rows, FastDiv div_strips, int flags,
+                  DecodeHeader* __restrict__ hdrs, unsigned int* __restrict__ ghists,
+                  u64* __restrict__ out_keys, size_t keys_per_image,
+                  const int band, const int b, const int c, unsigned char* s_raw, const bool reinit) {
   const int strips = (int)div_strips.d;
   const int cap = (K + kKeepSlack + 1) & ~1;                            // even: keeps the bitmap 16-byte aligned
   float* tile = reinterpret_cast<float*>(s_raw);                        // [(band_rows+2)][Wp]
@@ -221,7 +244,6 @@ decode_peaks_kernel(const float* __restrict__ heat, int C, int H, int W, int Wp,
   __shared__ __align__(8) uint64_t s_bar;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int band = blockIdx.x, b = blockIdx.y, c = blockIdx.z;
   const int plane = b * C + c;
   const bool logits = flags & CTDET_DECODE_LOGITS;
   const bool no_nms = flags & CTDET_DECODE_NO_NMS;
@@ -240,6 +262,7 @@ decode_peaks_kernel(const float* __restrict__ heat, int C, int H, int W, int Wp,
   const bool bulk = (Wp == W);
   const int n_words = nrows * strips * 4;
   if (tid == 0) {
+    if (reinit) asm volatile("mbarrier.inval.shared::cta.b64 [%0];" :: "r"((uint32_t)__cvta_generic_to_shared(&s_bar)) : "memory");
     mbar_init(&s_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     if (bulk) {
@@ -431,6 +454,265 @@ decode_peaks_kernel(const float* __restrict__ heat, int C, int H, int W, int Wp,
   }
 }
 
+// Launch forms.  gated == 0: grid (bands, B, C), one tile per CTA -- band fastest, then IMAGE, then class,
+// so CTAs that run concurrently belong to many images and most CTAs of an image start after its first
+// CTAs published a bound.  gated == 1: the exact fall-back behind decode_stream_kernel: a small 1-D grid
+// that returns at once unless some image was handed over (hdr->staged, written before this launch
+// started) and otherwise walks the tiles of those images in the same order.
+__global__ void __launch_bounds__(kDecThreads)
+decode_peaks_kernel(const float* __restrict__ heat, int B, int C, int H, int W, int Wp, int K,
+                    int band_rows, int sub_rows, FastDiv div_strips, int flags,
+                    DecodeHeader* __restrict__ hdrs, unsigned int* __restrict__ ghists,
+                    u64* __restrict__ out_keys, size_t keys_per_image, int gated, int bands) {
+  extern __shared__ __align__(128) unsigned char s_raw[];
+  pdl_wait();
+  pdl_launch_dependents();
+  if (!gated) {
+    decode_peaks_tile(heat, C, H, W, Wp, K, band_rows, sub_rows, div_strips, flags, hdrs, ghists, out_keys,
+                      keys_per_image, blockIdx.x, blockIdx.y, blockIdx.z, s_raw, false);
+    return;
+  }
+  int any = 0;
+  for (int i = threadIdx.x; i < B; i += kDecThreads) any |= (hdrs[i].staged != 0u);
+  if (!__syncthreads_or(any)) return;
+  const long long total = (long long)bands * B * C;
+  bool reinit = false;
+  for (long long t = blockIdx.x; t < total; t += gridDim.x) {
+    const int band = (int)(t % bands);
+    const long long bc = t / bands;
+    const int b = (int)(bc % B), c = (int)(bc / B);
+    if (hdrs[b].staged == 0u) continue;                      // CTA-uniform
+    __syncthreads();                                         // the previous tile's shared state is dead
+    decode_peaks_tile(heat, C, H, W, Wp, K, band_rows, sub_rows, div_strips, flags, hdrs, ghists, out_keys,
+                      keys_per_image, band, b, c, s_raw, reinit);
+    reinit = true;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Streaming path (the default when C*H*W and W are multiples of 4): seed bound from a sample, then a
+// pure threshold sweep over the logits.
+//
+// decode_seed_kernel: 3x3-peak-tests a SAMPLE of every image -- groups of kSeedRows rows every
+// kSeedPeriod rows of every class plane, interior columns only, ~1/8 of the cells for ~3/16 of the
+// bytes -- and histograms the sampled peaks per image over the same 11-bit bins as above.  Every
+// counted cell is a real peak of the image, so the bin where the sample's suffix count reaches K is
+// a valid lower bound of the image's K-th best peak (typically near its 8K-th best).  The last CTA of
+// an image (ticket) publishes it in hdr->thr_ord and leaves the sample histogram zeroed; with fewer
+// than K sampled peaks the image is handed to the staged path (hdr->staged = 1).
+constexpr int kSeedThreads = 256;
+constexpr int kSeedWarps = kSeedThreads / 32;
+constexpr int kSeedPeriod = 64, kSeedRows = 4;
+constexpr int kSeedHist = kHistBins + kHistBins / 32;   // per image: the 2048 fine bins, then 64 coarse bins (32 fine each)
+
+__global__ void __launch_bounds__(kSeedThreads)
+decode_seed_kernel(const float* __restrict__ heat, int C, int H, int W, int K, int flags,
+                   int groups, FastDiv div_strips, FastDiv div_groups, unsigned int* __restrict__ phists) {
+  pdl_launch_dependents();             // the sweep may be scheduled as soon as every CTA of this grid runs
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int b = blockIdx.y;
+  const int strips = (int)div_strips.d;
+  const bool logits = flags & CTDET_DECODE_LOGITS;
+  const bool no_nms = flags & CTDET_DECODE_NO_NMS;
+  const float NEG = -__int_as_float(0x7f800000);
+  const float floor_f = logits ? -3.402823466e38f : __int_as_float(1);
+  unsigned int* phist = phists + (size_t)b * kSeedHist;
+
+  const int items = C * groups * strips;
+  for (int item = blockIdx.x * kSeedWarps + warp; item < items; item += gridDim.x * kSeedWarps) {
+    const int cg = (int)div_strips.div((uint32_t)item), strip = item - cg * strips;
+    const int c = (int)div_groups.div((uint32_t)cg), g = cg - c * groups;
+    const int r0 = 1 + g * kSeedPeriod;                       // tested rows r0 .. r0+kSeedRows-1, all interior
+    const int x0 = strip * 128 + lane * 4;
+    const bool in = x0 < W;                                   // W % 4 == 0: the lane's 4 cells exist
+    const float* base = heat + (((size_t)b * C + c) * H + (r0 - 1)) * W + (in ? x0 : 0);
+    float4 q[kSeedRows + 2];
+#pragma unroll
+    for (int r = 0; r < kSeedRows + 2; ++r)
+      q[r] = in ? ldg_stream4(base + (size_t)r * W) : make_float4(NEG, NEG, NEG, NEG);
+    float hm[kSeedRows + 2][4];
+#pragma unroll
+    for (int r = 0; r < kSeedRows + 2; ++r) {
+      const float l = __shfl_up_sync(0xffffffffu, q[r].w, 1);
+      const float rr = __shfl_down_sync(0xffffffffu, q[r].x, 1);
+      hm[r][0] = fmaxf(fmaxf(l, q[r].x), q[r].y);             // lane 0 / lane 31 edge cells are never tested
+      hm[r][1] = fmaxf(fmaxf(q[r].x, q[r].y), q[r].z);
+      hm[r][2] = fmaxf(fmaxf(q[r].y, q[r].z), q[r].w);
+      hm[r][3] = fmaxf(fmaxf(q[r].z, q[r].w), rr);
+    }
+    // one histogram entry per (row, 128-column segment): its best sampled peak.  Distinct entries are
+    // distinct peaks, and near the top of the distribution almost every high peak is its segment's best.
+    float best[kSeedRows];
+#pragma unroll
+    for (int t = 1; t <= kSeedRows; ++t) {
+      const float v[4] = {q[t].x, q[t].y, q[t].z, q[t].w};
+      float bt = NEG;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int x = x0 + j;
+        const bool testable = in && x >= 1 && x <= W - 2 && !(lane == 0 && j == 0) && !(lane == 31 && j == 3);
+        const float nb = fmaxf(fmaxf(hm[t - 1][j], hm[t][j]), hm[t + 1][j]);
+        if (testable && (no_nms || v[j] >= nb) && v[j] >= floor_f) bt = fmaxf(bt, v[j]);
+      }
+      best[t - 1] = bt;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+      for (int t = 0; t < kSeedRows; ++t) best[t] = fmaxf(best[t], __shfl_xor_sync(0xffffffffu, best[t], o));
+    }
+    float mine = NEG;
+#pragma unroll
+    for (int t = 0; t < kSeedRows; ++t) if (lane == t) mine = best[t];
+    if (lane < kSeedRows && mine >= floor_f) {
+      const uint32_t bin = float_to_ordered(mine) >> kHistShift;
+      atomicAdd(phist + bin, 1u);
+      atomicAdd(phist + kHistBins + (bin >> 5), 1u);
+    }
+  }
+}
+
+// decode_stream_kernel: one CTA per 32 KB of one image's logits, read as a flat float4 stream with 8
+// independent 16-byte loads per thread in flight.  The only per-cell work is "max of 4 >= bound";
+// the few float4s that pass (~0.3 %) go to a shared-memory list and are peak-tested afterwards,
+// one thread per cell, with the 8 neighbours re-read through L2.  Peaks at or above the bound are
+// appended to the image's key list and counted in its histogram, exactly as in the staged kernel, so
+// the finalize kernel is shared.  A list overflow (ties / plateaus at the bound) hands the image to the
+// staged path, which is exact for any input.
+constexpr int kStrThreads = 256, kStrU = 8;
+constexpr int kStrChunk = kStrThreads * kStrU;   // float4s per CTA
+constexpr int kStrList = 1024;                   // hit float4s remembered per CTA
+constexpr int kStreamCap = 16384;                // keys per image on this path
+
+__device__ __forceinline__ void stream_test_cell(const float* __restrict__ img, uint32_t flat, int H, int W,
+                                                 FastDiv div_hw, FastDiv div_w, float thv, uint32_t thr_ord, bool no_nms,
+                                                 DecodeHeader* hdr, unsigned int* shist, u64* skeys) {
+  const float v = __ldg(img + flat);
+  if (!(v >= thv)) return;
+  const uint32_t ord = float_to_ordered(v);
+  if (ord < thr_ord) return;                                  // -0.0 against a +0.0 bound
+  if (!no_nms) {
+    const uint32_t c = div_hw.div(flat), sp = flat - c * (uint32_t)(H * W);
+    const int y = (int)div_w.div(sp), x = (int)sp - y * W;
+    const float* q = img + flat;
+    const bool up = y > 0, dn = y < H - 1, lf = x > 0, rt = x < W - 1;
+    const float NEG = -__int_as_float(0x7f800000);
+    float nb = NEG;
+    if (up) { nb = fmaxf(nb, __ldg(q - W)); if (lf) nb = fmaxf(nb, __ldg(q - W - 1)); if (rt) nb = fmaxf(nb, __ldg(q - W + 1)); }
+    if (dn) { nb = fmaxf(nb, __ldg(q + W)); if (lf) nb = fmaxf(nb, __ldg(q + W - 1)); if (rt) nb = fmaxf(nb, __ldg(q + W + 1)); }
+    if (lf) nb = fmaxf(nb, __ldg(q - 1));
+    if (rt) nb = fmaxf(nb, __ldg(q + 1));
+    if (!(v >= nb)) return;
+  }
+  const unsigned int pos = atomicAdd(&hdr->s_count, 1u);
+  if (pos < (unsigned)kStreamCap) {
+    skeys[pos] = ((u64)ord << 32) | (u64)(0xffffffffu - flat);
+    atomicAdd(shist + (ord >> kHistShift), 1u);
+  } else {
+    hdr->staged = 1u;
+  }
+}
+
+__global__ void __launch_bounds__(kStrThreads, 4)
+decode_stream_kernel(const float* __restrict__ heat, int C, int H, int W, int n4, int chunks, int flags,
+                     FastDiv div_hw, FastDiv div_w, int K, DecodeHeader* __restrict__ hdrs,
+                     const unsigned int* __restrict__ phists,
+                     unsigned int* __restrict__ shists, u64* __restrict__ skeys_all) {
+  __shared__ uint32_t s_list[kStrList];
+  __shared__ int s_n;
+  __shared__ unsigned int s_thr, s_staged;
+  const int tid = threadIdx.x;
+  const int b = blockIdx.y;
+  DecodeHeader* hdr = hdrs + b;
+  const float* img = heat + (size_t)b * n4 * 4;
+  const float NEG = -__int_as_float(0x7f800000);
+  float4 q[kStrU];
+  auto load_chunk = [&](int chunk) {
+    const int base = chunk * kStrChunk + tid;
+#pragma unroll
+    for (int u = 0; u < kStrU; ++u) {
+      const int i = base + u * kStrThreads;
+      q[u] = i < n4 ? ldg_stream4(img + (size_t)i * 4) : make_float4(NEG, NEG, NEG, NEG);
+    }
+  };
+  int chunk = blockIdx.x;
+  load_chunk(chunk);                   // the logits do not depend on the seed kernel: in flight before the wait
+  pdl_wait();
+  pdl_launch_dependents();
+  if (tid < 32) {
+    // Warp 0, under the latency of the loads above: the highest bin of the image's SAMPLE histogram whose
+    // suffix count reaches K -- two dependent 128/256-byte reads: the 64 coarse bins (32 fine bins each),
+    // then the 32 fine bins of the coarse bin that holds the K-th entry.  Lane 0 owns the highest bins.
+    const unsigned int* ph = phists + (size_t)b * kSeedHist;
+    const uint2 c2 = __ldcg(reinterpret_cast<const uint2*>(ph + kHistBins) + (31 - tid));   // coarse 62-2l, 63-2l
+    const unsigned int sum = c2.x + c2.y;
+    unsigned int incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const unsigned int t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (tid >= o) incl += t;
+    }
+    const unsigned int excl = incl - sum;
+    const unsigned int hit = __ballot_sync(0xffffffffu, excl < (unsigned)K && incl >= (unsigned)K);
+    unsigned int ord = 0u;
+    if (hit) {
+      const int src = __ffs(hit) - 1;
+      const bool upper = excl + c2.y >= (unsigned)K;          // meaningful on lane src only
+      const int coarse = __shfl_sync(0xffffffffu, upper ? 63 - 2 * tid : 62 - 2 * tid, src);
+      const unsigned int before = __shfl_sync(0xffffffffu, upper ? excl : excl + c2.y, src);
+      const unsigned int f = __ldcg(ph + coarse * 32 + (31 - tid));                          // descending by lane
+      unsigned int fi = f;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const unsigned int t = __shfl_up_sync(0xffffffffu, fi, o);
+        if (tid >= o) fi += t;
+      }
+      const unsigned int hit2 = __ballot_sync(0xffffffffu, before + fi - f < (unsigned)K && before + fi >= (unsigned)K);
+      if (hit2) ord = (unsigned int)(coarse * 32 + 31 - (__ffs(hit2) - 1)) << kHistShift;
+    }
+    if (tid == 0) {
+      s_n = 0; s_thr = ord;
+      s_staged = ord ? *((volatile unsigned int*)&hdr->staged) : 1u;
+    }
+  }
+  __syncthreads();
+  if (s_staged) {                                             // CTA-uniform: the staged path owns this image
+    if (tid == 0 && blockIdx.x == 0) hdr->staged = 1u;        // (no usable sample bound, or an overflow elsewhere)
+    return;
+  }
+  if (tid == 0 && blockIdx.x == 0) atomicMax(&hdr->thr_ord, s_thr);   // head start for the staged path after an overflow
+  const bool logits = flags & CTDET_DECODE_LOGITS;
+  const bool no_nms = flags & CTDET_DECODE_NO_NMS;
+  const uint32_t thr_ord = s_thr;
+  const float thv = fmaxf(ordered_to_float(thr_ord), logits ? -3.402823466e38f : __int_as_float(1));
+  unsigned int* shist = shists + (size_t)b * kHistBins;
+  u64* skeys = skeys_all + (size_t)b * kStreamCap;
+  for (;;) {
+    const int base = chunk * kStrChunk + tid;
+#pragma unroll
+    for (int u = 0; u < kStrU; ++u) {
+      const float m = fmaxf(fmaxf(q[u].x, q[u].y), fmaxf(q[u].z, q[u].w));
+      if (m >= thv) {
+        const uint32_t i = (uint32_t)(base + u * kStrThreads);
+        const int pos = atomicAdd(&s_n, 1);
+        if (pos < kStrList) {
+          s_list[pos] = i;
+        } else {                                              // list full: test the 4 cells right here
+          for (int j = 0; j < 4; ++j)
+            stream_test_cell(img, i * 4u + j, H, W, div_hw, div_w, thv, thr_ord, no_nms, hdr, shist, skeys);
+        }
+      }
+    }
+    chunk += gridDim.x;
+    if (chunk >= chunks) break;
+    load_chunk(chunk);
+  }
+  __syncthreads();
+  const int n = min(s_n, kStrList) * 4;
+  for (int e = tid; e < n; e += kStrThreads)
+    stream_test_cell(img, s_list[e >> 2] * 4u + (uint32_t)(e & 3), H, W, div_hw, div_w, thv, thr_ord, no_nms, hdr, shist, skeys);
+}
+
 // ------------------------------------------------------------------------------------------------
 // Kernel 2: per image, exact top-K of the emitted keys, sort, gather, boxes.
 constexpr int kSelCap = 2048;
@@ -438,6 +720,8 @@ constexpr int kSelCap = 2048;
 __global__ void __launch_bounds__(kFinThreads)
 decode_finalize_kernel(DecodeHeader* __restrict__ hdrs, unsigned int* __restrict__ ghists,
                        const u64* __restrict__ keys, size_t keys_per_image,
+                       unsigned int* __restrict__ shists, const u64* __restrict__ skeys,   // streaming path (or null)
+                       unsigned int* __restrict__ phists,
                        const float* __restrict__ wh, const float* __restrict__ reg, int C, int H,
                        int W, int K, float down_ratio, int flags, float* __restrict__ boxes,
                        float* __restrict__ scores, int32_t* __restrict__ classes,
@@ -448,10 +732,13 @@ decode_finalize_kernel(DecodeHeader* __restrict__ hdrs, unsigned int* __restrict
   __shared__ int s_n;
   const int tid = threadIdx.x;
   const int b = blockIdx.x;
-  const u64* kb = keys + (size_t)b * keys_per_image;
   DecodeHeader* hdr = hdrs + b;
-  unsigned int* ghist = ghists + (size_t)b * kHistBins;
-  const int n_keys = (int)hdr->count;
+  pdl_wait();
+  // which path produced this image's list (CTA-uniform; the header is reset only after the barriers below)
+  const bool staged = (skeys == nullptr) || hdr->staged != 0u;
+  const u64* kb = staged ? keys + (size_t)b * keys_per_image : skeys + (size_t)b * kStreamCap;
+  unsigned int* ghist = (staged ? ghists : shists) + (size_t)b * kHistBins;
+  const int n_keys = staged ? (int)hdr->count : (int)hdr->s_count;   // s_count <= kStreamCap unless staged
   const int HW = H * W;
 
   if (tid == 0) s_n = 0;
@@ -509,8 +796,13 @@ decode_finalize_kernel(DecodeHeader* __restrict__ hdrs, unsigned int* __restrict
     if (key != 0ull && key >= T) { const int pos = atomicAdd(&s_n, 1); if (pos < kSelCap) s_sel[pos] = key; }
   });
   for (int i = tid; i < kHistBins; i += kFinThreads) ghist[i] = 0u;     // leave the workspace zeroed
+  if (skeys != nullptr) {
+    for (int i = tid; i < kSeedHist; i += kFinThreads) phists[(size_t)b * kSeedHist + i] = 0u;   // sample histogram
+    if (staged)                                                         // overflowed streaming pass: its histogram too
+      for (int i = tid; i < kHistBins; i += kFinThreads) shists[(size_t)b * kHistBins + i] = 0u;
+  }
   __syncthreads();
-  if (tid == 0) { hdr->count = 0u; hdr->thr_ord = 0u; }
+  if (tid == 0) { hdr->count = 0u; hdr->thr_ord = 0u; hdr->s_count = 0u; hdr->staged = 0u; }
   int n = min(s_n, kSelCap);                              // >= min(#peaks, K)
   // fewer than K peaks: the reference's heat*keep zeros fill the rest (:405); by the tie rule
   // these are the lowest flat indices that are not selected peaks.
@@ -617,6 +909,11 @@ decode_finalize_kernel(DecodeHeader* __restrict__ hdrs, unsigned int* __restrict
 struct DecodePlan {
   int band_rows, bands, tiles_per_image, Wp, strips, sub_rows;
   size_t smem, keys_per_image, header_bytes, hist_bytes, total_bytes;
+  // streaming path
+  bool stream;
+  int seed_groups, seed_ctas, stream_ctas, n4;
+  size_t skeys_bytes, phist_bytes;
+  int stream_chunks;
 };
 
 static DecodePlan make_plan(int B, int C, int H, int W, int K) {
@@ -642,7 +939,24 @@ static DecodePlan make_plan(int B, int C, int H, int W, int K) {
   p.keys_per_image = (size_t)p.tiles_per_image * cap;
   p.header_bytes = (((size_t)B * sizeof(DecodeHeader)) + 255) / 256 * 256;
   p.hist_bytes = (size_t)B * kHistBins * sizeof(unsigned int);
-  p.total_bytes = p.header_bytes + p.hist_bytes + (size_t)B * p.keys_per_image * sizeof(u64);
+  // streaming path: flat float4 view of an image + interior sample rows; CTDET_DECODE_STREAM=0 disables it
+  static int stream_on = -1;
+  if (stream_on < 0) { const char* e = getenv("CTDET_DECODE_STREAM"); stream_on = e ? (atoi(e) != 0) : 1; }
+  p.seed_groups = (H - 2 - kSeedRows) >= 0 ? (H - 2 - kSeedRows) / kSeedPeriod + 1 : 0;   // r0 + kSeedRows <= H - 1
+  p.stream = stream_on && (W % 4) == 0 && W >= 8 && p.seed_groups > 0;
+  p.n4 = (int)((long long)C * H * W / 4);
+  p.stream_chunks = (p.n4 + kStrChunk - 1) / kStrChunk;
+  p.stream_ctas = (p.stream_chunks + 1) / 2;                    // two 32 KB chunks per CTA
+  {
+    const int items = C * p.seed_groups * strips;               // one warp-item = 6 row segments of 512 B
+    p.seed_ctas = (items + kSeedWarps - 1) / kSeedWarps;
+    if (p.seed_ctas < 1) p.seed_ctas = 1;
+  }
+  p.skeys_bytes = p.stream ? (size_t)B * kStreamCap * sizeof(u64) : 0;
+  p.phist_bytes = (((size_t)B * kSeedHist * sizeof(unsigned int)) + 255) / 256 * 256;
+  // layout: headers | staged histograms | streaming histograms | sample histograms | streaming keys | staged keys
+  p.total_bytes = p.header_bytes + p.hist_bytes * (p.stream ? 2 : 1) + (p.stream ? p.phist_bytes : 0) + p.skeys_bytes +
+                  (size_t)B * p.keys_per_image * sizeof(u64);
   return p;
 }
 
@@ -680,14 +994,41 @@ extern "C" int ctdet_decode(const float* heat, const float* wh, const float* reg
   unsigned char* base = reinterpret_cast<unsigned char*>(workspace);
   DecodeHeader* hdr = reinterpret_cast<DecodeHeader*>(base);
   unsigned int* ghist = reinterpret_cast<unsigned int*>(base + p.header_bytes);
-  u64* keys = reinterpret_cast<u64*>(base + p.header_bytes + p.hist_bytes);
+  unsigned int* shist = p.stream ? reinterpret_cast<unsigned int*>(base + p.header_bytes + p.hist_bytes) : nullptr;
+  unsigned int* phist = p.stream ? reinterpret_cast<unsigned int*>(base + p.header_bytes + 2 * p.hist_bytes) : nullptr;
+  u64* skeys = p.stream ? reinterpret_cast<u64*>(base + p.header_bytes + 2 * p.hist_bytes + p.phist_bytes) : nullptr;
+  u64* keys = reinterpret_cast<u64*>(base + p.header_bytes + p.hist_bytes * (p.stream ? 2 : 1) +
+                                     (p.stream ? p.phist_bytes : 0) + p.skeys_bytes);
   if (B > 65535 || C > 65535) return CTDET_EINVAL;
-  decode_peaks_kernel<<<dim3(p.bands, B, C), kDecThreads, p.smem, st>>>(
-      heat, C, H, W, p.Wp, K, p.band_rows, p.sub_rows, FastDiv((uint32_t)p.strips), flags, hdr, ghist, keys,
-      p.keys_per_image);
-  int rc = check_launch();
+  int rc;
+  if (p.stream) {
+    decode_seed_kernel<<<dim3(p.seed_ctas, B), kSeedThreads, 0, st>>>(
+        heat, C, H, W, K, flags, p.seed_groups, FastDiv((uint32_t)p.strips), FastDiv((uint32_t)p.seed_groups), phist);
+    if ((rc = check_launch())) return rc;
+    cudaError_t e = launch_pdl(decode_stream_kernel, dim3(p.stream_ctas, B), dim3(kStrThreads), 0, st,
+                               heat, C, H, W, p.n4, p.stream_chunks, flags, FastDiv((uint32_t)(H * W)),
+                               FastDiv((uint32_t)W), K, hdr, (const unsigned int*)phist, shist, skeys);
+    if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
+    if ((rc = check_launch())) return rc;
+  }
+  const dim3 peaks_grid = p.stream ? dim3(2 * kNumSMs) : dim3(p.bands, B, C);
+  if (p.stream) {
+    cudaError_t e = launch_pdl(decode_peaks_kernel, peaks_grid, dim3(kDecThreads), p.smem, st,
+                               heat, B, C, H, W, p.Wp, K, p.band_rows, p.sub_rows, FastDiv((uint32_t)p.strips), flags,
+                               hdr, ghist, keys, p.keys_per_image, 1, p.bands);
+    if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
+  } else {
+    decode_peaks_kernel<<<peaks_grid, kDecThreads, p.smem, st>>>(
+        heat, B, C, H, W, p.Wp, K, p.band_rows, p.sub_rows, FastDiv((uint32_t)p.strips), flags, hdr, ghist, keys,
+        p.keys_per_image, 0, p.bands);
+  }
+  rc = check_launch();
   if (rc) return rc;
-  decode_finalize_kernel<<<B, kFinThreads, 0, st>>>(hdr, ghist, keys, p.keys_per_image, wh, reg, C, H, W,
-                                                    K, down_ratio, flags, boxes, scores, classes, inds);
+  {
+    cudaError_t e = launch_pdl(decode_finalize_kernel, dim3(B), dim3(kFinThreads), 0, st,
+                               hdr, ghist, (const u64*)keys, p.keys_per_image, shist, (const u64*)skeys, phist, wh, reg,
+                               C, H, W, K, down_ratio, flags, boxes, scores, classes, inds);
+    if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
+  }
   return check_launch();
 }
