@@ -185,7 +185,7 @@ def run_ours(args):
 
     LAUNCHES_PER_STEP = 4      # target_gen, loss, decode_peaks, decode_finalize
 
-    # The device-resident step is captured ONCE into a CUDA graph (4 kernel nodes) and replayed:
+    # The device-resident step is captured ONCE into a CUDA graph (6 kernel nodes) and replayed:
     # the kernels take 30-100 us each, so per-call Python/ctypes overhead would otherwise show up
     # as idle gaps on the stream.
     for _ in range(2):
@@ -302,7 +302,7 @@ def run_ours(args):
         "data": "synthetic (seeded COCO-shaped boxes; logits ~N(-2.19,1.5^2) + planted peaks)",
         "config": {"workload": WORKLOAD, "images_per_gpu": B, "heatmap": [C, H, W], "K": K,
                    "l2": "flushed (256 MB memset) between timed iterations",
-                   "launch": "device-resident step replayed from a CUDA graph (4 kernel nodes); e2e uses plain calls",
+                   "launch": "device-resident step replayed from a CUDA graph (6 kernel nodes); e2e uses plain calls",
                    "sharding": "by image, no data-path collective"},
         "clocks": clocks,
         "e2e": {"value": round(e2e_value, 1), "unit": "images/s", "h2d_bytes_per_step": h2d,

@@ -4,7 +4,15 @@
 // max_pool2d + == + mul: three full passes), _topk (:408-424, two torch.topk + three gathers), two
 // full-map NHWC permutes (:435,:442) and the per-image Python loop of CenterNet.inference (:224).
 //
-// Kernel 1 (HBM-bound, reads every heatmap cell exactly once = 4 B/cell):
+// Two paths produce the per-image list of candidate keys (ordered(score) << 32) | ~flat_index -- one integer
+// compare implements the tie rule "higher score, then lower flat index" -- both HBM-bound at 4 B/cell:
+//
+// STREAMING (default when W % 4 == 0): decode_seed_kernel derives a valid lower bound of every image's
+//   K-th best peak from a ~1/16 sample of the image; decode_stream_kernel then reads the logits as a flat
+//   float4 stream, rejects ~99.7 % of the cells with one compare against the bound and peak-tests the rest
+//   (neighbours re-read through L2).  See the comments above those kernels.
+// STAGED (any shape; also the exact fall-back for images the streaming path hands over: no usable sample
+//   bound, or more candidates at the bound than its list holds -- ties, plateaus): decode_peaks_kernel,
 //   one CTA per (image, class plane, row band).  The band (+ halo rows) is staged into shared
 //   memory by ONE bulk async copy (TMA 1-D, mbarrier completion); several CTAs are resident per SM
 //   so the copies of some overlap the peak tests of others.  Warps walk down the rows of a
@@ -12,18 +20,17 @@
 //   registers, horizontal neighbours by warp shuffle) and record the candidate cells -- 3x3 peaks
 //   at or above the current bound -- as a bitmap (4 ballots per row).  No barriers, no atomics in
 //   this sweep.  The few candidates are then collected from the bitmap into 64-bit keys
-//   (ordered(score) << 32) | ~flat_index -- one integer compare implements the tie rule "higher
-//   score, then lower flat index" -- and each bumps (fire-and-forget RED) a per-IMAGE histogram in
+//   and each bumps (fire-and-forget RED) a per-IMAGE histogram in
 //   global memory over the top bits of its score.  The bin where that histogram's suffix count
 //   reaches K is a valid lower bound of the image's K-th best peak: the first CTAs of an image
 //   derive and publish it (atomicMax), later CTAs start from it, so one float compare rejects
 //   almost every cell and only a few thousand keys per image survive.  Survivors are appended to a
 //   per-image list.  Exactness never depends on the bounds: they are always lower bounds; an exact
 //   MSB-first radix select is the fallback when a tile holds too many near-ties.
-// Kernel 2 (one CTA per image): final bound from the histogram + bitonic sort of the survivors = the
+// FINALIZE (one CTA per image): final bound from the histogram + rank sort of the survivors = the
 //   exact K best (equivalent to the reference's per-class top-K followed by a top-K over C*K),
-//   gather of wh/reg, boxes, outputs; resets the per-image header and histogram.
-// Workspace: per-image header {count, bound} + histogram (zero on entry, left zero) + key lists.
+//   gather of wh/reg, boxes, outputs; resets the per-image header and histograms.
+// Workspace: per-image headers + histograms (zero on entry, left zero) + key lists of both paths.
 #include <cstdlib>
 #include "common.cuh"
 
@@ -604,7 +611,15 @@ __device__ __forceinline__ void stream_test_cell(const float* __restrict__ img, 
     if (rt) nb = fmaxf(nb, __ldg(q + 1));
     if (!(v >= nb)) return;
   }
-  const unsigned int pos = atomicAdd(&hdr->s_count, 1u);
+  // one reservation per warp: the image's counter is a single address, and ~3000 returning atomics per image
+  // serialise in L2 (measured in a persistent variant of this kernel: they, not the sweep, set its time).
+  // All lanes of a warp work on the same image here.
+  const unsigned int peers = __activemask();
+  const int leader = __ffs(peers) - 1, lane = threadIdx.x & 31;
+  unsigned int base = 0;
+  if (lane == leader) base = atomicAdd(&hdr->s_count, (unsigned)__popc(peers));
+  base = __shfl_sync(peers, base, leader);
+  const unsigned int pos = base + (unsigned)__popc(peers & ((1u << lane) - 1u));
   if (pos < (unsigned)kStreamCap) {
     skeys[pos] = ((u64)ord << 32) | (u64)(0xffffffffu - flat);
     atomicAdd(shist + (ord >> kHistShift), 1u);
@@ -620,7 +635,6 @@ decode_stream_kernel(const float* __restrict__ heat, int C, int H, int W, int n4
                      unsigned int* __restrict__ shists, u64* __restrict__ skeys_all) {
   __shared__ uint32_t s_list[kStrList];
   __shared__ int s_n;
-  __shared__ unsigned int s_thr, s_staged;
   const int tid = threadIdx.x;
   const int b = blockIdx.y;
   DecodeHeader* hdr = hdrs + b;
@@ -635,22 +649,29 @@ decode_stream_kernel(const float* __restrict__ heat, int C, int H, int W, int n4
       q[u] = i < n4 ? ldg_stream4(img + (size_t)i * 4) : make_float4(NEG, NEG, NEG, NEG);
     }
   };
+  if (tid == 0) s_n = 0;
+  __syncthreads();
   int chunk = blockIdx.x;
   load_chunk(chunk);                   // the logits do not depend on the seed kernel: in flight before the wait
   pdl_wait();
   pdl_launch_dependents();
-  if (tid < 32) {
-    // Warp 0, under the latency of the loads above: the highest bin of the image's SAMPLE histogram whose
-    // suffix count reaches K -- two dependent 128/256-byte reads: the 64 coarse bins (32 fine bins each),
-    // then the 32 fine bins of the coarse bin that holds the K-th entry.  Lane 0 owns the highest bins.
+  // EVERY warp, under the latency of the loads above, on its own (no barrier, no broadcast: the warps of a CTA
+  // stay independent until the epilogue): the highest bin of the image's SAMPLE histogram whose suffix count
+  // reaches K -- two dependent 256/128-byte reads: the 64 coarse bins (32 fine bins each), then the 32 fine
+  // bins of the coarse bin that holds the K-th entry.  Lane 0 owns the highest bins.
+  unsigned int thr_ord = 0u;
+  bool mine = false;                                          // warp-uniform; false: this warp only joins the barrier
+  {
+    const int lane = tid & 31;
     const unsigned int* ph = phists + (size_t)b * kSeedHist;
-    const uint2 c2 = __ldcg(reinterpret_cast<const uint2*>(ph + kHistBins) + (31 - tid));   // coarse 62-2l, 63-2l
+    const unsigned int was_staged = *((volatile unsigned int*)&hdr->staged);                 // (an overflow elsewhere)
+    const uint2 c2 = __ldcg(reinterpret_cast<const uint2*>(ph + kHistBins) + (31 - lane));  // coarse 62-2l, 63-2l
     const unsigned int sum = c2.x + c2.y;
     unsigned int incl = sum;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
       const unsigned int t = __shfl_up_sync(0xffffffffu, incl, o);
-      if (tid >= o) incl += t;
+      if (lane >= o) incl += t;
     }
     const unsigned int excl = incl - sum;
     const unsigned int hit = __ballot_sync(0xffffffffu, excl < (unsigned)K && incl >= (unsigned)K);
@@ -658,36 +679,32 @@ decode_stream_kernel(const float* __restrict__ heat, int C, int H, int W, int n4
     if (hit) {
       const int src = __ffs(hit) - 1;
       const bool upper = excl + c2.y >= (unsigned)K;          // meaningful on lane src only
-      const int coarse = __shfl_sync(0xffffffffu, upper ? 63 - 2 * tid : 62 - 2 * tid, src);
+      const int coarse = __shfl_sync(0xffffffffu, upper ? 63 - 2 * lane : 62 - 2 * lane, src);
       const unsigned int before = __shfl_sync(0xffffffffu, upper ? excl : excl + c2.y, src);
-      const unsigned int f = __ldcg(ph + coarse * 32 + (31 - tid));                          // descending by lane
+      const unsigned int f = __ldcg(ph + coarse * 32 + (31 - lane));                         // descending by lane
       unsigned int fi = f;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
         const unsigned int t = __shfl_up_sync(0xffffffffu, fi, o);
-        if (tid >= o) fi += t;
+        if (lane >= o) fi += t;
       }
       const unsigned int hit2 = __ballot_sync(0xffffffffu, before + fi - f < (unsigned)K && before + fi >= (unsigned)K);
       if (hit2) ord = (unsigned int)(coarse * 32 + 31 - (__ffs(hit2) - 1)) << kHistShift;
     }
-    if (tid == 0) {
-      s_n = 0; s_thr = ord;
-      s_staged = ord ? *((volatile unsigned int*)&hdr->staged) : 1u;
+    if (ord == 0u) {                                          // no usable sample bound: the staged path owns the image
+      if (tid == 0 && blockIdx.x == 0) hdr->staged = 1u;
+    } else {
+      thr_ord = ord;
+      mine = !__shfl_sync(0xffffffffu, was_staged, 0);
+      if (tid == 0 && blockIdx.x == 0) atomicMax(&hdr->thr_ord, ord);   // head start for the staged path after an overflow
     }
   }
-  __syncthreads();
-  if (s_staged) {                                             // CTA-uniform: the staged path owns this image
-    if (tid == 0 && blockIdx.x == 0) hdr->staged = 1u;        // (no usable sample bound, or an overflow elsewhere)
-    return;
-  }
-  if (tid == 0 && blockIdx.x == 0) atomicMax(&hdr->thr_ord, s_thr);   // head start for the staged path after an overflow
   const bool logits = flags & CTDET_DECODE_LOGITS;
   const bool no_nms = flags & CTDET_DECODE_NO_NMS;
-  const uint32_t thr_ord = s_thr;
   const float thv = fmaxf(ordered_to_float(thr_ord), logits ? -3.402823466e38f : __int_as_float(1));
   unsigned int* shist = shists + (size_t)b * kHistBins;
   u64* skeys = skeys_all + (size_t)b * kStreamCap;
-  for (;;) {
+  while (mine) {
     const int base = chunk * kStrChunk + tid;
 #pragma unroll
     for (int u = 0; u < kStrU; ++u) {

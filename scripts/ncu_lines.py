@@ -19,5 +19,5 @@ for r in csv.reader(out.splitlines()):
     a = agg.setdefault(k, [0, 0]); a[0] += e; a[1] += s
 tot = sum(a[0] for a in agg.values()) or 1; tots = sum(a[1] for a in agg.values()) or 1
 print("total warp-instr", tot, "samples", tots)
-for k, a in sorted(agg.items(), key=lambda kv: -kv[1][0])[:int(sys.argv[4]) if len(sys.argv) > 4 else 40]:
+for k, a in sorted(agg.items(), key=lambda kv: -kv[1][int(__import__("os").environ.get("SORTCOL","0"))])[:int(sys.argv[4]) if len(sys.argv) > 4 else 40]:
     print("%5.1f%% inst %5.1f%% samp  %s:%s  %s" % (100 * a[0] / tot, 100 * a[1] / tots, k[0], k[1], k[2]))

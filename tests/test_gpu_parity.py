@@ -391,6 +391,57 @@ def test_decode_odd_width():
         assert np.array_equal(g.cpu().numpy(), r)
 
 
+def test_decode_stream_path_handover_and_workspace_reuse():
+    """The streaming decode (seed bound + flat sweep) and its hand-over to the staged kernel in ONE batch:
+    image 0/2 = random logits (streaming path), image 1 = what a trained model emits after the clamp of
+    centernet.py:161 -- a 1e-4 plateau with a few real peaks, so fewer than K peaks stand above the floor,
+    the sampled bound lands on the plateau and the key list overflows -> staged path.  Then the same
+    workspace is reused with the roles swapped (it must have been left clean)."""
+    from detectron2_centernet_b200 import decode as D
+    B, C, H, W, K = 3, 80, 128, 128, 100
+    hm, wh, reg = S.make_head_outputs(4321, B, C, H, W)
+    heat = S.sigmoid_clamp(hm)
+    rng = np.random.default_rng(5)
+    plateau = np.full((C, H, W), 1e-4, np.float32)
+    for _ in range(30):
+        plateau[rng.integers(C), rng.integers(H), rng.integers(W)] = rng.uniform(0.1, 0.9)
+    for order in ((0, 1, 0), (1, 0, 1)):
+        h = heat.copy()
+        for b, flat in enumerate(order):
+            if flat:
+                h[b] = plateau
+        out = D.ctdet_decode_batch(*_cuda(h, wh, reg), down_ratio=4, K=K)
+        torch.cuda.synchronize()
+        ref = O.decode(h, wh, reg, 4, K)
+        for g, r in zip(out, ref):
+            assert np.array_equal(g.cpu().numpy(), r)
+    # logits mode on the same workspace shape, twice (second call sees whatever the first left behind)
+    t = _cuda(hm, wh, reg)
+    ref = O.decode(hm, wh, reg, 4, K, logits=True)
+    for _ in range(2):
+        out = D.ctdet_decode_batch(*t, down_ratio=4, K=K, logits=True)
+        for g, r in zip((out[0], out[2], out[3]), (ref[0], ref[2], ref[3])):
+            assert np.array_equal(g.cpu().numpy(), r)
+
+
+def test_decode_stream_path_no_nms_and_small_maps():
+    """nms=False (the bare _topk) through the streaming path, and maps too small for a sample (H < 6)."""
+    from detectron2_centernet_b200 import decode as D
+    B, C, H, W, K = 2, 8, 72, 64, 100
+    hm, wh, reg = S.make_head_outputs(99, B, C, H, W)
+    out = D.ctdet_decode_batch(*_cuda(hm, wh, reg), down_ratio=4, K=K, logits=True, nms=False)
+    flat = torch.from_numpy(hm).view(B, -1)
+    top = torch.topk(flat, K)
+    assert np.array_equal((out[3].cpu() + out[2].cpu().long() * (H * W)).numpy(), top.indices.numpy())
+    B, C, H, W, K = 2, 4, 5, 16, 10
+    hm, wh, reg = S.make_head_outputs(98, B, C, H, W)
+    heat = S.sigmoid_clamp(hm)
+    out = D.ctdet_decode_batch(*_cuda(heat, wh, reg), down_ratio=4, K=K)
+    ref = O.decode(heat, wh, reg, 4, K)
+    for g, r in zip(out, ref):
+        assert np.array_equal(g.cpu().numpy(), r)
+
+
 def test_nms_topk_gather_dropins(inputs):
     from detectron2_centernet_b200 import decode as D
     bl, cl, hm, wh, reg, (B, C, H, W, K, full) = inputs("dense_small")
