@@ -12,7 +12,45 @@ import math
 import torch
 from torch import nn
 
+from . import _lib
 from .deform_conv import DeformConvV2
+
+
+def _is_ida_up(up):
+    """True for the module IDAUp builds at dla.py:166-168: depth-wise ConvTranspose2d(o, o, 2f, stride f,
+    padding f // 2), no bias, f a power of two."""
+    if not isinstance(up, nn.ConvTranspose2d) or up.bias is not None:
+        return False
+    f = up.stride[0]
+    return (up.stride == (f, f) and up.kernel_size == (2 * f, 2 * f) and up.padding == (f // 2, f // 2) and
+            up.output_padding == (0, 0) and up.dilation == (1, 1) and up.groups == up.in_channels == up.out_channels and
+            2 <= f <= 16 and (f & (f - 1)) == 0)
+
+
+def upsample_add(up, x, skip=None):
+    """`up(x) + skip` of IDAUp.forward (dla.py:175-177) in one pass over HBM (C ABI ctdet_upsample_add).
+    Used when no gradient is needed (eval / no_grad); with autograd, or for a module that is not IDAUp's
+    up-sampling, the reference's own two torch ops run (the up-sampling weights are learnable)."""
+    fused = (x.is_cuda and x.dtype == torch.float32 and _is_ida_up(up) and up.weight.dtype == torch.float32 and
+             not (torch.is_grad_enabled() and (x.requires_grad or up.weight.requires_grad or
+                                               (skip is not None and skip.requires_grad))))
+    if not fused:
+        y = up(x)
+        return y if skip is None else y + skip
+    lib = _lib.load()
+    f = up.stride[0]
+    x = _lib.f32c(x, "x")
+    B, C, h, w = x.shape
+    if skip is not None:
+        skip = _lib.f32c(skip, "skip")
+        if tuple(skip.shape) != (B, C, h * f, w * f):
+            raise RuntimeError("skip must be [%d,%d,%d,%d], got %s" % (B, C, h * f, w * f, tuple(skip.shape)))
+    out = torch.empty((B, C, h * f, w * f), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        rc = lib.ctdet_upsample_add(_lib.ptr(x), _lib.ptr(_lib.f32c(up.weight.detach(), "weight")), _lib.ptr(skip),
+                                    B, C, h, w, f, _lib.ptr(out), _lib.stream_ptr(x.device))
+    _lib.check(rc, "ctdet_upsample_add")
+    return out
 
 
 def fill_up_weights(up):
@@ -45,8 +83,8 @@ class IDAUp(nn.Module):
     def forward(self, layers, startp, endp):
         for i in range(startp + 1, endp):
             k = i - startp
-            x = getattr(self, "up_%d" % k)(getattr(self, "proj_%d" % k)(layers[i]))
-            layers[i] = getattr(self, "node_%d" % k)(x + layers[i - 1])
+            x = upsample_add(getattr(self, "up_%d" % k), getattr(self, "proj_%d" % k)(layers[i]), layers[i - 1])
+            layers[i] = getattr(self, "node_%d" % k)(x)
 
 
 class DLAUp(nn.Module):

@@ -22,6 +22,8 @@
  *                        detectron2/modeling/postprocessing.py:10-74 detector_postprocess (scale, clip, nonempty)
  *   ctdet_preprocess     centernet.py:173-184 CenterNet.preprocess_image (x/255, normalise) and
  *                        detectron2/structures/image_list.py:58-130 ImageList.from_tensors (pad + batch)
+ *   ctdet_upsample_add   detectron2/modeling/backbone/dla.py:166-168 `up_i` (depth-wise ConvTranspose2d) applied at
+ *                        :175 and the `+ layers[i - 1]` of :176-177 (IDAUp.forward)
  *   dcnv2_forward        detectron2/layers/csrc/deformable/deform_conv.h:262 modulated_deform_conv_forward
  *                        -> deform_conv_cuda.cu:804 modulated_deform_conv_cuda_forward
  *                        (im2col kernel deform_conv_cuda_kernel.cu:786 + addmm_ :904 + bias :924)
@@ -178,6 +180,13 @@ int ctdet_postprocess(float* boxes, float* scores, int32_t* classes, const int32
 int ctdet_preprocess(const void* const* images, const int32_t* sizes_hw, int dtype,
                      int B, int C, int Hp, int Wp, const float* mean, const float* std,
                      float* out, ctdet_stream_t stream);
+
+/* IDAUp up-sampling + skip add (modeling/backbone/dla.py:166-168, :175-177):
+ *   out = ConvTranspose2d(C, C, 2f, stride=f, padding=f/2, groups=C, bias=False)(x) + skip
+ *   x f32 [B,C,h,w]   weight f32 [C,1,2f,2f] (the module's weight: bilinear at init, learnable)
+ *   skip f32 [B,C,f*h,f*w] or NULL (plain up-sampling)   out f32 [B,C,f*h,f*w]   f in {2,4,8,16} */
+int ctdet_upsample_add(const float* x, const float* weight, const float* skip, int B, int C, int h, int w,
+                       int f, float* out, ctdet_stream_t stream);
 
 /* ---------------------------------------------------------------- DCNv2 forward ----------
  * Modulated deformable 3x3 convolution, replaces modulated_deform_conv_forward

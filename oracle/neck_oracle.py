@@ -88,3 +88,13 @@ def randomize(module, seed):
             b.copy_(torch.randn(b.shape, generator=g) * 0.1)
         elif name.endswith("running_var"):
             b.copy_(torch.rand(b.shape, generator=g) * 0.5 + 0.75)
+
+
+def upsample_add_ref(x, weight, skip, f):
+    """The two torch ops IDAUp.forward runs (dla.py:175-177) on CPU fp32: `up(x)` with
+    up = ConvTranspose2d(o, o, 2f, stride=f, padding=f//2, groups=o, bias=False) (dla.py:166-168), then `+ skip`.
+    TEST INFRASTRUCTURE: the checker of ctdet_upsample_add."""
+    import torch.nn.functional as F
+    y = F.conv_transpose2d(torch.as_tensor(x), torch.as_tensor(weight), None, stride=f, padding=f // 2,
+                           groups=weight.shape[0])
+    return y if skip is None else y + torch.as_tensor(skip)

@@ -163,3 +163,52 @@ def test_neck_train_mode_layers_match_fp32_neck():
     assert fa[0].grad is None and fa[1].grad is None       # strides 1 and 2 do not feed the neck (first_level = 2)
     assert all(f.grad is not None and bool(torch.isfinite(f.grad).all()) for f in fa[2:])
     assert all(p.grad is not None and bool(torch.isfinite(p.grad).all()) for p in ours.parameters() if p.requires_grad)
+
+
+def test_upsample_add_cpu_and_autograd_use_the_reference_ops():
+    """No GPU / gradients wanted: `upsample_add` is literally `up(x) + skip` (dla.py:175-177)."""
+    from detectron2_centernet_b200 import neck as N
+    from oracle import neck_oracle as NO
+    torch.manual_seed(3)
+    up = torch.nn.ConvTranspose2d(8, 8, 4, stride=2, padding=1, groups=8, bias=False)
+    N.fill_up_weights(up)
+    x, skip = torch.randn(2, 8, 5, 7), torch.randn(2, 8, 10, 14)
+    with torch.no_grad():
+        assert torch.equal(N.upsample_add(up, x, skip), up(x) + skip)
+        assert torch.equal(N.upsample_add(up, x, skip), NO.upsample_add_ref(x, up.weight, skip, 2))
+    assert N._is_ida_up(up) and not N._is_ida_up(torch.nn.ConvTranspose2d(8, 8, 4, stride=2, padding=1, bias=False))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("f,shape", [(2, (2, 64, 64, 64)), (2, (3, 24, 7, 9)), (4, (2, 64, 16, 16)), (8, (1, 64, 8, 8)),
+                                      (2, (1, 5, 3, 3)), (16, (1, 3, 2, 5))])
+def test_upsample_add_kernel_matches_reference_ops(f, shape):
+    """ctdet_upsample_add against torch's CPU conv_transpose2d + add: learnable (random) weights and the
+    bilinear initialisation, with and without a skip tensor, odd sizes (scalar path).  fp32, 4 products per output in
+    a different order than cuDNN / the CPU kernel: tolerance 2e-6 of the output scale."""
+    from detectron2_centernet_b200 import neck as N
+    from oracle import neck_oracle as NO
+    B, C, h, w = shape
+    g = torch.Generator().manual_seed(100 + f + h)
+    x = torch.randn(shape, generator=g)
+    skip = torch.randn((B, C, h * f, w * f), generator=g)
+    up = torch.nn.ConvTranspose2d(C, C, 2 * f, stride=f, padding=f // 2, groups=C, bias=False)
+    for init in ("bilinear", "random"):
+        if init == "bilinear":
+            N.fill_up_weights(up)
+        else:
+            up.weight.data = torch.randn(up.weight.shape, generator=g)
+        up_d = torch.nn.ConvTranspose2d(C, C, 2 * f, stride=f, padding=f // 2, groups=C, bias=False).to("cuda:0")
+        up_d.weight.data.copy_(up.weight.data)
+        with torch.no_grad():
+            for sk in (skip, None):
+                ref = NO.upsample_add_ref(x, up.weight.data, sk, f)
+                got = N.upsample_add(up_d, x.to("cuda:0"), None if sk is None else sk.to("cuda:0")).cpu()
+                assert got.shape == ref.shape
+                tol = 2e-6 * float(ref.abs().max())
+                assert float((got - ref).abs().max()) <= tol, (init, sk is None, float((got - ref).abs().max()), tol)
+    # with autograd the torch ops run and gradients flow to the up-sampling weights
+    xg = x.to("cuda:0").requires_grad_(True)
+    y = N.upsample_add(up_d, xg, skip.to("cuda:0"))
+    y.sum().backward()
+    assert xg.grad is not None and up_d.weight.grad is not None
