@@ -514,7 +514,8 @@ constexpr int kSeedHist = kHistBins + kHistBins / 32;   // per image: the 2048 f
 
 __global__ void __launch_bounds__(kSeedThreads)
 decode_seed_kernel(const float* __restrict__ heat, int C, int H, int W, int K, int flags,
-                   int groups, FastDiv div_strips, FastDiv div_groups, unsigned int* __restrict__ phists) {
+                   int groups, FastDiv div_strips, FastDiv div_groups, unsigned int* __restrict__ phists,
+                   unsigned int* __restrict__ pvals_all, int n_vals) {
   pdl_launch_dependents();             // the sweep may be scheduled as soon as every CTA of this grid runs
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int b = blockIdx.y;
@@ -524,6 +525,7 @@ decode_seed_kernel(const float* __restrict__ heat, int C, int H, int W, int K, i
   const float NEG = -__int_as_float(0x7f800000);
   const float floor_f = logits ? -3.402823466e38f : __int_as_float(1);
   unsigned int* phist = phists + (size_t)b * kSeedHist;
+  unsigned int* pvals = pvals_all + (size_t)b * n_vals;  // [items][kSeedRows] ordered scores, 0 = no peak
 
   const int items = C * groups * strips;
   for (int item = blockIdx.x * kSeedWarps + warp; item < items; item += gridDim.x * kSeedWarps) {
@@ -571,10 +573,14 @@ decode_seed_kernel(const float* __restrict__ heat, int C, int H, int W, int K, i
     float mine = NEG;
 #pragma unroll
     for (int t = 0; t < kSeedRows; ++t) if (lane == t) mine = best[t];
-    if (lane < kSeedRows && mine >= floor_f) {
-      const uint32_t bin = float_to_ordered(mine) >> kHistShift;
-      atomicAdd(phist + bin, 1u);
-      atomicAdd(phist + kHistBins + (bin >> 5), 1u);
+    if (lane < kSeedRows) {
+      const bool has = mine >= floor_f;
+      const uint32_t ord = has ? float_to_ordered(mine) : 0u;
+      pvals[item * kSeedRows + lane] = ord;                  // the sample itself, for the rare refinement below 11 bits
+      if (has) {
+        atomicAdd(phist + (ord >> kHistShift), 1u);
+        atomicAdd(phist + kHistBins + (ord >> (kHistShift + 5)), 1u);
+      }
     }
   }
 }
@@ -631,9 +637,10 @@ __device__ __forceinline__ void stream_test_cell(const float* __restrict__ img, 
 __global__ void __launch_bounds__(kStrThreads, 4)
 decode_stream_kernel(const float* __restrict__ heat, int C, int H, int W, int n4, int chunks, int flags,
                      FastDiv div_hw, FastDiv div_w, int K, DecodeHeader* __restrict__ hdrs,
-                     const unsigned int* __restrict__ phists,
+                     const unsigned int* __restrict__ phists, const unsigned int* __restrict__ pvals_all, int n_vals,
                      unsigned int* __restrict__ shists, u64* __restrict__ skeys_all) {
   __shared__ uint32_t s_list[kStrList];
+  __shared__ unsigned int s_sub[kStrThreads / 32][32];        // per-warp 32-bin histogram of the refinement
   __shared__ int s_n;
   const int tid = threadIdx.x;
   const int b = blockIdx.y;
@@ -689,7 +696,49 @@ decode_stream_kernel(const float* __restrict__ heat, int C, int H, int W, int n4
         if (lane >= o) fi += t;
       }
       const unsigned int hit2 = __ballot_sync(0xffffffffu, before + fi - f < (unsigned)K && before + fi >= (unsigned)K);
-      if (hit2) ord = (unsigned int)(coarse * 32 + 31 - (__ffs(hit2) - 1)) << kHistShift;
+      if (hit2) {
+        const int l2 = __ffs(hit2) - 1;
+        ord = (unsigned int)(coarse * 32 + 31 - l2) << kHistShift;
+        // Concentrated scores (e.g. a random-init head: every logit within +-0.3 of the -2.19 bias) put most of the
+        // sample into this one quarter-octave bin, and its lower edge would pass the whole image.  Then refine
+        // on the sample itself, 5 more bits per round: a per-warp 32-bin histogram of the samples that share the
+        // prefix found so far, same suffix-count rule.  Still a valid lower bound: >= K samples are >= it.
+        unsigned int in_bin = __shfl_sync(0xffffffffu, f, l2);
+        unsigned int need = (unsigned)K - __shfl_sync(0xffffffffu, before + fi - f, l2);
+        unsigned int prefix = ord >> kHistShift;
+        int shift = kHistShift;
+        const unsigned int* pv = pvals_all + (size_t)b * n_vals;
+        unsigned int* sub = s_sub[tid >> 5];
+        // only when the bin really is crowded (a normal image has n_vals / 30 or so samples in it, and every warp
+        // of every CTA runs this code): then keep going until the sub-bin is small
+        const unsigned int crowded = max(2u * (unsigned)K, (unsigned)n_vals / 8u);
+        if (in_bin > crowded)
+        while (in_bin > 24u && shift >= 5) {
+          sub[lane] = 0u;
+          __syncwarp();
+          for (int i = lane; i < n_vals; i += 32) {
+            const unsigned int v = __ldcg(pv + i);
+            if ((v >> shift) == prefix) atomicAdd(&sub[(v >> (shift - 5)) & 31u], 1u);
+          }
+          __syncwarp();
+          const unsigned int cnt = sub[31 - lane];                // descending by lane
+          unsigned int ci = cnt;
+#pragma unroll
+          for (int o = 1; o < 32; o <<= 1) {
+            const unsigned int t = __shfl_up_sync(0xffffffffu, ci, o);
+            if (lane >= o) ci += t;
+          }
+          const unsigned int h3 = __ballot_sync(0xffffffffu, ci - cnt < need && ci >= need);
+          __syncwarp();
+          if (!h3) break;                                          // (cannot happen: the bin holds >= need samples)
+          const int l3 = __ffs(h3) - 1;
+          prefix = (prefix << 5) | (unsigned)(31 - l3);
+          shift -= 5;
+          need -= __shfl_sync(0xffffffffu, ci - cnt, l3);
+          in_bin = __shfl_sync(0xffffffffu, cnt, l3);
+        }
+        ord = prefix << shift;
+      }
     }
     if (ord == 0u) {                                          // no usable sample bound: the staged path owns the image
       if (tid == 0 && blockIdx.x == 0) hdr->staged = 1u;
@@ -928,8 +977,8 @@ struct DecodePlan {
   size_t smem, keys_per_image, header_bytes, hist_bytes, total_bytes;
   // streaming path
   bool stream;
-  int seed_groups, seed_ctas, stream_ctas, n4;
-  size_t skeys_bytes, phist_bytes;
+  int seed_groups, seed_ctas, stream_ctas, n4, seed_vals;
+  size_t skeys_bytes, phist_bytes, pvals_bytes;
   int stream_chunks;
 };
 
@@ -967,12 +1016,20 @@ static DecodePlan make_plan(int B, int C, int H, int W, int K) {
   {
     const int items = C * p.seed_groups * strips;               // one warp-item = 6 row segments of 512 B
     p.seed_ctas = (items + kSeedWarps - 1) / kSeedWarps;
+    p.seed_vals = items * kSeedRows;
     if (p.seed_ctas < 1) p.seed_ctas = 1;
   }
   p.skeys_bytes = p.stream ? (size_t)B * kStreamCap * sizeof(u64) : 0;
+  // sample histograms (zero on entry, left zero: a fixed stride per image, whatever the map shape, because calls
+  // of different shapes share one workspace), then the samples themselves (rewritten by every call)
   p.phist_bytes = (((size_t)B * kSeedHist * sizeof(unsigned int)) + 255) / 256 * 256;
-  // layout: headers | staged histograms | streaming histograms | sample histograms | streaming keys | staged keys
-  p.total_bytes = p.header_bytes + p.hist_bytes * (p.stream ? 2 : 1) + (p.stream ? p.phist_bytes : 0) + p.skeys_bytes +
+  p.pvals_bytes = (((size_t)B * p.seed_vals * sizeof(unsigned int)) + 255) / 256 * 256;
+  // layout: headers | staged histograms | streaming histograms | sample histograms | samples | streaming keys | staged keys
+  // The zero-on-entry regions (headers, the three histogram blocks) come first, at offsets that depend on B only:
+  // calls of different map shapes -- with or without the streaming path -- share one workspace per B, and the keys
+  // of one layout must never land in what another layout expects to be zero.
+  if (!p.stream) { p.pvals_bytes = 0; p.skeys_bytes = 0; }
+  p.total_bytes = p.header_bytes + 2 * p.hist_bytes + p.phist_bytes + p.pvals_bytes + p.skeys_bytes +
                   (size_t)B * p.keys_per_image * sizeof(u64);
   return p;
 }
@@ -1011,20 +1068,22 @@ extern "C" int ctdet_decode(const float* heat, const float* wh, const float* reg
   unsigned char* base = reinterpret_cast<unsigned char*>(workspace);
   DecodeHeader* hdr = reinterpret_cast<DecodeHeader*>(base);
   unsigned int* ghist = reinterpret_cast<unsigned int*>(base + p.header_bytes);
-  unsigned int* shist = p.stream ? reinterpret_cast<unsigned int*>(base + p.header_bytes + p.hist_bytes) : nullptr;
-  unsigned int* phist = p.stream ? reinterpret_cast<unsigned int*>(base + p.header_bytes + 2 * p.hist_bytes) : nullptr;
-  u64* skeys = p.stream ? reinterpret_cast<u64*>(base + p.header_bytes + 2 * p.hist_bytes + p.phist_bytes) : nullptr;
-  u64* keys = reinterpret_cast<u64*>(base + p.header_bytes + p.hist_bytes * (p.stream ? 2 : 1) +
-                                     (p.stream ? p.phist_bytes : 0) + p.skeys_bytes);
+  unsigned char* q = base + p.header_bytes + p.hist_bytes;
+  unsigned int* shist = reinterpret_cast<unsigned int*>(q); q += p.hist_bytes;
+  unsigned int* phist = reinterpret_cast<unsigned int*>(q); q += p.phist_bytes;
+  unsigned int* pvals = reinterpret_cast<unsigned int*>(q); q += p.pvals_bytes;
+  u64* skeys = reinterpret_cast<u64*>(q); q += p.skeys_bytes;
+  u64* keys = reinterpret_cast<u64*>(q);
+  if (!p.stream) { shist = nullptr; phist = nullptr; pvals = nullptr; skeys = nullptr; }
   if (B > 65535 || C > 65535) return CTDET_EINVAL;
   int rc;
   if (p.stream) {
     decode_seed_kernel<<<dim3(p.seed_ctas, B), kSeedThreads, 0, st>>>(
-        heat, C, H, W, K, flags, p.seed_groups, FastDiv((uint32_t)p.strips), FastDiv((uint32_t)p.seed_groups), phist);
+        heat, C, H, W, K, flags, p.seed_groups, FastDiv((uint32_t)p.strips), FastDiv((uint32_t)p.seed_groups), phist, pvals, p.seed_vals);
     if ((rc = check_launch())) return rc;
     cudaError_t e = launch_pdl(decode_stream_kernel, dim3(p.stream_ctas, B), dim3(kStrThreads), 0, st,
                                heat, C, H, W, p.n4, p.stream_chunks, flags, FastDiv((uint32_t)(H * W)),
-                               FastDiv((uint32_t)W), K, hdr, (const unsigned int*)phist, shist, skeys);
+                               FastDiv((uint32_t)W), K, hdr, (const unsigned int*)phist, (const unsigned int*)pvals, p.seed_vals, shist, skeys);
     if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
     if ((rc = check_launch())) return rc;
   }

@@ -140,8 +140,9 @@ int ctdet_scale_grad(float* d, size_t n, const float* g, ctdet_stream_t stream);
  * Tie rule: higher score first, then lower flat index c*H*W + y*W + x.  Requires K <= H*W,
  * K <= CTDET_MAX_K, C*H*W < 2^31.
  * workspace: ctdet_decode_workspace_bytes() bytes, 8-byte aligned, zero-filled ONCE by the caller
- * before first use (the first 256*ceil(8B/256) bytes hold per-image headers that every call
- * leaves zeroed); one workspace per stream. */
+ * before first use: it starts with per-image headers and histograms that every call leaves
+ * zeroed, at offsets that depend on B only, so one (large enough) workspace may serve calls of
+ * different C/H/W/K with the same B; one workspace per stream. */
 #define CTDET_DECODE_LOGITS 1
 #define CTDET_DECODE_CAT_SPEC_WH 2
 #define CTDET_DECODE_NO_NMS 4 /* rank every cell (the bare _topk of centernet.py:408) */

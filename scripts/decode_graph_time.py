@@ -8,11 +8,12 @@ from detectron2_centernet_b200 import decode as D
 dev = 'cuda:0'
 C, K = 80, 100
 flush = torch.empty(512 * 1024 * 1024 // 4, device=dev)
-cases = [(32, 128, True), (64, 128, True), (32, 128, False), (8, 256, True)]
+cases = [(32, 128, True), (64, 128, True), (32, 128, False), (8, 256, True), (32, 128, 'tight')]
 for B, H, logits in cases:
     W = H
     g = torch.Generator(device=dev).manual_seed(1)
-    hm = torch.randn((B, C, H, W), device=dev, generator=g) * 1.5 - 2.19
+    hm = torch.randn((B, C, H, W), device=dev, generator=g) * (0.1 if logits == 'tight' else 1.5) - 2.19
+    if logits == 'tight': logits = True   # a random-init head: logits within +-0.3 of the bias
     if not logits:
         hm = torch.clamp(torch.sigmoid(hm), 1e-4, 1 - 1e-4)
     wh = torch.rand((B, 2, H, W), device=dev, generator=g) * 64

@@ -440,6 +440,36 @@ def test_decode_stream_path_no_nms_and_small_maps():
     ref = O.decode(heat, wh, reg, 4, K)
     for g, r in zip(out, ref):
         assert np.array_equal(g.cpu().numpy(), r)
+    # the workspace is shared by every shape with the same B: a staged-only call (above) must leave the regions
+    # the streaming layout expects to be zero untouched (regression: its key list used to overlap them)
+    B, C, H, W, K = 2, 8, 72, 64, 100
+    hm, wh, reg = S.make_head_outputs(97, B, C, H, W)
+    out = D.ctdet_decode_batch(*_cuda(hm, wh, reg), down_ratio=4, K=K, logits=True)
+    ref = O.decode(hm, wh, reg, 4, K, logits=True)
+    assert np.array_equal(out[2].cpu().numpy(), ref[2]) and np.array_equal(out[3].cpu().numpy(), ref[3])
+    assert np.array_equal(out[0].cpu().numpy(), ref[0])
+
+
+def test_decode_concentrated_logits_refined_seed_bound():
+    """A random-init head (BASELINE config 5): every logit within a fraction of the -2.19 bias, i.e. the whole
+    image inside ONE quarter-octave bin of the bound histogram.  The streaming path refines its sample bound
+    below 11 bits instead of handing the image to the staged kernel; results stay exact."""
+    from detectron2_centernet_b200 import decode as D
+    B, C, H, W, K = 2, 80, 128, 128, 100
+    rng = np.random.default_rng(11)
+    hm = (-2.19 + 0.1 * rng.standard_normal((B, C, H, W))).astype(np.float32)
+    hm[1] = (-2.19 + 1e-3 * rng.standard_normal((C, H, W))).astype(np.float32)     # even tighter
+    wh = rng.uniform(0, 64, (B, 2, H, W)).astype(np.float32)
+    reg = rng.uniform(0, 1, (B, 2, H, W)).astype(np.float32)
+    out = D.ctdet_decode_batch(*_cuda(hm, wh, reg), down_ratio=4, K=K, logits=True)
+    ref = O.decode(hm, wh, reg, 4, K, logits=True)
+    assert np.array_equal(out[2].cpu().numpy(), ref[2]) and np.array_equal(out[3].cpu().numpy(), ref[3])
+    assert np.array_equal(out[0].cpu().numpy(), ref[0])
+    heat = S.sigmoid_clamp(hm)
+    out = D.ctdet_decode_batch(*_cuda(heat, wh, reg), down_ratio=4, K=K)
+    ref = O.decode(heat, wh, reg, 4, K)
+    for g, r in zip(out, ref):
+        assert np.array_equal(g.cpu().numpy(), r)
 
 
 def test_nms_topk_gather_dropins(inputs):
