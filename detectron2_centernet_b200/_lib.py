@@ -43,6 +43,8 @@ SIGNATURES = {
     "dcnv2_workspace_bytes": (c_size_t, [c_int] * 5),
     "dcnv2_forward": (c_int, [c_void_p] * 6 + [c_int] * 15 + [c_void_p, c_void_p, c_int] +
                       [c_void_p, c_size_t, c_void_p]),
+    "dcnv2_forward_raw27": (c_int, [c_void_p] * 6 + [c_int] * 8 + [c_void_p, c_void_p, c_int] +
+                            [c_void_p, c_size_t, c_void_p]),
     "dcnv2_backward_workspace_bytes": (c_size_t, [c_int] * 7),
     "dcnv2_backward": (c_int, [c_void_p] * 10 + [c_int] * 16 + [c_void_p, c_size_t, c_void_p]),
 }

@@ -289,13 +289,15 @@ extern "C" size_t dcnv2_workspace_bytes(int B, int Cin, int H, int W, int Cout) 
 
 using ctdet::dcn_env_int;
 
-extern "C" int dcnv2_forward(const float* input, const float* weight, const float* bias,
-                             const float* offset, const float* mask, float* output,
-                             int B, int Cin, int H, int W, int Cout, int kernel_h, int kernel_w,
-                             int stride_h, int stride_w, int pad_h, int pad_w, int dilation_h,
-                             int dilation_w, int group, int deformable_group,
-                             const float* scale, const float* shift, int flags,
-                             void* workspace, size_t workspace_bytes, ctdet_stream_t stream) {
+// raw27 != 0: `offset` is the raw [B,27,Ho,Wo] output of conv_offset_mask (offsets = its channels 0..17 as they
+// are, mask = sigmoid of channels 18..26), `om_bias` its bias or null; `mask` is ignored.
+static int dcn_forward_impl(const float* input, const float* weight, const float* bias,
+                            const float* offset, const float* mask, const float* om_bias, int raw27, float* output,
+                            int B, int Cin, int H, int W, int Cout, int kernel_h, int kernel_w,
+                            int stride_h, int stride_w, int pad_h, int pad_w, int dilation_h,
+                            int dilation_w, int group, int deformable_group,
+                            const float* scale, const float* shift, int flags,
+                            void* workspace, size_t workspace_bytes, ctdet_stream_t stream) {
   using namespace ctdet;
   if (B < 0 || Cin <= 0 || H <= 0 || W <= 0 || Cout <= 0) return CTDET_EINVAL;
   if (flags & ~(DCN_FLAG_RELU | DCN_FLAG_FP32_BLEND)) return CTDET_EINVAL;
@@ -310,7 +312,7 @@ extern "C" int dcnv2_forward(const float* input, const float* weight, const floa
   const int Wo = (W + 2 * pad_w - (dilation_w * 2 + 1)) / stride_w + 1;
   if (Ho <= 0 || Wo <= 0) return CTDET_EINVAL;
   if (B == 0) return CTDET_OK;
-  if (!input || !weight || !offset || !mask || !output || !workspace) return CTDET_ENULL;
+  if (!input || !weight || !offset || (!mask && !raw27) || !output || !workspace) return CTDET_ENULL;
   if (workspace_bytes < dcnv2_workspace_bytes(B, Cin, H, W, Cout)) return CTDET_EWORKSPACE;
   if (reinterpret_cast<uintptr_t>(workspace) & 15u) return CTDET_EALIGN;
   if ((size_t)H * W >= ((size_t)1 << 31) / (size_t)Cin) return CTDET_EINVAL;     // 32-bit element offsets per image
@@ -331,6 +333,12 @@ extern "C" int dcnv2_forward(const float* input, const float* weight, const floa
 
   DcnParams prm;
   prm.xh = xh; prm.offset = offset; prm.mask = mask; prm.wk = wk; prm.bias = bias;
+  prm.off_bstride = 18 * Ho * Wo; prm.mask_bstride = 9 * Ho * Wo; prm.mask_logit = 0; prm.om_bias = nullptr;
+  if (raw27) {
+    if ((long long)27 * Ho * Wo > 0x7fffffffLL) return CTDET_EINVAL;
+    prm.mask = offset + (size_t)18 * Ho * Wo;
+    prm.off_bstride = prm.mask_bstride = 27 * Ho * Wo; prm.mask_logit = 1; prm.om_bias = om_bias;
+  }
   prm.scale = scale; prm.shift = shift; prm.y = output;
   prm.Cin = Cin; prm.H = H; prm.W = W; prm.Ho = Ho; prm.Wo = Wo; prm.Cout = Cout;
   prm.stride = stride_h; prm.pad = pad_h; prm.dil = dilation_h; prm.relu = (flags & DCN_FLAG_RELU) ? 1 : 0;
@@ -367,4 +375,26 @@ extern "C" int dcnv2_forward(const float* input, const float* weight, const floa
   const unsigned grid = (unsigned)(tiles < kNumSMs ? tiles : kNumSMs);
   kern<<<grid, threads, smem, st>>>(prm);
   return check_launch();
+}
+
+extern "C" int dcnv2_forward(const float* input, const float* weight, const float* bias,
+                             const float* offset, const float* mask, float* output,
+                             int B, int Cin, int H, int W, int Cout, int kernel_h, int kernel_w,
+                             int stride_h, int stride_w, int pad_h, int pad_w, int dilation_h,
+                             int dilation_w, int group, int deformable_group,
+                             const float* scale, const float* shift, int flags,
+                             void* workspace, size_t workspace_bytes, ctdet_stream_t stream) {
+  return dcn_forward_impl(input, weight, bias, offset, mask, nullptr, 0, output, B, Cin, H, W, Cout, kernel_h, kernel_w,
+                          stride_h, stride_w, pad_h, pad_w, dilation_h, dilation_w, group, deformable_group,
+                          scale, shift, flags, workspace, workspace_bytes, stream);
+}
+
+extern "C" int dcnv2_forward_raw27(const float* input, const float* weight, const float* bias,
+                                   const float* offset_mask, const float* offset_mask_bias, float* output,
+                                   int B, int Cin, int H, int W, int Cout, int stride, int pad, int dilation,
+                                   const float* scale, const float* shift, int flags,
+                                   void* workspace, size_t workspace_bytes, ctdet_stream_t stream) {
+  return dcn_forward_impl(input, weight, bias, offset_mask, nullptr, offset_mask_bias, 1, output, B, Cin, H, W, Cout, 3, 3,
+                          stride, stride, pad, pad, dilation, dilation, 1, 1, scale, shift, flags,
+                          workspace, workspace_bytes, stream);
 }

@@ -672,6 +672,7 @@ extern "C" int dcnv2_backward(const float* input, const float* weight, const flo
 
   DcnParams prm;
   prm.xh = xh; prm.offset = offset; prm.mask = mask; prm.wk = nullptr; prm.bias = nullptr;
+  prm.off_bstride = 18 * Ho * Wo; prm.mask_bstride = 9 * Ho * Wo; prm.mask_logit = 0; prm.om_bias = nullptr;
   prm.scale = nullptr; prm.shift = nullptr; prm.y = nullptr;
   prm.Cin = Cin; prm.H = H; prm.W = W; prm.Ho = Ho; prm.Wo = Wo; prm.Cout = Cout;
   prm.stride = stride_h; prm.pad = pad_h; prm.dil = dilation_h; prm.relu = 0;

@@ -141,6 +141,9 @@ struct DcnParams {
   float* y;                    // [B][Cout][Ho*Wo]
   int Cin, H, W, Ho, Wo, Cout, stride, pad, dil, relu, tiles_per_image, tiles_x, num_tiles, stages, mma_sleep, ld_sleep;
   int xw, ximg, xorg;
+  int off_bstride, mask_bstride;   // elements between images in offset / mask (18*P / 9*P, or 27*P for the raw conv output)
+  int mask_logit;                  // 1: mask holds logits (raw conv_offset_mask output): sigmoid applied here
+  const float* om_bias;            // [27] bias of conv_offset_mask to add (offset channels 0..17, mask 18..26) or null
   uint32_t tmem_cols;
 };
 
@@ -296,8 +299,8 @@ __device__ __forceinline__ void dcn_geometry_tile(const DcnParams& prm, int tile
   const int ho = tile_y * kTileH + (r >> 4), wo = tile_x * kTileW + (r & 15);
   const bool valid = ho < prm.Ho && wo < prm.Wo;
   const int p = valid ? ho * prm.Wo + wo : 0;
-  const float* offb = prm.offset + (size_t)b * 18 * P + p;
-  const float* mskb = prm.mask + (size_t)b * 9 * P + p;
+  const float* offb = prm.offset + (size_t)b * prm.off_bstride + p;
+  const float* mskb = prm.mask + (size_t)b * prm.mask_bstride + p;
   const int buf = it & 1;
   // all 27 loads first (one DRAM round trip, issued before the buffer is even free)
   float ov[18], mv[9];
@@ -305,6 +308,16 @@ __device__ __forceinline__ void dcn_geometry_tile(const DcnParams& prm, int tile
   for (int k = 0; k < 18; ++k) ov[k] = ldg_stream1(offb + (size_t)k * P);
 #pragma unroll
   for (int k = 0; k < 9; ++k) mv[k] = ldg_stream1(mskb + (size_t)k * P);
+  if (prm.om_bias != nullptr) {          // conv_offset_mask's bias, not added by the caller
+#pragma unroll
+    for (int k = 0; k < 18; ++k) ov[k] += __ldg(prm.om_bias + k);
+#pragma unroll
+    for (int k = 0; k < 9; ++k) mv[k] += __ldg(prm.om_bias + 18 + k);
+  }
+  if (prm.mask_logit) {                  // mask = sigmoid(third chunk), resnet.py:311
+#pragma unroll
+    for (int k = 0; k < 9; ++k) mv[k] = 1.f / (1.f + expf(-mv[k]));
+  }
   dcn_mbar_wait_relaxed(&bars.geo_empty[buf], (unsigned)(((it >> 1) & 1) ^ 1));
 #pragma unroll
   for (int t = 0; t < 9; ++t) {

@@ -70,6 +70,46 @@ def dcnv2_forward(input, offset, mask, weight, bias=None, stride=1, padding=0, d
     return out
 
 
+def dcnv2_forward_raw27(input, offset_mask, weight, bias=None, offset_mask_bias=None, stride=1, padding=1, dilation=1,
+                        scale=None, shift=None, relu=False, fp32_blend=False):
+    """dcnv2_forward fed by the RAW 27-channel output of `conv_offset_mask` (C ABI dcnv2_forward_raw27): the kernel
+    itself takes channels 0..17 as the offsets, applies the sigmoid to channels 18..26 (resnet.py:308-311) and adds
+    `offset_mask_bias` when given, so the chunk / cat / sigmoid / bias-add passes over HBM disappear."""
+    if not input.is_cuda:
+        raise NotImplementedError("Deformable Conv is not supported on CPUs!")    # deform_conv.py:203-204
+    lib = _lib.load()
+    input = _lib.f32c(input, "input")
+    weight = _lib.f32c(weight, "weight")
+    offset_mask = _lib.f32c(offset_mask, "offset_mask")
+    bias = None if bias is None else _lib.f32c(bias, "bias")
+    om_bias = None if offset_mask_bias is None else _lib.f32c(offset_mask_bias, "offset_mask_bias")
+    scale = None if scale is None else _lib.f32c(scale, "scale")
+    shift = None if shift is None else _lib.f32c(shift, "shift")
+    B, Cin, H, W = input.shape
+    Cout, cin_w, kh, kw = weight.shape
+    if (kh, kw) != (3, 3) or cin_w != Cin:
+        raise NotImplementedError("dcnv2_forward_raw27: 3x3, one group")
+    Ho = (H + 2 * padding - (dilation * 2 + 1)) // stride + 1
+    Wo = (W + 2 * padding - (dilation * 2 + 1)) // stride + 1
+    if tuple(offset_mask.shape) != (B, 27, Ho, Wo):
+        raise RuntimeError("offset_mask must be [%d,27,%d,%d], got %s" % (B, Ho, Wo, tuple(offset_mask.shape)))
+    if om_bias is not None and om_bias.numel() != 27:
+        raise RuntimeError("offset_mask_bias must have 27 elements")
+    out = torch.empty((B, Cout, Ho, Wo), dtype=torch.float32, device=input.device)
+    if out.numel() == 0:
+        return out
+    nbytes = lib.dcnv2_workspace_bytes(B, Cin, H, W, Cout)
+    ws = _workspace(max(nbytes, 16), input.device)
+    flags = (FLAG_RELU if relu else 0) | (FLAG_FP32_BLEND if fp32_blend else 0)
+    with torch.cuda.device(input.device):
+        rc = lib.dcnv2_forward_raw27(_lib.ptr(input), _lib.ptr(weight), _lib.ptr(bias), _lib.ptr(offset_mask),
+                                     _lib.ptr(om_bias), _lib.ptr(out), B, Cin, H, W, Cout, stride, padding, dilation,
+                                     _lib.ptr(scale), _lib.ptr(shift), flags,
+                                     _lib.ptr(ws), ctypes.c_size_t(ws.numel()), _lib.stream_ptr(input.device))
+    _lib.check(rc, "dcnv2_forward_raw27")
+    return out
+
+
 def dcnv2_backward(input, offset, mask, weight, grad_output, stride=1, padding=0, dilation=1, groups=1,
                    deformable_groups=1, with_bias=True, need_input_grads=True, need_weight_grad=True):
     """Low-level call: returns (grad_input, grad_offset, grad_mask, grad_weight, grad_bias); entries that were
@@ -198,11 +238,14 @@ class DeformConvV2(nn.Module):
     def forward(self, x):
         bn = self.actf[0]
         if not self.training and not torch.is_grad_enabled() and bn.track_running_stats:
-            offset, mask = self.conv.offset_mask(x)
             scale = bn.weight / torch.sqrt(bn.running_var + bn.eps)
             shift = bn.bias - bn.running_mean * scale
-            return dcnv2_forward(x, offset, mask, self.conv.weight, self.conv.bias, 1, 1, 1, 1, 1,
-                                 scale=scale, shift=shift, relu=True)
+            com = self.conv.conv_offset_mask
+            # the 27-channel convolution without its bias; bias, chunk / cat and the mask's sigmoid happen inside
+            # the DCN kernel's geometry stage
+            raw = torch.nn.functional.conv2d(x, com.weight, None, com.stride, com.padding, com.dilation, com.groups)
+            return dcnv2_forward_raw27(x, raw, self.conv.weight, self.conv.bias, com.bias, 1, 1, 1,
+                                       scale=scale, shift=shift, relu=True)
         return self.actf(self.conv(x))
 
 

@@ -215,6 +215,18 @@ int dcnv2_forward(const float* input, const float* weight, const float* bias,
                   int group, int deformable_group, const float* scale, const float* shift, int flags,
                   void* workspace, size_t workspace_bytes, ctdet_stream_t stream);
 
+/* dcnv2_forward fed by the RAW output of DCN.conv_offset_mask (the 27-channel 3x3 convolution of `input`):
+ * replaces the chunk / cat / sigmoid glue between that convolution and the contraction
+ * (modeling/backbone/resnet.py:308-311: o1, o2, mask = chunk(out, 3); offset = cat(o1, o2) -- i.e. channels
+ * 0..17 unchanged -- and mask = sigmoid(channels 18..26)) and, with offset_mask_bias, the convolution's bias add.
+ *   offset_mask f32 [B,27,Ho,Wo]   offset_mask_bias f32 [27] or NULL (bias already added)
+ * Everything else as dcnv2_forward (3x3, one group, one deformable group). */
+int dcnv2_forward_raw27(const float* input, const float* weight, const float* bias,
+                        const float* offset_mask, const float* offset_mask_bias, float* output,
+                        int B, int Cin, int H, int W, int Cout, int stride, int pad, int dilation,
+                        const float* scale, const float* shift, int flags,
+                        void* workspace, size_t workspace_bytes, ctdet_stream_t stream);
+
 /* ---------------------------------------------------------------- DCNv2 backward ---------
  * Replaces modulated_deform_conv_backward (deform_conv.h:314-338; same argument meaning, minus the
  * `ones`/`columns` scratch tensors and the unused `bias`).  All gradient outputs are OVERWRITTEN

@@ -127,3 +127,29 @@ def test_dcn_unsupported_and_cpu():
     with pytest.raises(NotImplementedError):                           # Cin not a multiple of 64
         DC.dcnv2_forward(torch.zeros(1, 32, 8, 8, device=DEV), torch.zeros(1, 18, 8, 8, device=DEV),
                          torch.zeros(1, 9, 8, 8, device=DEV), torch.zeros(64, 32, 3, 3, device=DEV), None, 1, 1)
+
+
+@pytest.mark.gpu
+def test_raw27_entry_equals_the_split_offset_mask_call():
+    """dcnv2_forward_raw27 (raw conv_offset_mask output + its bias, sigmoid inside the kernel) against dcnv2_forward fed
+    with what DCN.offset_mask builds in torch (chunk / cat / sigmoid, resnet.py:308-311): same kernel, same
+    operands, only the sigmoid's last ulp may differ -> outputs agree to 1e-5 of the output scale."""
+    from detectron2_centernet_b200 import deform_conv as DC
+    torch.manual_seed(5)
+    dev = "cuda:0"
+    B, Cin, Cout, H, W = 2, 64, 128, 24, 40
+    x = torch.randn(B, Cin, H, W, device=dev)
+    raw = torch.randn(B, 27, H, W, device=dev) * 1.5
+    ob = torch.randn(27, device=dev) * 0.5
+    w = torch.randn(Cout, Cin, 3, 3, device=dev) / (9 * Cin) ** 0.5
+    b = torch.randn(Cout, device=dev)
+    sc, sh = torch.rand(Cout, device=dev) + 0.5, torch.randn(Cout, device=dev)
+    full = raw + ob.view(1, 27, 1, 1)
+    o1, o2, m = torch.chunk(full, 3, dim=1)
+    ref = DC.dcnv2_forward(x, torch.cat((o1, o2), dim=1), torch.sigmoid(m), w, b, 1, 1, 1, scale=sc, shift=sh, relu=True)
+    got = DC.dcnv2_forward_raw27(x, raw, w, b, ob, 1, 1, 1, scale=sc, shift=sh, relu=True)
+    assert float((got - ref).abs().max()) <= 1e-5 * float(ref.abs().max())
+    got2 = DC.dcnv2_forward_raw27(x, full, w, b, None, 1, 1, 1, scale=sc, shift=sh, relu=True)
+    assert float((got2 - ref).abs().max()) <= 1e-5 * float(ref.abs().max())
+    with pytest.raises(RuntimeError):
+        DC.dcnv2_forward_raw27(x, raw[:, :18], w, b)
