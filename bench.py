@@ -183,7 +183,11 @@ def run_ours(args):
         det = D.ctdet_decode_batch(hm, wh, reg, down_ratio=4, K=K, logits=True)
         return losses, det
 
-    LAUNCHES_PER_STEP = 4      # target_gen, loss, decode_peaks, decode_finalize
+    # kernels launched per step: target_gen + loss_kernel + the decode's launches -- 4 on the streaming path
+    # (decode_seed, decode_stream, the gated decode_peaks, decode_finalize; the default for these 128x128 maps,
+    # profiles/r1_launches.csv), 2 on the staged path (decode_peaks, decode_finalize; CTDET_DECODE_STREAM=0)
+    DECODE_LAUNCHES = 2 if os.environ.get("CTDET_DECODE_STREAM", "1") == "0" else 4
+    LAUNCHES_PER_STEP = 2 + DECODE_LAUNCHES
 
     # The device-resident step is captured ONCE into a CUDA graph (6 kernel nodes) and replayed:
     # the kernels take 30-100 us each, so per-call Python/ctypes overhead would otherwise show up
@@ -317,7 +321,8 @@ def run_ours(args):
             "what": "same step with ctdet_target_loss_fused: the Gaussian target is built in shared memory inside the loss "
                     "sweep and never written to HBM (SURVEY.md section 8 f2; 12 B/cell per step instead of 20)",
             "value": round(world * B / (fused_ms / args.steps * 1e-3), 1), "unit": "images/s",
-            "ms_per_step": round(fused_ms / args.steps, 4), "gpu_launches_per_step": 4},
+            "ms_per_step": round(fused_ms / args.steps, 4),
+            "gpu_launches_per_step": 2 + DECODE_LAUNCHES},   # target_slots + target_loss_fused + decode
     }
     traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.isfile(traffic_file):
