@@ -158,11 +158,16 @@ __global__ void preprocess_kernel(const T* const* __restrict__ images, const int
 // grouped cuDNN dgrad kernel (5.7 ms per DLA-34 step at batch 32) plus a separate add.
 // One thread = 4 consecutive outputs of a row (float4 skip load / out store); a CTA stays inside one (b, c) plane
 // and keeps the plane's weights in shared memory.
-template <int VEC>
+// LF > 0: f = 2^LF known at compile time (the neck's f = 2 and 4).  With 4 outputs per thread X0 = 4q is a multiple
+// of f, so the tap kx0 and the input column of output j depend on j only: the weight offsets and the column
+// selects below become constants (the capture of the runtime-f form showed the kernel issue-bound, 67
+// instructions per thread, most of them those selects and the row division).  LF == 0: runtime f (8, 16, odd widths).
+template <int VEC, int LF>
 __global__ void __launch_bounds__(256)
 upsample_add_kernel(const float* __restrict__ x, const float* __restrict__ wt, const float* __restrict__ skip,
-                    int C, int h, int w, int lf, float* __restrict__ out) {
+                    int C, int h, int w, int lf_rt, FastDiv div_wq, float* __restrict__ out) {
   __shared__ float s_w[32 * 32];                   // (2f)^2 <= 1024 (f <= 16)
+  const int lf = LF > 0 ? LF : lf_rt;
   const int f = 1 << lf, k = 2 * f, p = f >> 1;
   const int c = blockIdx.y, b = blockIdx.z;
   const int Ho = h << lf, Wo = w << lf, Wq = (Wo + VEC - 1) / VEC;
@@ -173,7 +178,7 @@ upsample_add_kernel(const float* __restrict__ x, const float* __restrict__ wt, c
   const float* sp = skip ? skip + plane * Ho * Wo : nullptr;
   float* op = out + plane * Ho * Wo;
   for (int item = blockIdx.x * blockDim.x + threadIdx.x; item < Ho * Wq; item += gridDim.x * blockDim.x) {
-    const int Y = item / Wq, q = item - Y * Wq, X0 = q * VEC;
+    const int Y = (int)div_wq.div((uint32_t)item), q = item - Y * Wq, X0 = q * VEC;
     const int ty = Y + p, ky0 = ty & (f - 1), iy0 = ty >> lf, iy1 = iy0 - 1;
     const float* w0 = s_w + ky0 * k;               // weights of input row iy0
     const float* w1 = s_w + (ky0 + f) * k;         //            of input row iy1
@@ -191,7 +196,13 @@ upsample_add_kernel(const float* __restrict__ x, const float* __restrict__ wt, c
     float res[VEC];
 #pragma unroll
     for (int j = 0; j < VEC; ++j) {
-      const int tx = X0 + j + p, kx0 = tx & (f - 1), d = (tx >> lf) - c_lo;     // d in {1, 2, 3}
+      int kx0, d;                                                              // d in {1, 2, 3}
+      if (LF > 0 && VEC == 4 && (1 << LF) <= 4) {          // X0 % f == 0: both depend on j only (compile-time)
+        kx0 = (p + j) & (f - 1); d = 1 + ((p + j) >> lf);
+      } else {
+        const int tx = X0 + j + p;
+        kx0 = tx & (f - 1); d = (tx >> lf) - c_lo;
+      }
       const float i00 = d == 1 ? a0[1] : (d == 2 ? a0[2] : a0[3]);               // (iy0, ix0)
       const float i01 = d == 1 ? a0[0] : (d == 2 ? a0[1] : a0[2]);               // (iy0, ix0 - 1)
       const float i10 = d == 1 ? a1[1] : (d == 2 ? a1[2] : a1[3]);
@@ -304,7 +315,10 @@ extern "C" int ctdet_upsample_add(const float* x, const float* weight, const flo
   if (bx < 1) bx = 1;
   const dim3 grid((unsigned)bx, (unsigned)C, (unsigned)B);
   cudaStream_t st = (cudaStream_t)stream;
-  if (vec) upsample_add_kernel<4><<<grid, 256, 0, st>>>(x, weight, skip, C, h, w, lf, out);
-  else upsample_add_kernel<1><<<grid, 256, 0, st>>>(x, weight, skip, C, h, w, lf, out);
+  const FastDiv dq((uint32_t)(vec ? Wo / 4 : Wo));
+  if (vec && f == 2) upsample_add_kernel<4, 1><<<grid, 256, 0, st>>>(x, weight, skip, C, h, w, lf, dq, out);
+  else if (vec && f == 4) upsample_add_kernel<4, 2><<<grid, 256, 0, st>>>(x, weight, skip, C, h, w, lf, dq, out);
+  else if (vec) upsample_add_kernel<4, 0><<<grid, 256, 0, st>>>(x, weight, skip, C, h, w, lf, dq, out);
+  else upsample_add_kernel<1, 0><<<grid, 256, 0, st>>>(x, weight, skip, C, h, w, lf, dq, out);
   return check_launch();
 }
