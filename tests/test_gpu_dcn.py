@@ -153,3 +153,31 @@ def test_raw27_entry_equals_the_split_offset_mask_call():
     assert float((got2 - ref).abs().max()) <= 1e-5 * float(ref.abs().max())
     with pytest.raises(RuntimeError):
         DC.dcnv2_forward_raw27(x, raw[:, :18], w, b)
+
+
+@pytest.mark.gpu
+def test_raw27_entry_matches_the_oracle_directly():
+    """dcnv2_forward_raw27 against the C restatement of the reference (oracle/dcn_oracle.c) fed with what the reference
+    computes from the raw conv_offset_mask output in fp32 on the CPU (resnet.py:308-311): offset = channels 0..17 + bias,
+    mask = sigmoid(channels 18..26 + bias).  Same stated tolerance as the plain entry (bf16 operands, fp32 accumulation):
+    max error <= 2e-2 of the output scale, relative L2 <= 1e-2.  Includes offsets that leave the image."""
+    from detectron2_centernet_b200 import deform_conv as DC
+    rng = np.random.default_rng(21)
+    B, Cin, Cout, H, W = 2, 64, 64, 20, 28
+    x = rng.normal(size=(B, Cin, H, W)).astype(np.float32)
+    raw = (rng.normal(size=(B, 27, H, W)) * 2.0).astype(np.float32)      # offsets up to ~ +-6 px: some taps leave the map
+    ob = rng.normal(size=(27,)).astype(np.float32)
+    w = (rng.uniform(-1, 1, (Cout, Cin, 3, 3)) / math.sqrt(9 * Cin)).astype(np.float32)
+    b = rng.normal(size=(Cout,)).astype(np.float32)
+    full = raw + ob.reshape(1, 27, 1, 1)
+    offset = np.ascontiguousarray(full[:, :18])
+    mask = (1.0 / (1.0 + np.exp(-full[:, 18:].astype(np.float64)))).astype(np.float32)
+    ref = DO.dcn_forward(x, offset, mask, w, b, 1, 1, 1)
+    dev = "cuda:0"
+    t = lambda a: torch.from_numpy(a).to(dev)
+    for om_bias, src in ((ob, raw), (None, full)):
+        got = DC.dcnv2_forward_raw27(t(x), t(np.ascontiguousarray(src)), t(w), t(b),
+                                     None if om_bias is None else t(om_bias), 1, 1, 1).cpu().numpy()
+        emax = np.abs(got - ref).max() / np.abs(ref).max()
+        el2 = np.linalg.norm(got - ref) / np.linalg.norm(ref)
+        assert emax <= 2e-2 and el2 <= 1e-2, (om_bias is None, emax, el2)
