@@ -247,27 +247,3 @@ class DeformConvV2(nn.Module):
             return dcnv2_forward_raw27(x, raw, self.conv.weight, self.conv.bias, com.bias, 1, 1, 1,
                                        scale=scale, shift=shift, relu=True)
         return self.actf(self.conv(x))
-
-
-def _smoke():
-    """One small DCN layer on cuda:0 against the C oracle (called from __graft_entry__.smoke)."""
-    import numpy as np
-    from oracle import dcn_oracle as DO
-    rng = np.random.default_rng(7)
-    B, Cin, Cout, H, W = 1, 64, 64, 16, 24
-    x = rng.normal(size=(B, Cin, H, W)).astype(np.float32)
-    off = rng.uniform(-2, 2, (B, 18, H, W)).astype(np.float32)
-    m = (1 / (1 + np.exp(-rng.normal(size=(B, 9, H, W))))).astype(np.float32)
-    w = rng.uniform(-1, 1, (Cout, Cin, 3, 3)).astype(np.float32) / math.sqrt(9 * Cin)
-    b = rng.normal(size=(Cout,)).astype(np.float32)
-    ref = DO.dcn_forward(x, off, m, w, b, 1, 1, 1)
-    dev = "cuda:0"
-    got = dcnv2_forward(*[torch.from_numpy(a).to(dev) for a in (x, off, m, w, b)], stride=1, padding=1).cpu().numpy()
-    err = np.abs(got - ref).max() / np.abs(ref).max()
-    assert err < 2e-2, "DCN smoke mismatch: %g" % err
-    gy = rng.normal(size=ref.shape).astype(np.float32)
-    ref_g = DO.dcn_backward(x, off, m, w, gy, 1, 1, 1)
-    got_g = dcnv2_backward(*[torch.from_numpy(a).to(dev) for a in (x, off, m, w, gy)], stride=1, padding=1)
-    for name, g, r in zip(("grad_input", "grad_offset", "grad_mask", "grad_weight", "grad_bias"), got_g, ref_g):
-        e = np.linalg.norm(g.cpu().numpy() - r) / np.linalg.norm(r)
-        assert e < 1.5e-2, "DCN backward smoke mismatch (%s): %g" % (name, e)
