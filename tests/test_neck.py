@@ -95,7 +95,7 @@ def test_neck_with_b200_dcn_matches_fp32_neck_eval():
 def test_neck_train_mode_layers_match_fp32_neck():
     """Train mode (batch-statistics BatchNorm, autograd through dcnv2_backward).  A random-weight neck
     with batch-stat BN amplifies any input perturbation 3-4x per layer, forward and backward (the fp32
-    stand-in does the same under fp32 noise: scripts/neck_layer_check.py, neck_layer_grad_check.py), so
+    stand-in does the same under fp32 noise: tests/tools/neck_layer_check.py, neck_layer_grad_check.py), so
     a free-running comparison measures the network's conditioning, not the kernels.  The well-posed
     check is per layer: each of the 16 DCNs of the neck (offset conv + contraction) is fed the
     stand-in's own input and output gradient of that layer, and its output and all its gradients are
