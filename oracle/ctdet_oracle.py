@@ -198,8 +198,9 @@ def decode(heat, wh, reg=None, down_ratio=1, K=100, cat_spec_wh=False, logits=Fa
     """ctdet_decode, centernet.py:426-458, batched over images (the reference is batch=1).
 
     heat: f32 [B,C,H,W], probabilities in (0,1] as produced at centernet.py:161, or raw head
-    logits when logits=True (sigmoid is monotone, so peaks and ranking are taken on the
-    logits and score = clamp(sigmoid(x), 1e-4, 1-1e-4) is applied to the K winners).
+    logits when logits=True (sigmoid is monotone, so the ranking is taken on the logits and
+    score = clamp(sigmoid(x), 1e-4, 1-1e-4) is applied to the K winners; the 3x3 peak test
+    runs on the fp32 probabilities, exactly the values the reference compares).
 
     Selection: the reference takes a per-class top-K (:411) then a top-K of those C*K (:417);
     that equals one top-K over all C*H*W cells because no class can hold more than K of the
@@ -212,10 +213,15 @@ def decode(heat, wh, reg=None, down_ratio=1, K=100, cat_spec_wh=False, logits=Fa
     B, C, H, W = h.shape
     if H * W < K:
         raise RuntimeError("selected index k out of range")   # torch.topk at :411
-    keep = peak_mask(h)
     if logits:
+        # the reference never sees logits: it ranks and peak-tests p = clamp(sigmoid(x)) in fp32 (:161, :401-404),
+        # and distinct logits can share one fp32 probability (clamp saturation, rounding) -- then the reference
+        # keeps every cell of such a plateau.  So the 3x3 test runs on p; the order among equal p is unspecified
+        # in the reference (torch.topk), ours: higher logit first, then lower flat index.
+        keep = peak_mask(_sigmoid_clamp(h))
         rank = np.where(keep, h, -np.inf)
     else:
+        keep = peak_mask(h)
         rank = np.where(keep & (h > 0), h, np.float32(0))
     flat = rank.reshape(B, -1)
     order = np.stack([np.lexsort((np.arange(flat.shape[1]), -flat[b].astype(np.float64)))[:K]
@@ -261,6 +267,47 @@ def postprocess_single(boxes, scores, classes, max_dets=100, score_thresh=0.05):
     b, s, c = boxes[:n], scores[:n], classes[:n]
     k = s > np.float32(score_thresh)
     return b[k], s[k], c[k]
+
+
+def detector_postprocess(boxes, scores, classes, image_size, output_size):
+    """detector_postprocess, modeling/postprocessing.py:11-74, for the fields ctdet produces: the python-float
+    quotients scale_x = out_w / in_w, scale_y = out_h / in_h (:39-42) multiply the fp32 box tensor in place
+    (Boxes.scale, structures/boxes.py:271-276: the scalar is rounded to fp32 first), Boxes.clip (:184-197) clamps
+    x to [0, out_w] and y to [0, out_h], and rows whose width or height is not > 0 are dropped (Boxes.nonempty
+    :199-213, postprocessing.py:57).  image_size / output_size are (h, w)."""
+    b = np.array(boxes, np.float32, copy=True).reshape(-1, 4)
+    sx = np.float32(float(output_size[1]) / float(image_size[1]))
+    sy = np.float32(float(output_size[0]) / float(image_size[0]))
+    b[:, 0::2] *= sx
+    b[:, 1::2] *= sy
+    b[:, 0::2] = np.clip(b[:, 0::2], np.float32(0), np.float32(output_size[1]))
+    b[:, 1::2] = np.clip(b[:, 1::2], np.float32(0), np.float32(output_size[0]))
+    keep = ((b[:, 2] - b[:, 0]) > 0) & ((b[:, 3] - b[:, 1]) > 0)
+    return b[keep], np.asarray(scores)[keep], np.asarray(classes)[keep]
+
+
+def inference(hm_logits, wh, reg, image_sizes, output_sizes=None, down_ratio=4, topk_candidates=100,
+              max_detections_per_image=100, score_threshold=0.05):
+    """The eval branch from the head outputs on: sigmoid_ + clamp (centernet.py:161), `inference` (:214-234) with
+    `inference_single_image` (:236-266) per image, then detector_postprocess (:169-171) when output_sizes is
+    given.  -> list of (boxes f32[n,4], scores f32[n], classes i32[n])."""
+    heat = _sigmoid_clamp(hm_logits)
+    ob, os_, oc, _ = decode(heat, wh, reg, down_ratio, topk_candidates)
+    res = []
+    for i in range(heat.shape[0]):
+        r = postprocess_single(ob[i], os_[i], oc[i], max_detections_per_image, score_threshold)
+        if output_sizes is not None:
+            r = detector_postprocess(r[0], r[1], r[2], image_sizes[i], output_sizes[i])
+        res.append(r)
+    return res
+
+
+def _sigmoid_clamp(x):
+    """clamp(sigmoid(x), 1e-4, 1 - 1e-4) in fp32 (centernet.py:161)."""
+    x = np.asarray(x, np.float32)
+    with np.errstate(over="ignore"):
+        p = (np.float32(1) / (np.float32(1) + np.exp(-x))).astype(np.float32)
+    return np.clip(p, np.float32(1e-4), np.float32(1 - 1e-4)).astype(np.float32)
 
 
 def decode_torch(heat, wh, reg=None, down_ratio=1, K=100):

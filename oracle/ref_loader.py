@@ -62,7 +62,7 @@ _CACHE = {}
 
 def load():
     """Returns a dict name -> reference object (functions / nn.Module classes)."""
-    if _CACHE:
+    if "gen_heatmap" in _CACHE:
         return _CACHE
     if not available():
         raise RuntimeError("reference tree not present at %s" % REF_ROOT)
@@ -164,3 +164,87 @@ def ref_decode(heat, wh, reg, down_ratio=4, K=100):
                down_ratio=down_ratio, K=K) for b in range(heat.shape[0])]
     return (torch.stack([o[0] for o in outs]), torch.stack([o[1] for o in outs]),
             torch.stack([o[2] for o in outs]))
+
+
+# --------------------------------------------------------------------------------------
+# Inference glue: CenterNet.inference / inference_single_image (centernet.py:214-266) and
+# detector_postprocess (modeling/postprocessing.py:11-74) with the reference's own Instances / Boxes.
+# --------------------------------------------------------------------------------------
+def load_structures():
+    """The reference's own `Boxes` and `Instances` (detectron2/structures/{boxes,instances}.py import only
+    torch / numpy / typing, so both files are exec'd whole and unmodified)."""
+    if "Instances" not in _CACHE:
+        for fname, names in (("boxes.py", ("Boxes",)), ("instances.py", ("Instances",))):
+            path = os.path.join(REF_ROOT, "detectron2/structures", fname)
+            ns = {"__name__": "ctdet_reference_" + fname[:-3]}
+            with open(path, "r") as f:
+                exec(compile(f.read(), path, "exec"), ns)
+            for n in names:
+                _CACHE[n] = ns[n]
+    return _CACHE["Boxes"], _CACHE["Instances"]
+
+
+def _extract_methods(path, cls_name, names):
+    with open(os.path.join(REF_ROOT, path), "r") as f:
+        tree = ast.parse(f.read())
+    cls = [n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == cls_name]
+    if not cls:
+        raise RuntimeError("class %s not found in %s" % (cls_name, path))
+    picked = [n for n in cls[0].body if isinstance(n, ast.FunctionDef) and n.name in names]
+    missing = set(names) - {n.name for n in picked}
+    if missing:
+        raise RuntimeError("reference methods not found in %s.%s: %s" % (path, cls_name, sorted(missing)))
+    return ast.Module(body=picked, type_ignores=[])
+
+
+def load_inference():
+    """-> (inference, inference_single_image, detector_postprocess): the reference's unmodified FunctionDef nodes.
+    The two methods are plain functions taking `self` first (call them with `DummyCenterNet`)."""
+    if "inference_single_image" not in _CACHE:
+        R = load()
+        Boxes, Instances = load_structures()
+        path = "detectron2/modeling/meta_arch/centernet.py"
+        ns = {"torch": torch, "nn": nn, "F": F, "np": np, "Instances": Instances, "Boxes": Boxes,
+              "ctdet_decode": R["ctdet_decode"], "__name__": "ctdet_reference_inference"}
+        exec(compile(_extract_methods(path, "CenterNet", ["inference", "inference_single_image"]),
+                     os.path.join(REF_ROOT, path), "exec"), ns)
+        _CACHE["inference"], _CACHE["inference_single_image"] = ns["inference"], ns["inference_single_image"]
+        path = "detectron2/modeling/postprocessing.py"
+        ns2 = {"torch": torch, "F": F, "Instances": Instances, "__name__": "ctdet_reference_postprocessing",
+               # only reached for pred_masks, which ctdet never produces (postprocessing.py:60-66)
+               "paste_masks_in_image": None, "retry_if_cuda_oom": lambda f: f}
+        exec(compile(_extract(path, ["detector_postprocess"]), os.path.join(REF_ROOT, path), "exec"), ns2)
+        _CACHE["detector_postprocess"] = ns2["detector_postprocess"]
+    return _CACHE["inference"], _CACHE["inference_single_image"], _CACHE["detector_postprocess"]
+
+
+class _Backbone:
+    def __init__(self, down_ratio):
+        self.down_ratio = down_ratio
+
+
+class DummyCenterNet:
+    """The four attributes `inference_single_image` reads from `self` (centernet.py:245-258), set from the
+    config fields the reference's __init__ reads (:50-57)."""
+
+    def __init__(self, down_ratio=4, topk_candidates=100, max_detections_per_image=100, score_threshold=0.05):
+        self.backbone = _Backbone(down_ratio)
+        self.topk_candidates = topk_candidates
+        self.max_detections_per_image = max_detections_per_image
+        self.score_threshold = score_threshold
+
+    def inference_single_image(self, output, image_size):
+        return load_inference()[1](self, output, image_size)
+
+
+def ref_inference(hm_logits, wh, reg, image_sizes, output_sizes=None, **cfg):
+    """The reference's eval path from the head outputs on: sigmoid_ + clamp (centernet.py:161), `inference`
+    (:214-234) and, when output_sizes is given, `detector_postprocess` per image (:169-171 of the reference's
+    forward).  Returns a list of the reference's own Instances."""
+    inference, _, post = load_inference()
+    net = DummyCenterNet(**cfg)
+    out = {"hm": torch.clamp(hm_logits.clone().sigmoid_(), min=1e-4, max=1 - 1e-4), "wh": wh, "reg": reg}
+    res = inference(net, out, image_sizes)
+    if output_sizes is not None:
+        res = [post(r, int(o[0]), int(o[1])) for r, o in zip(res, output_sizes)]
+    return res
