@@ -176,20 +176,20 @@ def run_ours(args):
     h_out = torch.empty(3 + B * K * 6, dtype=torch.float32).pin_memory()
 
     def hot_path(hm, wh, reg, bx, cls_, off):
-        """target-gen -> fused loss fwd+bwd -> decode; 4 kernel launches of ours."""
+        """target-gen -> fused loss fwd+bwd -> decode (seed, sweep, tail): 5 kernel launches of ours."""
         T.target_gen(bx, cls_, off, B, C, H, W, out=gt)
         losses, g_hm, g_wh, g_reg = L._call(hm, wh, reg, gt["hm"], gt["reg_mask"], gt["ind"], gt["wh"],
                                             gt["reg"], alpha, gt["num_pos"], None, 2, weights, True)
         det = D.ctdet_decode_batch(hm, wh, reg, down_ratio=4, K=K, logits=True)
         return losses, det
 
-    # kernels launched per step: target_gen + loss_kernel + the decode's launches -- 4 on the streaming path
-    # (decode_seed, decode_stream, the gated decode_peaks, decode_finalize; the default for these 128x128 maps,
-    # profiles/r1_launches.csv), 2 on the staged path (decode_peaks, decode_finalize; CTDET_DECODE_STREAM=0)
-    DECODE_LAUNCHES = 2 if os.environ.get("CTDET_DECODE_STREAM", "1") == "0" else 4
+    # kernels launched per step: target_gen + loss_kernel + the decode's launches -- 3 on the streaming path
+    # (decode_seed, decode_stream, decode_tail; the default for these 128x128 maps), 2 on the staged path
+    # (decode_peaks, decode_tail; CTDET_DECODE_STREAM=0)
+    DECODE_LAUNCHES = 2 if os.environ.get("CTDET_DECODE_STREAM", "1") == "0" else 3
     LAUNCHES_PER_STEP = 2 + DECODE_LAUNCHES
 
-    # The device-resident step is captured ONCE into a CUDA graph (6 kernel nodes) and replayed:
+    # The device-resident step is captured ONCE into a CUDA graph (5 kernel nodes) and replayed:
     # the kernels take 30-100 us each, so per-call Python/ctypes overhead would otherwise show up
     # as idle gaps on the stream.
     for _ in range(2):
@@ -306,7 +306,7 @@ def run_ours(args):
         "data": "synthetic (seeded COCO-shaped boxes; logits ~N(-2.19,1.5^2) + planted peaks)",
         "config": {"workload": WORKLOAD, "images_per_gpu": B, "heatmap": [C, H, W], "K": K,
                    "l2": "flushed (256 MB memset) between timed iterations",
-                   "launch": "device-resident step replayed from a CUDA graph (6 kernel nodes); e2e uses plain calls",
+                   "launch": "device-resident step replayed from a CUDA graph (%d kernel nodes); e2e uses plain calls" % LAUNCHES_PER_STEP,
                    "sharding": "by image, no data-path collective"},
         "clocks": clocks,
         "e2e": {"value": round(e2e_value, 1), "unit": "images/s", "h2d_bytes_per_step": h2d,

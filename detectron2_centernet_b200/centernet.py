@@ -76,7 +76,10 @@ class CenterNetHotPath:
         boxes, scores, classes, _ = self.decode(outputs)
         B = scores.shape[0]
         out_sizes = image_sizes if output_sizes is None else output_sizes
-        sizes = torch.tensor([[int(i[0]), int(i[1]), int(o[0]), int(o[1])] for i, o in zip(image_sizes, out_sizes)],
+        # without output_sizes this is the reference's `inference` alone: threshold + slice, boxes as decoded
+        # (out_h = out_w = 0 tells the kernel to skip detector_postprocess' scale / clip / nonempty)
+        sizes = torch.tensor([[int(i[0]), int(i[1]), int(o[0]), int(o[1])] if output_sizes is not None
+                              else [int(i[0]), int(i[1]), 0, 0] for i, o in zip(image_sizes, out_sizes)],
                              dtype=torch.int32).to(scores.device, non_blocking=True)
         n_keep = D.postprocess_batch(boxes, scores, classes, sizes, self.max_detections_per_image,
                                      self.score_threshold).cpu().numpy()

@@ -4,15 +4,18 @@
 // max_pool2d + == + mul: three full passes), _topk (:408-424, two torch.topk + three gathers), two
 // full-map NHWC permutes (:435,:442) and the per-image Python loop of CenterNet.inference (:224).
 //
-// Two paths produce the per-image list of candidate keys (ordered(score) << 32) | ~flat_index -- one integer
-// compare implements the tie rule "higher score, then lower flat index" -- both HBM-bound at 4 B/cell:
+// Two paths produce the per-image candidate keys (ordered(score) << 32) | ~flat_index -- one integer compare
+// implements the tie rule "higher score, then lower flat index" -- both HBM-bound at 4 B/cell:
 //
-// STREAMING (default when W % 4 == 0): decode_seed_kernel derives a valid lower bound of every image's
-//   K-th best peak from a ~1/16 sample of the image; decode_stream_kernel then reads the logits as a flat
-//   float4 stream, rejects ~99.7 % of the cells with one compare against the bound and peak-tests the rest
-//   (neighbours re-read through L2).  See the comments above those kernels.
+// STREAMING (default when W % 4 == 0): decode_seed_kernel histograms a ~1/16 sample of every image's peaks;
+//   decode_stream_kernel -- a lean TMA-staged sweep, one CTA per ~16 KB band of full-width rows moved into
+//   shared memory by ONE 1-D bulk async copy -- derives a valid lower bound of the image's K-th best peak from
+//   that histogram while its tile is in flight, rejects ~99.7 % of the cells with one compare and peak-tests
+//   the rest in shared memory; the keys go to the TILE's own segment (no atomics).  decode_tail_kernel (one
+//   CTA per image) gathers the segments and selects.  See the comments above those kernels.
 // STAGED (any shape; also the exact fall-back for images the streaming path hands over: no usable sample
-//   bound, or more candidates at the bound than its list holds -- ties, plateaus): decode_peaks_kernel,
+//   bound, or more candidates at the bound than a tile segment holds -- ties, plateaus; the fall-back runs
+//   INSIDE decode_tail_kernel, shared by a few helper CTAs per image): decode_peaks_tile,
 //   one CTA per (image, class plane, row band).  The band (+ halo rows) is staged into shared
 //   memory by ONE bulk async copy (TMA 1-D, mbarrier completion); several CTAs are resident per SM
 //   so the copies of some overlap the peak tests of others.  Warps walk down the rows of a
@@ -27,10 +30,14 @@
 //   almost every cell and only a few thousand keys per image survive.  Survivors are appended to a
 //   per-image list.  Exactness never depends on the bounds: they are always lower bounds; an exact
 //   MSB-first radix select is the fallback when a tile holds too many near-ties.
-// FINALIZE (one CTA per image): final bound from the histogram + rank sort of the survivors = the
+// TAIL (one CTA per image): threshold from a histogram of the survivors + rank sort = the
 //   exact K best (equivalent to the reference's per-class top-K followed by a top-K over C*K),
 //   gather of wh/reg, boxes, outputs; resets the per-image header and histograms.
-// Workspace: per-image headers + histograms (zero on entry, left zero) + key lists of both paths.
+// With CTDET_DECODE_LOGITS the 3x3 peak test is defined on the fp32 probabilities clamp(sigmoid(x)) -- the values
+//   the reference compares (centernet.py:161, :401-404) -- so cells that share a probability with their largest
+//   neighbour (clamp saturation, rounding near 1) are all kept, like the reference's plateaus; the ranking stays
+//   on the logits (same order; among equal probabilities: higher logit, then lower flat index).
+// Workspace: per-image headers + histograms (zero on entry, left zero) + tile counts / key segments + staged lists.
 #include <cstdlib>
 #include "common.cuh"
 
@@ -176,13 +183,27 @@ __device__ void find_threshold_bin(const unsigned int* hist, int need, BinScratc
   __syncthreads();
 }
 
+// clamp(sigmoid(x), 1e-4, 1 - 1e-4) exactly as the finalize step scores a winner (centernet.py:161).  With
+// CTDET_DECODE_LOGITS the 3x3 peak test is defined on THESE fp32 values, like the reference's hmax == heat
+// (:401-404): distinct logits can share one probability (clamp saturation, rounding near 1), and the reference
+// then keeps every cell of the plateau.  sigmoid is monotone, so "x_c >= max neighbour logit" already implies
+// the peak; only a centre BELOW its largest neighbour needs the two sigmoids.
+__device__ __forceinline__ float prob_of_logit(float x) {
+  const float p = 1.f / (1.f + expf(-x));
+  return fminf(fmaxf(p, 1e-4f), 1.f - 1e-4f);
+}
+__device__ __noinline__ bool same_prob(float a, float b) { return prob_of_logit(a) == prob_of_logit(b); }   // rare: out of line
+__device__ __forceinline__ bool is_peak(float v, float nb, bool logits) {
+  return v >= nb || (logits && same_prob(v, nb));
+}
+
 struct DecodeHeader {            // per image, zero on entry, reset by the finalize kernel
   unsigned int count;            // keys emitted so far by decode_peaks_kernel (the staged path)
   unsigned int thr_ord;          // a valid lower bound (ordered score) of the image's K-th best peak
   unsigned int s_count;          // keys emitted by decode_stream_kernel
   unsigned int staged;           // 1: the image is decoded by decode_peaks_kernel (no seed bound, or the
                                  //    streaming list overflowed); finalize then reads that path's list
-  unsigned int ticket;           // decode_seed_kernel: CTAs of the image that have flushed their histogram
+  unsigned int ticket;           // decode_tail_kernel: helper CTAs of a handed-over image that finished their tiles
   unsigned int pad[3];
 };
 
@@ -196,8 +217,9 @@ struct DecodeShared {
 
 // Re-derives the image-wide bound from the global histogram, publishes it and raises the local
 // threshold.  All threads.
+template <int NT>
 __device__ void refresh_bound(const unsigned int* ghist, DecodeHeader* hdr, DecodeShared* sh, int K) {
-  find_threshold_bin<kDecThreads>(ghist, K, &sh->bs);
+  find_threshold_bin<NT>(ghist, K, &sh->bs);
   if (threadIdx.x == 0) {
     unsigned int ord = ((unsigned int)sh->bs.bin) << kHistShift;      // lower edge of that bin
     if (sh->bs.cnt_ge < (unsigned)K) ord = 0u;
@@ -235,6 +257,7 @@ __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, unsig
 // heat [B,C,H,W]; per image b: hdr[b], ghist[b][kHistBins], keys[b][0 .. tiles*(K+kKeepSlack))
 // grid = (bands, B, C): band fastest, then IMAGE, then class.  CTAs that run concurrently therefore
 // belong to many images, and most CTAs of an image start after its first CTAs published a bound.
+template <int NT>
 __device__ __forceinline__ void
 decode_peaks_tile(const float* __restrict__ heat, int C, int H, int W, int Wp, int K,
                   int band_rows, int sub_rows, FastDiv div_strips, int flags,
@@ -262,7 +285,7 @@ decode_peaks_tile(const float* __restrict__ heat, int C, int H, int W, int Wp, i
   const float NEG = -__int_as_float(0x7f800000);                        // max_pool2d padding (:401)
   const float POS = __int_as_float(0x7f800000);
   // candidates: probabilities must be > 0 (heat*keep zeros rank last, :405); logits must be finite
-  const float floor_f = logits ? -3.402823466e38f : __int_as_float(1);
+  const float floor_f = (logits || no_nms) ? -3.402823466e38f : __int_as_float(1);
 
   // ---- stage the band (+ halo rows) -------------------------------------------------------------
   const int g_first = max(y_lo - 1, 0), g_last = min(y_hi, H - 1);      // map rows that exist
@@ -282,14 +305,14 @@ decode_peaks_tile(const float* __restrict__ heat, int C, int H, int W, int Wp, i
     sh.thresh = g ? (((u64)g << 32) - 1ull) : 0ull;
   }
   if (!bulk) {                                          // W % 4 != 0: padded rows, plain copies
-    for (int i = tid; i < (g_last - g_first + 1) * Wp; i += kDecThreads) {
+    for (int i = tid; i < (g_last - g_first + 1) * Wp; i += NT) {
       const int r = i / Wp, x = i - r * Wp;
       tile[(size_t)(g_first - (y_lo - 1) + r) * Wp + x] = x < W ? __ldg(p + (size_t)(g_first + r) * W + x) : NEG;
     }
   }
-  if (y_lo == 0) for (int x = tid; x < Wp; x += kDecThreads) tile[x] = NEG;
-  if (y_hi == H) for (int x = tid; x < Wp; x += kDecThreads) tile[(size_t)(nrows + 1) * Wp + x] = NEG;
-  for (int w = tid; w < n_words; w += kDecThreads) bitmap[w] = 0u;
+  if (y_lo == 0) for (int x = tid; x < Wp; x += NT) tile[x] = NEG;
+  if (y_hi == H) for (int x = tid; x < Wp; x += NT) tile[(size_t)(nrows + 1) * Wp + x] = NEG;
+  for (int w = tid; w < n_words; w += NT) bitmap[w] = 0u;
   __syncthreads();
   const u64 th0 = sh.thresh;
   const bool had_bound = th0 != 0ull;
@@ -304,7 +327,7 @@ decode_peaks_tile(const float* __restrict__ heat, int C, int H, int W, int Wp, i
     const int items = strips * ((nrows + sub_rows - 1) / sub_rows);
     const uint32_t th_ord = (uint32_t)(th0 >> 32);
     const float thv = fmaxf(th_ord ? ordered_to_float(th_ord) : NEG, floor_f);
-    for (int item = warp; item < items; item += kDecWarps) {
+    for (int item = warp; item < items; item += (NT / 32)) {
       const int sub = (int)div_strips.div((uint32_t)item), strip = item - sub * strips;
       const int t0 = 1 + sub * sub_rows;                        // tile rows [t0, t1) are tested
       const int t1 = min(nrows + 1, t0 + sub_rows);
@@ -340,7 +363,7 @@ decode_peaks_tile(const float* __restrict__ heat, int C, int H, int W, int Wp, i
         for (int j = 0; j < 4; ++j) {
           const float nb = fmaxf(fmaxf(hm[0][j], hm[1][j]), hm[2][j]);
           const float thj = (x0 + j < W) ? thv : POS;          // pad cells never pass
-          m[j] = __ballot_sync(0xffffffffu, (no_nms || v1[j] >= nb) && v1[j] >= thj);
+          m[j] = __ballot_sync(0xffffffffu, v1[j] >= thj && (no_nms || is_peak(v1[j], nb, logits)));
         }
         if (lane == 0 && (m[0] | m[1] | m[2] | m[3]))
           *reinterpret_cast<uint4*>(bitmap + ((size_t)(t - 1) * strips + strip) * 4) = make_uint4(m[0], m[1], m[2], m[3]);
@@ -360,7 +383,7 @@ decode_peaks_tile(const float* __restrict__ heat, int C, int H, int W, int Wp, i
   // ---- candidates -> keys -----------------------------------------------------------------------
   // calls f(key, word index, bit) for every candidate bit owned by this thread
   auto for_each_candidate = [&](auto f) {
-    for (int w = tid; w < n_words; w += kDecThreads) {
+    for (int w = tid; w < n_words; w += NT) {
       uint32_t bits = bitmap[w];
       if (!bits) continue;
       const int j = w & 3, rs = w >> 2;
@@ -393,7 +416,7 @@ decode_peaks_tile(const float* __restrict__ heat, int C, int H, int W, int Wp, i
     for_each_candidate([&](u64 key, int, int) { atomicAdd(ghist + ((uint32_t)(key >> 32) >> kHistShift), 1u); });
     __threadfence();
     __syncthreads();
-    refresh_bound(ghist, hdr, &sh, K);
+    refresh_bound<NT>(ghist, hdr, &sh, K);
     if (tid == 0) { sh.ncand = 0; sh.count = 0; }
     __syncthreads();
     {
@@ -408,7 +431,7 @@ decode_peaks_tile(const float* __restrict__ heat, int C, int H, int W, int Wp, i
     __syncthreads();
     if (sh.ncand > cap) {
       const int nc = sh.ncand;
-      const u64 T = radix_select_kth<kDecThreads>(
+      const u64 T = radix_select_kth<NT>(
           [&](auto f) { for_each_candidate([&](u64 key, int, int) { f(key); }); }, nc, K, &sh.sel);
       for_each_candidate([&](u64 key, int w, int ln) { if (key < T) atomicAnd(&bitmap[w], ~(1u << ln)); });
       if (tid == 0 && T - 1ull > sh.thresh) sh.thresh = T - 1ull;
@@ -424,7 +447,7 @@ decode_peaks_tile(const float* __restrict__ heat, int C, int H, int W, int Wp, i
     n = min(sh.count, cap);
   } else {
     // every collected key is counted exactly once in the image histogram
-    for (int i = tid; i < n; i += kDecThreads) atomicAdd(ghist + ((uint32_t)(buf[i] >> 32) >> kHistShift), 1u);
+    for (int i = tid; i < n; i += NT) atomicAdd(ghist + ((uint32_t)(buf[i] >> 32) >> kHistShift), 1u);
   }
 
   // ---- publish / pick up the image bound, emit --------------------------------------------------
@@ -433,11 +456,11 @@ decode_peaks_tile(const float* __restrict__ heat, int C, int H, int W, int Wp, i
   u64 th = sh.thresh;
   if (!had_bound || n > K / 2 + 32) {
     __threadfence();
-    refresh_bound(ghist, hdr, &sh, K);
+    refresh_bound<NT>(ghist, hdr, &sh, K);
     th = sh.thresh;
     // the bound may have risen: count, reserve and compact the keys that still pass
     int mine = 0;
-    for (int i = tid; i < n; i += kDecThreads) mine += (buf[i] > th);
+    for (int i = tid; i < n; i += NT) mine += (buf[i] > th);
     mine = warp_sum(mine);
     if (tid == 0) sh.count = 0;
     __syncthreads();
@@ -448,7 +471,7 @@ decode_peaks_tile(const float* __restrict__ heat, int C, int H, int W, int Wp, i
     if (tid == 0) sh.count = 0;
     __syncthreads();
     u64* dst = out_keys + (size_t)b * keys_per_image + s_base;
-    for (int i = tid; i < n; i += kDecThreads) {
+    for (int i = tid; i < n; i += NT) {
       const u64 key = buf[i];
       if (key > th) dst[atomicAdd(&sh.count, 1)] = key;
     }
@@ -457,43 +480,22 @@ decode_peaks_tile(const float* __restrict__ heat, int C, int H, int W, int Wp, i
     if (tid == 0) s_base = atomicAdd(&hdr->count, (unsigned)n);
     __syncthreads();
     u64* dst = out_keys + (size_t)b * keys_per_image + s_base;
-    for (int i = tid; i < n; i += kDecThreads) dst[i] = buf[i];
+    for (int i = tid; i < n; i += NT) dst[i] = buf[i];
   }
 }
 
-// Launch forms.  gated == 0: grid (bands, B, C), one tile per CTA -- band fastest, then IMAGE, then class,
-// so CTAs that run concurrently belong to many images and most CTAs of an image start after its first
-// CTAs published a bound.  gated == 1: the exact fall-back behind decode_stream_kernel: a small 1-D grid
-// that returns at once unless some image was handed over (hdr->staged, written before this launch
-// started) and otherwise walks the tiles of those images in the same order.
+// grid (bands, B, C), one tile per CTA -- band fastest, then IMAGE, then class, so CTAs that run concurrently
+// belong to many images and most CTAs of an image start after its first CTAs published a bound.  (The fall-back
+// behind the sweep runs the same tile function inside decode_tail_kernel.)
 __global__ void __launch_bounds__(kDecThreads)
-decode_peaks_kernel(const float* __restrict__ heat, int B, int C, int H, int W, int Wp, int K,
+decode_peaks_kernel(const float* __restrict__ heat, int C, int H, int W, int Wp, int K,
                     int band_rows, int sub_rows, FastDiv div_strips, int flags,
                     DecodeHeader* __restrict__ hdrs, unsigned int* __restrict__ ghists,
-                    u64* __restrict__ out_keys, size_t keys_per_image, int gated, int bands) {
+                    u64* __restrict__ out_keys, size_t keys_per_image) {
   extern __shared__ __align__(128) unsigned char s_raw[];
-  pdl_wait();
   pdl_launch_dependents();
-  if (!gated) {
-    decode_peaks_tile(heat, C, H, W, Wp, K, band_rows, sub_rows, div_strips, flags, hdrs, ghists, out_keys,
-                      keys_per_image, blockIdx.x, blockIdx.y, blockIdx.z, s_raw, false);
-    return;
-  }
-  int any = 0;
-  for (int i = threadIdx.x; i < B; i += kDecThreads) any |= (hdrs[i].staged != 0u);
-  if (!__syncthreads_or(any)) return;
-  const long long total = (long long)bands * B * C;
-  bool reinit = false;
-  for (long long t = blockIdx.x; t < total; t += gridDim.x) {
-    const int band = (int)(t % bands);
-    const long long bc = t / bands;
-    const int b = (int)(bc % B), c = (int)(bc / B);
-    if (hdrs[b].staged == 0u) continue;                      // CTA-uniform
-    __syncthreads();                                         // the previous tile's shared state is dead
-    decode_peaks_tile(heat, C, H, W, Wp, K, band_rows, sub_rows, div_strips, flags, hdrs, ghists, out_keys,
-                      keys_per_image, band, b, c, s_raw, reinit);
-    reinit = true;
-  }
+  decode_peaks_tile<kDecThreads>(heat, C, H, W, Wp, K, band_rows, sub_rows, div_strips, flags, hdrs, ghists, out_keys,
+                                 keys_per_image, blockIdx.x, blockIdx.y, blockIdx.z, s_raw, false);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -512,10 +514,87 @@ constexpr int kSeedWarps = kSeedThreads / 32;
 constexpr int kSeedPeriod = 64, kSeedRows = 4;
 constexpr int kSeedHist = kHistBins + kHistBins / 32;   // per image: the 2048 fine bins, then 64 coarse bins (32 fine each)
 
+// The bound of one image from its sample histogram (a whole warp, warp-uniform result): the highest bin whose
+// suffix count reaches K -- two dependent 256/128-byte reads: the 64 coarse bins (32 fine bins each), then the 32
+// fine bins of the coarse bin that holds the K-th entry; lane 0 owns the highest bins.  0 = fewer than K samples.
+__device__ unsigned int seed_bound_of_image(const unsigned int* ph, const unsigned int* pv, int n_vals, int K,
+                                            unsigned int* sub /* 32 shared words of this warp */) {
+  const int lane = threadIdx.x & 31;
+    const uint2 c2 = __ldcg(reinterpret_cast<const uint2*>(ph + kHistBins) + (31 - lane));  // coarse 62-2l, 63-2l
+    const unsigned int sum = c2.x + c2.y;
+    unsigned int incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const unsigned int t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    const unsigned int excl = incl - sum;
+    const unsigned int hit = __ballot_sync(0xffffffffu, excl < (unsigned)K && incl >= (unsigned)K);
+    unsigned int ord = 0u;
+    if (hit) {
+      const int src = __ffs(hit) - 1;
+      const bool upper = excl + c2.y >= (unsigned)K;          // meaningful on lane src only
+      const int coarse = __shfl_sync(0xffffffffu, upper ? 63 - 2 * lane : 62 - 2 * lane, src);
+      const unsigned int before = __shfl_sync(0xffffffffu, upper ? excl : excl + c2.y, src);
+      const unsigned int f = __ldcg(ph + coarse * 32 + (31 - lane));                         // descending by lane
+      unsigned int fi = f;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const unsigned int t = __shfl_up_sync(0xffffffffu, fi, o);
+        if (lane >= o) fi += t;
+      }
+      const unsigned int hit2 = __ballot_sync(0xffffffffu, before + fi - f < (unsigned)K && before + fi >= (unsigned)K);
+      if (hit2) {
+        const int l2 = __ffs(hit2) - 1;
+        ord = (unsigned int)(coarse * 32 + 31 - l2) << kHistShift;
+        // Concentrated scores (e.g. a random-init head: every logit within +-0.3 of the -2.19 bias) put most of the
+        // sample into this one quarter-octave bin, and its lower edge would pass the whole image.  Then refine
+        // on the sample itself, 5 more bits per round: a per-warp 32-bin histogram of the samples that share the
+        // prefix found so far, same suffix-count rule.  Still a valid lower bound: >= K samples are >= it.
+        unsigned int in_bin = __shfl_sync(0xffffffffu, f, l2);
+        unsigned int need = (unsigned)K - __shfl_sync(0xffffffffu, before + fi - f, l2);
+        unsigned int prefix = ord >> kHistShift;
+        int shift = kHistShift;
+        
+        
+        // only when the bin really is crowded (a normal image has n_vals / 30 or so samples in it, and every warp
+        // of every CTA runs this code): then keep going until the sub-bin is small
+        const unsigned int crowded = max(2u * (unsigned)K, (unsigned)n_vals / 8u);
+        if (in_bin > crowded)
+        while (in_bin > 24u && shift >= 5) {
+          sub[lane] = 0u;
+          __syncwarp();
+          for (int i = lane; i < n_vals; i += 32) {
+            const unsigned int v = __ldcg(pv + i);
+            if ((v >> shift) == prefix) atomicAdd(&sub[(v >> (shift - 5)) & 31u], 1u);
+          }
+          __syncwarp();
+          const unsigned int cnt = sub[31 - lane];                // descending by lane
+          unsigned int ci = cnt;
+#pragma unroll
+          for (int o = 1; o < 32; o <<= 1) {
+            const unsigned int t = __shfl_up_sync(0xffffffffu, ci, o);
+            if (lane >= o) ci += t;
+          }
+          const unsigned int h3 = __ballot_sync(0xffffffffu, ci - cnt < need && ci >= need);
+          __syncwarp();
+          if (!h3) break;                                          // (cannot happen: the bin holds >= need samples)
+          const int l3 = __ffs(h3) - 1;
+          prefix = (prefix << 5) | (unsigned)(31 - l3);
+          shift -= 5;
+          need -= __shfl_sync(0xffffffffu, ci - cnt, l3);
+          in_bin = __shfl_sync(0xffffffffu, cnt, l3);
+        }
+        ord = prefix << shift;
+      }
+    }
+    return ord;
+}
+
 __global__ void __launch_bounds__(kSeedThreads)
 decode_seed_kernel(const float* __restrict__ heat, int C, int H, int W, int K, int flags,
-                   int groups, FastDiv div_strips, FastDiv div_groups, unsigned int* __restrict__ phists,
-                   unsigned int* __restrict__ pvals_all, int n_vals) {
+                   int groups, FastDiv div_strips, FastDiv div_groups,
+                   unsigned int* __restrict__ phists, unsigned int* __restrict__ pvals_all, int n_vals) {
   pdl_launch_dependents();             // the sweep may be scheduled as soon as every CTA of this grid runs
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int b = blockIdx.y;
@@ -523,7 +602,7 @@ decode_seed_kernel(const float* __restrict__ heat, int C, int H, int W, int K, i
   const bool logits = flags & CTDET_DECODE_LOGITS;
   const bool no_nms = flags & CTDET_DECODE_NO_NMS;
   const float NEG = -__int_as_float(0x7f800000);
-  const float floor_f = logits ? -3.402823466e38f : __int_as_float(1);
+  const float floor_f = (logits || no_nms) ? -3.402823466e38f : __int_as_float(1);
   unsigned int* phist = phists + (size_t)b * kSeedHist;
   unsigned int* pvals = pvals_all + (size_t)b * n_vals;  // [items][kSeedRows] ordered scores, 0 = no peak
 
@@ -585,291 +664,202 @@ decode_seed_kernel(const float* __restrict__ heat, int C, int H, int W, int K, i
   }
 }
 
-// decode_stream_kernel: one CTA per 32 KB of one image's logits, read as a flat float4 stream with 8
-// independent 16-byte loads per thread in flight.  The only per-cell work is "max of 4 >= bound";
-// the few float4s that pass (~0.3 %) go to a shared-memory list and are peak-tested afterwards,
-// one thread per cell, with the 8 neighbours re-read through L2.  Peaks at or above the bound are
-// appended to the image's key list and counted in its histogram, exactly as in the staged kernel, so
-// the finalize kernel is shared.  A list overflow (ties / plateaus at the bound) hands the image to the
-// staged path, which is exact for any input.
-constexpr int kStrThreads = 256, kStrU = 8;
-constexpr int kStrChunk = kStrThreads * kStrU;   // float4s per CTA
-constexpr int kStrList = 1024;                   // hit float4s remembered per CTA
-constexpr int kStreamCap = 16384;                // keys per image on this path
+// decode_stream_kernel: the sweep proper -- a lean TMA-staged threshold sweep.  One CTA (4 warps) per tile = a
+// band of `rows` full-width rows of one class plane (~32 KB) plus its two halo rows: CONTIGUOUS in memory, so one
+// elected thread moves the whole tile into shared memory with ONE 1-D bulk async copy (mbarrier completion; issued
+// before griddepcontrol.wait -- the logits do not depend on the seed kernel).  Shared memory, not registers, is
+// the in-flight buffer: 6 CTAs x 34 KB = 200 KB per SM on the way at any time, with ~40 registers per thread.
+// While the tile is in flight warp 0 derives the image's bound from the sample histogram (two dependent L2 reads
+// that cost nothing behind the copy).  After the wait each warp walks its rows in a small ROLLED loop: one
+// conflict-free 16-byte shared-memory load per lane and row, "max of the lane's 4 cells >= bound", a vote; the ~1/4
+// of the rows where some lane passes run the 3x3 test on the neighbouring rows in shared memory.  Passing cells are
+// recorded in a per-lane 64-bit map and written to the TILE's own segment of the key list (count + keys): no list
+// reservation, no atomic at all.  One CTA barrier, no bitmap, no histogram, nothing read twice from DRAM (a band's
+// halo rows are its neighbours' own rows, in flight at the same time: L2 hits).
+// Forms of this kernel that were built, parity-green, and rejected (B = 32, 128x128x80, ncu durations):
+//   flat float4 stream, hits re-tested with neighbours through L2 (round 1)                          40.8 us
+//   18 rows in registers per warp, fully unrolled: 8 K instructions, instruction-cache-bound
+//     (13 "no instruction" stall cycles per issue)                                                   180 us
+//   the same with the row test out of line                                                           70 us
+//   rolled ring of 8 register rows per lane (2.5 KB in flight per warp, 24 warps / SM: latency)      66 us
+//   this kernel with ONE key list per image and a warp-aggregated reservation: ~1200 returning
+//     same-address atomics per image, ~75 ns each                                                    87 us
+//   per-tile segments, 16 KB tiles, generic strips: issue-bound (755 instructions / warp, 77 %)      38 us
+// A segment overflow (ties / plateaus at the bound) hands the image to the staged path, exact for any input.
+constexpr int kStrThreads = 128;
+constexpr int kStrWarps = kStrThreads / 32;
+constexpr int kTileCap = 64;                     // keys per tile on this path (~20 at K = 100)
 
-__device__ __forceinline__ void stream_test_cell(const float* __restrict__ img, uint32_t flat, int H, int W,
-                                                 FastDiv div_hw, FastDiv div_w, float thv, uint32_t thr_ord, bool no_nms,
-                                                 DecodeHeader* hdr, unsigned int* shist, u64* skeys) {
-  const float v = __ldg(img + flat);
-  if (!(v >= thv)) return;
-  const uint32_t ord = float_to_ordered(v);
-  if (ord < thr_ord) return;                                  // -0.0 against a +0.0 bound
-  if (!no_nms) {
-    const uint32_t c = div_hw.div(flat), sp = flat - c * (uint32_t)(H * W);
-    const int y = (int)div_w.div(sp), x = (int)sp - y * W;
-    const float* q = img + flat;
-    const bool up = y > 0, dn = y < H - 1, lf = x > 0, rt = x < W - 1;
-    const float NEG = -__int_as_float(0x7f800000);
-    float nb = NEG;
-    if (up) { nb = fmaxf(nb, __ldg(q - W)); if (lf) nb = fmaxf(nb, __ldg(q - W - 1)); if (rt) nb = fmaxf(nb, __ldg(q - W + 1)); }
-    if (dn) { nb = fmaxf(nb, __ldg(q + W)); if (lf) nb = fmaxf(nb, __ldg(q + W - 1)); if (rt) nb = fmaxf(nb, __ldg(q + W + 1)); }
-    if (lf) nb = fmaxf(nb, __ldg(q - 1));
-    if (rt) nb = fmaxf(nb, __ldg(q + 1));
-    if (!(v >= nb)) return;
-  }
-  // one reservation per warp: the image's counter is a single address, and ~3000 returning atomics per image
-  // serialise in L2 (measured in a persistent variant of this kernel: they, not the sweep, set its time).
-  // All lanes of a warp work on the same image here.
-  const unsigned int peers = __activemask();
-  const int leader = __ffs(peers) - 1, lane = threadIdx.x & 31;
-  unsigned int base = 0;
-  if (lane == leader) base = atomicAdd(&hdr->s_count, (unsigned)__popc(peers));
-  base = __shfl_sync(peers, base, leader);
-  const unsigned int pos = base + (unsigned)__popc(peers & ((1u << lane) - 1u));
-  if (pos < (unsigned)kStreamCap) {
-    skeys[pos] = ((u64)ord << 32) | (u64)(0xffffffffu - flat);
-    atomicAdd(shist + (ord >> kHistShift), 1u);
-  } else {
-    hdr->staged = 1u;
-  }
-}
-
-__global__ void __launch_bounds__(kStrThreads, 4)
-decode_stream_kernel(const float* __restrict__ heat, int C, int H, int W, int n4, int chunks, int flags,
-                     FastDiv div_hw, FastDiv div_w, int K, DecodeHeader* __restrict__ hdrs,
+template <bool kOneStrip>                        // W <= 128: a row is one warp-wide float4 load
+__global__ void __launch_bounds__(kStrThreads)
+decode_stream_kernel(const float* __restrict__ heat, int C, int H, int W, int band_rows, int bands, int flags, int K,
+                     FastDiv div_bands, FastDiv div_strips, DecodeHeader* __restrict__ hdrs,
                      const unsigned int* __restrict__ phists, const unsigned int* __restrict__ pvals_all, int n_vals,
-                     unsigned int* __restrict__ shists, u64* __restrict__ skeys_all) {
-  __shared__ uint32_t s_list[kStrList];
-  __shared__ unsigned int s_sub[kStrThreads / 32][32];        // per-warp 32-bin histogram of the refinement
-  __shared__ int s_n;
-  const int tid = threadIdx.x;
+                     u64* __restrict__ skeys_all, unsigned int* __restrict__ scnt_all) {
+  extern __shared__ __align__(128) unsigned char s_raw[];
+  __shared__ __align__(8) uint64_t s_bar;
+  __shared__ int s_wtot[kStrWarps];
+  __shared__ unsigned int s_sub[32];
+  __shared__ unsigned int s_thr, s_skip;
+  float* tile = reinterpret_cast<float*>(s_raw);              // [(band_rows + 2)][W]; tile row t <-> map row y_lo - 1 + t
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int b = blockIdx.y;
+  const int c = (int)div_bands.div(blockIdx.x), band = (int)blockIdx.x - c * bands;
+  const int y_lo = band * band_rows, y_hi = min(H, y_lo + band_rows);
+  const int nrows = y_hi - y_lo;
+  const float* plane = heat + ((size_t)b * C + c) * H * W;
   DecodeHeader* hdr = hdrs + b;
-  const float* img = heat + (size_t)b * n4 * 4;
   const float NEG = -__int_as_float(0x7f800000);
-  float4 q[kStrU];
-  auto load_chunk = [&](int chunk) {
-    const int base = chunk * kStrChunk + tid;
-#pragma unroll
-    for (int u = 0; u < kStrU; ++u) {
-      const int i = base + u * kStrThreads;
-      q[u] = i < n4 ? ldg_stream4(img + (size_t)i * 4) : make_float4(NEG, NEG, NEG, NEG);
-    }
-  };
-  if (tid == 0) s_n = 0;
-  __syncthreads();
-  int chunk = blockIdx.x;
-  load_chunk(chunk);                   // the logits do not depend on the seed kernel: in flight before the wait
+
+  const int g_first = max(y_lo - 1, 0), g_last = min(y_hi, H - 1);      // map rows that exist
+  if (tid == 0) {
+    mbar_init(&s_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    const unsigned bytes = (unsigned)((g_last - g_first + 1) * W * sizeof(float));
+    mbar_expect_tx(&s_bar, bytes);
+    bulk_g2s(tile + (size_t)(g_first - (y_lo - 1)) * W, plane + (size_t)g_first * W, bytes, &s_bar);
+  }
+  if (y_lo == 0) for (int x = tid; x < W; x += kStrThreads) tile[x] = NEG;                      // max_pool2d padding (:401)
+  if (y_hi == H) for (int x = tid; x < W; x += kStrThreads) tile[(size_t)(nrows + 1) * W + x] = NEG;
   pdl_wait();
-  pdl_launch_dependents();
-  // EVERY warp, under the latency of the loads above, on its own (no barrier, no broadcast: the warps of a CTA
-  // stay independent until the epilogue): the highest bin of the image's SAMPLE histogram whose suffix count
-  // reaches K -- two dependent 256/128-byte reads: the 64 coarse bins (32 fine bins each), then the 32 fine
-  // bins of the coarse bin that holds the K-th entry.  Lane 0 owns the highest bins.
-  unsigned int thr_ord = 0u;
-  bool mine = false;                                          // warp-uniform; false: this warp only joins the barrier
-  {
-    const int lane = tid & 31;
-    const unsigned int* ph = phists + (size_t)b * kSeedHist;
-    const unsigned int was_staged = *((volatile unsigned int*)&hdr->staged);                 // (an overflow elsewhere)
-    const uint2 c2 = __ldcg(reinterpret_cast<const uint2*>(ph + kHistBins) + (31 - lane));  // coarse 62-2l, 63-2l
-    const unsigned int sum = c2.x + c2.y;
-    unsigned int incl = sum;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const unsigned int t = __shfl_up_sync(0xffffffffu, incl, o);
-      if (lane >= o) incl += t;
-    }
-    const unsigned int excl = incl - sum;
-    const unsigned int hit = __ballot_sync(0xffffffffu, excl < (unsigned)K && incl >= (unsigned)K);
-    unsigned int ord = 0u;
-    if (hit) {
-      const int src = __ffs(hit) - 1;
-      const bool upper = excl + c2.y >= (unsigned)K;          // meaningful on lane src only
-      const int coarse = __shfl_sync(0xffffffffu, upper ? 63 - 2 * lane : 62 - 2 * lane, src);
-      const unsigned int before = __shfl_sync(0xffffffffu, upper ? excl : excl + c2.y, src);
-      const unsigned int f = __ldcg(ph + coarse * 32 + (31 - lane));                         // descending by lane
-      unsigned int fi = f;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const unsigned int t = __shfl_up_sync(0xffffffffu, fi, o);
-        if (lane >= o) fi += t;
-      }
-      const unsigned int hit2 = __ballot_sync(0xffffffffu, before + fi - f < (unsigned)K && before + fi >= (unsigned)K);
-      if (hit2) {
-        const int l2 = __ffs(hit2) - 1;
-        ord = (unsigned int)(coarse * 32 + 31 - l2) << kHistShift;
-        // Concentrated scores (e.g. a random-init head: every logit within +-0.3 of the -2.19 bias) put most of the
-        // sample into this one quarter-octave bin, and its lower edge would pass the whole image.  Then refine
-        // on the sample itself, 5 more bits per round: a per-warp 32-bin histogram of the samples that share the
-        // prefix found so far, same suffix-count rule.  Still a valid lower bound: >= K samples are >= it.
-        unsigned int in_bin = __shfl_sync(0xffffffffu, f, l2);
-        unsigned int need = (unsigned)K - __shfl_sync(0xffffffffu, before + fi - f, l2);
-        unsigned int prefix = ord >> kHistShift;
-        int shift = kHistShift;
-        const unsigned int* pv = pvals_all + (size_t)b * n_vals;
-        unsigned int* sub = s_sub[tid >> 5];
-        // only when the bin really is crowded (a normal image has n_vals / 30 or so samples in it, and every warp
-        // of every CTA runs this code): then keep going until the sub-bin is small
-        const unsigned int crowded = max(2u * (unsigned)K, (unsigned)n_vals / 8u);
-        if (in_bin > crowded)
-        while (in_bin > 24u && shift >= 5) {
-          sub[lane] = 0u;
-          __syncwarp();
-          for (int i = lane; i < n_vals; i += 32) {
-            const unsigned int v = __ldcg(pv + i);
-            if ((v >> shift) == prefix) atomicAdd(&sub[(v >> (shift - 5)) & 31u], 1u);
-          }
-          __syncwarp();
-          const unsigned int cnt = sub[31 - lane];                // descending by lane
-          unsigned int ci = cnt;
-#pragma unroll
-          for (int o = 1; o < 32; o <<= 1) {
-            const unsigned int t = __shfl_up_sync(0xffffffffu, ci, o);
-            if (lane >= o) ci += t;
-          }
-          const unsigned int h3 = __ballot_sync(0xffffffffu, ci - cnt < need && ci >= need);
-          __syncwarp();
-          if (!h3) break;                                          // (cannot happen: the bin holds >= need samples)
-          const int l3 = __ffs(h3) - 1;
-          prefix = (prefix << 5) | (unsigned)(31 - l3);
-          shift -= 5;
-          need -= __shfl_sync(0xffffffffu, ci - cnt, l3);
-          in_bin = __shfl_sync(0xffffffffu, cnt, l3);
-        }
-        ord = prefix << shift;
+  if (warp == 0) {                     // the image's bound, while the tile is in flight
+    const unsigned int was_staged = *((volatile unsigned int*)&hdr->staged);        // (an overflow elsewhere)
+    const unsigned int ord = seed_bound_of_image(phists + (size_t)b * kSeedHist, pvals_all + (size_t)b * n_vals, n_vals, K, s_sub);
+    if (lane == 0) {
+      s_thr = ord;
+      s_skip = (ord == 0u || was_staged) ? 1u : 0u;
+      if (blockIdx.x == 0) {           // for the tail kernel (every streamed key is >= it) and the staged fall-back
+        if (ord == 0u) hdr->staged = 1u;                      // no usable sample bound: the staged path owns the image
+        else hdr->thr_ord = ord;
       }
     }
-    if (ord == 0u) {                                          // no usable sample bound: the staged path owns the image
-      if (tid == 0 && blockIdx.x == 0) hdr->staged = 1u;
-    } else {
-      thr_ord = ord;
-      mine = !__shfl_sync(0xffffffffu, was_staged, 0);
-      if (tid == 0 && blockIdx.x == 0) atomicMax(&hdr->thr_ord, ord);   // head start for the staged path after an overflow
-    }
+  }
+  __syncthreads();                                            // bound, barrier init, padding rows
+  const size_t tile_id = (size_t)b * gridDim.x + blockIdx.x;
+  const unsigned int thr_ord = s_thr;
+  if (s_skip) {                                               // CTA-uniform
+    if (tid == 0) scnt_all[tile_id] = 0u;
+    mbar_wait(&s_bar, 0);                                     // (the copy must land before the CTA's memory is released)
+    pdl_launch_dependents();
+    return;
   }
   const bool logits = flags & CTDET_DECODE_LOGITS;
   const bool no_nms = flags & CTDET_DECODE_NO_NMS;
-  const float thv = fmaxf(ordered_to_float(thr_ord), logits ? -3.402823466e38f : __int_as_float(1));
-  unsigned int* shist = shists + (size_t)b * kHistBins;
-  u64* skeys = skeys_all + (size_t)b * kStreamCap;
-  while (mine) {
-    const int base = chunk * kStrChunk + tid;
+  const float thv = fmaxf(ordered_to_float(thr_ord), (logits || no_nms) ? -3.402823466e38f : __int_as_float(1));
+  const int strips = kOneStrip ? 1 : (int)div_strips.d;
+  const int pairs = nrows * strips;                           // (row, 128-column strip) work items of the tile
+  // a warp takes a contiguous run of at most 16 pairs: the per-lane hit map is 64 bits
+  const int per_warp = (pairs + kStrWarps - 1) / kStrWarps;
+  const int p0 = warp * per_warp, pn = min(per_warp, pairs - p0);
+  const bool lane_in = kOneStrip ? (lane * 4 < W) : true;
+  const float thl = lane_in ? thv : __int_as_float(0x7f800000);         // lanes beyond the map never pass
+  mbar_wait(&s_bar, 0);
+
+  unsigned long long hits = 0ull;
+  const float* rowp1 = tile + (size_t)(p0 + 1) * W + (lane_in ? lane * 4 : 0);      // kOneStrip: pair = row
+  for (int i = 0; i < pn; ++i) {
+    const float* rowp;
+    int x0;
+    bool in;
+    if (kOneStrip) {
+      rowp = rowp1 + (size_t)i * W; x0 = lane * 4; in = lane_in;
+    } else {
+      const int pr = p0 + i;
+      const int t = (int)div_strips.div((uint32_t)pr), strip = pr - t * strips;    // tile row t + 1
+      x0 = strip * 128 + lane * 4;
+      in = x0 < W;
+      rowp = tile + (size_t)(t + 1) * W + (in ? x0 : 0);
+    }
+    const float4 cur = *reinterpret_cast<const float4*>(rowp);
+    const float m = fmaxf(fmaxf(cur.x, cur.y), fmaxf(cur.z, cur.w));
+    const bool mine = m >= (kOneStrip ? thl : (in ? thv : __int_as_float(0x7f800000)));
+    {
+      if (mine) {                                             // ~1/4 of the rows, 1-2 lanes of the warp
+        // per passing cell (usually one of the four): its 8 neighbours straight from shared memory
+        const float v[4] = {cur.x, cur.y, cur.z, cur.w};
+        unsigned bits = 0u;
 #pragma unroll
-    for (int u = 0; u < kStrU; ++u) {
-      const float m = fmaxf(fmaxf(q[u].x, q[u].y), fmaxf(q[u].z, q[u].w));
-      if (m >= thv) {
-        const uint32_t i = (uint32_t)(base + u * kStrThreads);
-        const int pos = atomicAdd(&s_n, 1);
-        if (pos < kStrList) {
-          s_list[pos] = i;
-        } else {                                              // list full: test the 4 cells right here
-          for (int j = 0; j < 4; ++j)
-            stream_test_cell(img, i * 4u + j, H, W, div_hw, div_w, thv, thr_ord, no_nms, hdr, shist, skeys);
+        for (int j = 0; j < 4; ++j) {
+          if (v[j] >= thv && float_to_ordered(v[j]) >= thr_ord) {                 // (-0.0 against a +0.0 bound)
+            bool pk = no_nms;
+            if (!pk) {
+              const float* q = rowp + j;
+              float nbm = fmaxf(q[-W], q[W]);
+              if (j > 0 || x0 > 0) nbm = fmaxf(nbm, fmaxf(fmaxf(q[-W - 1], q[-1]), q[W - 1]));
+              if (j < 3 || x0 + 4 < W) nbm = fmaxf(nbm, fmaxf(fmaxf(q[-W + 1], q[1]), q[W + 1]));
+              pk = v[j] >= nbm || (logits && same_prob(v[j], nbm));
+            }
+            bits |= (unsigned)pk << j;
+          }
         }
+        hits |= (unsigned long long)bits << (4 * i);
       }
     }
-    chunk += gridDim.x;
-    if (chunk >= chunks) break;
-    load_chunk(chunk);
   }
+  // ---- emit into the TILE's own segment of the key list; the tail kernel gathers the segments ------------------
+  const int mine_n = __popcll(hits);
+  int incl = mine_n;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  if (lane == 31) s_wtot[warp] = incl;
   __syncthreads();
-  const int n = min(s_n, kStrList) * 4;
-  for (int e = tid; e < n; e += kStrThreads)
-    stream_test_cell(img, s_list[e >> 2] * 4u + (uint32_t)(e & 3), H, W, div_hw, div_w, thv, thr_ord, no_nms, hdr, shist, skeys);
+  int base = 0, total = 0;
+#pragma unroll
+  for (int w = 0; w < kStrWarps; ++w) { const int t = s_wtot[w]; if (w < warp) base += t; total += t; }
+  pdl_launch_dependents();
+  if (tid == 0) {
+    scnt_all[tile_id] = total <= kTileCap ? (unsigned)total : 0u;
+    if (total > kTileCap) hdr->staged = 1u;                   // ties / plateaus at the bound: the staged path redoes the image
+  }
+  if (total > kTileCap) return;
+  u64* dst = skeys_all + tile_id * kTileCap + base + (incl - mine_n);
+  while (hits) {
+    const int bit = __ffsll((long long)hits) - 1;
+    hits &= hits - 1ull;
+    const int pr = p0 + (bit >> 2);
+    const int t = kOneStrip ? pr : (int)div_strips.div((uint32_t)pr), strip = kOneStrip ? 0 : pr - t * strips;
+    const int x = strip * 128 + lane * 4 + (bit & 3);
+    const float v = tile[(size_t)(t + 1) * W + x];
+    const uint32_t flat = (uint32_t)((c * H + (y_lo + t)) * W + x);
+    *dst++ = ((u64)float_to_ordered(v) << 32) | (u64)(0xffffffffu - flat);
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
-// Kernel 2: per image, exact top-K of the emitted keys, sort, gather, boxes.
+// Tail kernel: per image, exact top-K of the emitted keys, sort, gather, boxes -- and, for the images the sweep
+// handed over, the staged fall-back itself (no separate, normally empty launch).
 constexpr int kSelCap = 2048;
+#ifdef CTDET_DECODE_TIMING
+__device__ unsigned long long g_tail_ts[64][8];
+__device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#define TAIL_TS(i) do { if (threadIdx.x == 0 && blockIdx.x < 64) g_tail_ts[blockIdx.x][i] = gtime(); } while (0)
+#else
+#define TAIL_TS(i) do {} while (0)
+#endif
+constexpr int kTailHelpers = 4;                  // CTAs per image that share the tiles of a handed-over image
+constexpr int kTailSmemKeys = 6144;              // keys of an image held in shared memory by its tail CTA (48 KB)
 
-__global__ void __launch_bounds__(kFinThreads)
-decode_finalize_kernel(DecodeHeader* __restrict__ hdrs, unsigned int* __restrict__ ghists,
-                       const u64* __restrict__ keys, size_t keys_per_image,
-                       unsigned int* __restrict__ shists, const u64* __restrict__ skeys,   // streaming path (or null)
-                       unsigned int* __restrict__ phists,
-                       const float* __restrict__ wh, const float* __restrict__ reg, int C, int H,
-                       int W, int K, float down_ratio, int flags, float* __restrict__ boxes,
-                       float* __restrict__ scores, int32_t* __restrict__ classes,
-                       int64_t* __restrict__ inds) {
-  __shared__ SelectScratch sc;
-  __shared__ BinScratch bs;
-  __shared__ __align__(16) u64 s_sel[kSelCap];
-  __shared__ int s_n;
+struct FinShared {
+  SelectScratch sc;
+  BinScratch bs;
+  __align__(16) u64 sel[kSelCap];
+  unsigned int h2[kHistBins];
+  int rank[kFinThreads];
+  int n, above;
+  unsigned int last, maxord;
+};
+
+// Output stage shared by both list sources: fs->sel holds fs->n >= min(#candidates, K) keys that contain the K best.
+__device__ void finalize_emit(FinShared* fs, int b, const float* __restrict__ wh, const float* __restrict__ reg,
+                              int C, int H, int W, int K, float down_ratio, int flags, float* __restrict__ boxes,
+                              float* __restrict__ scores, int32_t* __restrict__ classes, int64_t* __restrict__ inds) {
   const int tid = threadIdx.x;
-  const int b = blockIdx.x;
-  DecodeHeader* hdr = hdrs + b;
-  pdl_wait();
-  // which path produced this image's list (CTA-uniform; the header is reset only after the barriers below)
-  const bool staged = (skeys == nullptr) || hdr->staged != 0u;
-  const u64* kb = staged ? keys + (size_t)b * keys_per_image : skeys + (size_t)b * kStreamCap;
-  unsigned int* ghist = (staged ? ghists : shists) + (size_t)b * kHistBins;
-  const int n_keys = staged ? (int)hdr->count : (int)hdr->s_count;   // s_count <= kStreamCap unless staged
   const int HW = H * W;
-
-  if (tid == 0) s_n = 0;
-  // The list is read by ONE CTA: every pass keeps 8 loads per thread in flight (a plain loop exposes
-  // one L2 round trip per 512 keys).  f is called for every key of the list; 0 = no key.
-  auto scan_keys = [&](auto f) {
-    for (int i0 = 0; i0 < n_keys; i0 += 8 * kFinThreads) {
-      u64 kk[8];
-#pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const int i = i0 + u * kFinThreads + tid;
-        kk[u] = i < n_keys ? __ldcg(kb + i) : 0ull;       // real keys are never 0 (low word = ~flat index)
-      }
-#pragma unroll
-      for (int u = 0; u < 8; ++u) f(kk[u]);
-    }
-  };
-  // every collected peak of the image was counted once in ghist: its K-th best bin is final now
-  find_threshold_bin<kFinThreads>(ghist, K, &bs);
-  u64 T = ((u64)bs.bin << kHistShift) << 32;
-  if (bs.cnt_ge < (unsigned)K) T = 0ull;                  // fewer than K peaks in the whole image
-  if (T != 0ull && bs.cnt_ge > (unsigned)kFinThreads) {
-    // The 11-bit bins are coarse near the top (sign + exponent + 2 mantissa bits: all of [0.875, 1) is one
-    // bin, ~3800 peaks of a 512^2 image).  Refine once: histogram the NEXT 11 bits of the keys inside the
-    // threshold bin (shared memory), find the sub-bin of the K-th best and collect from there up --
-    // K plus a handful of keys, which the rank sort below takes.  Two passes over the list instead of
-    // the 8 of an exact radix select, which remains the fall-back when ties keep the count too high.
-    __shared__ unsigned int s_h2[kHistBins];
-    __shared__ int s_above;
-    const uint32_t tbin = (uint32_t)bs.bin;
-    for (int i = tid; i < kHistBins; i += kFinThreads) s_h2[i] = 0u;
-    if (tid == 0) s_above = 0;
-    __syncthreads();
-    int above = 0;
-    scan_keys([&](u64 key) {
-      const uint32_t ord = (uint32_t)(key >> 32), ob = ord >> kHistShift;
-      if (key == 0ull || ob < tbin) return;
-      if (ob > tbin) ++above;
-      else atomicAdd(&s_h2[(ord >> (kHistShift - kHistBits)) & (kHistBins - 1)], 1u);
-    });
-    above = warp_sum(above);
-    if ((tid & 31) == 0 && above) atomicAdd(&s_above, above);
-    __syncthreads();
-    const int hi = s_above;                               // < K: that is what made tbin the threshold bin
-    find_threshold_bin<kFinThreads, true>(s_h2, K - hi, &bs);
-    if ((unsigned)hi + bs.cnt_ge <= (unsigned)kSelCap) {
-      T = (u64)((tbin << kHistShift) | ((uint32_t)bs.bin << (kHistShift - kHistBits))) << 32;
-    } else {
-      T = radix_select_kth<kFinThreads>(
-          [&](auto f) { for (int i = tid; i < n_keys; i += kFinThreads) f(kb[i]); }, n_keys, K, &sc);
-    }
-  }
-  __syncthreads();
-  scan_keys([&](u64 key) {
-    if (key != 0ull && key >= T) { const int pos = atomicAdd(&s_n, 1); if (pos < kSelCap) s_sel[pos] = key; }
-  });
-  for (int i = tid; i < kHistBins; i += kFinThreads) ghist[i] = 0u;     // leave the workspace zeroed
-  if (skeys != nullptr) {
-    for (int i = tid; i < kSeedHist; i += kFinThreads) phists[(size_t)b * kSeedHist + i] = 0u;   // sample histogram
-    if (staged)                                                         // overflowed streaming pass: its histogram too
-      for (int i = tid; i < kHistBins; i += kFinThreads) shists[(size_t)b * kHistBins + i] = 0u;
-  }
-  __syncthreads();
-  if (tid == 0) { hdr->count = 0u; hdr->thr_ord = 0u; hdr->s_count = 0u; hdr->staged = 0u; }
-  int n = min(s_n, kSelCap);                              // >= min(#peaks, K)
+  u64* s_sel = fs->sel;
+  int n = min(fs->n, kSelCap);                            // >= min(#peaks, K)
   // fewer than K peaks: the reference's heat*keep zeros fill the rest (:405); by the tie rule
   // these are the lowest flat indices that are not selected peaks.
   if (n < K && tid == 0) {
@@ -888,7 +878,7 @@ decode_finalize_kernel(DecodeHeader* __restrict__ hdrs, unsigned int* __restrict
     // of the list (two keys per 16-byte shared-memory broadcast load); partial ranks are combined
     // with shared-memory atomics.  No barriers inside the compare loop (a bitonic network of this
     // size costs ~36 __syncthreads).
-    __shared__ int s_rank[kFinThreads];
+    int* s_rank = fs->rank;
     int P2 = 32; while (P2 < n) P2 <<= 1;
     const int parts = kFinThreads / P2, idx = tid & (P2 - 1), part = tid / P2;
     s_rank[tid] = 0;
@@ -940,10 +930,7 @@ decode_finalize_kernel(DecodeHeader* __restrict__ hdrs, unsigned int* __restrict
     float score = 0.f;
     if (ord != 0u) {
       score = ordered_to_float(ord);
-      if (flags & CTDET_DECODE_LOGITS) {
-        score = 1.f / (1.f + expf(-score));
-        score = fminf(fmaxf(score, 1e-4f), 1.f - 1e-4f);    // centernet.py:161
-      }
+      if (flags & CTDET_DECODE_LOGITS) score = prob_of_logit(score);   // centernet.py:161
     }
     float xs = (float)(sp % W), ys = (float)(sp / W);        // :414-415
     if (reg != nullptr) {
@@ -972,14 +959,253 @@ decode_finalize_kernel(DecodeHeader* __restrict__ hdrs, unsigned int* __restrict
   }
 }
 
+// Two-level threshold over a key list `kb[0..n_keys)`: level 1 = 2048 bins over the top 11 bits of the ordered
+// score (hist1; every key counted once), level 2 = the next 11 bits inside the threshold bin, histogrammed in
+// shared memory.  Leaves in fs->sel the keys >= the refined threshold: K plus a handful; the exact radix select
+// is the fall-back when ties keep the count above kSelCap.  scan(f) calls f(key) for every key (0 = none).
+template <bool kSharedHist, typename Scan>
+__device__ void finalize_select(FinShared* fs, const unsigned int* hist1, Scan scan, const u64* kb, int n_keys, int K) {
+  const int tid = threadIdx.x;
+  find_threshold_bin<kFinThreads, kSharedHist>(hist1, K, &fs->bs);
+  u64 T = ((u64)fs->bs.bin << kHistShift) << 32;
+  if (fs->bs.cnt_ge < (unsigned)K) T = 0ull;              // fewer than K candidates in the whole image
+  if (T != 0ull && fs->bs.cnt_ge > (unsigned)kFinThreads) {
+    // The 11-bit bins are coarse near the top (sign + exponent + 2 mantissa bits: all of [0.875, 1) is one
+    // bin, ~3800 peaks of a 512^2 image).  Refine once on the NEXT 11 bits of the keys inside the bin.
+    unsigned int* s_h2 = fs->h2;
+    const uint32_t tbin = (uint32_t)fs->bs.bin;
+    for (int i = tid; i < kHistBins; i += kFinThreads) s_h2[i] = 0u;
+    if (tid == 0) fs->above = 0;
+    __syncthreads();
+    int above = 0;
+    scan([&](u64 key) {
+      const uint32_t ord = (uint32_t)(key >> 32), ob = ord >> kHistShift;
+      if (key == 0ull || ob < tbin) return;
+      if (ob > tbin) ++above;
+      else atomicAdd(&s_h2[(ord >> (kHistShift - kHistBits)) & (kHistBins - 1)], 1u);
+    });
+    above = warp_sum(above);
+    if ((tid & 31) == 0 && above) atomicAdd(&fs->above, above);
+    __syncthreads();
+    const int hi = fs->above;                             // < K: that is what made tbin the threshold bin
+    find_threshold_bin<kFinThreads, true>(s_h2, K - hi, &fs->bs);
+    if ((unsigned)hi + fs->bs.cnt_ge <= (unsigned)kSelCap) {
+      T = (u64)((tbin << kHistShift) | ((uint32_t)fs->bs.bin << (kHistShift - kHistBits))) << 32;
+    } else {
+      T = radix_select_kth<kFinThreads>(
+          [&](auto f) { for (int i = tid; i < n_keys; i += kFinThreads) f(kb[i]); }, n_keys, K, &fs->sc);
+    }
+  }
+  __syncthreads();
+  scan([&](u64 key) {
+    if (key != 0ull && key >= T) { const int pos = atomicAdd(&fs->n, 1); if (pos < kSelCap) fs->sel[pos] = key; }
+  });
+}
+
+// (out of line on purpose: the tail kernel runs once, cold -- its time is instruction fetch, so the rarely taken
+// fall-back must not sit in the middle of the hot path)
+__device__ __noinline__ void
+tail_fallback_tile(const float* __restrict__ heat, int C, int H, int W, int Wp, int K, int band_rows, int sub_rows,
+                   FastDiv div_strips, int flags, DecodeHeader* __restrict__ hdrs, unsigned int* __restrict__ ghists,
+                   u64* __restrict__ out_keys, size_t keys_per_image, int band, int b, int c, unsigned char* s_raw, bool reinit) {
+  decode_peaks_tile<kFinThreads>(heat, C, H, W, Wp, K, band_rows, sub_rows, div_strips, flags, hdrs, ghists, out_keys,
+                                 keys_per_image, band, b, c, s_raw, reinit);
+}
+
+// grid = (B + (helpers - 1) * B): CTAs [0, B) are the images' own tail CTAs (scheduled first), the others
+// are helpers that return at once unless their image was handed over.
+//   mode 0 (behind decode_stream_kernel): image not handed over -> CTA b copies the image's key list (<= 16 K
+//     keys, ~3 K typically) into shared memory ONCE, histograms it there and selects -- no global histogram, no
+//     second trip to L2.  Image handed over (hdr->staged) -> its `helpers` CTAs run the staged tiles of the image
+//     (decode_peaks_tile, exact for any input), and the last of them to finish (ticket) finalizes from that list.
+//   mode 1 (behind decode_peaks_kernel, shapes the sweep does not take): finalize from the staged list only.
+__global__ void __launch_bounds__(kFinThreads, 1)
+decode_tail_kernel(const float* __restrict__ heat, int B, int mode, int helpers,
+                   DecodeHeader* __restrict__ hdrs, unsigned int* __restrict__ ghists,
+                   u64* __restrict__ keys, size_t keys_per_image,
+                   const u64* __restrict__ skeys, const unsigned int* __restrict__ scnt, int sw_tiles,
+                   unsigned int* __restrict__ phists,
+                   int Wp, int band_rows, int sub_rows, FastDiv div_strips, int bands,
+                   const float* __restrict__ wh, const float* __restrict__ reg, int C, int H,
+                   int W, int K, float down_ratio, int flags, float* __restrict__ boxes,
+                   float* __restrict__ scores, int32_t* __restrict__ classes,
+                   int64_t* __restrict__ inds) {
+  extern __shared__ __align__(128) unsigned char s_dyn[];   // staged tile | the image's key list (mode 0)
+  __shared__ FinShared fs;
+  const int tid = threadIdx.x;
+  const int b = blockIdx.x < B ? blockIdx.x : (blockIdx.x - B) % B;
+  const int helper = blockIdx.x < B ? 0 : 1 + (blockIdx.x - B) / B;
+  DecodeHeader* hdr = hdrs + b;
+  TAIL_TS(0);
+  pdl_wait();
+  TAIL_TS(1);
+  // this thread's tile counts, requested together with the header (independent loads: one L2 trip, not two)
+  constexpr int kCntPer = 4;                                 // tiles per thread: sw_tiles <= 2048
+  unsigned int my_cnt[kCntPer];
+#pragma unroll
+  for (int u = 0; u < kCntPer; ++u) {
+    const int t = tid * kCntPer + u;
+    my_cnt[u] = (mode == 0 && helper == 0 && t < sw_tiles) ? __ldcg(scnt + (size_t)b * sw_tiles + t) : 0u;
+  }
+  // which path produced this image's list (CTA-uniform; the header is reset only at the very end)
+  const bool staged = (mode == 1) || hdr->staged != 0u;
+  if (!staged && helper != 0) return;
+  const unsigned int thr_lo = *((volatile unsigned int*)&hdr->thr_ord);   // the sweep's bound (every streamed key is >= it)
+  if (tid == 0) { fs.n = 0; fs.last = 1u; }
+  if (staged && mode == 0) {
+    // ---- exact fall-back: this image's tiles, shared by its `helpers` CTAs -----------------------------
+    bool reinit = false;
+    const int tiles = bands * C;
+    for (int t = helper; t < tiles; t += helpers) {
+      const int band = t % bands, c = t / bands;
+      __syncthreads();                                       // the previous tile's shared state is dead
+      tail_fallback_tile(heat, C, H, W, Wp, K, band_rows, sub_rows, div_strips, flags, hdrs, ghists, keys,
+                         keys_per_image, band, b, c, s_dyn, reinit);
+      reinit = true;
+    }
+    __threadfence();                                         // every thread's keys / histogram counts, then the ticket
+    __syncthreads();
+    if (tid == 0) {
+      __threadfence();
+      fs.last = (atomicAdd(&hdr->ticket, 1u) == (unsigned)(helpers - 1)) ? 1u : 0u;
+      __threadfence();
+    }
+  }
+  __syncthreads();
+  if (!fs.last) return;                                      // CTA-uniform: another CTA of the image finalizes
+
+  if (!staged) {
+    // ---- streaming path: the image's keys sit in per-tile segments (count + <= kTileCap keys each) --------------
+    // Block scan of the tile counts (held in registers since the header read) -> exclusive offsets in shared
+    // memory; then the keys are fetched over a FLAT index: key i belongs to the tile found by binary search in the
+    // offsets, so every thread has all its ~7 loads in flight at once: one L2 trip for the whole list.
+    const u64* segs = skeys + (size_t)b * sw_tiles * kTileCap;
+    u64* s_keys = reinterpret_cast<u64*>(s_dyn);
+    unsigned int* s_h1 = reinterpret_cast<unsigned int*>(s_keys + kTailSmemKeys);
+    unsigned int* s_off = s_h1 + kHistBins;                  // [sw_tiles + 1] exclusive offsets
+    const int lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < kHistBins; i += kFinThreads) s_h1[i] = 0u;
+    {
+      unsigned int mine_tot = 0;
+#pragma unroll
+      for (int u = 0; u < kCntPer; ++u) mine_tot += my_cnt[u];
+      unsigned int incl = mine_tot;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { const unsigned int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+      if (lane == 31) fs.bs.warp_tot[warp] = incl;
+      if (tid == 0) fs.maxord = 0u;
+      __syncthreads();
+      unsigned int before = 0;
+      for (int w = 0; w < warp; ++w) before += fs.bs.warp_tot[w];
+      unsigned int run = before + incl - mine_tot;
+#pragma unroll
+      for (int u = 0; u < kCntPer; ++u) {
+        const int t = tid * kCntPer + u;
+        if (t < sw_tiles) s_off[t] = run;
+        run += my_cnt[u];
+      }
+      if (tid == kFinThreads - 1) s_off[sw_tiles] = run;      // (threads past the last tile carry the total)
+    }
+    __syncthreads();
+    TAIL_TS(2);
+    const int n_keys = (int)s_off[sw_tiles];
+    const bool fits = n_keys <= kTailSmemKeys;               // CTA-uniform
+    // calls f(key, i) for every key of the image, i = its flat index.  A thread owns the tiles tid, tid + 512, ...:
+    // its keys are fetched 16 at a time with independent loads (a tile holds ~10 keys: one L2 trip for nearly all).
+    auto scan_tiles = [&](auto f) {
+      for (int tile = tid; tile < sw_tiles; tile += kFinThreads) {
+        const int off = (int)s_off[tile], cnt = (int)s_off[tile + 1] - off;
+        const u64* seg = segs + (size_t)tile * kTileCap;
+        for (int k0 = 0; k0 < cnt; k0 += 16) {
+          u64 kk[16];
+#pragma unroll
+          for (int u = 0; u < 16; ++u) kk[u] = __ldcg(seg + min(k0 + u, cnt - 1));   // (clamped, not predicated: a
+#pragma unroll                                                                      //  select would serialise the loads)
+          for (int u = 0; u < 16; ++u) if (k0 + u < cnt) f(kk[u], off + k0 + u);
+        }
+      }
+    };
+    // pass 1: copy (when it fits) and the largest score
+    unsigned int mx = 0u;
+    scan_tiles([&](u64 key, int slot) {
+      if (slot < kTailSmemKeys) s_keys[slot] = key;
+      mx = max(mx, (unsigned int)(key >> 32));
+    });
+    mx = __reduce_max_sync(0xffffffffu, mx);
+    if (lane == 0 && mx) atomicMax(&fs.maxord, mx);
+    __syncthreads();
+    TAIL_TS(3);
+    if (tid == 0) fs.above = 0;
+    if (n_keys <= kFinThreads) {                             // small list: the rank sort takes it whole
+      for (int i = tid; i < n_keys; i += kFinThreads) fs.sel[i] = s_keys[i];
+      if (tid == 0) fs.n = n_keys;
+    } else {
+      // Every key is >= the sweep's bound, and the K-th best sits a little above it: histogram the keys over
+      // 2048 bins of (ordered score - bound) >> sh, sh chosen from the largest score so that the bins span
+      // exactly [bound, max] -- the keys spread over the whole histogram instead of piling into the 2-3
+      // quarter-octave bins of the plain top bits (shared-memory atomics on one address serialise).
+      const unsigned int lo = thr_lo;
+      const unsigned int range = fs.maxord - lo;
+      int sh = 0;
+      while ((range >> sh) >= (unsigned)kHistBins) ++sh;
+      auto scan = [&](auto f) {
+        if (fits) { for (int i = tid; i < n_keys; i += kFinThreads) f(s_keys[i]); }
+        else scan_tiles([&](u64 key, int) { f(key); });
+      };
+      scan([&](u64 key) { atomicAdd(&s_h1[((unsigned int)(key >> 32) - lo) >> sh], 1u); });
+      __syncthreads();
+      find_threshold_bin<kFinThreads, true>(s_h1, K, &fs.bs);
+      u64 T = 0ull;
+      if (fs.bs.cnt_ge >= (unsigned)K) T = (u64)(lo + ((unsigned int)fs.bs.bin << sh)) << 32;
+      if (fs.bs.cnt_ge > (unsigned)kSelCap)                  // ties: too many keys share the threshold bin
+        T = radix_select_kth<kFinThreads>([&](auto f) { scan([&](u64 key) { f(key); }); }, n_keys, K, &fs.sc);
+      __syncthreads();
+      scan([&](u64 key) {
+        if (key >= T) { const int pos = atomicAdd(&fs.n, 1); if (pos < kSelCap) fs.sel[pos] = key; }
+      });
+    }
+  } else {
+    // ---- staged list (global memory; its per-image histogram was filled by the tiles) ---------------------
+    const u64* kb = keys + (size_t)b * keys_per_image;
+    unsigned int* ghist = ghists + (size_t)b * kHistBins;
+    const int n_keys = (int)*((volatile unsigned int*)&hdr->count);
+    // The list is read by ONE CTA: every pass keeps 8 loads per thread in flight (a plain loop exposes
+    // one L2 round trip per 512 keys).
+    auto scan = [&](auto f) {
+      for (int i0 = 0; i0 < n_keys; i0 += 8 * kFinThreads) {
+        u64 kk[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int i = i0 + u * kFinThreads + tid;
+          kk[u] = i < n_keys ? __ldcg(kb + i) : 0ull;       // real keys are never 0 (low word = ~flat index)
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) f(kk[u]);
+      }
+    };
+    finalize_select<false>(&fs, ghist, scan, kb, n_keys, K);
+    for (int i = tid; i < kHistBins; i += kFinThreads) ghist[i] = 0u;     // leave the workspace zeroed
+  }
+  TAIL_TS(4);
+  if (phists != nullptr)
+    for (int i = tid; i < kSeedHist; i += kFinThreads) phists[(size_t)b * kSeedHist + i] = 0u;   // sample histogram
+  __syncthreads();
+  TAIL_TS(5);
+  if (tid == 0) { hdr->count = 0u; hdr->thr_ord = 0u; hdr->s_count = 0u; hdr->staged = 0u; hdr->ticket = 0u; }
+  finalize_emit(&fs, b, wh, reg, C, H, W, K, down_ratio, flags, boxes, scores, classes, inds);
+  __syncthreads();
+  TAIL_TS(6);
+}
+
 struct DecodePlan {
   int band_rows, bands, tiles_per_image, Wp, strips, sub_rows;
   size_t smem, keys_per_image, header_bytes, hist_bytes, total_bytes;
   // streaming path
   bool stream;
-  int seed_groups, seed_ctas, stream_ctas, n4, seed_vals;
-  size_t skeys_bytes, phist_bytes, pvals_bytes;
-  int stream_chunks;
+  int seed_groups, seed_ctas, seed_vals;
+  int sw_rows, sw_bands; size_t sw_smem;          // sweep: rows per tile, tiles per class plane, shared memory per CTA
+  int tail_sub_rows; size_t tail_smem;            // tail kernel (512 threads)
+  size_t skeys_bytes, scnt_bytes, phist_bytes, pvals_bytes;
 };
 
 static DecodePlan make_plan(int B, int C, int H, int W, int K) {
@@ -1009,17 +1235,34 @@ static DecodePlan make_plan(int B, int C, int H, int W, int K) {
   static int stream_on = -1;
   if (stream_on < 0) { const char* e = getenv("CTDET_DECODE_STREAM"); stream_on = e ? (atoi(e) != 0) : 1; }
   p.seed_groups = (H - 2 - kSeedRows) >= 0 ? (H - 2 - kSeedRows) / kSeedPeriod + 1 : 0;   // r0 + kSeedRows <= H - 1
-  p.stream = stream_on && (W % 4) == 0 && W >= 8 && p.seed_groups > 0;
-  p.n4 = (int)((long long)C * H * W / 4);
-  p.stream_chunks = (p.n4 + kStrChunk - 1) / kStrChunk;
-  p.stream_ctas = (p.stream_chunks + 1) / 2;                    // two 32 KB chunks per CTA
+  p.stream = stream_on && (W % 4) == 0 && W >= 8 && p.seed_groups > 0 && strips <= 64;   // (+ the tile count, below)
+  {
+    static int sw_kb = 0;                                       // tuning knob: CTDET_DECODE_TILE_KB (read once)
+    if (sw_kb == 0) { const char* e = getenv("CTDET_DECODE_TILE_KB"); sw_kb = e ? atoi(e) : 16; if (sw_kb < 1) sw_kb = 16; }
+    int sr = (sw_kb * 1024) / (W * 4);                          // ~16 KB of full-width rows per tile (measured best of 8 / 16 / 32)
+    if (sr * strips > 64) sr = 64 / strips;                     // <= 16 (row, strip) pairs per warp
+    if (sr < 1) sr = 1;
+    if (sr > H) sr = H;
+    p.sw_rows = sr;
+    p.sw_bands = (H + sr - 1) / sr;
+    p.sw_smem = (size_t)(sr + 2) * W * sizeof(float);
+    if ((long long)C * p.sw_bands > 2048) p.stream = false;     // the tail kernel holds 4 tile counts per thread
+  }
+  {
+    int tsubs = (kFinThreads / 32) / strips; if (tsubs < 1) tsubs = 1;
+    p.tail_sub_rows = (rows + tsubs - 1) / tsubs;
+    const size_t list = (size_t)kTailSmemKeys * sizeof(u64) + (size_t)kHistBins * sizeof(unsigned int) +
+                        (size_t)(C * p.sw_bands + 1) * sizeof(unsigned int);
+    p.tail_smem = p.stream ? (p.smem > list ? p.smem : list) : 16;
+  }
   {
     const int items = C * p.seed_groups * strips;               // one warp-item = 6 row segments of 512 B
     p.seed_ctas = (items + kSeedWarps - 1) / kSeedWarps;
     p.seed_vals = items * kSeedRows;
     if (p.seed_ctas < 1) p.seed_ctas = 1;
   }
-  p.skeys_bytes = p.stream ? (size_t)B * kStreamCap * sizeof(u64) : 0;
+  p.scnt_bytes = p.stream ? (((size_t)B * C * p.sw_bands * sizeof(unsigned int)) + 255) / 256 * 256 : 0;
+  p.skeys_bytes = p.stream ? (size_t)B * C * p.sw_bands * kTileCap * sizeof(u64) : 0;
   // sample histograms (zero on entry, left zero: a fixed stride per image, whatever the map shape, because calls
   // of different shapes share one workspace), then the samples themselves (rewritten by every call)
   p.phist_bytes = (((size_t)B * kSeedHist * sizeof(unsigned int)) + 255) / 256 * 256;
@@ -1028,8 +1271,8 @@ static DecodePlan make_plan(int B, int C, int H, int W, int K) {
   // The zero-on-entry regions (headers, the three histogram blocks) come first, at offsets that depend on B only:
   // calls of different map shapes -- with or without the streaming path -- share one workspace per B, and the keys
   // of one layout must never land in what another layout expects to be zero.
-  if (!p.stream) { p.pvals_bytes = 0; p.skeys_bytes = 0; }
-  p.total_bytes = p.header_bytes + 2 * p.hist_bytes + p.phist_bytes + p.pvals_bytes + p.skeys_bytes +
+  if (!p.stream) { p.pvals_bytes = 0; p.skeys_bytes = 0; p.scnt_bytes = 0; }
+  p.total_bytes = p.header_bytes + 2 * p.hist_bytes + p.phist_bytes + p.pvals_bytes + p.scnt_bytes + p.skeys_bytes +
                   (size_t)B * p.keys_per_image * sizeof(u64);
   return p;
 }
@@ -1061,50 +1304,63 @@ extern "C" int ctdet_decode(const float* heat, const float* wh, const float* reg
   if (p.smem > 200 * 1024) return CTDET_EUNSUPPORTED;          // W > ~5000 columns
   cudaStream_t st = (cudaStream_t)stream;
   {
-    cudaError_t e = cudaFuncSetAttribute(decode_peaks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)p.smem);
+    // (the attribute is per function and sticky; setting it costs ~1 us of host time, not a launch)
+    cudaError_t e = cudaFuncSetAttribute(decode_peaks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(decode_tail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.tail_smem);
+
     if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
   }
   unsigned char* base = reinterpret_cast<unsigned char*>(workspace);
   DecodeHeader* hdr = reinterpret_cast<DecodeHeader*>(base);
   unsigned int* ghist = reinterpret_cast<unsigned int*>(base + p.header_bytes);
-  unsigned char* q = base + p.header_bytes + p.hist_bytes;
-  unsigned int* shist = reinterpret_cast<unsigned int*>(q); q += p.hist_bytes;
+  unsigned char* q = base + p.header_bytes + 2 * p.hist_bytes;    // (the second histogram block is unused since r2)
   unsigned int* phist = reinterpret_cast<unsigned int*>(q); q += p.phist_bytes;
   unsigned int* pvals = reinterpret_cast<unsigned int*>(q); q += p.pvals_bytes;
+  unsigned int* scnt = reinterpret_cast<unsigned int*>(q); q += p.scnt_bytes;
   u64* skeys = reinterpret_cast<u64*>(q); q += p.skeys_bytes;
   u64* keys = reinterpret_cast<u64*>(q);
-  if (!p.stream) { shist = nullptr; phist = nullptr; pvals = nullptr; skeys = nullptr; }
+  if (!p.stream) { phist = nullptr; pvals = nullptr; skeys = nullptr; scnt = nullptr; }
   if (B > 65535 || C > 65535) return CTDET_EINVAL;
   int rc;
+  const FastDiv div_strips((uint32_t)p.strips);
   if (p.stream) {
+    // seed (sample bound) -> sweep -> tail, chained with programmatic dependent launch
     decode_seed_kernel<<<dim3(p.seed_ctas, B), kSeedThreads, 0, st>>>(
-        heat, C, H, W, K, flags, p.seed_groups, FastDiv((uint32_t)p.strips), FastDiv((uint32_t)p.seed_groups), phist, pvals, p.seed_vals);
+        heat, C, H, W, K, flags, p.seed_groups, div_strips, FastDiv((uint32_t)p.seed_groups), phist, pvals, p.seed_vals);
     if ((rc = check_launch())) return rc;
-    cudaError_t e = launch_pdl(decode_stream_kernel, dim3(p.stream_ctas, B), dim3(kStrThreads), 0, st,
-                               heat, C, H, W, p.n4, p.stream_chunks, flags, FastDiv((uint32_t)(H * W)),
-                               FastDiv((uint32_t)W), K, hdr, (const unsigned int*)phist, (const unsigned int*)pvals, p.seed_vals, shist, skeys);
+    auto sweep = p.strips == 1 ? decode_stream_kernel<true> : decode_stream_kernel<false>;
+    cudaError_t e = cudaFuncSetAttribute(sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.sw_smem);
+    if (e == cudaSuccess)
+      e = launch_pdl(sweep, dim3(C * p.sw_bands, B), dim3(kStrThreads), p.sw_smem, st,
+                     heat, C, H, W, p.sw_rows, p.sw_bands, flags, K, FastDiv((uint32_t)p.sw_bands), div_strips, hdr,
+                     (const unsigned int*)phist, (const unsigned int*)pvals, p.seed_vals, skeys, scnt);
     if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
     if ((rc = check_launch())) return rc;
-  }
-  const dim3 peaks_grid = p.stream ? dim3(2 * kNumSMs) : dim3(p.bands, B, C);
-  if (p.stream) {
-    cudaError_t e = launch_pdl(decode_peaks_kernel, peaks_grid, dim3(kDecThreads), p.smem, st,
-                               heat, B, C, H, W, p.Wp, K, p.band_rows, p.sub_rows, FastDiv((uint32_t)p.strips), flags,
-                               hdr, ghist, keys, p.keys_per_image, 1, p.bands);
+    e = launch_pdl(decode_tail_kernel, dim3(B * kTailHelpers), dim3(kFinThreads), p.tail_smem, st,
+                   heat, B, 0, kTailHelpers, hdr, ghist, keys, p.keys_per_image, (const u64*)skeys,
+                   (const unsigned int*)scnt, C * p.sw_bands, phist,
+                   p.Wp, p.band_rows, p.tail_sub_rows, div_strips, p.bands,
+                   wh, reg, C, H, W, K, down_ratio, flags, boxes, scores, classes, inds);
     if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
-  } else {
-    decode_peaks_kernel<<<peaks_grid, kDecThreads, p.smem, st>>>(
-        heat, B, C, H, W, p.Wp, K, p.band_rows, p.sub_rows, FastDiv((uint32_t)p.strips), flags, hdr, ghist, keys,
-        p.keys_per_image, 0, p.bands);
+    return check_launch();
   }
-  rc = check_launch();
-  if (rc) return rc;
+  decode_peaks_kernel<<<dim3(p.bands, B, C), kDecThreads, p.smem, st>>>(
+      heat, C, H, W, p.Wp, K, p.band_rows, p.sub_rows, div_strips, flags, hdr, ghist, keys, p.keys_per_image);
+  if ((rc = check_launch())) return rc;
   {
-    cudaError_t e = launch_pdl(decode_finalize_kernel, dim3(B), dim3(kFinThreads), 0, st,
-                               hdr, ghist, (const u64*)keys, p.keys_per_image, shist, (const u64*)skeys, phist, wh, reg,
-                               C, H, W, K, down_ratio, flags, boxes, scores, classes, inds);
+    cudaError_t e = launch_pdl(decode_tail_kernel, dim3(B), dim3(kFinThreads), p.tail_smem, st,
+                               heat, B, 1, 1, hdr, ghist, keys, p.keys_per_image, (const u64*)nullptr,
+                               (const unsigned int*)nullptr, 0, (unsigned int*)nullptr,
+                               p.Wp, p.band_rows, p.tail_sub_rows, div_strips, p.bands,
+                               wh, reg, C, H, W, K, down_ratio, flags, boxes, scores, classes, inds);
     if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
   }
   return check_launch();
 }
+
+#ifdef CTDET_DECODE_TIMING
+extern "C" int ctdet_debug_tail_times(unsigned long long* out /* [64][8] host */) {
+  return cudaMemcpyFromSymbol(out, ctdet::g_tail_ts, sizeof(unsigned long long) * 64 * 8) == cudaSuccess ? 0 : 1;
+}
+#endif

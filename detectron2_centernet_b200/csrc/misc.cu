@@ -60,20 +60,25 @@ __global__ void postprocess_kernel(float* __restrict__ boxes, float* __restrict_
   const int b = blockIdx.x, tid = threadIdx.x;
   const int in_h = sizes[4 * b], in_w = sizes[4 * b + 1];
   const int out_h = sizes[4 * b + 2], out_w = sizes[4 * b + 3];
-  const float sx = (float)((double)out_w / (double)in_w);   // postprocessing.py:39-42: python-float
-  const float sy = (float)((double)out_h / (double)in_h);   // quotient, applied to an fp32 tensor
+  const float sx = (float)((double)out_w / (double)max(in_w, 1));   // postprocessing.py:39-42: python-float
+  const float sy = (float)((double)out_h / (double)max(in_h, 1));   // quotient, applied to an fp32 tensor
   const int n = min(max_dets, K);                   // centernet.py:252
   float* bx = boxes + (size_t)b * K * 4;
   float* sc = scores + (size_t)b * K;
   int32_t* cl = classes + (size_t)b * K;
+  // out_h <= 0: CenterNet.inference alone (centernet.py:214-266) -- slice + threshold, the boxes stay as decoded;
+  // detector_postprocess (scale, clip, nonempty) is what the reference's forward applies afterwards (:169-171)
+  const bool resize = out_h > 0 && out_w > 0;
   for (int k = tid; k < K; k += blockDim.x) {
-    float x1 = bx[4 * k] * sx, y1 = bx[4 * k + 1] * sy;          // Boxes.scale (boxes.py:271)
-    float x2 = bx[4 * k + 2] * sx, y2 = bx[4 * k + 3] * sy;
-    x1 = fminf(fmaxf(x1, 0.f), (float)out_w); x2 = fminf(fmaxf(x2, 0.f), (float)out_w);   // Boxes.clip (:184)
-    y1 = fminf(fmaxf(y1, 0.f), (float)out_h); y2 = fminf(fmaxf(y2, 0.f), (float)out_h);
+    float x1 = bx[4 * k], y1 = bx[4 * k + 1], x2 = bx[4 * k + 2], y2 = bx[4 * k + 3];
+    bool keep = (k < n) && (sc[k] > thresh);                      // strict > (centernet.py:258)
+    if (resize) {
+      x1 *= sx; y1 *= sy; x2 *= sx; y2 *= sy;                     // Boxes.scale (boxes.py:271)
+      x1 = fminf(fmaxf(x1, 0.f), (float)out_w); x2 = fminf(fmaxf(x2, 0.f), (float)out_w);   // Boxes.clip (:184)
+      y1 = fminf(fmaxf(y1, 0.f), (float)out_h); y2 = fminf(fmaxf(y2, 0.f), (float)out_h);
+      keep = keep && ((x2 - x1) > 0.f) && ((y2 - y1) > 0.f);      // Boxes.nonempty (:199)
+    }
     s_box[4 * k] = x1; s_box[4 * k + 1] = y1; s_box[4 * k + 2] = x2; s_box[4 * k + 3] = y2;
-    const bool keep = (k < n) && (sc[k] > thresh) &&              // strict > (centernet.py:258)
-                      ((x2 - x1) > 0.f) && ((y2 - y1) > 0.f);     // Boxes.nonempty (:199)
     s_pos[k] = keep ? 1 : 0;
   }
   __syncthreads();

@@ -164,6 +164,8 @@ int ctdet_gather_feat(const float* feat, const int64_t* ind, int B, int Ch, int 
  * min(max_dets,K) detections with score > score_thresh, scale boxes by
  * (out_w/in_w, out_h/in_h), clip to the output size, drop empty boxes; survivors are compacted
  * to the front (order preserved).  sizes i32 [B,4] = {in_h, in_w, out_h, out_w}; n_keep i32 [B].
+ * out_h <= 0 or out_w <= 0 for an image: CenterNet.inference alone (slice + threshold; no scale / clip / nonempty),
+ * i.e. the Instances `inference` returns before the reference's forward calls detector_postprocess (:169-171).
  * In place on boxes/scores/classes [B,K,...]. */
 int ctdet_postprocess(float* boxes, float* scores, int32_t* classes, const int32_t* sizes,
                       int B, int K, int max_dets, float score_thresh, int32_t* n_keep,

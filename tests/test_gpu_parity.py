@@ -492,6 +492,32 @@ def test_nms_topk_gather_dropins(inputs):
     assert np.array_equal(g, ref)
 
 
+def test_topk_dropin_on_arbitrary_scores():
+    """`_topk` (centernet.py:408-424) is a bare torch.topk: on inputs that are not post-NMS heat maps -- negative
+    scores, zeros, post-NMS maps where most cells are exactly 0 -- it must return the true top K (the
+    candidate floor used to drop every score <= 0)."""
+    from detectron2_centernet_b200 import decode as D
+    rng = np.random.default_rng(5)
+    B, C, H, W, K = 2, 6, 40, 64, 50
+    for name, x in (("negative", -np.abs(rng.standard_normal((B, C, H, W))).astype(np.float32) - 0.5),
+                    ("mixed", rng.standard_normal((B, C, H, W)).astype(np.float32))):
+        x = x + (np.arange(C * H * W, dtype=np.float64) / (C * H * W) * 1e-3).astype(np.float32).reshape(C, H, W)   # tie-free
+        s, inds, cls, ys, xs = D._topk(torch.from_numpy(x).to(DEV), K=K)
+        ref = torch.topk(torch.from_numpy(x).view(B, -1), K)
+        assert np.array_equal(s.cpu().numpy(), ref.values.numpy()), name
+        assert np.array_equal((cls.cpu().long() * (H * W) + inds.cpu()).numpy(), ref.indices.numpy()), name
+    # a post-NMS map: fewer than K positive cells, the rest exactly 0 -- scores must match torch.topk (the order of
+    # the tied zeros is unspecified there; ours: lowest flat indices)
+    heat = np.zeros((1, 3, 16, 16), np.float32)
+    pos = rng.choice(3 * 16 * 16, 20, replace=False)
+    heat.reshape(-1)[pos] = rng.uniform(0.1, 1.0, 20).astype(np.float32)
+    s, inds, cls, _, _ = D._topk(torch.from_numpy(heat).to(DEV), K=40)
+    ref = torch.topk(torch.from_numpy(heat).view(1, -1), 40)
+    assert np.array_equal(s.cpu().numpy(), ref.values.numpy())
+    flat = (cls.cpu().long() * 256 + inds.cpu()).numpy()[0]
+    assert np.array_equal(np.sort(flat[:20]), np.sort(pos)) and len(set(flat.tolist())) == 40
+
+
 def test_cpu_tensors_raise():
     from detectron2_centernet_b200 import decode as D
     with pytest.raises(NotImplementedError):
