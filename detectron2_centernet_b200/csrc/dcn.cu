@@ -287,7 +287,6 @@ extern "C" size_t dcnv2_workspace_bytes(int B, int Cin, int H, int W, int Cout) 
   return dcn_align256((size_t)B * H * W * Cin * 2) + dcn_align256((size_t)Cout * Cin * 9 * 2);
 }
 
-using ctdet::dcn_env_int;
 
 // raw27 != 0: `offset` is the raw [B,27,Ho,Wo] output of conv_offset_mask (offsets = its channels 0..17 as they
 // are, mask = sigmoid of channels 18..26), `om_bias` its bias or null; `mask` is ignored.
@@ -356,15 +355,16 @@ static int dcn_forward_impl(const float* input, const float* weight, const float
   const size_t stage_bytes = (size_t)kTileM * kBK * 2 + (size_t)Cout * kBK * 2;
   const size_t budget = 230 * 1024 - 1024 - kGeoBytes;
   int stages = (int)(budget / stage_bytes);
-  const int cap = dcn_env_int("CTDET_DCN_STAGES", 4);
+  const DcnTunables& tune = dcn_tunables();
+  const int cap = tune.stages;
   if (stages > cap) stages = cap;
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages < 2) return CTDET_EUNSUPPORTED;
   prm.stages = stages;
-  prm.mma_sleep = dcn_env_int("CTDET_DCN_MMA_SLEEP", 0);
-  prm.ld_sleep = dcn_env_int("CTDET_DCN_LD_SLEEP", 20);
+  prm.mma_sleep = tune.mma_sleep;
+  prm.ld_sleep = tune.ld_sleep;
   const size_t smem = (size_t)stages * stage_bytes + kGeoBytes + 1024;
-  const int np = dcn_env_int("CTDET_DCN_PRODUCER_WARPS", 16);
+  const int np = tune.producer_warps;
   const bool f32 = (flags & DCN_FLAG_FP32_BLEND) != 0;
   void (*kern)(const DcnParams) = nullptr;
   if (np == 16) kern = f32 ? dcn_forward_kernel<true, 16> : dcn_forward_kernel<false, 16>;

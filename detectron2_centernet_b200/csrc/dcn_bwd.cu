@@ -730,7 +730,7 @@ extern "C" int dcnv2_backward(const float* input, const float* weight, const flo
     if (ring < 2) return CTDET_EUNSUPPORTED;
     bw.g_stages = bw.w_stages = ring;
     const size_t smem = fixed + (size_t)ring * unit;
-    const int npd = dcn_env_int("CTDET_DCN_DGRAD_WARPS", 16) == 8 ? 8 : 16;
+    const int npd = dcn_tunables().dgrad_warps;
     void (*kern)(const DcnParams, const DcnBwdParams) = npd == 8 ? dcn_dgrad_kernel<8> : dcn_dgrad_kernel<16>;
     e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }

@@ -332,9 +332,27 @@ __device__ __forceinline__ void dcn_geometry_tile(const DcnParams& prm, int tile
 __global__ void dcn_pack_input_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ xh, int C, int P, int vec,
                                       float* __restrict__ chan_sum, int chunks, int border_w);
 
-static inline int dcn_env_int(const char* name, int dflt) {
-  const char* v = getenv(name);
-  return (v && *v) ? atoi(v) : dflt;
+// Tuning knobs (experiments only; the defaults are the shipped configuration).  Read from the environment ONCE per
+// process -- function-local static, thread-safe initialisation -- never on the launch path.
+struct DcnTunables {
+  int stages;            // CTDET_DCN_STAGES          A/B ring depth cap of the forward kernel (4)
+  int mma_sleep;         // CTDET_DCN_MMA_SLEEP       ns back-off of the MMA warp's barrier polls (0)
+  int ld_sleep;          // CTDET_DCN_LD_SLEEP        ns back-off of the weight loader's polls (20)
+  int producer_warps;    // CTDET_DCN_PRODUCER_WARPS  gather warps of the forward kernel, 16 or 8 (16)
+  int dgrad_warps;       // CTDET_DCN_DGRAD_WARPS     consumer warps of the dgrad kernel, 16 or 8 (16)
+};
+static inline const DcnTunables& dcn_tunables() {
+  static const DcnTunables t = [] {
+    auto env = [](const char* name, int dflt) { const char* v = getenv(name); return (v && *v) ? atoi(v) : dflt; };
+    DcnTunables r;
+    r.stages = env("CTDET_DCN_STAGES", 4);
+    r.mma_sleep = env("CTDET_DCN_MMA_SLEEP", 0);
+    r.ld_sleep = env("CTDET_DCN_LD_SLEEP", 20);
+    r.producer_warps = env("CTDET_DCN_PRODUCER_WARPS", 16) == 8 ? 8 : 16;
+    r.dgrad_warps = env("CTDET_DCN_DGRAD_WARPS", 16) == 8 ? 8 : 16;
+    return r;
+  }();
+  return t;
 }
 
 }  // namespace ctdet
