@@ -40,6 +40,7 @@ SIGNATURES = {
     "ctdet_postprocess": (c_int, [c_void_p] * 4 + [c_int] * 3 + [c_float, c_void_p, c_void_p]),
     "ctdet_preprocess": (c_int, [c_void_p, c_void_p] + [c_int] * 5 + [c_void_p] * 4),
     "ctdet_upsample_add": (c_int, [c_void_p] * 3 + [c_int] * 5 + [c_void_p, c_void_p]),
+    "ctdet_upsample_add_backward": (c_int, [c_void_p] * 3 + [c_int] * 5 + [c_void_p, c_void_p, c_void_p]),
     "dcnv2_workspace_bytes": (c_size_t, [c_int] * 5),
     "dcnv2_forward": (c_int, [c_void_p] * 6 + [c_int] * 15 + [c_void_p, c_void_p, c_int] +
                       [c_void_p, c_size_t, c_void_p]),

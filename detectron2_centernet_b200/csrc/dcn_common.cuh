@@ -275,13 +275,19 @@ __device__ __forceinline__ void dcn_producer_loop(const DcnParams& prm, uint8_t*
         q.w = blend_bf16x2(va[i].w, vb[i].w, vc[i].w, vd[i].w, wq.x, wq.y, wq.z, wq.w);
       }
       *reinterpret_cast<uint4*>(a_tile + (row0 + (uint32_t)(i * NP * 4)) * 128u + swz) = q;
-      if (have_next) gather(i, l_xc, gg[i * NP * 4]);        // refill the slot: K block n+1, same row group
     }
+    // The proxy fence compiles to MEMBAR.ALL.CTA + FENCE.VIEW.ASYNC: it waits for every memory operation this warp
+    // has in flight.  It therefore comes BEFORE the gathers of the next K block are issued (it used to follow them
+    // and stalled every warp for a full gather round trip per K block, which defeated the register double-buffering).
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> tensor-core reads
     __syncwarp();
     if (lane == 0) {
       dcn_mbar_arrive(&bars.full[s]);
       if (l_it != c_it) dcn_mbar_arrive(&bars.geo_empty[c_it & 1]);   // tile c_it fully consumed by this warp
+    }
+    if (have_next) {
+#pragma unroll
+      for (int i = 0; i < ITERS; ++i) gather(i, l_xc, gg[i * NP * 4]);   // refill: K block n+1, same row groups
     }
     if (++s == NS) { s = 0; ph ^= 1u; }
   }

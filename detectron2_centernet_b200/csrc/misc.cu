@@ -304,6 +304,60 @@ extern "C" int ctdet_preprocess(const void* const* images, const int32_t* sizes_
   return check_launch();
 }
 
+// Backward of the IDAUp up-sampling + skip add (out = ConvTranspose2d_depthwise(x, wt) + skip, dla.py:166-177):
+//   grad_skip = grad_out (the caller aliases it: no pass)
+//   grad_x[c,i,j]  = sum_{u,v} grad_out[c, f*i - f/2 + u, f*j - f/2 + v] * wt[c,u,v]        (u, v < 2f)
+//   grad_wt[c,u,v] = sum_{b,i,j} x[b,c,i,j] * grad_out[b,c, f*i - f/2 + u, f*j - f/2 + v]
+// One pass over grad_out: a thread owns (input cell, kernel row u) -- the 2f lanes of a cell sit next to each other,
+// so grad_x is a shuffle reduction over them -- and keeps the 2f products of its row as running grad_wt sums over
+// every cell it visits; per CTA they meet in shared memory and leave as ONE atomic per (u, v).  grid = (chunks of
+// the plane, C, B).  HBM-bound: grad_out is read once from DRAM (each element 4x through L1), x once, grad_x written.
+template <int F>
+__global__ void __launch_bounds__(256)
+upsample_add_bwd_kernel(const float* __restrict__ gout, const float* __restrict__ x, const float* __restrict__ wt,
+                        int C, int h, int w, int cells_per_cta, float* __restrict__ gx, float* __restrict__ gw) {
+  constexpr int K = 2 * F;                       // kernel side
+  constexpr int CELLS = 256 / K;                 // input cells in flight per CTA
+  __shared__ float s_w[K * K], s_gw[K * K];
+  const int c = blockIdx.y, b = blockIdx.z, tid = threadIdx.x;
+  const int u = tid % K, slot = tid / K;
+  for (int i = tid; i < K * K; i += 256) { s_w[i] = __ldg(wt + (size_t)c * K * K + i); s_gw[i] = 0.f; }
+  __syncthreads();
+  float wrow[K], acc[K];
+#pragma unroll
+  for (int v = 0; v < K; ++v) { wrow[v] = s_w[u * K + v]; acc[v] = 0.f; }
+  const int Ho = h * F, Wo = w * F, n_cells = h * w;
+  const float* go = gout + ((size_t)b * C + c) * Ho * Wo;
+  const float* xp = x ? x + ((size_t)b * C + c) * n_cells : nullptr;
+  float* gxp = gx ? gx + ((size_t)b * C + c) * n_cells : nullptr;
+  const int cell0 = blockIdx.x * cells_per_cta, cell1 = min(n_cells, cell0 + cells_per_cta);
+  for (int base = cell0; base < cell1; base += CELLS) {
+    const int cell = base + slot;
+    const bool ok = cell < cell1;                // (the K lanes of a cell agree)
+    const int i = ok ? cell / w : 0, j = ok ? cell - i * w : 0;
+    const int Y = F * i - F / 2 + u, X0 = F * j - F / 2;
+    const bool row_ok = ok && Y >= 0 && Y < Ho;
+    const float xv = (ok && xp) ? __ldg(xp + cell) : 0.f;
+    float part = 0.f;
+#pragma unroll
+    for (int v = 0; v < K; ++v) {
+      const int X = X0 + v;
+      const float g = (row_ok && X >= 0 && X < Wo) ? __ldg(go + (size_t)Y * Wo + X) : 0.f;
+      part = fmaf(g, wrow[v], part);
+      acc[v] = fmaf(g, xv, acc[v]);
+    }
+#pragma unroll
+    for (int o = K / 2; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);    // over the cell's K lanes
+    if (ok && u == 0 && gxp) gxp[cell] = part;
+  }
+  if (gw) {
+#pragma unroll
+    for (int v = 0; v < K; ++v) atomicAdd(&s_gw[u * K + v], acc[v]);
+    __syncthreads();
+    for (int i = tid; i < K * K; i += 256) atomicAdd(gw + (size_t)c * K * K + i, s_gw[i]);
+  }
+}
+
 extern "C" int ctdet_upsample_add(const float* x, const float* weight, const float* skip, int B, int C, int h, int w,
                                   int f, float* out, ctdet_stream_t stream) {
   using namespace ctdet;
@@ -325,5 +379,27 @@ extern "C" int ctdet_upsample_add(const float* x, const float* weight, const flo
   else if (vec && f == 4) upsample_add_kernel<4, 2><<<grid, 256, 0, st>>>(x, weight, skip, C, h, w, lf, dq, out);
   else if (vec) upsample_add_kernel<4, 0><<<grid, 256, 0, st>>>(x, weight, skip, C, h, w, lf, dq, out);
   else upsample_add_kernel<1, 0><<<grid, 256, 0, st>>>(x, weight, skip, C, h, w, lf, dq, out);
+  return check_launch();
+}
+
+extern "C" int ctdet_upsample_add_backward(const float* grad_out, const float* x, const float* weight, int B, int C, int h,
+                                           int w, int f, float* grad_x, float* grad_weight, ctdet_stream_t stream) {
+  using namespace ctdet;
+  if (B < 0 || C <= 0 || h <= 0 || w <= 0) return CTDET_EINVAL;
+  if (f != 2 && f != 4) return CTDET_EUNSUPPORTED;        // IDAUp in DLA-34 uses 2 and 4 (8 only with a deeper base)
+  if (!grad_out || !weight || (!grad_x && !grad_weight) || (grad_weight && !x)) return CTDET_ENULL;
+  if (B > 65535 || C > 65535 || (long long)h * f * w * f >= (1ll << 31)) return CTDET_EINVAL;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (grad_weight) {                                       // accumulated with atomics: zero first (same stream)
+    cudaError_t e = cudaMemsetAsync(grad_weight, 0, (size_t)C * 4 * f * f * sizeof(float), st);
+    if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
+  }
+  if (B == 0) return CTDET_OK;
+  const int n_cells = h * w;
+  int per = 2048;                                          // input cells per CTA: >= 32 visits of every thread
+  if (per > n_cells) per = n_cells;
+  const dim3 grid((unsigned)((n_cells + per - 1) / per), (unsigned)C, (unsigned)B);
+  if (f == 2) upsample_add_bwd_kernel<2><<<grid, 256, 0, st>>>(grad_out, x, weight, C, h, w, per, grad_x, grad_weight);
+  else upsample_add_bwd_kernel<4><<<grid, 256, 0, st>>>(grad_out, x, weight, C, h, w, per, grad_x, grad_weight);
   return check_launch();
 }

@@ -27,18 +27,8 @@ def _is_ida_up(up):
             2 <= f <= 16 and (f & (f - 1)) == 0)
 
 
-def upsample_add(up, x, skip=None):
-    """`up(x) + skip` of IDAUp.forward (dla.py:175-177) in one pass over HBM (C ABI ctdet_upsample_add).
-    Used when no gradient is needed (eval / no_grad); with autograd, or for a module that is not IDAUp's
-    up-sampling, the reference's own two torch ops run (the up-sampling weights are learnable)."""
-    fused = (x.is_cuda and x.dtype == torch.float32 and _is_ida_up(up) and up.weight.dtype == torch.float32 and
-             not (torch.is_grad_enabled() and (x.requires_grad or up.weight.requires_grad or
-                                               (skip is not None and skip.requires_grad))))
-    if not fused:
-        y = up(x)
-        return y if skip is None else y + skip
+def _upsample_add_fwd(x, weight, skip, f):
     lib = _lib.load()
-    f = up.stride[0]
     x = _lib.f32c(x, "x")
     B, C, h, w = x.shape
     if skip is not None:
@@ -47,10 +37,58 @@ def upsample_add(up, x, skip=None):
             raise RuntimeError("skip must be [%d,%d,%d,%d], got %s" % (B, C, h * f, w * f, tuple(skip.shape)))
     out = torch.empty((B, C, h * f, w * f), dtype=torch.float32, device=x.device)
     with torch.cuda.device(x.device):
-        rc = lib.ctdet_upsample_add(_lib.ptr(x), _lib.ptr(_lib.f32c(up.weight.detach(), "weight")), _lib.ptr(skip),
+        rc = lib.ctdet_upsample_add(_lib.ptr(x), _lib.ptr(_lib.f32c(weight, "weight")), _lib.ptr(skip),
                                     B, C, h, w, f, _lib.ptr(out), _lib.stream_ptr(x.device))
     _lib.check(rc, "ctdet_upsample_add")
     return out
+
+
+class _UpsampleAdd(torch.autograd.Function):
+    """`up(x) + skip` with its backward on the GPU kernels too (C ABI ctdet_upsample_add_backward): grad_x and
+    grad_weight in one pass over grad_out, grad_skip = grad_out.  In the reference this is the grouped
+    ConvTranspose2d's cuDNN forward / backward-data / backward-filter plus the add (dla.py:175-177)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, skip, f):
+        ctx.f = f
+        ctx.has_skip = skip is not None
+        ctx.save_for_backward(x, weight)
+        return _upsample_add_fwd(x, weight.detach(), skip, f)
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, grad_out):
+        x, weight = ctx.saved_tensors
+        lib = _lib.load()
+        f = ctx.f
+        grad_out = _lib.f32c(grad_out, "grad_out")
+        B, C, h, w = x.shape
+        gx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
+        gw = torch.empty_like(weight) if ctx.needs_input_grad[1] else None
+        if gx is not None or gw is not None:
+            with torch.cuda.device(x.device):
+                rc = lib.ctdet_upsample_add_backward(_lib.ptr(grad_out), _lib.ptr(_lib.f32c(x, "x")),
+                                                     _lib.ptr(_lib.f32c(weight, "weight")), B, C, h, w, f, _lib.ptr(gx),
+                                                     _lib.ptr(gw), _lib.stream_ptr(x.device))
+            _lib.check(rc, "ctdet_upsample_add_backward")
+        return gx, gw, (grad_out if ctx.has_skip and ctx.needs_input_grad[2] else None), None
+
+
+def upsample_add(up, x, skip=None):
+    """`up(x) + skip` of IDAUp.forward (dla.py:175-177) in one pass over HBM (C ABI ctdet_upsample_add); with autograd
+    the backward runs on ctdet_upsample_add_backward (f = 2 / 4, what DLA-34 uses).  For a module that is not
+    IDAUp's up-sampling (or f = 8 / 16 under autograd) the reference's own two torch ops run."""
+    fused = x.is_cuda and x.dtype == torch.float32 and _is_ida_up(up) and up.weight.dtype == torch.float32
+    needs_grad = torch.is_grad_enabled() and (x.requires_grad or up.weight.requires_grad or
+                                              (skip is not None and skip.requires_grad))
+    if fused and needs_grad and up.stride[0] not in (2, 4):
+        fused = False
+    if not fused:
+        y = up(x)
+        return y if skip is None else y + skip
+    if needs_grad:
+        return _UpsampleAdd.apply(x, up.weight, skip, up.stride[0])
+    return _upsample_add_fwd(x, up.weight.detach(), skip, up.stride[0])
 
 
 def fill_up_weights(up):

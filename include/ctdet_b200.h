@@ -191,6 +191,14 @@ int ctdet_preprocess(const void* const* images, const int32_t* sizes_hw, int dty
 int ctdet_upsample_add(const float* x, const float* weight, const float* skip, int B, int C, int h, int w,
                        int f, float* out, ctdet_stream_t stream);
 
+/* Backward of ctdet_upsample_add (autograd of `up_i(x) + layers[i-1]`, dla.py:175-177; in the reference: the
+ * grouped ConvTranspose2d's cuDNN backward-data / backward-filter kernels + the add's pass-through):
+ *   grad_out f32 [B,C,f*h,f*w]   x f32 [B,C,h,w] (needed for grad_weight only)   weight f32 [C,1,2f,2f]
+ *   grad_x f32 [B,C,h,w] or NULL   grad_weight f32 [C,1,2f,2f] or NULL (overwritten)   f in {2,4}
+ * grad_skip is grad_out itself (no pass). */
+int ctdet_upsample_add_backward(const float* grad_out, const float* x, const float* weight, int B, int C, int h,
+                                int w, int f, float* grad_x, float* grad_weight, ctdet_stream_t stream);
+
 /* ---------------------------------------------------------------- DCNv2 forward ----------
  * Modulated deformable 3x3 convolution, replaces modulated_deform_conv_forward
  * (detectron2/layers/csrc/deformable/deform_conv.h:262-312; same argument meaning, minus the

@@ -212,3 +212,44 @@ def test_upsample_add_kernel_matches_reference_ops(f, shape):
     y = N.upsample_add(up_d, xg, skip.to("cuda:0"))
     y.sum().backward()
     assert xg.grad is not None and up_d.weight.grad is not None
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("f,shape", [(2, (2, 64, 64, 64)), (2, (3, 24, 7, 9)), (4, (2, 64, 16, 16)), (4, (1, 5, 3, 7)),
+                                      (2, (1, 5, 3, 3))])
+def test_upsample_add_backward_matches_torch_autograd(f, shape):
+    """ctdet_upsample_add_backward (the training path of IDAUp's `up_i(x) + layers[i-1]`, dla.py:175-177) against
+    torch autograd through conv_transpose2d + add on the CPU in fp64: grad_x, grad_weight (learnable up-sampling
+    weights), grad_skip; with and without a skip, odd sizes.  fp32 sums of 4*f*f products (grad_x) and of B*h*w
+    products in atomic order (grad_weight): tolerance 1e-5 of each tensor's scale."""
+    from detectron2_centernet_b200 import neck as N
+    B, C, h, w = shape
+    g = torch.Generator().manual_seed(300 + f + h)
+    x = torch.randn(shape, generator=g)
+    skip = torch.randn((B, C, h * f, w * f), generator=g)
+    gy = torch.randn((B, C, h * f, w * f), generator=g)
+    wt = torch.randn((C, 1, 2 * f, 2 * f), generator=g)
+    for with_skip in (True, False):
+        xr, wr, sr = x.double().requires_grad_(True), wt.double().requires_grad_(True), skip.double().requires_grad_(True)
+        y = torch.nn.functional.conv_transpose2d(xr, wr, stride=f, padding=f // 2, groups=C)
+        if with_skip:
+            y = y + sr
+        y.backward(gy.double())
+        up = torch.nn.ConvTranspose2d(C, C, 2 * f, stride=f, padding=f // 2, groups=C, bias=False).to("cuda:0")
+        up.weight.data.copy_(wt)
+        xd = x.to("cuda:0").requires_grad_(True)
+        sd = skip.to("cuda:0").requires_grad_(True) if with_skip else None
+        out = N.upsample_add(up, xd, sd)
+        assert out.grad_fn is not None and "UpsampleAdd" in type(out.grad_fn).__name__      # the fused path, not torch's
+        assert float((out.detach().cpu().double() - y.detach()).abs().max()) <= 2e-6 * float(y.abs().max())
+        out.backward(gy.to("cuda:0"))
+        for name, got, want in (("grad_x", xd.grad, xr.grad), ("grad_weight", up.weight.grad, wr.grad)):
+            err = float((got.cpu().double() - want).abs().max())
+            assert err <= 1e-5 * float(want.abs().max()), (name, with_skip, err)
+        if with_skip:
+            assert torch.equal(sd.grad.cpu(), gy)
+    # only the input gradient wanted (frozen up-sampling weights, the reference's bilinear init)
+    up.weight.requires_grad_(False)
+    xd = x.to("cuda:0").requires_grad_(True)
+    N.upsample_add(up, xd, None).backward(gy.to("cuda:0"))
+    assert float((xd.grad.cpu().double() - xr.grad).abs().max()) <= 1e-5 * float(xr.grad.abs().max())
