@@ -82,9 +82,15 @@ def load():
     return lib
 
 
+_ws_cache = {}
+
+
 def check(code, what):
     if code == 0:
         return
+    # The cached loss / decode workspaces rely on "zero on entry, left zero on exit".  A multi-launch call that failed
+    # part-way may have left them dirty: drop them, the next call allocates fresh zeroed ones.
+    _ws_cache.clear()
     lib = load()
     msg = lib.ctdet_error_string(code).decode()
     if code == 5:
@@ -114,9 +120,6 @@ def f32c(t, what):
     if t.dtype != torch.float32:
         raise RuntimeError("%s must be float32, got %s" % (what, t.dtype))
     return t if t.is_contiguous() else t.contiguous()
-
-
-_ws_cache = {}
 
 
 def zero_workspace(key, nbytes, device):

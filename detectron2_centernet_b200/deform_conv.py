@@ -153,6 +153,11 @@ class _ModulatedDeformConv(torch.autograd.Function):
         ctx.cfg = (stride, padding, dilation, groups, deformable_groups)
         ctx.with_bias = bias is not None
         if weight.requires_grad or mask.requires_grad or offset.requires_grad or input.requires_grad:
+            if weight.shape[0] % 64 != 0:
+                # the backward kernels tile Cout by 64 (the forward takes multiples of 16): fail here, not inside
+                # autograd's backward
+                raise NotImplementedError("modulated_deform_conv: training needs out_channels %% 64 == 0 (got %d); "
+                                          "the forward alone supports multiples of 16" % weight.shape[0])
             ctx.save_for_backward(input, offset, mask, weight)               # deform_conv.py:211
         return dcnv2_forward(input, offset, mask, weight, bias, stride, padding, dilation, groups, deformable_groups)
 

@@ -114,6 +114,10 @@ class _FusedLoss(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, g):
+        if ctx.grads is None:
+            raise RuntimeError("the fused ctdet losses were already back-propagated: the gradients of the three losses are "
+                               "produced by ONE forward sweep and released by the first backward -- sum hm_loss, wh_loss "
+                               "and off_loss before calling backward once (retain_graph / per-loss backward is not supported)")
         d_hm, d_wh, d_reg = ctx.grads
         ctx.grads = None
         g = g.contiguous()
@@ -179,6 +183,10 @@ class _FusedTargetLoss(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, g):
+        if ctx.grads is None:
+            raise RuntimeError("the fused ctdet losses were already back-propagated: the gradients of the three losses are "
+                               "produced by ONE forward sweep and released by the first backward -- sum hm_loss, wh_loss "
+                               "and off_loss before calling backward once (retain_graph / per-loss backward is not supported)")
         d_hm, d_wh, d_reg = ctx.grads
         ctx.grads = None
         g = g.contiguous()

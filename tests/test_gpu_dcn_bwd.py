@@ -88,3 +88,16 @@ def test_dcn_autograd_module():
     for n, prm in layer.named_parameters():
         assert prm.grad is not None and torch.isfinite(prm.grad).all(), n
     assert torch.isfinite(x.grad).all() and float(x.grad.abs().max()) > 0
+
+
+def test_training_constraints_are_checked_in_forward():
+    """Cout = 48 runs forward-only, but with autograd the unsupported backward shape is reported by the FORWARD call
+    (it used to surface as a NotImplementedError inside autograd's backward)."""
+    from detectron2_centernet_b200 import deform_conv as DC
+    x = torch.randn(1, 64, 10, 11, device=DEV)
+    off = torch.zeros(1, 18, 10, 11, device=DEV)
+    m = torch.ones(1, 9, 10, 11, device=DEV)
+    w = torch.randn(48, 64, 3, 3, device=DEV) * 0.05
+    assert DC.modulated_deform_conv(x, off, m, w, None, 1, 1, 1, 1, 1).shape == (1, 48, 10, 11)
+    with pytest.raises(NotImplementedError, match="out_channels"):
+        DC.modulated_deform_conv(x.requires_grad_(True), off, m, w, None, 1, 1, 1, 1, 1)

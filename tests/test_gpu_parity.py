@@ -715,3 +715,16 @@ def test_centernet_hot_path_losses_and_inference(inputs):
         assert np.array_equal(r.pred_classes.cpu().numpy(), cc[keep.numpy()])
         np.testing.assert_allclose(r.scores.cpu().numpy(), ss[keep.numpy()], rtol=2e-7)
         assert np.array_equal(r.pred_boxes.tensor.cpu().numpy(), t[keep].numpy())
+
+
+def test_fused_losses_second_backward_raises_clearly(inputs):
+    """The three losses share one autograd node whose gradients are released by the first backward."""
+    import detectron2_centernet_b200 as P
+    bl, cl, hm, wh, reg, (B, C, H, W, K, full) = inputs("tiny")
+    boxes, classes, offsets = S.pack_objects(bl, cl)
+    gt = P.target.target_gen(*_cuda(boxes, classes, offsets), B, C, H, W)
+    t = [a.requires_grad_(True) for a in _cuda(hm, wh, reg)]
+    out = P.losses.ctdet_losses({"hm": t[0], "wh": t[1], "reg": t[2]}, gt, alpha=[1.0])
+    out["hm_loss"].backward(retain_graph=True)
+    with pytest.raises(RuntimeError, match="already back-propagated"):
+        out["wh_loss"].backward()
