@@ -695,7 +695,7 @@ __global__ void __launch_bounds__(kStrThreads)
 decode_stream_kernel(const float* __restrict__ heat, int C, int H, int W, int band_rows, int bands, int flags, int K,
                      FastDiv div_bands, FastDiv div_strips, DecodeHeader* __restrict__ hdrs,
                      const unsigned int* __restrict__ phists, const unsigned int* __restrict__ pvals_all, int n_vals,
-                     u64* __restrict__ skeys_all, unsigned int* __restrict__ scnt_all) {
+                     u64* __restrict__ skeys_all) {
   extern __shared__ __align__(128) unsigned char s_raw[];
   __shared__ __align__(8) uint64_t s_bar;
   __shared__ int s_wtot[kStrWarps];
@@ -737,8 +737,7 @@ decode_stream_kernel(const float* __restrict__ heat, int C, int H, int W, int ba
   __syncthreads();                                            // bound, barrier init, padding rows
   const size_t tile_id = (size_t)b * gridDim.x + blockIdx.x;
   const unsigned int thr_ord = s_thr;
-  if (s_skip) {                                               // CTA-uniform
-    if (tid == 0) scnt_all[tile_id] = 0u;
+  if (s_skip) {                                               // CTA-uniform (the tail ignores this image's segments)
     mbar_wait(&s_bar, 0);                                     // (the copy must land before the CTA's memory is released)
     pdl_launch_dependents();
     return;
@@ -810,11 +809,13 @@ decode_stream_kernel(const float* __restrict__ heat, int C, int H, int W, int ba
 #pragma unroll
   for (int w = 0; w < kStrWarps; ++w) { const int t = s_wtot[w]; if (w < warp) base += t; total += t; }
   pdl_launch_dependents();
-  if (tid == 0) {
-    scnt_all[tile_id] = total <= kTileCap ? (unsigned)total : 0u;
-    if (total > kTileCap) hdr->staged = 1u;                   // ties / plateaus at the bound: the staged path redoes the image
+  if (total > kTileCap) {                                     // ties / plateaus at the bound: the staged path redoes the image
+    if (tid == 0) hdr->staged = 1u;
+    return;
   }
-  if (total > kTileCap) return;
+  // the segment is always written in full -- keys, then zeros -- so the tail reads it as one dense, coalesced vector
+  // without knowing the counts (no count array, no dependent second trip)
+  for (int i = total + tid; i < kTileCap; i += kStrThreads) skeys_all[tile_id * kTileCap + i] = 0ull;
   u64* dst = skeys_all + tile_id * kTileCap + base + (incl - mine_n);
   while (hits) {
     const int bit = __ffsll((long long)hits) - 1;
@@ -834,7 +835,7 @@ decode_stream_kernel(const float* __restrict__ heat, int C, int H, int W, int ba
 constexpr int kSelCap = 2048;
 #ifdef CTDET_DECODE_TIMING
 __device__ unsigned long long g_tail_ts[64][8];
-__device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+__device__ __forceinline__ unsigned long long gtime() { return (unsigned long long)clock64(); }   // SM cycles (1.965 GHz)
 #define TAIL_TS(i) do { if (threadIdx.x == 0 && blockIdx.x < 64) g_tail_ts[blockIdx.x][i] = gtime(); } while (0)
 #else
 #define TAIL_TS(i) do {} while (0)
@@ -853,11 +854,61 @@ struct FinShared {
 };
 
 // Output stage shared by both list sources: fs->sel holds fs->n >= min(#candidates, K) keys that contain the K best.
+// One detection from its key: score, gathered wh / reg, box in the reference's fp32 operation order.
+struct DetGather { float rx, ry, w, h; };
+__device__ __forceinline__ DetGather det_gather(u64 key, int b, const float* __restrict__ wh, const float* __restrict__ reg,
+                                                int C, int HW, int flags) {
+  const uint32_t flat = 0xffffffffu - (uint32_t)key;
+  const int cls = (int)(flat / (uint32_t)HW);
+  const int sp = (int)(flat - (uint32_t)cls * HW);
+  DetGather g;
+  g.rx = g.ry = 0.5f;                                              // :440-441
+  if (reg != nullptr) {
+    g.rx = __ldg(reg + ((size_t)b * 2 + 0) * HW + sp);             // :436-439
+    g.ry = __ldg(reg + ((size_t)b * 2 + 1) * HW + sp);
+  }
+  if (flags & CTDET_DECODE_CAT_SPEC_WH) {                          // :443-446
+    g.w = __ldg(wh + ((size_t)b * 2 * C + 2 * cls) * HW + sp);
+    g.h = __ldg(wh + ((size_t)b * 2 * C + 2 * cls + 1) * HW + sp);
+  } else {
+    g.w = __ldg(wh + ((size_t)b * 2 + 0) * HW + sp);
+    g.h = __ldg(wh + ((size_t)b * 2 + 1) * HW + sp);
+  }
+  return g;
+}
+__device__ __forceinline__ void det_store(u64 key, const DetGather& g, int b, int k, int K, int HW, int W, float down_ratio,
+                                          int flags, float* __restrict__ boxes, float* __restrict__ scores,
+                                          int32_t* __restrict__ classes, int64_t* __restrict__ inds) {
+  const uint32_t ord = (uint32_t)(key >> 32);
+  const uint32_t flat = 0xffffffffu - (uint32_t)key;
+  const int cls = (int)(flat / (uint32_t)HW);
+  const int sp = (int)(flat - (uint32_t)cls * HW);
+  float score = 0.f;
+  if (ord != 0u) {
+    score = ordered_to_float(ord);
+    if (flags & CTDET_DECODE_LOGITS) score = prob_of_logit(score);   // centernet.py:161
+  }
+  float xs = (float)(sp % W), ys = (float)(sp / W);                // :414-415
+  if (flags & 0x40000000) { xs += 0.5f; ys += 0.5f; }              // (reg == nullptr, :440-441)
+  else { xs = __fadd_rn(xs, g.rx); ys = __fadd_rn(ys, g.ry); }     // :436-439
+  const float hw_ = g.w * 0.5f, hh_ = g.h * 0.5f;                  // "/ 2" is exact
+  float* bx = boxes + ((size_t)b * K + k) * 4;                     // :452-455
+  bx[0] = __fmul_rn(__fsub_rn(xs, hw_), down_ratio);
+  bx[1] = __fmul_rn(__fsub_rn(ys, hh_), down_ratio);
+  bx[2] = __fmul_rn(__fadd_rn(xs, hw_), down_ratio);
+  bx[3] = __fmul_rn(__fadd_rn(ys, hh_), down_ratio);
+  scores[(size_t)b * K + k] = score;
+  classes[(size_t)b * K + k] = cls;                                // int32 (:418)
+  if (inds != nullptr) inds[(size_t)b * K + k] = sp;
+}
+
+// Output stage shared by both list sources: fs->sel holds fs->n >= min(#candidates, K) keys that contain the K best.
 __device__ void finalize_emit(FinShared* fs, int b, const float* __restrict__ wh, const float* __restrict__ reg,
                               int C, int H, int W, int K, float down_ratio, int flags, float* __restrict__ boxes,
                               float* __restrict__ scores, int32_t* __restrict__ classes, int64_t* __restrict__ inds) {
   const int tid = threadIdx.x;
   const int HW = H * W;
+  const int sflags = flags | (reg == nullptr ? 0x40000000 : 0);
   u64* s_sel = fs->sel;
   int n = min(fs->n, kSelCap);                            // >= min(#peaks, K)
   // fewer than K peaks: the reference's heat*keep zeros fill the rest (:405); by the tie rule
@@ -877,7 +928,8 @@ __device__ void finalize_emit(FinShared* fs, int b, const float* __restrict__ wh
     // P2 = next power of two >= n, thread t owns key t % P2 and compares it against slice t / P2
     // of the list (two keys per 16-byte shared-memory broadcast load); partial ranks are combined
     // with shared-memory atomics.  No barriers inside the compare loop (a bitonic network of this
-    // size costs ~36 __syncthreads).
+    // size costs ~36 __syncthreads).  The owner of a key (slice 0) requests its wh / reg values BEFORE the compare
+    // loop -- their L2 round trip hides behind the ranking -- and writes the detection at its rank itself.
     int* s_rank = fs->rank;
     int P2 = 32; while (P2 < n) P2 <<= 1;
     const int parts = kFinThreads / P2, idx = tid & (P2 - 1), part = tid / P2;
@@ -887,8 +939,10 @@ __device__ void finalize_emit(FinShared* fs, int b, const float* __restrict__ wh
     const int npair = (n + 1) >> 1;
     const int j_lo = (int)(((long long)part * npair) / parts), j_hi = (int)(((long long)(part + 1) * npair) / parts);
     u64 mine = 0ull;
+    DetGather g = {0.f, 0.f, 0.f, 0.f};
     if (idx < n) {
       mine = s_sel[idx];
+      if (part == 0) g = det_gather(mine, b, wh, reg, C, HW, flags);
       int rank = 0;
       const ulonglong2* pairs = reinterpret_cast<const ulonglong2*>(s_sel);
 #pragma unroll 4
@@ -899,12 +953,14 @@ __device__ void finalize_emit(FinShared* fs, int b, const float* __restrict__ wh
       if (rank) atomicAdd(&s_rank[idx], rank);
     }
     __syncthreads();
-    const int rank = (part == 0 && idx < n) ? s_rank[idx] : K;
-    __syncthreads();
-    if (rank < K) s_sel[rank] = mine;
-    __syncthreads();
-  } else {
-    // bitonic sort, descending, padded to a power of two with zeros; the first K are the answer
+    if (part == 0 && idx < n) {
+      const int rank = s_rank[idx];
+      if (rank < K) det_store(mine, g, b, rank, K, HW, W, down_ratio, sflags, boxes, scores, classes, inds);
+    }
+    return;
+  }
+  // bitonic sort, descending, padded to a power of two with zeros; the first K are the answer
+  {
     int P = 1; while (P < n) P <<= 1;
     for (int i = n + tid; i < P; i += kFinThreads) s_sel[i] = 0ull;
     __syncthreads();
@@ -923,39 +979,8 @@ __device__ void finalize_emit(FinShared* fs, int b, const float* __restrict__ wh
   }
   for (int k = tid; k < K; k += kFinThreads) {
     const u64 key = s_sel[k];
-    const uint32_t ord = (uint32_t)(key >> 32);
-    const uint32_t flat = 0xffffffffu - (uint32_t)key;
-    const int cls = (int)(flat / (uint32_t)HW);
-    const int sp = (int)(flat - (uint32_t)cls * HW);
-    float score = 0.f;
-    if (ord != 0u) {
-      score = ordered_to_float(ord);
-      if (flags & CTDET_DECODE_LOGITS) score = prob_of_logit(score);   // centernet.py:161
-    }
-    float xs = (float)(sp % W), ys = (float)(sp / W);        // :414-415
-    if (reg != nullptr) {
-      xs = __fadd_rn(xs, reg[((size_t)b * 2 + 0) * HW + sp]);  // :436-439
-      ys = __fadd_rn(ys, reg[((size_t)b * 2 + 1) * HW + sp]);
-    } else {
-      xs += 0.5f; ys += 0.5f;                                  // :440-441
-    }
-    float w_, h_;
-    if (flags & CTDET_DECODE_CAT_SPEC_WH) {                    // :443-446
-      w_ = wh[((size_t)b * 2 * C + 2 * cls) * HW + sp];
-      h_ = wh[((size_t)b * 2 * C + 2 * cls + 1) * HW + sp];
-    } else {
-      w_ = wh[((size_t)b * 2 + 0) * HW + sp];
-      h_ = wh[((size_t)b * 2 + 1) * HW + sp];
-    }
-    const float hw_ = w_ * 0.5f, hh_ = h_ * 0.5f;             // "/ 2" is exact
-    float* bx = boxes + ((size_t)b * K + k) * 4;               // :452-455
-    bx[0] = __fmul_rn(__fsub_rn(xs, hw_), down_ratio);
-    bx[1] = __fmul_rn(__fsub_rn(ys, hh_), down_ratio);
-    bx[2] = __fmul_rn(__fadd_rn(xs, hw_), down_ratio);
-    bx[3] = __fmul_rn(__fadd_rn(ys, hh_), down_ratio);
-    scores[(size_t)b * K + k] = score;
-    classes[(size_t)b * K + k] = cls;                          // int32 (:418)
-    if (inds != nullptr) inds[(size_t)b * K + k] = sp;
+    const DetGather g = det_gather(key, b, wh, reg, C, HW, flags);
+    det_store(key, g, b, k, K, HW, W, down_ratio, sflags, boxes, scores, classes, inds);
   }
 }
 
@@ -1023,7 +1048,7 @@ __global__ void __launch_bounds__(kFinThreads, 1)
 decode_tail_kernel(const float* __restrict__ heat, int B, int mode, int helpers,
                    DecodeHeader* __restrict__ hdrs, unsigned int* __restrict__ ghists,
                    u64* __restrict__ keys, size_t keys_per_image,
-                   const u64* __restrict__ skeys, const unsigned int* __restrict__ scnt, int sw_tiles,
+                   const u64* __restrict__ skeys, int sw_tiles,
                    unsigned int* __restrict__ phists,
                    int Wp, int band_rows, int sub_rows, FastDiv div_strips, int bands,
                    const float* __restrict__ wh, const float* __restrict__ reg, int C, int H,
@@ -1039,13 +1064,17 @@ decode_tail_kernel(const float* __restrict__ heat, int B, int mode, int helpers,
   TAIL_TS(0);
   pdl_wait();
   TAIL_TS(1);
-  // this thread's tile counts, requested together with the header (independent loads: one L2 trip, not two)
-  constexpr int kCntPer = 4;                                 // tiles per thread: sw_tiles <= 2048
-  unsigned int my_cnt[kCntPer];
+  // The image's key segments (every tile's segment is fully written: keys, then zeros) are ONE dense vector: the first
+  // batch of 16-byte loads is requested together with the header -- independent loads, one L2 trip.
+  constexpr int kBatch = 20;                                 // uint4 (2 keys) per thread and batch: 160 KB per CTA and trip
+  const int n_vec = (mode == 0 && helper == 0) ? sw_tiles * (kTileCap / 2) : 0;
+  const uint4* segv = reinterpret_cast<const uint4*>(skeys + (mode == 0 ? (size_t)b * sw_tiles * kTileCap : 0));
+  uint4 kq[kBatch];
 #pragma unroll
-  for (int u = 0; u < kCntPer; ++u) {
-    const int t = tid * kCntPer + u;
-    my_cnt[u] = (mode == 0 && helper == 0 && t < sw_tiles) ? __ldcg(scnt + (size_t)b * sw_tiles + t) : 0u;
+  for (int u = 0; u < kBatch; ++u) {
+    const int i = u * kFinThreads + tid;
+    kq[u] = make_uint4(0u, 0u, 0u, 0u);
+    if (i < n_vec) asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(kq[u].x), "=r"(kq[u].y), "=r"(kq[u].z), "=r"(kq[u].w) : "l"(segv + i));
   }
   // which path produced this image's list (CTA-uniform; the header is reset only at the very end)
   const bool staged = (mode == 1) || hdr->staged != 0u;
@@ -1075,66 +1104,52 @@ decode_tail_kernel(const float* __restrict__ heat, int B, int mode, int helpers,
   if (!fs.last) return;                                      // CTA-uniform: another CTA of the image finalizes
 
   if (!staged) {
-    // ---- streaming path: the image's keys sit in per-tile segments (count + <= kTileCap keys each) --------------
-    // Block scan of the tile counts (held in registers since the header read) -> exclusive offsets in shared
-    // memory; then the keys are fetched over a FLAT index: key i belongs to the tile found by binary search in the
-    // offsets, so every thread has all its ~7 loads in flight at once: one L2 trip for the whole list.
-    const u64* segs = skeys + (size_t)b * sw_tiles * kTileCap;
+    // ---- streaming path: the image's keys sit in per-tile segments, read as one dense vector (zeros = empty slots)
+    // and compacted into shared memory: per batch each warp reserves its slots with ONE shared-memory atomic.
     u64* s_keys = reinterpret_cast<u64*>(s_dyn);
     unsigned int* s_h1 = reinterpret_cast<unsigned int*>(s_keys + kTailSmemKeys);
-    unsigned int* s_off = s_h1 + kHistBins;                  // [sw_tiles + 1] exclusive offsets
-    const int lane = tid & 31, warp = tid >> 5;
+    const int lane = tid & 31;
     for (int i = tid; i < kHistBins; i += kFinThreads) s_h1[i] = 0u;
-    {
-      unsigned int mine_tot = 0;
-#pragma unroll
-      for (int u = 0; u < kCntPer; ++u) mine_tot += my_cnt[u];
-      unsigned int incl = mine_tot;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) { const unsigned int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
-      if (lane == 31) fs.bs.warp_tot[warp] = incl;
-      if (tid == 0) fs.maxord = 0u;
-      __syncthreads();
-      unsigned int before = 0;
-      for (int w = 0; w < warp; ++w) before += fs.bs.warp_tot[w];
-      unsigned int run = before + incl - mine_tot;
-#pragma unroll
-      for (int u = 0; u < kCntPer; ++u) {
-        const int t = tid * kCntPer + u;
-        if (t < sw_tiles) s_off[t] = run;
-        run += my_cnt[u];
-      }
-      if (tid == kFinThreads - 1) s_off[sw_tiles] = run;      // (threads past the last tile carry the total)
-    }
+    if (tid == 0) { fs.above = 0; fs.maxord = 0u; }
     __syncthreads();
-    TAIL_TS(2);
-    const int n_keys = (int)s_off[sw_tiles];
-    const bool fits = n_keys <= kTailSmemKeys;               // CTA-uniform
-    // calls f(key, i) for every key of the image, i = its flat index.  A thread owns the tiles tid, tid + 512, ...:
-    // its keys are fetched 16 at a time with independent loads (a tile holds ~10 keys: one L2 trip for nearly all).
-    auto scan_tiles = [&](auto f) {
-      for (int tile = tid; tile < sw_tiles; tile += kFinThreads) {
-        const int off = (int)s_off[tile], cnt = (int)s_off[tile + 1] - off;
-        const u64* seg = segs + (size_t)tile * kTileCap;
-        for (int k0 = 0; k0 < cnt; k0 += 16) {
-          u64 kk[16];
+    unsigned int mx = 0u;
+    for (int v0 = 0; v0 < n_vec; v0 += kBatch * kFinThreads) {
+      if (v0 > 0) {                                           // (maps with more than 320 tiles per image: further batches)
 #pragma unroll
-          for (int u = 0; u < 16; ++u) kk[u] = __ldcg(seg + min(k0 + u, cnt - 1));   // (clamped, not predicated: a
-#pragma unroll                                                                      //  select would serialise the loads)
-          for (int u = 0; u < 16; ++u) if (k0 + u < cnt) f(kk[u], off + k0 + u);
+        for (int u = 0; u < kBatch; ++u) {
+          const int i = v0 + u * kFinThreads + tid;
+          kq[u] = make_uint4(0u, 0u, 0u, 0u);
+          if (i < n_vec) asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(kq[u].x), "=r"(kq[u].y), "=r"(kq[u].z), "=r"(kq[u].w) : "l"(segv + i));
         }
       }
-    };
-    // pass 1: copy (when it fits) and the largest score
-    unsigned int mx = 0u;
-    scan_tiles([&](u64 key, int slot) {
-      if (slot < kTailSmemKeys) s_keys[slot] = key;
-      mx = max(mx, (unsigned int)(key >> 32));
-    });
+      int cnt = 0;
+#pragma unroll
+      for (int u = 0; u < kBatch; ++u) cnt += ((kq[u].x | kq[u].y) != 0u) + ((kq[u].z | kq[u].w) != 0u);
+      if (v0 == 0 && cnt >= 0) TAIL_TS(2);
+      int incl = cnt;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+      int wbase = 0;
+      if (lane == 31 && incl) wbase = atomicAdd(&fs.above, incl);
+      int slot = __shfl_sync(0xffffffffu, wbase, 31) + incl - cnt;
+#pragma unroll
+      for (int u = 0; u < kBatch; ++u) {
+        if ((kq[u].x | kq[u].y) != 0u) { if (slot < kTailSmemKeys) s_keys[slot] = ((u64)kq[u].y << 32) | kq[u].x; ++slot; mx = max(mx, kq[u].y); }
+        if ((kq[u].z | kq[u].w) != 0u) { if (slot < kTailSmemKeys) s_keys[slot] = ((u64)kq[u].w << 32) | kq[u].z; ++slot; mx = max(mx, kq[u].w); }
+      }
+    }
     mx = __reduce_max_sync(0xffffffffu, mx);
     if (lane == 0 && mx) atomicMax(&fs.maxord, mx);
     __syncthreads();
     TAIL_TS(3);
+    const int n_keys = fs.above;                             // the slot counter = number of keys
+    const bool fits = n_keys <= kTailSmemKeys;               // CTA-uniform
+    const u64* segs = skeys + (size_t)b * sw_tiles * kTileCap;
+    // (only when the list does not fit shared memory: f(key) for every key, straight from the segments)
+    auto scan_tiles = [&](auto f) {
+      for (int i = tid; i < sw_tiles * kTileCap; i += kFinThreads) { const u64 key = __ldcg(segs + i); if (key) f(key, 0); }
+    };
+    __syncthreads();
     if (tid == 0) fs.above = 0;
     if (n_keys <= kFinThreads) {                             // small list: the rank sort takes it whole
       for (int i = tid; i < n_keys; i += kFinThreads) fs.sel[i] = s_keys[i];
@@ -1246,13 +1261,12 @@ static DecodePlan make_plan(int B, int C, int H, int W, int K) {
     p.sw_rows = sr;
     p.sw_bands = (H + sr - 1) / sr;
     p.sw_smem = (size_t)(sr + 2) * W * sizeof(float);
-    if ((long long)C * p.sw_bands > 2048) p.stream = false;     // the tail kernel holds 4 tile counts per thread
+    if ((long long)C * p.sw_bands * kTileCap >= (1ll << 28)) p.stream = false;
   }
   {
     int tsubs = (kFinThreads / 32) / strips; if (tsubs < 1) tsubs = 1;
     p.tail_sub_rows = (rows + tsubs - 1) / tsubs;
-    const size_t list = (size_t)kTailSmemKeys * sizeof(u64) + (size_t)kHistBins * sizeof(unsigned int) +
-                        (size_t)(C * p.sw_bands + 1) * sizeof(unsigned int);
+    const size_t list = (size_t)kTailSmemKeys * sizeof(u64) + (size_t)kHistBins * sizeof(unsigned int);
     p.tail_smem = p.stream ? (p.smem > list ? p.smem : list) : 16;
   }
   {
@@ -1261,7 +1275,7 @@ static DecodePlan make_plan(int B, int C, int H, int W, int K) {
     p.seed_vals = items * kSeedRows;
     if (p.seed_ctas < 1) p.seed_ctas = 1;
   }
-  p.scnt_bytes = p.stream ? (((size_t)B * C * p.sw_bands * sizeof(unsigned int)) + 255) / 256 * 256 : 0;
+  p.scnt_bytes = 0;                                             // (tile counts of an earlier layout)
   p.skeys_bytes = p.stream ? (size_t)B * C * p.sw_bands * kTileCap * sizeof(u64) : 0;
   // sample histograms (zero on entry, left zero: a fixed stride per image, whatever the map shape, because calls
   // of different shapes share one workspace), then the samples themselves (rewritten by every call)
@@ -1317,10 +1331,10 @@ extern "C" int ctdet_decode(const float* heat, const float* wh, const float* reg
   unsigned char* q = base + p.header_bytes + 2 * p.hist_bytes;    // (the second histogram block is unused since r2)
   unsigned int* phist = reinterpret_cast<unsigned int*>(q); q += p.phist_bytes;
   unsigned int* pvals = reinterpret_cast<unsigned int*>(q); q += p.pvals_bytes;
-  unsigned int* scnt = reinterpret_cast<unsigned int*>(q); q += p.scnt_bytes;
+  q += p.scnt_bytes;                                            // (the tile-count array of an earlier layout: unused)
   u64* skeys = reinterpret_cast<u64*>(q); q += p.skeys_bytes;
   u64* keys = reinterpret_cast<u64*>(q);
-  if (!p.stream) { phist = nullptr; pvals = nullptr; skeys = nullptr; scnt = nullptr; }
+  if (!p.stream) { phist = nullptr; pvals = nullptr; skeys = nullptr; }
   if (B > 65535 || C > 65535) return CTDET_EINVAL;
   int rc;
   const FastDiv div_strips((uint32_t)p.strips);
@@ -1334,12 +1348,11 @@ extern "C" int ctdet_decode(const float* heat, const float* wh, const float* reg
     if (e == cudaSuccess)
       e = launch_pdl(sweep, dim3(C * p.sw_bands, B), dim3(kStrThreads), p.sw_smem, st,
                      heat, C, H, W, p.sw_rows, p.sw_bands, flags, K, FastDiv((uint32_t)p.sw_bands), div_strips, hdr,
-                     (const unsigned int*)phist, (const unsigned int*)pvals, p.seed_vals, skeys, scnt);
+                     (const unsigned int*)phist, (const unsigned int*)pvals, p.seed_vals, skeys);
     if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
     if ((rc = check_launch())) return rc;
     e = launch_pdl(decode_tail_kernel, dim3(B * kTailHelpers), dim3(kFinThreads), p.tail_smem, st,
-                   heat, B, 0, kTailHelpers, hdr, ghist, keys, p.keys_per_image, (const u64*)skeys,
-                   (const unsigned int*)scnt, C * p.sw_bands, phist,
+                   heat, B, 0, kTailHelpers, hdr, ghist, keys, p.keys_per_image, (const u64*)skeys, C * p.sw_bands, phist,
                    p.Wp, p.band_rows, p.tail_sub_rows, div_strips, p.bands,
                    wh, reg, C, H, W, K, down_ratio, flags, boxes, scores, classes, inds);
     if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
@@ -1350,8 +1363,7 @@ extern "C" int ctdet_decode(const float* heat, const float* wh, const float* reg
   if ((rc = check_launch())) return rc;
   {
     cudaError_t e = launch_pdl(decode_tail_kernel, dim3(B), dim3(kFinThreads), p.tail_smem, st,
-                               heat, B, 1, 1, hdr, ghist, keys, p.keys_per_image, (const u64*)nullptr,
-                               (const unsigned int*)nullptr, 0, (unsigned int*)nullptr,
+                               heat, B, 1, 1, hdr, ghist, keys, p.keys_per_image, (const u64*)nullptr, 0, (unsigned int*)nullptr,
                                p.Wp, p.band_rows, p.tail_sub_rows, div_strips, p.bands,
                                wh, reg, C, H, W, K, down_ratio, flags, boxes, scores, classes, inds);
     if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
