@@ -204,7 +204,8 @@ struct DecodeHeader {            // per image, zero on entry, reset by the final
   unsigned int staged;           // 1: the image is decoded by decode_peaks_kernel (no seed bound, or the
                                  //    streaming list overflowed); finalize then reads that path's list
   unsigned int ticket;           // decode_tail_kernel: helper CTAs of a handed-over image that finished their tiles
-  unsigned int pad[3];
+  unsigned int seed_ticket;      // decode_seed_kernel: CTAs of the image that have flushed their sample histogram
+  unsigned int pad[2];
 };
 
 struct DecodeShared {
@@ -593,8 +594,10 @@ __device__ unsigned int seed_bound_of_image(const unsigned int* ph, const unsign
 
 __global__ void __launch_bounds__(kSeedThreads)
 decode_seed_kernel(const float* __restrict__ heat, int C, int H, int W, int K, int flags,
-                   int groups, FastDiv div_strips, FastDiv div_groups,
+                   int groups, FastDiv div_strips, FastDiv div_groups, DecodeHeader* __restrict__ hdrs,
                    unsigned int* __restrict__ phists, unsigned int* __restrict__ pvals_all, int n_vals) {
+  __shared__ unsigned int s_sub[32];
+  __shared__ unsigned int s_last;
   pdl_launch_dependents();             // the sweep may be scheduled as soon as every CTA of this grid runs
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int b = blockIdx.y;
@@ -662,6 +665,25 @@ decode_seed_kernel(const float* __restrict__ heat, int C, int H, int W, int K, i
       }
     }
   }
+  // ---- the last CTA of the image (ticket) derives the bound ONCE and publishes it.  The sweep's CTAs then need a
+  // single header read, requested before their tile copy even starts: with 30 MB of bulk copies in flight a small
+  // dependent load queues behind them for ~2 us, and three of them in a row (header, coarse bins, fine bins) per
+  // sweep CTA were the longest thing in its life (clock64 stamps: 5 us of ~7) ------------------------------------
+  DecodeHeader* hdr = hdrs + b;
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) {
+    __threadfence();
+    s_last = (atomicAdd(&hdr->seed_ticket, 1u) == gridDim.x - 1) ? 1u : 0u;
+    __threadfence();
+  }
+  __syncthreads();
+  if (!s_last || warp != 0) return;
+  const unsigned int ord = seed_bound_of_image(phist, pvals, n_vals, K, s_sub);
+  if (lane == 0) {
+    if (ord == 0u) *((volatile unsigned int*)&hdr->staged) = 1u;      // no usable sample bound: the staged path owns the image
+    else *((volatile unsigned int*)&hdr->thr_ord) = ord;              // (also the head start of the staged path after an overflow)
+  }
 }
 
 // decode_stream_kernel: the sweep proper -- a lean TMA-staged threshold sweep.  One CTA (4 warps) per tile = a
@@ -721,18 +743,23 @@ decode_stream_kernel(const float* __restrict__ heat, int C, int H, int W, int ba
   }
   if (y_lo == 0) for (int x = tid; x < W; x += kStrThreads) tile[x] = NEG;                      // max_pool2d padding (:401)
   if (y_hi == H) for (int x = tid; x < W; x += kStrThreads) tile[(size_t)(nrows + 1) * W + x] = NEG;
-  pdl_wait();
-  if (warp == 0) {                     // the image's bound, while the tile is in flight
-    const unsigned int was_staged = *((volatile unsigned int*)&hdr->staged);        // (an overflow elsewhere)
-    const unsigned int ord = seed_bound_of_image(phists + (size_t)b * kSeedHist, pvals_all + (size_t)b * n_vals, n_vals, K, s_sub);
-    if (lane == 0) {
-      s_thr = ord;
-      s_skip = (ord == 0u || was_staged) ? 1u : 0u;
-      if (blockIdx.x == 0) {           // for the tail kernel (every streamed key is >= it) and the staged fall-back
-        if (ord == 0u) hdr->staged = 1u;                      // no usable sample bound: the staged path owns the image
-        else hdr->thr_ord = ord;
-      }
+  // NO griddepcontrol.wait: this grid is launched as soon as every seed CTA has started (programmatic dependent launch)
+  // and each of its CTAs waits only for the bound of ITS image, which the last seed CTA of that image publishes
+  // (thr_ord != 0, or staged = 1 when the sample gives no bound; both are zero on entry).  Image 0 is swept while images
+  // 1.. are still sampled, and the seed's ticket + derivation latency hides behind the first tile copies.  Every
+  // seed CTA is resident by then, so the wait cannot deadlock; it is bounded anyway (~4 ms, then the image is handed
+  // to the staged path, which needs no sample).
+  if (tid == 32) {                     // (not the thread that issues the copy)
+    unsigned int ord = 0u, st_ = 0u, polls = 0u;
+    for (;;) {
+      asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(ord) : "l"(&hdr->thr_ord) : "memory");
+      st_ = *((volatile unsigned int*)&hdr->staged);          // no sample bound, or an overflow elsewhere
+      if (ord != 0u || st_ != 0u) break;
+      if (++polls > 65536u) { hdr->staged = 1u; st_ = 1u; break; }
+      __nanosleep(64);
     }
+    s_thr = ord;
+    s_skip = (ord == 0u || st_ != 0u) ? 1u : 0u;
   }
   __syncthreads();                                            // bound, barrier init, padding rows
   const size_t tile_id = (size_t)b * gridDim.x + blockIdx.x;
@@ -1206,7 +1233,7 @@ decode_tail_kernel(const float* __restrict__ heat, int B, int mode, int helpers,
     for (int i = tid; i < kSeedHist; i += kFinThreads) phists[(size_t)b * kSeedHist + i] = 0u;   // sample histogram
   __syncthreads();
   TAIL_TS(5);
-  if (tid == 0) { hdr->count = 0u; hdr->thr_ord = 0u; hdr->s_count = 0u; hdr->staged = 0u; hdr->ticket = 0u; }
+  if (tid == 0) { hdr->count = 0u; hdr->thr_ord = 0u; hdr->s_count = 0u; hdr->staged = 0u; hdr->ticket = 0u; hdr->seed_ticket = 0u; }
   finalize_emit(&fs, b, wh, reg, C, H, W, K, down_ratio, flags, boxes, scores, classes, inds);
   __syncthreads();
   TAIL_TS(6);
@@ -1341,7 +1368,7 @@ extern "C" int ctdet_decode(const float* heat, const float* wh, const float* reg
   if (p.stream) {
     // seed (sample bound) -> sweep -> tail, chained with programmatic dependent launch
     decode_seed_kernel<<<dim3(p.seed_ctas, B), kSeedThreads, 0, st>>>(
-        heat, C, H, W, K, flags, p.seed_groups, div_strips, FastDiv((uint32_t)p.seed_groups), phist, pvals, p.seed_vals);
+        heat, C, H, W, K, flags, p.seed_groups, div_strips, FastDiv((uint32_t)p.seed_groups), hdr, phist, pvals, p.seed_vals);
     if ((rc = check_launch())) return rc;
     auto sweep = p.strips == 1 ? decode_stream_kernel<true> : decode_stream_kernel<false>;
     cudaError_t e = cudaFuncSetAttribute(sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.sw_smem);
