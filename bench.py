@@ -103,7 +103,7 @@ def dcn_stack(dev, B, reps=5):
             "gflop_per_image_fwd": round(flops / B / 1e9, 2),
             "roofline": {"bound": "tensor", "achieved": round(tf, 1), "peak": peak, "unit": "TFLOP/s",
                          "frac": round(tf / peak, 4), "peak_source": src,
-                         "note": "the sampler is L1-bandwidth-bound (8 B of L1 reads per im2col element), see DESIGN.md section 5"}}
+                         "note": "bound by the SM's L1 / shared-memory pipe (82 % busy: corner gathers, A-tile stores and the tensor core's own operand reads), see DESIGN.md section 5.1"}}
 
 
 def graph_timed_us(call, flush, reps=20):
