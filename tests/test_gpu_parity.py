@@ -728,3 +728,42 @@ def test_fused_losses_second_backward_raises_clearly(inputs):
     out["hm_loss"].backward(retain_graph=True)
     with pytest.raises(RuntimeError, match="already back-propagated"):
         out["wh_loss"].backward()
+
+
+def test_config2_full_size_against_the_oracle():
+    """BASELINE config 2 at its real size -- B = 32 @512^2, the bench's own inputs (seeds 1236 / 2236) -- compared with
+    the pinned oracle, not only through properties: targets (hm <= 1e-6, slots bit-exact), the three
+    losses (1e-5 relative) and the dense hm gradient (1e-5 relative to its scale), for the two-kernel form AND the
+    fused target+loss sweep; and the decode of the same batch in logits mode (classes / indices / boxes bit-exact)."""
+    import detectron2_centernet_b200 as P
+    B, C, H, W, K = 32, 80, 128, 128, 100
+    bl, cl = S.make_batch_objects(1236, B, 512)
+    hm, wh, reg = S.make_head_outputs(2236, B, C, H, W, bl, tie_free=True)
+    boxes, classes, offsets = S.pack_objects(bl, cl)
+    t_b, t_c, t_o = _cuda(boxes, classes, offsets)
+    gt = P.target.target_gen(t_b, t_c, t_o, B, C, H, W)
+    ref_gt = O.gen_heatmap_batch(bl, cl, H, W, C)
+    assert float(np.abs(gt["hm"].cpu().numpy() - ref_gt["hm"]).max()) <= 1e-6
+    for k in ("ind", "reg_mask", "wh", "reg"):
+        assert np.array_equal(gt[k].cpu().numpy(), ref_gt[k]), k
+    torch.set_num_threads(max(1, torch.get_num_threads()))
+    ref_l, ref_g = O.losses_and_grads(torch.from_numpy(hm), torch.from_numpy(wh), torch.from_numpy(reg), ref_gt, alpha=[1.0])
+    scale = float(ref_g[0].abs().max())
+    for fused in (False, True):
+        t = [a.requires_grad_(True) for a in _cuda(hm, wh, reg)]
+        if fused:
+            out, _ = P.losses.ctdet_losses_from_objects({"hm": t[0], "wh": t[1], "reg": t[2]}, t_b, t_c, t_o, alpha=[1.0])
+        else:
+            out = P.losses.ctdet_losses({"hm": t[0], "wh": t[1], "reg": t[2]}, gt, alpha=[1.0])
+        sum(out.values()).backward()
+        for k in ref_l:
+            np.testing.assert_allclose(out[k].item(), float(ref_l[k]), rtol=1e-5, err_msg="%s fused=%s" % (k, fused))
+        err = float((t[0].grad.cpu() - ref_g[0]).abs().max())
+        assert err <= 1e-5 * scale, (fused, err, scale)
+        for g, r in ((t[1].grad, ref_g[1]), (t[2].grad, ref_g[2])):
+            assert float((g.cpu() - r).abs().max()) <= 1e-5 * max(float(r.abs().max()), 1e-12)
+    det = P.decode.ctdet_decode_batch(*_cuda(hm, wh, reg), down_ratio=4, K=K, logits=True)
+    rb, rs, rc, ri = O.decode(hm, wh, reg, 4, K, logits=True)
+    assert np.array_equal(det[2].cpu().numpy(), rc) and np.array_equal(det[3].cpu().numpy(), ri)
+    assert np.array_equal(det[0].cpu().numpy(), rb)
+    np.testing.assert_allclose(det[1].cpu().numpy(), rs, rtol=2e-7)
