@@ -13,6 +13,7 @@ namespace ctdet {
 constexpr int kNumSMs = 148;          // B200: 2 dies x 74 SMs
 
 void set_last_cuda_error(cudaError_t e);
+void set_last_error_text(const char* s);
 
 // Checks the launch that was just enqueued; maps to the C ABI code.
 inline int check_launch() {

@@ -1403,3 +1403,86 @@ extern "C" int ctdet_debug_tail_times(unsigned long long* out /* [64][8] host */
   return cudaMemcpyFromSymbol(out, ctdet::g_tail_ts, sizeof(unsigned long long) * 64 * 8) == cudaSuccess ? 0 : 1;
 }
 #endif
+
+// ---------------------------------------------------------------------------------------------------------------
+// ctdet_decode_static: ctdet_decode for callers that cannot allocate device memory (code under CUDA graph
+// capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The decode workspace lives in a file-scope device array of
+// CTDET_DECODE_STATIC_BYTES that every GPU loading the library holds until exit.  Nothing on this path calls
+// cudaMalloc / cudaFree or an allocating library routine: one cudaGetSymbolAddress per device (set-up), one
+// cudaMemsetAsync per call, then the launches of ctdet_decode.
+//
+// In HOST code `g_decode_static_ws` is only a stand-in the runtime maps to the device symbol -- not a device
+// address.  The address the kernels are given comes from cudaGetSymbolAddress, resolved once per device with that
+// device current (each device holds its own copy of the array at its own address).
+#include <cstdio>
+namespace ctdet {
+
+static __device__ __align__(256) unsigned char g_decode_static_ws[CTDET_DECODE_STATIC_BYTES];
+
+constexpr int kStaticMaxDevices = 64;
+static void* g_decode_static_addr[kStaticMaxDevices];      // device address of the array on device i; nullptr = not resolved yet
+static int g_decode_static_lock = 0;                       // spin lock around the table (set-up only)
+
+// -> CTDET_OK and *out = device address of the scratch array on the CURRENT device
+static int decode_static_address(void** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
+  if (dev < 0 || dev >= kStaticMaxDevices) {
+    set_last_error_text("ctdet_decode_static: device ordinal beyond the 64 this library keeps a scratch address for");
+    return CTDET_EUNSUPPORTED;
+  }
+  while (__atomic_exchange_n(&g_decode_static_lock, 1, __ATOMIC_ACQUIRE)) {}
+  void* p = g_decode_static_addr[dev];
+  int rc = CTDET_OK;
+  if (p == nullptr) {
+    e = cudaGetSymbolAddress(&p, g_decode_static_ws);
+    if (e != cudaSuccess || p == nullptr) {
+      if (e != cudaSuccess) set_last_cuda_error(e);
+      else set_last_error_text("ctdet_decode_static: cudaGetSymbolAddress returned a null address");
+      rc = CTDET_ECUDA;
+      p = nullptr;
+    } else {
+      g_decode_static_addr[dev] = p;
+    }
+  }
+  __atomic_store_n(&g_decode_static_lock, 0, __ATOMIC_RELEASE);
+  *out = p;
+  return rc;
+}
+
+}  // namespace ctdet
+
+extern "C" size_t ctdet_decode_static_max_bytes(void) { return (size_t)CTDET_DECODE_STATIC_BYTES; }
+
+extern "C" int ctdet_decode_static(const float* heat, const float* wh, const float* reg,
+                                   int B, int C, int H, int W, int K, float down_ratio, int flags,
+                                   float* boxes, float* scores, int32_t* classes, int64_t* inds,
+                                   ctdet_stream_t stream) {
+  using namespace ctdet;
+  if (B < 0 || C <= 0 || H <= 0 || W <= 0 || K <= 0) return CTDET_EINVAL;
+  if (K > CTDET_MAX_K || (int64_t)K > (int64_t)H * W) return CTDET_EINVAL;
+  if ((int64_t)C * H * W >= ((int64_t)1 << 31)) return CTDET_EINVAL;
+  if (B == 0) return CTDET_OK;
+  const DecodePlan p = make_plan(B, C, H, W, K);
+  if (p.total_bytes > (size_t)CTDET_DECODE_STATIC_BYTES) {
+    char msg[256];
+    snprintf(msg, sizeof(msg),
+             "ctdet_decode_static: B=%d C=%d H=%d W=%d K=%d needs %zu bytes of scratch, the static array holds %zu "
+             "(CTDET_DECODE_STATIC_BYTES); use ctdet_decode with a caller-owned workspace",
+             B, C, H, W, K, p.total_bytes, (size_t)CTDET_DECODE_STATIC_BYTES);
+    set_last_error_text(msg);
+    return CTDET_EWORKSPACE;
+  }
+  void* ws = nullptr;
+  int rc = decode_static_address(&ws);
+  if (rc != CTDET_OK) return rc;
+  // The array is shared by every call and keeps the last call's contents: a call with another B leaves key segments
+  // where this B's headers / histograms (zero on entry) sit, so that prefix is cleared on the stream every time.
+  const size_t zero_bytes = p.header_bytes + 2 * p.hist_bytes + p.phist_bytes;
+  cudaError_t e = cudaMemsetAsync(ws, 0, zero_bytes, (cudaStream_t)stream);
+  if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
+  return ctdet_decode(heat, wh, reg, B, C, H, W, K, down_ratio, flags, boxes, scores, classes, inds,
+                      ws, (size_t)CTDET_DECODE_STATIC_BYTES, stream);
+}

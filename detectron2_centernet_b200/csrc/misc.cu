@@ -13,6 +13,13 @@ void set_last_cuda_error(cudaError_t e) {
   g_last_cuda_error[i] = 0;
 }
 
+// Free-text detail for an error code that has no CUDA error behind it (read back through ctdet_last_cuda_error).
+void set_last_error_text(const char* s) {
+  int i = 0;
+  for (; s && s[i] && i < 255; ++i) g_last_cuda_error[i] = s[i];
+  g_last_cuda_error[i] = 0;
+}
+
 // heat*keep of _nms (centernet.py:399-405), dense output.  One thread per cell; the 3x3
 // neighbourhood comes through L1/L2 (this is the API-compatible standalone op, not the hot path:
 // ctdet_decode fuses the peak test and never materialises this tensor).

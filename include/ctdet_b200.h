@@ -152,6 +152,24 @@ int ctdet_decode(const float* heat, const float* wh, const float* reg,
                  float* boxes, float* scores, int32_t* classes, int64_t* inds,
                  void* workspace, size_t workspace_bytes, ctdet_stream_t stream);
 
+/* ctdet_decode without a caller workspace, for callers that cannot allocate device memory (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments and results as ctdet_decode; the scratch is a file-scope
+ * `static __device__` array of CTDET_DECODE_STATIC_BYTES inside the library (every GPU that loads the library holds
+ * it until exit).  The call allocates nothing: no cudaMalloc / cudaFree, no allocating library routine -- one
+ * cudaGetSymbolAddress per device at first use, one cudaMemsetAsync of the zero-on-entry prefix per call, then
+ * ctdet_decode's launches.  Shapes whose ctdet_decode_workspace_bytes(B,C,H,W,K) exceeds CTDET_DECODE_STATIC_BYTES
+ * (16 MiB: B <= 8 at 80 x 128 x 128, K = 100) return CTDET_EWORKSPACE and ctdet_last_cuda_error() names the bytes
+ * needed and the limit.  ALL calls on a device share the one array (it keeps the last call's contents; what must
+ * start at zero is cleared by the call): two calls that overlap on the GPU -- different streams, or graph branches --
+ * RACE; serialise them, or use ctdet_decode with one workspace per stream. */
+#define CTDET_DECODE_STATIC_BYTES (16u << 20)
+size_t ctdet_decode_static_max_bytes(void);
+int ctdet_decode_static(const float* heat, const float* wh, const float* reg,
+                        int B, int C, int H, int W, int K, float down_ratio, int flags,
+                        float* boxes, float* scores, int32_t* classes, int64_t* inds,
+                        ctdet_stream_t stream);
+
 /* heat*keep of centernet.py:399-405, dense: out f32 [B,C,H,W]. */
 int ctdet_nms(const float* heat, int B, int C, int H, int W, float* out, ctdet_stream_t stream);
 
