@@ -33,6 +33,7 @@ struct DcnBwdParams {
   float* gmask;                // grad_mask   [B][9][Ho*Wo]
   int n_groups, kb_per_group;  // wgrad: K blocks are split into groups that fit TMEM
   int g_stages, w_stages, gout_bufs;   // dgrad ring depths
+  int s_bufs;                          // dgrad (GEMM scatter): S chunk ring depth
 };
 
 // MN-major, 128-byte-swizzled operand: rows of 64 contiguous M/N elements (128 B) per K index, 8-row
@@ -598,6 +599,8 @@ dcn_dgrad_kernel(const DcnParams prm, const DcnBwdParams bw) {
   __syncthreads();
   if (warp == NP + 8) tmem_dealloc(tmem, 128);
 }
+#include "dcn_dgrad2.cuh"
+
 }  // namespace ctdet
 
 static inline size_t dcnb_align256(size_t v) { return (v + 255) / 256 * 256; }
@@ -722,22 +725,46 @@ extern "C" int dcnv2_backward(const float* input, const float* weight, const flo
     rc = check_launch();
     if (rc) return rc;
     const size_t gout_bytes = (size_t)(Cout / 64) * kTileM * 128;
-    bw.gout_bufs = Cout <= 128 ? 2 : 1;
-    const size_t fixed = 1024 + (size_t)bw.gout_bufs * gout_bytes + kDgGeoBytes + kDgAccBytes;
-    const size_t unit = (size_t)Cout * 128 + (size_t)kTileM * 128;
-    int ring = (int)((226 * 1024 - fixed) / unit);
-    if (ring > kDgMaxRing) ring = kDgMaxRing;
-    if (ring < 2) return CTDET_EUNSUPPORTED;
-    bw.g_stages = bw.w_stages = ring;
-    const size_t smem = fixed + (size_t)ring * unit;
-    const int npd = dcn_tunables().dgrad_warps;
-    void (*kern)(const DcnParams, const DcnBwdParams) = npd == 8 ? dcn_dgrad_kernel<8> : dcn_dgrad_kernel<16>;
-    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
     const unsigned grid = (unsigned)(tiles < kNumSMs ? tiles : kNumSMs);
-    kern<<<grid, (npd + 10) * 32, smem, st>>>(prm, bw);
-    rc = check_launch();
-    if (rc) return rc;
+    const int npd = dcn_tunables().dgrad_warps;
+    bool launched = false;
+    if (dcn_tunables().dgrad_gemm && npd == 16 && stride_h == 1 && dilation_h == 1 && Cout <= 128) {
+      // second form: the grad_input scatter as a tensor-core GEMM (dcn_dgrad2.cuh)
+      bw.gout_bufs = Cout <= 64 ? 2 : 1;
+      bw.s_bufs = dcn_tunables().dgrad_sbufs;
+      const size_t fixed = 1024 + (size_t)bw.gout_bufs * gout_bytes + (size_t)bw.s_bufs * kSChunkBytes + kDgGeoBytes +
+                           kDg2SqBytes + kDgAccBytes + (size_t)bw.s_bufs * kTileM * 4;
+      const size_t unit = (size_t)Cout * 128 + (size_t)kTileM * 128;
+      int ring = fixed < 226 * 1024 ? (int)((226 * 1024 - fixed) / unit) : 0;
+      if (ring > kDgMaxRing) ring = kDgMaxRing;
+      if (ring >= 2) {
+        bw.g_stages = bw.w_stages = ring;
+        const size_t smem = fixed + (size_t)ring * unit;
+        auto kern = dcn_dgrad2_kernel<16>;
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
+        kern<<<grid, (16 + 12) * 32, smem, st>>>(prm, bw);
+        rc = check_launch();
+        if (rc) return rc;
+        launched = true;
+      }
+    }
+    if (!launched) {
+      bw.gout_bufs = Cout <= 128 ? 2 : 1;
+      const size_t fixed = 1024 + (size_t)bw.gout_bufs * gout_bytes + kDgGeoBytes + kDgAccBytes;
+      const size_t unit = (size_t)Cout * 128 + (size_t)kTileM * 128;
+      int ring = (int)((226 * 1024 - fixed) / unit);
+      if (ring > kDgMaxRing) ring = kDgMaxRing;
+      if (ring < 2) return CTDET_EUNSUPPORTED;
+      bw.g_stages = bw.w_stages = ring;
+      const size_t smem = fixed + (size_t)ring * unit;
+      void (*kern)(const DcnParams, const DcnBwdParams) = npd == 8 ? dcn_dgrad_kernel<8> : dcn_dgrad_kernel<16>;
+      e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
+      kern<<<grid, (npd + 10) * 32, smem, st>>>(prm, bw);
+      rc = check_launch();
+      if (rc) return rc;
+    }
     dcn_unpack_grad_input_kernel<<<dim3((Pin + 63) / 64, Cin / 64, B), 256, 0, st>>>(gx, grad_input, Cin, Pin, W);
     rc = check_launch();
     if (rc) return rc;

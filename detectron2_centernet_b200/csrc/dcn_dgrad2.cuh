@@ -1,0 +1,516 @@
+// dgrad, second form: the grad_input scatter as a SECOND tensor-core GEMM (included by dcn_bwd.cu inside
+// namespace ctdet).  Replaces the col2im kernel of the reference (deform_conv_cuda_kernel.cu:871-949: one scalar
+// atomicAdd per (pixel, tap, channel, corner)) and the vector REDs of dcn_dgrad_kernel, whose way out of the SM
+// (L1 -> crossbar request port) bounded that kernel.
+//
+// For one 8 x 16 pixel tile and one 64-channel block the gradient of every input cell the tile can reach,
+//     patch[q, ci] = sum_t sum_p S_t[q, p] * G_t[p, ci],      S_t[q, p] = mask[p, t] * (bilinear weight of cell q)
+// is a GEMM with K = 9 taps x 128 pixels.  S_t has four non-zeros per column (the four corners of the tap), distinct
+// pixels are distinct columns, so it is WRITTEN WITH PLAIN STORES into a zeroed shared-memory tile (and un-written
+// after use); G_t is the bf16 column-gradient tile that already sits in shared memory for the consumers, read here
+// as the MN-major B operand.  The patch -- 16 x 24 input cells around the tile = 3 M blocks of 128 -- accumulates
+// over the 9 taps in TMEM and leaves the SM ONCE per (tile, channel block): 98 KB of REDs instead of 1.18 MB.
+// Taps whose top-left corner falls outside the patch (offsets beyond +-3 pixels) keep the old path: the consumer
+// warps RED them directly (flag = sign bit of the geometry's lh field).
+//
+// TMEM (512 columns): [0,128) two G accumulators, [128,512) two patch buffers of 3 x 64 columns.
+// Requires stride = dilation = 1 and Cout <= 128 (shared-memory budget); the host falls back to dcn_dgrad_kernel.
+#pragma once
+
+constexpr int kPatchH = 16, kPatchW = 24, kPatchR = 3;     // cells; the tile's 10 x 18 tap bases + 3 either side
+constexpr int kPatchMB = kPatchH * kPatchW / kTileM;       // 3 M blocks
+constexpr int kSChunkBytes = kTileM * kTileM * 2;          // S[128 q][128 p] bf16 = two K halves of [128][128 B]
+constexpr int kDg2MaxS = 3;
+constexpr int kDg2SqBytes = 2 * 9 * kTileM * 4;
+static_assert(kPatchH * kPatchW == kPatchMB * kTileM, "patch must be whole M blocks");
+
+struct Dgrad2Barriers {
+  uint64_t geo_full[2], geo_empty[2];       // raw geometry + patch index of a tile   (geometry -> consumers, builders)
+  uint64_t gout_full[2], gout_empty[2];     // grad_output tile                       (geometry -> MMA)
+  uint64_t wt_full[kDgMaxRing], wt_empty[kDgMaxRing];   // transposed weight tiles    (bulk copies -> MMA)
+  uint64_t acc_full[2], acc_empty[2];       // TMEM column-gradient accumulators      (MMA -> transfer)
+  uint64_t g_full[kDgMaxRing], g_empty[kDgMaxRing];     // bf16 column-gradient tile  (transfer -> consumers + MMA)
+  uint64_t s_full[kDg2MaxS], s_empty[kDg2MaxS];         // scatter-matrix chunk       (builders -> MMA)
+  uint64_t patch_full[2], patch_empty[2];   // TMEM patch accumulators                (MMA -> transfer)
+};
+
+// {e, lh | flag, lw, mask} as tap_geometry_raw, plus the patch cell of the top-left corner: *sq = qy*24 + qx when
+// all four corners lie inside the tile's patch (then bit 31 of .y is set: the GEMM scatters this tap), else -1.
+__device__ __forceinline__ uint4 tap_geometry_patch(const DcnParams& prm, float off_h, float off_w, float m,
+                                                    int ho, int wo, bool valid, int t, int py0, int px0, int* sq) {
+  uint4 o = make_uint4(0u, 0u, 0u, 0u);
+  *sq = -1;
+  if (valid) {
+    const int i = t / 3, j = t - 3 * i;
+    const float h_im = (float)(ho - prm.pad + i) + off_h;
+    const float w_im = (float)(wo - prm.pad + j) + off_w;
+    if (h_im > -1.f && w_im > -1.f && h_im < (float)prm.H && w_im < (float)prm.W) {
+      const int h_low = (int)floorf(h_im), w_low = (int)floorf(w_im);
+      o.x = (uint32_t)((h_low + 1) * prm.xw + w_low + 1) * (uint32_t)prm.Cin;
+      o.y = __float_as_uint(h_im - (float)h_low);
+      o.z = __float_as_uint(w_im - (float)w_low);
+      o.w = __float_as_uint(m);
+      const int qy = h_low - py0, qx = w_low - px0;
+      if (qy >= 0 && qy <= kPatchH - 2 && qx >= 0 && qx <= kPatchW - 2) {
+        *sq = qy * kPatchW + qx;
+        o.y |= 0x80000000u;
+      }
+    }
+  }
+  return o;
+}
+
+// byte offset of S[qrow][p] inside a chunk: K-major, 128-byte swizzle, K halves of 64 pixels 16 KB apart
+__device__ __forceinline__ uint32_t s_chunk_offset(uint32_t qrow, uint32_t p) {
+  return ((p >> 6) << 14) + (qrow << 7) + (((((p & 63u) >> 3) ^ (qrow & 7u))) << 4) + ((p & 7u) << 1);
+}
+
+// Persistent, warp-specialised; one CTA per SM over 8 x 16 pixel tiles; K block n = (tile, channel block, tap):
+//   warps [0, NP)          consumers: grad_mask / grad_offset from G and the four gathered corners of x (as
+//                          dcn_dgrad_kernel); grad_input REDs only for taps the patch does not cover
+//   warps [NP, NP+4)       transfer: TMEM G accumulator -> bf16 G tile in shared memory; every 9 K blocks the
+//                          finished patch TMEM -> fp32 REDs into the bordered NHWC grad_input workspace
+//   warps [NP+4, NP+8)     grad_output tile + sampling geometry + patch cell of the tiles ahead (thread = pixel)
+//   warp  NP+8             one lane issues both GEMMs: G = gout * Wt (K block n) and patch += S * G (K block n-2)
+//   warp  NP+9             one lane streams the transposed weight tiles with 1-D bulk copies
+//   warps [NP+10, NP+12)   builders: write / un-write the four non-zeros per pixel of the S chunks
+template <int NP>
+__global__ void __launch_bounds__((NP + 12) * 32, 1)
+dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
+  static_assert(NP % 4 == 0 && 32 % NP == 0, "consumer warps must tile the 32 row groups");
+  extern __shared__ __align__(1024) uint8_t dcn_smem[];
+  __shared__ Dgrad2Barriers bars;
+  __shared__ uint32_t s_tmem;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int Cin = prm.Cin, Cout = prm.Cout;
+  const int P = prm.Ho * prm.Wo;
+  const int NG = bw.g_stages, NW = bw.w_stages, GB = bw.gout_bufs, NSB = bw.s_bufs;
+  const uint32_t gout_bytes = (uint32_t)(Cout / 64) * kTileM * 128u, wt_bytes = (uint32_t)Cout * 128u;
+  const uint32_t g_bytes = (uint32_t)kTileM * 128u;
+  uint8_t* smem = dcn_smem + ((1024u - (smem_u32(dcn_smem) & 1023u)) & 1023u);
+  uint8_t* gout = smem;                                               // [GB][Cout/64][128][128 B]
+  uint8_t* wtr = gout + (size_t)GB * gout_bytes;                      // [NW][Cout/64][64][128 B]
+  uint8_t* gring = wtr + (size_t)NW * wt_bytes;                       // [NG][128][128 B]
+  uint8_t* sring = gring + (size_t)NG * g_bytes;                      // [NSB][2][128][128 B]
+  uint4* geo = reinterpret_cast<uint4*>(sring + (size_t)NSB * kSChunkBytes);   // [2][9][128] {e, lh | flag, lw, mask}
+  int* sqt = reinterpret_cast<int*>(reinterpret_cast<uint8_t*>(geo) + kDgGeoBytes);      // [2][9][128] patch cell or -1
+  float* acc = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(sqt) + kDg2SqBytes);  // [27][128]
+  int* sprev = reinterpret_cast<int*>(reinterpret_cast<uint8_t*>(acc) + kDgAccBytes);    // [NSB][128] cell written last
+  const int cpb = Cin / kBK, KB = 9 * cpb;
+  const int tile_first = (int)(((long long)blockIdx.x * prm.num_tiles) / gridDim.x);
+  const int my_tiles = (int)(((long long)(blockIdx.x + 1) * prm.num_tiles) / gridDim.x) - tile_first;
+  const int total = my_tiles * KB;
+
+  if (tid == 0) {
+    for (int i = 0; i < 2; ++i) {
+      dcn_mbar_init(&bars.geo_full[i], 4);    dcn_mbar_init(&bars.geo_empty[i], NP + 2);
+      dcn_mbar_init(&bars.gout_full[i], 4);   dcn_mbar_init(&bars.gout_empty[i], 1);
+      dcn_mbar_init(&bars.acc_full[i], 1);    dcn_mbar_init(&bars.acc_empty[i], 4);
+      dcn_mbar_init(&bars.patch_full[i], 1);  dcn_mbar_init(&bars.patch_empty[i], 4);
+    }
+    for (int i = 0; i < kDgMaxRing; ++i) {
+      dcn_mbar_init(&bars.wt_full[i], 1);     dcn_mbar_init(&bars.wt_empty[i], 1);
+      dcn_mbar_init(&bars.g_full[i], 4);      dcn_mbar_init(&bars.g_empty[i], NP + 1);
+    }
+    for (int i = 0; i < kDg2MaxS; ++i) { dcn_mbar_init(&bars.s_full[i], 2); dcn_mbar_init(&bars.s_empty[i], 1); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == NP + 8) tmem_alloc(&s_tmem, 512);
+  if (warp >= NP + 10) {                       // the S ring starts (and is always left) all zero
+    const int bt = tid - (NP + 10) * 32;       // 0..63
+    uint4* z = reinterpret_cast<uint4*>(sring);
+    const int n16 = NSB * kSChunkBytes / 16;
+    for (int i = bt; i < n16; i += 64) z[i] = make_uint4(0u, 0u, 0u, 0u);
+    for (int i = bt; i < NSB * kTileM; i += 64) sprev[i] = -1;
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = s_tmem;
+
+  if (warp < NP) {
+    // ===================================== consumers ==============================================
+    if (NP == 16) asm volatile("setmaxnreg.inc.sync.aligned.u32 80;");
+    constexpr int ITERS = 32 / NP;
+    const int sub = lane >> 3, chunk = lane & 7;
+    const uint32_t r7 = (uint32_t)(((warp & 1) << 2) + sub);                       // row & 7 is fixed per thread
+    const uint32_t g_half = (uint32_t)(chunk & 1) * 8u;                             // 8-byte half of a 16-byte chunk
+    const uint32_t g_sw_lo = (((uint32_t)(chunk >> 1)) ^ r7) << 4, g_sw_hi = ((4u + (uint32_t)(chunk >> 1)) ^ r7) << 4;
+    const uint32_t row0 = (uint32_t)(warp << 2) + sub;
+    const ptrdiff_t ex = Cin, ey = (ptrdiff_t)prm.xw * Cin;                        // bordered rows
+    uint4 va[ITERS], vb[ITERS], vc[ITERS], vd[ITERS];
+    auto gather = [&](int i, const __nv_bfloat16* xc, uint32_t e0) {
+      const __nv_bfloat16* p = xc + e0;
+      va[i] = ldg_gather8x2(p);
+      vb[i] = ldg_gather8x2(p + ex);
+      vc[i] = ldg_gather8x2(p + ey);
+      vd[i] = ldg_gather8x2(p + ey + ex);
+    };
+    int c_img = 0, c_pix[ITERS];
+    auto set_tile = [&](int it) {
+      int tile = tile_first + it;
+      c_img = tile / prm.tiles_per_image;
+      tile -= c_img * prm.tiles_per_image;
+      const int tile_y = tile / prm.tiles_x, tile_x = tile - tile_y * prm.tiles_x;
+#pragma unroll
+      for (int i = 0; i < ITERS; ++i) {
+        const int r = (int)row0 + i * NP * 4;
+        const int ho = tile_y * kTileH + (r >> 4), wo = tile_x * kTileW + (r & 15);
+        c_pix[i] = (ho < prm.Ho && wo < prm.Wo) ? ho * prm.Wo + wo : -1;
+      }
+    };
+    int l_it = 0, l_cb = 0, l_t = 0;             // load cursor: the K block whose gathers are in flight
+    const __nv_bfloat16* l_x = prm.xh + chunk * 4;
+    if (total > 0) {
+      set_tile(0);
+      l_x = prm.xh + (size_t)c_img * prm.ximg + chunk * 4;
+      dcn_mbar_wait(&bars.geo_full[0], 0u);
+#pragma unroll
+      for (int i = 0; i < ITERS; ++i) gather(i, l_x, geo[row0 + i * NP * 4].x);
+    }
+    int gs = 0; unsigned gph = 0;
+    for (int n = 0; n < total; ++n) {
+      const int c_it = l_it, c_cb = l_cb, c_t = l_t;
+      const bool have_next = n + 1 < total;
+      if (++l_t == 9) {
+        l_t = 0;
+        if (++l_cb == cpb) {
+          l_cb = 0; ++l_it;
+          if (have_next) {
+            const int tile = tile_first + l_it;
+            l_x = prm.xh + (size_t)(tile / prm.tiles_per_image) * prm.ximg + chunk * 4;
+            dcn_mbar_wait(&bars.geo_full[l_it & 1], (unsigned)((l_it >> 1) & 1));
+          }
+        }
+      }
+      const __nv_bfloat16* l_xc = l_x + l_cb * kBK;
+      const uint4* geo_n = geo + ((l_it & 1) * 9 + l_t) * kTileM + row0;
+      const uint4* geo_c = geo + ((c_it & 1) * 9 + c_t) * kTileM + row0;
+      float* gxp = bw.gx + (size_t)c_img * prm.ximg + c_cb * kBK + chunk * 4;
+      asm volatile("" : "+l"(gxp));
+      dcn_mbar_wait(&bars.g_full[gs], gph);
+      const uint8_t* g_tile = gring + (size_t)gs * g_bytes;
+#pragma unroll
+      for (int i = 0; i < ITERS; ++i) {
+        const uint4 q4 = geo_c[i * NP * 4];
+        uint4 gq;                                  // G channels [4c,4c+4) and [32+4c,32+4c+4) of this row
+        {
+          const uint8_t* grow = g_tile + (row0 + (uint32_t)(i * NP * 4)) * 128u + g_half;
+          const uint2 lo = *reinterpret_cast<const uint2*>(grow + g_sw_lo);
+          const uint2 hi = *reinterpret_cast<const uint2*>(grow + g_sw_hi);
+          gq = make_uint4(lo.x, lo.y, hi.x, hi.y);
+        }
+        const uint32_t e0 = q4.x;
+        const float lh = __uint_as_float(q4.y & 0x7fffffffu), lw = __uint_as_float(q4.z), m = __uint_as_float(q4.w);
+        const pk2 g2[4] = {bf2(gq.x), bf2(gq.y), bf2(gq.z), bf2(gq.w)};
+        const float d1 = dot8(g2, va[i]), d2 = dot8(g2, vb[i]), d3 = dot8(g2, vc[i]), d4 = dot8(g2, vd[i]);
+        const float hh = 1.f - lh, hw = 1.f - lw;
+        const float w1 = hh * hw, w2 = hh * lw, w3 = lh * hw, w4 = lh * lw;
+        if ((q4.y >> 31) == 0u) {                // tap outside the patch: scatter it here (deform_conv_cuda_kernel.cu:944)
+          float* gp = gxp + e0;
+          asm volatile("" : "+l"(gp));
+          auto scat = [&](float* q, float c) {
+            if (c != 0.f) {
+              const pk2 cc = pk(c, c);
+              float a0, a1, a2, a3;
+              upk(mul2(g2[0], cc), a0, a1); upk(mul2(g2[1], cc), a2, a3);
+              red_add_v4(q, a0, a1, a2, a3);
+              upk(mul2(g2[2], cc), a0, a1); upk(mul2(g2[3], cc), a2, a3);
+              red_add_v4(q + 32, a0, a1, a2, a3);
+            }
+          };
+          scat(gp, m * w1); scat(gp + ex, m * w2); scat(gp + ey, m * w3); scat(gp + ey + ex, m * w4);
+        }
+        if (have_next) gather(i, l_xc, geo_n[i * NP * 4].x);   // refill the slot: K block n+1, same row group
+        float vm = w1 * d1 + w2 * d2 + w3 * d3 + w4 * d4;             // :1019-1030
+        float vh = hw * (d3 - d1) + lw * (d4 - d2);                   // dmcn_get_coordinate_weight, bp_dir 0 (x mask below)
+        float vw = hh * (d2 - d1) + lh * (d4 - d3);                   // bp_dir 1
+#pragma unroll
+        for (int o = 1; o < 8; o <<= 1) {
+          vm += __shfl_xor_sync(0xffffffffu, vm, o);
+          vh += __shfl_xor_sync(0xffffffffu, vh, o);
+          vw += __shfl_xor_sync(0xffffffffu, vw, o);
+        }
+        if (chunk == 0) {
+          vh *= m; vw *= m;
+          float* a = acc + (3 * c_t) * kTileM + row0 + i * NP * 4;      // partial sums over channel blocks
+          if (c_cb > 0) { vm += a[0]; vh += a[kTileM]; vw += a[2 * kTileM]; }
+          if (c_cb == cpb - 1) {
+            if (c_pix[i] >= 0) {
+              bw.goff[((size_t)c_img * 18 + 2 * c_t) * P + c_pix[i]] = vh;
+              bw.goff[((size_t)c_img * 18 + 2 * c_t + 1) * P + c_pix[i]] = vw;
+              bw.gmask[((size_t)c_img * 9 + c_t) * P + c_pix[i]] = vm;
+            }
+          } else {
+            a[0] = vm; a[kTileM] = vh; a[2 * kTileM] = vw;
+          }
+        }
+      }
+      __syncwarp();
+      if (lane == 0) {
+        dcn_mbar_arrive(&bars.g_empty[gs]);
+        if (l_it != c_it) dcn_mbar_arrive(&bars.geo_empty[c_it & 1]);
+      }
+      if (++gs == NG) { gs = 0; gph ^= 1u; }
+      if (l_it != c_it && have_next) set_tile(l_it);
+    }
+  } else if (warp < NP + 4) {
+    // ===================================== transfer: TMEM -> bf16 G tile; patch flush =============
+    const int quarter = warp - NP;               // = warp % 4: the TMEM lane quarter this warp may read
+    const int r = (quarter << 5) + lane;
+    const uint32_t lane_base = (uint32_t)(quarter * 32) << 16;
+    // group = (tile, channel block): its patch sits in TMEM buffer group & 1 once the MMA warp has committed tap 8
+    auto flush = [&](int group) {
+      const int pb = group & 1;
+      const int it = group / cpb, cb = group - it * cpb;
+      int tile = tile_first + it;
+      const int img = tile / prm.tiles_per_image;
+      tile -= img * prm.tiles_per_image;
+      const int tile_y = tile / prm.tiles_x, tile_x = tile - tile_y * prm.tiles_x;
+      const int by0 = tile_y * kTileH - prm.pad - kPatchR + 1, bx0 = tile_x * kTileW - prm.pad - kPatchR + 1;   // bordered coordinates
+      float* base = bw.gx + (size_t)img * prm.ximg + cb * kBK;
+      dcn_mbar_wait(&bars.patch_full[pb], (unsigned)((group >> 1) & 1));
+      tc_fence_after();
+#pragma unroll 1
+      for (int mb = 0; mb < kPatchMB; ++mb) {
+        const int q = mb * kTileM + r;
+        const int qy = q / kPatchW, qx = q - qy * kPatchW;
+        const int by = by0 + qy, bx = bx0 + qx;
+        const bool ok = by >= 0 && by <= prm.H + 1 && bx >= 0 && bx <= prm.W + 1;
+        float* dst = base + ((size_t)(ok ? by : 0) * prm.xw + (ok ? bx : 0)) * Cin;
+#pragma unroll
+        for (int c0 = 0; c0 < kBK; c0 += 16) {
+          uint32_t v[16];
+          tmem_ld16(tmem + lane_base + (uint32_t)(128 + pb * (kPatchMB * kBK) + mb * kBK + c0), v);
+          uint32_t any = 0u;
+#pragma unroll
+          for (int k = 0; k < 16; ++k) any |= v[k] << 1;            // +-0 -> 0
+          if (ok && any != 0u) {
+#pragma unroll
+            for (int k = 0; k < 16; k += 4)
+              red_add_v4(dst + c0 + k, __uint_as_float(v[k]), __uint_as_float(v[k + 1]), __uint_as_float(v[k + 2]),
+                         __uint_as_float(v[k + 3]));
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) dcn_mbar_arrive(&bars.patch_empty[pb]);
+    };
+    int gs = 0; unsigned gph = 0;
+    for (int n = 0; n < total; ++n) {
+      if (n >= 9 && (n % 9) == 3) flush(n / 9 - 1);                   // (its last MMA retired before acc_full[n - 1] did)
+      const int ab = n & 1;
+      dcn_mbar_wait(&bars.acc_full[ab], (unsigned)((n >> 1) & 1));
+      tc_fence_after();
+      uint32_t pk[32];
+#pragma unroll
+      for (int c0 = 0; c0 < kBK; c0 += 16) {
+        uint32_t v[16];
+        tmem_ld16(tmem + lane_base + (uint32_t)(ab * kBK + c0), v);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(v[2 * k]), __uint_as_float(v[2 * k + 1]));
+          pk[c0 / 2 + k] = *reinterpret_cast<const uint32_t*>(&h);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) dcn_mbar_arrive(&bars.acc_empty[ab]);            // TMEM buffer may be overwritten
+      dcn_mbar_wait(&bars.g_empty[gs], gph ^ 1u);
+      uint8_t* dst = gring + (size_t)gs * g_bytes + r * 128;
+#pragma unroll
+      for (int c = 0; c < 8; ++c)
+        *reinterpret_cast<uint4*>(dst + ((c ^ (r & 7)) << 4)) = make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the tile is also a tensor-core operand now
+      __syncwarp();
+      if (lane == 0) dcn_mbar_arrive(&bars.g_full[gs]);
+      if (++gs == NG) { gs = 0; gph ^= 1u; }
+    }
+    if (total > 0) flush(total / 9 - 1);
+  } else if (warp < NP + 8) {
+    // ===================================== grad_output tile + geometry ============================
+    if (NP == 16) asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+    const int r = ((warp - NP - 4) << 5) + lane;
+    for (int it = 0; it < my_tiles; ++it) {
+      int tile = tile_first + it;
+      const int gb = it % GB;
+      dcn_mbar_wait_relaxed(&bars.gout_empty[gb], (unsigned)(((it / GB) & 1) ^ 1));
+      dcn_load_gout_tile(prm, bw.gh, tile, r, gout + (size_t)gb * gout_bytes);
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) dcn_mbar_arrive(&bars.gout_full[gb]);
+
+      const int b = tile / prm.tiles_per_image;
+      tile -= b * prm.tiles_per_image;
+      const int tile_y = tile / prm.tiles_x, tile_x = tile - tile_y * prm.tiles_x;
+      const int ho = tile_y * kTileH + (r >> 4), wo = tile_x * kTileW + (r & 15);
+      const int py0 = tile_y * kTileH - prm.pad - kPatchR, px0 = tile_x * kTileW - prm.pad - kPatchR;
+      const bool valid = ho < prm.Ho && wo < prm.Wo;
+      const int p = valid ? ho * prm.Wo + wo : 0;
+      const float* offb = prm.offset + (size_t)b * 18 * P + p;
+      const float* mskb = prm.mask + (size_t)b * 9 * P + p;
+      float ov[18], mv[9];
+#pragma unroll
+      for (int k = 0; k < 18; ++k) ov[k] = ldg_stream1(offb + (size_t)k * P);
+#pragma unroll
+      for (int k = 0; k < 9; ++k) mv[k] = ldg_stream1(mskb + (size_t)k * P);
+      const int buf = it & 1;
+      dcn_mbar_wait_relaxed(&bars.geo_empty[buf], (unsigned)(((it >> 1) & 1) ^ 1));
+#pragma unroll
+      for (int t = 0; t < 9; ++t) {
+        int sq;
+        geo[(buf * 9 + t) * kTileM + r] = tap_geometry_patch(prm, ov[2 * t], ov[2 * t + 1], mv[t], ho, wo, valid, t, py0, px0, &sq);
+        sqt[(buf * 9 + t) * kTileM + r] = sq;
+      }
+      __syncwarp();
+      if (lane == 0) dcn_mbar_arrive(&bars.geo_full[buf]);
+    }
+  } else if (warp == NP + 8) {
+    // ===================================== MMA issuer =============================================
+    if (lane == 0) {
+      const uint32_t idesc1 = make_idesc_bf16(kTileM, kBK);                       // G[128 px, 64 ci]: A, B K-major
+      const uint32_t idesc2 = make_idesc_bf16(kTileM, kBK) | (1u << 16);          // patch[128 q, 64 ci]: B (= G) MN-major
+      int ws = 0; unsigned wph = 0;
+      uint32_t a_addr = 0u;
+      int kb1 = 0, it1 = 0;                        // cursor of GEMM 1: K block inside the tile, tile
+      int t2 = 0, grp2 = 0;                        // cursor of GEMM 2: tap, (tile, channel block) group
+      int gs2 = 0; unsigned gph2 = 0;
+      int sb = 0; unsigned sph = 0;
+      constexpr int D = 2;                         // GEMM 2 runs D K blocks behind GEMM 1
+      for (int n = 0; n < total + D; ++n) {
+        if (n < total) {
+          // ---- GEMM 1: G = gout[128 px, Cout] * Wt_kb[Cout, 64 ci] into accumulator n & 1 ----
+          const int gb = it1 % GB;
+          if (kb1 == 0) {
+            dcn_mbar_wait_relaxed(&bars.gout_full[gb], (unsigned)((it1 / GB) & 1), 0u);
+            a_addr = smem_u32(gout + (size_t)gb * gout_bytes);
+          }
+          const int ab = n & 1;
+          dcn_mbar_wait_relaxed(&bars.acc_empty[ab], (unsigned)(((n >> 1) & 1) ^ 1), 0u);
+          dcn_mbar_wait_relaxed(&bars.wt_full[ws], wph, 0u);
+          tc_fence_after();
+          const uint32_t b_addr = smem_u32(wtr + (size_t)ws * wt_bytes);
+          for (int j = 0; j < Cout / 64; ++j) {
+            const uint64_t adesc = make_sw128_desc(a_addr + (uint32_t)j * kTileM * 128u);
+            const uint64_t bdesc = make_sw128_desc(b_addr + (uint32_t)j * 64u * 128u);
+#pragma unroll
+            for (int k4 = 0; k4 < 4; ++k4)
+              umma_bf16(tmem + (uint32_t)(ab * kBK), adesc + 2 * k4, bdesc + 2 * k4, idesc1, (uint32_t)((j | k4) != 0));
+          }
+          umma_commit(&bars.wt_empty[ws]);
+          umma_commit(&bars.acc_full[ab]);
+          if (++ws == NW) { ws = 0; wph ^= 1u; }
+          if (++kb1 == KB) { kb1 = 0; ++it1; umma_commit(&bars.gout_empty[gb]); }
+        }
+        if (n >= D) {
+          // ---- GEMM 2: patch[mb] += S_chunk[128 q, 128 px] * G[128 px, 64 ci], K block n - D ----
+          const int pb = grp2 & 1;
+          if (t2 == 0) dcn_mbar_wait_relaxed(&bars.patch_empty[pb], (unsigned)(((grp2 >> 1) & 1) ^ 1), 0u);
+          dcn_mbar_wait_relaxed(&bars.g_full[gs2], gph2, 0u);
+          const uint32_t g_addr = smem_u32(gring + (size_t)gs2 * g_bytes);
+          for (int mb = 0; mb < kPatchMB; ++mb) {
+            dcn_mbar_wait_relaxed(&bars.s_full[sb], sph, 0u);
+            tc_fence_after();
+            const uint32_t s_addr = smem_u32(sring + (size_t)sb * kSChunkBytes);
+            const uint32_t d_tmem = tmem + (uint32_t)(128 + pb * (kPatchMB * kBK) + mb * kBK);
+#pragma unroll
+            for (int k8 = 0; k8 < kTileM / 16; ++k8) {     // K = 16 pixels: 32 B of an S row, 2 swizzle atoms of G
+              const uint64_t adesc = make_sw128_desc(s_addr + (uint32_t)(k8 >> 2) * 16384u) + 2 * (k8 & 3);
+              const uint64_t bdesc = make_sw128_desc_mn(g_addr + k8 * 2048u, 1024u);
+              umma_bf16(d_tmem, adesc, bdesc, idesc2, (uint32_t)((t2 | k8) != 0));
+            }
+            umma_commit(&bars.s_empty[sb]);
+            if (++sb == NSB) { sb = 0; sph ^= 1u; }
+          }
+          umma_commit(&bars.g_empty[gs2]);
+          if (++gs2 == NG) { gs2 = 0; gph2 ^= 1u; }
+          if (++t2 == 9) { t2 = 0; umma_commit(&bars.patch_full[pb]); ++grp2; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == NP + 9) {
+    // ===================================== transposed-weight tile loader ==========================
+    if (lane == 0) {
+      int ws = 0; unsigned wph = 0;
+      for (int it = 0; it < my_tiles; ++it) {
+        for (int kb = 0; kb < KB; ++kb) {
+          dcn_mbar_wait_relaxed(&bars.wt_empty[ws], wph ^ 1u, 20u);
+          dcn_mbar_arrive_expect_tx(&bars.wt_full[ws], wt_bytes);
+          dcn_bulk_g2s(wtr + (size_t)ws * wt_bytes, bw.wt + (size_t)kb * Cout * kBK, wt_bytes, &bars.wt_full[ws]);
+          if (++ws == NW) { ws = 0; wph ^= 1u; }
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    // ===================================== S builders ==============================================
+    // thread = 2 pixels (columns p of S); per chunk: clear what this thread wrote into the buffer last time,
+    // write the corners of this tap that fall into M block mb
+    const int bt = tid - (NP + 10) * 32;           // 0..63
+    int sb = 0; unsigned sph = 0;
+    int it = 0, cbk = 0, t = 0;
+    for (int n = 0; n < total; ++n) {
+      if (cbk == 0 && t == 0) dcn_mbar_wait(&bars.geo_full[it & 1], (unsigned)((it >> 1) & 1));
+      const int gi = ((it & 1) * 9 + t) * kTileM;
+      int q0[2]; uint32_t wv[2][4];
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int p = bt + 64 * h;
+        q0[h] = sqt[gi + p];
+        const uint4 g4 = geo[gi + p];
+        const float lh = __uint_as_float(g4.y & 0x7fffffffu), lw = __uint_as_float(g4.z), m = __uint_as_float(g4.w);
+        const float hh = 1.f - lh, hw = 1.f - lw;
+        wv[h][0] = (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(m * (hh * hw)));
+        wv[h][1] = (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(m * (hh * lw)));
+        wv[h][2] = (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(m * (lh * hw)));
+        wv[h][3] = (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(m * (lh * lw)));
+      }
+      for (int mb = 0; mb < kPatchMB; ++mb) {
+        dcn_mbar_wait(&bars.s_empty[sb], sph ^ 1u);
+        uint8_t* chunk = sring + (size_t)sb * kSChunkBytes;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int p = bt + 64 * h;
+          const int pe = sprev[sb * kTileM + p];                   // (cell written last | M block << 16), -1: nothing
+          const int pq = (int)(short)(pe & 0xffff), mbp = pe >> 16;
+          if (pq >= 0) {
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              const int qc = pq + (c & 1) + (c >> 1) * kPatchW;
+              if ((qc >> 7) == mbp) *reinterpret_cast<unsigned short*>(chunk + s_chunk_offset((uint32_t)(qc & 127), (uint32_t)p)) = 0;
+            }
+          }
+          if (q0[h] >= 0) {
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              const int qc = q0[h] + (c & 1) + (c >> 1) * kPatchW;
+              if ((qc >> 7) == mb)
+                *reinterpret_cast<unsigned short*>(chunk + s_chunk_offset((uint32_t)(qc & 127), (uint32_t)p)) = (unsigned short)wv[h][c];
+            }
+          }
+          sprev[sb * kTileM + p] = q0[h] >= 0 ? (q0[h] | (mb << 16)) : -1;
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) dcn_mbar_arrive(&bars.s_full[sb]);
+        if (++sb == NSB) { sb = 0; sph ^= 1u; }
+      }
+      if (++t == 9) {
+        t = 0;
+        if (++cbk == cpb) {
+          cbk = 0;
+          __syncwarp();
+          if (lane == 0) dcn_mbar_arrive(&bars.geo_empty[it & 1]);
+          ++it;
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == NP + 8) tmem_dealloc(tmem, 512);
+}
