@@ -731,9 +731,9 @@ extern "C" int dcnv2_backward(const float* input, const float* weight, const flo
     if (dcn_tunables().dgrad_gemm && npd == 16 && stride_h == 1 && dilation_h == 1 && Cout <= 128) {
       // second form: the grad_input scatter as a tensor-core GEMM (dcn_dgrad2.cuh)
       bw.gout_bufs = Cout <= 64 ? 2 : 1;
-      bw.s_bufs = dcn_tunables().dgrad_sbufs;
+      bw.s_bufs = 2;                                     // (the builders' un-write bookkeeping assumes two buffers)
       const size_t fixed = 1024 + (size_t)bw.gout_bufs * gout_bytes + (size_t)bw.s_bufs * kSChunkBytes + kDgGeoBytes +
-                           kDg2SqBytes + kDgAccBytes + (size_t)bw.s_bufs * kTileM * 4;
+                           kDg2SqBytes + kDgAccBytes;
       const size_t unit = (size_t)Cout * 128 + (size_t)kTileM * 128;
       int ring = fixed < 226 * 1024 ? (int)((226 * 1024 - fixed) / unit) : 0;
       if (ring > kDgMaxRing) ring = kDgMaxRing;

@@ -347,7 +347,6 @@ struct DcnTunables {
   int producer_warps;    // CTDET_DCN_PRODUCER_WARPS  gather warps of the forward kernel, 16 or 8 (16)
   int dgrad_warps;       // CTDET_DCN_DGRAD_WARPS     consumer warps of the dgrad kernel, 16 or 8 (16)
   int dgrad_gemm;        // CTDET_DCN_DGRAD_GEMM      1: grad_input scatter as a tensor-core GEMM where supported (1)
-  int dgrad_sbufs;       // CTDET_DCN_DGRAD_SBUFS     S chunk ring of that kernel, 2 or 3 (2)
 };
 static inline const DcnTunables& dcn_tunables() {
   static const DcnTunables t = [] {
@@ -359,7 +358,6 @@ static inline const DcnTunables& dcn_tunables() {
     r.producer_warps = env("CTDET_DCN_PRODUCER_WARPS", 16) == 8 ? 8 : 16;
     r.dgrad_warps = env("CTDET_DCN_DGRAD_WARPS", 16) == 8 ? 8 : 16;
     r.dgrad_gemm = env("CTDET_DCN_DGRAD_GEMM", 1) != 0;
-    r.dgrad_sbufs = env("CTDET_DCN_DGRAD_SBUFS", 2) == 3 ? 3 : 2;
     return r;
   }();
   return t;

@@ -65,14 +65,36 @@ __device__ __forceinline__ uint32_t s_chunk_offset(uint32_t qrow, uint32_t p) {
   return ((p >> 6) << 14) + (qrow << 7) + (((((p & 63u) >> 3) ^ (qrow & 7u))) << 4) + ((p & 7u) << 1);
 }
 
+// bf16 x bf16 + fp32 -> fp32 on the FMA pipe (SASS: FHFMA.BF16, operand halves selected for free)
+__device__ __forceinline__ float fma_bf16(uint32_t a, uint32_t b, float c, bool hi) {
+  float d;
+  const unsigned short ah = (unsigned short)(hi ? (a >> 16) : (a & 0xffffu)), bh = (unsigned short)(hi ? (b >> 16) : (b & 0xffffu));
+  asm("fma.rn.f32.bf16 %0, %1, %2, %3;" : "=f"(d) : "h"(ah), "h"(bh), "f"(c));
+  return d;
+}
+__device__ __forceinline__ float dot8_bf(uint4 g, uint4 v) {     // two chains of four
+  float a = fma_bf16(g.x, v.x, 0.f, false), b = fma_bf16(g.x, v.x, 0.f, true);
+  a = fma_bf16(g.y, v.y, a, false); b = fma_bf16(g.y, v.y, b, true);
+  a = fma_bf16(g.z, v.z, a, false); b = fma_bf16(g.z, v.z, b, true);
+  a = fma_bf16(g.w, v.w, a, false); b = fma_bf16(g.w, v.w, b, true);
+  return a + b;
+}
+// grad_input += G[8 channels] * c for one corner (the rare out-of-patch path): 32 B = one sector
+__device__ __noinline__ void dgrad_scatter8(float* q, uint4 g, float c) {
+  if (c != 0.f) {
+    red_add_v4(q, bf_lo(g.x) * c, bf_hi(g.x) * c, bf_lo(g.y) * c, bf_hi(g.y) * c);
+    red_add_v4(q + 4, bf_lo(g.z) * c, bf_hi(g.z) * c, bf_lo(g.w) * c, bf_hi(g.w) * c);
+  }
+}
+
 // Persistent, warp-specialised; one CTA per SM over 8 x 16 pixel tiles; K block n = (tile, channel block, tap):
 //   warps [0, NP)          consumers: grad_mask / grad_offset from G and the four gathered corners of x (as
 //                          dcn_dgrad_kernel); grad_input REDs only for taps the patch does not cover
 //   warps [NP, NP+4)       transfer: TMEM G accumulator -> bf16 G tile in shared memory; every 9 K blocks the
 //                          finished patch TMEM -> fp32 REDs into the bordered NHWC grad_input workspace
 //   warps [NP+4, NP+8)     grad_output tile + sampling geometry + patch cell of the tiles ahead (thread = pixel)
-//   warp  NP+8             one lane issues both GEMMs: G = gout * Wt (K block n) and patch += S * G (K block n-2)
-//   warp  NP+9             one lane streams the transposed weight tiles with 1-D bulk copies
+//   warp  NP+8             one lane issues GEMM 1 (G = gout * Wt) and streams the transposed weight tiles (bulk copies)
+//   warp  NP+9             one lane issues GEMM 2 (patch += S * G), gated by the G tile and the S chunks
 //   warps [NP+10, NP+12)   builders: write / un-write the four non-zeros per pixel of the S chunks
 template <int NP>
 __global__ void __launch_bounds__((NP + 12) * 32, 1)
@@ -96,7 +118,6 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
   uint4* geo = reinterpret_cast<uint4*>(sring + (size_t)NSB * kSChunkBytes);   // [2][9][128] {e, lh | flag, lw, mask}
   int* sqt = reinterpret_cast<int*>(reinterpret_cast<uint8_t*>(geo) + kDgGeoBytes);      // [2][9][128] patch cell or -1
   float* acc = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(sqt) + kDg2SqBytes);  // [27][128]
-  int* sprev = reinterpret_cast<int*>(reinterpret_cast<uint8_t*>(acc) + kDgAccBytes);    // [NSB][128] cell written last
   const int cpb = Cin / kBK, KB = 9 * cpb;
   const int tile_first = (int)(((long long)blockIdx.x * prm.num_tiles) / gridDim.x);
   const int my_tiles = (int)(((long long)(blockIdx.x + 1) * prm.num_tiles) / gridDim.x) - tile_first;
@@ -122,7 +143,6 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
     uint4* z = reinterpret_cast<uint4*>(sring);
     const int n16 = NSB * kSChunkBytes / 16;
     for (int i = bt; i < n16; i += 64) z[i] = make_uint4(0u, 0u, 0u, 0u);
-    for (int i = bt; i < NSB * kTileM; i += 64) sprev[i] = -1;
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
   tc_fence_before();
@@ -132,21 +152,24 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
 
   if (warp < NP) {
     // ===================================== consumers ==============================================
+    // lane = (row group `sub`, 16-byte channel chunk `chunk`): 8 consecutive channels per lane, so one LDG.128
+    // per corner and one conflict-free LDS.128 of the G row; the dot products run on the mixed-precision FMA
+    // (bf16 x bf16 + fp32 -> fp32, FHFMA.BF16): no unpacking of the operands.
     if (NP == 16) asm volatile("setmaxnreg.inc.sync.aligned.u32 80;");
     constexpr int ITERS = 32 / NP;
     const int sub = lane >> 3, chunk = lane & 7;
     const uint32_t r7 = (uint32_t)(((warp & 1) << 2) + sub);                       // row & 7 is fixed per thread
-    const uint32_t g_half = (uint32_t)(chunk & 1) * 8u;                             // 8-byte half of a 16-byte chunk
-    const uint32_t g_sw_lo = (((uint32_t)(chunk >> 1)) ^ r7) << 4, g_sw_hi = ((4u + (uint32_t)(chunk >> 1)) ^ r7) << 4;
     const uint32_t row0 = (uint32_t)(warp << 2) + sub;
-    const ptrdiff_t ex = Cin, ey = (ptrdiff_t)prm.xw * Cin;                        // bordered rows
+    const uint32_t g_off = row0 * 128u + (((uint32_t)chunk ^ r7) << 4);           // this lane's 16 B of G row `row0`
+    const uint32_t ex = (uint32_t)Cin, ey = (uint32_t)prm.xw * (uint32_t)Cin;      // bordered rows
+    const bool b0 = (chunk & 1) != 0, b1 = (chunk & 2) != 0;
     uint4 va[ITERS], vb[ITERS], vc[ITERS], vd[ITERS];
     auto gather = [&](int i, const __nv_bfloat16* xc, uint32_t e0) {
       const __nv_bfloat16* p = xc + e0;
-      va[i] = ldg_gather8x2(p);
-      vb[i] = ldg_gather8x2(p + ex);
-      vc[i] = ldg_gather8x2(p + ey);
-      vd[i] = ldg_gather8x2(p + ey + ex);
+      va[i] = ldg_gather16(p);
+      vb[i] = ldg_gather16(p + ex);
+      vc[i] = ldg_gather16(p + ey);
+      vd[i] = ldg_gather16(p + ey + ex);
     };
     int c_img = 0, c_pix[ITERS];
     auto set_tile = [&](int it) {
@@ -162,10 +185,10 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
       }
     };
     int l_it = 0, l_cb = 0, l_t = 0;             // load cursor: the K block whose gathers are in flight
-    const __nv_bfloat16* l_x = prm.xh + chunk * 4;
+    const __nv_bfloat16* l_x = prm.xh + chunk * 8;
     if (total > 0) {
       set_tile(0);
-      l_x = prm.xh + (size_t)c_img * prm.ximg + chunk * 4;
+      l_x = prm.xh + (size_t)c_img * prm.ximg + chunk * 8;
       dcn_mbar_wait(&bars.geo_full[0], 0u);
 #pragma unroll
       for (int i = 0; i < ITERS; ++i) gather(i, l_x, geo[row0 + i * NP * 4].x);
@@ -180,7 +203,7 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
           l_cb = 0; ++l_it;
           if (have_next) {
             const int tile = tile_first + l_it;
-            l_x = prm.xh + (size_t)(tile / prm.tiles_per_image) * prm.ximg + chunk * 4;
+            l_x = prm.xh + (size_t)(tile / prm.tiles_per_image) * prm.ximg + chunk * 8;
             dcn_mbar_wait(&bars.geo_full[l_it & 1], (unsigned)((l_it >> 1) & 1));
           }
         }
@@ -188,63 +211,51 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
       const __nv_bfloat16* l_xc = l_x + l_cb * kBK;
       const uint4* geo_n = geo + ((l_it & 1) * 9 + l_t) * kTileM + row0;
       const uint4* geo_c = geo + ((c_it & 1) * 9 + c_t) * kTileM + row0;
-      float* gxp = bw.gx + (size_t)c_img * prm.ximg + c_cb * kBK + chunk * 4;
-      asm volatile("" : "+l"(gxp));
       dcn_mbar_wait(&bars.g_full[gs], gph);
-      const uint8_t* g_tile = gring + (size_t)gs * g_bytes;
+      const uint8_t* g_lane = gring + (size_t)gs * g_bytes + g_off;
 #pragma unroll
       for (int i = 0; i < ITERS; ++i) {
         const uint4 q4 = geo_c[i * NP * 4];
-        uint4 gq;                                  // G channels [4c,4c+4) and [32+4c,32+4c+4) of this row
-        {
-          const uint8_t* grow = g_tile + (row0 + (uint32_t)(i * NP * 4)) * 128u + g_half;
-          const uint2 lo = *reinterpret_cast<const uint2*>(grow + g_sw_lo);
-          const uint2 hi = *reinterpret_cast<const uint2*>(grow + g_sw_hi);
-          gq = make_uint4(lo.x, lo.y, hi.x, hi.y);
-        }
-        const uint32_t e0 = q4.x;
+        const uint4 gq = *reinterpret_cast<const uint4*>(g_lane + (uint32_t)(i * NP * 4) * 128u);   // G channels [8c, 8c+8)
         const float lh = __uint_as_float(q4.y & 0x7fffffffu), lw = __uint_as_float(q4.z), m = __uint_as_float(q4.w);
-        const pk2 g2[4] = {bf2(gq.x), bf2(gq.y), bf2(gq.z), bf2(gq.w)};
-        const float d1 = dot8(g2, va[i]), d2 = dot8(g2, vb[i]), d3 = dot8(g2, vc[i]), d4 = dot8(g2, vd[i]);
+        const float d1 = dot8_bf(gq, va[i]), d2 = dot8_bf(gq, vb[i]), d3 = dot8_bf(gq, vc[i]), d4 = dot8_bf(gq, vd[i]);
         const float hh = 1.f - lh, hw = 1.f - lw;
         const float w1 = hh * hw, w2 = hh * lw, w3 = lh * hw, w4 = lh * lw;
-        if ((q4.y >> 31) == 0u) {                // tap outside the patch: scatter it here (deform_conv_cuda_kernel.cu:944)
-          float* gp = gxp + e0;
-          asm volatile("" : "+l"(gp));
-          auto scat = [&](float* q, float c) {
-            if (c != 0.f) {
-              const pk2 cc = pk(c, c);
-              float a0, a1, a2, a3;
-              upk(mul2(g2[0], cc), a0, a1); upk(mul2(g2[1], cc), a2, a3);
-              red_add_v4(q, a0, a1, a2, a3);
-              upk(mul2(g2[2], cc), a0, a1); upk(mul2(g2[3], cc), a2, a3);
-              red_add_v4(q + 32, a0, a1, a2, a3);
-            }
-          };
-          scat(gp, m * w1); scat(gp + ex, m * w2); scat(gp + ey, m * w3); scat(gp + ey + ex, m * w4);
+        if ((q4.y >> 31) == 0u && m != 0.f) {    // tap outside the patch (rare): scatter it here (deform_conv_cuda_kernel.cu:944)
+          float* gp = bw.gx + (size_t)c_img * prm.ximg + c_cb * kBK + chunk * 8 + q4.x;
+          dgrad_scatter8(gp, gq, m * w1); dgrad_scatter8(gp + ex, gq, m * w2);
+          dgrad_scatter8(gp + ey, gq, m * w3); dgrad_scatter8(gp + ey + ex, gq, m * w4);
         }
         if (have_next) gather(i, l_xc, geo_n[i * NP * 4].x);   // refill the slot: K block n+1, same row group
+        // this lane's share of the three per-(pixel, tap) sums
         float vm = w1 * d1 + w2 * d2 + w3 * d3 + w4 * d4;             // :1019-1030
         float vh = hw * (d3 - d1) + lw * (d4 - d2);                   // dmcn_get_coordinate_weight, bp_dir 0 (x mask below)
         float vw = hh * (d2 - d1) + lh * (d4 - d3);                   // bp_dir 1
-#pragma unroll
-        for (int o = 1; o < 8; o <<= 1) {
-          vm += __shfl_xor_sync(0xffffffffu, vm, o);
-          vh += __shfl_xor_sync(0xffffffffu, vh, o);
-          vw += __shfl_xor_sync(0xffffffffu, vw, o);
+        // 8-lane reduction of the three sums in 4 shuffles: after the first exchange the even lanes carry
+        // {vm, vh} and the odd lanes vw, after the second the lanes = 0 (mod 4) carry vm, = 2 (mod 4) vh
+        {
+          const float s1 = b0 ? vm : vw, r1 = __shfl_xor_sync(0xffffffffu, s1, 1);
+          const float r2 = __shfl_xor_sync(0xffffffffu, vh, 1);
+          float k0 = (b0 ? vw : vm) + r1;                              // even: vm, odd: vw
+          const float k1 = vh + r2;                                   // even lanes: vh
+          const float s3 = b0 ? k0 : (b1 ? k0 : k1), r3 = __shfl_xor_sync(0xffffffffu, s3, 2);
+          k0 = (b0 ? k0 : (b1 ? k1 : k0)) + r3;                       // 0 mod 4: vm, 2 mod 4: vh, odd: vw
+          k0 += __shfl_xor_sync(0xffffffffu, k0, 4);
+          vm = k0;
         }
-        if (chunk == 0) {
-          vh *= m; vw *= m;
-          float* a = acc + (3 * c_t) * kTileM + row0 + i * NP * 4;      // partial sums over channel blocks
-          if (c_cb > 0) { vm += a[0]; vh += a[kTileM]; vw += a[2 * kTileM]; }
+        if (chunk < 3) {                         // lane 0: grad_mask, lane 1: grad_offset w, lane 2: grad_offset h
+          const int which = chunk == 0 ? 0 : (chunk == 2 ? 1 : 2);    // slot in acc: {vm, vh, vw}
+          if (which) vm *= m;
+          float* a = acc + (3 * c_t + which) * kTileM + row0 + i * NP * 4;      // partial sums over channel blocks
+          if (c_cb > 0) vm += a[0];
           if (c_cb == cpb - 1) {
             if (c_pix[i] >= 0) {
-              bw.goff[((size_t)c_img * 18 + 2 * c_t) * P + c_pix[i]] = vh;
-              bw.goff[((size_t)c_img * 18 + 2 * c_t + 1) * P + c_pix[i]] = vw;
-              bw.gmask[((size_t)c_img * 9 + c_t) * P + c_pix[i]] = vm;
+              float* dst = which == 0 ? bw.gmask + ((size_t)c_img * 9 + c_t) * P
+                                      : bw.goff + ((size_t)c_img * 18 + 2 * c_t + (which - 1)) * P;
+              dst[c_pix[i]] = vm;
             }
           } else {
-            a[0] = vm; a[kTileM] = vh; a[2 * kTileM] = vw;
+            a[0] = vm;
           }
         }
       }
@@ -301,7 +312,7 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
     };
     int gs = 0; unsigned gph = 0;
     for (int n = 0; n < total; ++n) {
-      if (n >= 9 && (n % 9) == 3) flush(n / 9 - 1);                   // (its last MMA retired before acc_full[n - 1] did)
+      if (n >= 9 && (n % 9) == 5) flush(n / 9 - 1);                   // (GEMM 2 of that group has normally retired by now)
       const int ab = n & 1;
       dcn_mbar_wait(&bars.acc_full[ab], (unsigned)((n >> 1) & 1));
       tc_fence_after();
@@ -369,135 +380,139 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
       if (lane == 0) dcn_mbar_arrive(&bars.geo_full[buf]);
     }
   } else if (warp == NP + 8) {
-    // ===================================== MMA issuer =============================================
+    // ===================================== GEMM 1 issuer + weight loader ===========================
+    // One lane: G = gout[128 px, Cout] * Wt_kb[Cout, 64 ci] per K block, and the 1-D bulk copies of the
+    // transposed weight tiles (the slot of K block n - 1 is refilled with K block n - 1 + NW right after GEMM 1
+    // of K block n has been issued: its predecessor has normally retired by then).
     if (lane == 0) {
-      const uint32_t idesc1 = make_idesc_bf16(kTileM, kBK);                       // G[128 px, 64 ci]: A, B K-major
-      const uint32_t idesc2 = make_idesc_bf16(kTileM, kBK) | (1u << 16);          // patch[128 q, 64 ci]: B (= G) MN-major
+      const uint32_t idesc1 = make_idesc_bf16(kTileM, kBK);                       // A, B K-major
+      auto load_w = [&](int slot, int kblock) {
+        dcn_mbar_arrive_expect_tx(&bars.wt_full[slot], wt_bytes);
+        dcn_bulk_g2s(wtr + (size_t)slot * wt_bytes, bw.wt + (size_t)(kblock % KB) * Cout * kBK, wt_bytes, &bars.wt_full[slot]);
+      };
+      for (int k = 0; k < NW && k < total; ++k) load_w(k, k);
       int ws = 0; unsigned wph = 0;
-      uint32_t a_addr = 0u;
-      int kb1 = 0, it1 = 0;                        // cursor of GEMM 1: K block inside the tile, tile
-      int t2 = 0, grp2 = 0;                        // cursor of GEMM 2: tap, (tile, channel block) group
-      int gs2 = 0; unsigned gph2 = 0;
-      int sb = 0; unsigned sph = 0;
-      constexpr int D = 2;                         // GEMM 2 runs D K blocks behind GEMM 1
-      for (int n = 0; n < total + D; ++n) {
-        if (n < total) {
-          // ---- GEMM 1: G = gout[128 px, Cout] * Wt_kb[Cout, 64 ci] into accumulator n & 1 ----
-          const int gb = it1 % GB;
-          if (kb1 == 0) {
-            dcn_mbar_wait_relaxed(&bars.gout_full[gb], (unsigned)((it1 / GB) & 1), 0u);
-            a_addr = smem_u32(gout + (size_t)gb * gout_bytes);
-          }
-          const int ab = n & 1;
-          dcn_mbar_wait_relaxed(&bars.acc_empty[ab], (unsigned)(((n >> 1) & 1) ^ 1), 0u);
-          dcn_mbar_wait_relaxed(&bars.wt_full[ws], wph, 0u);
-          tc_fence_after();
-          const uint32_t b_addr = smem_u32(wtr + (size_t)ws * wt_bytes);
-          for (int j = 0; j < Cout / 64; ++j) {
-            const uint64_t adesc = make_sw128_desc(a_addr + (uint32_t)j * kTileM * 128u);
-            const uint64_t bdesc = make_sw128_desc(b_addr + (uint32_t)j * 64u * 128u);
-#pragma unroll
-            for (int k4 = 0; k4 < 4; ++k4)
-              umma_bf16(tmem + (uint32_t)(ab * kBK), adesc + 2 * k4, bdesc + 2 * k4, idesc1, (uint32_t)((j | k4) != 0));
-          }
-          umma_commit(&bars.wt_empty[ws]);
-          umma_commit(&bars.acc_full[ab]);
-          if (++ws == NW) { ws = 0; wph ^= 1u; }
-          if (++kb1 == KB) { kb1 = 0; ++it1; umma_commit(&bars.gout_empty[gb]); }
+      int ps = 0; unsigned pph = 0;                // slot / phase of the K block issued last
+      uint64_t a0 = 0ull;
+      int kb1 = 0, it1 = 0;
+      for (int n = 0; n < total; ++n) {
+        const int gb = it1 % GB;
+        if (kb1 == 0) {
+          dcn_mbar_wait_relaxed(&bars.gout_full[gb], (unsigned)((it1 / GB) & 1), 0u);
+          a0 = make_sw128_desc(smem_u32(gout + (size_t)gb * gout_bytes));
         }
-        if (n >= D) {
-          // ---- GEMM 2: patch[mb] += S_chunk[128 q, 128 px] * G[128 px, 64 ci], K block n - D ----
-          const int pb = grp2 & 1;
-          if (t2 == 0) dcn_mbar_wait_relaxed(&bars.patch_empty[pb], (unsigned)(((grp2 >> 1) & 1) ^ 1), 0u);
-          dcn_mbar_wait_relaxed(&bars.g_full[gs2], gph2, 0u);
-          const uint32_t g_addr = smem_u32(gring + (size_t)gs2 * g_bytes);
-          for (int mb = 0; mb < kPatchMB; ++mb) {
-            dcn_mbar_wait_relaxed(&bars.s_full[sb], sph, 0u);
-            tc_fence_after();
-            const uint32_t s_addr = smem_u32(sring + (size_t)sb * kSChunkBytes);
-            const uint32_t d_tmem = tmem + (uint32_t)(128 + pb * (kPatchMB * kBK) + mb * kBK);
+        const int ab = n & 1;
+        dcn_mbar_wait_relaxed(&bars.acc_empty[ab], (unsigned)(((n >> 1) & 1) ^ 1), 0u);
+        dcn_mbar_wait_relaxed(&bars.wt_full[ws], wph, 0u);
+        tc_fence_after();
+        const uint64_t b0 = make_sw128_desc(smem_u32(wtr + (size_t)ws * wt_bytes));
+        const uint32_t d_tmem = tmem + (uint32_t)(ab * kBK);
+        for (int j = 0; j < Cout / 64; ++j) {
+          const uint64_t adesc = a0 + (uint64_t)(j * (kTileM * 128 / 16)), bdesc = b0 + (uint64_t)(j * (64 * 128 / 16));
 #pragma unroll
-            for (int k8 = 0; k8 < kTileM / 16; ++k8) {     // K = 16 pixels: 32 B of an S row, 2 swizzle atoms of G
-              const uint64_t adesc = make_sw128_desc(s_addr + (uint32_t)(k8 >> 2) * 16384u) + 2 * (k8 & 3);
-              const uint64_t bdesc = make_sw128_desc_mn(g_addr + k8 * 2048u, 1024u);
-              umma_bf16(d_tmem, adesc, bdesc, idesc2, (uint32_t)((t2 | k8) != 0));
-            }
-            umma_commit(&bars.s_empty[sb]);
-            if (++sb == NSB) { sb = 0; sph ^= 1u; }
-          }
-          umma_commit(&bars.g_empty[gs2]);
-          if (++gs2 == NG) { gs2 = 0; gph2 ^= 1u; }
-          if (++t2 == 9) { t2 = 0; umma_commit(&bars.patch_full[pb]); ++grp2; }
+          for (int k4 = 0; k4 < 4; ++k4)
+            umma_bf16(d_tmem, adesc + 2 * k4, bdesc + 2 * k4, idesc1, (uint32_t)((j | k4) != 0));
         }
+        umma_commit(&bars.wt_empty[ws]);
+        umma_commit(&bars.acc_full[ab]);
+        if (++kb1 == KB) { kb1 = 0; ++it1; umma_commit(&bars.gout_empty[gb]); }
+        if (n > 0 && n - 1 + NW < total) {
+          dcn_mbar_wait_relaxed(&bars.wt_empty[ps], pph, 0u);
+          load_w(ps, n - 1 + NW);
+        }
+        ps = ws; pph = wph;
+        if (++ws == NW) { ws = 0; wph ^= 1u; }
       }
     }
     __syncwarp();
   } else if (warp == NP + 9) {
-    // ===================================== transposed-weight tile loader ==========================
+    // ===================================== GEMM 2 issuer ===========================================
+    // One lane: patch[mb] += S_chunk[128 q, 128 px] * G[128 px, 64 ci] for the three M blocks of every K block
     if (lane == 0) {
-      int ws = 0; unsigned wph = 0;
-      for (int it = 0; it < my_tiles; ++it) {
-        for (int kb = 0; kb < KB; ++kb) {
-          dcn_mbar_wait_relaxed(&bars.wt_empty[ws], wph ^ 1u, 20u);
-          dcn_mbar_arrive_expect_tx(&bars.wt_full[ws], wt_bytes);
-          dcn_bulk_g2s(wtr + (size_t)ws * wt_bytes, bw.wt + (size_t)kb * Cout * kBK, wt_bytes, &bars.wt_full[ws]);
-          if (++ws == NW) { ws = 0; wph ^= 1u; }
+      const uint32_t idesc2 = make_idesc_bf16(kTileM, kBK) | (1u << 16);          // B (= the G tile) MN-major
+      int t2 = 0, grp2 = 0;
+      int gs2 = 0; unsigned gph2 = 0;
+      int sb = 0; unsigned sph = 0;
+      for (int n = 0; n < total; ++n) {
+        const int pb = grp2 & 1;
+        if (t2 == 0) dcn_mbar_wait_relaxed(&bars.patch_empty[pb], (unsigned)(((grp2 >> 1) & 1) ^ 1), 0u);
+        dcn_mbar_wait_relaxed(&bars.g_full[gs2], gph2, 0u);
+        const uint64_t b0 = make_sw128_desc_mn(smem_u32(gring + (size_t)gs2 * g_bytes), 1024u);
+        const uint32_t d0 = tmem + (uint32_t)(128 + pb * (kPatchMB * kBK));
+#pragma unroll
+        for (int mb = 0; mb < kPatchMB; ++mb) {
+          dcn_mbar_wait_relaxed(&bars.s_full[sb], sph, 0u);
+          tc_fence_after();
+          const uint64_t a0 = make_sw128_desc(smem_u32(sring + (size_t)sb * kSChunkBytes));
+#pragma unroll
+          for (int k8 = 0; k8 < kTileM / 16; ++k8)         // K = 16 pixels: 32 B of an S row, 2 swizzle atoms (2 KB) of G
+            umma_bf16(d0 + (uint32_t)(mb * kBK), a0 + (uint64_t)((k8 >> 2) * 1024 + 2 * (k8 & 3)), b0 + (uint64_t)(k8 * 128),
+                      idesc2, (uint32_t)((t2 | k8) != 0));
+          umma_commit(&bars.s_empty[sb]);
+          sb ^= 1; if (sb == 0) sph ^= 1u;
         }
+        umma_commit(&bars.g_empty[gs2]);
+        if (++gs2 == NG) { gs2 = 0; gph2 ^= 1u; }
+        if (++t2 == 9) { t2 = 0; umma_commit(&bars.patch_full[pb]); ++grp2; }
       }
     }
     __syncwarp();
   } else {
     // ===================================== S builders ==============================================
-    // thread = 2 pixels (columns p of S); per chunk: clear what this thread wrote into the buffer last time,
-    // write the corners of this tap that fall into M block mb
+    // thread = 2 pixels (columns p of S).  An entry e = (M block << 16) | byte offset inside the chunk, ~0 = none.
+    // Chunk c = 3 n + mb lives in buffer c & 1, whose previous content was chunk c - 2 = (n, 0) for mb = 2,
+    // (n - 1, 2) for mb = 1, (n - 1, 1) for mb = 0: un-written from the entries of this / the previous K block.
     const int bt = tid - (NP + 10) * 32;           // 0..63
+    uint32_t cur[2][4], prv[2][4];
+#pragma unroll
+    for (int h = 0; h < 2; ++h)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) cur[h][c] = 0xffffffffu;
     int sb = 0; unsigned sph = 0;
     int it = 0, cbk = 0, t = 0;
     for (int n = 0; n < total; ++n) {
       if (cbk == 0 && t == 0) dcn_mbar_wait(&bars.geo_full[it & 1], (unsigned)((it >> 1) & 1));
       const int gi = ((it & 1) * 9 + t) * kTileM;
-      int q0[2]; uint32_t wv[2][4];
+      unsigned short wv[2][4];
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
-        const int p = bt + 64 * h;
-        q0[h] = sqt[gi + p];
+        const uint32_t p = (uint32_t)(bt + 64 * h);
+        const int q0 = sqt[gi + p];
         const uint4 g4 = geo[gi + p];
         const float lh = __uint_as_float(g4.y & 0x7fffffffu), lw = __uint_as_float(g4.z), m = __uint_as_float(g4.w);
         const float hh = 1.f - lh, hw = 1.f - lw;
-        wv[h][0] = (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(m * (hh * hw)));
-        wv[h][1] = (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(m * (hh * lw)));
-        wv[h][2] = (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(m * (lh * hw)));
-        wv[h][3] = (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(m * (lh * lw)));
+        wv[h][0] = __bfloat16_as_ushort(__float2bfloat16_rn(m * (hh * hw)));
+        wv[h][1] = __bfloat16_as_ushort(__float2bfloat16_rn(m * (hh * lw)));
+        wv[h][2] = __bfloat16_as_ushort(__float2bfloat16_rn(m * (lh * hw)));
+        wv[h][3] = __bfloat16_as_ushort(__float2bfloat16_rn(m * (lh * lw)));
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          prv[h][c] = cur[h][c];
+          const uint32_t qc = (uint32_t)(q0 + (c & 1) + (c >> 1) * kPatchW);
+          cur[h][c] = q0 >= 0 ? (((qc >> 7) << 16) | s_chunk_offset(qc & 127u, p)) : 0xffffffffu;
+        }
       }
+#pragma unroll
       for (int mb = 0; mb < kPatchMB; ++mb) {
         dcn_mbar_wait(&bars.s_empty[sb], sph ^ 1u);
         uint8_t* chunk = sring + (size_t)sb * kSChunkBytes;
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          const int p = bt + 64 * h;
-          const int pe = sprev[sb * kTileM + p];                   // (cell written last | M block << 16), -1: nothing
-          const int pq = (int)(short)(pe & 0xffff), mbp = pe >> 16;
-          if (pq >= 0) {
+        for (int h = 0; h < 2; ++h)
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
-              const int qc = pq + (c & 1) + (c >> 1) * kPatchW;
-              if ((qc >> 7) == mbp) *reinterpret_cast<unsigned short*>(chunk + s_chunk_offset((uint32_t)(qc & 127), (uint32_t)p)) = 0;
-            }
+          for (int c = 0; c < 4; ++c) {
+            const uint32_t old = mb == 2 ? cur[h][c] : prv[h][c];
+            const uint32_t old_mb = mb == 2 ? 0u : (mb == 1 ? 2u : 1u);
+            if ((old >> 16) == old_mb) *reinterpret_cast<unsigned short*>(chunk + (old & 0xffffu)) = 0;
           }
-          if (q0[h] >= 0) {
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
-              const int qc = q0[h] + (c & 1) + (c >> 1) * kPatchW;
-              if ((qc >> 7) == mb)
-                *reinterpret_cast<unsigned short*>(chunk + s_chunk_offset((uint32_t)(qc & 127), (uint32_t)p)) = (unsigned short)wv[h][c];
-            }
-          }
-          sprev[sb * kTileM + p] = q0[h] >= 0 ? (q0[h] | (mb << 16)) : -1;
-        }
+        for (int h = 0; h < 2; ++h)
+#pragma unroll
+          for (int c = 0; c < 4; ++c)
+            if ((cur[h][c] >> 16) == (uint32_t)mb) *reinterpret_cast<unsigned short*>(chunk + (cur[h][c] & 0xffffu)) = wv[h][c];
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncwarp();
         if (lane == 0) dcn_mbar_arrive(&bars.s_full[sb]);
-        if (++sb == NSB) { sb = 0; sph ^= 1u; }
+        sb ^= 1; if (sb == 0) sph ^= 1u;
       }
       if (++t == 9) {
         t = 0;
