@@ -213,49 +213,65 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
       const uint4* geo_c = geo + ((c_it & 1) * 9 + c_t) * kTileM + row0;
       dcn_mbar_wait(&bars.g_full[gs], gph);
       const uint8_t* g_lane = gring + (size_t)gs * g_bytes + g_off;
+      // both rows of the thread in lock step (16 independent FMA chains, the shuffles of the two reductions
+      // overlap): the loop is latency-bound with 4 consumer warps per scheduler
+      uint4 q4[ITERS], gq[ITERS];
+      float d[ITERS][4];
 #pragma unroll
       for (int i = 0; i < ITERS; ++i) {
-        const uint4 q4 = geo_c[i * NP * 4];
-        const uint4 gq = *reinterpret_cast<const uint4*>(g_lane + (uint32_t)(i * NP * 4) * 128u);   // G channels [8c, 8c+8)
-        const float lh = __uint_as_float(q4.y & 0x7fffffffu), lw = __uint_as_float(q4.z), m = __uint_as_float(q4.w);
-        const float d1 = dot8_bf(gq, va[i]), d2 = dot8_bf(gq, vb[i]), d3 = dot8_bf(gq, vc[i]), d4 = dot8_bf(gq, vd[i]);
+        q4[i] = geo_c[i * NP * 4];
+        gq[i] = *reinterpret_cast<const uint4*>(g_lane + (uint32_t)(i * NP * 4) * 128u);   // G channels [8c, 8c+8)
+      }
+#pragma unroll
+      for (int i = 0; i < ITERS; ++i) {
+        d[i][0] = dot8_bf(gq[i], va[i]); d[i][1] = dot8_bf(gq[i], vb[i]);
+        d[i][2] = dot8_bf(gq[i], vc[i]); d[i][3] = dot8_bf(gq[i], vd[i]);
+      }
+      if (have_next) {
+#pragma unroll
+        for (int i = 0; i < ITERS; ++i) gather(i, l_xc, geo_n[i * NP * 4].x);   // refill: K block n+1, same row groups
+      }
+      float red[ITERS], msk[ITERS];
+#pragma unroll
+      for (int i = 0; i < ITERS; ++i) {
+        const float lh = __uint_as_float(q4[i].y & 0x7fffffffu), lw = __uint_as_float(q4[i].z), m = __uint_as_float(q4[i].w);
         const float hh = 1.f - lh, hw = 1.f - lw;
         const float w1 = hh * hw, w2 = hh * lw, w3 = lh * hw, w4 = lh * lw;
-        if ((q4.y >> 31) == 0u && m != 0.f) {    // tap outside the patch (rare): scatter it here (deform_conv_cuda_kernel.cu:944)
-          float* gp = bw.gx + (size_t)c_img * prm.ximg + c_cb * kBK + chunk * 8 + q4.x;
-          dgrad_scatter8(gp, gq, m * w1); dgrad_scatter8(gp + ex, gq, m * w2);
-          dgrad_scatter8(gp + ey, gq, m * w3); dgrad_scatter8(gp + ey + ex, gq, m * w4);
+        msk[i] = m;
+        if ((q4[i].y >> 31) == 0u && m != 0.f) {  // tap outside the patch (rare): scatter it here (deform_conv_cuda_kernel.cu:944)
+          float* gp = bw.gx + (size_t)c_img * prm.ximg + c_cb * kBK + chunk * 8 + q4[i].x;
+          dgrad_scatter8(gp, gq[i], m * w1); dgrad_scatter8(gp + ex, gq[i], m * w2);
+          dgrad_scatter8(gp + ey, gq[i], m * w3); dgrad_scatter8(gp + ey + ex, gq[i], m * w4);
         }
-        if (have_next) gather(i, l_xc, geo_n[i * NP * 4].x);   // refill the slot: K block n+1, same row group
         // this lane's share of the three per-(pixel, tap) sums
-        float vm = w1 * d1 + w2 * d2 + w3 * d3 + w4 * d4;             // :1019-1030
-        float vh = hw * (d3 - d1) + lw * (d4 - d2);                   // dmcn_get_coordinate_weight, bp_dir 0 (x mask below)
-        float vw = hh * (d2 - d1) + lh * (d4 - d3);                   // bp_dir 1
+        const float vm = w1 * d[i][0] + w2 * d[i][1] + w3 * d[i][2] + w4 * d[i][3];   // :1019-1030
+        const float vh = hw * (d[i][2] - d[i][0]) + lw * (d[i][3] - d[i][1]);         // dmcn_get_coordinate_weight, bp_dir 0 (x mask below)
+        const float vw = hh * (d[i][1] - d[i][0]) + lh * (d[i][3] - d[i][2]);         // bp_dir 1
         // 8-lane reduction of the three sums in 4 shuffles: after the first exchange the even lanes carry
         // {vm, vh} and the odd lanes vw, after the second the lanes = 0 (mod 4) carry vm, = 2 (mod 4) vh
-        {
-          const float s1 = b0 ? vm : vw, r1 = __shfl_xor_sync(0xffffffffu, s1, 1);
-          const float r2 = __shfl_xor_sync(0xffffffffu, vh, 1);
-          float k0 = (b0 ? vw : vm) + r1;                              // even: vm, odd: vw
-          const float k1 = vh + r2;                                   // even lanes: vh
-          const float s3 = b0 ? k0 : (b1 ? k0 : k1), r3 = __shfl_xor_sync(0xffffffffu, s3, 2);
-          k0 = (b0 ? k0 : (b1 ? k1 : k0)) + r3;                       // 0 mod 4: vm, 2 mod 4: vh, odd: vw
-          k0 += __shfl_xor_sync(0xffffffffu, k0, 4);
-          vm = k0;
-        }
-        if (chunk < 3) {                         // lane 0: grad_mask, lane 1: grad_offset w, lane 2: grad_offset h
-          const int which = chunk == 0 ? 0 : (chunk == 2 ? 1 : 2);    // slot in acc: {vm, vh, vw}
-          if (which) vm *= m;
+        const float r1 = __shfl_xor_sync(0xffffffffu, b0 ? vm : vw, 1);
+        const float r2 = __shfl_xor_sync(0xffffffffu, vh, 1);
+        float k0 = (b0 ? vw : vm) + r1;                                // even: vm, odd: vw
+        const float k1 = vh + r2;                                     // even lanes: vh
+        const float r3 = __shfl_xor_sync(0xffffffffu, (b0 || b1) ? k0 : k1, 2);
+        k0 = ((!b0 && b1) ? k1 : k0) + r3;                             // 0 mod 4: vm, 2 mod 4: vh, odd: vw
+        red[i] = k0 + __shfl_xor_sync(0xffffffffu, k0, 4);
+      }
+      if (chunk < 3) {                           // lane 0: grad_mask, lane 2: grad_offset h, lane 1: grad_offset w
+        const int which = chunk == 0 ? 0 : (chunk == 2 ? 1 : 2);      // slot in acc: {vm, vh, vw}
+#pragma unroll
+        for (int i = 0; i < ITERS; ++i) {
+          float v = which ? red[i] * msk[i] : red[i];
           float* a = acc + (3 * c_t + which) * kTileM + row0 + i * NP * 4;      // partial sums over channel blocks
-          if (c_cb > 0) vm += a[0];
+          if (c_cb > 0) v += a[0];
           if (c_cb == cpb - 1) {
             if (c_pix[i] >= 0) {
               float* dst = which == 0 ? bw.gmask + ((size_t)c_img * 9 + c_t) * P
                                       : bw.goff + ((size_t)c_img * 18 + 2 * c_t + (which - 1)) * P;
-              dst[c_pix[i]] = vm;
+              dst[c_pix[i]] = v;
             }
           } else {
-            a[0] = vm;
+            a[0] = v;
           }
         }
       }
