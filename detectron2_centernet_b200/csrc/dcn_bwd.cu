@@ -728,12 +728,12 @@ extern "C" int dcnv2_backward(const float* input, const float* weight, const flo
     const unsigned grid = (unsigned)(tiles < kNumSMs ? tiles : kNumSMs);
     const int npd = dcn_tunables().dgrad_warps;
     bool launched = false;
-    if (dcn_tunables().dgrad_gemm && npd == 16 && stride_h == 1 && dilation_h == 1 && Cout <= 128) {
+    if (dcn_tunables().dgrad_gemm && npd == 16 && stride_h == 1 && dilation_h == 1 && Cout <= 128 && H < 32000 && W < 32000) {
       // second form: the grad_input scatter as a tensor-core GEMM (dcn_dgrad2.cuh)
-      bw.gout_bufs = Cout <= 64 ? 2 : 1;
+      bw.gout_bufs = Cout <= 64 ? dcn_tunables().dgrad_gb : 1;
       bw.s_bufs = 2;                                     // (the builders' un-write bookkeeping assumes two buffers)
       const size_t fixed = 1024 + (size_t)bw.gout_bufs * gout_bytes + (size_t)bw.s_bufs * kSChunkBytes + kDgGeoBytes +
-                           kDg2SqBytes + kDgAccBytes;
+                           2 * kDgAccBytes;
       const size_t unit = (size_t)Cout * 128 + (size_t)kTileM * 128;
       int ring = fixed < 226 * 1024 ? (int)((226 * 1024 - fixed) / unit) : 0;
       if (ring > kDgMaxRing) ring = kDgMaxRing;

@@ -347,6 +347,7 @@ struct DcnTunables {
   int producer_warps;    // CTDET_DCN_PRODUCER_WARPS  gather warps of the forward kernel, 16 or 8 (16)
   int dgrad_warps;       // CTDET_DCN_DGRAD_WARPS     consumer warps of the dgrad kernel, 16 or 8 (16)
   int dgrad_gemm;        // CTDET_DCN_DGRAD_GEMM      1: grad_input scatter as a tensor-core GEMM where supported (1)
+  int dgrad_gb;          // CTDET_DCN_DGRAD_GB        grad_output tile buffers of that kernel at Cout = 64: 1 or 2 (1)
 };
 static inline const DcnTunables& dcn_tunables() {
   static const DcnTunables t = [] {
@@ -358,6 +359,7 @@ static inline const DcnTunables& dcn_tunables() {
     r.producer_warps = env("CTDET_DCN_PRODUCER_WARPS", 16) == 8 ? 8 : 16;
     r.dgrad_warps = env("CTDET_DCN_DGRAD_WARPS", 16) == 8 ? 8 : 16;
     r.dgrad_gemm = env("CTDET_DCN_DGRAD_GEMM", 1) != 0;
+    r.dgrad_gb = env("CTDET_DCN_DGRAD_GB", 1) == 2 ? 2 : 1;
     return r;
   }();
   return t;

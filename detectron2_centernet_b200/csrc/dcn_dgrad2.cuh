@@ -21,7 +21,6 @@ constexpr int kPatchH = 16, kPatchW = 24, kPatchR = 3;     // cells; the tile's 
 constexpr int kPatchMB = kPatchH * kPatchW / kTileM;       // 3 M blocks
 constexpr int kSChunkBytes = kTileM * kTileM * 2;          // S[128 q][128 p] bf16 = two K halves of [128][128 B]
 constexpr int kDg2MaxS = 3;
-constexpr int kDg2SqBytes = 2 * 9 * kTileM * 4;
 static_assert(kPatchH * kPatchW == kPatchMB * kTileM, "patch must be whole M blocks");
 
 struct Dgrad2Barriers {
@@ -34,30 +33,34 @@ struct Dgrad2Barriers {
   uint64_t patch_full[2], patch_empty[2];   // TMEM patch accumulators                (MMA -> transfer)
 };
 
-// {e, lh | flag, lw, mask} as tap_geometry_raw, plus the patch cell of the top-left corner: *sq = qy*24 + qx when
-// all four corners lie inside the tile's patch (then bit 31 of .y is set: the GEMM scatters this tap), else -1.
+// Sampling geometry of one (pixel, tap): {h_low | w_low << 16 (two int16), lh | flag, lw, mask}.  The element offset
+// of the top-left corner in the bordered NHWC image and the patch cell are derived from (h_low, w_low) by their
+// users (16 B per entry, no second table: the kernel is short of shared memory).  A tap the reference does not
+// sample (deform_conv_cuda_kernel.cu:852) has h_low = w_low = -1 (the zero corner pixel of the border) and mask 0.
+// Bit 31 of .y (lh >= 0) is set when all four corners lie inside the tile's patch: the GEMM scatters this tap.
 __device__ __forceinline__ uint4 tap_geometry_patch(const DcnParams& prm, float off_h, float off_w, float m,
-                                                    int ho, int wo, bool valid, int t, int py0, int px0, int* sq) {
-  uint4 o = make_uint4(0u, 0u, 0u, 0u);
-  *sq = -1;
+                                                    int ho, int wo, bool valid, int t, int py0, int px0) {
+  uint4 o = make_uint4(0xffffffffu, 0u, 0u, 0u);
   if (valid) {
     const int i = t / 3, j = t - 3 * i;
     const float h_im = (float)(ho - prm.pad + i) + off_h;
     const float w_im = (float)(wo - prm.pad + j) + off_w;
     if (h_im > -1.f && w_im > -1.f && h_im < (float)prm.H && w_im < (float)prm.W) {
       const int h_low = (int)floorf(h_im), w_low = (int)floorf(w_im);
-      o.x = (uint32_t)((h_low + 1) * prm.xw + w_low + 1) * (uint32_t)prm.Cin;
+      o.x = ((uint32_t)h_low & 0xffffu) | ((uint32_t)w_low << 16);
       o.y = __float_as_uint(h_im - (float)h_low);
       o.z = __float_as_uint(w_im - (float)w_low);
       o.w = __float_as_uint(m);
       const int qy = h_low - py0, qx = w_low - px0;
-      if (qy >= 0 && qy <= kPatchH - 2 && qx >= 0 && qx <= kPatchW - 2) {
-        *sq = qy * kPatchW + qx;
-        o.y |= 0x80000000u;
-      }
+      if (qy >= 0 && qy <= kPatchH - 2 && qx >= 0 && qx <= kPatchW - 2) o.y |= 0x80000000u;
     }
   }
   return o;
+}
+// element offset of the top-left corner in the bordered image (rows of xw pixels, one border pixel either side)
+__device__ __forceinline__ uint32_t geo_corner_offset(uint32_t hw, int xw, int Cin) {
+  const int hl = (int)(short)(hw & 0xffffu), wl = (int)hw >> 16;
+  return (uint32_t)((hl + 1) * xw + wl + 1) * (uint32_t)Cin;
 }
 
 // byte offset of S[qrow][p] inside a chunk: K-major, 128-byte swizzle, K halves of 64 pixels 16 KB apart
@@ -115,9 +118,8 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
   uint8_t* wtr = gout + (size_t)GB * gout_bytes;                      // [NW][Cout/64][64][128 B]
   uint8_t* gring = wtr + (size_t)NW * wt_bytes;                       // [NG][128][128 B]
   uint8_t* sring = gring + (size_t)NG * g_bytes;                      // [NSB][2][128][128 B]
-  uint4* geo = reinterpret_cast<uint4*>(sring + (size_t)NSB * kSChunkBytes);   // [2][9][128] {e, lh | flag, lw, mask}
-  int* sqt = reinterpret_cast<int*>(reinterpret_cast<uint8_t*>(geo) + kDgGeoBytes);      // [2][9][128] patch cell or -1
-  float* acc = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(sqt) + kDg2SqBytes);  // [27][128]
+  uint4* geo = reinterpret_cast<uint4*>(sring + (size_t)NSB * kSChunkBytes);   // [2][9][128] {h_low | w_low, lh | flag, lw, mask}
+  float* acc = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(geo) + kDgGeoBytes);  // [2][27][128] per-tile sums
   const int cpb = Cin / kBK, KB = 9 * cpb;
   const int tile_first = (int)(((long long)blockIdx.x * prm.num_tiles) / gridDim.x);
   const int my_tiles = (int)(((long long)(blockIdx.x + 1) * prm.num_tiles) / gridDim.x) - tile_first;
@@ -171,27 +173,13 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
       vc[i] = ldg_gather16(p + ey);
       vd[i] = ldg_gather16(p + ey + ex);
     };
-    int c_img = 0, c_pix[ITERS];
-    auto set_tile = [&](int it) {
-      int tile = tile_first + it;
-      c_img = tile / prm.tiles_per_image;
-      tile -= c_img * prm.tiles_per_image;
-      const int tile_y = tile / prm.tiles_x, tile_x = tile - tile_y * prm.tiles_x;
-#pragma unroll
-      for (int i = 0; i < ITERS; ++i) {
-        const int r = (int)row0 + i * NP * 4;
-        const int ho = tile_y * kTileH + (r >> 4), wo = tile_x * kTileW + (r & 15);
-        c_pix[i] = (ho < prm.Ho && wo < prm.Wo) ? ho * prm.Wo + wo : -1;
-      }
-    };
     int l_it = 0, l_cb = 0, l_t = 0;             // load cursor: the K block whose gathers are in flight
     const __nv_bfloat16* l_x = prm.xh + chunk * 8;
     if (total > 0) {
-      set_tile(0);
-      l_x = prm.xh + (size_t)c_img * prm.ximg + chunk * 8;
+      l_x = prm.xh + (size_t)(tile_first / prm.tiles_per_image) * prm.ximg + chunk * 8;
       dcn_mbar_wait(&bars.geo_full[0], 0u);
 #pragma unroll
-      for (int i = 0; i < ITERS; ++i) gather(i, l_x, geo[row0 + i * NP * 4].x);
+      for (int i = 0; i < ITERS; ++i) gather(i, l_x, geo_corner_offset(geo[row0 + i * NP * 4].x, prm.xw, Cin));
     }
     int gs = 0; unsigned gph = 0;
     for (int n = 0; n < total; ++n) {
@@ -229,7 +217,7 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
       }
       if (have_next) {
 #pragma unroll
-        for (int i = 0; i < ITERS; ++i) gather(i, l_xc, geo_n[i * NP * 4].x);   // refill: K block n+1, same row groups
+        for (int i = 0; i < ITERS; ++i) gather(i, l_xc, geo_corner_offset(geo_n[i * NP * 4].x, prm.xw, Cin));   // refill: K block n+1
       }
       float red[ITERS], msk[ITERS];
 #pragma unroll
@@ -239,7 +227,8 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
         const float w1 = hh * hw, w2 = hh * lw, w3 = lh * hw, w4 = lh * lw;
         msk[i] = m;
         if ((q4[i].y >> 31) == 0u && m != 0.f) {  // tap outside the patch (rare): scatter it here (deform_conv_cuda_kernel.cu:944)
-          float* gp = bw.gx + (size_t)c_img * prm.ximg + c_cb * kBK + chunk * 8 + q4[i].x;
+          float* gp = bw.gx + (size_t)((tile_first + c_it) / prm.tiles_per_image) * prm.ximg + c_cb * kBK + chunk * 8 +
+                      geo_corner_offset(q4[i].x, prm.xw, Cin);
           dgrad_scatter8(gp, gq[i], m * w1); dgrad_scatter8(gp + ex, gq[i], m * w2);
           dgrad_scatter8(gp + ey, gq[i], m * w3); dgrad_scatter8(gp + ey + ex, gq[i], m * w4);
         }
@@ -258,21 +247,14 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
         red[i] = k0 + __shfl_xor_sync(0xffffffffu, k0, 4);
       }
       if (chunk < 3) {                           // lane 0: grad_mask, lane 2: grad_offset h, lane 1: grad_offset w
-        const int which = chunk == 0 ? 0 : (chunk == 2 ? 1 : 2);      // slot in acc: {vm, vh, vw}
+        // into the tile's table of sums over channel blocks; the geometry warps write it out once the tile is done
+        const int which = chunk == 0 ? 0 : (chunk == 2 ? 1 : 2);      // slot: {vm, vh, vw}
+        float* a = acc + ((c_it & 1) * 27 + 3 * c_t + which) * kTileM + row0;
 #pragma unroll
         for (int i = 0; i < ITERS; ++i) {
           float v = which ? red[i] * msk[i] : red[i];
-          float* a = acc + (3 * c_t + which) * kTileM + row0 + i * NP * 4;      // partial sums over channel blocks
-          if (c_cb > 0) v += a[0];
-          if (c_cb == cpb - 1) {
-            if (c_pix[i] >= 0) {
-              float* dst = which == 0 ? bw.gmask + ((size_t)c_img * 9 + c_t) * P
-                                      : bw.goff + ((size_t)c_img * 18 + 2 * c_t + (which - 1)) * P;
-              dst[c_pix[i]] = v;
-            }
-          } else {
-            a[0] = v;
-          }
+          if (c_cb > 0) v += a[i * NP * 4];
+          a[i * NP * 4] = v;
         }
       }
       __syncwarp();
@@ -281,7 +263,6 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
         if (l_it != c_it) dcn_mbar_arrive(&bars.geo_empty[c_it & 1]);
       }
       if (++gs == NG) { gs = 0; gph ^= 1u; }
-      if (l_it != c_it && have_next) set_tile(l_it);
     }
   } else if (warp < NP + 4) {
     // ===================================== transfer: TMEM -> bf16 G tile; patch flush =============
@@ -361,6 +342,26 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
     // ===================================== grad_output tile + geometry ============================
     if (NP == 16) asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
     const int r = ((warp - NP - 4) << 5) + lane;
+    // grad_offset / grad_mask of a finished tile: acc[tile & 1] -> global (the consumers' arrivals on geo_empty
+    // order their shared-memory writes before this)
+    auto drain = [&](int itd) {
+      int tile = tile_first + itd;
+      const int b = tile / prm.tiles_per_image;
+      tile -= b * prm.tiles_per_image;
+      const int tile_y = tile / prm.tiles_x, tile_x = tile - tile_y * prm.tiles_x;
+      const int ho = tile_y * kTileH + (r >> 4), wo = tile_x * kTileW + (r & 15);
+      if (ho < prm.Ho && wo < prm.Wo) {
+        const float* a = acc + (itd & 1) * 27 * kTileM + r;
+        float* gm = bw.gmask + (size_t)b * 9 * P + ho * prm.Wo + wo;
+        float* go = bw.goff + (size_t)b * 18 * P + ho * prm.Wo + wo;
+#pragma unroll
+        for (int t = 0; t < 9; ++t) {
+          gm[(size_t)t * P] = a[(3 * t) * kTileM];
+          go[(size_t)(2 * t) * P] = a[(3 * t + 1) * kTileM];
+          go[(size_t)(2 * t + 1) * P] = a[(3 * t + 2) * kTileM];
+        }
+      }
+    };
     for (int it = 0; it < my_tiles; ++it) {
       int tile = tile_first + it;
       const int gb = it % GB;
@@ -370,6 +371,9 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
       __syncwarp();
       if (lane == 0) dcn_mbar_arrive(&bars.gout_full[gb]);
 
+      const int buf = it & 1;
+      dcn_mbar_wait_relaxed(&bars.geo_empty[buf], (unsigned)(((it >> 1) & 1) ^ 1));   // tile it - 2 is done
+      if (it >= 2) drain(it - 2);
       const int b = tile / prm.tiles_per_image;
       tile -= b * prm.tiles_per_image;
       const int tile_y = tile / prm.tiles_x, tile_x = tile - tile_y * prm.tiles_x;
@@ -384,16 +388,16 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
       for (int k = 0; k < 18; ++k) ov[k] = ldg_stream1(offb + (size_t)k * P);
 #pragma unroll
       for (int k = 0; k < 9; ++k) mv[k] = ldg_stream1(mskb + (size_t)k * P);
-      const int buf = it & 1;
-      dcn_mbar_wait_relaxed(&bars.geo_empty[buf], (unsigned)(((it >> 1) & 1) ^ 1));
 #pragma unroll
-      for (int t = 0; t < 9; ++t) {
-        int sq;
-        geo[(buf * 9 + t) * kTileM + r] = tap_geometry_patch(prm, ov[2 * t], ov[2 * t + 1], mv[t], ho, wo, valid, t, py0, px0, &sq);
-        sqt[(buf * 9 + t) * kTileM + r] = sq;
-      }
+      for (int t = 0; t < 9; ++t)
+        geo[(buf * 9 + t) * kTileM + r] = tap_geometry_patch(prm, ov[2 * t], ov[2 * t + 1], mv[t], ho, wo, valid, t, py0, px0);
       __syncwarp();
       if (lane == 0) dcn_mbar_arrive(&bars.geo_full[buf]);
+    }
+    for (int it = my_tiles; it < my_tiles + 2; ++it) {            // the last two tiles
+      if (it < 2) continue;
+      dcn_mbar_wait_relaxed(&bars.geo_empty[it & 1], (unsigned)(((it >> 1) & 1) ^ 1));
+      drain(it - 2);
     }
   } else if (warp == NP + 8) {
     // ===================================== GEMM 1 issuer + weight loader ===========================
@@ -485,16 +489,21 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
 #pragma unroll
       for (int c = 0; c < 4; ++c) cur[h][c] = 0xffffffffu;
     int sb = 0; unsigned sph = 0;
-    int it = 0, cbk = 0, t = 0;
+    int it = 0, cbk = 0, t = 0, py0 = 0, px0 = 0;
     for (int n = 0; n < total; ++n) {
-      if (cbk == 0 && t == 0) dcn_mbar_wait(&bars.geo_full[it & 1], (unsigned)((it >> 1) & 1));
+      if (cbk == 0 && t == 0) {
+        dcn_mbar_wait(&bars.geo_full[it & 1], (unsigned)((it >> 1) & 1));
+        int tile = (tile_first + it) % prm.tiles_per_image;
+        const int tile_y = tile / prm.tiles_x, tile_x = tile - tile_y * prm.tiles_x;
+        py0 = tile_y * kTileH - prm.pad - kPatchR; px0 = tile_x * kTileW - prm.pad - kPatchR;
+      }
       const int gi = ((it & 1) * 9 + t) * kTileM;
       unsigned short wv[2][4];
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
         const uint32_t p = (uint32_t)(bt + 64 * h);
-        const int q0 = sqt[gi + p];
         const uint4 g4 = geo[gi + p];
+        const int q0 = (g4.y >> 31) ? ((int)(short)(g4.x & 0xffffu) - py0) * kPatchW + (((int)g4.x >> 16) - px0) : -1;
         const float lh = __uint_as_float(g4.y & 0x7fffffffu), lw = __uint_as_float(g4.z), m = __uint_as_float(g4.w);
         const float hh = 1.f - lh, hw = 1.f - lw;
         wv[h][0] = __bfloat16_as_ushort(__float2bfloat16_rn(m * (hh * hw)));
