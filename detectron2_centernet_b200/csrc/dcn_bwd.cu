@@ -771,3 +771,9 @@ extern "C" int dcnv2_backward(const float* input, const float* weight, const flo
   }
   return CTDET_OK;
 }
+
+#ifdef CTDET_DGRAD_TIMING
+extern "C" int ctdet_debug_dgrad_times(unsigned long long* out /* [16][64] host */) {
+  return cudaMemcpyFromSymbol(out, ctdet::g_dg2_ts, sizeof(unsigned long long) * 16 * 64) == cudaSuccess ? 0 : 1;
+}
+#endif

@@ -90,6 +90,13 @@ __device__ __noinline__ void dgrad_scatter8(float* q, uint4 g, float c) {
   }
 }
 
+#ifdef CTDET_DGRAD_TIMING
+__device__ unsigned long long g_dg2_ts[16][64];
+#define DG2_TS(role, n) do { if (blockIdx.x == 0 && (n) < 64) g_dg2_ts[role][n] = clock64(); } while (0)
+#else
+#define DG2_TS(role, n) do {} while (0)
+#endif
+
 // Persistent, warp-specialised; one CTA per SM over 8 x 16 pixel tiles; K block n = (tile, channel block, tap):
 //   warps [0, NP)          consumers: grad_mask / grad_offset from G and the four gathered corners of x (as
 //                          dcn_dgrad_kernel); grad_input REDs only for taps the patch does not cover
@@ -200,6 +207,8 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
       const uint4* geo_n = geo + ((l_it & 1) * 9 + l_t) * kTileM + row0;
       const uint4* geo_c = geo + ((c_it & 1) * 9 + c_t) * kTileM + row0;
       dcn_mbar_wait(&bars.g_full[gs], gph);
+      if (tid == 0) DG2_TS(13, n);
+      {
       const uint8_t* g_lane = gring + (size_t)gs * g_bytes + g_off;
       // both rows of the thread in lock step (16 independent FMA chains, the shuffles of the two reductions
       // overlap): the loop is latency-bound with 4 consumer warps per scheduler
@@ -257,7 +266,9 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
           a[i * NP * 4] = v;
         }
       }
+      }
       __syncwarp();
+      if (tid == 0) DG2_TS(14, n);
       if (lane == 0) {
         dcn_mbar_arrive(&bars.g_empty[gs]);
         if (l_it != c_it) dcn_mbar_arrive(&bars.geo_empty[c_it & 1]);
@@ -312,6 +323,7 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
       if (n >= 9 && (n % 9) == 5) flush(n / 9 - 1);                   // (GEMM 2 of that group has normally retired by now)
       const int ab = n & 1;
       dcn_mbar_wait(&bars.acc_full[ab], (unsigned)((n >> 1) & 1));
+      if (quarter == 0 && lane == 0) DG2_TS(1, n);
       tc_fence_after();
       uint32_t pk[32];
 #pragma unroll
@@ -327,7 +339,9 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
       tc_fence_before();
       __syncwarp();
       if (lane == 0) dcn_mbar_arrive(&bars.acc_empty[ab]);            // TMEM buffer may be overwritten
+      if (quarter == 0 && lane == 0) DG2_TS(15, n);
       dcn_mbar_wait(&bars.g_empty[gs], gph ^ 1u);
+      if (quarter == 0 && lane == 0) DG2_TS(2, n);
       uint8_t* dst = gring + (size_t)gs * g_bytes + r * 128;
 #pragma unroll
       for (int c = 0; c < 8; ++c)
@@ -335,6 +349,7 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the tile is also a tensor-core operand now
       __syncwarp();
       if (lane == 0) dcn_mbar_arrive(&bars.g_full[gs]);
+      if (quarter == 0 && lane == 0) DG2_TS(3, n);
       if (++gs == NG) { gs = 0; gph ^= 1u; }
     }
     if (total > 0) flush(total / 9 - 1);
@@ -363,26 +378,20 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
       }
     };
     for (int it = 0; it < my_tiles; ++it) {
+      // geometry first: its buffer frees up a whole tile before the grad_output buffer does (one buffer at Cout >= 64...)
       int tile = tile_first + it;
-      const int gb = it % GB;
-      dcn_mbar_wait_relaxed(&bars.gout_empty[gb], (unsigned)(((it / GB) & 1) ^ 1));
-      dcn_load_gout_tile(prm, bw.gh, tile, r, gout + (size_t)gb * gout_bytes);
-      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-      __syncwarp();
-      if (lane == 0) dcn_mbar_arrive(&bars.gout_full[gb]);
-
-      const int buf = it & 1;
-      dcn_mbar_wait_relaxed(&bars.geo_empty[buf], (unsigned)(((it >> 1) & 1) ^ 1));   // tile it - 2 is done
-      if (it >= 2) drain(it - 2);
       const int b = tile / prm.tiles_per_image;
-      tile -= b * prm.tiles_per_image;
-      const int tile_y = tile / prm.tiles_x, tile_x = tile - tile_y * prm.tiles_x;
+      const int tl = tile - b * prm.tiles_per_image;
+      const int tile_y = tl / prm.tiles_x, tile_x = tl - tile_y * prm.tiles_x;
       const int ho = tile_y * kTileH + (r >> 4), wo = tile_x * kTileW + (r & 15);
       const int py0 = tile_y * kTileH - prm.pad - kPatchR, px0 = tile_x * kTileW - prm.pad - kPatchR;
       const bool valid = ho < prm.Ho && wo < prm.Wo;
       const int p = valid ? ho * prm.Wo + wo : 0;
       const float* offb = prm.offset + (size_t)b * 18 * P + p;
       const float* mskb = prm.mask + (size_t)b * 9 * P + p;
+      const int buf = it & 1;
+      dcn_mbar_wait_relaxed(&bars.geo_empty[buf], (unsigned)(((it >> 1) & 1) ^ 1));   // tile it - 2 is done
+      if (it >= 2) drain(it - 2);
       float ov[18], mv[9];
 #pragma unroll
       for (int k = 0; k < 18; ++k) ov[k] = ldg_stream1(offb + (size_t)k * P);
@@ -393,6 +402,13 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
         geo[(buf * 9 + t) * kTileM + r] = tap_geometry_patch(prm, ov[2 * t], ov[2 * t + 1], mv[t], ho, wo, valid, t, py0, px0);
       __syncwarp();
       if (lane == 0) dcn_mbar_arrive(&bars.geo_full[buf]);
+
+      const int gb = it % GB;
+      dcn_mbar_wait_relaxed(&bars.gout_empty[gb], (unsigned)(((it / GB) & 1) ^ 1));
+      dcn_load_gout_tile(prm, bw.gh, tile, r, gout + (size_t)gb * gout_bytes);
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) dcn_mbar_arrive(&bars.gout_full[gb]);
     }
     for (int it = my_tiles; it < my_tiles + 2; ++it) {            // the last two tiles
       if (it < 2) continue;
@@ -424,6 +440,7 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
         const int ab = n & 1;
         dcn_mbar_wait_relaxed(&bars.acc_empty[ab], (unsigned)(((n >> 1) & 1) ^ 1), 0u);
         dcn_mbar_wait_relaxed(&bars.wt_full[ws], wph, 0u);
+        DG2_TS(0, n);
         tc_fence_after();
         const uint64_t b0 = make_sw128_desc(smem_u32(wtr + (size_t)ws * wt_bytes));
         const uint32_t d_tmem = tmem + (uint32_t)(ab * kBK);
@@ -457,11 +474,13 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
         const int pb = grp2 & 1;
         if (t2 == 0) dcn_mbar_wait_relaxed(&bars.patch_empty[pb], (unsigned)(((grp2 >> 1) & 1) ^ 1), 0u);
         dcn_mbar_wait_relaxed(&bars.g_full[gs2], gph2, 0u);
+        DG2_TS(4, n);
         const uint64_t b0 = make_sw128_desc_mn(smem_u32(gring + (size_t)gs2 * g_bytes), 1024u);
         const uint32_t d0 = tmem + (uint32_t)(128 + pb * (kPatchMB * kBK));
 #pragma unroll
         for (int mb = 0; mb < kPatchMB; ++mb) {
           dcn_mbar_wait_relaxed(&bars.s_full[sb], sph, 0u);
+          DG2_TS(5 + mb, n);
           tc_fence_after();
           const uint64_t a0 = make_sw128_desc(smem_u32(sring + (size_t)sb * kSChunkBytes));
 #pragma unroll
@@ -471,6 +490,7 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
           umma_commit(&bars.s_empty[sb]);
           sb ^= 1; if (sb == 0) sph ^= 1u;
         }
+        DG2_TS(8, n);
         umma_commit(&bars.g_empty[gs2]);
         if (++gs2 == NG) { gs2 = 0; gph2 ^= 1u; }
         if (++t2 == 9) { t2 = 0; umma_commit(&bars.patch_full[pb]); ++grp2; }
@@ -520,6 +540,7 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
 #pragma unroll
       for (int mb = 0; mb < kPatchMB; ++mb) {
         dcn_mbar_wait(&bars.s_empty[sb], sph ^ 1u);
+        if (bt == 0) DG2_TS(9 + mb, n);
         uint8_t* chunk = sring + (size_t)sb * kSChunkBytes;
 #pragma unroll
         for (int h = 0; h < 2; ++h)
@@ -537,6 +558,7 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncwarp();
         if (lane == 0) dcn_mbar_arrive(&bars.s_full[sb]);
+        if (bt == 0 && mb == 2) DG2_TS(12, n);
         sb ^= 1; if (sb == 0) sph ^= 1u;
       }
       if (++t == 9) {
