@@ -1279,9 +1279,12 @@ static DecodePlan make_plan(int B, int C, int H, int W, int K) {
   p.seed_groups = (H - 2 - kSeedRows) >= 0 ? (H - 2 - kSeedRows) / kSeedPeriod + 1 : 0;   // r0 + kSeedRows <= H - 1
   p.stream = stream_on && (W % 4) == 0 && W >= 8 && p.seed_groups > 0 && strips <= 64;   // (+ the tile count, below)
   {
-    static int sw_kb = 0;                                       // tuning knob: CTDET_DECODE_TILE_KB (read once)
-    if (sw_kb == 0) { const char* e = getenv("CTDET_DECODE_TILE_KB"); sw_kb = e ? atoi(e) : 16; if (sw_kb < 1) sw_kb = 16; }
-    int sr = (sw_kb * 1024) / (W * 4);                          // ~16 KB of full-width rows per tile (measured best of 8 / 16 / 32)
+    static int sw_kb_env = -1;                                  // tuning knob: CTDET_DECODE_TILE_KB (read once; 0 = automatic)
+    if (sw_kb_env < 0) { const char* e = getenv("CTDET_DECODE_TILE_KB"); sw_kb_env = e ? atoi(e) : 0; if (sw_kb_env < 0) sw_kb_env = 0; }
+    // ~16 KB of full-width rows per tile (measured best of 8 / 16 / 32 / 64 at W = 128: 66 / 58 / 59 / 59 us); rows of
+    // 1 KB and more get 32 KB (W = 256, B = 8: 82 / 70 / 63 / 63 us) -- a tile should hold a few dozen rows per halo pair
+    const int sw_kb = sw_kb_env ? sw_kb_env : (W >= 256 ? 32 : 16);
+    int sr = (sw_kb * 1024) / (W * 4);
     if (sr * strips > 64) sr = 64 / strips;                     // <= 16 (row, strip) pairs per warp
     if (sr < 1) sr = 1;
     if (sr > H) sr = H;
