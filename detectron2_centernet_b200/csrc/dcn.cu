@@ -37,7 +37,10 @@ namespace ctdet {
 __global__ void __launch_bounds__(256)
 dcn_pack_input_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ xh, int C, int P, int vec,
                       float* __restrict__ chan_sum, int chunks, int border_w) {
-  __shared__ __nv_bfloat16 t[64][64 + 8];                 // [pixel][channel], padded rows (144 B)
+  // [pixel][32 words of 2 channels], word w of pixel row r stored at w ^ s(r), s(r) = ((q & 7) << 2) | ((q >> 3) << 1)
+  // with q = r >> 2: the transposing stores of a warp (16 pixel groups q x 2 channel pairs) hit 32 distinct banks, and a
+  // 16-byte read of 8 channels stays one aligned vector (its two halves swapped when q >= 8)
+  __shared__ uint32_t t[64][32];
   const int b = blockIdx.z, c0 = blockIdx.y * 64;
   const float* src = x + (size_t)b * C * P;
   // border_w = W > 0: the image is written inside a one-pixel border (rows of W + 2 pixels, pixel (y, x) at
@@ -48,33 +51,47 @@ dcn_pack_input_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ x
   // with channel sums a CTA walks `chunks` 64-pixel blocks and keeps the sums in registers: one
   // atomic per channel per CTA instead of one per 64 pixels (8192 same-address atomics per channel
   // on a 64-channel 128^2 x 32 tensor cost 4x the pack itself)
-  float csum[4] = {0.f, 0.f, 0.f, 0.f};
+  float csum[4] = {0.f, 0.f, 0.f, 0.f};                   // [k][channel of the pair]
   for (int it = 0; it < chunks; ++it) {
     const int p0 = (blockIdx.x * chunks + it) * 64;
     if (p0 >= P) break;
     if (it) __syncthreads();                              // the previous block's stores are done with t
+    float4 v[2][2];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const int idx = tid + k * 256;                      // 64 channels x 16 float4
-      const int c = idx >> 4, q = idx & 15;
+    for (int k = 0; k < 2; ++k) {
+      const int idx = tid + k * 256;                      // 32 channel pairs x 16 float4
+      const int cp = idx >> 4, q = idx & 15;
       const int p = p0 + q * 4;
-      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (c0 + c < C && p < P) {
-        const float* sp = src + (size_t)(c0 + c) * P + p;
-        if (vec) {
-          v = ldg_stream4(sp);
-        } else {                                          // P % 4 != 0 or unaligned base: scalar loads
-          v.x = __ldg(sp);
-          if (p + 1 < P) v.y = __ldg(sp + 1);
-          if (p + 2 < P) v.z = __ldg(sp + 2);
-          if (p + 3 < P) v.w = __ldg(sp + 3);
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int c = c0 + 2 * cp + h;
+        float4 u = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (c < C && p < P) {
+          const float* sp = src + (size_t)c * P + p;
+          if (vec) {
+            u = ldg_stream4(sp);
+          } else {                                        // P % 4 != 0 or unaligned base: scalar loads
+            u.x = __ldg(sp);
+            if (p + 1 < P) u.y = __ldg(sp + 1);
+            if (p + 2 < P) u.z = __ldg(sp + 2);
+            if (p + 3 < P) u.w = __ldg(sp + 3);
+          }
         }
+        v[k][h] = u;
       }
-      csum[k] += (v.x + v.y) + (v.z + v.w);
-      t[q * 4 + 0][c] = __float2bfloat16_rn(v.x);
-      t[q * 4 + 1][c] = __float2bfloat16_rn(v.y);
-      t[q * 4 + 2][c] = __float2bfloat16_rn(v.z);
-      t[q * 4 + 3][c] = __float2bfloat16_rn(v.w);
+    }
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const int idx = tid + k * 256;
+      const int cp = idx >> 4, q = idx & 15;
+      const int col = cp ^ (((q & 7) << 2) | ((q >> 3) << 1));
+      csum[2 * k] += (v[k][0].x + v[k][0].y) + (v[k][0].z + v[k][0].w);
+      csum[2 * k + 1] += (v[k][1].x + v[k][1].y) + (v[k][1].z + v[k][1].w);
+      __nv_bfloat162 w;
+      w = __floats2bfloat162_rn(v[k][0].x, v[k][1].x); t[q * 4 + 0][col] = *reinterpret_cast<const uint32_t*>(&w);
+      w = __floats2bfloat162_rn(v[k][0].y, v[k][1].y); t[q * 4 + 1][col] = *reinterpret_cast<const uint32_t*>(&w);
+      w = __floats2bfloat162_rn(v[k][0].z, v[k][1].z); t[q * 4 + 2][col] = *reinterpret_cast<const uint32_t*>(&w);
+      w = __floats2bfloat162_rn(v[k][0].w, v[k][1].w); t[q * 4 + 3][col] = *reinterpret_cast<const uint32_t*>(&w);
     }
     __syncthreads();
 #pragma unroll
@@ -84,17 +101,20 @@ dcn_pack_input_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ x
       if (p0 + pp < P && c0 + ch * 8 < C) {
         int q = p0 + pp;
         if (border_w) { const int y = q / border_w; q += (y + 1) * 2 + border_w + 1; }   // (y+1)*(W+2) + x+1
-        *reinterpret_cast<uint4*>(dst + (size_t)q * C + c0 + ch * 8) = *reinterpret_cast<const uint4*>(&t[pp][ch * 8]);
+        const int qq = pp >> 2;
+        uint4 u = *reinterpret_cast<const uint4*>(&t[pp][(ch ^ (qq & 7)) << 2]);
+        if (qq >> 3) u = make_uint4(u.z, u.w, u.x, u.y);
+        *reinterpret_cast<uint4*>(dst + (size_t)q * C + c0 + ch * 8) = u;
       }
     }
   }
   if (chan_sum) {                                         // per-channel sums (grad_bias of the backward):
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {                         // 16 consecutive lanes share one channel
+    for (int k = 0; k < 4; ++k) {                         // 16 consecutive lanes share one channel pair
       float sum = csum[k];
 #pragma unroll
       for (int o = 8; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-      const int c = (tid + k * 256) >> 4;
+      const int c = 2 * ((tid + (k >> 1) * 256) >> 4) + (k & 1);
       if ((tid & 15) == 0 && c0 + c < C) atomicAdd(chan_sum + c0 + c, sum);
     }
   }
