@@ -666,7 +666,7 @@ extern "C" int dcnv2_backward(const float* input, const float* weight, const flo
     const int blocks = (P + 63) / 64;
     int chunks = 1;
     if (grad_bias)
-      while (chunks < 16 && (long long)(blocks / (chunks * 2)) * ((Cout + 63) / 64) * B >= 4LL * kNumSMs) chunks *= 2;
+      while (chunks < 16 && (long long)(blocks / (chunks * 2)) * ((Cout + 63) / 64) * B >= 2LL * kNumSMs) chunks *= 2;
     dcn_pack_input_kernel<<<dim3((blocks + chunks - 1) / chunks, (Cout + 63) / 64, B), 256, 0, st>>>(grad_output, gh, Cout, P, vec,
                                                                                                     grad_bias, chunks, 0);
   }
