@@ -32,6 +32,7 @@ struct DcnBwdParams {
   float* goff;                 // grad_offset [B][18][Ho*Wo]
   float* gmask;                // grad_mask   [B][9][Ho*Wo]
   int n_groups, kb_per_group;  // wgrad: K blocks are split into groups that fit TMEM
+  int paired;                  // wgrad, Cout = 64: D[(2 K blocks x 64 ci), co] -- two K blocks per MMA, rows fully used
   int g_stages, w_stages, gout_bufs;   // dgrad ring depths
   int s_bufs;                          // dgrad (GEMM scatter): S chunk ring depth
 };
@@ -110,8 +111,10 @@ dcn_wgrad_kernel(const DcnParams prm, const DcnBwdParams bw) {
   const bool work = my_tiles > 0 && nkb > 0;
 
   if (warp < NP) {
-    if (nkb > 0)
-      dcn_producer_loop<false, NP>(prm, smem, stage_bytes, NS, geo_w, geo_g, bars, warp, lane, tile_first, my_tiles, kb0, kb1);
+    if (nkb > 0) {
+      if (bw.paired) dcn_producer_loop<false, NP, true>(prm, smem, stage_bytes, NS, geo_w, geo_g, bars, warp, lane, tile_first, my_tiles, kb0, kb1);
+      else dcn_producer_loop<false, NP>(prm, smem, stage_bytes, NS, geo_w, geo_g, bars, warp, lane, tile_first, my_tiles, kb0, kb1);
+    }
   } else if (warp < NP + 4) {
     // ============ final flush: TMEM -> fp32 atomics into grad_weight[co][ci][t] ====================
     if (work) {
@@ -119,6 +122,24 @@ dcn_wgrad_kernel(const DcnParams prm, const DcnBwdParams bw) {
       const int r = (quarter << 5) + lane;
       dcn_mbar_wait_relaxed(&bars.acc_full[0], 0u);
       tc_fence_after();
+      if (bw.paired) {
+        // rows = (K block of the pair, ci), columns = (pair, co)
+        const int h = r >> 6, ci = r & 63;
+        for (int j = 0; 2 * j < nkb; ++j) {
+          const int kbl = 2 * j + h;
+          const bool ok = kbl < nkb;                 // the odd last K block has no partner: rows 64..127 hold garbage
+          const int kb = kb0 + (ok ? kbl : 0), cb = kb / 9, t = kb - 9 * cb;
+          float* dst = bw.gw + ((size_t)cb * kBK + ci) * 9 + t;
+          for (int c0 = 0; c0 < 64; c0 += 16) {
+            uint32_t v[16];
+            tmem_ld16(tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(j * 64 + c0), v);
+            if (ok) {
+#pragma unroll
+              for (int k = 0; k < 16; ++k) atomicAdd(dst + (size_t)(c0 + k) * Cin * 9, __uint_as_float(v[k]));
+            }
+          }
+        }
+      } else
       for (int mt = 0; mt < MT; ++mt) {
         const int co = mt * 128 + r;
         const bool ok = co < Cout;                 // Cout = 64: rows 64..127 duplicate rows 0..63
@@ -155,6 +176,34 @@ dcn_wgrad_kernel(const DcnParams prm, const DcnBwdParams bw) {
       const uint32_t idesc = make_idesc_bf16(kTileM, kBK) | (1u << 15) | (1u << 16);   // A and B MN-major
       const uint32_t lbo = Cout >= 128 ? (uint32_t)kTileM * 128u : 0u;   // second 64-channel atom of the M tile
       int s = 0; unsigned ph = 0;
+      if (bw.paired) {
+        // D[(h, ci), co] += col_{2j+h}^T[ci, p] * gout[p, co]: A = two adjacent stages (M atoms one stage apart),
+        // B = the grad_output tile, both MN-major; a lone last K block is paired with the (empty) pad stage
+        for (int it = 0; it < my_tiles; ++it) {
+          const int buf = it & 1;
+          dcn_mbar_wait_relaxed(&bars.geo_full[buf], (unsigned)((it >> 1) & 1), 0u);
+          tc_fence_after();
+          const uint32_t g_addr = smem_u32(gout + (size_t)buf * gout_bytes);
+          for (int j = 0; 2 * j < nkb; ++j) {
+            dcn_mbar_wait_relaxed(&bars.full[s], ph, 0u);
+            dcn_mbar_wait_relaxed(&bars.full[s + 1], ph, 0u);
+            tc_fence_after();
+            const uint32_t c_addr = smem_u32(smem + (size_t)s * stage_bytes);
+            const uint32_t d_tmem = tmem + (uint32_t)(j * 64);
+#pragma unroll
+            for (int k8 = 0; k8 < kTileM / 16; ++k8) {
+              const uint64_t adesc = make_sw128_desc_mn(c_addr + k8 * 2048u, stage_bytes);
+              const uint64_t bdesc = make_sw128_desc_mn(g_addr + k8 * 2048u, 1024u);
+              umma_bf16(d_tmem, adesc, bdesc, idesc, (uint32_t)((it | k8) != 0));
+            }
+            umma_commit(&bars.empty[s]);
+            umma_commit(&bars.empty[s + 1]);
+            s += 2;
+            if (s == NS) { s = 0; ph ^= 1u; }
+          }
+          umma_commit(&bars.geo_empty[buf]);
+        }
+      } else
       for (int it = 0; it < my_tiles; ++it) {
         const int buf = it & 1;
         dcn_mbar_wait_relaxed(&bars.geo_full[buf], (unsigned)((it >> 1) & 1), 0u);
@@ -695,17 +744,19 @@ extern "C" int dcnv2_backward(const float* input, const float* weight, const flo
     e = cudaMemsetAsync(grad_weight, 0, (size_t)Cout * Cin * 9 * 4, st);
     if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
     const int MT = Cout > 128 ? 2 : 1;
-    const int max_kb = 512 / (kBK * MT);                       // accumulators that fit TMEM
+    bw.paired = (Cout == 64 && dcn_tunables().wgrad_paired) ? 1 : 0;
+    const int max_kb = bw.paired ? 16 : 512 / (kBK * MT);      // accumulators that fit TMEM
     bw.n_groups = (KB + max_kb - 1) / max_kb;
     bw.kb_per_group = (KB + bw.n_groups - 1) / bw.n_groups;
     uint32_t cols = 32;
-    while (cols < (uint32_t)(bw.kb_per_group * kBK * MT)) cols <<= 1;
+    while (cols < (uint32_t)(bw.paired ? (bw.kb_per_group + 1) / 2 * 64 : bw.kb_per_group * kBK * MT)) cols <<= 1;
     prm.tmem_cols = cols;
     const size_t gout_bytes = (size_t)(Cout / 64) * kTileM * 128;
     const size_t fixed = 1024 + kGeoBytes + 2 * gout_bytes;
     int stages = (int)((230 * 1024 - fixed) / (kTileM * kBK * 2));
     if (stages > 4) stages = 4;
     if (stages < 2) return CTDET_EUNSUPPORTED;
+    if (bw.paired) stages &= ~1;                               // stage pairs
     prm.stages = stages;
     const size_t smem = fixed + (size_t)stages * kTileM * kBK * 2;
     int chunks = kNumSMs / bw.n_groups;

@@ -206,7 +206,7 @@ struct DcnBarriers {
 // swizzled layout, one pipeline stage per K block.  8 lanes x 16 B gather one pixel's 64 channels
 // (one warp-wide load = 4 full 128-byte lines); the gathers of K block n+1 are issued while block n
 // is blended (register double-buffering across K blocks AND tiles).
-template <bool kFp32Blend, int NP>
+template <bool kFp32Blend, int NP, bool kPadOdd = false>
 __device__ __forceinline__ void dcn_producer_loop(const DcnParams& prm, uint8_t* smem, uint32_t stage_bytes, int NS,
                                                   const uint4* geo_w, const uint32_t* geo_g, DcnBarriers& bars,
                                                   int warp, int lane, int tile_first, int my_tiles, int kb0, int kb1) {
@@ -290,6 +290,14 @@ __device__ __forceinline__ void dcn_producer_loop(const DcnParams& prm, uint8_t*
       for (int i = 0; i < ITERS; ++i) gather(i, l_xc, gg[i * NP * 4]);   // refill: K block n+1, same row groups
     }
     if (++s == NS) { s = 0; ph ^= 1u; }
+    if (kPadOdd && l_it != c_it && ((kb1 - kb0) & 1)) {
+      // wgrad pairs two K blocks per MMA (two adjacent stages): a tile with an odd number of K blocks hands over
+      // one empty stage so that every tile starts on an even stage
+      dcn_mbar_wait(&bars.empty[s], ph ^ 1u);
+      __syncwarp();
+      if (lane == 0) dcn_mbar_arrive(&bars.full[s]);
+      if (++s == NS) { s = 0; ph ^= 1u; }
+    }
   }
 }
 
@@ -346,6 +354,7 @@ struct DcnTunables {
   int ld_sleep;          // CTDET_DCN_LD_SLEEP        ns back-off of the weight loader's polls (20)
   int producer_warps;    // CTDET_DCN_PRODUCER_WARPS  gather warps of the forward kernel, 16 or 8 (16)
   int dgrad_warps;       // CTDET_DCN_DGRAD_WARPS     consumer warps of the dgrad kernel, 16 or 8 (16)
+  int wgrad_paired;      // CTDET_DCN_WGRAD_PAIRED    wgrad at Cout = 64: two K blocks per MMA (1)
   int dgrad_gemm;        // CTDET_DCN_DGRAD_GEMM      1: grad_input scatter as a tensor-core GEMM where supported (1)
   int dgrad_gb;          // CTDET_DCN_DGRAD_GB        grad_output tile buffers of that kernel at Cout = 64: 1 or 2 (1)
 };
@@ -358,6 +367,7 @@ static inline const DcnTunables& dcn_tunables() {
     r.ld_sleep = env("CTDET_DCN_LD_SLEEP", 20);
     r.producer_warps = env("CTDET_DCN_PRODUCER_WARPS", 16) == 8 ? 8 : 16;
     r.dgrad_warps = env("CTDET_DCN_DGRAD_WARPS", 16) == 8 ? 8 : 16;
+    r.wgrad_paired = env("CTDET_DCN_WGRAD_PAIRED", 1) != 0;
     r.dgrad_gemm = env("CTDET_DCN_DGRAD_GEMM", 1) != 0;
     r.dgrad_gb = env("CTDET_DCN_DGRAD_GB", 1) == 2 ? 2 : 1;
     return r;
