@@ -779,7 +779,8 @@ extern "C" int dcnv2_backward(const float* input, const float* weight, const flo
     const unsigned grid = (unsigned)(tiles < kNumSMs ? tiles : kNumSMs);
     const int npd = dcn_tunables().dgrad_warps;
     bool launched = false;
-    if (dcn_tunables().dgrad_gemm && npd == 16 && stride_h == 1 && dilation_h == 1 && Cout <= 128 && H < 32000 && W < 32000) {
+    if (dcn_tunables().dgrad_gemm && npd == 16 && stride_h == 1 && dilation_h == 1 && Cout <= 128 &&
+        (size_t)(H + 2) * (W + 2) <= ((size_t)1 << 23)) {
       // second form: the grad_input scatter as a tensor-core GEMM (dcn_dgrad2.cuh)
       bw.gout_bufs = Cout <= 64 ? dcn_tunables().dgrad_gb : 1;
       bw.s_bufs = 2;                                     // (the builders' un-write bookkeeping assumes two buffers)
@@ -794,7 +795,7 @@ extern "C" int dcnv2_backward(const float* input, const float* weight, const flo
         auto kern = dcn_dgrad2_kernel<16>;
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
-        kern<<<grid, (16 + 12) * 32, smem, st>>>(prm, bw);
+        kern<<<grid, (16 + 10) * 32, smem, st>>>(prm, bw);
         rc = check_launch();
         if (rc) return rc;
         launched = true;

@@ -33,35 +33,35 @@ struct Dgrad2Barriers {
   uint64_t patch_full[2], patch_empty[2];   // TMEM patch accumulators                (MMA -> transfer)
 };
 
-// Sampling geometry of one (pixel, tap): {h_low | w_low << 16 (two int16), lh | flag, lw, mask}.  The element offset
-// of the top-left corner in the bordered NHWC image and the patch cell are derived from (h_low, w_low) by their
-// users (16 B per entry, no second table: the kernel is short of shared memory).  A tap the reference does not
-// sample (deform_conv_cuda_kernel.cu:852) has h_low = w_low = -1 (the zero corner pixel of the border) and mask 0.
-// Bit 31 of .y (lh >= 0) is set when all four corners lie inside the tile's patch: the GEMM scatters this tap.
+// Sampling geometry of one (pixel, tap): {pixel << 9 | cell, lh | flag, lw, mask}.  `pixel` = index of the top-left corner
+// in the bordered NHWC image ((h_low + 1) * (W + 2) + w_low + 1 < 2^23, checked by the host), `cell` = its cell in the
+// tile's 16 x 24 patch.  A tap the reference does not sample (deform_conv_cuda_kernel.cu:852) has pixel 0 (the zero
+// corner of the border) and mask 0.  Bit 31 of .y (lh >= 0) is set when all four corners lie inside the patch: the GEMM
+// scatters this tap; otherwise `cell` is 0 and the consumers RED it.
 __device__ __forceinline__ uint4 tap_geometry_patch(const DcnParams& prm, float off_h, float off_w, float m,
                                                     int ho, int wo, bool valid, int t, int py0, int px0) {
-  uint4 o = make_uint4(0xffffffffu, 0u, 0u, 0u);
+  uint4 o = make_uint4(0u, 0u, 0u, 0u);
   if (valid) {
     const int i = t / 3, j = t - 3 * i;
     const float h_im = (float)(ho - prm.pad + i) + off_h;
     const float w_im = (float)(wo - prm.pad + j) + off_w;
     if (h_im > -1.f && w_im > -1.f && h_im < (float)prm.H && w_im < (float)prm.W) {
       const int h_low = (int)floorf(h_im), w_low = (int)floorf(w_im);
-      o.x = ((uint32_t)h_low & 0xffffu) | ((uint32_t)w_low << 16);
+      o.x = (uint32_t)((h_low + 1) * prm.xw + w_low + 1) << 9;
       o.y = __float_as_uint(h_im - (float)h_low);
       o.z = __float_as_uint(w_im - (float)w_low);
       o.w = __float_as_uint(m);
       const int qy = h_low - py0, qx = w_low - px0;
-      if (qy >= 0 && qy <= kPatchH - 2 && qx >= 0 && qx <= kPatchW - 2) o.y |= 0x80000000u;
+      if (qy >= 0 && qy <= kPatchH - 2 && qx >= 0 && qx <= kPatchW - 2) {
+        o.x |= (uint32_t)(qy * kPatchW + qx);
+        o.y |= 0x80000000u;
+      }
     }
   }
   return o;
 }
-// element offset of the top-left corner in the bordered image (rows of xw pixels, one border pixel either side)
-__device__ __forceinline__ uint32_t geo_corner_offset(uint32_t hw, int xw, int Cin) {
-  const int hl = (int)(short)(hw & 0xffffu), wl = (int)hw >> 16;
-  return (uint32_t)((hl + 1) * xw + wl + 1) * (uint32_t)Cin;
-}
+// element offset of the top-left corner in the bordered image
+__device__ __forceinline__ uint32_t geo_corner_offset(uint32_t x, int Cin) { return (x >> 9) * (uint32_t)Cin; }
 
 // byte offset of S[qrow][p] inside a chunk: K-major, 128-byte swizzle, K halves of 64 pixels 16 KB apart
 __device__ __forceinline__ uint32_t s_chunk_offset(uint32_t qrow, uint32_t p) {
@@ -99,15 +99,16 @@ __device__ unsigned long long g_dg2_ts[16][64];
 
 // Persistent, warp-specialised; one CTA per SM over 8 x 16 pixel tiles; K block n = (tile, channel block, tap):
 //   warps [0, NP)          consumers: grad_mask / grad_offset from G and the four gathered corners of x (as
-//                          dcn_dgrad_kernel); grad_input REDs only for taps the patch does not cover
+//                          dcn_dgrad_kernel); one non-zero of S per lane and K block (written / un-written with plain
+//                          stores); grad_input REDs only for taps the patch does not cover
 //   warps [NP, NP+4)       transfer: TMEM G accumulator -> bf16 G tile in shared memory; every 9 K blocks the
 //                          finished patch TMEM -> fp32 REDs into the bordered NHWC grad_input workspace
 //   warps [NP+4, NP+8)     grad_output tile + sampling geometry + patch cell of the tiles ahead (thread = pixel)
 //   warp  NP+8             one lane issues GEMM 1 (G = gout * Wt) and streams the transposed weight tiles (bulk copies)
 //   warp  NP+9             one lane issues GEMM 2 (patch += S * G), gated by the G tile and the S chunks
-//   warps [NP+10, NP+12)   builders: write / un-write the four non-zeros per pixel of the S chunks
+// (a separate pair of builder warps for S was the bottleneck of the first form: ~1100 cycles per chunk)
 template <int NP>
-__global__ void __launch_bounds__((NP + 12) * 32, 1)
+__global__ void __launch_bounds__((NP + 10) * 32, 1)
 dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
   static_assert(NP % 4 == 0 && 32 % NP == 0, "consumer warps must tile the 32 row groups");
   extern __shared__ __align__(1024) uint8_t dcn_smem[];
@@ -125,7 +126,7 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
   uint8_t* wtr = gout + (size_t)GB * gout_bytes;                      // [NW][Cout/64][64][128 B]
   uint8_t* gring = wtr + (size_t)NW * wt_bytes;                       // [NG][128][128 B]
   uint8_t* sring = gring + (size_t)NG * g_bytes;                      // [NSB][2][128][128 B]
-  uint4* geo = reinterpret_cast<uint4*>(sring + (size_t)NSB * kSChunkBytes);   // [2][9][128] {h_low | w_low, lh | flag, lw, mask}
+  uint4* geo = reinterpret_cast<uint4*>(sring + (size_t)NSB * kSChunkBytes);   // [2][9][128] {pixel << 9 | cell, lh | flag, lw, mask}
   float* acc = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(geo) + kDgGeoBytes);  // [2][27][128] per-tile sums
   const int cpb = Cin / kBK, KB = 9 * cpb;
   const int tile_first = (int)(((long long)blockIdx.x * prm.num_tiles) / gridDim.x);
@@ -134,7 +135,7 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
 
   if (tid == 0) {
     for (int i = 0; i < 2; ++i) {
-      dcn_mbar_init(&bars.geo_full[i], 4);    dcn_mbar_init(&bars.geo_empty[i], NP + 2);
+      dcn_mbar_init(&bars.geo_full[i], 4);    dcn_mbar_init(&bars.geo_empty[i], NP);
       dcn_mbar_init(&bars.gout_full[i], 4);   dcn_mbar_init(&bars.gout_empty[i], 1);
       dcn_mbar_init(&bars.acc_full[i], 1);    dcn_mbar_init(&bars.acc_empty[i], 4);
       dcn_mbar_init(&bars.patch_full[i], 1);  dcn_mbar_init(&bars.patch_empty[i], 4);
@@ -143,15 +144,15 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
       dcn_mbar_init(&bars.wt_full[i], 1);     dcn_mbar_init(&bars.wt_empty[i], 1);
       dcn_mbar_init(&bars.g_full[i], 4);      dcn_mbar_init(&bars.g_empty[i], NP + 1);
     }
-    for (int i = 0; i < kDg2MaxS; ++i) { dcn_mbar_init(&bars.s_full[i], 2); dcn_mbar_init(&bars.s_empty[i], 1); }
+    for (int i = 0; i < kDg2MaxS; ++i) { dcn_mbar_init(&bars.s_full[i], NP); dcn_mbar_init(&bars.s_empty[i], 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == NP + 8) tmem_alloc(&s_tmem, 512);
-  if (warp >= NP + 10) {                       // the S ring starts (and is always left) all zero
-    const int bt = tid - (NP + 10) * 32;       // 0..63
+  if (warp >= NP + 4 && warp < NP + 8) {       // the S ring starts (and is always left) all zero
+    const int bt = tid - (NP + 4) * 32;        // 0..127
     uint4* z = reinterpret_cast<uint4*>(sring);
     const int n16 = NSB * kSChunkBytes / 16;
-    for (int i = bt; i < n16; i += 64) z[i] = make_uint4(0u, 0u, 0u, 0u);
+    for (int i = bt; i < n16; i += 128) z[i] = make_uint4(0u, 0u, 0u, 0u);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
   tc_fence_before();
@@ -186,8 +187,29 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
       l_x = prm.xh + (size_t)(tile_first / prm.tiles_per_image) * prm.ximg + chunk * 8;
       dcn_mbar_wait(&bars.geo_full[0], 0u);
 #pragma unroll
-      for (int i = 0; i < ITERS; ++i) gather(i, l_x, geo_corner_offset(geo[row0 + i * NP * 4].x, prm.xw, Cin));
+      for (int i = 0; i < ITERS; ++i) gather(i, l_x, geo_corner_offset(geo[row0 + i * NP * 4].x, Cin));
     }
+    // S (the scatter matrix of GEMM 2): lane (chunk & 3) of a row's 8 lanes owns corner (chunk & 3) of pixel row
+    // row0 (chunk < 4) or row0 + 64 (chunk >= 4) -- one non-zero of S per lane and K block, written with a plain store.
+    // An entry = (M block << 16) | byte offset inside the chunk, ~0 = none.  Chunk c = 3 n + mb lives in buffer c & 1,
+    // whose previous content was chunk c - 2 = (n, 0) for mb = 2, (n - 1, 2) for mb = 1, (n - 1, 1) for mb = 0: it is
+    // un-written from this lane's entry of this / the previous K block.
+    const uint32_t s_p = row0 + (uint32_t)(chunk >> 2) * 64u;                      // column of S = pixel of the tile
+    const uint32_t s_k = (uint32_t)chunk & 3u;                                     // corner
+    uint32_t s_cur = 0xffffffffu, s_prv = 0xffffffffu, s_c = 0u;
+    unsigned short s_w = 0;
+    auto s_chunk = [&](uint32_t mb) {
+      const uint32_t sbuf = s_c & 1u;
+      dcn_mbar_wait(&bars.s_empty[sbuf], ((s_c >> 1) & 1u) ^ 1u);
+      uint8_t* chunk_base = sring + (size_t)sbuf * kSChunkBytes;
+      const uint32_t old = mb == 2u ? s_cur : s_prv, old_mb = mb == 2u ? 0u : (mb == 1u ? 2u : 1u);
+      if ((old >> 16) == old_mb) *reinterpret_cast<unsigned short*>(chunk_base + (old & 0xffffu)) = 0;
+      if ((s_cur >> 16) == mb) *reinterpret_cast<unsigned short*>(chunk_base + (s_cur & 0xffffu)) = s_w;
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) dcn_mbar_arrive(&bars.s_full[sbuf]);
+      ++s_c;
+    };
     int gs = 0; unsigned gph = 0;
     for (int n = 0; n < total; ++n) {
       const int c_it = l_it, c_cb = l_cb, c_t = l_t;
@@ -206,6 +228,16 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
       const __nv_bfloat16* l_xc = l_x + l_cb * kBK;
       const uint4* geo_n = geo + ((l_it & 1) * 9 + l_t) * kTileM + row0;
       const uint4* geo_c = geo + ((c_it & 1) * 9 + c_t) * kTileM + row0;
+      {                                          // this lane's non-zero of S for this K block (geometry only: before G)
+        const uint4 g4 = geo_c[(chunk >> 2) * NP * 4];
+        const float lh = __uint_as_float(g4.y & 0x7fffffffu), lw = __uint_as_float(g4.z), m = __uint_as_float(g4.w);
+        const float wy = (s_k & 2u) ? lh : 1.f - lh, wx = (s_k & 1u) ? lw : 1.f - lw;
+        s_w = __bfloat16_as_ushort(__float2bfloat16_rn(m * (wy * wx)));
+        const uint32_t qc = (g4.x & 511u) + (s_k & 1u) + (s_k >> 1) * kPatchW;
+        s_prv = s_cur;
+        s_cur = (g4.y >> 31) ? (((qc >> 7) << 16) | s_chunk_offset(qc & 127u, s_p)) : 0xffffffffu;
+      }
+      s_chunk(0u);
       dcn_mbar_wait(&bars.g_full[gs], gph);
       if (tid == 0) DG2_TS(13, n);
       {
@@ -226,8 +258,9 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
       }
       if (have_next) {
 #pragma unroll
-        for (int i = 0; i < ITERS; ++i) gather(i, l_xc, geo_corner_offset(geo_n[i * NP * 4].x, prm.xw, Cin));   // refill: K block n+1
+        for (int i = 0; i < ITERS; ++i) gather(i, l_xc, geo_corner_offset(geo_n[i * NP * 4].x, Cin));   // refill: K block n+1
       }
+      s_chunk(1u);
       float red[ITERS], msk[ITERS];
 #pragma unroll
       for (int i = 0; i < ITERS; ++i) {
@@ -237,7 +270,7 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
         msk[i] = m;
         if ((q4[i].y >> 31) == 0u && m != 0.f) {  // tap outside the patch (rare): scatter it here (deform_conv_cuda_kernel.cu:944)
           float* gp = bw.gx + (size_t)((tile_first + c_it) / prm.tiles_per_image) * prm.ximg + c_cb * kBK + chunk * 8 +
-                      geo_corner_offset(q4[i].x, prm.xw, Cin);
+                      geo_corner_offset(q4[i].x, Cin);
           dgrad_scatter8(gp, gq[i], m * w1); dgrad_scatter8(gp + ex, gq[i], m * w2);
           dgrad_scatter8(gp + ey, gq[i], m * w3); dgrad_scatter8(gp + ey + ex, gq[i], m * w4);
         }
@@ -267,7 +300,7 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
         }
       }
       }
-      __syncwarp();
+      s_chunk(2u);
       if (tid == 0) DG2_TS(14, n);
       if (lane == 0) {
         dcn_mbar_arrive(&bars.g_empty[gs]);
@@ -462,7 +495,7 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
       }
     }
     __syncwarp();
-  } else if (warp == NP + 9) {
+  } else {
     // ===================================== GEMM 2 issuer ===========================================
     // One lane: patch[mb] += S_chunk[128 q, 128 px] * G[128 px, 64 ci] for the three M blocks of every K block
     if (lane == 0) {
@@ -497,80 +530,6 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
       }
     }
     __syncwarp();
-  } else {
-    // ===================================== S builders ==============================================
-    // thread = 2 pixels (columns p of S).  An entry e = (M block << 16) | byte offset inside the chunk, ~0 = none.
-    // Chunk c = 3 n + mb lives in buffer c & 1, whose previous content was chunk c - 2 = (n, 0) for mb = 2,
-    // (n - 1, 2) for mb = 1, (n - 1, 1) for mb = 0: un-written from the entries of this / the previous K block.
-    const int bt = tid - (NP + 10) * 32;           // 0..63
-    uint32_t cur[2][4], prv[2][4];
-#pragma unroll
-    for (int h = 0; h < 2; ++h)
-#pragma unroll
-      for (int c = 0; c < 4; ++c) cur[h][c] = 0xffffffffu;
-    int sb = 0; unsigned sph = 0;
-    int it = 0, cbk = 0, t = 0, py0 = 0, px0 = 0;
-    for (int n = 0; n < total; ++n) {
-      if (cbk == 0 && t == 0) {
-        dcn_mbar_wait(&bars.geo_full[it & 1], (unsigned)((it >> 1) & 1));
-        int tile = (tile_first + it) % prm.tiles_per_image;
-        const int tile_y = tile / prm.tiles_x, tile_x = tile - tile_y * prm.tiles_x;
-        py0 = tile_y * kTileH - prm.pad - kPatchR; px0 = tile_x * kTileW - prm.pad - kPatchR;
-      }
-      const int gi = ((it & 1) * 9 + t) * kTileM;
-      unsigned short wv[2][4];
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const uint32_t p = (uint32_t)(bt + 64 * h);
-        const uint4 g4 = geo[gi + p];
-        const int q0 = (g4.y >> 31) ? ((int)(short)(g4.x & 0xffffu) - py0) * kPatchW + (((int)g4.x >> 16) - px0) : -1;
-        const float lh = __uint_as_float(g4.y & 0x7fffffffu), lw = __uint_as_float(g4.z), m = __uint_as_float(g4.w);
-        const float hh = 1.f - lh, hw = 1.f - lw;
-        wv[h][0] = __bfloat16_as_ushort(__float2bfloat16_rn(m * (hh * hw)));
-        wv[h][1] = __bfloat16_as_ushort(__float2bfloat16_rn(m * (hh * lw)));
-        wv[h][2] = __bfloat16_as_ushort(__float2bfloat16_rn(m * (lh * hw)));
-        wv[h][3] = __bfloat16_as_ushort(__float2bfloat16_rn(m * (lh * lw)));
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          prv[h][c] = cur[h][c];
-          const uint32_t qc = (uint32_t)(q0 + (c & 1) + (c >> 1) * kPatchW);
-          cur[h][c] = q0 >= 0 ? (((qc >> 7) << 16) | s_chunk_offset(qc & 127u, p)) : 0xffffffffu;
-        }
-      }
-#pragma unroll
-      for (int mb = 0; mb < kPatchMB; ++mb) {
-        dcn_mbar_wait(&bars.s_empty[sb], sph ^ 1u);
-        if (bt == 0) DG2_TS(9 + mb, n);
-        uint8_t* chunk = sring + (size_t)sb * kSChunkBytes;
-#pragma unroll
-        for (int h = 0; h < 2; ++h)
-#pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            const uint32_t old = mb == 2 ? cur[h][c] : prv[h][c];
-            const uint32_t old_mb = mb == 2 ? 0u : (mb == 1 ? 2u : 1u);
-            if ((old >> 16) == old_mb) *reinterpret_cast<unsigned short*>(chunk + (old & 0xffffu)) = 0;
-          }
-#pragma unroll
-        for (int h = 0; h < 2; ++h)
-#pragma unroll
-          for (int c = 0; c < 4; ++c)
-            if ((cur[h][c] >> 16) == (uint32_t)mb) *reinterpret_cast<unsigned short*>(chunk + (cur[h][c] & 0xffffu)) = wv[h][c];
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        __syncwarp();
-        if (lane == 0) dcn_mbar_arrive(&bars.s_full[sb]);
-        if (bt == 0 && mb == 2) DG2_TS(12, n);
-        sb ^= 1; if (sb == 0) sph ^= 1u;
-      }
-      if (++t == 9) {
-        t = 0;
-        if (++cbk == cpb) {
-          cbk = 0;
-          __syncwarp();
-          if (lane == 0) dcn_mbar_arrive(&bars.geo_empty[it & 1]);
-          ++it;
-        }
-      }
-    }
   }
   tc_fence_before();
   __syncthreads();
