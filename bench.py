@@ -67,7 +67,7 @@ def dcn_stack(dev, B, reps=5):
     import math
     from detectron2_centernet_b200 import deform_conv as DC
     g = torch.Generator(device=dev).manual_seed(0)
-    fwd_ms = bwd_ms = flops = 0.0
+    fwd_ms = bwd_ms = fwdp_ms = flops = 0.0
     for Cin, Cout, S_, cnt in DCN_LAYERS:
         x = torch.randn((B, Cin, S_, S_), device=dev, generator=g)
         off = (torch.rand((B, 18, S_, S_), device=dev, generator=g) - 0.5) * 4
@@ -75,9 +75,12 @@ def dcn_stack(dev, B, reps=5):
         w = (torch.rand((Cout, Cin, 3, 3), device=dev, generator=g) - 0.5) * 2 / math.sqrt(9 * Cin)
         bias = torch.zeros(Cout, device=dev)
         gy = torch.randn((B, Cout, S_, S_), device=dev, generator=g)
-        for which in ("fwd", "bwd"):
+        pw = DC.dcnv2_pack_weight(w)             # inference: packed once per weight version (what DeformConvV2.eval() keeps)
+        for which in ("fwd", "fwdp", "bwd"):
             if which == "fwd":
                 fn = lambda: DC.dcnv2_forward(x, off, m, w, bias, 1, 1, 1)          # noqa: E731
+            elif which == "fwdp":
+                fn = lambda: DC.dcnv2_forward(x, off, m, w, bias, 1, 1, 1, packed_weight=pw)   # noqa: E731
             else:
                 fn = lambda: DC.dcnv2_backward(x, off, m, w, gy, 1, 1, 1)           # noqa: E731
             for _ in range(2):
@@ -92,6 +95,8 @@ def dcn_stack(dev, B, reps=5):
             ms = s.elapsed_time(e) / reps
             if which == "fwd":
                 fwd_ms += ms * cnt
+            elif which == "fwdp":
+                fwdp_ms += ms * cnt
             else:
                 bwd_ms += ms * cnt
         flops += 2.0 * Cout * Cin * 9 * S_ * S_ * B * cnt
@@ -99,6 +104,7 @@ def dcn_stack(dev, B, reps=5):
     tf = flops / fwd_ms / 1e9
     return {"workload": "16 DCNv2 layers of the DLA-34 neck @512^2, batch %d, fp32 NCHW in/out, bf16 operands" % B,
             "fwd_ms": round(fwd_ms, 3), "fwd_images_per_s": round(B / fwd_ms * 1e3, 1), "fwd_tflops": round(tf, 1),
+            "fwd_ms_packed_weights": round(fwdp_ms, 3), "fwd_tflops_packed_weights": round(flops / fwdp_ms / 1e9, 1),
             "bwd_ms": round(bwd_ms, 3), "bwd_tflops": round(2 * flops / bwd_ms / 1e9, 1),
             "gflop_per_image_fwd": round(flops / B / 1e9, 2),
             "roofline": {"bound": "tensor", "achieved": round(tf, 1), "peak": peak, "unit": "TFLOP/s",

@@ -44,6 +44,8 @@ SIGNATURES = {
     "ctdet_upsample_add": (c_int, [c_void_p] * 3 + [c_int] * 5 + [c_void_p, c_void_p]),
     "ctdet_upsample_add_backward": (c_int, [c_void_p] * 3 + [c_int] * 5 + [c_void_p, c_void_p, c_void_p]),
     "dcnv2_workspace_bytes": (c_size_t, [c_int] * 5),
+    "dcnv2_packed_weight_bytes": (c_size_t, [c_int] * 2),
+    "dcnv2_pack_weight": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "dcnv2_forward": (c_int, [c_void_p] * 6 + [c_int] * 15 + [c_void_p, c_void_p, c_int] +
                       [c_void_p, c_size_t, c_void_p]),
     "dcnv2_forward_raw27": (c_int, [c_void_p] * 6 + [c_int] * 8 + [c_void_p, c_void_p, c_int] +

@@ -308,6 +308,21 @@ extern "C" size_t dcnv2_workspace_bytes(int B, int Cin, int H, int W, int Cout) 
 }
 
 
+extern "C" size_t dcnv2_packed_weight_bytes(int Cin, int Cout) {
+  if (Cin <= 0 || Cout <= 0) return 0;
+  return dcn_align256((size_t)Cout * Cin * 9 * 2);
+}
+
+extern "C" int dcnv2_pack_weight(const float* weight, int Cin, int Cout, void* packed, ctdet_stream_t stream) {
+  using namespace ctdet;
+  if (Cin <= 0 || Cout <= 0) return CTDET_EINVAL;
+  if (Cin % kBK != 0 || Cout % 16 != 0 || Cout < 16 || Cout > 256) return CTDET_EUNSUPPORTED;
+  if (!weight || !packed) return CTDET_ENULL;
+  if (reinterpret_cast<uintptr_t>(packed) & 15u) return CTDET_EALIGN;
+  dcn_pack_weight_kernel<<<kNumSMs, 256, 0, (cudaStream_t)stream>>>(weight, reinterpret_cast<__nv_bfloat16*>(packed), Cout, Cin);
+  return check_launch();
+}
+
 // raw27 != 0: `offset` is the raw [B,27,Ho,Wo] output of conv_offset_mask (offsets = its channels 0..17 as they
 // are, mask = sigmoid of channels 18..26), `om_bias` its bias or null; `mask` is ignored.
 static int dcn_forward_impl(const float* input, const float* weight, const float* bias,
@@ -319,7 +334,7 @@ static int dcn_forward_impl(const float* input, const float* weight, const float
                             void* workspace, size_t workspace_bytes, ctdet_stream_t stream) {
   using namespace ctdet;
   if (B < 0 || Cin <= 0 || H <= 0 || W <= 0 || Cout <= 0) return CTDET_EINVAL;
-  if (flags & ~(DCN_FLAG_RELU | DCN_FLAG_FP32_BLEND)) return CTDET_EINVAL;
+  if (flags & ~(DCN_FLAG_RELU | DCN_FLAG_FP32_BLEND | DCN_FLAG_PACKED_WEIGHT)) return CTDET_EINVAL;
   if ((scale == nullptr) != (shift == nullptr)) return CTDET_EINVAL;
   // what DLA-34's DeformConvV2 uses (deform_conv.py:505-513): 3x3, one group, one deformable group
   if (kernel_h != 3 || kernel_w != 3 || group != 1 || deformable_group != 1) return CTDET_EUNSUPPORTED;
@@ -346,6 +361,10 @@ static int dcn_forward_impl(const float* input, const float* weight, const float
   dcn_pack_input_kernel<<<dim3((Pin + 63) / 64, (Cin + 63) / 64, B), 256, 0, st>>>(input, xh, Cin, Pin, vec, nullptr, 1, 0);
   int rc = check_launch();
   if (rc) return rc;
+  if (flags & DCN_FLAG_PACKED_WEIGHT) {        // `weight` is the caller's dcnv2_pack_weight output for these weights
+    if (reinterpret_cast<uintptr_t>(weight) & 15u) return CTDET_EALIGN;
+    wk = reinterpret_cast<__nv_bfloat16*>(const_cast<float*>(weight));
+  } else
   dcn_pack_weight_kernel<<<kNumSMs, 256, 0, st>>>(weight, wk, Cout, Cin);
   rc = check_launch();
   if (rc) return rc;

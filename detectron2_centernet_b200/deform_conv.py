@@ -17,7 +17,7 @@ from torch.nn.modules.utils import _pair
 
 from . import _lib
 
-FLAG_RELU, FLAG_FP32_BLEND = 1, 2
+FLAG_RELU, FLAG_FP32_BLEND, FLAG_PACKED_WEIGHT = 1, 2, 4
 
 _ws = {}
 
@@ -31,9 +31,28 @@ def _workspace(nbytes, device):
     return buf
 
 
+def dcnv2_pack_weight(weight):
+    """The bf16, swizzled tensor-core image of `weight` [Cout,Cin,3,3] that `dcnv2_forward` / `dcnv2_forward_raw27`
+    otherwise rebuild on every call (C ABI dcnv2_pack_weight).  Keep it per module and weight version and pass it as
+    `packed_weight=`; it is only valid for the weight values it was made from."""
+    if not weight.is_cuda:
+        raise NotImplementedError("Deformable Conv is not supported on CPUs!")
+    lib = _lib.load()
+    weight = _lib.f32c(weight.detach(), "weight")
+    Cout, Cin, kh, kw = weight.shape
+    if (kh, kw) != (3, 3):
+        raise NotImplementedError("dcnv2_pack_weight: 3x3 kernels")
+    packed = torch.empty(lib.dcnv2_packed_weight_bytes(Cin, Cout), dtype=torch.uint8, device=weight.device)
+    with torch.cuda.device(weight.device):
+        rc = lib.dcnv2_pack_weight(_lib.ptr(weight), Cin, Cout, _lib.ptr(packed), _lib.stream_ptr(weight.device))
+    _lib.check(rc, "dcnv2_pack_weight")
+    return packed
+
+
 def dcnv2_forward(input, offset, mask, weight, bias=None, stride=1, padding=0, dilation=1, groups=1,
-                  deformable_groups=1, scale=None, shift=None, relu=False, fp32_blend=False):
-    """Low-level call.  Optional fused epilogue: (conv + bias) * scale[c] + shift[c], then ReLU."""
+                  deformable_groups=1, scale=None, shift=None, relu=False, fp32_blend=False, packed_weight=None):
+    """Low-level call.  Optional fused epilogue: (conv + bias) * scale[c] + shift[c], then ReLU.
+    packed_weight: `dcnv2_pack_weight(weight)` of the same weights (skips the per-call weight pack)."""
     if not input.is_cuda:
         raise NotImplementedError("Deformable Conv is not supported on CPUs!")    # deform_conv.py:203-204
     lib = _lib.load()
@@ -61,8 +80,12 @@ def dcnv2_forward(input, offset, mask, weight, bias=None, stride=1, padding=0, d
     nbytes = lib.dcnv2_workspace_bytes(B, Cin, H, W, Cout)
     ws = _workspace(max(nbytes, 16), input.device)
     flags = (FLAG_RELU if relu else 0) | (FLAG_FP32_BLEND if fp32_blend else 0)
+    if packed_weight is not None:
+        if packed_weight.numel() != lib.dcnv2_packed_weight_bytes(Cin, Cout) or packed_weight.device != input.device:
+            raise RuntimeError("packed_weight does not belong to a [%d,%d,3,3] weight on %s" % (Cout, Cin, input.device))
+        flags |= FLAG_PACKED_WEIGHT
     with torch.cuda.device(input.device):
-        rc = lib.dcnv2_forward(_lib.ptr(input), _lib.ptr(weight), _lib.ptr(bias), _lib.ptr(offset), _lib.ptr(mask),
+        rc = lib.dcnv2_forward(_lib.ptr(input), _lib.ptr(weight if packed_weight is None else packed_weight), _lib.ptr(bias), _lib.ptr(offset), _lib.ptr(mask),
                                _lib.ptr(out), B, Cin, H, W, Cout, kh, kw, s[0], s[1], p[0], p[1], d[0], d[1],
                                groups, deformable_groups, _lib.ptr(scale), _lib.ptr(shift), flags,
                                _lib.ptr(ws), ctypes.c_size_t(ws.numel()), _lib.stream_ptr(input.device))
@@ -71,7 +94,7 @@ def dcnv2_forward(input, offset, mask, weight, bias=None, stride=1, padding=0, d
 
 
 def dcnv2_forward_raw27(input, offset_mask, weight, bias=None, offset_mask_bias=None, stride=1, padding=1, dilation=1,
-                        scale=None, shift=None, relu=False, fp32_blend=False):
+                        scale=None, shift=None, relu=False, fp32_blend=False, packed_weight=None):
     """dcnv2_forward fed by the RAW 27-channel output of `conv_offset_mask` (C ABI dcnv2_forward_raw27): the kernel
     itself takes channels 0..17 as the offsets, applies the sigmoid to channels 18..26 (resnet.py:308-311) and adds
     `offset_mask_bias` when given, so the chunk / cat / sigmoid / bias-add passes over HBM disappear."""
@@ -101,8 +124,12 @@ def dcnv2_forward_raw27(input, offset_mask, weight, bias=None, offset_mask_bias=
     nbytes = lib.dcnv2_workspace_bytes(B, Cin, H, W, Cout)
     ws = _workspace(max(nbytes, 16), input.device)
     flags = (FLAG_RELU if relu else 0) | (FLAG_FP32_BLEND if fp32_blend else 0)
+    if packed_weight is not None:
+        if packed_weight.numel() != lib.dcnv2_packed_weight_bytes(Cin, Cout) or packed_weight.device != input.device:
+            raise RuntimeError("packed_weight does not belong to a [%d,%d,3,3] weight on %s" % (Cout, Cin, input.device))
+        flags |= FLAG_PACKED_WEIGHT
     with torch.cuda.device(input.device):
-        rc = lib.dcnv2_forward_raw27(_lib.ptr(input), _lib.ptr(weight), _lib.ptr(bias), _lib.ptr(offset_mask),
+        rc = lib.dcnv2_forward_raw27(_lib.ptr(input), _lib.ptr(weight if packed_weight is None else packed_weight), _lib.ptr(bias), _lib.ptr(offset_mask),
                                      _lib.ptr(om_bias), _lib.ptr(out), B, Cin, H, W, Cout, stride, padding, dilation,
                                      _lib.ptr(scale), _lib.ptr(shift), flags,
                                      _lib.ptr(ws), ctypes.c_size_t(ws.numel()), _lib.stream_ptr(input.device))
@@ -240,6 +267,19 @@ class DeformConvV2(nn.Module):
         self.conv = DCN(chi, cho, kernel_size=(3, 3), stride=1, padding=1, dilation=1, deformable_groups=1)
         nn.init.uniform_(self.actf[0].weight.data)
 
+    def _packed_weight(self):
+        """Inference: the tensor-core image of the DCN weights, rebuilt when the parameter is replaced, moved or
+        modified in place (`_version`; writes through `.data` do not bump it -- call `.invalidate_packed_weight()`)."""
+        w = self.conv.weight
+        key = (w.data_ptr(), w._version, str(w.device))
+        if getattr(self, "_packed_key", None) != key:
+            self._packed = dcnv2_pack_weight(w)
+            self._packed_key = key
+        return self._packed
+
+    def invalidate_packed_weight(self):
+        self._packed_key = None
+
     def forward(self, x):
         bn = self.actf[0]
         if not self.training and not torch.is_grad_enabled() and bn.track_running_stats:
@@ -250,5 +290,5 @@ class DeformConvV2(nn.Module):
             # the DCN kernel's geometry stage
             raw = torch.nn.functional.conv2d(x, com.weight, None, com.stride, com.padding, com.dilation, com.groups)
             return dcnv2_forward_raw27(x, raw, self.conv.weight, self.conv.bias, com.bias, 1, 1, 1,
-                                       scale=scale, shift=shift, relu=True)
+                                       scale=scale, shift=shift, relu=True, packed_weight=self._packed_weight())
         return self.actf(self.conv(x))

@@ -235,7 +235,14 @@ int ctdet_upsample_add_backward(const float* grad_out, const float* x, const flo
  * weights), no initialisation needed. */
 #define DCN_FLAG_RELU 1
 #define DCN_FLAG_FP32_BLEND 2
+#define DCN_FLAG_PACKED_WEIGHT 4 /* `weight` points at dcnv2_pack_weight's output for these weights: skips the per-call pack */
 size_t dcnv2_workspace_bytes(int B, int Cin, int H, int W, int Cout);
+/* The bf16, swizzled UMMA image of weight f32 [Cout,Cin,3,3] (dcnv2_packed_weight_bytes() bytes, 16-byte aligned) that
+ * dcnv2_forward / dcnv2_forward_raw27 otherwise rebuild on every call.  A caller keeps it per module and weight version
+ * (the reference has no counterpart: its GEMM reads the fp32 weights, deform_conv_cuda.cu:904) and passes it as `weight`
+ * with DCN_FLAG_PACKED_WEIGHT. */
+size_t dcnv2_packed_weight_bytes(int Cin, int Cout);
+int dcnv2_pack_weight(const float* weight, int Cin, int Cout, void* packed, ctdet_stream_t stream);
 int dcnv2_forward(const float* input, const float* weight, const float* bias,
                   const float* offset, const float* mask, float* output,
                   int B, int Cin, int H, int W, int Cout, int kernel_h, int kernel_w,

@@ -181,3 +181,39 @@ def test_raw27_entry_matches_the_oracle_directly():
         emax = np.abs(got - ref).max() / np.abs(ref).max()
         el2 = np.linalg.norm(got - ref) / np.linalg.norm(ref)
         assert emax <= 2e-2 and el2 <= 1e-2, (om_bias is None, emax, el2)
+
+
+def test_packed_weight_path_is_bit_equal_and_the_module_cache_tracks_the_weight_version():
+    """`dcnv2_pack_weight` + DCN_FLAG_PACKED_WEIGHT (no counterpart in the reference: its GEMM reads the fp32 weights,
+    deform_conv_cuda.cu:904) must give the bits of the per-call pack; the eval-mode module keeps the packed image per
+    weight version."""
+    from detectron2_centernet_b200 import deform_conv as DC
+    g = torch.Generator(device="cpu").manual_seed(5)
+    B, Cin, Cout, H, W = 2, 128, 64, 20, 24
+    x = torch.randn(B, Cin, H, W, generator=g).to(DEV)
+    off = ((torch.rand(B, 18, H, W, generator=g) - 0.5) * 4).to(DEV)
+    m = torch.sigmoid(torch.randn(B, 9, H, W, generator=g)).to(DEV)
+    w = ((torch.rand(Cout, Cin, 3, 3, generator=g) - 0.5) * 0.1).to(DEV)
+    b = torch.randn(Cout, generator=g).to(DEV)
+    want = DC.dcnv2_forward(x, off, m, w, b, 1, 1, 1)
+    pw = DC.dcnv2_pack_weight(w)
+    assert pw.numel() == DC._lib.load().dcnv2_packed_weight_bytes(Cin, Cout)
+    assert torch.equal(DC.dcnv2_forward(x, off, m, w, b, 1, 1, 1, packed_weight=pw), want)
+    raw = torch.randn(B, 27, H, W, generator=g).to(DEV)
+    assert torch.equal(DC.dcnv2_forward_raw27(x, raw, w, b, None, 1, 1, 1, packed_weight=pw),
+                       DC.dcnv2_forward_raw27(x, raw, w, b, None, 1, 1, 1))
+    with pytest.raises(RuntimeError):
+        DC.dcnv2_forward(x, off, m, w, b, 1, 1, 1, packed_weight=pw[:-256])
+    # module: the cache follows in-place updates of the weight
+    mod = DC.DeformConvV2(Cin, Cout).to(DEV).eval()
+    with torch.no_grad():
+        mod.conv.conv_offset_mask.weight.normal_(0, 0.05)
+        y1 = mod(x)
+        k1 = mod._packed_key
+        assert torch.equal(mod(x), y1) and mod._packed_key == k1
+        mod.conv.weight.mul_(0.5)
+        y2 = mod(x)
+        assert mod._packed_key != k1
+        mod.invalidate_packed_weight()
+        assert torch.equal(mod(x), y2)
+    assert float((y1 - y2).abs().max()) > 0
