@@ -169,6 +169,25 @@ def test_backward_matches_reference_at_dla_shapes(ref, shape):
     assert el2 <= 1e-4, (shape, "grad_bias", emax, el2)
 
 
+@pytest.mark.parametrize("cfg", [(64, 64, 64, 24, 2.0), (128, 128, 32, 96, 2.0), (128, 64, 48, 20, 4.5)])
+def test_backward_with_many_tiles_per_cta_matches_reference(ref, cfg):
+    """The bench's regime: several tiles per CTA (768 / 768 / 360 tiles on 148 CTAs), so the persistent kernels'
+    double-buffered geometry, the patch flush every 9 K blocks / the per-tile write-out of grad_offset and grad_mask and
+    the wgrad accumulators across tiles are all exercised; the last case has offsets beyond the +-3-pixel patch of the
+    GEMM scatter (fall-back REDs next to GEMM-scattered taps) and a ragged 48-pixel width."""
+    from detectron2_centernet_b200 import deform_conv as DC
+    Cin, Cout, S, B, off_range = cfg
+    x, off, m, w, b, gy = _case(400 + Cin + Cout + S, B, Cin, Cout, S, S + (8 if S == 48 else 0), off_range=off_range, far=True)
+    want = ref.backward(x, off, m, w, gy, b, 1, 1, 1)
+    got = DC.dcnv2_backward(x, off, m, w, gy, 1, 1, 1)
+    torch.cuda.synchronize()
+    for name, g_, r_ in zip(("grad_input", "grad_offset", "grad_mask", "grad_weight"), got, want):
+        emax, el2 = _errs(g_, r_)
+        assert el2 <= 1.5e-2 and emax <= 4e-2, (cfg, name, emax, el2)
+    emax, el2 = _errs(got[4], want[4])
+    assert el2 <= 1e-4, (cfg, "grad_bias", emax, el2)
+
+
 def test_autograd_module_matches_reference_chain(ref):
     """The DCN module of DeformConvV2 (conv_offset_mask -> chunk / cat / sigmoid -> modulated deformable conv,
     deform_conv.py:505-513 + resnet.py:308-311) under autograd against the same chain around the reference's
