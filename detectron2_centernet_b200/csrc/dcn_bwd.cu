@@ -754,7 +754,8 @@ extern "C" int dcnv2_backward(const float* input, const float* weight, const flo
     const size_t gout_bytes = (size_t)(Cout / 64) * kTileM * 128;
     const size_t fixed = 1024 + kGeoBytes + 2 * gout_bytes;
     int stages = (int)((230 * 1024 - fixed) / (kTileM * kBK * 2));
-    if (stages > 4) stages = 4;
+    const int stage_cap = dcn_tunables().wgrad_stages;
+    if (stages > stage_cap) stages = stage_cap;
     if (stages < 2) return CTDET_EUNSUPPORTED;
     if (bw.paired) stages &= ~1;                               // stage pairs
     prm.stages = stages;

@@ -354,6 +354,7 @@ struct DcnTunables {
   int ld_sleep;          // CTDET_DCN_LD_SLEEP        ns back-off of the weight loader's polls (20)
   int producer_warps;    // CTDET_DCN_PRODUCER_WARPS  gather warps of the forward kernel, 16 or 8 (16)
   int dgrad_warps;       // CTDET_DCN_DGRAD_WARPS     consumer warps of the dgrad kernel, 16 or 8 (16)
+  int wgrad_stages;      // CTDET_DCN_WGRAD_STAGES    im2col ring depth cap of the wgrad kernel, 2..8 (4)
   int wgrad_paired;      // CTDET_DCN_WGRAD_PAIRED    wgrad at Cout = 64: two K blocks per MMA (1)
   int dgrad_gemm;        // CTDET_DCN_DGRAD_GEMM      1: grad_input scatter as a tensor-core GEMM where supported (1)
   int dgrad_gb;          // CTDET_DCN_DGRAD_GB        grad_output tile buffers of that kernel at Cout = 64: 1 or 2 (1)
@@ -367,6 +368,7 @@ static inline const DcnTunables& dcn_tunables() {
     r.ld_sleep = env("CTDET_DCN_LD_SLEEP", 20);
     r.producer_warps = env("CTDET_DCN_PRODUCER_WARPS", 16) == 8 ? 8 : 16;
     r.dgrad_warps = env("CTDET_DCN_DGRAD_WARPS", 16) == 8 ? 8 : 16;
+    r.wgrad_stages = env("CTDET_DCN_WGRAD_STAGES", 4); if (r.wgrad_stages < 2) r.wgrad_stages = 2; if (r.wgrad_stages > kMaxStages) r.wgrad_stages = kMaxStages;
     r.wgrad_paired = env("CTDET_DCN_WGRAD_PAIRED", 1) != 0;
     r.dgrad_gemm = env("CTDET_DCN_DGRAD_GEMM", 1) != 0;
     r.dgrad_gb = env("CTDET_DCN_DGRAD_GB", 1) == 2 ? 2 : 1;
