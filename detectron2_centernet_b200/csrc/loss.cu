@@ -12,6 +12,7 @@
 //              CTAs [2B, grid) -> grid-stride float4 streaming sweep of the heatmap
 //              last CTA to finish -> the three loss scalars; resets the workspace to zero.
 #include "target_common.cuh"
+#include "dcn_common.cuh"      // tcgen05 / TMEM / mbarrier wrappers (the fused hm-head kernel at the end of this file)
 
 namespace ctdet {
 
@@ -130,7 +131,7 @@ __device__ __forceinline__ pk2 log_unit2(pk2 a) {
 // there is no positive to fix up.
 template <bool kProb, bool kZeroGt = false>
 __device__ __forceinline__ pk2 cell2(float x0, float x1, float g0, float g1, float alpha, float gscale,
-                                     pk2& tot, float& tot_pos) {
+                                     pk2& tot, float& tot_pos, float alpha_b) {
   const pk2 one = bcast2(1.f);
   pk2 coef = bcast2(gscale);
   if (!kZeroGt) {
@@ -177,12 +178,18 @@ __device__ __forceinline__ pk2 cell2(float x0, float x1, float g0, float g1, flo
     if (g1 == 1.f) {
       const float lp = log_unit(pc1);
       const float dsb = kProb ? 1.f : (pc1 == p1 ? pc1 * omb : 0.f);
-      tot_pos += gscale * alpha * (lp * (omb * omb));
-      d1 = gscale * alpha * (omb * omb * rcp_approx(pc1) - 2.f * omb * lp) * dsb;
+      tot_pos += gscale * alpha_b * (lp * (omb * omb));
+      d1 = gscale * alpha_b * (omb * omb * rcp_approx(pc1) - 2.f * omb * lp) * dsb;
     }
     d = pack2(d0, d1);
   }
   return d;
+}
+
+template <bool kProb, bool kZeroGt = false>      // both cells of one class plane: one alpha
+__device__ __forceinline__ pk2 cell2(float x0, float x1, float g0, float g1, float alpha, float gscale,
+                                     pk2& tot, float& tot_pos) {
+  return cell2<kProb, kZeroGt>(x0, x1, g0, g1, alpha, gscale, tot, tot_pos, alpha);
 }
 
 // ---- pieces shared by loss_kernel and target_loss_fused_kernel ------------------------------------
@@ -532,6 +539,8 @@ target_loss_fused_kernel(const int4* __restrict__ obj_geo, const double* __restr
   loss_tail(acc0, acc1, is_reg, s_norm[1], w_wh, w_off, losses, ws, s_red, &s_last);
 }
 
+#include "head_loss.cuh"
+
 }  // namespace ctdet
 
 extern "C" size_t ctdet_loss_workspace_bytes(void) { return sizeof(ctdet::LossWs); }
@@ -667,5 +676,46 @@ extern "C" int ctdet_target_loss_fused(const float* boxes, const int64_t* classe
       norm_override, B, C, H, W, CTDET_MAX_OBJS, band_rows, bands, FastDiv((uint32_t)bands), FastDiv((uint32_t)C),
       flags, n_reg, w_hm, w_wh, w_off,
       losses, d_hm, d_wh, d_reg, reinterpret_cast<LossWs*>(workspace));
+  return check_launch();
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// f2, second half: hm head 1x1 convolution + focal loss in one kernel (head_loss.cuh)
+extern "C" int ctdet_head_focal_fused(const float* feat, const float* weight, const float* bias, const float* gt_hm,
+                                      const float* alpha, const int32_t* num_pos_img, const float* norm_override,
+                                      int B, int Cf, int C, int H, int W, int flags, float w_hm,
+                                      float* loss, float* d_logits, void* workspace, size_t workspace_bytes,
+                                      ctdet_stream_t stream) {
+  using namespace ctdet;
+  if (B <= 0 || Cf <= 0 || C <= 0 || H <= 0 || W <= 0) return CTDET_EINVAL;
+  if (flags & ~CTDET_LOSS_ALPHA_UNIFORM) return CTDET_EINVAL;
+  if (!feat || !weight || !gt_hm || !alpha || !loss || !workspace) return CTDET_ENULL;
+  if (workspace_bytes < sizeof(LossWs)) return CTDET_EWORKSPACE;
+  if (reinterpret_cast<uintptr_t>(workspace) & 7u) return CTDET_EALIGN;
+  if (!aligned16(weight)) return CTDET_EALIGN;
+  const int64_t P = (int64_t)H * W;
+  // tensor-core tiling: K blocks of 64 channels, UMMA N = C, tiles of 128 pixels inside one image
+  if (Cf % kBK != 0 || C % 16 != 0 || C > 128 || P % kTileM != 0) return CTDET_EUNSUPPORTED;
+  if ((int64_t)B * C * P >= ((int64_t)1 << 33) || P >= ((int64_t)1 << 30) || (int64_t)B * (P / kTileM) > 0x7fffffffLL) return CTDET_EINVAL;
+  cudaStream_t st = (cudaStream_t)stream;
+  LossWs* ws = reinterpret_cast<LossWs*>(workspace);
+  if (num_pos_img == nullptr && norm_override == nullptr) {
+    const size_t n4 = (size_t)B * C * P / 4;
+    if (!aligned16(gt_hm)) return CTDET_EALIGN;
+    count_pos_kernel<<<kNumSMs * 8, kLossThreads, 0, st>>>(gt_hm, n4, ws);
+    int rc = check_launch();
+    if (rc) return rc;
+  }
+  const size_t w_bytes = (size_t)(Cf / kBK) * C * 128 + (size_t)2 * C * sizeof(float);
+  int stages = (int)((226 * 1024 - 1024 - w_bytes) / (kTileM * 128));
+  if (stages > kHfMaxStages) stages = kHfMaxStages;
+  if (stages < 2) return CTDET_EUNSUPPORTED;
+  const size_t smem = 1024 + (size_t)stages * kTileM * 128 + w_bytes;
+  cudaError_t e = cudaFuncSetAttribute(head_focal_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
+  const long long tiles = (long long)B * (P / kTileM);
+  const unsigned grid = (unsigned)(tiles < kNumSMs ? tiles : kNumSMs);
+  head_focal_fused_kernel<<<grid, kHfThreads, smem, st>>>(feat, weight, bias, gt_hm, alpha, num_pos_img, norm_override,
+                                                          B, Cf, C, (int)P, flags, stages, w_hm, loss, d_logits, ws);
   return check_launch();
 }

@@ -258,3 +258,72 @@ class RegL1Loss(nn.Module):
                                _prep(target, "RegL1Loss target"), None, None, None, None, 0,
                                (0.0, 1.0, 0.0))
         return out[1]
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# SURVEY section 8 f2, second half: hm head 1x1 convolution + focal loss in one kernel
+def _head_focal_call(feat, weight, bias, gt_hm, alpha, num_pos, norm, uniform, w_hm, need_grad):
+    lib = _lib.load()
+    dev = feat.device
+    B, Cf, H, W = feat.shape
+    C = weight.shape[0]
+    loss = torch.empty(1, dtype=torch.float32, device=dev)
+    d_logits = torch.empty((B, C, H, W), dtype=torch.float32, device=dev) if need_grad else None
+    ws = _lib.zero_workspace("loss", lib.ctdet_loss_workspace_bytes(), dev)
+    with torch.cuda.device(dev):
+        rc = lib.ctdet_head_focal_fused(_lib.ptr(feat), _lib.ptr(weight), _lib.ptr(bias), _lib.ptr(gt_hm), _lib.ptr(alpha),
+                                        _lib.ptr(num_pos), _lib.ptr(norm), B, Cf, C, H, W, _FLAG_ALPHA_UNIFORM if uniform else 0,
+                                        float(w_hm), _lib.ptr(loss), _lib.ptr(d_logits), _lib.ptr(ws),
+                                        ctypes.c_size_t(ws.numel()), _lib.stream_ptr(dev))
+    _lib.check(rc, "ctdet_head_focal_fused")
+    return loss, d_logits
+
+
+class _HeadFocalFused(torch.autograd.Function):
+    """hm_loss * w_hm of `Conv2d(Cf, C, 1)(feat)` without the logits in HBM.  The kernel returns d(loss)/d(logits); the
+    convolution's own backward (grad_input / grad_weight / grad_bias: two GEMMs over [B*H*W, C] x [C, Cf]) runs on it."""
+
+    @staticmethod
+    def forward(ctx, feat, weight, bias, gt_hm, alpha, num_pos, norm, uniform, w_hm):
+        need = feat.requires_grad or weight.requires_grad or (bias is not None and bias.requires_grad)
+        loss, d_logits = _head_focal_call(feat, weight, bias, gt_hm, alpha, num_pos, norm, uniform, w_hm, need)
+        ctx.save_for_backward(feat, weight)
+        ctx.d_logits = d_logits
+        ctx.has_bias = bias is not None
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        feat, weight = ctx.saved_tensors
+        d = ctx.d_logits
+        if d is None:
+            raise RuntimeError("the fused hm head loss was already back-propagated (or no input required a gradient)")
+        ctx.d_logits = None
+        d = _scaled(d, g.contiguous()[0:1])
+        B, C = d.shape[0], d.shape[1]
+        d2 = d.view(B, C, -1)                                     # [B, C, P]
+        f2 = feat.view(B, feat.shape[1], -1)                      # [B, Cf, P]
+        g_feat = torch.matmul(weight.t().unsqueeze(0), d2).view_as(feat) if ctx.needs_input_grad[0] else None
+        g_w = torch.einsum("bcp,bfp->cf", d2, f2) if ctx.needs_input_grad[1] else None
+        g_b = d2.sum(dim=(0, 2)) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
+        return g_feat, g_w, g_b, None, None, None, None, None, None
+
+
+def hm_head_focal_loss(feat, weight, bias, gt_hm, alpha=None, num_pos=None, norm=None, w_hm=1.0):
+    """`FocalLoss()(clamp(sigmoid_(Conv2d(Cf, C, 1)(feat))), gt_hm) * w_hm` (centernet.py:118-123, :152, :204, :323-369)
+    in one kernel: the logits are formed per pixel tile on the tensor cores (bf16 operands) and never written to HBM.
+    feat f32 [B,Cf,H,W]; weight f32 [C,Cf] or [C,Cf,1,1]; bias f32 [C] or None; gt_hm f32 [B,C,H,W];
+    num_pos i32 [B] (from generate_targets) or norm f32 [2] = {num_pos, .}; both None: positives are counted."""
+    feat = _prep(feat, "feat")
+    gt_hm = _prep(gt_hm, "gt_hm")
+    if weight.dim() == 4:
+        if weight.shape[2:] != (1, 1):
+            raise NotImplementedError("hm_head_focal_loss fuses the head's final 1x1 convolution")
+        weight = weight.reshape(weight.shape[0], weight.shape[1])
+    weight = _prep(weight, "weight")
+    bias = _prep(bias, "bias")
+    C = weight.shape[0]
+    if tuple(gt_hm.shape) != (feat.shape[0], C, feat.shape[2], feat.shape[3]):
+        raise RuntimeError("gt_hm must be [%d,%d,%d,%d]" % (feat.shape[0], C, feat.shape[2], feat.shape[3]))
+    a = alpha_tensor(alpha, C, feat.device)
+    return _HeadFocalFused.apply(feat, weight, bias, gt_hm, a, num_pos, norm, alpha_is_uniform(alpha), w_hm)

@@ -16,6 +16,7 @@
  *                        FocalLoss/_neg_loss, :372-381 RegL1Loss (+ :383 _transpose_and_gather_feat)
  *                        and their autograd backward
  *   ctdet_target_loss_fused  the two rows above in one pass (gen_heatmap at centernet.py:188 + losses :191-212)
+ *   ctdet_head_focal_fused   centernet.py:118-123 / :152 (the hm head's final 1x1 Conv2d) + :204 + :323-369 (focal loss)
  *   ctdet_decode         centernet.py:426 ctdet_decode = :399 _nms, :408 _topk, :383 gather, boxes
  *   ctdet_nms / ctdet_gather_feat   centernet.py:399 _nms / :383 _transpose_and_gather_feat
  *   ctdet_postprocess    centernet.py:236-266 inference_single_image (slice + score threshold) and
@@ -126,6 +127,24 @@ int ctdet_target_loss_fused(const float* boxes, const int64_t* classes, const in
                             uint8_t* reg_mask, int64_t* ind, float* gt_wh, float* gt_reg, int32_t* num_pos,
                             float* losses, float* d_hm, float* d_wh, float* d_reg,
                             void* workspace, size_t workspace_bytes, ctdet_stream_t stream);
+
+/* ---------------------------------------------------------------- fused hm head + focal loss --
+ * SURVEY.md section 8 f2, second half: the hm head's final 1x1 convolution (centernet.py:118-123: nn.Conv2d(head_conv,
+ * num_classes, kernel_size=1), bias -2.19; applied at :152) AND the focal term of CenterNet.losses (:204 sigmoid_ + clamp,
+ * :323-369 FocalLoss / _neg_loss) with its backward down to the logits, in one kernel:
+ *   logits[128 px, C] = feat[128 px, Cf] * weight^T + bias   per tile on the tensor cores (bf16 operands, fp32 accumulation)
+ * are consumed from TMEM by the loss arithmetic of ctdet_loss_fwd_bwd; the [B,C,H,W] logits never exist in HBM.
+ *   feat f32 [B,Cf,H,W] (the ReLU output of the head's 3x3 convolution)   weight f32 [C,Cf] (= the [C,Cf,1,1] kernel)
+ *   bias f32 [C] or NULL   gt_hm f32 [B,C,H,W]   alpha / num_pos_img / norm_override / w_hm as in ctdet_loss_fwd_bwd
+ *   loss f32 [1] = hm_loss * w_hm   d_logits f32 [B,C,H,W] or NULL: d(loss)/d(logits) -- the grad_output of the
+ *   convolution's own backward (grad_input, grad_weight, grad_bias stay with the caller's Conv2d).
+ * Requires Cf % 64 == 0, C % 16 == 0, C <= 128, H*W % 128 == 0; weight 16-byte aligned.
+ * workspace: ctdet_loss_workspace_bytes() bytes, the ctdet_loss_fwd_bwd contract (zero on entry, left zero). */
+int ctdet_head_focal_fused(const float* feat, const float* weight, const float* bias, const float* gt_hm,
+                           const float* alpha, const int32_t* num_pos_img, const float* norm_override,
+                           int B, int Cf, int C, int H, int W, int flags, float w_hm,
+                           float* loss, float* d_logits, void* workspace, size_t workspace_bytes,
+                           ctdet_stream_t stream);
 
 /* d[i] *= *g for i < n, entirely skipped on the device when *g == 1 (autograd upstream gradient,
  * no host sync).  g: f32 device scalar. */

@@ -1,0 +1,103 @@
+"""GPU: SURVEY section 8 f2, second half -- `ctdet_head_focal_fused` (the hm head's final 1x1 convolution + focal loss in
+one kernel; the logits never reach HBM) against the reference chain
+    Conv2d(head_conv, C, 1) (centernet.py:118-123, applied :152) -> sigmoid_ + clamp (:204) -> _neg_loss (:333-369)
+evaluated in fp32 by torch + the pinned oracle port (oracle/ref_gpu_chain.neg_loss), with autograd for the gradients.
+
+Stated tolerance (feat and weight are rounded to bf16 for the tensor cores, fp32 accumulation over Cf = 256):
+  loss <= 2e-3 relative;  d_logits relative L2 <= 2e-2, max <= 5e-2 of the max;  the convolution's parameter / input
+  gradients (torch GEMMs on d_logits) relative L2 <= 2e-2.
+With bf16-representable feat / weight the only difference to `ctdet_loss_fwd_bwd` on torch's fp32 logits is the summation
+order of the 256-term dot products: d_logits relative L2 <= 1e-4.
+"""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _setup(seed, B, Cf, C, H, W, bf16_exact=False):
+    from detectron2_centernet_b200 import synthetic as S
+    from detectron2_centernet_b200 import target as T
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    feat = torch.relu(torch.randn(B, Cf, H, W, generator=g))              # the head's ReLU output
+    w = torch.randn(C, Cf, generator=g) * (1.0 / Cf ** 0.5)
+    b = torch.full((C,), -2.19)
+    if bf16_exact:
+        feat, w = feat.bfloat16().float(), w.bfloat16().float()
+    bl, cl = S.make_batch_objects(seed, B, 4 * max(H, W), num_classes=C)
+    boxes, classes, offsets = S.pack_objects(bl, cl)
+    tg = T.target_gen(*[torch.from_numpy(np.ascontiguousarray(a)).to(DEV) for a in (boxes, classes, offsets)], B, C, H, W)
+    return feat.to(DEV), w.to(DEV), b.to(DEV), tg
+
+
+def _reference(feat, w, b, gt, alpha):
+    from oracle import ref_gpu_chain as RC
+    feat = feat.clone().requires_grad_(True)
+    w = w.clone().requires_grad_(True)
+    b = b.clone().requires_grad_(True)
+    logits = torch.nn.functional.conv2d(feat, w[:, :, None, None], b)
+    logits.retain_grad()
+    hm = torch.clamp(torch.sigmoid(logits), min=1e-4, max=1 - 1e-4)
+    loss = RC.neg_loss(hm, gt, alpha)
+    loss.backward()
+    return loss.detach(), logits.grad, feat.grad, w.grad, b.grad
+
+
+def _rel(a, b):
+    a, b = a.double(), b.double()
+    return float((a - b).norm() / b.norm().clamp_min(1e-30)), float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+@pytest.mark.parametrize("cfg", [(2, 256, 80, 32, 32), (1, 64, 16, 16, 8), (3, 128, 96, 24, 16)])
+def test_fused_head_loss_matches_conv_plus_reference_loss(cfg):
+    from detectron2_centernet_b200 import losses as L
+    B, Cf, C, H, W = cfg
+    feat, w, b, tg = _setup(11 + Cf, B, Cf, C, H, W)
+    alpha = [1.0] if C != 16 else [0.5 + 0.1 * i for i in range(16)]      # per-class alpha on the small case
+    want = _reference(feat, w, b, tg["hm"], alpha)
+    f = feat.clone().requires_grad_(True)
+    ww = w.clone().requires_grad_(True)
+    bb = b.clone().requires_grad_(True)
+    loss = L.hm_head_focal_loss(f, ww, bb, tg["hm"], alpha=alpha, num_pos=tg.get("num_pos"))
+    loss.sum().backward()
+    torch.cuda.synchronize()
+    assert abs(float(loss) - float(want[0])) <= 2e-3 * abs(float(want[0])), (float(loss), float(want[0]))
+    for name, got, ref in (("feat", f.grad, want[2]), ("weight", ww.grad, want[3]), ("bias", bb.grad, want[4])):
+        l2, mx = _rel(got, ref)
+        assert l2 <= 2e-2, (cfg, name, l2, mx)
+    # the kernel's own output, d(loss)/d(logits)
+    loss2, d = L._head_focal_call(feat, w, b, tg["hm"], L.alpha_tensor(alpha, C, feat.device), tg.get("num_pos"), None,
+                                  L.alpha_is_uniform(alpha), 1.0, True)
+    l2, mx = _rel(d, want[1])
+    assert l2 <= 2e-2 and mx <= 5e-2, (cfg, "d_logits", l2, mx)
+    assert float(loss2) == float(loss)
+
+
+def test_fused_head_loss_equals_the_unfused_kernel_on_bf16_representable_operands():
+    from detectron2_centernet_b200 import losses as L
+    B, Cf, C, H, W = 2, 256, 80, 32, 32
+    feat, w, b, tg = _setup(5, B, Cf, C, H, W, bf16_exact=True)
+    logits = torch.nn.functional.conv2d(feat.double(), w.double()[:, :, None, None], b.double()).float()
+    a = L.alpha_tensor(None, C, feat.device)
+    losses, d_hm, _, _ = L._call(logits, None, None, tg["hm"], None, None, None, None, a, tg.get("num_pos"), None,
+                                 L._FLAG_ALPHA_UNIFORM, (1.0, 0.1, 1.0), True)
+    loss, d = L._head_focal_call(feat, w, b, tg["hm"], a, tg.get("num_pos"), None, True, 1.0, True)
+    torch.cuda.synchronize()
+    l2, mx = _rel(d, d_hm)
+    assert l2 <= 1e-4, (l2, mx)
+    assert abs(float(loss) - float(losses[0])) <= 1e-5 * abs(float(losses[0]))
+    # counted normaliser (no num_pos given) and the forward-only call
+    loss3, none = L._head_focal_call(feat, w, b, tg["hm"], a, None, None, True, 1.0, False)
+    assert none is None and abs(float(loss3) - float(loss)) <= 1e-6 * abs(float(loss))
+
+
+def test_fused_head_loss_rejects_what_it_does_not_tile():
+    from detectron2_centernet_b200 import losses as L
+    feat = torch.zeros(1, 64, 10, 10, device=DEV)                           # H*W % 128 != 0
+    with pytest.raises(NotImplementedError):
+        L.hm_head_focal_loss(feat, torch.zeros(16, 64, device=DEV), None, torch.zeros(1, 16, 10, 10, device=DEV))
+    with pytest.raises(NotImplementedError):                                 # 3x3 kernel
+        L.hm_head_focal_loss(torch.zeros(1, 64, 16, 8, device=DEV), torch.zeros(16, 64, 3, 3, device=DEV), None,
+                             torch.zeros(1, 16, 16, 8, device=DEV))
