@@ -32,6 +32,7 @@ SIGNATURES = {
     "ctdet_target_loss_fused": (c_int, [c_void_p] * 8 + [c_int] * 5 + [c_float] * 3 + [c_void_p] * 9 +
                                 [c_void_p, c_size_t, c_void_p]),
     "ctdet_head_focal_fused": (c_int, [c_void_p] * 7 + [c_int] * 6 + [c_float] + [c_void_p] * 3 + [c_size_t, c_void_p]),
+    "ctdet_head_focal_fused_bwd": (c_int, [c_void_p] * 7 + [c_int] * 6 + [c_float] + [c_void_p] * 6 + [c_size_t, c_void_p]),
     "ctdet_scale_grad": (c_int, [c_void_p, c_size_t, c_void_p, c_void_p]),
     "ctdet_decode_workspace_bytes": (c_size_t, [c_int] * 5),
     "ctdet_decode": (c_int, [c_void_p] * 3 + [c_int] * 5 + [c_float, c_int] + [c_void_p] * 4 +

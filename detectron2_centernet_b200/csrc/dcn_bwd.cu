@@ -37,13 +37,6 @@ struct DcnBwdParams {
   int s_bufs;                          // dgrad (GEMM scatter): S chunk ring depth
 };
 
-// MN-major, 128-byte-swizzled operand: rows of 64 contiguous M/N elements (128 B) per K index, 8-row
-// (K) groups 1024 B apart (SBO); LBO = distance between 64-element atoms along M/N.
-__device__ __forceinline__ uint64_t make_sw128_desc_mn(uint32_t smem_addr, uint32_t lbo_bytes) {
-  return (uint64_t)((smem_addr >> 4) & 0x3fffu) | ((uint64_t)((lbo_bytes >> 4) & 0x3fffu) << 16) |
-         ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
-}
-
 // grad_output tile [128 pixels][Cout] bf16 -> shared memory, Cout/64 slabs of [128][64] in the
 // 128-byte swizzled layout (read K-major by dgrad, MN-major by wgrad).  thread r = pixel of the tile.
 __device__ __forceinline__ void dcn_load_gout_tile(const DcnParams& prm, const __nv_bfloat16* gh, int tile, int r,

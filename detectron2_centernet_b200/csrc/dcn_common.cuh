@@ -63,6 +63,13 @@ __device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr) {
   return (uint64_t)((smem_addr >> 4) & 0x3fffu) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) |
          (1ull << 46) | (2ull << 61);
 }
+// MN-major, 128-byte-swizzled operand: rows of 64 contiguous M/N elements (128 B) per K index, 8-row
+// (K) groups 1024 B apart (SBO); LBO = distance between 64-element atoms along M/N.
+__device__ __forceinline__ uint64_t make_sw128_desc_mn(uint32_t smem_addr, uint32_t lbo_bytes) {
+  return (uint64_t)((smem_addr >> 4) & 0x3fffu) | ((uint64_t)((lbo_bytes >> 4) & 0x3fffu) << 16) |
+         ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+
 // kind::f16 instruction descriptor: D = fp32, A = B = bf16, both K-major, N>>3 at [17,23), M>>4 at [24,29)
 __device__ __forceinline__ uint32_t make_idesc_bf16(int M, int N) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);

@@ -719,3 +719,50 @@ extern "C" int ctdet_head_focal_fused(const float* feat, const float* weight, co
                                                           B, Cf, C, (int)P, flags, stages, w_hm, loss, d_logits, ws);
   return check_launch();
 }
+
+// The same with the convolution's backward inside (head_loss.cuh: head_focal_fused_bwd_kernel)
+extern "C" int ctdet_head_focal_fused_bwd(const float* feat, const float* weight, const float* bias, const float* gt_hm,
+                                          const float* alpha, const int32_t* num_pos_img, const float* norm_override,
+                                          int B, int Cf, int C, int H, int W, int flags, float w_hm,
+                                          float* loss, float* d_logits, float* d_feat, float* d_weight, float* d_bias,
+                                          void* workspace, size_t workspace_bytes, ctdet_stream_t stream) {
+  using namespace ctdet;
+  if (B <= 0 || Cf <= 0 || C <= 0 || H <= 0 || W <= 0) return CTDET_EINVAL;
+  if (flags & ~CTDET_LOSS_ALPHA_UNIFORM) return CTDET_EINVAL;
+  if (!feat || !weight || !gt_hm || !alpha || !loss || !d_feat || !d_weight || !workspace) return CTDET_ENULL;
+  if (workspace_bytes < sizeof(LossWs)) return CTDET_EWORKSPACE;
+  if (reinterpret_cast<uintptr_t>(workspace) & 7u) return CTDET_EALIGN;
+  if (!aligned16(weight)) return CTDET_EALIGN;
+  const int64_t P = (int64_t)H * W;
+  // tiling as ctdet_head_focal_fused, plus: dW^T tiles of 128 channels, and logits + dW^T + d_feat must fit 512 TMEM columns
+  if (Cf % kTileM != 0 || Cf > 256 || C % 16 != 0 || C > 128 || P % kTileM != 0) return CTDET_EUNSUPPORTED;
+  if (C + (Cf / kTileM) * C + Cf > 512) return CTDET_EUNSUPPORTED;
+  if ((int64_t)B * C * P >= ((int64_t)1 << 33) || P >= ((int64_t)1 << 30) || (int64_t)B * (P / kTileM) > 0x7fffffffLL) return CTDET_EINVAL;
+  cudaStream_t st = (cudaStream_t)stream;
+  LossWs* ws = reinterpret_cast<LossWs*>(workspace);
+  cudaError_t e = cudaMemsetAsync(d_weight, 0, (size_t)C * Cf * sizeof(float), st);
+  if (e == cudaSuccess && d_bias) e = cudaMemsetAsync(d_bias, 0, (size_t)C * sizeof(float), st);
+  if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
+  if (num_pos_img == nullptr && norm_override == nullptr) {
+    const size_t n4 = (size_t)B * C * P / 4;
+    if (!aligned16(gt_hm)) return CTDET_EALIGN;
+    count_pos_kernel<<<kNumSMs * 8, kLossThreads, 0, st>>>(gt_hm, n4, ws);
+    int rc = check_launch();
+    if (rc) return rc;
+  }
+  const int KB = Cf / kBK;
+  const size_t fixed = 1024 + (size_t)2 * kTileM * 128 + (size_t)KB * C * 128 + (size_t)2 * C * sizeof(float);
+  int stages = (int)((226 * 1024 - fixed) / (kTileM * 128));
+  if (stages > kHfMaxStages) stages = kHfMaxStages;
+  stages = stages / KB * KB;                                  // whole tiles: the ring is released tile by tile
+  if (stages < KB) return CTDET_EUNSUPPORTED;
+  const size_t smem = fixed + (size_t)stages * kTileM * 128;
+  e = cudaFuncSetAttribute(head_focal_fused_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
+  const long long tiles = (long long)B * (P / kTileM);
+  const unsigned grid = (unsigned)(tiles < kNumSMs ? tiles : kNumSMs);
+  head_focal_fused_bwd_kernel<<<grid, kHfThreads, smem, st>>>(feat, weight, bias, gt_hm, alpha, num_pos_img, norm_override,
+                                                              B, Cf, C, (int)P, flags, stages, w_hm, loss, d_logits, d_feat,
+                                                              d_weight, d_bias, ws);
+  return check_launch();
+}

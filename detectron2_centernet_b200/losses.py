@@ -279,37 +279,77 @@ def _head_focal_call(feat, weight, bias, gt_hm, alpha, num_pos, norm, uniform, w
     return loss, d_logits
 
 
+def _head_focal_bwd_call(feat, weight, bias, gt_hm, alpha, num_pos, norm, uniform, w_hm, want_d_logits=False):
+    """The kernel with the convolution's backward inside: -> loss, d_feat, d_weight, d_bias (, d_logits)."""
+    lib = _lib.load()
+    dev = feat.device
+    B, Cf, H, W = feat.shape
+    C = weight.shape[0]
+    loss = torch.empty(1, dtype=torch.float32, device=dev)
+    d_feat = torch.empty_like(feat)
+    d_weight = torch.empty((C, Cf), dtype=torch.float32, device=dev)
+    d_bias = torch.empty((C,), dtype=torch.float32, device=dev)
+    d_logits = torch.empty((B, C, H, W), dtype=torch.float32, device=dev) if want_d_logits else None
+    ws = _lib.zero_workspace("loss", lib.ctdet_loss_workspace_bytes(), dev)
+    with torch.cuda.device(dev):
+        rc = lib.ctdet_head_focal_fused_bwd(_lib.ptr(feat), _lib.ptr(weight), _lib.ptr(bias), _lib.ptr(gt_hm), _lib.ptr(alpha),
+                                            _lib.ptr(num_pos), _lib.ptr(norm), B, Cf, C, H, W,
+                                            _FLAG_ALPHA_UNIFORM if uniform else 0, float(w_hm), _lib.ptr(loss), _lib.ptr(d_logits),
+                                            _lib.ptr(d_feat), _lib.ptr(d_weight), _lib.ptr(d_bias), _lib.ptr(ws),
+                                            ctypes.c_size_t(ws.numel()), _lib.stream_ptr(dev))
+    _lib.check(rc, "ctdet_head_focal_fused_bwd")
+    return loss, d_feat, d_weight, d_bias, d_logits
+
+
+def head_bwd_fusable(Cf, C, HW):
+    """Shapes `ctdet_head_focal_fused_bwd` tiles (TMEM: logits + dW^T + d_feat <= 512 columns)."""
+    return Cf % 128 == 0 and Cf <= 256 and C % 16 == 0 and C + (Cf // 128) * C + Cf <= 512 and HW % 128 == 0
+
+
 class _HeadFocalFused(torch.autograd.Function):
-    """hm_loss * w_hm of `Conv2d(Cf, C, 1)(feat)` without the logits in HBM.  The kernel returns d(loss)/d(logits); the
-    convolution's own backward (grad_input / grad_weight / grad_bias: two GEMMs over [B*H*W, C] x [C, Cf]) runs on it."""
+    """hm_loss * w_hm of `Conv2d(Cf, C, 1)(feat)` without the logits in HBM.  Where the shapes allow it the convolution's
+    backward (grad_input / grad_weight / grad_bias) is produced by the same kernel -- the gradient of the logits never
+    reaches HBM either; otherwise the kernel returns d(loss)/d(logits) and two torch GEMMs finish the job."""
 
     @staticmethod
-    def forward(ctx, feat, weight, bias, gt_hm, alpha, num_pos, norm, uniform, w_hm):
+    def forward(ctx, feat, weight, bias, gt_hm, alpha, num_pos, norm, uniform, w_hm, fuse_backward):
         need = feat.requires_grad or weight.requires_grad or (bias is not None and bias.requires_grad)
+        ctx.has_bias = bias is not None
+        ctx.fused = bool(need and fuse_backward and head_bwd_fusable(feat.shape[1], weight.shape[0], feat.shape[2] * feat.shape[3]))
+        if ctx.fused:
+            loss, d_feat, d_weight, d_bias, _ = _head_focal_bwd_call(feat, weight, bias, gt_hm, alpha, num_pos, norm, uniform, w_hm)
+            ctx.grads = (d_feat, d_weight, d_bias)
+            return loss
         loss, d_logits = _head_focal_call(feat, weight, bias, gt_hm, alpha, num_pos, norm, uniform, w_hm, need)
         ctx.save_for_backward(feat, weight)
-        ctx.d_logits = d_logits
-        ctx.has_bias = bias is not None
+        ctx.grads = d_logits
         return loss
 
     @staticmethod
     def backward(ctx, g):
-        feat, weight = ctx.saved_tensors
-        d = ctx.d_logits
-        if d is None:
+        if ctx.grads is None:
             raise RuntimeError("the fused hm head loss was already back-propagated (or no input required a gradient)")
-        ctx.d_logits = None
-        d = _scaled(d, g.contiguous()[0:1])
+        g = g.contiguous()[0:1]
+        if ctx.fused:
+            d_feat, d_weight, d_bias = ctx.grads
+            ctx.grads = None
+            return (_scaled(d_feat, g) if ctx.needs_input_grad[0] else None,
+                    _scaled(d_weight, g) if ctx.needs_input_grad[1] else None,
+                    _scaled(d_bias, g) if (ctx.has_bias and ctx.needs_input_grad[2]) else None,
+                    None, None, None, None, None, None, None)
+        feat, weight = ctx.saved_tensors
+        d = _scaled(ctx.grads, g)
+        ctx.grads = None
         B, C = d.shape[0], d.shape[1]
         d2 = d.view(B, C, -1)                                     # [B, C, P]
         f2 = feat.view(B, feat.shape[1], -1)                      # [B, Cf, P]
         g_feat = torch.matmul(weight.t().unsqueeze(0), d2).view_as(feat) if ctx.needs_input_grad[0] else None
         g_w = torch.einsum("bcp,bfp->cf", d2, f2) if ctx.needs_input_grad[1] else None
         g_b = d2.sum(dim=(0, 2)) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
-        return g_feat, g_w, g_b, None, None, None, None, None, None
+        return g_feat, g_w, g_b, None, None, None, None, None, None, None
 
 
-def hm_head_focal_loss(feat, weight, bias, gt_hm, alpha=None, num_pos=None, norm=None, w_hm=1.0):
+def hm_head_focal_loss(feat, weight, bias, gt_hm, alpha=None, num_pos=None, norm=None, w_hm=1.0, fuse_backward=True):
     """`FocalLoss()(clamp(sigmoid_(Conv2d(Cf, C, 1)(feat))), gt_hm) * w_hm` (centernet.py:118-123, :152, :204, :323-369)
     in one kernel: the logits are formed per pixel tile on the tensor cores (bf16 operands) and never written to HBM.
     feat f32 [B,Cf,H,W]; weight f32 [C,Cf] or [C,Cf,1,1]; bias f32 [C] or None; gt_hm f32 [B,C,H,W];
@@ -326,4 +366,4 @@ def hm_head_focal_loss(feat, weight, bias, gt_hm, alpha=None, num_pos=None, norm
     if tuple(gt_hm.shape) != (feat.shape[0], C, feat.shape[2], feat.shape[3]):
         raise RuntimeError("gt_hm must be [%d,%d,%d,%d]" % (feat.shape[0], C, feat.shape[2], feat.shape[3]))
     a = alpha_tensor(alpha, C, feat.device)
-    return _HeadFocalFused.apply(feat, weight, bias, gt_hm, a, num_pos, norm, alpha_is_uniform(alpha), w_hm)
+    return _HeadFocalFused.apply(feat, weight, bias, gt_hm, a, num_pos, norm, alpha_is_uniform(alpha), w_hm, fuse_backward)

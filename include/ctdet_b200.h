@@ -146,6 +146,18 @@ int ctdet_head_focal_fused(const float* feat, const float* weight, const float* 
                            float* loss, float* d_logits, void* workspace, size_t workspace_bytes,
                            ctdet_stream_t stream);
 
+/* The same with the convolution's backward inside (autograd of the nn.Conv2d at centernet.py:118-123): neither the logits nor
+ * their gradient reach HBM (feat in, d_feat out).
+ *   d_feat f32 [B,Cf,H,W] = d_logits x weight   d_weight f32 [C,Cf] = d_logits^T x feat   d_bias f32 [C] or NULL = sum d_logits
+ *   (all OVERWRITTEN; d_logits is rounded to bf16 as the operand of the two contractions)   d_logits f32 [B,C,H,W] or NULL
+ * Requires, beyond ctdet_head_focal_fused: Cf % 128 == 0, Cf <= 256 and C + (Cf/128) C + Cf <= 512 (TMEM columns: C = 80,
+ * Cf = 256 uses 496). */
+int ctdet_head_focal_fused_bwd(const float* feat, const float* weight, const float* bias, const float* gt_hm,
+                               const float* alpha, const int32_t* num_pos_img, const float* norm_override,
+                               int B, int Cf, int C, int H, int W, int flags, float w_hm,
+                               float* loss, float* d_logits, float* d_feat, float* d_weight, float* d_bias,
+                               void* workspace, size_t workspace_bytes, ctdet_stream_t stream);
+
 /* d[i] *= *g for i < n, entirely skipped on the device when *g == 1 (autograd upstream gradient,
  * no host sync).  g: f32 device scalar. */
 int ctdet_scale_grad(float* d, size_t n, const float* g, ctdet_stream_t stream);

@@ -50,8 +50,11 @@ def _rel(a, b):
     return float((a - b).norm() / b.norm().clamp_min(1e-30)), float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
 
 
-@pytest.mark.parametrize("cfg", [(2, 256, 80, 32, 32), (1, 64, 16, 16, 8), (3, 128, 96, 24, 16)])
-def test_fused_head_loss_matches_conv_plus_reference_loss(cfg):
+@pytest.mark.parametrize("fuse_backward", [False, True])
+@pytest.mark.parametrize("cfg", [(2, 256, 80, 32, 32), (1, 64, 16, 16, 8), (3, 128, 96, 24, 16), (5, 256, 80, 64, 64)])
+def test_fused_head_loss_matches_conv_plus_reference_loss(cfg, fuse_backward):
+    """fuse_backward: the convolution's backward inside the kernel where the shapes allow it (cases 1, 3 and 4: the last
+    one runs several tiles per CTA), else d_logits + torch GEMMs."""
     from detectron2_centernet_b200 import losses as L
     B, Cf, C, H, W = cfg
     feat, w, b, tg = _setup(11 + Cf, B, Cf, C, H, W)
@@ -60,7 +63,7 @@ def test_fused_head_loss_matches_conv_plus_reference_loss(cfg):
     f = feat.clone().requires_grad_(True)
     ww = w.clone().requires_grad_(True)
     bb = b.clone().requires_grad_(True)
-    loss = L.hm_head_focal_loss(f, ww, bb, tg["hm"], alpha=alpha, num_pos=tg.get("num_pos"))
+    loss = L.hm_head_focal_loss(f, ww, bb, tg["hm"], alpha=alpha, num_pos=tg.get("num_pos"), fuse_backward=fuse_backward)
     loss.sum().backward()
     torch.cuda.synchronize()
     assert abs(float(loss) - float(want[0])) <= 2e-3 * abs(float(want[0])), (float(loss), float(want[0]))
@@ -73,6 +76,12 @@ def test_fused_head_loss_matches_conv_plus_reference_loss(cfg):
     l2, mx = _rel(d, want[1])
     assert l2 <= 2e-2 and mx <= 5e-2, (cfg, "d_logits", l2, mx)
     assert float(loss2) == float(loss)
+    if fuse_backward and L.head_bwd_fusable(Cf, C, H * W):           # the kernel's optional d_logits output
+        out = L._head_focal_bwd_call(feat, w, b, tg["hm"], L.alpha_tensor(alpha, C, feat.device), tg.get("num_pos"), None,
+                                     L.alpha_is_uniform(alpha), 1.0, want_d_logits=True)
+        assert torch.equal(out[4], d) and float(out[0]) == float(loss)
+        assert torch.equal(out[1], f.grad)
+        assert torch.allclose(out[3], bb.grad, rtol=1e-5, atol=1e-7)      # fp32 atomics: the order varies from run to run
 
 
 def test_fused_head_loss_equals_the_unfused_kernel_on_bf16_representable_operands():
