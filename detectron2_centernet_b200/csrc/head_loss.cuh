@@ -98,24 +98,35 @@ head_focal_fused_kernel(const float* __restrict__ feat, const float* __restrict_
   double acc = 0.0;                                          // this thread's share of the weighted focal loss
   if (warp < kHfProducerWarps) {
     // ===================================== producers ==============================================
+    // the loads of K block n + 1 are in flight while K block n is converted and stored (64 x 4 B per thread in flight)
     int s = 0; unsigned ph = 0;
     const uint32_t swz = (uint32_t)((warp ^ (lane & 7)) << 4);              // rows l + 32 j: row & 7 = lane & 7
-    for (int it = 0; it < my_tiles; ++it) {
+    const int total_kb = my_tiles * KB;
+    float v[2][8][4];
+    auto load_kb = [&](int n, float (&dst)[8][4]) {
+      const int it = n / KB, kb = n - it * KB;
       const int tile = tile_first + it;
       const int b = tile / tiles_per_image, p0 = (tile - b * tiles_per_image) * kTileM;
-      const float* src = feat + ((size_t)b * Cf + warp * 8) * P + p0 + lane;
-      for (int kb = 0; kb < KB; ++kb) {
-        float v[8][4];
+      const float* src = feat + ((size_t)b * Cf + kb * kBK + warp * 8) * P + p0 + lane;
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
+      for (int i = 0; i < 8; ++i)
 #pragma unroll
-          for (int j = 0; j < 4; ++j) v[i][j] = ldg_stream1(src + ((size_t)kb * kBK + i) * P + 32 * j);
+        for (int j = 0; j < 4; ++j) dst[i][j] = ldg_stream1(src + (size_t)i * P + 32 * j);
+    };
+    if (total_kb > 0) load_kb(0, v[0]);
+#pragma unroll 1
+    for (int n2 = 0; n2 < total_kb; n2 += 2) {
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int n = n2 + u;
+        if (n >= total_kb) break;
+        if (n + 1 < total_kb) load_kb(n + 1, v[u ^ 1]);
         dcn_mbar_wait(&bars.empty[s], ph ^ 1u);
         uint8_t* a_tile = ring + (size_t)s * (kTileM * 128);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          const __nv_bfloat162 q0 = __floats2bfloat162_rn(v[0][j], v[1][j]), q1 = __floats2bfloat162_rn(v[2][j], v[3][j]);
-          const __nv_bfloat162 q2 = __floats2bfloat162_rn(v[4][j], v[5][j]), q3 = __floats2bfloat162_rn(v[6][j], v[7][j]);
+          const __nv_bfloat162 q0 = __floats2bfloat162_rn(v[u][0][j], v[u][1][j]), q1 = __floats2bfloat162_rn(v[u][2][j], v[u][3][j]);
+          const __nv_bfloat162 q2 = __floats2bfloat162_rn(v[u][4][j], v[u][5][j]), q3 = __floats2bfloat162_rn(v[u][6][j], v[u][7][j]);
           *reinterpret_cast<uint4*>(a_tile + (uint32_t)(lane + 32 * j) * 128u + swz) =
               make_uint4(*reinterpret_cast<const uint32_t*>(&q0), *reinterpret_cast<const uint32_t*>(&q1),
                          *reinterpret_cast<const uint32_t*>(&q2), *reinterpret_cast<const uint32_t*>(&q3));
@@ -140,24 +151,34 @@ head_focal_fused_kernel(const float* __restrict__ feat, const float* __restrict_
       const int ab = it & 1;
       const float* g_src = gt + ((size_t)b * C + c_lo) * P + p;
       float* d_dst = d_logits ? d_logits + ((size_t)b * C + c_lo) * P + p : nullptr;
+      // gt does not depend on the logits: the first group's loads are issued before the accumulator is waited for,
+      // group g + 1's while group g is computed
+      float g[2][8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[0][k] = ldg_stream1(g_src + (size_t)k * P);
       dcn_mbar_wait(&bars.acc_full[ab], (unsigned)((it >> 1) & 1));
       tc_fence_after();
-      for (int c0 = 0; c0 < ch; c0 += 8) {
-        float g[8];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) g[k] = ldg_stream1(g_src + (size_t)(c0 + k) * P);
-        uint32_t v[8];
-        tmem_ld8(tmem + lane_base + (uint32_t)(ab * 128 + c_lo + c0), v);
+      for (int g8 = 0; g8 < 8; ++g8) {
+        const int c0 = g8 * 8;
+        if (c0 < ch) {
+          if (c0 + 8 < ch) {
 #pragma unroll
-        for (int k = 0; k < 8; k += 2) {
-          const int c = c_lo + c0 + k;
-          const pk2 d = cell2<false>(__uint_as_float(v[k]) + s_bias[c], __uint_as_float(v[k + 1]) + s_bias[c + 1], g[k], g[k + 1],
-                                     s_alpha[c], gscale, tot, tot_pos, s_alpha[c + 1]);
-          if (d_dst != nullptr) {
-            float d0, d1;
-            unpack2(d, d0, d1);
-            d_dst[(size_t)(c0 + k) * P] = d0;
-            d_dst[(size_t)(c0 + k + 1) * P] = d1;
+            for (int k = 0; k < 8; ++k) g[(g8 + 1) & 1][k] = ldg_stream1(g_src + (size_t)(c0 + 8 + k) * P);
+          }
+          uint32_t v[8];
+          tmem_ld8(tmem + lane_base + (uint32_t)(ab * 128 + c_lo + c0), v);
+#pragma unroll
+          for (int k = 0; k < 8; k += 2) {
+            const int c = c_lo + c0 + k;
+            const pk2 d = cell2<false>(__uint_as_float(v[k]) + s_bias[c], __uint_as_float(v[k + 1]) + s_bias[c + 1],
+                                       g[g8 & 1][k], g[g8 & 1][k + 1], s_alpha[c], gscale, tot, tot_pos, s_alpha[c + 1]);
+            if (d_dst != nullptr) {
+              float d0, d1;
+              unpack2(d, d0, d1);
+              d_dst[(size_t)(c0 + k) * P] = d0;
+              d_dst[(size_t)(c0 + k + 1) * P] = d1;
+            }
           }
         }
       }
@@ -297,24 +318,35 @@ head_focal_fused_bwd_kernel(const float* __restrict__ feat, const float* __restr
   double acc = 0.0;
   if (warp < kHfProducerWarps) {
     // ===================================== producers (as above) ====================================
+    // the loads of K block n + 1 are in flight while K block n is converted and stored (64 x 4 B per thread in flight)
     int s = 0; unsigned ph = 0;
-    const uint32_t swz = (uint32_t)((warp ^ (lane & 7)) << 4);
-    for (int it = 0; it < my_tiles; ++it) {
+    const uint32_t swz = (uint32_t)((warp ^ (lane & 7)) << 4);              // rows l + 32 j: row & 7 = lane & 7
+    const int total_kb = my_tiles * KB;
+    float v[2][8][4];
+    auto load_kb = [&](int n, float (&dst)[8][4]) {
+      const int it = n / KB, kb = n - it * KB;
       const int tile = tile_first + it;
       const int b = tile / tiles_per_image, p0 = (tile - b * tiles_per_image) * kTileM;
-      const float* src = feat + ((size_t)b * Cf + warp * 8) * P + p0 + lane;
-      for (int kb = 0; kb < KB; ++kb) {
-        float v[8][4];
+      const float* src = feat + ((size_t)b * Cf + kb * kBK + warp * 8) * P + p0 + lane;
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
+      for (int i = 0; i < 8; ++i)
 #pragma unroll
-          for (int j = 0; j < 4; ++j) v[i][j] = ldg_stream1(src + ((size_t)kb * kBK + i) * P + 32 * j);
+        for (int j = 0; j < 4; ++j) dst[i][j] = ldg_stream1(src + (size_t)i * P + 32 * j);
+    };
+    if (total_kb > 0) load_kb(0, v[0]);
+#pragma unroll 1
+    for (int n2 = 0; n2 < total_kb; n2 += 2) {
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int n = n2 + u;
+        if (n >= total_kb) break;
+        if (n + 1 < total_kb) load_kb(n + 1, v[u ^ 1]);
         dcn_mbar_wait(&bars.empty[s], ph ^ 1u);
         uint8_t* a_tile = ring + (size_t)s * (kTileM * 128);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          const __nv_bfloat162 q0 = __floats2bfloat162_rn(v[0][j], v[1][j]), q1 = __floats2bfloat162_rn(v[2][j], v[3][j]);
-          const __nv_bfloat162 q2 = __floats2bfloat162_rn(v[4][j], v[5][j]), q3 = __floats2bfloat162_rn(v[6][j], v[7][j]);
+          const __nv_bfloat162 q0 = __floats2bfloat162_rn(v[u][0][j], v[u][1][j]), q1 = __floats2bfloat162_rn(v[u][2][j], v[u][3][j]);
+          const __nv_bfloat162 q2 = __floats2bfloat162_rn(v[u][4][j], v[u][5][j]), q3 = __floats2bfloat162_rn(v[u][6][j], v[u][7][j]);
           *reinterpret_cast<uint4*>(a_tile + (uint32_t)(lane + 32 * j) * 128u + swz) =
               make_uint4(*reinterpret_cast<const uint32_t*>(&q0), *reinterpret_cast<const uint32_t*>(&q1),
                          *reinterpret_cast<const uint32_t*>(&q2), *reinterpret_cast<const uint32_t*>(&q3));
@@ -345,6 +377,9 @@ head_focal_fused_bwd_kernel(const float* __restrict__ feat, const float* __restr
       const unsigned par = (unsigned)(it & 1);
       const float* g_src = gt + ((size_t)b * C + c_lo) * P + p;
       float* d_dst = d_logits ? d_logits + ((size_t)b * C + c_lo) * P + p : nullptr;
+      float g[2][8];                                          // gt: group g + 1 in flight while group g is computed
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[0][k] = ldg_stream1(g_src + (size_t)k * P);
       dcn_mbar_wait(&bars.lg_full, par);
       tc_fence_after();
       dcn_mbar_wait(&bars.d_empty, par ^ 1u);                 // GEMM 2 / 3 of the previous tile are done with D
@@ -352,17 +387,18 @@ head_focal_fused_bwd_kernel(const float* __restrict__ feat, const float* __restr
       for (int g8 = 0; g8 < 8; ++g8) {
         const int c0 = g8 * 8;
         if (c0 < ch) {
-          float g[8];
+          if (c0 + 8 < ch) {
 #pragma unroll
-          for (int k = 0; k < 8; ++k) g[k] = ldg_stream1(g_src + (size_t)(c0 + k) * P);
+            for (int k = 0; k < 8; ++k) g[(g8 + 1) & 1][k] = ldg_stream1(g_src + (size_t)(c0 + 8 + k) * P);
+          }
           uint32_t v[8];
           tmem_ld8(tmem + lane_base + (uint32_t)(c_lo + c0), v);
           float dd[8];
 #pragma unroll
           for (int k = 0; k < 8; k += 2) {
             const int c = c_lo + c0 + k;
-            const pk2 d = cell2<false>(__uint_as_float(v[k]) + s_bias[c], __uint_as_float(v[k + 1]) + s_bias[c + 1], g[k], g[k + 1],
-                                       s_alpha[c], gscale, tot, tot_pos, s_alpha[c + 1]);
+            const pk2 d = cell2<false>(__uint_as_float(v[k]) + s_bias[c], __uint_as_float(v[k + 1]) + s_bias[c + 1],
+                                       g[g8 & 1][k], g[g8 & 1][k + 1], s_alpha[c], gscale, tot, tot_pos, s_alpha[c + 1]);
             unpack2(d, dd[k], dd[k + 1]);
             if (d_dst != nullptr) { d_dst[(size_t)(c0 + k) * P] = dd[k]; d_dst[(size_t)(c0 + k + 1) * P] = dd[k + 1]; }
           }
