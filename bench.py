@@ -166,6 +166,68 @@ def configs_3_4(dev, flush, peak):
     return out
 
 
+def fused_head_variant(dev, flush, peak, B):
+    """SURVEY.md section 8 f2, second half: the hm head's final 1x1 convolution (256 -> 80, centernet.py:118-123) fused with
+    the focal loss -- logits formed per 128-pixel tile on the tensor cores and consumed from TMEM -- and, in the second
+    kernel, with the convolution's backward (d_feat, d_weight, d_bias): neither the logits nor their gradient reach HBM.
+    A variant with its own algorithmic-bytes denominator (per pixel: feat 4*Cf [+ d_feat 4*Cf] + gt 4*C [+ d_logits 4*C]);
+    the unfused chain it replaces (cuDNN conv + ctdet_loss_fwd_bwd + cuDNN conv backward) is timed beside it."""
+    from detectron2_centernet_b200 import losses as L
+    from detectron2_centernet_b200 import target as T
+    Cf, S_ = 256, 128
+    g = torch.Generator(device=dev).manual_seed(1239)
+    feat = torch.relu(torch.randn((B, Cf, S_, S_), device=dev, generator=g))
+    w = torch.randn((C, Cf), device=dev, generator=g) / 16
+    w4 = w[:, :, None, None].contiguous()
+    bias = torch.full((C,), -2.19, device=dev)
+    bl, cl = S.make_batch_objects(1235, B, 512)
+    boxes, classes, offsets = S.pack_objects(bl, cl)
+    tg = T.target_gen(*[torch.from_numpy(a).to(dev) for a in (boxes, classes, offsets)], B, C, S_, S_)
+    a = L.alpha_tensor(None, C, dev)
+    px = B * S_ * S_
+
+    def unfused_fwd():
+        logits = torch.nn.functional.conv2d(feat, w4, bias)
+        return L._call(logits, None, None, tg["hm"], None, None, None, None, a, tg["num_pos"], None, L._FLAG_ALPHA_UNIFORM,
+                       (1.0, 0.1, 1.0), True)
+
+    def unfused_chain():
+        logits = torch.nn.functional.conv2d(feat, w4, bias)
+        _, d_hm, _, _ = L._call(logits, None, None, tg["hm"], None, None, None, None, a, tg["num_pos"], None,
+                                L._FLAG_ALPHA_UNIFORM, (1.0, 0.1, 1.0), True)
+        return torch.ops.aten.convolution_backward(d_hm, feat, w4, [C], [1, 1], [0, 0], [1, 1], False, [0, 0], 1,
+                                                   [True, True, True])      # what autograd runs for the reference's Conv2d
+
+    def timed(fn, reps=10):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        tot = 0.0
+        for _ in range(reps):
+            flush.zero_()
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record()
+            fn()
+            e.record()
+            torch.cuda.synchronize()
+            tot += s.elapsed_time(e)
+        return tot / reps * 1e3
+
+    us_f = timed(lambda: L._head_focal_call(feat, w, bias, tg["hm"], a, tg["num_pos"], None, True, 1.0, True))
+    us_fb = timed(lambda: L._head_focal_bwd_call(feat, w, bias, tg["hm"], a, tg["num_pos"], None, True, 1.0))
+    us_uf, us_uc = timed(unfused_fwd), timed(unfused_chain)
+    bpp_f, bpp_fb = 4 * Cf + 8 * C, 8 * Cf + 4 * C
+    return {"what": "hm head 1x1 conv (256->80) + focal loss in one tcgen05 kernel, batch %d @512^2; bf16 operands, fp32 accumulation" % B,
+            "fwd": {"us": round(us_f, 1), "bytes_per_pixel": bpp_f, "GBps": round(px * bpp_f / us_f / 1e3, 1),
+                    "frac": round(px * bpp_f / us_f / 1e3 / peak, 3), "images_per_s": round(B / us_f * 1e6),
+                    "outputs": "loss, d_logits", "unfused_us": round(us_uf, 1),
+                    "unfused": "cuDNN fp32 conv + ctdet_loss_fwd_bwd"},
+            "fwd_bwd": {"us": round(us_fb, 1), "bytes_per_pixel": bpp_fb, "GBps": round(px * bpp_fb / us_fb / 1e3, 1),
+                        "frac": round(px * bpp_fb / us_fb / 1e3 / peak, 3), "images_per_s": round(B / us_fb * 1e6),
+                        "outputs": "loss, d_feat, d_weight, d_bias", "unfused_us": round(us_uc, 1),
+                        "unfused": "cuDNN fp32 conv + ctdet_loss_fwd_bwd + aten convolution_backward (cuDNN)"}}
+
+
 def config5(dev, rank, world, images=512, micro=32, reps=2):
     """BASELINE.json configs[4]: DLA-34 IDAUp/DLAUp neck (16 DCNv2 on the tcgen05 kernels, random offsets) + ctdet head
     + top-100 decode, eval, `images` images sharded BY IMAGE over the ranks in micro-batches of 32, synthetic
@@ -630,6 +692,7 @@ def run_ours(args):
         out["dcn_stack"] = dcn_stack(dev, B)
     if not args.no_configs:
         out["configs"] = configs_3_4(dev, flush, peak)
+        out["fused_head_variant"] = fused_head_variant(dev, flush, peak, B)
         out["configs"]["config5"] = cfg5
         out["configs"]["config2"] = {"workload": "this line's step without the decode: target-gen + fused loss fwd+bwd, B=32",
                                      "us": round(per_kernel["target_gen"]["us"] + per_kernel["loss"]["us"], 1),
