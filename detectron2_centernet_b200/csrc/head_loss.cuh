@@ -283,7 +283,7 @@ head_focal_fused_bwd_kernel(const float* __restrict__ feat, const float* __restr
     for (int s = 0; s < kHfMaxStages; ++s) { dcn_mbar_init(&bars.full[s], kHfProducerWarps); dcn_mbar_init(&bars.empty[s], 1); }
     dcn_mbar_init(&bars.lg_full, 1);   dcn_mbar_init(&bars.lg_empty, kHfEpiWarps);
     dcn_mbar_init(&bars.d_full, kHfEpiWarps);  dcn_mbar_init(&bars.d_empty, 1);
-    dcn_mbar_init(&bars.df_full, 1);   dcn_mbar_init(&bars.df_empty, kHfEpiWarps);
+    dcn_mbar_init(&bars.df_full, 1);   dcn_mbar_init(&bars.df_empty, kHfProducerWarps);
     dcn_mbar_init(&bars.dw_full, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     float npos = 0.f;
@@ -317,51 +317,76 @@ head_focal_fused_bwd_kernel(const float* __restrict__ feat, const float* __restr
 
   double acc = 0.0;
   if (warp < kHfProducerWarps) {
-    // ===================================== producers (as above) ====================================
-    // the loads of K block n + 1 are in flight while K block n is converted and stored (64 x 4 B per thread in flight)
+    // ===================================== producers + epilogue 2 ==================================
+    // Fill the ring with the next tile (the loads of K block kb + 1 in flight while kb is converted and stored), then
+    // drain d_feat of the PREVIOUS tile from TMEM (any warp reads the TMEM lane quarter warp & 3): by the time GEMM 2 of
+    // that tile has run, its GEMM 3 is about to free the ring slots this warp would otherwise be waiting for.
     int s = 0; unsigned ph = 0;
     const uint32_t swz = (uint32_t)((warp ^ (lane & 7)) << 4);              // rows l + 32 j: row & 7 = lane & 7
-    const int total_kb = my_tiles * KB;
-    float v[2][8][4];
-    auto load_kb = [&](int n, float (&dst)[8][4]) {
-      const int it = n / KB, kb = n - it * KB;
+    const int quarter = warp & 3, fh = Cf / 2, f_lo = (warp >> 2) * fh;     // epilogue 2: this warp's pixels and channels
+    const uint32_t lane_base = (uint32_t)(quarter * 32) << 16;
+    auto drain = [&](int itd) {
+      const int tile = tile_first + itd;
+      const int b = tile / tiles_per_image, p = (tile - b * tiles_per_image) * kTileM + quarter * 32 + lane;
+      float* fq = d_feat + ((size_t)b * Cf + f_lo) * P + p;
+      dcn_mbar_wait(&bars.df_full, (unsigned)(itd & 1));
+      tc_fence_after();
+#pragma unroll 1
+      for (int c0 = 0; c0 < fh; c0 += 16) {
+        uint32_t w[16];
+        tmem_ld16(tmem + lane_base + col_df + (uint32_t)(f_lo + c0), w);
+#pragma unroll
+        for (int k = 0; k < 16; ++k) { *fq = __uint_as_float(w[k]); fq += P; }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) dcn_mbar_arrive(&bars.df_empty);
+    };
+    for (int it = 0; it < my_tiles; ++it) {
       const int tile = tile_first + it;
       const int b = tile / tiles_per_image, p0 = (tile - b * tiles_per_image) * kTileM;
-      const float* src = feat + ((size_t)b * Cf + kb * kBK + warp * 8) * P + p0 + lane;
+      const float* src = feat + ((size_t)b * Cf + warp * 8) * P + p0 + lane;
+      float v[2][8][4];
+      auto load_kb = [&](int kb, float (&dst)[8][4]) {
+        const float* q = src + (size_t)kb * kBK * P;
 #pragma unroll
-      for (int i = 0; i < 8; ++i)
+        for (int i = 0; i < 8; ++i) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) dst[i][j] = ldg_stream1(src + (size_t)i * P + 32 * j);
-    };
-    if (total_kb > 0) load_kb(0, v[0]);
-#pragma unroll 1
-    for (int n2 = 0; n2 < total_kb; n2 += 2) {
-#pragma unroll
-      for (int u = 0; u < 2; ++u) {
-        const int n = n2 + u;
-        if (n >= total_kb) break;
-        if (n + 1 < total_kb) load_kb(n + 1, v[u ^ 1]);
-        dcn_mbar_wait(&bars.empty[s], ph ^ 1u);
-        uint8_t* a_tile = ring + (size_t)s * (kTileM * 128);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const __nv_bfloat162 q0 = __floats2bfloat162_rn(v[u][0][j], v[u][1][j]), q1 = __floats2bfloat162_rn(v[u][2][j], v[u][3][j]);
-          const __nv_bfloat162 q2 = __floats2bfloat162_rn(v[u][4][j], v[u][5][j]), q3 = __floats2bfloat162_rn(v[u][6][j], v[u][7][j]);
-          *reinterpret_cast<uint4*>(a_tile + (uint32_t)(lane + 32 * j) * 128u + swz) =
-              make_uint4(*reinterpret_cast<const uint32_t*>(&q0), *reinterpret_cast<const uint32_t*>(&q1),
-                         *reinterpret_cast<const uint32_t*>(&q2), *reinterpret_cast<const uint32_t*>(&q3));
+          for (int j = 0; j < 4; ++j) dst[i][j] = ldg_stream1(q + 32 * j);
+          q += P;
         }
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        __syncwarp();
-        if (lane == 0) dcn_mbar_arrive(&bars.full[s]);
-        if (++s == NS) { s = 0; ph ^= 1u; }
+      };
+      load_kb(0, v[0]);
+#pragma unroll 1
+      for (int kb2 = 0; kb2 < KB; kb2 += 2) {
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          const int kb = kb2 + u;
+          if (kb >= KB) break;
+          if (kb + 1 < KB) load_kb(kb + 1, v[u ^ 1]);
+          dcn_mbar_wait(&bars.empty[s], ph ^ 1u);
+          uint8_t* a_tile = ring + (size_t)s * (kTileM * 128);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const __nv_bfloat162 q0 = __floats2bfloat162_rn(v[u][0][j], v[u][1][j]), q1 = __floats2bfloat162_rn(v[u][2][j], v[u][3][j]);
+            const __nv_bfloat162 q2 = __floats2bfloat162_rn(v[u][4][j], v[u][5][j]), q3 = __floats2bfloat162_rn(v[u][6][j], v[u][7][j]);
+            *reinterpret_cast<uint4*>(a_tile + (uint32_t)(lane + 32 * j) * 128u + swz) =
+                make_uint4(*reinterpret_cast<const uint32_t*>(&q0), *reinterpret_cast<const uint32_t*>(&q1),
+                           *reinterpret_cast<const uint32_t*>(&q2), *reinterpret_cast<const uint32_t*>(&q3));
+          }
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          __syncwarp();
+          if (lane == 0) dcn_mbar_arrive(&bars.full[s]);
+          if (++s == NS) { s = 0; ph ^= 1u; }
+        }
       }
+      if (it >= 1) drain(it - 1);
     }
+    if (my_tiles > 0) drain(my_tiles - 1);
   } else if (warp < kHfProducerWarps + kHfEpiWarps) {
     // ===================================== epilogues ===============================================
     const int quarter = warp & 3, half = (warp - kHfProducerWarps) >> 2;
     const int ch = C / 2, c_lo = half * ch;
-    const int fh = Cf / 2, f_lo = half * fh;                  // this warp's feature channels in epilogue 2
     const int r = quarter * 32 + lane;                        // row of the tile = TMEM lane
     const uint32_t lane_base = (uint32_t)(quarter * 32) << 16;
     const float gscale = s_gscale;
@@ -427,19 +452,6 @@ head_focal_fused_bwd_kernel(const float* __restrict__ feat, const float* __restr
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       __syncwarp();
       if (lane == 0) { dcn_mbar_arrive(&bars.lg_empty); dcn_mbar_arrive(&bars.d_full); }
-      // ---- epilogue 2: d_feat[pixel, f_lo .. f_lo + Cf/2) -> NCHW fp32 ----
-      float* f_dst = d_feat + ((size_t)b * Cf + f_lo) * P + p;
-      dcn_mbar_wait(&bars.df_full, par);
-      tc_fence_after();
-      for (int c0 = 0; c0 < fh; c0 += 16) {
-        uint32_t v[16];
-        tmem_ld16(tmem + lane_base + col_df + (uint32_t)(f_lo + c0), v);
-#pragma unroll
-        for (int k = 0; k < 16; ++k) f_dst[(size_t)(c0 + k) * P] = __uint_as_float(v[k]);
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) dcn_mbar_arrive(&bars.df_empty);
     }
     float t0, t1;
     unpack2(tot, t0, t1);
