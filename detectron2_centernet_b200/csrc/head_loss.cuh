@@ -56,7 +56,7 @@ head_focal_fused_kernel(const float* __restrict__ feat, const float* __restrict_
   uint8_t* wsm = ring + (size_t)NS * (kTileM * 128);        // [KB][C rows][128 B]  W^T, K-major over the channels
   float* s_bias = reinterpret_cast<float*>(wsm + (size_t)KB * C * 128);   // [C]
   float* s_alpha = s_bias + C;                              // [C]
-  const int tiles_per_image = P / kTileM;
+  const int tiles_per_image = (P + kTileM - 1) / kTileM;      // the last tile of an image may be ragged
   const int num_tiles = B * tiles_per_image;
   const int tile_first = (int)(((long long)blockIdx.x * num_tiles) / gridDim.x);
   const int my_tiles = (int)(((long long)(blockIdx.x + 1) * num_tiles) / gridDim.x) - tile_first;
@@ -108,10 +108,17 @@ head_focal_fused_kernel(const float* __restrict__ feat, const float* __restrict_
       const int tile = tile_first + it;
       const int b = tile / tiles_per_image, p0 = (tile - b * tiles_per_image) * kTileM;
       const float* src = feat + ((size_t)b * Cf + kb * kBK + warp * 8) * P + p0 + lane;
+      if (p0 + kTileM <= P) {
 #pragma unroll
-      for (int i = 0; i < 8; ++i)
+        for (int i = 0; i < 8; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) dst[i][j] = ldg_stream1(src + (size_t)i * P + 32 * j);
+          for (int j = 0; j < 4; ++j) dst[i][j] = ldg_stream1(src + (size_t)i * P + 32 * j);
+      } else {                                   // ragged tile: rows past the image are zero
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) dst[i][j] = (p0 + lane + 32 * j < P) ? ldg_stream1(src + (size_t)i * P + 32 * j) : 0.f;
+      }
     };
     if (total_kb > 0) load_kb(0, v[0]);
 #pragma unroll 1
@@ -142,15 +149,17 @@ head_focal_fused_kernel(const float* __restrict__ feat, const float* __restrict_
     const int quarter = warp & 3, half = (warp - kHfProducerWarps) >> 2;
     const int ch = C / 2, c_lo = half * ch;                  // this warp's classes
     const uint32_t lane_base = (uint32_t)(quarter * 32) << 16;
-    const float gscale = s_gscale;
+    const float gscale_all = s_gscale;
     pk2 tot = pack2(0.f, 0.f);
     float tot_pos = 0.f;
     for (int it = 0; it < my_tiles; ++it) {
       const int tile = tile_first + it;
       const int b = tile / tiles_per_image, p = (tile - b * tiles_per_image) * kTileM + quarter * 32 + lane;
       const int ab = it & 1;
-      const float* g_src = gt + ((size_t)b * C + c_lo) * P + p;
-      float* d_dst = d_logits ? d_logits + ((size_t)b * C + c_lo) * P + p : nullptr;
+      const bool valid = p < P;                  // ragged tile: the pixel contributes nothing (coefficient 0) and is not stored
+      const float gscale = valid ? gscale_all : 0.f;
+      const float* g_src = gt + ((size_t)b * C + c_lo) * P + (valid ? p : 0);
+      float* d_dst = (d_logits && valid) ? d_logits + ((size_t)b * C + c_lo) * P + p : nullptr;
       // gt does not depend on the logits: the first group's loads are issued before the accumulator is waited for,
       // group g + 1's while group g is computed
       float g[2][8];
@@ -273,7 +282,7 @@ head_focal_fused_bwd_kernel(const float* __restrict__ feat, const float* __restr
   uint8_t* wsm = dtile + 2 * (kTileM * 128);                // [KB][C rows][128 B]
   float* s_bias = reinterpret_cast<float*>(wsm + (size_t)KB * C * 128);
   float* s_alpha = s_bias + C;
-  const int tiles_per_image = P / kTileM;
+  const int tiles_per_image = (P + kTileM - 1) / kTileM;      // the last tile of an image may be ragged
   const int num_tiles = B * tiles_per_image;
   const int tile_first = (int)(((long long)blockIdx.x * num_tiles) / gridDim.x);
   const int my_tiles = (int)(((long long)(blockIdx.x + 1) * num_tiles) / gridDim.x) - tile_first;
@@ -328,7 +337,8 @@ head_focal_fused_bwd_kernel(const float* __restrict__ feat, const float* __restr
     auto drain = [&](int itd) {
       const int tile = tile_first + itd;
       const int b = tile / tiles_per_image, p = (tile - b * tiles_per_image) * kTileM + quarter * 32 + lane;
-      float* fq = d_feat + ((size_t)b * Cf + f_lo) * P + p;
+      const bool valid = p < P;
+      float* fq = d_feat + ((size_t)b * Cf + f_lo) * P + (valid ? p : 0);
       dcn_mbar_wait(&bars.df_full, (unsigned)(itd & 1));
       tc_fence_after();
 #pragma unroll 1
@@ -336,7 +346,7 @@ head_focal_fused_bwd_kernel(const float* __restrict__ feat, const float* __restr
         uint32_t w[16];
         tmem_ld16(tmem + lane_base + col_df + (uint32_t)(f_lo + c0), w);
 #pragma unroll
-        for (int k = 0; k < 16; ++k) { *fq = __uint_as_float(w[k]); fq += P; }
+        for (int k = 0; k < 16; ++k) { if (valid) *fq = __uint_as_float(w[k]); fq += P; }
       }
       tc_fence_before();
       __syncwarp();
@@ -349,11 +359,20 @@ head_focal_fused_bwd_kernel(const float* __restrict__ feat, const float* __restr
       float v[2][8][4];
       auto load_kb = [&](int kb, float (&dst)[8][4]) {
         const float* q = src + (size_t)kb * kBK * P;
+        if (p0 + kTileM <= P) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
+          for (int i = 0; i < 8; ++i) {
 #pragma unroll
-          for (int j = 0; j < 4; ++j) dst[i][j] = ldg_stream1(q + 32 * j);
-          q += P;
+            for (int j = 0; j < 4; ++j) dst[i][j] = ldg_stream1(q + 32 * j);
+            q += P;
+          }
+        } else {                                 // ragged tile: rows past the image are zero
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) dst[i][j] = (p0 + lane + 32 * j < P) ? ldg_stream1(q + 32 * j) : 0.f;
+            q += P;
+          }
         }
       };
       load_kb(0, v[0]);
@@ -389,7 +408,7 @@ head_focal_fused_bwd_kernel(const float* __restrict__ feat, const float* __restr
     const int ch = C / 2, c_lo = half * ch;
     const int r = quarter * 32 + lane;                        // row of the tile = TMEM lane
     const uint32_t lane_base = (uint32_t)(quarter * 32) << 16;
-    const float gscale = s_gscale;
+    const float gscale_all = s_gscale;
     const bool b4 = (lane & 4) != 0, b2 = (lane & 2) != 0, b1 = (lane & 1) != 0;
     pk2 tot = pack2(0.f, 0.f);
     float tot_pos = 0.f;
@@ -400,8 +419,10 @@ head_focal_fused_bwd_kernel(const float* __restrict__ feat, const float* __restr
       const int tile = tile_first + it;
       const int b = tile / tiles_per_image, p = (tile - b * tiles_per_image) * kTileM + r;
       const unsigned par = (unsigned)(it & 1);
-      const float* g_src = gt + ((size_t)b * C + c_lo) * P + p;
-      float* d_dst = d_logits ? d_logits + ((size_t)b * C + c_lo) * P + p : nullptr;
+      const bool valid = p < P;                  // ragged tile: coefficient 0 (no loss, zero row of D), nothing stored
+      const float gscale = valid ? gscale_all : 0.f;
+      const float* g_src = gt + ((size_t)b * C + c_lo) * P + (valid ? p : 0);
+      float* d_dst = (d_logits && valid) ? d_logits + ((size_t)b * C + c_lo) * P + p : nullptr;
       float g[2][8];                                          // gt: group g + 1 in flight while group g is computed
 #pragma unroll
       for (int k = 0; k < 8; ++k) g[0][k] = ldg_stream1(g_src + (size_t)k * P);

@@ -695,8 +695,8 @@ extern "C" int ctdet_head_focal_fused(const float* feat, const float* weight, co
   if (!aligned16(weight)) return CTDET_EALIGN;
   const int64_t P = (int64_t)H * W;
   // tensor-core tiling: K blocks of 64 channels, UMMA N = C, tiles of 128 pixels inside one image
-  if (Cf % kBK != 0 || C % 16 != 0 || C > 128 || P % kTileM != 0) return CTDET_EUNSUPPORTED;
-  if ((int64_t)B * C * P >= ((int64_t)1 << 33) || P >= ((int64_t)1 << 30) || (int64_t)B * (P / kTileM) > 0x7fffffffLL) return CTDET_EINVAL;
+  if (Cf % kBK != 0 || C % 16 != 0 || C > 128) return CTDET_EUNSUPPORTED;
+  if ((int64_t)B * C * P >= ((int64_t)1 << 33) || P >= ((int64_t)1 << 30) || (int64_t)B * ((P + kTileM - 1) / kTileM) > 0x7fffffffLL) return CTDET_EINVAL;
   cudaStream_t st = (cudaStream_t)stream;
   LossWs* ws = reinterpret_cast<LossWs*>(workspace);
   if (num_pos_img == nullptr && norm_override == nullptr) {
@@ -713,7 +713,7 @@ extern "C" int ctdet_head_focal_fused(const float* feat, const float* weight, co
   const size_t smem = 1024 + (size_t)stages * kTileM * 128 + w_bytes;
   cudaError_t e = cudaFuncSetAttribute(head_focal_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
-  const long long tiles = (long long)B * (P / kTileM);
+  const long long tiles = (long long)B * ((P + kTileM - 1) / kTileM);
   const unsigned grid = (unsigned)(tiles < kNumSMs ? tiles : kNumSMs);
   head_focal_fused_kernel<<<grid, kHfThreads, smem, st>>>(feat, weight, bias, gt_hm, alpha, num_pos_img, norm_override,
                                                           B, Cf, C, (int)P, flags, stages, w_hm, loss, d_logits, ws);
@@ -735,9 +735,9 @@ extern "C" int ctdet_head_focal_fused_bwd(const float* feat, const float* weight
   if (!aligned16(weight)) return CTDET_EALIGN;
   const int64_t P = (int64_t)H * W;
   // tiling as ctdet_head_focal_fused, plus: dW^T tiles of 128 channels, and logits + dW^T + d_feat must fit 512 TMEM columns
-  if (Cf % kTileM != 0 || Cf > 256 || C % 16 != 0 || C > 128 || P % kTileM != 0) return CTDET_EUNSUPPORTED;
+  if (Cf % kTileM != 0 || Cf > 256 || C % 16 != 0 || C > 128) return CTDET_EUNSUPPORTED;
   if (C + (Cf / kTileM) * C + Cf > 512) return CTDET_EUNSUPPORTED;
-  if ((int64_t)B * C * P >= ((int64_t)1 << 33) || P >= ((int64_t)1 << 30) || (int64_t)B * (P / kTileM) > 0x7fffffffLL) return CTDET_EINVAL;
+  if ((int64_t)B * C * P >= ((int64_t)1 << 33) || P >= ((int64_t)1 << 30) || (int64_t)B * ((P + kTileM - 1) / kTileM) > 0x7fffffffLL) return CTDET_EINVAL;
   cudaStream_t st = (cudaStream_t)stream;
   LossWs* ws = reinterpret_cast<LossWs*>(workspace);
   cudaError_t e = cudaMemsetAsync(d_weight, 0, (size_t)C * Cf * sizeof(float), st);
@@ -759,7 +759,7 @@ extern "C" int ctdet_head_focal_fused_bwd(const float* feat, const float* weight
   const size_t smem = fixed + (size_t)stages * kTileM * 128;
   e = cudaFuncSetAttribute(head_focal_fused_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
-  const long long tiles = (long long)B * (P / kTileM);
+  const long long tiles = (long long)B * ((P + kTileM - 1) / kTileM);
   const unsigned grid = (unsigned)(tiles < kNumSMs ? tiles : kNumSMs);
   head_focal_fused_bwd_kernel<<<grid, kHfThreads, smem, st>>>(feat, weight, bias, gt_hm, alpha, num_pos_img, norm_override,
                                                               B, Cf, C, (int)P, flags, stages, w_hm, loss, d_logits, d_feat,

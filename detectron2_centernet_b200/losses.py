@@ -303,7 +303,7 @@ def _head_focal_bwd_call(feat, weight, bias, gt_hm, alpha, num_pos, norm, unifor
 
 def head_bwd_fusable(Cf, C, HW):
     """Shapes `ctdet_head_focal_fused_bwd` tiles (TMEM: logits + dW^T + d_feat <= 512 columns)."""
-    return Cf % 128 == 0 and Cf <= 256 and C % 16 == 0 and C + (Cf // 128) * C + Cf <= 512 and HW % 128 == 0
+    return Cf % 128 == 0 and Cf <= 256 and C % 16 == 0 and C + (Cf // 128) * C + Cf <= 512
 
 
 class _HeadFocalFused(torch.autograd.Function):

@@ -138,7 +138,7 @@ int ctdet_target_loss_fused(const float* boxes, const int64_t* classes, const in
  *   bias f32 [C] or NULL   gt_hm f32 [B,C,H,W]   alpha / num_pos_img / norm_override / w_hm as in ctdet_loss_fwd_bwd
  *   loss f32 [1] = hm_loss * w_hm   d_logits f32 [B,C,H,W] or NULL: d(loss)/d(logits) -- the grad_output of the
  *   convolution's own backward (grad_input, grad_weight, grad_bias stay with the caller's Conv2d).
- * Requires Cf % 64 == 0, C % 16 == 0, C <= 128, H*W % 128 == 0; weight 16-byte aligned.
+ * Requires Cf % 64 == 0, C % 16 == 0, C <= 128; weight 16-byte aligned (tiles of 128 pixels, the last one of an image may be ragged).
  * workspace: ctdet_loss_workspace_bytes() bytes, the ctdet_loss_fwd_bwd contract (zero on entry, left zero). */
 int ctdet_head_focal_fused(const float* feat, const float* weight, const float* bias, const float* gt_hm,
                            const float* alpha, const int32_t* num_pos_img, const float* norm_override,

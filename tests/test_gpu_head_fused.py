@@ -51,10 +51,12 @@ def _rel(a, b):
 
 
 @pytest.mark.parametrize("fuse_backward", [False, True])
-@pytest.mark.parametrize("cfg", [(2, 256, 80, 32, 32), (1, 64, 16, 16, 8), (3, 128, 96, 24, 16), (5, 256, 80, 64, 64)])
+@pytest.mark.parametrize("cfg", [(2, 256, 80, 32, 32), (1, 64, 16, 16, 8), (3, 128, 96, 24, 16), (5, 256, 80, 64, 64), (3, 256, 80, 13, 11),
+                                 (2, 128, 32, 26, 26)])
 def test_fused_head_loss_matches_conv_plus_reference_loss(cfg, fuse_backward):
     """fuse_backward: the convolution's backward inside the kernel where the shapes allow it (cases 1, 3 and 4: the last
-    one runs several tiles per CTA), else d_logits + torch GEMMs."""
+    one runs several tiles per CTA), else d_logits + torch GEMMs.  The last two shapes have H*W % 128 != 0: the last tile of
+    every image is ragged (143 = 128 + 15 pixels; 676 = 5 x 128 + 36 -- what a 416^2 input gives at stride 4 is 104^2 = 84.5 tiles)."""
     from detectron2_centernet_b200 import losses as L
     B, Cf, C, H, W = cfg
     feat, w, b, tg = _setup(11 + Cf, B, Cf, C, H, W)
@@ -104,9 +106,9 @@ def test_fused_head_loss_equals_the_unfused_kernel_on_bf16_representable_operand
 
 def test_fused_head_loss_rejects_what_it_does_not_tile():
     from detectron2_centernet_b200 import losses as L
-    feat = torch.zeros(1, 64, 10, 10, device=DEV)                           # H*W % 128 != 0
-    with pytest.raises(NotImplementedError):
-        L.hm_head_focal_loss(feat, torch.zeros(16, 64, device=DEV), None, torch.zeros(1, 16, 10, 10, device=DEV))
+    with pytest.raises(NotImplementedError):                                 # C % 16 != 0
+        L.hm_head_focal_loss(torch.zeros(1, 64, 16, 8, device=DEV), torch.zeros(20, 64, device=DEV), None,
+                             torch.zeros(1, 20, 16, 8, device=DEV))
     with pytest.raises(NotImplementedError):                                 # 3x3 kernel
         L.hm_head_focal_loss(torch.zeros(1, 64, 16, 8, device=DEV), torch.zeros(16, 64, 3, 3, device=DEV), None,
                              torch.zeros(1, 16, 16, 8, device=DEV))
