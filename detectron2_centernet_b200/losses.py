@@ -367,3 +367,25 @@ def hm_head_focal_loss(feat, weight, bias, gt_hm, alpha=None, num_pos=None, norm
         raise RuntimeError("gt_hm must be [%d,%d,%d,%d]" % (feat.shape[0], C, feat.shape[2], feat.shape[3]))
     a = alpha_tensor(alpha, C, feat.device)
     return _HeadFocalFused.apply(feat, weight, bias, gt_hm, a, num_pos, norm, alpha_is_uniform(alpha), w_hm, fuse_backward)
+
+
+def ctdet_losses_fused_head(feat, weight, bias, outputs, targets, alpha=None, weights=(1.0, 0.1, 1.0), norm=None,
+                            fuse_backward=True):
+    """CenterNet.losses (centernet.py:191-212) with the 'hm' branch's final 1x1 convolution folded in: `feat` is the
+    input of that convolution (the ReLU output of centernet.py:118-123), `weight` / `bias` its parameters, and
+    `outputs` holds only 'wh' and 'reg'.  hm_loss comes from hm_head_focal_loss (the logits never reach HBM), wh_loss /
+    off_loss from the RegL1 sections of ctdet_loss_fwd_bwd (hm == NULL).  Returns the reference's dict; as with
+    ctdet_losses, sum the three before calling backward once."""
+    if "hm" in outputs and outputs["hm"] is not None:
+        raise RuntimeError("ctdet_losses_fused_head forms the hm logits itself: pass the head's input as `feat`, not "
+                           "outputs['hm'] (use ctdet_losses for materialised logits)")
+    wh = _prep(outputs["wh"], "ctdet losses")
+    reg = _prep(outputs["reg"], "ctdet losses")
+    num_pos = targets.get("num_pos")
+    hm_loss = hm_head_focal_loss(feat, weight, bias, targets["hm"], alpha=alpha, num_pos=num_pos, norm=norm,
+                                 w_hm=float(weights[0]), fuse_backward=fuse_backward)
+    a = alpha_tensor(alpha, 1, wh.device)
+    out = _FusedLoss.apply(None, wh, reg, None, targets["reg_mask"].contiguous(), targets["ind"].contiguous(),
+                           _prep(targets["wh"], "gt wh"), _prep(targets["reg"], "gt reg"), a, num_pos, norm, 0,
+                           (0.0, float(weights[1]), float(weights[2])))
+    return {"hm_loss": hm_loss.reshape(()), "wh_loss": out[1], "off_loss": out[2]}

@@ -112,3 +112,34 @@ def test_fused_head_loss_rejects_what_it_does_not_tile():
     with pytest.raises(NotImplementedError):                                 # 3x3 kernel
         L.hm_head_focal_loss(torch.zeros(1, 64, 16, 8, device=DEV), torch.zeros(16, 64, 3, 3, device=DEV), None,
                              torch.zeros(1, 16, 16, 8, device=DEV))
+
+
+def test_losses_dict_with_the_fused_head_equals_ctdet_losses_on_materialised_logits():
+    """`ctdet_losses_fused_head` (CenterNet.losses, centernet.py:191-212, with the hm branch's last convolution folded in):
+    wh_loss / off_loss and their gradients are the same kernel's -> bit-exact; hm_loss within the bf16 tolerance above."""
+    from detectron2_centernet_b200 import losses as L
+    B, Cf, C, H, W = 3, 256, 80, 32, 32
+    feat, w, b, tg = _setup(77, B, Cf, C, H, W)
+    g = torch.Generator(device="cpu").manual_seed(5)
+    wh0 = (torch.randn(B, 2, H, W, generator=g) * 4).to(DEV)
+    reg0 = torch.rand(B, 2, H, W, generator=g).to(DEV)
+
+    def leaves():
+        return [t.clone().requires_grad_(True) for t in (feat, w, b, wh0, reg0)]
+
+    f1, w1, b1, wh1, reg1 = leaves()
+    logits = torch.nn.functional.conv2d(f1, w1[:, :, None, None], b1)
+    want = L.ctdet_losses({"hm": logits, "wh": wh1, "reg": reg1}, tg)
+    sum(want.values()).backward()
+    f2, w2, b2, wh2, reg2 = leaves()
+    got = L.ctdet_losses_fused_head(f2, w2, b2, {"wh": wh2, "reg": reg2}, tg)
+    sum(got.values()).backward()
+    torch.cuda.synchronize()
+    assert set(got) == {"hm_loss", "wh_loss", "off_loss"}
+    assert float(got["wh_loss"]) == float(want["wh_loss"]) and float(got["off_loss"]) == float(want["off_loss"])
+    assert torch.equal(wh2.grad, wh1.grad) and torch.equal(reg2.grad, reg1.grad)
+    assert abs(float(got["hm_loss"]) - float(want["hm_loss"])) <= 2e-3 * abs(float(want["hm_loss"]))
+    for name, a, r in (("feat", f2.grad, f1.grad), ("weight", w2.grad, w1.grad), ("bias", b2.grad, b1.grad)):
+        assert _rel(a, r)[0] <= 2e-2, name
+    with pytest.raises(RuntimeError, match="forms the hm logits itself"):
+        L.ctdet_losses_fused_head(f2, w2, b2, {"hm": logits.detach(), "wh": wh2, "reg": reg2}, tg)
