@@ -39,6 +39,9 @@ SIGNATURES = {
                      [c_void_p, c_size_t, c_void_p]),
     "ctdet_decode_static_max_bytes": (c_size_t, []),
     "ctdet_decode_static": (c_int, [c_void_p] * 3 + [c_int] * 5 + [c_float, c_int] + [c_void_p] * 4 + [c_void_p]),
+    "ctdet_head_decode_fused_workspace_bytes": (c_size_t, [c_int] * 6),
+    "ctdet_head_decode_fused": (c_int, [c_void_p] * 5 + [c_int] * 6 + [c_float, c_int] + [c_void_p] * 5 +
+                                [c_void_p, c_size_t, c_void_p]),
     "ctdet_nms": (c_int, [c_void_p] + [c_int] * 4 + [c_void_p, c_void_p]),
     "ctdet_gather_feat": (c_int, [c_void_p] * 2 + [c_int] * 4 + [c_void_p, c_void_p]),
     "ctdet_postprocess": (c_int, [c_void_p] * 4 + [c_int] * 3 + [c_float, c_void_p, c_void_p]),

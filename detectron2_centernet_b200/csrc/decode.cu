@@ -38,8 +38,9 @@
 //   neighbour (clamp saturation, rounding near 1) are all kept, like the reference's plateaus; the ranking stays
 //   on the logits (same order; among equal probabilities: higher logit, then lower flat index).
 // Workspace: per-image headers + histograms (zero on entry, left zero) + tile counts / key segments + staged lists.
+#include <algorithm>
 #include <cstdlib>
-#include "common.cuh"
+#include "dcn_common.cuh"      // common.cuh + the tcgen05 / TMEM / mbarrier wrappers (head_decode.cuh at the end of this file)
 
 namespace ctdet {
 
@@ -1489,3 +1490,5 @@ extern "C" int ctdet_decode_static(const float* heat, const float* wh, const flo
   return ctdet_decode(heat, wh, reg, B, C, H, W, K, down_ratio, flags, boxes, scores, classes, inds,
                       ws, (size_t)CTDET_DECODE_STATIC_BYTES, stream);
 }
+
+#include "head_decode.cuh"

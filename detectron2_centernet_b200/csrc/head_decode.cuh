@@ -1,0 +1,457 @@
+// SURVEY section 8 f2, second half, decode side: the hm head's final 1x1 convolution fused with the decode (included at
+// the end of decode.cu).
+//
+// Reference chain replaced: `self.hm[-1]` = nn.Conv2d(head_conv, num_classes, kernel_size=1) with bias -2.19
+// (detectron2/modeling/meta_arch/centernet.py:118-123, applied :152), `hm.sigmoid_()` (:161) and ctdet_decode (:426-458:
+// _nms :399, _topk :408).  The [B, C, H, W] logits never reach HBM: each map row (W = 128 pixels = the UMMA M) is
+//     logits[128 px, C] = feat[128 px, Cf] * W^T[Cf, C] + bias          (bf16 operands, fp32 accumulation in TMEM)
+// and the epilogue warps keep a rolling window of three rows in shared memory, which is all the 3x3 peak test needs.
+// ONE kernel, three sinks (the GEMM sequence of a row is identical in all of them, so the logits are bit-identical):
+//   mode 0  seed:   one sampled row out of every 32 (with its two neighbours): the best peak of every (class, sampled row)
+//                   goes into the image's sample histogram; the last CTA-half of an image derives the bound and publishes
+//                   it in the image's header (the protocol of decode_seed_kernel)
+//   mode 1  sweep:  every row; cells >= the bound are 3x3-tested in the window and leave as keys in the (row, class half)
+//                   segment of the key list (the protocol of decode_stream_kernel: segments always written in full)
+//   mode 2  logits: rows of the images the first two handed over (no sample bound / a segment overflow: ties and plateaus)
+//                   -- or of every image when the caller asks for the logits -- are stored as fp32 NCHW; the tail
+//                   kernel's exact fall-back then runs on them.  Returns at once when no image is flagged.
+// decode_tail_kernel (mode 0) finishes as it does behind the plain sweep.
+//
+// Persistent, warp-specialised, one CTA per SM: warps [0, 8) producers (feat NCHW fp32 -> bf16 swizzled A stages),
+// [8, 16) epilogue (thread = pixel, warp >> 2 = half of the classes), warp 16 the MMA issuer (two TMEM accumulators).
+#pragma once
+
+namespace ctdet {
+
+constexpr int kHdProducerWarps = 8, kHdEpiWarps = 8;
+constexpr int kHdThreads = (kHdProducerWarps + kHdEpiWarps + 1) * 32;
+constexpr int kHdMaxStages = 6;
+constexpr int kHdMaxRows = 512;               // GEMM rows per CTA (row list in shared memory)
+constexpr int kHdSeedPeriod = 32;             // one sampled row per 32 map rows
+constexpr int kHdW = 128;                     // map width this kernel takes: a row is one UMMA M tile
+
+struct HeadDecodeBarriers {
+  uint64_t full[kHdMaxStages], empty[kHdMaxStages];   // A ring (producers -> MMA)
+  uint64_t acc_full[2], acc_empty[2];                 // TMEM accumulators (MMA -> epilogue)
+};
+
+__host__ __device__ inline int hd_seed_rows(int H) { const int n = (H + kHdSeedPeriod / 2) / kHdSeedPeriod; return n < 1 ? 1 : n; }
+__host__ __device__ inline int hd_seed_row(int H, int j) {
+  const int y = kHdSeedPeriod / 2 + kHdSeedPeriod * j;
+  return H < kHdSeedPeriod ? H / 2 : (y < H ? y : H - 1);
+}
+
+__device__ __forceinline__ void hd_tmem_ld8(uint32_t taddr, uint32_t (&v)[8]) {   // 32 lanes x 8 columns
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+               : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void hd_bar_half(int half) {      // the 4 epilogue warps of one class half
+  asm volatile("bar.sync %0, 128;" ::"r"(1 + half) : "memory");
+}
+
+// max over the existing 3x3 neighbours of (c, t, x) in the window (rows t-1 / t+1 only when `up` / `down`)
+__device__ __forceinline__ float hd_neighbour_max(const float* win, int C, int c, int t, int x, bool up, bool down) {
+  const float NEG = -__int_as_float(0x7f800000);
+  const float* r1 = win + ((size_t)(t % 3) * C + c) * kHdW + x;
+  const bool l = x > 0, r = x < kHdW - 1;
+  float m = NEG;
+  if (l) m = fmaxf(m, r1[-1]);
+  if (r) m = fmaxf(m, r1[1]);
+  if (up) {
+    const float* r0 = win + ((size_t)((t + 2) % 3) * C + c) * kHdW + x;
+    m = fmaxf(m, r0[0]);
+    if (l) m = fmaxf(m, r0[-1]);
+    if (r) m = fmaxf(m, r0[1]);
+  }
+  if (down) {
+    const float* r2 = win + ((size_t)((t + 1) % 3) * C + c) * kHdW + x;
+    m = fmaxf(m, r2[0]);
+    if (l) m = fmaxf(m, r2[-1]);
+    if (r) m = fmaxf(m, r2[1]);
+  }
+  return m;
+}
+
+template <int kMode>
+__global__ void __launch_bounds__(kHdThreads, 1)
+head_decode_kernel(const float* __restrict__ feat, const float* __restrict__ weight, const float* __restrict__ bias,
+                   int B, int Cf, int C, int H, int K, int stages, int force,
+                   DecodeHeader* __restrict__ hdrs, unsigned int* __restrict__ phists, unsigned int* __restrict__ pvals_all,
+                   u64* __restrict__ skeys, float* __restrict__ logits_out) {
+  extern __shared__ __align__(1024) uint8_t hd_smem[];
+  __shared__ HeadDecodeBarriers bars;
+  __shared__ uint32_t s_tmem;
+  __shared__ int s_nrows;
+  __shared__ unsigned int s_cnt[2], s_lastf[2];
+  __shared__ unsigned int s_sub[2][32];
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int KB = Cf / kBK;
+  const int NS = stages;
+  const int P = H * kHdW;
+  const int ns = hd_seed_rows(H);
+  uint8_t* smem = hd_smem + ((1024u - (smem_u32(hd_smem) & 1023u)) & 1023u);
+  uint8_t* ring = smem;                                     // [NS][128 px][128 B]
+  uint8_t* wsm = ring + (size_t)NS * (kTileM * 128);        // [KB][C rows][128 B]  W^T, K-major over the channels
+  float* s_bias = reinterpret_cast<float*>(wsm + (size_t)KB * C * 128);   // [C]
+  float* win = s_bias + C;                                  // [3 rows][C][128 px] fp32 logits
+  u64* s_keys = reinterpret_cast<u64*>(win + (size_t)3 * C * kHdW);       // [2 halves][kTileCap]
+  unsigned int* s_best = reinterpret_cast<unsigned int*>(s_keys + 2 * kTileCap);   // [C] best sampled peak of the class
+  int* s_g = reinterpret_cast<int*>(s_best + C);            // [kHdMaxRows] GEMM rows of this CTA: b * H + y
+  int* s_fl = s_g + kHdMaxRows;                             // 1: test row y-1 now, 2: test row y now (last map row),
+                                                            // 4: first GEMM row of a run, bits 8..: sample index (mode 0)
+  // ---- this CTA's rows: contiguous runs of tested rows, each with its halo rows inside the same image ----
+  if (tid == 0) {
+    int n = 0;
+    auto push_run = [&](int b, int y_lo, int y_hi, int extra) {
+      const int first = kMode == 2 ? y_lo : max(y_lo - 1, 0), last = kMode == 2 ? y_hi - 1 : min(y_hi, H - 1);
+      for (int y = first; y <= last && n < kHdMaxRows; ++y) {
+        s_g[n] = b * H + y;
+        s_fl[n] = extra | (y == first ? 4 : 0) | ((kMode != 2 && y - 1 >= y_lo) ? 1 : 0) |
+                  ((kMode != 2 && y == last && y == y_hi - 1) ? 2 : 0);
+        ++n;
+      }
+    };
+    if (kMode == 0) {
+      const long long items = (long long)B * ns;
+      const int i0 = (int)((blockIdx.x * items) / gridDim.x), i1 = (int)(((blockIdx.x + 1) * items) / gridDim.x);
+      for (int i = i0; i < i1; ++i) {
+        const int b = i / ns, j = i - b * ns;
+        const int yc = hd_seed_row(H, j);
+        push_run(b, yc, yc + 1, j << 8);
+      }
+    } else {
+      const long long rows = (long long)B * H;
+      int g = (int)((blockIdx.x * rows) / gridDim.x);
+      const int g1 = (int)(((blockIdx.x + 1) * rows) / gridDim.x);
+      while (g < g1) {
+        const int b = g / H, y_lo = g - b * H;
+        const int y_hi = min(H, y_lo + (g1 - g));
+        if (kMode != 2 || force || *((volatile unsigned int*)&hdrs[b].staged) != 0u) push_run(b, y_lo, y_hi, 0);
+        g += y_hi - y_lo;
+      }
+    }
+    s_nrows = n;
+    s_cnt[0] = 0u; s_cnt[1] = 0u;
+    for (int s = 0; s < kHdMaxStages; ++s) { dcn_mbar_init(&bars.full[s], kHdProducerWarps); dcn_mbar_init(&bars.empty[s], 1); }
+    for (int i = 0; i < 2; ++i) { dcn_mbar_init(&bars.acc_full[i], 1); dcn_mbar_init(&bars.acc_empty[i], kHdEpiWarps); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  const int n_rows = s_nrows;
+  if (n_rows == 0) return;                                  // (mode 2: no image was handed over -- the normal case)
+  if (warp == kHdProducerWarps + kHdEpiWarps) tmem_alloc(&s_tmem, 256);
+  // W^T -> bf16, swizzled: slab kb, row n (class), 16-byte chunk j (8 channels) at ((j ^ (n & 7)) << 4)
+  for (int i = tid; i < C * (Cf / 8); i += kHdThreads) {
+    const int n = i / (Cf / 8), j8 = i - n * (Cf / 8);
+    const float4 a = __ldg(reinterpret_cast<const float4*>(weight + (size_t)n * Cf + j8 * 8));
+    const float4 b = __ldg(reinterpret_cast<const float4*>(weight + (size_t)n * Cf + j8 * 8 + 4));
+    const __nv_bfloat162 p0 = __floats2bfloat162_rn(a.x, a.y), p1 = __floats2bfloat162_rn(a.z, a.w);
+    const __nv_bfloat162 p2 = __floats2bfloat162_rn(b.x, b.y), p3 = __floats2bfloat162_rn(b.z, b.w);
+    const int kb = j8 >> 3, j = j8 & 7;
+    *reinterpret_cast<uint4*>(wsm + (size_t)kb * C * 128 + n * 128 + ((j ^ (n & 7)) << 4)) =
+        make_uint4(*reinterpret_cast<const uint32_t*>(&p0), *reinterpret_cast<const uint32_t*>(&p1),
+                   *reinterpret_cast<const uint32_t*>(&p2), *reinterpret_cast<const uint32_t*>(&p3));
+  }
+  for (int i = tid; i < C; i += kHdThreads) { s_bias[i] = bias ? __ldg(bias + i) : 0.f; s_best[i] = 0u; }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = s_tmem;
+
+  if (warp < kHdProducerWarps) {
+    // ===================================== producers ==============================================
+    // warp w owns channels 8w..8w+7 of the K block, lane l pixels l, l+32, l+64, l+96: every load instruction is one
+    // coalesced 128-byte line; the loads of K block n + 1 are in flight while K block n is converted and stored
+    int s = 0; unsigned ph = 0;
+    const uint32_t swz = (uint32_t)((warp ^ (lane & 7)) << 4);
+    const int total_kb = n_rows * KB;
+    float v[2][8][4];
+    auto load_kb = [&](int n, float (&dst)[8][4]) {
+      const int it = n / KB, kb = n - it * KB;
+      const int g = s_g[it];
+      const int b = g / H, y = g - b * H;
+      const float* src = feat + ((size_t)b * Cf + kb * kBK + warp * 8) * P + y * kHdW + lane;
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) dst[i][j] = ldg_stream1(src + (size_t)i * P + 32 * j);
+    };
+    load_kb(0, v[0]);
+#pragma unroll 1
+    for (int n2 = 0; n2 < total_kb; n2 += 2) {
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int n = n2 + u;
+        if (n >= total_kb) break;
+        if (n + 1 < total_kb) load_kb(n + 1, v[u ^ 1]);
+        dcn_mbar_wait(&bars.empty[s], ph ^ 1u);
+        uint8_t* a_tile = ring + (size_t)s * (kTileM * 128);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const __nv_bfloat162 q0 = __floats2bfloat162_rn(v[u][0][j], v[u][1][j]), q1 = __floats2bfloat162_rn(v[u][2][j], v[u][3][j]);
+          const __nv_bfloat162 q2 = __floats2bfloat162_rn(v[u][4][j], v[u][5][j]), q3 = __floats2bfloat162_rn(v[u][6][j], v[u][7][j]);
+          *reinterpret_cast<uint4*>(a_tile + (uint32_t)(lane + 32 * j) * 128u + swz) =
+              make_uint4(*reinterpret_cast<const uint32_t*>(&q0), *reinterpret_cast<const uint32_t*>(&q1),
+                         *reinterpret_cast<const uint32_t*>(&q2), *reinterpret_cast<const uint32_t*>(&q3));
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) dcn_mbar_arrive(&bars.full[s]);
+        if (++s == NS) { s = 0; ph ^= 1u; }
+      }
+    }
+  } else if (warp < kHdProducerWarps + kHdEpiWarps) {
+    // ===================================== epilogue ================================================
+    const int quarter = warp & 3, half = (warp - kHdProducerWarps) >> 2;
+    const int ch = C / 2, c_lo = half * ch;                  // this warp's classes (ch % 8 == 0, ch <= 64)
+    const int x = quarter * 32 + lane;                       // this thread's pixel of the row
+    const uint32_t lane_base = (uint32_t)(quarter * 32) << 16;
+    const int n_vals = C * ns;
+    unsigned long long m_prev = 0ull, m_cur = 0ull;          // classes of rows y-1 / y whose cell passed the bound
+    unsigned int thr_ord = 0u;
+    float thv = 0.f;
+    bool live = false;                                       // mode 1: the image has a bound (else the tail's fall-back owns it)
+
+    // mode 1: 3x3 test of the flagged cells of row t, keys -> the (row, half) segment, always written in full
+    auto sweep_row = [&](int b, int t, bool up, bool down, unsigned long long m) {
+      hd_bar_half(half);                                     // the window rows are stored; the staging area is clean
+      while (m) {
+        const int k = __ffsll((long long)m) - 1;
+        m &= m - 1ull;
+        const int c = c_lo + k;
+        const float v = win[((size_t)(t % 3) * C + c) * kHdW + x];
+        const float nbm = hd_neighbour_max(win, C, c, t, x, up, down);
+        if (is_peak(v, nbm, true)) {
+          const unsigned int pos = atomicAdd(&s_cnt[half], 1u);
+          const uint32_t flat = (uint32_t)((c * H + t) * kHdW + x);
+          if (pos < (unsigned)kTileCap) s_keys[half * kTileCap + pos] = ((u64)float_to_ordered(v) << 32) | (u64)(0xffffffffu - flat);
+        }
+      }
+      hd_bar_half(half);
+      if (quarter == 0) {
+        const unsigned int cnt = s_cnt[half];
+        u64* dst = skeys + ((size_t)(b * H + t) * 2 + half) * kTileCap;
+        dst[lane] = (unsigned)lane < cnt ? s_keys[half * kTileCap + lane] : 0ull;
+        dst[lane + 32] = (unsigned)(lane + 32) < cnt ? s_keys[half * kTileCap + lane + 32] : 0ull;
+        if (cnt > (unsigned)kTileCap && lane == 0) hdrs[b].staged = 1u;      // ties / plateaus at the bound: exact fall-back
+        __syncwarp();
+        if (lane == 0) s_cnt[half] = 0u;
+      }
+    };
+    // mode 0: the best 3x3 peak of every class in row t -> sample histogram; the image's last half derives the bound
+    auto seed_row = [&](int b, int j, int t, bool up, bool down) {
+      hd_bar_half(half);
+      for (int k = 0; k < ch; ++k) {
+        const int c = c_lo + k;
+        const float v = win[((size_t)(t % 3) * C + c) * kHdW + x];
+        const float nbm = hd_neighbour_max(win, C, c, t, x, up, down);
+        unsigned int val = (v >= nbm) ? float_to_ordered(v) : 0u;             // (a strict subset of the peaks is still valid)
+        val = __reduce_max_sync(0xffffffffu, val);
+        if (lane == 0 && val) atomicMax(&s_best[c], val);
+      }
+      hd_bar_half(half);
+      const int tih = quarter * 32 + lane;
+      unsigned int* phist = phists + (size_t)b * kSeedHist;
+      if (tih < ch) {
+        const int c = c_lo + tih;
+        const unsigned int ord = s_best[c];
+        s_best[c] = 0u;
+        pvals_all[(size_t)b * n_vals + c * ns + j] = ord;
+        if (ord) {
+          atomicAdd(phist + (ord >> kHistShift), 1u);
+          atomicAdd(phist + kHistBins + (ord >> (kHistShift + 5)), 1u);
+        }
+      }
+      __threadfence();
+      hd_bar_half(half);
+      if (tih == 0) {
+        __threadfence();
+        s_lastf[half] = (atomicAdd(&hdrs[b].seed_ticket, 1u) == (unsigned)(2 * ns - 1)) ? 1u : 0u;
+        __threadfence();
+      }
+      hd_bar_half(half);
+      if (quarter == 0 && s_lastf[half]) {
+        const unsigned int ord = seed_bound_of_image(phist, pvals_all + (size_t)b * n_vals, n_vals, K, s_sub[half]);
+        if (lane == 0) {
+          if (ord == 0u) *((volatile unsigned int*)&hdrs[b].staged) = 1u;
+          else *((volatile unsigned int*)&hdrs[b].thr_ord) = ord;
+        }
+      }
+    };
+
+    for (int it = 0; it < n_rows; ++it) {
+      const int g = s_g[it], fl = s_fl[it];
+      const int b = g / H, y = g - b * H;
+      const int ab = it & 1;
+      m_prev = m_cur;
+      m_cur = 0ull;
+      if (fl & 4) {
+        m_prev = 0ull;
+        if (kMode == 1) {
+          thr_ord = *((volatile unsigned int*)&hdrs[b].thr_ord);       // published by the seed launch (stream order)
+          live = thr_ord != 0u;
+          thv = fmaxf(ordered_to_float(thr_ord), -3.402823466e38f);
+        }
+      }
+      dcn_mbar_wait(&bars.acc_full[ab], (unsigned)((it >> 1) & 1));
+      tc_fence_after();
+      for (int c0 = 0; c0 < ch; c0 += 8) {
+        uint32_t v[8];
+        hd_tmem_ld8(tmem + lane_base + (uint32_t)(ab * 128 + c_lo + c0), v);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const int c = c_lo + c0 + k;
+          const float l = __uint_as_float(v[k]) + s_bias[c];
+          if (kMode == 2) {
+            logits_out[((size_t)b * C + c) * P + y * kHdW + x] = l;
+          } else {
+            win[((size_t)(y % 3) * C + c) * kHdW + x] = l;
+            if (kMode == 1 && live && l >= thv && float_to_ordered(l) >= thr_ord) m_cur |= 1ull << (c0 + k);
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) dcn_mbar_arrive(&bars.acc_empty[ab]);
+      if (kMode == 1 && live) {
+        if (fl & 1) sweep_row(b, y - 1, y - 2 >= 0, true, m_prev);
+        if (fl & 2) sweep_row(b, y, y - 1 >= 0, false, m_cur);
+      }
+      if (kMode == 0) {
+        if (fl & 1) seed_row(b, fl >> 8, y - 1, y - 2 >= 0, true);
+        if (fl & 2) seed_row(b, fl >> 8, y, y - 1 >= 0, false);
+      }
+    }
+  } else {
+    // ===================================== MMA issuer ==============================================
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_bf16(kTileM, C);
+      const uint32_t w_addr = smem_u32(wsm);
+      int s = 0; unsigned ph = 0;
+      for (int it = 0; it < n_rows; ++it) {
+        const int ab = it & 1;
+        dcn_mbar_wait_relaxed(&bars.acc_empty[ab], (unsigned)(((it >> 1) & 1) ^ 1), 0u);
+        tc_fence_after();
+        for (int kb = 0; kb < KB; ++kb) {
+          dcn_mbar_wait_relaxed(&bars.full[s], ph, 0u);
+          tc_fence_after();
+          const uint64_t adesc = make_sw128_desc(smem_u32(ring + (size_t)s * (kTileM * 128)));
+          const uint64_t bdesc = make_sw128_desc(w_addr + (uint32_t)kb * (uint32_t)C * 128u);
+#pragma unroll
+          for (int k4 = 0; k4 < 4; ++k4)
+            umma_bf16(tmem + (uint32_t)(ab * 128), adesc + 2 * k4, bdesc + 2 * k4, idesc, (uint32_t)((kb | k4) != 0));
+          umma_commit(&bars.empty[s]);
+          if (++s == NS) { s = 0; ph ^= 1u; }
+        }
+        umma_commit(&bars.acc_full[ab]);
+      }
+    }
+    __syncwarp();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kHdProducerWarps + kHdEpiWarps) tmem_dealloc(tmem, 256);
+}
+
+struct HeadDecodePlan {
+  DecodePlan dec;                   // the tail kernel's parameters and the zero-on-entry prefix of ctdet_decode's layout
+  int stages, ns;
+  size_t smem, tail_smem;
+  size_t pvals_bytes, skeys_bytes, staged_keys_bytes, logits_bytes, total_bytes;
+};
+
+static HeadDecodePlan make_head_decode_plan(int B, int Cf, int C, int H, int W, int K) {
+  HeadDecodePlan p;
+  p.dec = make_plan(B, C, H, W, K);
+  p.ns = hd_seed_rows(H);
+  const size_t fixed = 1024 + (size_t)(Cf / kBK) * C * 128 + (size_t)C * 4 + (size_t)3 * C * kHdW * 4 +
+                       (size_t)2 * kTileCap * 8 + (size_t)C * 4 + (size_t)2 * kHdMaxRows * 4;
+  int st = kHdMaxStages;
+  while (st > 2 && fixed + (size_t)st * (kTileM * 128) > 226 * 1024) --st;
+  p.stages = st;
+  p.smem = fixed + (size_t)st * (kTileM * 128);
+  const size_t list = (size_t)kTailSmemKeys * sizeof(u64) + (size_t)kHistBins * sizeof(unsigned int);
+  p.tail_smem = p.dec.smem > list ? p.dec.smem : list;
+  p.pvals_bytes = (((size_t)B * C * p.ns * sizeof(unsigned int)) + 255) / 256 * 256;
+  p.skeys_bytes = (size_t)B * 2 * H * kTileCap * sizeof(u64);
+  p.staged_keys_bytes = (((size_t)B * p.dec.keys_per_image * sizeof(u64)) + 255) / 256 * 256;
+  p.logits_bytes = (size_t)B * C * H * W * sizeof(float);
+  // layout: headers | staged histograms (x2) | sample histograms   (zero on entry, the prefix of ctdet_decode's layout)
+  //         | samples | key segments | staged keys | logits of handed-over images
+  p.total_bytes = p.dec.header_bytes + 2 * p.dec.hist_bytes + p.dec.phist_bytes + p.pvals_bytes + p.skeys_bytes +
+                  p.staged_keys_bytes + p.logits_bytes;
+  return p;
+}
+
+static int head_decode_check(int B, int Cf, int C, int H, int W, int K) {
+  if (B < 0 || Cf <= 0 || C <= 0 || H <= 0 || W <= 0 || K <= 0) return CTDET_EINVAL;
+  if (K > CTDET_MAX_K || (int64_t)K > (int64_t)H * W) return CTDET_EINVAL;
+  if ((int64_t)C * H * W >= ((int64_t)1 << 31) || (int64_t)B * H >= ((int64_t)1 << 30)) return CTDET_EINVAL;
+  if (W != kHdW || (Cf % kBK) != 0 || (C % 16) != 0 || C > 128) return CTDET_EUNSUPPORTED;
+  return CTDET_OK;
+}
+
+}  // namespace ctdet
+
+extern "C" size_t ctdet_head_decode_fused_workspace_bytes(int B, int Cf, int C, int H, int W, int K) {
+  using namespace ctdet;
+  if (B <= 0 || head_decode_check(B, Cf, C, H, W, K) != CTDET_OK) return 0;
+  return make_head_decode_plan(B, Cf, C, H, W, K).total_bytes;
+}
+
+extern "C" int ctdet_head_decode_fused(const float* feat, const float* weight, const float* bias,
+                                       const float* wh, const float* reg, int B, int Cf, int C, int H, int W, int K,
+                                       float down_ratio, int flags, float* boxes, float* scores, int32_t* classes,
+                                       int64_t* inds, float* logits_out, void* workspace, size_t workspace_bytes,
+                                       ctdet_stream_t stream) {
+  using namespace ctdet;
+  int rc = head_decode_check(B, Cf, C, H, W, K);
+  if (rc != CTDET_OK) return rc;
+  if (flags & ~CTDET_DECODE_CAT_SPEC_WH) return CTDET_EINVAL;       // logits in, 3x3 peak test always (centernet.py:161, :399)
+  if (B == 0) return CTDET_OK;
+  if (!feat || !weight || !wh || !boxes || !scores || !classes || !workspace) return CTDET_ENULL;
+  if (!aligned16(weight) || !aligned16(feat) || (reinterpret_cast<uintptr_t>(workspace) & 255u)) return CTDET_EALIGN;
+  if (B > 65535) return CTDET_EINVAL;
+  const HeadDecodePlan p = make_head_decode_plan(B, Cf, C, H, W, K);
+  if (workspace_bytes < p.total_bytes) return CTDET_EWORKSPACE;
+  if (p.smem > 227 * 1024 || p.dec.smem > 200 * 1024) return CTDET_EUNSUPPORTED;
+  const int grid_rows = (int)std::min<long long>((long long)B * H, kNumSMs);
+  const int grid_seed = (int)std::min<long long>((long long)B * p.ns, kNumSMs);
+  // rows per CTA incl. the halo rows of every run (a run ends at an image boundary)
+  if (((long long)B * H + grid_rows - 1) / grid_rows + 2 * (((long long)B * H / grid_rows) / H + 2) > kHdMaxRows) return CTDET_EUNSUPPORTED;
+  if (3LL * (((long long)B * p.ns + grid_seed - 1) / grid_seed) > kHdMaxRows) return CTDET_EUNSUPPORTED;
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t e = cudaFuncSetAttribute(head_decode_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(head_decode_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(head_decode_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(decode_tail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.tail_smem);
+  if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
+  unsigned char* base = reinterpret_cast<unsigned char*>(workspace);
+  DecodeHeader* hdr = reinterpret_cast<DecodeHeader*>(base);
+  unsigned int* ghist = reinterpret_cast<unsigned int*>(base + p.dec.header_bytes);
+  unsigned char* q = base + p.dec.header_bytes + 2 * p.dec.hist_bytes;
+  unsigned int* phist = reinterpret_cast<unsigned int*>(q); q += p.dec.phist_bytes;
+  unsigned int* pvals = reinterpret_cast<unsigned int*>(q); q += p.pvals_bytes;
+  u64* skeys = reinterpret_cast<u64*>(q); q += p.skeys_bytes;
+  u64* keys = reinterpret_cast<u64*>(q); q += p.staged_keys_bytes;
+  float* logits = logits_out ? logits_out : reinterpret_cast<float*>(q);
+  head_decode_kernel<0><<<grid_seed, kHdThreads, p.smem, st>>>(feat, weight, bias, B, Cf, C, H, K, p.stages, 0, hdr, phist,
+                                                                pvals, skeys, logits);
+  if ((rc = check_launch())) return rc;
+  head_decode_kernel<1><<<grid_rows, kHdThreads, p.smem, st>>>(feat, weight, bias, B, Cf, C, H, K, p.stages, 0, hdr, phist,
+                                                                pvals, skeys, logits);
+  if ((rc = check_launch())) return rc;
+  head_decode_kernel<2><<<grid_rows, kHdThreads, p.smem, st>>>(feat, weight, bias, B, Cf, C, H, K, p.stages,
+                                                                logits_out ? 1 : 0, hdr, phist, pvals, skeys, logits);
+  if ((rc = check_launch())) return rc;
+  const FastDiv div_strips((uint32_t)p.dec.strips);
+  decode_tail_kernel<<<dim3(B * kTailHelpers), dim3(kFinThreads), p.tail_smem, st>>>(
+      logits, B, 0, kTailHelpers, hdr, ghist, keys, p.dec.keys_per_image, (const u64*)skeys, 2 * H, phist,
+      p.dec.Wp, p.dec.band_rows, p.dec.tail_sub_rows, div_strips, p.dec.bands,
+      wh, reg, C, H, W, K, down_ratio, flags | CTDET_DECODE_LOGITS, boxes, scores, classes, inds);
+  return check_launch();
+}

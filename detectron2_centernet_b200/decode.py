@@ -57,6 +57,62 @@ def ctdet_decode_batch(heat, wh, reg=None, down_ratio=1, cat_spec_wh=False, K=10
     return boxes, scores, classes, inds
 
 
+def head_decode_fusable(Cf, C, H, W):
+    """Shapes `ctdet_head_decode_fused` takes (include/ctdet_b200.h): a map row is one 128-pixel tensor-core tile."""
+    return W == 128 and Cf % 64 == 0 and C % 16 == 0 and C <= 128 and \
+        1024 + (Cf // 64) * C * 128 + 3 * C * 512 + 2 * 16384 + 8 * C + 5120 <= 226 * 1024
+
+
+def hm_head_decode_batch(feat, weight, bias, wh, reg=None, down_ratio=1, cat_spec_wh=False, K=100, return_logits=False):
+    """`ctdet_decode(Conv2d(Cf, C, 1)(feat).sigmoid_(), wh, reg, ...)` (centernet.py:118-123, :152, :161, :426-458) for a
+    batch, without the logits in HBM: the 1x1 convolution runs per map row on the tensor cores (bf16 operands) and the
+    decode's peak test / threshold sweep on a three-row window in shared memory.  feat f32 [B,Cf,H,128]; weight f32 [C,Cf]
+    or [C,Cf,1,1]; bias f32 [C] or None.  Returns boxes, scores, classes, inds as ctdet_decode_batch (+ the logits
+    f32 [B,C,H,W] with return_logits=True: an extra pass, for verification)."""
+    _lib.require_cuda("hm_head_decode", feat, weight, bias, wh, reg)
+    lib = _lib.load()
+    feat = _lib.f32c(feat, "feat")
+    if weight.dim() == 4:
+        if weight.shape[2:] != (1, 1):
+            raise NotImplementedError("hm_head_decode fuses the head's final 1x1 convolution")
+        weight = weight.reshape(weight.shape[0], weight.shape[1])
+    weight = _lib.f32c(weight, "weight")
+    bias = None if bias is None else _lib.f32c(bias, "bias")
+    wh = _lib.f32c(wh, "wh")
+    reg = None if reg is None else _lib.f32c(reg, "reg")
+    B, Cf, H, W = feat.shape
+    C = weight.shape[0]
+    if weight.shape[1] != Cf:
+        raise RuntimeError("weight must be [%d,%d]" % (C, Cf))
+    want_wh = 2 * C if cat_spec_wh else 2
+    if tuple(wh.shape) != (B, want_wh, H, W):
+        raise RuntimeError("wh must be [%d,%d,%d,%d], got %s" % (B, want_wh, H, W, tuple(wh.shape)))
+    if reg is not None and tuple(reg.shape) != (B, 2, H, W):
+        raise RuntimeError("reg must be [%d,2,%d,%d]" % (B, H, W))
+    if K > H * W:
+        raise RuntimeError("selected index k out of range")
+    if not head_decode_fusable(Cf, C, H, W):
+        raise NotImplementedError("hm_head_decode_batch needs W == 128, Cf %% 64 == 0, C %% 16 == 0, C <= 128 (got Cf=%d C=%d "
+                                  "W=%d): run the convolution and ctdet_decode_batch(logits=True)" % (Cf, C, W))
+    dev = feat.device
+    boxes = torch.empty((B, K, 4), dtype=torch.float32, device=dev)
+    scores = torch.empty((B, K), dtype=torch.float32, device=dev)
+    classes = torch.empty((B, K), dtype=torch.int32, device=dev)
+    inds = torch.empty((B, K), dtype=torch.int64, device=dev)
+    logits = torch.empty((B, C, H, W), dtype=torch.float32, device=dev) if return_logits else None
+    nbytes = lib.ctdet_head_decode_fused_workspace_bytes(B, Cf, C, H, W, K)
+    ws = _lib.zero_workspace("head_decode%d" % B, max(nbytes, 8), dev)
+    with torch.cuda.device(dev):
+        rc = lib.ctdet_head_decode_fused(_lib.ptr(feat), _lib.ptr(weight), _lib.ptr(bias), _lib.ptr(wh), _lib.ptr(reg),
+                                         B, Cf, C, H, W, K, float(down_ratio), FLAG_CAT_SPEC_WH if cat_spec_wh else 0,
+                                         _lib.ptr(boxes), _lib.ptr(scores), _lib.ptr(classes), _lib.ptr(inds),
+                                         _lib.ptr(logits), _lib.ptr(ws), ctypes.c_size_t(ws.numel()), _lib.stream_ptr(dev))
+    _lib.check(rc, "ctdet_head_decode_fused")
+    if return_logits:
+        return boxes, scores, classes, inds, logits
+    return boxes, scores, classes, inds
+
+
 def ctdet_decode(heat, wh, reg=None, down_ratio=1, cat_spec_wh=False, K=100):
     """Drop-in for centernet.py:426 (batch must be 1, as the reference's `view(K)` at :450-456
     requires): returns (bboxes [K,4], scores [K], clses [K] int32)."""

@@ -1,0 +1,124 @@
+"""GPU: SURVEY section 8 f2, second half, decode side -- `ctdet_head_decode_fused` (the hm head's final 1x1 convolution +
+sigmoid + ctdet_decode without the logits in HBM) against the reference chain
+    Conv2d(head_conv, C, 1) (centernet.py:118-123, applied :152) -> hm.sigmoid_() (:161) -> ctdet_decode (:426-458).
+
+Two-step parity, because the convolution's operands are rounded to bf16 for the tensor cores:
+  1. the logits the kernel forms (its optional `logits_out`) against torch's fp32 conv2d: relative L2 <= 1e-2 (stated bf16
+     tolerance; exact to fp32 summation order when feat / weight are bf16-representable: <= 1e-5);
+  2. the detections against `ctdet_decode` (pinned on the reference's golden vectors in tests/test_gpu_parity.py) run on
+     THOSE logits: bit for bit (`torch.equal`) -- boxes, scores, classes, inds -- with and without `logits_out`.
+With bf16-representable, well-separated inputs the detections are also compared with the oracle port of the reference's own
+ctdet_decode on torch's fp32 logits (classes / inds equal, scores and boxes to 1e-5).
+"""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _setup(seed, B, Cf, C, H, W=128, bf16_exact=False, peaks=60):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    feat = torch.relu(torch.randn(B, Cf, H, W, generator=g))
+    w = torch.randn(C, Cf, generator=g) * (1.0 / Cf ** 0.5)
+    b = torch.full((C,), -2.19)
+    # planted objects: a few cells whose features line up with one class's weights
+    for bi in range(B):
+        for _ in range(peaks):
+            c = int(torch.randint(0, C, (1,), generator=g))
+            y, x = int(torch.randint(0, H, (1,), generator=g)), int(torch.randint(0, W, (1,), generator=g))
+            feat[bi, :, y, x] += torch.relu(w[c]) * float(torch.rand(1, generator=g) * 6 + 2) * Cf ** 0.5 / 8
+    if bf16_exact:
+        feat, w = feat.bfloat16().float(), w.bfloat16().float()
+    wh = torch.rand(B, 2, H, W, generator=g) * 20 + 1
+    reg = torch.rand(B, 2, H, W, generator=g)
+    return [t.to(DEV) for t in (feat, w, b, wh, reg)]
+
+
+def _rel(a, b):
+    a, b = a.double(), b.double()
+    return float((a - b).norm() / b.norm().clamp_min(1e-30))
+
+
+@pytest.mark.parametrize("cfg", [(2, 64, 16, 12, 40), (3, 256, 80, 32, 100), (2, 128, 32, 128, 100), (5, 256, 80, 64, 100),
+                                 (1, 64, 16, 1, 20), (2, 64, 16, 2, 30), (1, 192, 48, 33, 100)])
+def test_fused_head_decode_equals_decode_of_its_own_logits(cfg):
+    """The last three shapes: one and two map rows (no halo rows exist), an odd row count (runs that end inside an image)."""
+    from detectron2_centernet_b200 import decode as D
+    B, Cf, C, H, K = cfg
+    feat, w, b, wh, reg = _setup(3 + H, B, Cf, C, H)
+    boxes, scores, classes, inds, logits = D.hm_head_decode_batch(feat, w, b, wh, reg, down_ratio=4, K=K, return_logits=True)
+    want_logits = torch.nn.functional.conv2d(feat, w[:, :, None, None], b)
+    assert _rel(logits, want_logits) <= 1e-2
+    want = D.ctdet_decode_batch(logits, wh, reg, down_ratio=4, K=K, logits=True)
+    for name, a, r in zip(("boxes", "scores", "classes", "inds"), (boxes, scores, classes, inds), want):
+        assert torch.equal(a, r), (cfg, name)
+    again = D.hm_head_decode_batch(feat, w, b, wh, reg, down_ratio=4, K=K)          # without the logits pass
+    for name, a, r in zip(("boxes", "scores", "classes", "inds"), again, want):
+        assert torch.equal(a, r), (cfg, name, "no logits_out")
+
+
+def test_fused_head_decode_matches_reference_chain_on_bf16_exact_inputs():
+    from oracle import ctdet_oracle as O
+    from detectron2_centernet_b200 import decode as D
+    B, Cf, C, H, K = 2, 128, 16, 24, 50
+    feat, w, b, wh, reg = _setup(91, B, Cf, C, H, bf16_exact=True)
+    boxes, scores, classes, inds, logits = D.hm_head_decode_batch(feat, w, b, wh, reg, down_ratio=4, K=K, return_logits=True)
+    want_logits = torch.nn.functional.conv2d(feat.double(), w.double()[:, :, None, None], b.double()).float()
+    assert _rel(logits, want_logits) <= 1e-5
+    rb, rs, rc, ri = O.decode(want_logits.cpu().numpy(), wh.cpu().numpy(), reg.cpu().numpy(), down_ratio=4, K=K, logits=True)
+    for bi in range(B):
+        # the top detections are planted, well-separated peaks: compare while the reference's scores are distinct by > 1e-4
+        n = K
+        for i in range(1, K):
+            if rs[bi, i - 1] - rs[bi, i] < 1e-4:
+                n = i
+                break
+        assert n >= 10
+        assert np.array_equal(classes[bi, :n].cpu().numpy(), rc[bi, :n])
+        assert np.array_equal(inds[bi, :n].cpu().numpy(), ri[bi, :n])
+        np.testing.assert_allclose(scores[bi, :n].cpu().numpy(), rs[bi, :n], rtol=0, atol=2e-5)
+        np.testing.assert_allclose(boxes[bi, :n].cpu().numpy(), rb[bi, :n], rtol=0, atol=2e-3)
+
+
+def test_plateaus_take_the_exact_fallback():
+    """weight = 0: every logit equals the bias, every cell ties with its neighbours (a peak by the reference's `hmax == heat`),
+    every key segment overflows -> the images are handed to the staged path on the stored logits; one image of the batch is
+    normal, so both paths run in one call."""
+    from detectron2_centernet_b200 import decode as D
+    B, Cf, C, H, K = 3, 64, 16, 16, 100
+    feat, w, b, wh, reg = _setup(5, B, Cf, C, H)
+    feat[0].zero_()
+    feat[2].zero_()
+    out = D.hm_head_decode_batch(feat, w, b, wh, reg, down_ratio=4, K=K, return_logits=True)
+    want = D.ctdet_decode_batch(out[4], wh, reg, down_ratio=4, K=K, logits=True)
+    for name, a, r in zip(("boxes", "scores", "classes", "inds"), out[:4], want):
+        assert torch.equal(a, r), name
+    assert torch.equal(out[3][0], torch.arange(K, device=DEV, dtype=torch.int64))      # ties: lowest flat index first
+    out2 = D.hm_head_decode_batch(feat, w, b, wh, reg, down_ratio=4, K=K)               # fall-back on the workspace's logits
+    for name, a, r in zip(("boxes", "scores", "classes", "inds"), out2, want):
+        assert torch.equal(a, r), (name, "no logits_out")
+
+
+def test_two_calls_in_a_row_and_shape_changes_share_the_workspace():
+    from detectron2_centernet_b200 import decode as D
+    for i, (B, Cf, C, H, K) in enumerate([(2, 64, 16, 40, 100), (2, 64, 16, 40, 100), (2, 128, 32, 8, 50), (2, 64, 16, 40, 100)]):
+        feat, w, b, wh, reg = _setup(20 + i, B, Cf, C, H)
+        out = D.hm_head_decode_batch(feat, w, b, wh, reg, down_ratio=4, K=K, return_logits=True)
+        want = D.ctdet_decode_batch(out[4], wh, reg, down_ratio=4, K=K, logits=True)
+        for name, a, r in zip(("boxes", "scores", "classes", "inds"), out[:4], want):
+            assert torch.equal(a, r), (i, name)
+
+
+def test_unsupported_shapes_are_rejected():
+    from detectron2_centernet_b200 import _lib
+    from detectron2_centernet_b200 import decode as D
+    lib = _lib.load()
+    assert lib.ctdet_head_decode_fused_workspace_bytes(2, 64, 16, 16, 64, 10) == 0          # W != 128
+    assert lib.ctdet_head_decode_fused_workspace_bytes(2, 60, 16, 16, 128, 10) == 0         # Cf % 64
+    assert lib.ctdet_head_decode_fused_workspace_bytes(2, 64, 20, 16, 128, 10) == 0         # C % 16
+    assert not D.head_decode_fusable(64, 16, 16, 64)
+    feat = torch.zeros(1, 64, 4, 64, device=DEV)
+    with pytest.raises(NotImplementedError):
+        D.hm_head_decode_batch(feat, torch.zeros(16, 64, device=DEV), None, torch.zeros(1, 2, 4, 64, device=DEV))
