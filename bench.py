@@ -213,6 +213,60 @@ def fused_head_variant(dev, flush, peak, B):
             tot += s.elapsed_time(e)
         return tot / reps * 1e3
 
+    # ---- decode side: conv + sigmoid + ctdet_decode in one pass over feat (ctdet_head_decode_fused), through the C ABI
+    # with preallocated outputs, replayed from a CUDA graph (the Python wrappers' host time would hide the difference);
+    # zero-mean features so that the logits are iid ~N(-2.19, 1.5^2) like the headline step's (no exact fall-back)
+    import ctypes
+    from detectron2_centernet_b200 import _lib
+    lib = _lib.load()
+    featd = torch.randn((B, Cf, S_, S_), device=dev, generator=g)
+    wd = (torch.randn((C, Cf), device=dev, generator=g) * (1.5 / 16)).contiguous()
+    wd4 = wd[:, :, None, None].contiguous()
+    whd = torch.rand((B, 2, S_, S_), device=dev, generator=g) * 20
+    regd = torch.rand((B, 2, S_, S_), device=dev, generator=g)
+    outs = (torch.empty((B, K, 4), device=dev), torch.empty((B, K), device=dev),
+            torch.empty((B, K), dtype=torch.int32, device=dev), torch.empty((B, K), dtype=torch.int64, device=dev))
+    n_f = lib.ctdet_head_decode_fused_workspace_bytes(B, Cf, C, S_, S_, K)
+    ws_f = torch.zeros(n_f, dtype=torch.uint8, device=dev)
+    n_d = lib.ctdet_decode_workspace_bytes(B, C, S_, S_, K)
+    ws_d = torch.zeros(n_d, dtype=torch.uint8, device=dev)
+    logits_d = torch.empty((B, C, S_, S_), device=dev)
+
+    def dec_fused():
+        _lib.check(lib.ctdet_head_decode_fused(_lib.ptr(featd), _lib.ptr(wd), _lib.ptr(bias), _lib.ptr(whd), _lib.ptr(regd),
+                                               B, Cf, C, S_, S_, K, 4.0, 0, *[_lib.ptr(o) for o in outs], None, _lib.ptr(ws_f),
+                                               ctypes.c_size_t(n_f), _lib.stream_ptr(dev)), "ctdet_head_decode_fused")
+
+    def dec_unfused():
+        torch.ops.aten.convolution.out(featd, wd4, bias, [1, 1], [0, 0], [1, 1], False, [0, 0], 1, out=logits_d)
+        _lib.check(lib.ctdet_decode(_lib.ptr(logits_d), _lib.ptr(whd), _lib.ptr(regd), B, C, S_, S_, K, 4.0, 1,
+                                    *[_lib.ptr(o) for o in outs], _lib.ptr(ws_d), ctypes.c_size_t(n_d), _lib.stream_ptr(dev)),
+                   "ctdet_decode")
+
+    def timed_graph(fn, reps=10):
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                fn()
+            torch.cuda.synchronize()
+            with torch.cuda.graph(gr, stream=side):
+                fn()
+        torch.cuda.current_stream().wait_stream(side)
+        tot = 0.0
+        for _ in range(reps):
+            flush.zero_()
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record()
+            gr.replay()
+            e.record()
+            torch.cuda.synchronize()
+            tot += s.elapsed_time(e)
+        return tot / reps * 1e3
+
+    us_df, us_du = timed_graph(dec_fused), timed_graph(dec_unfused)
+
     us_f = timed(lambda: L._head_focal_call(feat, w, bias, tg["hm"], a, tg["num_pos"], None, True, 1.0, True))
     us_fb = timed(lambda: L._head_focal_bwd_call(feat, w, bias, tg["hm"], a, tg["num_pos"], None, True, 1.0))
     us_uf, us_uc = timed(unfused_fwd), timed(unfused_chain)
@@ -225,7 +279,13 @@ def fused_head_variant(dev, flush, peak, B):
             "fwd_bwd": {"us": round(us_fb, 1), "bytes_per_pixel": bpp_fb, "GBps": round(px * bpp_fb / us_fb / 1e3, 1),
                         "frac": round(px * bpp_fb / us_fb / 1e3 / peak, 3), "images_per_s": round(B / us_fb * 1e6),
                         "outputs": "loss, d_feat, d_weight, d_bias", "unfused_us": round(us_uc, 1),
-                        "unfused": "cuDNN fp32 conv + ctdet_loss_fwd_bwd + aten convolution_backward (cuDNN)"}}
+                        "unfused": "cuDNN fp32 conv + ctdet_loss_fwd_bwd + aten convolution_backward (cuDNN)"},
+            "decode": {"us": round(us_df, 1), "bytes_per_pixel": 4 * Cf, "GBps": round(px * 4 * Cf / us_df / 1e3, 1),
+                       "frac": round(px * 4 * Cf / us_df / 1e3 / peak, 3), "images_per_s": round(B / us_df * 1e6),
+                       "outputs": "boxes, scores, classes, inds (top-%d)" % K, "unfused_us": round(us_du, 1),
+                       "unfused": "cuDNN fp32 conv + ctdet_decode on the logits",
+                       "launch": "both replayed from a CUDA graph, C ABI, preallocated outputs; zero-mean synthetic "
+                                 "features (iid logits: no image takes the exact fall-back)"}}
 
 
 def config5(dev, rank, world, images=512, micro=32, reps=2):

@@ -712,16 +712,18 @@ decode_seed_kernel(const float* __restrict__ heat, int C, int H, int W, int K, i
 constexpr int kStrThreads = 128;
 constexpr int kStrWarps = kStrThreads / 32;
 constexpr int kTileCap = 64;                     // keys per tile on this path (~20 at K = 100)
+constexpr int kSpillCap = 8192;                  // keys per image beyond their tiles' segments (class- / object-concentrated scores)
 
 template <bool kOneStrip>                        // W <= 128: a row is one warp-wide float4 load
 __global__ void __launch_bounds__(kStrThreads)
 decode_stream_kernel(const float* __restrict__ heat, int C, int H, int W, int band_rows, int bands, int flags, int K,
                      FastDiv div_bands, FastDiv div_strips, DecodeHeader* __restrict__ hdrs,
                      const unsigned int* __restrict__ phists, const unsigned int* __restrict__ pvals_all, int n_vals,
-                     u64* __restrict__ skeys_all) {
+                     u64* __restrict__ skeys_all, u64* __restrict__ spill_all, size_t keys_per_image, int spill_cap) {
   extern __shared__ __align__(128) unsigned char s_raw[];
   __shared__ __align__(8) uint64_t s_bar;
   __shared__ int s_wtot[kStrWarps];
+  __shared__ unsigned int s_spill;
   __shared__ unsigned int s_sub[32];
   __shared__ unsigned int s_thr, s_skip;
   float* tile = reinterpret_cast<float*>(s_raw);              // [(band_rows + 2)][W]; tile row t <-> map row y_lo - 1 + t
@@ -836,15 +838,26 @@ decode_stream_kernel(const float* __restrict__ heat, int C, int H, int W, int ba
   int base = 0, total = 0;
 #pragma unroll
   for (int w = 0; w < kStrWarps; ++w) { const int t = s_wtot[w]; if (w < warp) base += t; total += t; }
-  pdl_launch_dependents();
-  if (total > kTileCap) {                                     // ties / plateaus at the bound: the staged path redoes the image
-    if (tid == 0) hdr->staged = 1u;
-    return;
+  u64* spill = nullptr;
+  if (total > kTileCap) {
+    // More keys than the tile's segment holds (scores concentrated in a few classes or around a few objects; ties and
+    // plateaus at the bound): the first kTileCap keys go to the segment, the others to the image's spill list -- ONE
+    // returning atomic per overflowing tile.  Only when that list is full too is the image handed to the staged path.
+    if (tid == 0) s_spill = atomicAdd(&hdr->s_count, (unsigned int)(total - kTileCap));
+    __syncthreads();                                          // (CTA-uniform branch)
+    if (s_spill + (unsigned int)(total - kTileCap) > (unsigned int)spill_cap) {
+      if (tid == 0) hdr->staged = 1u;
+      pdl_launch_dependents();
+      return;
+    }
+    spill = spill_all + (size_t)b * keys_per_image + s_spill;
   }
+  pdl_launch_dependents();
   // the segment is always written in full -- keys, then zeros -- so the tail reads it as one dense, coalesced vector
   // without knowing the counts (no count array, no dependent second trip)
   for (int i = total + tid; i < kTileCap; i += kStrThreads) skeys_all[tile_id * kTileCap + i] = 0ull;
-  u64* dst = skeys_all + tile_id * kTileCap + base + (incl - mine_n);
+  int pos = base + (incl - mine_n);                           // this lane's first slot in CTA order
+  u64* seg = skeys_all + tile_id * kTileCap;
   while (hits) {
     const int bit = __ffsll((long long)hits) - 1;
     hits &= hits - 1ull;
@@ -853,7 +866,9 @@ decode_stream_kernel(const float* __restrict__ heat, int C, int H, int W, int ba
     const int x = strip * 128 + lane * 4 + (bit & 3);
     const float v = tile[(size_t)(t + 1) * W + x];
     const uint32_t flat = (uint32_t)((c * H + (y_lo + t)) * W + x);
-    *dst++ = ((u64)float_to_ordered(v) << 32) | (u64)(0xffffffffu - flat);
+    const u64 key = ((u64)float_to_ordered(v) << 32) | (u64)(0xffffffffu - flat);
+    if (pos < kTileCap) seg[pos] = key; else spill[pos - kTileCap] = key;
+    ++pos;
   }
 }
 
@@ -1076,7 +1091,7 @@ __global__ void __launch_bounds__(kFinThreads, 1)
 decode_tail_kernel(const float* __restrict__ heat, int B, int mode, int helpers,
                    DecodeHeader* __restrict__ hdrs, unsigned int* __restrict__ ghists,
                    u64* __restrict__ keys, size_t keys_per_image,
-                   const u64* __restrict__ skeys, int sw_tiles,
+                   const u64* __restrict__ skeys, int sw_tiles, int spill_cap,
                    unsigned int* __restrict__ phists,
                    int Wp, int band_rows, int sub_rows, FastDiv div_strips, int bands,
                    const float* __restrict__ wh, const float* __restrict__ reg, int C, int H,
@@ -1166,6 +1181,16 @@ decode_tail_kernel(const float* __restrict__ heat, int B, int mode, int helpers,
         if ((kq[u].z | kq[u].w) != 0u) { if (slot < kTailSmemKeys) s_keys[slot] = ((u64)kq[u].w << 32) | kq[u].z; ++slot; mx = max(mx, kq[u].w); }
       }
     }
+    // the image's spill list (keys of tiles whose segment was full; normally empty): it lives at the start of the image's
+    // staged-list region, which only a handed-over image would use
+    const u64* spill = keys + (size_t)b * keys_per_image;
+    const int n_spill = (int)min(*((volatile unsigned int*)&hdr->s_count), (unsigned int)spill_cap);
+    for (int i = tid; i < n_spill; i += kFinThreads) {
+      const u64 key = __ldcg(spill + i);
+      const int slot = atomicAdd(&fs.above, 1);
+      if (slot < kTailSmemKeys) s_keys[slot] = key;
+      mx = max(mx, (unsigned int)(key >> 32));
+    }
     mx = __reduce_max_sync(0xffffffffu, mx);
     if (lane == 0 && mx) atomicMax(&fs.maxord, mx);
     __syncthreads();
@@ -1173,9 +1198,10 @@ decode_tail_kernel(const float* __restrict__ heat, int B, int mode, int helpers,
     const int n_keys = fs.above;                             // the slot counter = number of keys
     const bool fits = n_keys <= kTailSmemKeys;               // CTA-uniform
     const u64* segs = skeys + (size_t)b * sw_tiles * kTileCap;
-    // (only when the list does not fit shared memory: f(key) for every key, straight from the segments)
+    // (only when the list does not fit shared memory: f(key) for every key, straight from the segments and the spill list)
     auto scan_tiles = [&](auto f) {
       for (int i = tid; i < sw_tiles * kTileCap; i += kFinThreads) { const u64 key = __ldcg(segs + i); if (key) f(key, 0); }
+      for (int i = tid; i < n_spill; i += kFinThreads) f(__ldcg(spill + i), 0);
     };
     __syncthreads();
     if (tid == 0) fs.above = 0;
@@ -1379,11 +1405,13 @@ extern "C" int ctdet_decode(const float* heat, const float* wh, const float* reg
     if (e == cudaSuccess)
       e = launch_pdl(sweep, dim3(C * p.sw_bands, B), dim3(kStrThreads), p.sw_smem, st,
                      heat, C, H, W, p.sw_rows, p.sw_bands, flags, K, FastDiv((uint32_t)p.sw_bands), div_strips, hdr,
-                     (const unsigned int*)phist, (const unsigned int*)pvals, p.seed_vals, skeys);
+                     (const unsigned int*)phist, (const unsigned int*)pvals, p.seed_vals, skeys, keys, p.keys_per_image,
+                     (int)std::min<size_t>(kSpillCap, p.keys_per_image));
     if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
     if ((rc = check_launch())) return rc;
     e = launch_pdl(decode_tail_kernel, dim3(B * kTailHelpers), dim3(kFinThreads), p.tail_smem, st,
-                   heat, B, 0, kTailHelpers, hdr, ghist, keys, p.keys_per_image, (const u64*)skeys, C * p.sw_bands, phist,
+                   heat, B, 0, kTailHelpers, hdr, ghist, keys, p.keys_per_image, (const u64*)skeys, C * p.sw_bands,
+                   (int)std::min<size_t>(kSpillCap, p.keys_per_image), phist,
                    p.Wp, p.band_rows, p.tail_sub_rows, div_strips, p.bands,
                    wh, reg, C, H, W, K, down_ratio, flags, boxes, scores, classes, inds);
     if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
@@ -1394,7 +1422,7 @@ extern "C" int ctdet_decode(const float* heat, const float* wh, const float* reg
   if ((rc = check_launch())) return rc;
   {
     cudaError_t e = launch_pdl(decode_tail_kernel, dim3(B), dim3(kFinThreads), p.tail_smem, st,
-                               heat, B, 1, 1, hdr, ghist, keys, p.keys_per_image, (const u64*)nullptr, 0, (unsigned int*)nullptr,
+                               heat, B, 1, 1, hdr, ghist, keys, p.keys_per_image, (const u64*)nullptr, 0, 0, (unsigned int*)nullptr,
                                p.Wp, p.band_rows, p.tail_sub_rows, div_strips, p.bands,
                                wh, reg, C, H, W, K, down_ratio, flags, boxes, scores, classes, inds);
     if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }

@@ -79,7 +79,8 @@ __global__ void __launch_bounds__(kHdThreads, 1)
 head_decode_kernel(const float* __restrict__ feat, const float* __restrict__ weight, const float* __restrict__ bias,
                    int B, int Cf, int C, int H, int K, int stages, int force,
                    DecodeHeader* __restrict__ hdrs, unsigned int* __restrict__ phists, unsigned int* __restrict__ pvals_all,
-                   u64* __restrict__ skeys, float* __restrict__ logits_out) {
+                   u64* __restrict__ skeys, u64* __restrict__ spill_all, size_t keys_per_image, int spill_cap,
+                   float* __restrict__ logits_out) {
   extern __shared__ __align__(1024) uint8_t hd_smem[];
   __shared__ HeadDecodeBarriers bars;
   __shared__ uint32_t s_tmem;
@@ -228,7 +229,14 @@ head_decode_kernel(const float* __restrict__ feat, const float* __restrict__ wei
         if (is_peak(v, nbm, true)) {
           const unsigned int pos = atomicAdd(&s_cnt[half], 1u);
           const uint32_t flat = (uint32_t)((c * H + t) * kHdW + x);
-          if (pos < (unsigned)kTileCap) s_keys[half * kTileCap + pos] = ((u64)float_to_ordered(v) << 32) | (u64)(0xffffffffu - flat);
+          const u64 key = ((u64)float_to_ordered(v) << 32) | (u64)(0xffffffffu - flat);
+          if (pos < (unsigned)kTileCap) {
+            s_keys[half * kTileCap + pos] = key;
+          } else {                                           // the segment is full: the image's spill list (decode_stream_kernel's)
+            const unsigned int sp = atomicAdd(&hdrs[b].s_count, 1u);
+            if (sp < (unsigned)spill_cap) spill_all[(size_t)b * keys_per_image + sp] = key;
+            else hdrs[b].staged = 1u;                        // that one is full too: exact fall-back
+          }
         }
       }
       hd_bar_half(half);
@@ -237,7 +245,6 @@ head_decode_kernel(const float* __restrict__ feat, const float* __restrict__ wei
         u64* dst = skeys + ((size_t)(b * H + t) * 2 + half) * kTileCap;
         dst[lane] = (unsigned)lane < cnt ? s_keys[half * kTileCap + lane] : 0ull;
         dst[lane + 32] = (unsigned)(lane + 32) < cnt ? s_keys[half * kTileCap + lane + 32] : 0ull;
-        if (cnt > (unsigned)kTileCap && lane == 0) hdrs[b].staged = 1u;      // ties / plateaus at the bound: exact fall-back
         __syncwarp();
         if (lane == 0) s_cnt[half] = 0u;
       }
@@ -439,18 +446,20 @@ extern "C" int ctdet_head_decode_fused(const float* feat, const float* weight, c
   u64* skeys = reinterpret_cast<u64*>(q); q += p.skeys_bytes;
   u64* keys = reinterpret_cast<u64*>(q); q += p.staged_keys_bytes;
   float* logits = logits_out ? logits_out : reinterpret_cast<float*>(q);
+  const int spill_cap = (int)std::min<size_t>(kSpillCap, p.dec.keys_per_image);
   head_decode_kernel<0><<<grid_seed, kHdThreads, p.smem, st>>>(feat, weight, bias, B, Cf, C, H, K, p.stages, 0, hdr, phist,
-                                                                pvals, skeys, logits);
+                                                                pvals, skeys, keys, p.dec.keys_per_image, spill_cap, logits);
   if ((rc = check_launch())) return rc;
   head_decode_kernel<1><<<grid_rows, kHdThreads, p.smem, st>>>(feat, weight, bias, B, Cf, C, H, K, p.stages, 0, hdr, phist,
-                                                                pvals, skeys, logits);
+                                                                pvals, skeys, keys, p.dec.keys_per_image, spill_cap, logits);
   if ((rc = check_launch())) return rc;
   head_decode_kernel<2><<<grid_rows, kHdThreads, p.smem, st>>>(feat, weight, bias, B, Cf, C, H, K, p.stages,
-                                                                logits_out ? 1 : 0, hdr, phist, pvals, skeys, logits);
+                                                                logits_out ? 1 : 0, hdr, phist, pvals, skeys, keys,
+                                                                p.dec.keys_per_image, spill_cap, logits);
   if ((rc = check_launch())) return rc;
   const FastDiv div_strips((uint32_t)p.dec.strips);
   decode_tail_kernel<<<dim3(B * kTailHelpers), dim3(kFinThreads), p.tail_smem, st>>>(
-      logits, B, 0, kTailHelpers, hdr, ghist, keys, p.dec.keys_per_image, (const u64*)skeys, 2 * H, phist,
+      logits, B, 0, kTailHelpers, hdr, ghist, keys, p.dec.keys_per_image, (const u64*)skeys, 2 * H, spill_cap, phist,
       p.dec.Wp, p.dec.band_rows, p.dec.tail_sub_rows, div_strips, p.dec.bands,
       wh, reg, C, H, W, K, down_ratio, flags | CTDET_DECODE_LOGITS, boxes, scores, classes, inds);
   return check_launch();

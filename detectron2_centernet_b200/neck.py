@@ -201,3 +201,18 @@ class CtdetHead(nn.Module):
 
     def forward(self, x):
         return {name: getattr(self, name.lower())(x) for name in self.heads}
+
+    def decode(self, x, down_ratio=4, K=100, fuse=True):
+        """Eval path `ctdet_decode(hm.sigmoid_(), wh, reg, K)` (centernet.py:151-166) on the heads of `x` for a batch: with
+        `fuse` and shapes `decode.head_decode_fusable` takes, the hm branch's final 1x1 convolution runs inside the decode
+        (`hm_head_decode_batch`: the logits never reach HBM); otherwise forward() + ctdet_decode_batch(logits=True).
+        Returns boxes, scores, classes, inds."""
+        from . import decode as D
+        hm = self.hm
+        wh, reg = self.wh(x), (self.reg(x) if "reg" in self.heads else None)
+        last = hm[-1] if isinstance(hm, nn.Sequential) else None
+        if (fuse and last is not None and last.kernel_size == (1, 1) and
+                D.head_decode_fusable(last.in_channels, last.out_channels, x.shape[2], x.shape[3])):
+            feat = hm[:-1](x)
+            return D.hm_head_decode_batch(feat, last.weight, last.bias, wh, reg, down_ratio=down_ratio, K=K)
+        return D.ctdet_decode_batch(hm(x), wh, reg, down_ratio=down_ratio, K=K, logits=True)

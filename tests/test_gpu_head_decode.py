@@ -101,6 +101,23 @@ def test_plateaus_take_the_exact_fallback():
         assert torch.equal(a, r), (name, "no logits_out")
 
 
+def test_object_concentrated_scores_use_the_spill_list():
+    """A hot region (many cells far above the rest in many classes): its rows' (row, class half) segments hold more than 64
+    keys -> the surplus goes to the image's spill list; still bit-equal to ctdet_decode on the kernel's logits."""
+    from detectron2_centernet_b200 import decode as D
+    B, Cf, C, H, K = 2, 64, 32, 64, 100
+    feat, w, b, wh, reg = _setup(31, B, Cf, C, H, peaks=0)
+    g = torch.Generator(device="cpu").manual_seed(2)
+    feat[1, :, 20:26, 10:90] *= 1.0 + 2.0 * torch.rand(Cf, 6, 80, generator=g).to(DEV)
+    out = D.hm_head_decode_batch(feat, w, b, wh, reg, down_ratio=4, K=K, return_logits=True)
+    want = D.ctdet_decode_batch(out[4], wh, reg, down_ratio=4, K=K, logits=True)
+    for name, a, r in zip(("boxes", "scores", "classes", "inds"), out[:4], want):
+        assert torch.equal(a, r), name
+    out2 = D.hm_head_decode_batch(feat, w, b, wh, reg, down_ratio=4, K=K)
+    for name, a, r in zip(("boxes", "scores", "classes", "inds"), out2, want):
+        assert torch.equal(a, r), (name, "second call")
+
+
 def test_two_calls_in_a_row_and_shape_changes_share_the_workspace():
     from detectron2_centernet_b200 import decode as D
     for i, (B, Cf, C, H, K) in enumerate([(2, 64, 16, 40, 100), (2, 64, 16, 40, 100), (2, 128, 32, 8, 50), (2, 64, 16, 40, 100)]):
@@ -122,3 +139,29 @@ def test_unsupported_shapes_are_rejected():
     feat = torch.zeros(1, 64, 4, 64, device=DEV)
     with pytest.raises(NotImplementedError):
         D.hm_head_decode_batch(feat, torch.zeros(16, 64, device=DEV), None, torch.zeros(1, 2, 4, 64, device=DEV))
+
+
+def test_ctdet_head_decode_method_fused_vs_unfused():
+    """`CtdetHead.decode` (the eval path of centernet.py:151-166 on the head modules): the fused and the unfused route agree
+    on the planted, well-separated top detections (classes / cells equal, scores to 2e-3: bf16 operands)."""
+    from detectron2_centernet_b200 import neck as N
+    torch.manual_seed(7)
+    head = N.CtdetHead(64, 80, 256).to(DEV).eval()
+    x = torch.randn(2, 64, 16, 128, device=DEV)
+    with torch.no_grad():
+        last = head.hm[-1]
+        feat = head.hm[:-1](x)
+        for b in range(2):                                     # plant 12 peaks per image through the last layer's weights
+            for i in range(12):
+                c, yy, xx = (7 * i + b) % 80, (5 * i + 1) % 16, (19 * i + 3) % 128
+                # raise the 3x3-conv output so that class c's logit at the cell is high: solve roughly through the bias of hm[0]
+                feat[b, :, yy, xx] += torch.relu(last.weight[c, :, 0, 0]) * (40.0 + 5 * i)
+        wh, reg = head.wh(x), head.reg(x)
+        from detectron2_centernet_b200 import decode as D
+        fused = D.hm_head_decode_batch(feat, last.weight, last.bias, wh, reg, down_ratio=4, K=50)
+        plain = D.ctdet_decode_batch(last(feat), wh, reg, down_ratio=4, K=50, logits=True)
+        assert torch.equal(fused[2][:, :8], plain[2][:, :8]) and torch.equal(fused[3][:, :8], plain[3][:, :8])
+        assert float((fused[1][:, :8] - plain[1][:, :8]).abs().max()) <= 2e-3
+        a, b_ = head.decode(x, K=50), head.decode(x, K=50, fuse=False)
+        assert a[1].shape == b_[1].shape == (2, 50)
+        assert float((a[1][:, 0] - b_[1][:, 0]).abs().max()) <= 2e-3

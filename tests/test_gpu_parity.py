@@ -472,6 +472,31 @@ def test_decode_concentrated_logits_refined_seed_bound():
         assert np.array_equal(g.cpu().numpy(), r)
 
 
+def test_decode_class_concentrated_scores_use_the_spill_list():
+    """Scores concentrated in a few classes (what a trained head emits: a class prior per channel) and around a few
+    objects: the candidates above the sampled bound pile into a few tiles, more than a tile's 64-key segment holds.
+    Those tiles spill into the image's spill list (one atomic per overflowing tile) instead of handing the whole image to
+    the 4x slower staged path; results stay exact.  Image 2 is a plateau: its spill list overflows too -> staged path."""
+    from detectron2_centernet_b200 import decode as D
+    B, C, H, W, K = 3, 80, 128, 128, 100
+    rng = np.random.default_rng(23)
+    hm = (0.7 * rng.standard_normal((B, C, H, W)) + (-2.19 + 0.6 * rng.standard_normal((1, C, 1, 1)))).astype(np.float32)
+    hm[1, :, 40:56, 30:70] += 2.0                                   # a hot region on top of it
+    hm[2] = -2.19
+    wh = rng.uniform(0, 64, (B, 2, H, W)).astype(np.float32)
+    reg = rng.uniform(0, 1, (B, 2, H, W)).astype(np.float32)
+    ref = O.decode(hm, wh, reg, 4, K, logits=True)
+    for _ in range(2):                                              # twice: the spill counter must be left at zero
+        out = D.ctdet_decode_batch(*_cuda(hm, wh, reg), down_ratio=4, K=K, logits=True)
+        assert np.array_equal(out[2].cpu().numpy(), ref[2]) and np.array_equal(out[3].cpu().numpy(), ref[3])
+        assert np.array_equal(out[0].cpu().numpy(), ref[0])
+    heat = S.sigmoid_clamp(hm)
+    out = D.ctdet_decode_batch(*_cuda(heat, wh, reg), down_ratio=4, K=K)
+    ref = O.decode(heat, wh, reg, 4, K)
+    for g, r in zip(out, ref):
+        assert np.array_equal(g.cpu().numpy(), r)
+
+
 def test_nms_topk_gather_dropins(inputs):
     from detectron2_centernet_b200 import decode as D
     bl, cl, hm, wh, reg, (B, C, H, W, K, full) = inputs("dense_small")
