@@ -26,9 +26,10 @@ namespace ctdet {
 constexpr int kHdProducerWarps = 8, kHdEpiWarps = 8;
 constexpr int kHdThreads = (kHdProducerWarps + kHdEpiWarps + 1) * 32;
 constexpr int kHdMaxStages = 6;
-constexpr int kHdMaxRows = 512;               // GEMM rows per CTA (row list in shared memory)
+constexpr int kHdMaxRows = 256;               // GEMM rows per CTA (row list in shared memory)
 constexpr int kHdSeedPeriod = 32;             // one sampled row per 32 map rows
 constexpr int kHdW = 128;                     // map width this kernel takes: a row is one UMMA M tile
+constexpr int kHdListCap = 1024;              // mode 3: scores of a run's emitted keys kept per class half (the running bound)
 
 struct HeadDecodeBarriers {
   uint64_t full[kHdMaxStages], empty[kHdMaxStages];   // A ring (producers -> MMA)
@@ -51,28 +52,98 @@ __device__ __forceinline__ void hd_bar_half(int half) {      // the 4 epilogue w
   asm volatile("bar.sync %0, 128;" ::"r"(1 + half) : "memory");
 }
 
-// max over the existing 3x3 neighbours of (c, t, x) in the window (rows t-1 / t+1 only when `up` / `down`)
-__device__ __forceinline__ float hd_neighbour_max(const float* win, int C, int c, int t, int x, bool up, bool down) {
-  const float NEG = -__int_as_float(0x7f800000);
-  const float* r1 = win + ((size_t)(t % 3) * C + c) * kHdW + x;
-  const bool l = x > 0, r = x < kHdW - 1;
-  float m = NEG;
-  if (l) m = fmaxf(m, r1[-1]);
-  if (r) m = fmaxf(m, r1[1]);
-  if (up) {
-    const float* r0 = win + ((size_t)((t + 2) % 3) * C + c) * kHdW + x;
-    m = fmaxf(m, r0[0]);
-    if (l) m = fmaxf(m, r0[-1]);
-    if (r) m = fmaxf(m, r0[1]);
+// K-th largest of list[0, n) (n >= K) by the 128 threads of one class half (uniform call): MSB-first radix select,
+// 8 bits per round over a 256-bin shared-memory histogram; three named barriers per round.  Every thread returns the value.
+__device__ __forceinline__ unsigned int hd_kth_largest(const unsigned int* list, int n, int K, unsigned int* hist /*[256]*/,
+                                                       unsigned int* sel /*[2]*/, int half, int tih) {
+  unsigned int prefix = 0u;
+  int need = K;
+  const int lane = tih & 31;
+#pragma unroll 1
+  for (int shift = 24; shift >= 0; shift -= 8) {
+    hist[tih] = 0u;
+    hist[tih + 128] = 0u;
+    hd_bar_half(half);
+    for (int i = tih; i < n; i += 128) {
+      const unsigned int v = list[i];
+      if (shift == 24 || (v >> (shift + 8)) == (prefix >> (shift + 8))) atomicAdd(&hist[(v >> shift) & 255u], 1u);
+    }
+    hd_bar_half(half);
+    if (tih < 32) {                                          // bins 255 - 8 lane .. 248 - 8 lane, descending
+      unsigned int h[8], sum = 0u;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) { h[k] = hist[255 - 8 * lane - k]; sum += h[k]; }
+      unsigned int incl = sum;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { const unsigned int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+      const unsigned int excl = incl - sum;
+      if (excl < (unsigned)need && incl >= (unsigned)need) {  // exactly one lane
+        unsigned int acc = excl;
+        int bin = 255 - 8 * lane;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          if (acc + h[k] >= (unsigned)need) { bin = 255 - 8 * lane - k; break; }
+          acc += h[k];
+        }
+        sel[0] = (unsigned int)bin;
+        sel[1] = (unsigned int)need - acc;                   // rank inside the bin
+      }
+    }
+    hd_bar_half(half);
+    prefix |= sel[0] << shift;
+    need = (int)sel[1];
   }
-  if (down) {
-    const float* r2 = win + ((size_t)((t + 1) % 3) * C + c) * kHdW + x;
-    m = fmaxf(m, r2[0]);
-    if (l) m = fmaxf(m, r2[-1]);
-    if (r) m = fmaxf(m, r2[1]);
-  }
-  return m;
+  return prefix;
 }
+// keeps the entries >= thr, in place; returns how many (one warp)
+__device__ __forceinline__ int hd_compact_ge(unsigned int* list, int n, unsigned int thr, int lane) {
+  int w = 0;
+  for (int i0 = 0; i0 < n; i0 += 32) {
+    const int i = i0 + lane;
+    const unsigned int v = i < n ? list[i] : 0u;
+    const bool keep = i < n && v >= thr;
+    const unsigned int ball = __ballot_sync(0xffffffffu, keep);
+    __syncwarp();
+    if (keep) list[w + __popc(ball & ((1u << lane) - 1u))] = v;
+    w += __popc(ball);
+    __syncwarp();
+  }
+  return w;
+}
+
+// The 3x3 neighbourhood of this thread's cell of row t in the window, as nine float indices relative to the cell of class
+// c_lo (class k adds k * 128): computed once per row.  The max below includes the centre (v >= that max <=> v >= every
+// neighbour, and the tie rule only looks at a max above v) and reads nine UNCONDITIONAL loads from clamped addresses -- a
+// missing row / column (map border) re-reads the centre row / column -- so that all nine are in flight together and a cell
+// costs ~35 instructions (the first form, addresses rebuilt and one branch per load, cost ~120: 15 us for a full row).
+struct HdNbr { int a0, a1, a2, b0, b1, b2, c0, c1, c2; };
+__device__ __forceinline__ HdNbr hd_nbr(int C, int c_lo, int t, int x, bool up, bool down) {
+  const int xl = x > 0 ? x - 1 : x, xr = x < kHdW - 1 ? x + 1 : x;
+  const int r1 = ((t % 3) * C + c_lo) * kHdW;
+  const int r0 = up ? (((t + 2) % 3) * C + c_lo) * kHdW : r1;
+  const int r2 = down ? (((t + 1) % 3) * C + c_lo) * kHdW : r1;
+  HdNbr n;
+  n.a0 = r0 + xl; n.a1 = r0 + x; n.a2 = r0 + xr;
+  n.b0 = r1 + xl; n.b1 = r1 + x; n.b2 = r1 + xr;
+  n.c0 = r2 + xl; n.c1 = r2 + x; n.c2 = r2 + xr;
+  return n;
+}
+__device__ __forceinline__ float hd_max9(const float* win, const HdNbr& n, int k, float& centre) {
+  const float* w = win + k * kHdW;
+  const float a0 = w[n.a0], a1 = w[n.a1], a2 = w[n.a2], b0 = w[n.b0], b1 = w[n.b1], b2 = w[n.b2], c0 = w[n.c0], c1 = w[n.c1],
+              c2 = w[n.c2];
+  centre = b1;
+  return fmaxf(fmaxf(fmaxf(a0, a1), fmaxf(a2, b0)), fmaxf(fmaxf(b1, b2), fmaxf(fmaxf(c0, c1), c2)));
+}
+
+#ifdef CTDET_HD_TIMING
+__device__ unsigned long long g_hd_ts[16];      // CTA 0, half 0, leader lane: cycles per phase, summed over the rows (+ counters)
+#define HD_T(i, expr) do { if (blockIdx.x == 0 && half == 0 && quarter == 0 && lane == 0) g_hd_ts[i] += (unsigned long long)(expr); } while (0)
+#define HD_CLK() clock64()
+#else
+#define HD_T(i, expr) do {} while (0)
+#define HD_CLK() 0ll
+#endif
 
 template <int kMode>
 __global__ void __launch_bounds__(kHdThreads, 1)
@@ -87,6 +158,8 @@ head_decode_kernel(const float* __restrict__ feat, const float* __restrict__ wei
   __shared__ int s_nrows;
   __shared__ unsigned int s_cnt[2], s_lastf[2];
   __shared__ unsigned int s_sub[2][32];
+  __shared__ unsigned int s_thr[2], s_nl[2];                // mode 3: running bound (ordered; 0 = none yet) and list length per half
+  __shared__ unsigned int s_sel[2][2];                      // mode 3: radix-select hand-over per half
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int KB = Cf / kBK;
@@ -101,6 +174,8 @@ head_decode_kernel(const float* __restrict__ feat, const float* __restrict__ wei
   u64* s_keys = reinterpret_cast<u64*>(win + (size_t)3 * C * kHdW);       // [2 halves][kTileCap]
   unsigned int* s_best = reinterpret_cast<unsigned int*>(s_keys + 2 * kTileCap);   // [C] best sampled peak of the class
   int* s_g = reinterpret_cast<int*>(s_best + C);            // [kHdMaxRows] GEMM rows of this CTA: b * H + y
+  unsigned int* s_list = reinterpret_cast<unsigned int*>(s_g + 2 * kHdMaxRows);   // [2][kHdListCap] (mode 3)
+  unsigned int* s_hist = s_list + 2 * kHdListCap;          // [2][256] (mode 3)
   int* s_fl = s_g + kHdMaxRows;                             // 1: test row y-1 now, 2: test row y now (last map row),
                                                             // 4: first GEMM row of a run, bits 8..: sample index (mode 0)
   // ---- this CTA's rows: contiguous runs of tested rows, each with its halo rows inside the same image ----
@@ -135,10 +210,18 @@ head_decode_kernel(const float* __restrict__ feat, const float* __restrict__ wei
       }
     }
     s_nrows = n;
-    s_cnt[0] = 0u; s_cnt[1] = 0u;
+    s_cnt[0] = 0u; s_cnt[1] = 0u; s_thr[0] = 0u; s_thr[1] = 0u; s_nl[0] = 0u; s_nl[1] = 0u;
     for (int s = 0; s < kHdMaxStages; ++s) { dcn_mbar_init(&bars.full[s], kHdProducerWarps); dcn_mbar_init(&bars.empty[s], 1); }
     for (int i = 0; i < 2; ++i) { dcn_mbar_init(&bars.acc_full[i], 1); dcn_mbar_init(&bars.acc_empty[i], kHdEpiWarps); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (kMode == 2 && blockIdx.x == 0) {
+    // behind a mode-3 sweep: the image's lower bound of all emitted keys was collected as max(~bound) (the header is zero on
+    // entry); the tail kernel wants it in thr_ord
+    for (int b = tid; b < B; b += kHdThreads) {
+      const unsigned int inv = hdrs[b].pad[0];
+      if (inv != 0u) { hdrs[b].thr_ord = ~inv; hdrs[b].pad[0] = 0u; }
+    }
   }
   __syncthreads();
   const int n_rows = s_nrows;
@@ -216,16 +299,18 @@ head_decode_kernel(const float* __restrict__ feat, const float* __restrict__ wei
     unsigned int thr_ord = 0u;
     float thv = 0.f;
     bool live = false;                                       // mode 1: the image has a bound (else the tail's fall-back owns it)
+    int run_b = 0, rows_in_run = 0, tested_in_run = 0;      // mode 3
 
     // mode 1: 3x3 test of the flagged cells of row t, keys -> the (row, half) segment, always written in full
     auto sweep_row = [&](int b, int t, bool up, bool down, unsigned long long m) {
       hd_bar_half(half);                                     // the window rows are stored; the staging area is clean
+      const HdNbr nb = hd_nbr(C, c_lo, t, x, up, down);
       while (m) {
         const int k = __ffsll((long long)m) - 1;
         m &= m - 1ull;
         const int c = c_lo + k;
-        const float v = win[((size_t)(t % 3) * C + c) * kHdW + x];
-        const float nbm = hd_neighbour_max(win, C, c, t, x, up, down);
+        float v;
+        const float nbm = hd_max9(win, nb, k, v);
         if (is_peak(v, nbm, true)) {
           const unsigned int pos = atomicAdd(&s_cnt[half], 1u);
           const uint32_t flat = (uint32_t)((c * H + t) * kHdW + x);
@@ -249,13 +334,130 @@ head_decode_kernel(const float* __restrict__ feat, const float* __restrict__ wei
         if (lane == 0) s_cnt[half] = 0u;
       }
     };
+    // mode 3: the sweep without a seed launch.  The bound is the CTA-half's own: the K-th best peak among the rows of the
+    // run it has tested so far (a subset of the image's peaks of these classes, so a valid lower bound of the image's K-th
+    // best), raised after every row.  The first tested row of a run has no bound: every cell is peak-tested, the peaks'
+    // scores are listed, the leader warp selects the K-th best, and only then are the keys emitted.
+    unsigned int* list = s_list + half * kHdListCap;
+    // the keys of this thread's cells `bits` of row t -> the half's staging area (the surplus beyond the 64-key segment to
+    // the image's spill list); ONE shared-memory atomic per warp (same-address atomics serialise: ~570 of them per row and
+    // half cost 75 k cycles in the first form of this code)
+    auto stage_keys = [&](int b, int t, unsigned long long bits) {
+      const int cnt = __popcll(bits);
+      int incl = cnt;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { const int u = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += u; }
+      unsigned int base = 0u;
+      if (lane == 31 && incl) base = atomicAdd(&s_cnt[half], (unsigned int)incl);
+      unsigned int pos = __shfl_sync(0xffffffffu, base, 31) + (unsigned int)(incl - cnt);
+      while (bits) {
+        const int k = __ffsll((long long)bits) - 1;
+        bits &= bits - 1ull;
+        const int c = c_lo + k;
+        const float v = win[((size_t)(t % 3) * C + c) * kHdW + x];
+        const uint32_t flat = (uint32_t)((c * H + t) * kHdW + x);
+        const u64 key = ((u64)float_to_ordered(v) << 32) | (u64)(0xffffffffu - flat);
+        if (pos < (unsigned)kTileCap) {
+          s_keys[half * kTileCap + pos] = key;
+        } else {
+          const unsigned int sp = atomicAdd(&hdrs[b].s_count, 1u);
+          if (sp < (unsigned)spill_cap) spill_all[(size_t)b * keys_per_image + sp] = key;
+          else hdrs[b].staged = 1u;
+        }
+        ++pos;
+      }
+    };
+    auto running_row = [&](int b, int t, bool up, bool down, unsigned long long m, bool first_of_run) {
+      long long c0 = HD_CLK();
+      const int tih = quarter * 32 + lane;
+      hd_bar_half(half);                                     // window rows stored; staging clean; s_thr / the list up to date
+      HD_T(0, HD_CLK() - c0); c0 = HD_CLK();
+      const unsigned int thr_now = s_thr[half];              // uniform over the half
+      HD_T(8, __popcll(m)); HD_T(9, 1); if (thr_now == 0u) HD_T(10, 1);
+      unsigned long long pk = 0ull;                          // this thread's peaks >= the bound
+      const HdNbr nb = hd_nbr(C, c_lo, t, x, up, down);
+      while (m) {
+        const int k = __ffsll((long long)m) - 1;
+        m &= m - 1ull;
+        float v;
+        const float nbm = hd_max9(win, nb, k, v);
+        if (float_to_ordered(v) < thr_now) continue;
+        // a centre more than 1e-3 below its largest neighbour cannot share its fp32 probability unless one of the clamps of
+        // centernet.py:161 (|logit| > 9.2) or the saturation towards 1 is near: skip the two sigmoids of the tie rule
+        if (nbm - v > 1e-3f && v > -9.f && v < 5.f) continue;
+        if (is_peak(v, nbm, true)) pk |= 1ull << k;
+      }
+      {                                                      // their scores -> the run's list (one atomic per warp)
+        const int cnt = __popcll(pk);
+        int incl = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int u = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += u; }
+        unsigned int base = 0u;
+        if (lane == 31 && incl) base = atomicAdd(&s_nl[half], (unsigned int)incl);
+        unsigned int idx = __shfl_sync(0xffffffffu, base, 31) + (unsigned int)(incl - cnt);
+        unsigned long long q = pk;
+        while (q) {
+          const int k = __ffsll((long long)q) - 1;
+          q &= q - 1ull;
+          if (idx < (unsigned)kHdListCap)                    // (a truncated list still bounds from below)
+            list[idx] = float_to_ordered(win[nb.b1 + k * kHdW]);
+          ++idx;
+        }
+      }
+      if (thr_now != 0u) stage_keys(b, t, pk);
+      HD_T(1, HD_CLK() - c0); c0 = HD_CLK();
+      hd_bar_half(half);                                     // list and staging complete
+      HD_T(3, HD_CLK() - c0); c0 = HD_CLK();
+      // raise (or find) the bound: K-th best of everything listed so far in this run.  With a bound in hand only when the
+      // list has doubled (the bound stays valid, just a little stale); without one as soon as K peaks are listed.
+      const int n = (int)min(s_nl[half], (unsigned int)kHdListCap);     // uniform
+      const bool select = thr_now == 0u ? n >= K : n >= min(2 * K, kHdListCap);
+      unsigned int thr_emit = thr_now;
+      if (select) {
+        const unsigned int th = hd_kth_largest(list, n, K, s_hist + half * 256, s_sel[half], half, tih);
+        if (quarter == 0) {
+          const int w = hd_compact_ge(list, n, th, lane);
+          if (lane == 0) { s_thr[half] = th; s_nl[half] = (unsigned int)w; }
+        }
+        if (thr_now == 0u) thr_emit = th;
+      } else if (tih == 0) {
+        s_nl[half] = (unsigned int)n;
+      }
+      HD_T(5, HD_CLK() - c0); c0 = HD_CLK();
+      if (thr_now == 0u) {                                   // uniform: the keys of this row were held back until now
+        unsigned long long q = pk, keep = 0ull;
+        while (q) {
+          const int k = __ffsll((long long)q) - 1;
+          q &= q - 1ull;
+          if (float_to_ordered(win[nb.b1 + k * kHdW]) >= thr_emit) keep |= 1ull << k;
+        }
+        stage_keys(b, t, keep);
+        hd_bar_half(half);
+        HD_T(2, HD_CLK() - c0); c0 = HD_CLK();
+      }
+      if (quarter == 0) {
+        const unsigned int cnt = s_cnt[half];
+        HD_T(11, cnt); HD_T(12, n);
+        u64* dst = skeys + ((size_t)(b * H + t) * 2 + half) * kTileCap;
+        dst[lane] = (unsigned)lane < cnt ? s_keys[half * kTileCap + lane] : 0ull;
+        dst[lane + 32] = (unsigned)(lane + 32) < cnt ? s_keys[half * kTileCap + lane + 32] : 0ull;
+        __syncwarp();
+        if (lane == 0) {
+          s_cnt[half] = 0u;
+          // every key this run emits is >= the bound of its first row (0: everything was emitted): the tail's histogram base
+          if (first_of_run) atomicMax(&hdrs[b].pad[0], ~thr_emit);
+        }
+        HD_T(4, HD_CLK() - c0);
+      }
+    };
     // mode 0: the best 3x3 peak of every class in row t -> sample histogram; the image's last half derives the bound
     auto seed_row = [&](int b, int j, int t, bool up, bool down) {
       hd_bar_half(half);
+      const HdNbr nb = hd_nbr(C, c_lo, t, x, up, down);
       for (int k = 0; k < ch; ++k) {
         const int c = c_lo + k;
-        const float v = win[((size_t)(t % 3) * C + c) * kHdW + x];
-        const float nbm = hd_neighbour_max(win, C, c, t, x, up, down);
+        float v;
+        const float nbm = hd_max9(win, nb, k, v);
         unsigned int val = (v >= nbm) ? float_to_ordered(v) : 0u;             // (a strict subset of the peaks is still valid)
         val = __reduce_max_sync(0xffffffffu, val);
         if (lane == 0 && val) atomicMax(&s_best[c], val);
@@ -296,6 +498,17 @@ head_decode_kernel(const float* __restrict__ feat, const float* __restrict__ wei
       const int ab = it & 1;
       m_prev = m_cur;
       m_cur = 0ull;
+      if (kMode == 3) {
+        if (fl & 4) {
+          // a run that ends without a bound saw fewer than K peaks: the image may hold fewer than K in all -> exact path
+          if (it > 0 && quarter == 0 && lane == 0 && s_thr[half] == 0u) hdrs[run_b].staged = 1u;
+          run_b = b; rows_in_run = 0; tested_in_run = 0;
+          if (quarter == 0 && lane == 0) { s_thr[half] = 0u; s_nl[half] = 0u; }
+        }
+        // the first rows of a run are stored before any barrier separates them from the reset above: no bound for them
+        thr_ord = rows_in_run < 3 ? 0u : *((volatile unsigned int*)&s_thr[half]);
+        ++rows_in_run;
+      }
       if (fl & 4) {
         m_prev = 0ull;
         if (kMode == 1) {
@@ -318,6 +531,7 @@ head_decode_kernel(const float* __restrict__ feat, const float* __restrict__ wei
           } else {
             win[((size_t)(y % 3) * C + c) * kHdW + x] = l;
             if (kMode == 1 && live && l >= thv && float_to_ordered(l) >= thr_ord) m_cur |= 1ull << (c0 + k);
+            if (kMode == 3 && float_to_ordered(l) >= thr_ord) m_cur |= 1ull << (c0 + k);
           }
         }
       }
@@ -328,11 +542,16 @@ head_decode_kernel(const float* __restrict__ feat, const float* __restrict__ wei
         if (fl & 1) sweep_row(b, y - 1, y - 2 >= 0, true, m_prev);
         if (fl & 2) sweep_row(b, y, y - 1 >= 0, false, m_cur);
       }
+      if (kMode == 3) {
+        if (fl & 1) { running_row(b, y - 1, y - 2 >= 0, true, m_prev, tested_in_run == 0); ++tested_in_run; }
+        if (fl & 2) { running_row(b, y, y - 1 >= 0, false, m_cur, tested_in_run == 0); ++tested_in_run; }
+      }
       if (kMode == 0) {
         if (fl & 1) seed_row(b, fl >> 8, y - 1, y - 2 >= 0, true);
         if (fl & 2) seed_row(b, fl >> 8, y, y - 1 >= 0, false);
       }
     }
+    if (kMode == 3 && quarter == 0 && lane == 0 && s_thr[half] == 0u) hdrs[run_b].staged = 1u;
   } else {
     // ===================================== MMA issuer ==============================================
     if (lane == 0) {
@@ -376,7 +595,7 @@ static HeadDecodePlan make_head_decode_plan(int B, int Cf, int C, int H, int W, 
   p.dec = make_plan(B, C, H, W, K);
   p.ns = hd_seed_rows(H);
   const size_t fixed = 1024 + (size_t)(Cf / kBK) * C * 128 + (size_t)C * 4 + (size_t)3 * C * kHdW * 4 +
-                       (size_t)2 * kTileCap * 8 + (size_t)C * 4 + (size_t)2 * kHdMaxRows * 4;
+                       (size_t)2 * kTileCap * 8 + (size_t)C * 4 + (size_t)2 * kHdMaxRows * 4 + (size_t)2 * kHdListCap * 4 + (size_t)2 * 256 * 4;
   int st = kHdMaxStages;
   while (st > 2 && fixed + (size_t)st * (kTileM * 128) > 226 * 1024) --st;
   p.stages = st;
@@ -435,6 +654,7 @@ extern "C" int ctdet_head_decode_fused(const float* feat, const float* weight, c
   cudaError_t e = cudaFuncSetAttribute(head_decode_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(head_decode_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(head_decode_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(head_decode_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(decode_tail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.tail_smem);
   if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
   unsigned char* base = reinterpret_cast<unsigned char*>(workspace);
@@ -447,11 +667,22 @@ extern "C" int ctdet_head_decode_fused(const float* feat, const float* weight, c
   u64* keys = reinterpret_cast<u64*>(q); q += p.staged_keys_bytes;
   float* logits = logits_out ? logits_out : reinterpret_cast<float*>(q);
   const int spill_cap = (int)std::min<size_t>(kSpillCap, p.dec.keys_per_image);
-  head_decode_kernel<0><<<grid_seed, kHdThreads, p.smem, st>>>(feat, weight, bias, B, Cf, C, H, K, p.stages, 0, hdr, phist,
-                                                                pvals, skeys, keys, p.dec.keys_per_image, spill_cap, logits);
-  if ((rc = check_launch())) return rc;
-  head_decode_kernel<1><<<grid_rows, kHdThreads, p.smem, st>>>(feat, weight, bias, B, Cf, C, H, K, p.stages, 0, hdr, phist,
-                                                                pvals, skeys, keys, p.dec.keys_per_image, spill_cap, logits);
+  // default: the sampled bound -- seed launch (mode 0) + sweep (mode 1): 182 us at B = 32.  CTDET_HEAD_DECODE_SEED=0 (read
+  // once) selects the sweep with a running bound per CTA (mode 3, no seed launch): parity-green, but every run starts with a
+  // row whose 10 240 cells are all peak-tested and whose keys wait for a selection, the MMA can only run two rows ahead, and
+  // the stall is never recovered: 236 us
+  static int with_seed = -1;
+  if (with_seed < 0) { const char* ev = getenv("CTDET_HEAD_DECODE_SEED"); with_seed = ev ? (atoi(ev) != 0) : 1; }
+  if (with_seed) {
+    head_decode_kernel<0><<<grid_seed, kHdThreads, p.smem, st>>>(feat, weight, bias, B, Cf, C, H, K, p.stages, 0, hdr, phist,
+                                                                  pvals, skeys, keys, p.dec.keys_per_image, spill_cap, logits);
+    if ((rc = check_launch())) return rc;
+    head_decode_kernel<1><<<grid_rows, kHdThreads, p.smem, st>>>(feat, weight, bias, B, Cf, C, H, K, p.stages, 0, hdr, phist,
+                                                                  pvals, skeys, keys, p.dec.keys_per_image, spill_cap, logits);
+  } else {
+    head_decode_kernel<3><<<grid_rows, kHdThreads, p.smem, st>>>(feat, weight, bias, B, Cf, C, H, K, p.stages, 0, hdr, phist,
+                                                                  pvals, skeys, keys, p.dec.keys_per_image, spill_cap, logits);
+  }
   if ((rc = check_launch())) return rc;
   head_decode_kernel<2><<<grid_rows, kHdThreads, p.smem, st>>>(feat, weight, bias, B, Cf, C, H, K, p.stages,
                                                                 logits_out ? 1 : 0, hdr, phist, pvals, skeys, keys,
@@ -464,3 +695,11 @@ extern "C" int ctdet_head_decode_fused(const float* feat, const float* weight, c
       wh, reg, C, H, W, K, down_ratio, flags | CTDET_DECODE_LOGITS, boxes, scores, classes, inds);
   return check_launch();
 }
+
+#ifdef CTDET_HD_TIMING
+extern "C" int ctdet_debug_hd_times(unsigned long long* out /* [16] host */, int reset) {
+  unsigned long long z[16] = {0};
+  if (reset) return cudaMemcpyToSymbol(ctdet::g_hd_ts, z, sizeof(z)) == cudaSuccess ? 0 : 5;
+  return cudaMemcpyFromSymbol(out, ctdet::g_hd_ts, sizeof(z)) == cudaSuccess ? 0 : 5;
+}
+#endif

@@ -60,7 +60,7 @@ def ctdet_decode_batch(heat, wh, reg=None, down_ratio=1, cat_spec_wh=False, K=10
 def head_decode_fusable(Cf, C, H, W):
     """Shapes `ctdet_head_decode_fused` takes (include/ctdet_b200.h): a map row is one 128-pixel tensor-core tile."""
     return W == 128 and Cf % 64 == 0 and C % 16 == 0 and C <= 128 and \
-        1024 + (Cf // 64) * C * 128 + 3 * C * 512 + 2 * 16384 + 8 * C + 5120 <= 226 * 1024
+        1024 + (Cf // 64) * C * 128 + 3 * C * 512 + 2 * 16384 + 8 * C + 5120 + 8192 <= 226 * 1024
 
 
 def hm_head_decode_batch(feat, weight, bias, wh, reg=None, down_ratio=1, cat_spec_wh=False, K=100, return_logits=False):

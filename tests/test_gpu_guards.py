@@ -116,3 +116,54 @@ def test_dcn_backward_stays_inside_its_buffers(cfg):
     torch.cuda.synchronize()
     assert torch.equal(go.view(), want[1]) and torch.equal(gm.view(), want[2])          # deterministic outputs
     assert torch.allclose(gi.view(), want[0], rtol=1e-4, atol=1e-5)                      # fp32 atomics: order varies
+
+
+def test_head_decode_fused_and_spilling_decode_stay_inside_their_buffers():
+    """`ctdet_head_decode_fused` (workspace incl. the spill list and the fall-back logits, outputs, optional logits_out) and
+    `ctdet_decode` on class-concentrated logits (tiles that spill): guards untouched, outputs fully written."""
+    lib = _lib.load()
+    B, Cf, C, H, W, K = 3, 64, 32, 40, 128, 100
+    g = torch.Generator(device="cpu").manual_seed(9)
+    feat = torch.relu(torch.randn(B, Cf, H, W, generator=g))
+    feat[1, :, 10:16, 20:100] *= 3.0                          # a hot region: segments overflow into the spill list
+    feat[2].zero_()                                           # a plateau: spill list overflows -> staged path on stored logits
+    feat = feat.to(DEV)
+    w = (torch.randn(C, Cf, generator=g) / 8).to(DEV)
+    bias = torch.full((C,), -2.19, device=DEV)
+    wh = (torch.rand(B, 2, H, W, generator=g) * 20).to(DEV)
+    reg = torch.rand(B, 2, H, W, generator=g).to(DEV)
+    for with_logits in (False, True):
+        outs = [Carved((B, K, 4), torch.float32), Carved((B, K), torch.float32), Carved((B, K), torch.int32),
+                Carved((B, K), torch.int64)]
+        lg = Carved((B, C, H, W), torch.float32) if with_logits else None
+        n = lib.ctdet_head_decode_fused_workspace_bytes(B, Cf, C, H, W, K)
+        ws = Carved((n,), torch.uint8)
+        ws.view().zero_()
+        for _ in range(2):
+            rc = lib.ctdet_head_decode_fused(_lib.ptr(feat), _lib.ptr(w), _lib.ptr(bias), _lib.ptr(wh), _lib.ptr(reg),
+                                             B, Cf, C, H, W, K, 4.0, 0, *[o.ptr() for o in outs], lg.ptr() if lg else None,
+                                             ws.ptr(), ctypes.c_size_t(n), _lib.stream_ptr(DEV))
+            assert rc == 0, lib.ctdet_error_string(rc)
+            torch.cuda.synchronize()
+        for o in outs + [ws] + ([lg] if lg else []):
+            assert o.guards_intact()
+        assert outs[0].fully_written() and outs[1].fully_written() and (lg is None or lg.fully_written())
+        assert bool((outs[2].view() >= 0).all()) and bool((outs[2].view() < C).all())
+        assert bool((outs[3].view() >= 0).all()) and bool((outs[3].view() < H * W).all())
+    # the plain decode on logits with a per-class mean (tiles spill)
+    C2, H2 = 80, 128
+    hm = (0.7 * torch.randn(B, C2, H2, W, generator=g) + (-2.19 + 0.6 * torch.randn(1, C2, 1, 1, generator=g))).to(DEV)
+    wh2 = (torch.rand(B, 2, H2, W, generator=g) * 20).to(DEV)
+    outs = [Carved((B, K, 4), torch.float32), Carved((B, K), torch.float32), Carved((B, K), torch.int32),
+            Carved((B, K), torch.int64)]
+    n = lib.ctdet_decode_workspace_bytes(B, C2, H2, W, K)
+    ws = Carved((n,), torch.uint8)
+    ws.view().zero_()
+    for _ in range(2):
+        rc = lib.ctdet_decode(_lib.ptr(hm), _lib.ptr(wh2), None, B, C2, H2, W, K, 4.0, 1, *[o.ptr() for o in outs],
+                              ws.ptr(), ctypes.c_size_t(n), _lib.stream_ptr(DEV))
+        assert rc == 0, lib.ctdet_error_string(rc)
+        torch.cuda.synchronize()
+    for o in outs + [ws]:
+        assert o.guards_intact()
+    assert outs[0].fully_written() and outs[1].fully_written()

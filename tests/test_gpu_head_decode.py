@@ -165,3 +165,18 @@ def test_ctdet_head_decode_method_fused_vs_unfused():
         a, b_ = head.decode(x, K=50), head.decode(x, K=50, fuse=False)
         assert a[1].shape == b_[1].shape == (2, 50)
         assert float((a[1][:, 0] - b_[1][:, 0]).abs().max()) <= 2e-3
+
+
+def test_running_bound_variant_in_a_fresh_process():
+    """`CTDET_HEAD_DECODE_SEED=0` (read once per process) selects the sweep with a running bound per CTA (no seed launch)
+    instead of the default seed launch + sweep: the same parity tests in a child process."""
+    import os
+    import subprocess
+    import sys
+    if os.environ.get("CTDET_HEAD_DECODE_SEED"):
+        pytest.skip("already the child")
+    env = dict(os.environ, CTDET_HEAD_DECODE_SEED="0")
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-x", "-q", "-k",
+                        "own_logits or plateaus or spill or share_the_workspace"], env=env, capture_output=True, text=True,
+                       timeout=300, cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
