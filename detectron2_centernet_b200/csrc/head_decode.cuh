@@ -28,7 +28,7 @@ constexpr int kHdThreads = (kHdProducerWarps + kHdEpiWarps + 1) * 32;
 constexpr int kHdMaxStages = 6;
 constexpr int kHdMaxRows = 256;               // GEMM rows per CTA (row list in shared memory)
 constexpr int kHdSeedPeriod = 32;             // one sampled row per 32 map rows
-constexpr int kHdW = 128;                     // map width this kernel takes: a row is one UMMA M tile
+constexpr int kHdW = 128;                     // pixels per tile = UMMA M: a map row of W <= 128 pixels is one tile
 constexpr int kHdListCap = 1024;              // mode 3: scores of a run's emitted keys kept per class half (the running bound)
 
 struct HeadDecodeBarriers {
@@ -117,8 +117,8 @@ __device__ __forceinline__ int hd_compact_ge(unsigned int* list, int n, unsigned
 // missing row / column (map border) re-reads the centre row / column -- so that all nine are in flight together and a cell
 // costs ~35 instructions (the first form, addresses rebuilt and one branch per load, cost ~120: 15 us for a full row).
 struct HdNbr { int a0, a1, a2, b0, b1, b2, c0, c1, c2; };
-__device__ __forceinline__ HdNbr hd_nbr(int C, int c_lo, int t, int x, bool up, bool down) {
-  const int xl = x > 0 ? x - 1 : x, xr = x < kHdW - 1 ? x + 1 : x;
+__device__ __forceinline__ HdNbr hd_nbr(int C, int c_lo, int t, int x, int W, bool up, bool down) {
+  const int xl = x > 0 ? x - 1 : x, xr = x < W - 1 ? x + 1 : x;
   const int r1 = ((t % 3) * C + c_lo) * kHdW;
   const int r0 = up ? (((t + 2) % 3) * C + c_lo) * kHdW : r1;
   const int r2 = down ? (((t + 1) % 3) * C + c_lo) * kHdW : r1;
@@ -148,7 +148,7 @@ __device__ unsigned long long g_hd_ts[16];      // CTA 0, half 0, leader lane: c
 template <int kMode>
 __global__ void __launch_bounds__(kHdThreads, 1)
 head_decode_kernel(const float* __restrict__ feat, const float* __restrict__ weight, const float* __restrict__ bias,
-                   int B, int Cf, int C, int H, int K, int stages, int force,
+                   int B, int Cf, int C, int H, int W, int K, int stages, int force,
                    DecodeHeader* __restrict__ hdrs, unsigned int* __restrict__ phists, unsigned int* __restrict__ pvals_all,
                    u64* __restrict__ skeys, u64* __restrict__ spill_all, size_t keys_per_image, int spill_cap,
                    float* __restrict__ logits_out) {
@@ -164,7 +164,7 @@ head_decode_kernel(const float* __restrict__ feat, const float* __restrict__ wei
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int KB = Cf / kBK;
   const int NS = stages;
-  const int P = H * kHdW;
+  const int P = H * W;                                      // W <= 128: a map row is the first W pixels of a 128-pixel tile
   const int ns = hd_seed_rows(H);
   uint8_t* smem = hd_smem + ((1024u - (smem_u32(hd_smem) & 1023u)) & 1023u);
   uint8_t* ring = smem;                                     // [NS][128 px][128 B]
@@ -258,11 +258,18 @@ head_decode_kernel(const float* __restrict__ feat, const float* __restrict__ wei
       const int it = n / KB, kb = n - it * KB;
       const int g = s_g[it];
       const int b = g / H, y = g - b * H;
-      const float* src = feat + ((size_t)b * Cf + kb * kBK + warp * 8) * P + y * kHdW + lane;
+      const float* src = feat + ((size_t)b * Cf + kb * kBK + warp * 8) * P + y * W + lane;
+      if (W == kHdW) {
 #pragma unroll
-      for (int i = 0; i < 8; ++i)
+        for (int i = 0; i < 8; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) dst[i][j] = ldg_stream1(src + (size_t)i * P + 32 * j);
+          for (int j = 0; j < 4; ++j) dst[i][j] = ldg_stream1(src + (size_t)i * P + 32 * j);
+      } else {                                   // narrow map: the tile's pixels past the row are zero
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) dst[i][j] = (lane + 32 * j < W) ? ldg_stream1(src + (size_t)i * P + 32 * j) : 0.f;
+      }
     };
     load_kb(0, v[0]);
 #pragma unroll 1
@@ -304,7 +311,7 @@ head_decode_kernel(const float* __restrict__ feat, const float* __restrict__ wei
     // mode 1: 3x3 test of the flagged cells of row t, keys -> the (row, half) segment, always written in full
     auto sweep_row = [&](int b, int t, bool up, bool down, unsigned long long m) {
       hd_bar_half(half);                                     // the window rows are stored; the staging area is clean
-      const HdNbr nb = hd_nbr(C, c_lo, t, x, up, down);
+      const HdNbr nb = hd_nbr(C, c_lo, t, x, W, up, down);
       while (m) {
         const int k = __ffsll((long long)m) - 1;
         m &= m - 1ull;
@@ -313,7 +320,7 @@ head_decode_kernel(const float* __restrict__ feat, const float* __restrict__ wei
         const float nbm = hd_max9(win, nb, k, v);
         if (is_peak(v, nbm, true)) {
           const unsigned int pos = atomicAdd(&s_cnt[half], 1u);
-          const uint32_t flat = (uint32_t)((c * H + t) * kHdW + x);
+          const uint32_t flat = (uint32_t)((c * H + t) * W + x);
           const u64 key = ((u64)float_to_ordered(v) << 32) | (u64)(0xffffffffu - flat);
           if (pos < (unsigned)kTileCap) {
             s_keys[half * kTileCap + pos] = key;
@@ -355,7 +362,7 @@ head_decode_kernel(const float* __restrict__ feat, const float* __restrict__ wei
         bits &= bits - 1ull;
         const int c = c_lo + k;
         const float v = win[((size_t)(t % 3) * C + c) * kHdW + x];
-        const uint32_t flat = (uint32_t)((c * H + t) * kHdW + x);
+        const uint32_t flat = (uint32_t)((c * H + t) * W + x);
         const u64 key = ((u64)float_to_ordered(v) << 32) | (u64)(0xffffffffu - flat);
         if (pos < (unsigned)kTileCap) {
           s_keys[half * kTileCap + pos] = key;
@@ -375,7 +382,7 @@ head_decode_kernel(const float* __restrict__ feat, const float* __restrict__ wei
       const unsigned int thr_now = s_thr[half];              // uniform over the half
       HD_T(8, __popcll(m)); HD_T(9, 1); if (thr_now == 0u) HD_T(10, 1);
       unsigned long long pk = 0ull;                          // this thread's peaks >= the bound
-      const HdNbr nb = hd_nbr(C, c_lo, t, x, up, down);
+      const HdNbr nb = hd_nbr(C, c_lo, t, x, W, up, down);
       while (m) {
         const int k = __ffsll((long long)m) - 1;
         m &= m - 1ull;
@@ -453,12 +460,12 @@ head_decode_kernel(const float* __restrict__ feat, const float* __restrict__ wei
     // mode 0: the best 3x3 peak of every class in row t -> sample histogram; the image's last half derives the bound
     auto seed_row = [&](int b, int j, int t, bool up, bool down) {
       hd_bar_half(half);
-      const HdNbr nb = hd_nbr(C, c_lo, t, x, up, down);
+      const HdNbr nb = hd_nbr(C, c_lo, t, x, W, up, down);
       for (int k = 0; k < ch; ++k) {
         const int c = c_lo + k;
         float v;
         const float nbm = hd_max9(win, nb, k, v);
-        unsigned int val = (v >= nbm) ? float_to_ordered(v) : 0u;             // (a strict subset of the peaks is still valid)
+        unsigned int val = (v >= nbm && x < W) ? float_to_ordered(v) : 0u;    // (a strict subset of the peaks is still valid)
         val = __reduce_max_sync(0xffffffffu, val);
         if (lane == 0 && val) atomicMax(&s_best[c], val);
       }
@@ -527,7 +534,7 @@ head_decode_kernel(const float* __restrict__ feat, const float* __restrict__ wei
           const int c = c_lo + c0 + k;
           const float l = __uint_as_float(v[k]) + s_bias[c];
           if (kMode == 2) {
-            logits_out[((size_t)b * C + c) * P + y * kHdW + x] = l;
+            if (x < W) logits_out[((size_t)b * C + c) * P + y * W + x] = l;
           } else {
             win[((size_t)(y % 3) * C + c) * kHdW + x] = l;
             if (kMode == 1 && live && l >= thv && float_to_ordered(l) >= thr_ord) m_cur |= 1ull << (c0 + k);
@@ -535,6 +542,7 @@ head_decode_kernel(const float* __restrict__ feat, const float* __restrict__ wei
           }
         }
       }
+      if (x >= W) m_cur = 0ull;                              // pixels past the map row never become candidates
       tc_fence_before();
       __syncwarp();
       if (lane == 0) dcn_mbar_arrive(&bars.acc_empty[ab]);
@@ -617,7 +625,7 @@ static int head_decode_check(int B, int Cf, int C, int H, int W, int K) {
   if (B < 0 || Cf <= 0 || C <= 0 || H <= 0 || W <= 0 || K <= 0) return CTDET_EINVAL;
   if (K > CTDET_MAX_K || (int64_t)K > (int64_t)H * W) return CTDET_EINVAL;
   if ((int64_t)C * H * W >= ((int64_t)1 << 31) || (int64_t)B * H >= ((int64_t)1 << 30)) return CTDET_EINVAL;
-  if (W != kHdW || (Cf % kBK) != 0 || (C % 16) != 0 || C > 128) return CTDET_EUNSUPPORTED;
+  if (W > kHdW || (Cf % kBK) != 0 || (C % 16) != 0 || C > 128) return CTDET_EUNSUPPORTED;
   return CTDET_OK;
 }
 
@@ -640,7 +648,8 @@ extern "C" int ctdet_head_decode_fused(const float* feat, const float* weight, c
   if (flags & ~CTDET_DECODE_CAT_SPEC_WH) return CTDET_EINVAL;       // logits in, 3x3 peak test always (centernet.py:161, :399)
   if (B == 0) return CTDET_OK;
   if (!feat || !weight || !wh || !boxes || !scores || !classes || !workspace) return CTDET_ENULL;
-  if (!aligned16(weight) || !aligned16(feat) || (reinterpret_cast<uintptr_t>(workspace) & 255u)) return CTDET_EALIGN;
+  if (!aligned16(weight) || (reinterpret_cast<uintptr_t>(workspace) & 255u)) return CTDET_EALIGN;
+  if (logits_out && (W % 4) == 0 && !aligned16(logits_out)) return CTDET_EALIGN;      // (the fall-back's bulk copies)
   if (B > 65535) return CTDET_EINVAL;
   const HeadDecodePlan p = make_head_decode_plan(B, Cf, C, H, W, K);
   if (workspace_bytes < p.total_bytes) return CTDET_EWORKSPACE;
@@ -674,17 +683,17 @@ extern "C" int ctdet_head_decode_fused(const float* feat, const float* weight, c
   static int with_seed = -1;
   if (with_seed < 0) { const char* ev = getenv("CTDET_HEAD_DECODE_SEED"); with_seed = ev ? (atoi(ev) != 0) : 1; }
   if (with_seed) {
-    head_decode_kernel<0><<<grid_seed, kHdThreads, p.smem, st>>>(feat, weight, bias, B, Cf, C, H, K, p.stages, 0, hdr, phist,
+    head_decode_kernel<0><<<grid_seed, kHdThreads, p.smem, st>>>(feat, weight, bias, B, Cf, C, H, W, K, p.stages, 0, hdr, phist,
                                                                   pvals, skeys, keys, p.dec.keys_per_image, spill_cap, logits);
     if ((rc = check_launch())) return rc;
-    head_decode_kernel<1><<<grid_rows, kHdThreads, p.smem, st>>>(feat, weight, bias, B, Cf, C, H, K, p.stages, 0, hdr, phist,
+    head_decode_kernel<1><<<grid_rows, kHdThreads, p.smem, st>>>(feat, weight, bias, B, Cf, C, H, W, K, p.stages, 0, hdr, phist,
                                                                   pvals, skeys, keys, p.dec.keys_per_image, spill_cap, logits);
   } else {
-    head_decode_kernel<3><<<grid_rows, kHdThreads, p.smem, st>>>(feat, weight, bias, B, Cf, C, H, K, p.stages, 0, hdr, phist,
+    head_decode_kernel<3><<<grid_rows, kHdThreads, p.smem, st>>>(feat, weight, bias, B, Cf, C, H, W, K, p.stages, 0, hdr, phist,
                                                                   pvals, skeys, keys, p.dec.keys_per_image, spill_cap, logits);
   }
   if ((rc = check_launch())) return rc;
-  head_decode_kernel<2><<<grid_rows, kHdThreads, p.smem, st>>>(feat, weight, bias, B, Cf, C, H, K, p.stages,
+  head_decode_kernel<2><<<grid_rows, kHdThreads, p.smem, st>>>(feat, weight, bias, B, Cf, C, H, W, K, p.stages,
                                                                 logits_out ? 1 : 0, hdr, phist, pvals, skeys, keys,
                                                                 p.dec.keys_per_image, spill_cap, logits);
   if ((rc = check_launch())) return rc;

@@ -58,15 +58,15 @@ def ctdet_decode_batch(heat, wh, reg=None, down_ratio=1, cat_spec_wh=False, K=10
 
 
 def head_decode_fusable(Cf, C, H, W):
-    """Shapes `ctdet_head_decode_fused` takes (include/ctdet_b200.h): a map row is one 128-pixel tensor-core tile."""
-    return W == 128 and Cf % 64 == 0 and C % 16 == 0 and C <= 128 and \
+    """Shapes `ctdet_head_decode_fused` takes (include/ctdet_b200.h): a map row is one tensor-core tile of <= 128 pixels."""
+    return 1 <= W <= 128 and Cf % 64 == 0 and C % 16 == 0 and C <= 128 and \
         1024 + (Cf // 64) * C * 128 + 3 * C * 512 + 2 * 16384 + 8 * C + 5120 + 8192 <= 226 * 1024
 
 
 def hm_head_decode_batch(feat, weight, bias, wh, reg=None, down_ratio=1, cat_spec_wh=False, K=100, return_logits=False):
     """`ctdet_decode(Conv2d(Cf, C, 1)(feat).sigmoid_(), wh, reg, ...)` (centernet.py:118-123, :152, :161, :426-458) for a
     batch, without the logits in HBM: the 1x1 convolution runs per map row on the tensor cores (bf16 operands) and the
-    decode's peak test / threshold sweep on a three-row window in shared memory.  feat f32 [B,Cf,H,128]; weight f32 [C,Cf]
+    decode's peak test / threshold sweep on a three-row window in shared memory.  feat f32 [B,Cf,H,W], W <= 128; weight f32 [C,Cf]
     or [C,Cf,1,1]; bias f32 [C] or None.  Returns boxes, scores, classes, inds as ctdet_decode_batch (+ the logits
     f32 [B,C,H,W] with return_logits=True: an extra pass, for verification)."""
     _lib.require_cuda("hm_head_decode", feat, weight, bias, wh, reg)
@@ -92,7 +92,7 @@ def hm_head_decode_batch(feat, weight, bias, wh, reg=None, down_ratio=1, cat_spe
     if K > H * W:
         raise RuntimeError("selected index k out of range")
     if not head_decode_fusable(Cf, C, H, W):
-        raise NotImplementedError("hm_head_decode_batch needs W == 128, Cf %% 64 == 0, C %% 16 == 0, C <= 128 (got Cf=%d C=%d "
+        raise NotImplementedError("hm_head_decode_batch needs W <= 128, Cf %% 64 == 0, C %% 16 == 0, C <= 128 (got Cf=%d C=%d "
                                   "W=%d): run the convolution and ctdet_decode_batch(logits=True)" % (Cf, C, W))
     dev = feat.device
     boxes = torch.empty((B, K, 4), dtype=torch.float32, device=dev)

@@ -203,7 +203,7 @@ int ctdet_decode_static(const float* heat, const float* wh, const float* reg,
 
 /* ---------------------------------------------------------------- fused hm head + decode --
  * SURVEY.md section 8 f2, second half, decode side: the hm head's final 1x1 convolution (centernet.py:118-123, applied :152),
- * hm.sigmoid_() (:161) and ctdet_decode (:426-458) without the [B,C,H,W] logits in HBM: every map row (W = 128 pixels) is
+ * hm.sigmoid_() (:161) and ctdet_decode (:426-458) without the [B,C,H,W] logits in HBM: every map row (W <= 128 pixels) is
  *   logits[128 px, C] = feat[128 px, Cf] * weight^T + bias   on the tensor cores (bf16 operands, fp32 accumulation)
  * and the 3x3 peak test / threshold sweep of ctdet_decode runs on a three-row window of them in shared memory (a sampled
  * pass for the bound, then the full sweep; the exact fall-back for ties / plateaus / tiny maps stores the logits of the
@@ -212,7 +212,8 @@ int ctdet_decode_static(const float* heat, const float* wh, const float* reg,
  *   feat f32 [B,Cf,H,W]   weight f32 [C,Cf]   bias f32 [C] or NULL   wh / reg / outputs as ctdet_decode
  *   logits_out f32 [B,C,H,W] or NULL: when given, the logits are ALSO written (one extra pass; verification / callers
  *   that want both) -- ctdet_decode(logits_out, CTDET_DECODE_LOGITS) then returns the same detections bit for bit.
- * Requires W == 128 (a 512-pixel-wide input at stride 4), Cf % 64 == 0, C % 16 == 0, C <= 128, shared memory for
+ * Requires W <= 128 (a map row is one tensor-core tile: 128 = a 512-pixel-wide input at stride 4 uses it fully, 104 = a
+ * 416-pixel one to 81 %), Cf % 64 == 0, C % 16 == 0, C <= 128, shared memory for
  * 3 rows of logits (C = 80, Cf = 256: 213 KB); else CTDET_EUNSUPPORTED (run the convolution + ctdet_decode).
  * workspace: ctdet_head_decode_fused_workspace_bytes() bytes, 256-byte aligned, zero on first use, left zero where it must
  * be (it starts with ctdet_decode's zero-on-entry prefix and may be the same buffer for a given B). */

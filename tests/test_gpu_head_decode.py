@@ -42,12 +42,16 @@ def _rel(a, b):
 
 
 @pytest.mark.parametrize("cfg", [(2, 64, 16, 12, 40), (3, 256, 80, 32, 100), (2, 128, 32, 128, 100), (5, 256, 80, 64, 100),
-                                 (1, 64, 16, 1, 20), (2, 64, 16, 2, 30), (1, 192, 48, 33, 100)])
+                                 (1, 64, 16, 1, 20), (2, 64, 16, 2, 30), (1, 192, 48, 33, 100),
+                                 (2, 256, 80, 104, 100, 104), (3, 64, 16, 40, 60, 40), (2, 64, 32, 9, 25, 7), (1, 128, 16, 50, 100, 97)])
 def test_fused_head_decode_equals_decode_of_its_own_logits(cfg):
-    """The last three shapes: one and two map rows (no halo rows exist), an odd row count (runs that end inside an image)."""
+    """Shapes 5-7: one and two map rows (no halo rows exist), an odd row count (runs that end inside an image).  The last
+    four are narrow maps (W < 128: a 416^2 input at stride 4 is 104 x 104; odd widths take ctdet_decode's own odd-width
+    path in the check)."""
     from detectron2_centernet_b200 import decode as D
-    B, Cf, C, H, K = cfg
-    feat, w, b, wh, reg = _setup(3 + H, B, Cf, C, H)
+    B, Cf, C, H, K = cfg[:5]
+    W = cfg[5] if len(cfg) > 5 else 128
+    feat, w, b, wh, reg = _setup(3 + H, B, Cf, C, H, W)
     boxes, scores, classes, inds, logits = D.hm_head_decode_batch(feat, w, b, wh, reg, down_ratio=4, K=K, return_logits=True)
     want_logits = torch.nn.functional.conv2d(feat, w[:, :, None, None], b)
     assert _rel(logits, want_logits) <= 1e-2
@@ -132,13 +136,13 @@ def test_unsupported_shapes_are_rejected():
     from detectron2_centernet_b200 import _lib
     from detectron2_centernet_b200 import decode as D
     lib = _lib.load()
-    assert lib.ctdet_head_decode_fused_workspace_bytes(2, 64, 16, 16, 64, 10) == 0          # W != 128
+    assert lib.ctdet_head_decode_fused_workspace_bytes(2, 64, 16, 16, 132, 10) == 0         # W > 128
     assert lib.ctdet_head_decode_fused_workspace_bytes(2, 60, 16, 16, 128, 10) == 0         # Cf % 64
     assert lib.ctdet_head_decode_fused_workspace_bytes(2, 64, 20, 16, 128, 10) == 0         # C % 16
-    assert not D.head_decode_fusable(64, 16, 16, 64)
-    feat = torch.zeros(1, 64, 4, 64, device=DEV)
+    assert not D.head_decode_fusable(64, 16, 16, 256) and D.head_decode_fusable(64, 16, 16, 64)
+    feat = torch.zeros(1, 64, 4, 256, device=DEV)
     with pytest.raises(NotImplementedError):
-        D.hm_head_decode_batch(feat, torch.zeros(16, 64, device=DEV), None, torch.zeros(1, 2, 4, 64, device=DEV))
+        D.hm_head_decode_batch(feat, torch.zeros(16, 64, device=DEV), None, torch.zeros(1, 2, 4, 256, device=DEV))
 
 
 def test_ctdet_head_decode_method_fused_vs_unfused():
