@@ -125,7 +125,7 @@ dcn_pack_input_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ x
 // swizzled shared-memory image the UMMA descriptor expects (row n at n*128 B, 16-byte chunk ch at
 // (ch ^ (n & 7)) << 4), so the main kernel moves it with one 1-D bulk async copy.
 __global__ void dcn_pack_weight_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ wk,
-                                       int Cout, int Cin) {
+                                       int Cout, int Cin, int cout_real) {    // rows >= cout_real are zero (N padding)
   const size_t n_el = (size_t)Cout * Cin * 9;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_el; i += (size_t)gridDim.x * blockDim.x) {
     const int c = (int)(i & 63);                         // channel inside the block
@@ -135,7 +135,7 @@ __global__ void dcn_pack_weight_kernel(const float* __restrict__ w, __nv_bfloat1
     const int ci = cb * 64 + c;
     const int ch = c >> 3, e = c & 7;
     wk[(size_t)kb * Cout * 64 + (size_t)n * 64 + ((ch ^ (n & 7)) << 3) + e] =
-        __float2bfloat16_rn(w[((size_t)n * Cin + ci) * 9 + t]);
+        __float2bfloat16_rn(n < cout_real ? w[((size_t)n * Cin + ci) * 9 + t] : 0.f);
   }
 }
 
@@ -154,7 +154,7 @@ __global__ void dcn_pack_weight_kernel(const float* __restrict__ w, __nv_bfloat1
 //   warp  NP+8           one lane issues tcgen05.mma / tcgen05.commit
 //   warp  NP+9           one lane streams the pre-swizzled B (weight) tiles with 1-D bulk copies
 // TMEM holds two accumulator buffers, so the epilogue of tile i overlaps the MMAs of tile i+1.
-template <bool kFp32Blend, int NP>
+template <bool kFp32Blend, int NP, bool kPlain = false>
 __global__ void __launch_bounds__((NP + 10) * 32, 1)
 dcn_forward_kernel(const DcnParams prm) {
   static_assert(NP % 4 == 0 && 32 % NP == 0, "producer warps must tile the 32 row groups and keep warp%4 aligned");
@@ -182,18 +182,19 @@ dcn_forward_kernel(const DcnParams prm) {
   const int tile_step = 1, tile_base = tile_first;
 
   if (tid == 0) {
-    for (int s = 0; s < NS; ++s) { dcn_mbar_init(&bars.full[s], NP + 1); dcn_mbar_init(&bars.empty[s], 1); }
+    for (int s = 0; s < NS; ++s) { dcn_mbar_init(&bars.full[s], kPlain ? NP / NS + 1 : NP + 1); dcn_mbar_init(&bars.empty[s], 1); }
     for (int i = 0; i < 2; ++i) {
       dcn_mbar_init(&bars.geo_full[i], 4);  dcn_mbar_init(&bars.geo_empty[i], NP);
       dcn_mbar_init(&bars.acc_full[i], 1);  dcn_mbar_init(&bars.acc_empty[i], 4);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
+  const int cout_store = prm.cout_store ? prm.cout_store : Cout;
   for (int c = tid; c < Cout; c += blockDim.x) {
-    const float sc = prm.scale ? __ldg(prm.scale + c) : 1.f;
-    const float bi = prm.bias ? __ldg(prm.bias + c) : 0.f;
+    const float sc = (prm.scale && c < cout_store) ? __ldg(prm.scale + c) : 1.f;
+    const float bi = (prm.bias && c < cout_store) ? __ldg(prm.bias + c) : 0.f;
     s_sc[c] = sc;
-    s_sh[c] = prm.scale ? bi * sc + __ldg(prm.shift + c) : bi;
+    s_sh[c] = (prm.scale && c < cout_store) ? bi * sc + __ldg(prm.shift + c) : bi;
   }
   if (warp == NP + 8) tmem_alloc(&s_tmem, prm.tmem_cols);
   tc_fence_before();
@@ -204,8 +205,9 @@ dcn_forward_kernel(const DcnParams prm) {
 
   if (warp < NP) {
     // ===================================== producers ==============================================
-    dcn_producer_loop<kFp32Blend, NP>(prm, smem, stage_bytes, NS, geo_w, geo_g, bars, warp, lane,
-                                      tile_first, my_tiles, 0, KB);
+    if (kPlain) dcn_plain_producer_loop<NP>(prm, smem, stage_bytes, NS, geo_w, geo_g, bars, warp, lane, tile_first, my_tiles, KB);
+    else dcn_producer_loop<kFp32Blend, NP>(prm, smem, stage_bytes, NS, geo_w, geo_g, bars, warp, lane,
+                                           tile_first, my_tiles, 0, KB);
   } else if (warp < NP + 4) {
     // ===================================== epilogue ===============================================
     const int quarter = warp - NP;                                        // == warp % 4: TMEM lane quarter
@@ -219,7 +221,7 @@ dcn_forward_kernel(const DcnParams prm) {
       const int tile_y = tile / prm.tiles_x, tile_x = tile - tile_y * prm.tiles_x;
       const int eho = tile_y * kTileH + (r >> 4), ewo = tile_x * kTileW + (r & 15);
       const bool evalid = eho < prm.Ho && ewo < prm.Wo;
-      float* yp = prm.y + (size_t)b * Cout * P + (evalid ? eho * prm.Wo + ewo : 0);
+      float* yp = prm.y + (size_t)b * cout_store * P + (evalid ? eho * prm.Wo + ewo : 0);
       dcn_mbar_wait_relaxed(&bars.acc_full[ab], (unsigned)((j >> 1) & 1));
       tc_fence_after();
       const uint32_t tbase = tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)ab * acc_stride;
@@ -236,7 +238,7 @@ dcn_forward_kernel(const DcnParams prm) {
         for (int k = 0; k < 16; ++k) {
           float q = fmaf(__uint_as_float(v[k]), sc[k], sh[k]);
           if (relu) q = fmaxf(q, 0.f);
-          if (evalid) *yp = q;
+          if (evalid && c0 + k < cout_store) *yp = q;
           yp += P;
         }
       }
@@ -319,7 +321,7 @@ extern "C" int dcnv2_pack_weight(const float* weight, int Cin, int Cout, void* p
   if (Cin % kBK != 0 || Cout % 16 != 0 || Cout < 16 || Cout > 256) return CTDET_EUNSUPPORTED;
   if (!weight || !packed) return CTDET_ENULL;
   if (reinterpret_cast<uintptr_t>(packed) & 15u) return CTDET_EALIGN;
-  dcn_pack_weight_kernel<<<kNumSMs, 256, 0, (cudaStream_t)stream>>>(weight, reinterpret_cast<__nv_bfloat16*>(packed), Cout, Cin);
+  dcn_pack_weight_kernel<<<kNumSMs, 256, 0, (cudaStream_t)stream>>>(weight, reinterpret_cast<__nv_bfloat16*>(packed), Cout, Cin, Cout);
   return check_launch();
 }
 
@@ -331,7 +333,7 @@ static int dcn_forward_impl(const float* input, const float* weight, const float
                             int stride_h, int stride_w, int pad_h, int pad_w, int dilation_h,
                             int dilation_w, int group, int deformable_group,
                             const float* scale, const float* shift, int flags,
-                            void* workspace, size_t workspace_bytes, ctdet_stream_t stream) {
+                            void* workspace, size_t workspace_bytes, ctdet_stream_t stream, int input_is_packed = 0) {
   using namespace ctdet;
   if (B < 0 || Cin <= 0 || H <= 0 || W <= 0 || Cout <= 0) return CTDET_EINVAL;
   if (flags & ~(DCN_FLAG_RELU | DCN_FLAG_FP32_BLEND | DCN_FLAG_PACKED_WEIGHT)) return CTDET_EINVAL;
@@ -358,14 +360,17 @@ static int dcn_forward_impl(const float* input, const float* weight, const float
   const int Pin = H * W;
   if (B > 65535) return CTDET_EINVAL;
   const int vec = (Pin % 4 == 0 && aligned16(input)) ? 1 : 0;          // float4 loads of the NCHW input
-  dcn_pack_input_kernel<<<dim3((Pin + 63) / 64, (Cin + 63) / 64, B), 256, 0, st>>>(input, xh, Cin, Pin, vec, nullptr, 1, 0);
-  int rc = check_launch();
-  if (rc) return rc;
+  int rc = CTDET_OK;
+  if (!input_is_packed) {                      // (dcnv2_forward_fused_offsets packed it for both of its kernels)
+    dcn_pack_input_kernel<<<dim3((Pin + 63) / 64, (Cin + 63) / 64, B), 256, 0, st>>>(input, xh, Cin, Pin, vec, nullptr, 1, 0);
+    rc = check_launch();
+    if (rc) return rc;
+  }
   if (flags & DCN_FLAG_PACKED_WEIGHT) {        // `weight` is the caller's dcnv2_pack_weight output for these weights
     if (reinterpret_cast<uintptr_t>(weight) & 15u) return CTDET_EALIGN;
     wk = reinterpret_cast<__nv_bfloat16*>(const_cast<float*>(weight));
   } else
-  dcn_pack_weight_kernel<<<kNumSMs, 256, 0, st>>>(weight, wk, Cout, Cin);
+  dcn_pack_weight_kernel<<<kNumSMs, 256, 0, st>>>(weight, wk, Cout, Cin, Cout);
   rc = check_launch();
   if (rc) return rc;
 
@@ -436,4 +441,86 @@ extern "C" int dcnv2_forward_raw27(const float* input, const float* weight, cons
   return dcn_forward_impl(input, weight, bias, offset_mask, nullptr, offset_mask_bias, 1, output, B, Cin, H, W, Cout, 3, 3,
                           stride, stride, pad, pad, dilation, dilation, 1, 1, scale, shift, flags,
                           workspace, workspace_bytes, stream);
+}
+
+// ------------------------------------------------------------------------------------------------
+// conv_offset_mask on the tensor cores, feeding the DCN that follows: the 27-channel 3x3
+// convolution of deform_conv.py:505-513 (convention resnet.py:308-313) is the main kernel in its `plain` mode -- zero
+// offsets, mask 1, ONE corner gathered per (pixel, tap), N = 32 (27 real rows) -- over the same NHWC bf16 copy of x the DCN
+// samples, so x is packed once, cuDNN's NCHW <-> NHWC conversions disappear and the raw 27 channels go straight into the
+// DCN kernel's geometry stage (which adds the bias and applies the mask's sigmoid).
+extern "C" size_t dcnv2_fused_offsets_workspace_bytes(int B, int Cin, int H, int W, int Cout) {
+  if (B <= 0 || Cin <= 0 || H <= 0 || W <= 0 || Cout <= 0) return 0;
+  return dcnv2_workspace_bytes(B, Cin, H, W, Cout) + dcn_align256((size_t)32 * Cin * 9 * 2) +
+         dcn_align256((size_t)B * 27 * H * W * 4);
+}
+
+extern "C" int dcnv2_forward_fused_offsets(const float* input, const float* weight, const float* bias,
+                                           const float* om_weight, const float* om_bias, float* output,
+                                           float* offset_mask_out, int B, int Cin, int H, int W, int Cout,
+                                           const float* scale, const float* shift, int flags,
+                                           void* workspace, size_t workspace_bytes, ctdet_stream_t stream) {
+  using namespace ctdet;
+  if (B < 0 || Cin <= 0 || H <= 0 || W <= 0 || Cout <= 0) return CTDET_EINVAL;
+  if (flags & ~(DCN_FLAG_RELU | DCN_FLAG_FP32_BLEND | DCN_FLAG_PACKED_WEIGHT)) return CTDET_EINVAL;
+  if (Cin % kBK != 0 || Cout % 16 != 0 || Cout < 16 || Cout > 256) return CTDET_EUNSUPPORTED;
+  if (B == 0) return CTDET_OK;
+  if (!input || !weight || !om_weight || !output || !workspace) return CTDET_ENULL;
+  if (workspace_bytes < dcnv2_fused_offsets_workspace_bytes(B, Cin, H, W, Cout)) return CTDET_EWORKSPACE;
+  if (reinterpret_cast<uintptr_t>(workspace) & 15u) return CTDET_EALIGN;
+  if ((size_t)H * W >= ((size_t)1 << 31) / (size_t)Cin || B > 65535 || (long long)27 * H * W > 0x7fffffffLL) return CTDET_EINVAL;
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t base_bytes = dcnv2_workspace_bytes(B, Cin, H, W, Cout);
+  unsigned char* wsp = reinterpret_cast<unsigned char*>(workspace);
+  __nv_bfloat16* xh = reinterpret_cast<__nv_bfloat16*>(wsp);
+  __nv_bfloat16* wk_om = reinterpret_cast<__nv_bfloat16*>(wsp + base_bytes);
+  float* raw = offset_mask_out ? offset_mask_out
+                               : reinterpret_cast<float*>(wsp + base_bytes + dcn_align256((size_t)32 * Cin * 9 * 2));
+  const int Pin = H * W;
+  const int vec = (Pin % 4 == 0 && aligned16(input)) ? 1 : 0;
+  dcn_pack_input_kernel<<<dim3((Pin + 63) / 64, (Cin + 63) / 64, B), 256, 0, st>>>(input, xh, Cin, Pin, vec, nullptr, 1, 0);
+  int rc = check_launch();
+  if (rc) return rc;
+  dcn_pack_weight_kernel<<<kNumSMs, 256, 0, st>>>(om_weight, wk_om, 32, Cin, 27);
+  rc = check_launch();
+  if (rc) return rc;
+
+  DcnParams prm;
+  prm.xh = xh; prm.offset = raw; prm.mask = raw; prm.wk = wk_om; prm.bias = nullptr;       // (offset / mask are not read)
+  prm.off_bstride = 0; prm.mask_bstride = 0; prm.mask_logit = 0; prm.om_bias = nullptr;
+  prm.scale = nullptr; prm.shift = nullptr; prm.y = raw;
+  prm.Cin = Cin; prm.H = H; prm.W = W; prm.Ho = H; prm.Wo = W; prm.Cout = 32;
+  prm.stride = 1; prm.pad = 1; prm.dil = 1; prm.relu = 0;
+  prm.xw = W; prm.ximg = Pin * Cin; prm.xorg = 0;
+  prm.tiles_x = (W + kTileW - 1) / kTileW;
+  prm.tiles_per_image = prm.tiles_x * ((H + kTileH - 1) / kTileH);
+  const long long tiles = (long long)B * prm.tiles_per_image;
+  if (tiles > 0x7fffffffLL) return CTDET_EINVAL;
+  prm.num_tiles = (int)tiles;
+  prm.tmem_cols = 64;
+  prm.plain = 1; prm.cout_store = 27;
+  const size_t stage_bytes = (size_t)kTileM * kBK * 2 + (size_t)32 * kBK * 2;
+  const DcnTunables& tune = dcn_tunables();
+  static int plain_stages = 0;                  // CTDET_DCN_PLAIN_STAGES (read once): 4 (default) or 8
+  if (plain_stages == 0) {
+    const char* ev = getenv("CTDET_DCN_PLAIN_STAGES");
+    plain_stages = ev ? atoi(ev) : 4;
+    if (plain_stages != 4 && plain_stages != 8) plain_stages = 4;
+  }
+  const int stages = plain_stages;
+  prm.stages = stages;
+  prm.mma_sleep = tune.mma_sleep;
+  // the weight loader is one lane that serves every K block in turn: a __nanosleep between its polls (20 ns asked for, ~0.45 us
+  // slept) was free next to the 1568-cycle K blocks of the deformable kernel, but here it WAS the K block time (950 cycles
+  // whatever the producers did: ncu showed them waiting for empty stages)
+  prm.ld_sleep = 0;
+  const size_t smem = (size_t)stages * stage_bytes + kGeoBytes + 1024;
+  auto kern = dcn_forward_kernel<false, 16, true>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
+  kern<<<(unsigned)(tiles < kNumSMs ? tiles : kNumSMs), (16 + 10) * 32, smem, st>>>(prm);
+  rc = check_launch();
+  if (rc) return rc;
+  return dcn_forward_impl(input, weight, bias, raw, nullptr, om_bias, 1, output, B, Cin, H, W, Cout, 3, 3, 1, 1, 1, 1, 1, 1, 1, 1,
+                          scale, shift, flags, workspace, base_bytes, stream, 1);
 }

@@ -152,6 +152,9 @@ struct DcnParams {
   int mask_logit;                  // 1: mask holds logits (raw conv_offset_mask output): sigmoid applied here
   const float* om_bias;            // [27] bias of conv_offset_mask to add (offset channels 0..17, mask 18..26) or null
   uint32_t tmem_cols;
+  int plain = 0;                   // 1: an ordinary 3x3 convolution (zero offsets, mask 1): conv_offset_mask itself on the
+                                   //    tensor cores -- the geometry stage loads nothing, the producers gather one corner
+  int cout_store = 0;              // output channels written (0 = Cout; 27 of the 32 computed for conv_offset_mask)
 };
 
 
@@ -213,7 +216,7 @@ struct DcnBarriers {
 // swizzled layout, one pipeline stage per K block.  8 lanes x 16 B gather one pixel's 64 channels
 // (one warp-wide load = 4 full 128-byte lines); the gathers of K block n+1 are issued while block n
 // is blended (register double-buffering across K blocks AND tiles).
-template <bool kFp32Blend, int NP, bool kPadOdd = false>
+template <bool kFp32Blend, int NP, bool kPadOdd = false, bool kPlain = false>
 __device__ __forceinline__ void dcn_producer_loop(const DcnParams& prm, uint8_t* smem, uint32_t stage_bytes, int NS,
                                                   const uint4* geo_w, const uint32_t* geo_g, DcnBarriers& bars,
                                                   int warp, int lane, int tile_first, int my_tiles, int kb0, int kb1) {
@@ -233,9 +236,11 @@ __device__ __forceinline__ void dcn_producer_loop(const DcnParams& prm, uint8_t*
     const uint32_t dx = (g & 1u) ? ex : 0u;
     const uint32_t e2 = e0 + ((g & 2u) ? ey : 0u);
     va[i] = ldg_gather16(xc + e0);
-    vb[i] = ldg_gather16(xc + e0 + dx);
-    vc[i] = ldg_gather16(xc + e2);
-    vd[i] = ldg_gather16(xc + e2 + dx);
+    if (!kPlain) {                               // (plain convolution: integer positions, the top-left corner is the sample)
+      vb[i] = ldg_gather16(xc + e0 + dx);
+      vc[i] = ldg_gather16(xc + e2);
+      vd[i] = ldg_gather16(xc + e2 + dx);
+    }
   };
   const int total = my_tiles * (kb1 - kb0);
   const int cb0 = kb0 / 9, t0 = kb0 - 9 * cb0;
@@ -268,7 +273,9 @@ __device__ __forceinline__ void dcn_producer_loop(const DcnParams& prm, uint8_t*
     for (int i = 0; i < ITERS; ++i) {
       const uint4 wq = gw[i * NP * 4];
       uint4 q;
-      if (kFp32Blend) {
+      if (kPlain) {                              // weight of the one corner: 1, or 0 outside the image
+        q = wq.x != 0u ? va[i] : make_uint4(0u, 0u, 0u, 0u);
+      } else if (kFp32Blend) {
         const float w1 = __uint_as_float(wq.x), w2 = __uint_as_float(wq.y),
                     w3 = __uint_as_float(wq.z), w4 = __uint_as_float(wq.w);
         q.x = blend_fp32(va[i].x, vb[i].x, vc[i].x, vd[i].x, w1, w2, w3, w4);
@@ -308,6 +315,75 @@ __device__ __forceinline__ void dcn_producer_loop(const DcnParams& prm, uint8_t*
   }
 }
 
+// Producer warps of the PLAIN 3x3 convolution (conv_offset_mask on the tensor cores): the A tile of a K block is a copy --
+// one 128-byte row of 64 channels per pixel from the integer tap position, zeros outside the image -- so a K block has
+// no arithmetic to hide its ~1000 cycles of per-block pipeline bookkeeping behind (the deformable producer loop, where all
+// NP warps build every K block together, ran this at 1180 cycles per K block against 1568 with four corners and the blend).
+// Here the NP warps are split into NS groups of NP / NS: group s owns pipeline stage s and builds blocks s, s + NS, ...
+// (a stage has ONE group of writers: parity waits on its `empty` barrier only tell consecutive phases apart), each warp of
+// the group 128 / (NP / NS) rows of the block, 8 independent 16-byte loads per lane in flight per pass of 32 rows, NS blocks
+// under construction at once.  full[s] expects NP / NS producer arrivals (+ the weight loader's).  NS = 4 (not 8): the
+// gathers live on L1 hits -- the nine taps of a tile read the same 23 KB patch -- and 8 stages of shared memory leave 30 KB
+// of L1 (measured: 119 us at 8 stages with one warp per stage, 64 channels @128^2, B = 32).
+template <int NP>
+__device__ __forceinline__ void dcn_plain_producer_loop(const DcnParams& prm, uint8_t* smem, uint32_t stage_bytes, int NS,
+                                                        const uint4* geo_w, const uint32_t* geo_g, DcnBarriers& bars,
+                                                        int warp, int lane, int tile_first, int my_tiles, int KB) {
+  const int Cin = prm.Cin;
+  const int sub = lane >> 3, chunk = lane & 7;
+  const int total = my_tiles * KB;
+  int done_tile = 0;                              // tiles [0, done_tile) were released (geo_empty) by this warp
+  const int wps = NP / NS;                        // warps per stage (NP % NS == 0)
+  const int s = warp / wps, part = warp - s * wps;
+  const int rows = kTileM / wps;                  // rows of a block built by this warp (a multiple of 32)
+  for (int n = s; n < total; n += NS) {
+    const int it = n / KB, kb = n - it * KB;
+    const int cb = kb / 9, t = kb - 9 * cb;
+    while (done_tile < it) {                      // tiles this warp is through with (or never had a block of)
+      // (its own blocks of those tiles are complete: program order; the wait below keeps the arrivals in tile order)
+      dcn_mbar_wait(&bars.geo_full[done_tile & 1], (unsigned)((done_tile >> 1) & 1));
+      __syncwarp();
+      if (lane == 0) dcn_mbar_arrive(&bars.geo_empty[done_tile & 1]);
+      ++done_tile;
+    }
+    dcn_mbar_wait(&bars.geo_full[it & 1], (unsigned)((it >> 1) & 1));
+    dcn_mbar_wait(&bars.empty[s], (unsigned)(((n / NS) & 1) ^ 1));
+    const int tile = tile_first + it;
+    const __nv_bfloat16* xc = prm.xh + (size_t)(tile / prm.tiles_per_image) * prm.ximg + prm.xorg + chunk * 8 + cb * kBK;
+    const uint32_t* gg = geo_g + ((it & 1) * 9 + t) * kTileM + sub;
+    const uint4* gw = geo_w + ((it & 1) * 9 + t) * kTileM + sub;
+    uint8_t* a_tile = smem + (size_t)s * stage_bytes;
+#pragma unroll 1
+    for (int r0 = part * rows; r0 < (part + 1) * rows; r0 += 32) {   // a pass = 8 x 4 rows (sub); 8 loads per lane in flight
+      uint4 v[8];
+      uint32_t keep = 0u;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int row = r0 + i * 4;
+        const uint32_t g = gg[row];
+        keep |= (gw[row].x != 0u ? 1u : 0u) << i;
+        v[i] = ldg_gather16(xc + (g & ~3u));
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const uint32_t row = (uint32_t)(r0 + i * 4 + sub);
+        const uint4 q = (keep >> i) & 1u ? v[i] : make_uint4(0u, 0u, 0u, 0u);
+        *reinterpret_cast<uint4*>(a_tile + row * 128u + ((uint32_t)(chunk ^ (int)(row & 7u)) << 4)) = q;
+      }
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncwarp();
+    if (lane == 0) dcn_mbar_arrive(&bars.full[s]);
+  }
+  while (done_tile < my_tiles) {
+    dcn_mbar_wait(&bars.geo_full[done_tile & 1], (unsigned)((done_tile >> 1) & 1));
+    __syncwarp();
+    if (lane == 0) dcn_mbar_arrive(&bars.geo_empty[done_tile & 1]);
+    ++done_tile;
+  }
+  (void)Cin;
+}
+
 // Geometry of one tile (thread r = pixel of the tile, all 9 taps) into geometry buffer it & 1.
 // Waits for the buffer to be free; the caller arrives on geo_full afterwards.
 template <bool kFp32Blend>
@@ -325,10 +401,17 @@ __device__ __forceinline__ void dcn_geometry_tile(const DcnParams& prm, int tile
   const int buf = it & 1;
   // all 27 loads first (one DRAM round trip, issued before the buffer is even free)
   float ov[18], mv[9];
+  if (prm.plain) {
 #pragma unroll
-  for (int k = 0; k < 18; ++k) ov[k] = ldg_stream1(offb + (size_t)k * P);
+    for (int k = 0; k < 18; ++k) ov[k] = 0.f;
 #pragma unroll
-  for (int k = 0; k < 9; ++k) mv[k] = ldg_stream1(mskb + (size_t)k * P);
+    for (int k = 0; k < 9; ++k) mv[k] = 1.f;
+  } else {
+#pragma unroll
+    for (int k = 0; k < 18; ++k) ov[k] = ldg_stream1(offb + (size_t)k * P);
+#pragma unroll
+    for (int k = 0; k < 9; ++k) mv[k] = ldg_stream1(mskb + (size_t)k * P);
+  }
   if (prm.om_bias != nullptr) {          // conv_offset_mask's bias, not added by the caller
 #pragma unroll
     for (int k = 0; k < 18; ++k) ov[k] += __ldg(prm.om_bias + k);

@@ -137,6 +137,48 @@ def dcnv2_forward_raw27(input, offset_mask, weight, bias=None, offset_mask_bias=
     return out
 
 
+def dcnv2_forward_fused_offsets(input, weight, bias, om_weight, om_bias=None, scale=None, shift=None, relu=False,
+                                fp32_blend=False, packed_weight=None, return_offset_mask=False):
+    """`DCN.forward` of deform_conv.py:505-513 in one call (C ABI dcnv2_forward_fused_offsets): `conv_offset_mask` (`om_weight`
+    [27,Cin,3,3], `om_bias` [27]) runs on the tensor cores over the same NHWC bf16 copy of `input` the deformable
+    convolution samples, and its raw output goes straight into the DCN kernel (chunk / cat / sigmoid / bias inside).
+    stride = padding = dilation = 1.  return_offset_mask: also return the raw 27-channel output (without bias)."""
+    if not input.is_cuda:
+        raise NotImplementedError("Deformable Conv is not supported on CPUs!")    # deform_conv.py:203-204
+    lib = _lib.load()
+    input = _lib.f32c(input, "input")
+    weight = _lib.f32c(weight, "weight")
+    om_weight = _lib.f32c(om_weight, "om_weight")
+    bias = None if bias is None else _lib.f32c(bias, "bias")
+    om_bias = None if om_bias is None else _lib.f32c(om_bias, "om_bias")
+    scale = None if scale is None else _lib.f32c(scale, "scale")
+    shift = None if shift is None else _lib.f32c(shift, "shift")
+    B, Cin, H, W = input.shape
+    Cout, cin_w, kh, kw = weight.shape
+    if (kh, kw) != (3, 3) or cin_w != Cin or tuple(om_weight.shape) != (27, Cin, 3, 3):
+        raise NotImplementedError("dcnv2_forward_fused_offsets: 3x3, one group, conv_offset_mask [27,Cin,3,3]")
+    if om_bias is not None and om_bias.numel() != 27:
+        raise RuntimeError("om_bias must have 27 elements")
+    out = torch.empty((B, Cout, H, W), dtype=torch.float32, device=input.device)
+    raw = torch.empty((B, 27, H, W), dtype=torch.float32, device=input.device) if return_offset_mask else None
+    if out.numel() == 0:
+        return (out, raw) if return_offset_mask else out
+    nbytes = lib.dcnv2_fused_offsets_workspace_bytes(B, Cin, H, W, Cout)
+    ws = _workspace(max(nbytes, 16), input.device)
+    flags = (FLAG_RELU if relu else 0) | (FLAG_FP32_BLEND if fp32_blend else 0)
+    if packed_weight is not None:
+        if packed_weight.numel() != lib.dcnv2_packed_weight_bytes(Cin, Cout) or packed_weight.device != input.device:
+            raise RuntimeError("packed_weight does not belong to a [%d,%d,3,3] weight on %s" % (Cout, Cin, input.device))
+        flags |= FLAG_PACKED_WEIGHT
+    with torch.cuda.device(input.device):
+        rc = lib.dcnv2_forward_fused_offsets(_lib.ptr(input), _lib.ptr(weight if packed_weight is None else packed_weight),
+                                             _lib.ptr(bias), _lib.ptr(om_weight), _lib.ptr(om_bias), _lib.ptr(out), _lib.ptr(raw),
+                                             B, Cin, H, W, Cout, _lib.ptr(scale), _lib.ptr(shift), flags,
+                                             _lib.ptr(ws), ctypes.c_size_t(ws.numel()), _lib.stream_ptr(input.device))
+    _lib.check(rc, "dcnv2_forward_fused_offsets")
+    return (out, raw) if return_offset_mask else out
+
+
 def dcnv2_backward(input, offset, mask, weight, grad_output, stride=1, padding=0, dilation=1, groups=1,
                    deformable_groups=1, with_bias=True, need_input_grads=True, need_weight_grad=True):
     """Low-level call: returns (grad_input, grad_offset, grad_mask, grad_weight, grad_bias); entries that were
@@ -266,6 +308,7 @@ class DeformConvV2(nn.Module):
         self.actf = nn.Sequential(nn.BatchNorm2d(cho, momentum=0.1), nn.ReLU(inplace=True))
         self.conv = DCN(chi, cho, kernel_size=(3, 3), stride=1, padding=1, dilation=1, deformable_groups=1)
         nn.init.uniform_(self.actf[0].weight.data)
+        self.fuse_offset_conv = True      # eval: conv_offset_mask on the tensor cores inside the DCN call (bf16 operands)
 
     def _packed_weight(self):
         """Inference: the tensor-core image of the DCN weights, rebuilt when the parameter is replaced, moved or
@@ -288,6 +331,10 @@ class DeformConvV2(nn.Module):
             com = self.conv.conv_offset_mask
             # the 27-channel convolution without its bias; bias, chunk / cat and the mask's sigmoid happen inside
             # the DCN kernel's geometry stage
+            if self.fuse_offset_conv and com.stride == (1, 1) and com.padding == (1, 1) and com.dilation == (1, 1):
+                # conv_offset_mask on the tensor cores over the DCN's own NHWC bf16 copy of x (one call, x packed once)
+                return dcnv2_forward_fused_offsets(x, self.conv.weight, self.conv.bias, com.weight, com.bias, scale=scale,
+                                                   shift=shift, relu=True, packed_weight=self._packed_weight())
             raw = torch.nn.functional.conv2d(x, com.weight, None, com.stride, com.padding, com.dilation, com.groups)
             return dcnv2_forward_raw27(x, raw, self.conv.weight, self.conv.bias, com.bias, 1, 1, 1,
                                        scale=scale, shift=shift, relu=True, packed_weight=self._packed_weight())

@@ -316,6 +316,21 @@ int dcnv2_forward_raw27(const float* input, const float* weight, const float* bi
                         const float* scale, const float* shift, int flags,
                         void* workspace, size_t workspace_bytes, ctdet_stream_t stream);
 
+/* The same with conv_offset_mask itself inside the call: `om_weight` f32 [27,Cin,3,3] /
+ * `om_bias` f32 [27] or NULL are the parameters of the DCN's `nn.Conv2d(Cin, 27, 3, stride 1, padding 1)`
+ * (deform_conv.py:505-513; chunk / cat / sigmoid convention resnet.py:308-313).  x is packed to NHWC bf16 ONCE; the
+ * 27-channel convolution runs on the tensor cores over that copy (the main kernel in its plain mode: zero offsets, mask 1,
+ * one corner per tap, bf16 operands, fp32 accumulation) and its raw output feeds the DCN kernel's geometry stage as in
+ * dcnv2_forward_raw27.  stride = padding = dilation = 1 (what DLA-34 uses).
+ *   offset_mask_out f32 [B,27,H,W] or NULL: where the raw convolution output (without bias) goes; NULL = in the workspace.
+ * workspace: dcnv2_fused_offsets_workspace_bytes() bytes, 16-byte aligned.  Other arguments / flags as dcnv2_forward. */
+size_t dcnv2_fused_offsets_workspace_bytes(int B, int Cin, int H, int W, int Cout);
+int dcnv2_forward_fused_offsets(const float* input, const float* weight, const float* bias,
+                                const float* om_weight, const float* om_bias, float* output,
+                                float* offset_mask_out, int B, int Cin, int H, int W, int Cout,
+                                const float* scale, const float* shift, int flags,
+                                void* workspace, size_t workspace_bytes, ctdet_stream_t stream);
+
 /* ---------------------------------------------------------------- DCNv2 backward ---------
  * Replaces modulated_deform_conv_backward (deform_conv.h:314-338; same argument meaning, minus the
  * `ones`/`columns` scratch tensors and the unused `bias`).  All gradient outputs are OVERWRITTEN

@@ -217,3 +217,57 @@ def test_packed_weight_path_is_bit_equal_and_the_module_cache_tracks_the_weight_
         mod.invalidate_packed_weight()
         assert torch.equal(mod(x), y2)
     assert float((y1 - y2).abs().max()) > 0
+
+
+@pytest.mark.parametrize("cfg", [(2, 64, 64, 24, 20), (1, 128, 64, 16, 16), (1, 256, 128, 9, 7), (2, 64, 256, 33, 17), (1, 512, 256, 16, 16)])
+def test_fused_offset_conv_matches_conv2d_plus_the_raw27_call(cfg):
+    """`dcnv2_forward_fused_offsets`: conv_offset_mask (deform_conv.py:505-513, convention resnet.py:308-313) on the tensor
+    cores inside the DCN call.  (i) its raw 27 channels against F.conv2d -- exact to fp32 summation order on
+    bf16-representable operands (<= 1e-5 of the scale), <= 1e-2 relative L2 on general fp32 operands (bf16 rounding over
+    K = 9 Cin); (ii) the DCN output bit-equal to `dcnv2_forward_raw27` fed with those same 27 channels (same main kernel, same
+    packed input); (iii) against the unfused pair on cuDNN's fp32 offsets within the forward's stated tolerance, with small
+    conv_offset_mask weights as in a trained / freshly initialised DCN (offsets of a few pixels)."""
+    from detectron2_centernet_b200 import deform_conv as DC
+    B, Cin, Cout, H, W = cfg
+    g = torch.Generator(device="cpu").manual_seed(5 + Cin)
+    x = torch.randn(B, Cin, H, W, generator=g).to(DEV)
+    w = ((torch.rand(Cout, Cin, 3, 3, generator=g) - 0.5) * 2 / math.sqrt(9 * Cin)).to(DEV)
+    b = (torch.randn(Cout, generator=g) * 0.1).to(DEV)
+    wo = (torch.randn(27, Cin, 3, 3, generator=g) * (1.5 / math.sqrt(9 * Cin))).to(DEV)
+    bo = (torch.randn(27, generator=g) * 0.2).to(DEV)
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        # (i) exactness on bf16-representable operands
+        xb, wob = x.bfloat16().float(), wo.bfloat16().float()
+        _, raw = DC.dcnv2_forward_fused_offsets(xb, w, b, wob, bo, return_offset_mask=True)
+        ref = torch.nn.functional.conv2d(xb.double(), wob.double(), None, 1, 1).float()
+        assert float((raw - ref).abs().max()) <= 1e-5 * float(ref.abs().max())
+        # general operands
+        out, raw = DC.dcnv2_forward_fused_offsets(x, w, b, wo, bo, return_offset_mask=True)
+        ref = torch.nn.functional.conv2d(x, wo, None, 1, 1)
+        assert float((raw - ref).norm() / ref.norm()) <= 1e-2
+        # (ii) same main kernel on the same 27 channels
+        want = DC.dcnv2_forward_raw27(x, raw, w, b, bo, 1, 1, 1)
+        assert torch.equal(out, want)
+        # (iii) against the unfused pair (fp32 offsets from cuDNN)
+        unf = DC.dcnv2_forward_raw27(x, ref, w, b, bo, 1, 1, 1)
+        emax, el2 = _errs(out.cpu().numpy(), unf.cpu().numpy())
+        assert emax <= 2e-2 and el2 <= 1e-2, (cfg, emax, el2)
+    finally:
+        torch.backends.cudnn.allow_tf32 = True
+
+
+def test_deformconvv2_eval_uses_the_fused_offset_conv():
+    from detectron2_centernet_b200 import deform_conv as DC
+    torch.manual_seed(3)
+    m = DC.DeformConvV2(64, 64).to(DEV).eval()
+    torch.nn.init.normal_(m.conv.conv_offset_mask.weight, std=1.0 / math.sqrt(9 * 64))
+    torch.nn.init.normal_(m.conv.conv_offset_mask.bias, std=0.2)
+    x = torch.randn(2, 64, 24, 40, device=DEV)
+    with torch.no_grad():
+        a = m(x)
+        m.fuse_offset_conv = False
+        b = m(x)
+    emax, el2 = _errs(a.cpu().numpy(), b.cpu().numpy())
+    assert emax <= 2e-2 and el2 <= 1e-2, (emax, el2)
+    assert not torch.equal(a, b)                               # (two different offset convolutions really ran)
