@@ -356,14 +356,17 @@ __device__ __forceinline__ void dcn_plain_producer_loop(const DcnParams& prm, ui
 #pragma unroll 1
     for (int r0 = part * rows; r0 < (part + 1) * rows; r0 += 32) {   // a pass = 8 x 4 rows (sub); 8 loads per lane in flight
       uint4 v[8];
-      uint32_t keep = 0u;
+      uint32_t keep = 0u, g8[8];
+      // the table reads first, all of them: the volatile loads below stay in program order, and a table read between
+      // two of them would put its shared-memory latency on every load's issue
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         const int row = r0 + i * 4;
-        const uint32_t g = gg[row];
+        g8[i] = gg[row] & ~3u;
         keep |= (gw[row].x != 0u ? 1u : 0u) << i;
-        v[i] = ldg_gather16(xc + (g & ~3u));
       }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[i] = ldg_gather16(xc + g8[i]);
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         const uint32_t row = (uint32_t)(r0 + i * 4 + sub);
