@@ -155,6 +155,7 @@ struct DcnParams {
   int plain = 0;                   // 1: an ordinary 3x3 convolution (zero offsets, mask 1): conv_offset_mask itself on the
                                    //    tensor cores -- the geometry stage loads nothing, the producers gather one corner
   int cout_store = 0;              // output channels written (0 = Cout; 27 of the 32 computed for conv_offset_mask)
+  long long y_bstride = 0;         // elements between images in y (0 = cout_store * Ho * Wo): a chunk of a wider output
 };
 
 

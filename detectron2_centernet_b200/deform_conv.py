@@ -179,6 +179,33 @@ def dcnv2_forward_fused_offsets(input, weight, bias, om_weight, om_bias=None, sc
     return (out, raw) if return_offset_mask else out
 
 
+def conv3x3(input, weight, bias=None, relu=False):
+    """`F.conv2d(input, weight, bias, stride=1, padding=1)` (+ ReLU) for a 3x3 kernel on the tensor cores (C ABI
+    ctdet_conv3x3: the DCN forward kernel in its plain mode; bf16 operands, fp32 accumulation) -- the first layer of the ctdet
+    heads, centernet.py:112-121.  Inference only (no autograd)."""
+    if not input.is_cuda:
+        raise NotImplementedError("conv3x3 runs on CUDA tensors only")
+    lib = _lib.load()
+    input = _lib.f32c(input, "input")
+    weight = _lib.f32c(weight, "weight")
+    bias = None if bias is None else _lib.f32c(bias, "bias")
+    B, Cin, H, W = input.shape
+    Cout = weight.shape[0]
+    if tuple(weight.shape) != (Cout, Cin, 3, 3) or Cin % 64 != 0:
+        raise NotImplementedError("conv3x3: weight [Cout,Cin,3,3] with Cin % 64 == 0")
+    out = torch.empty((B, Cout, H, W), dtype=torch.float32, device=input.device)
+    if out.numel() == 0:
+        return out
+    nbytes = lib.ctdet_conv3x3_workspace_bytes(B, Cin, H, W, Cout)
+    ws = _workspace(max(nbytes, 16), input.device)
+    with torch.cuda.device(input.device):
+        rc = lib.ctdet_conv3x3(_lib.ptr(input), _lib.ptr(weight), _lib.ptr(bias), _lib.ptr(out), B, Cin, H, W, Cout,
+                               FLAG_RELU if relu else 0, _lib.ptr(ws), ctypes.c_size_t(ws.numel()),
+                               _lib.stream_ptr(input.device))
+    _lib.check(rc, "ctdet_conv3x3")
+    return out
+
+
 def dcnv2_backward(input, offset, mask, weight, grad_output, stride=1, padding=0, dilation=1, groups=1,
                    deformable_groups=1, with_bias=True, need_input_grads=True, need_weight_grad=True):
     """Low-level call: returns (grad_input, grad_offset, grad_mask, grad_weight, grad_bias); entries that were

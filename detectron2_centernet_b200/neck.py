@@ -199,8 +199,26 @@ class CtdetHead(nn.Module):
                         nn.init.constant_(m.bias, 0)
             setattr(self, name.lower(), fc)
 
+    fuse_first_conv = True     # eval, no autograd: the 3x3 convolution + ReLU of every branch on the tensor cores (bf16 operands)
+
+    def _trunk(self, fc, x):
+        """Everything of a branch but its last layer: Conv3x3 + ReLU (centernet.py:112-121)."""
+        c = fc[0]
+        if (self.fuse_first_conv and not torch.is_grad_enabled() and x.is_cuda and isinstance(c, nn.Conv2d) and
+                c.kernel_size == (3, 3) and c.stride == (1, 1) and c.padding == (1, 1) and c.dilation == (1, 1) and
+                c.groups == 1 and c.in_channels % 64 == 0 and len(fc) == 3 and isinstance(fc[1], nn.ReLU)):
+            from .deform_conv import conv3x3
+            return conv3x3(x, c.weight, c.bias, relu=True)
+        return fc[:-1](x)
+
+    def _branch(self, name, x):
+        fc = getattr(self, name.lower())
+        if isinstance(fc, nn.Sequential):
+            return fc[-1](self._trunk(fc, x))
+        return fc(x)
+
     def forward(self, x):
-        return {name: getattr(self, name.lower())(x) for name in self.heads}
+        return {name: self._branch(name, x) for name in self.heads}
 
     def decode(self, x, down_ratio=4, K=100, fuse=True):
         """Eval path `ctdet_decode(hm.sigmoid_(), wh, reg, K)` (centernet.py:151-166) on the heads of `x` for a batch: with
@@ -209,10 +227,10 @@ class CtdetHead(nn.Module):
         Returns boxes, scores, classes, inds."""
         from . import decode as D
         hm = self.hm
-        wh, reg = self.wh(x), (self.reg(x) if "reg" in self.heads else None)
+        wh, reg = self._branch("wh", x), (self._branch("reg", x) if "reg" in self.heads else None)
         last = hm[-1] if isinstance(hm, nn.Sequential) else None
         if (fuse and last is not None and last.kernel_size == (1, 1) and
                 D.head_decode_fusable(last.in_channels, last.out_channels, x.shape[2], x.shape[3])):
-            feat = hm[:-1](x)
+            feat = self._trunk(hm, x)
             return D.hm_head_decode_batch(feat, last.weight, last.bias, wh, reg, down_ratio=down_ratio, K=K)
-        return D.ctdet_decode_batch(hm(x), wh, reg, down_ratio=down_ratio, K=K, logits=True)
+        return D.ctdet_decode_batch(self._branch("hm", x), wh, reg, down_ratio=down_ratio, K=K, logits=True)

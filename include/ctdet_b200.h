@@ -331,6 +331,15 @@ int dcnv2_forward_fused_offsets(const float* input, const float* weight, const f
                                 const float* scale, const float* shift, int flags,
                                 void* workspace, size_t workspace_bytes, ctdet_stream_t stream);
 
+/* An ordinary 3x3 convolution, stride 1, padding 1, + bias + optional ReLU (DCN_FLAG_RELU) on the tensor cores (bf16
+ * operands, fp32 accumulation): the first layer of the ctdet heads, nn.Conv2d(64, head_conv, 3, padding=1) + ReLU
+ * (centernet.py:112-121), as the same kernel in its plain mode.  input f32 [B,Cin,H,W], weight f32 [Cout,Cin,3,3], bias
+ * f32 [Cout] or NULL, output f32 [B,Cout,H,W].  Requires Cin % 64 == 0.  workspace: ctdet_conv3x3_workspace_bytes(). */
+size_t ctdet_conv3x3_workspace_bytes(int B, int Cin, int H, int W, int Cout);
+int ctdet_conv3x3(const float* input, const float* weight, const float* bias, float* output,
+                  int B, int Cin, int H, int W, int Cout, int flags,
+                  void* workspace, size_t workspace_bytes, ctdet_stream_t stream);
+
 /* ---------------------------------------------------------------- DCNv2 backward ---------
  * Replaces modulated_deform_conv_backward (deform_conv.h:314-338; same argument meaning, minus the
  * `ones`/`columns` scratch tensors and the unused `bias`).  All gradient outputs are OVERWRITTEN

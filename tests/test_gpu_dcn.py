@@ -271,3 +271,48 @@ def test_deformconvv2_eval_uses_the_fused_offset_conv():
     emax, el2 = _errs(a.cpu().numpy(), b.cpu().numpy())
     assert emax <= 2e-2 and el2 <= 1e-2, (emax, el2)
     assert not torch.equal(a, b)                               # (two different offset convolutions really ran)
+
+
+@pytest.mark.parametrize("cfg", [(2, 64, 256, 24, 20), (1, 64, 80, 16, 16), (1, 128, 200, 9, 7), (2, 64, 16, 33, 40)])
+def test_plain_conv3x3_matches_conv2d(cfg):
+    """`ctdet_conv3x3` (the heads' first layer, centernet.py:112-121, on the tensor cores): exact to fp32 summation order on
+    bf16-representable operands (<= 1e-5 of the scale), <= 1e-2 relative L2 on general fp32 operands; output channels
+    beyond 128 come from a second chunk, counts that are not multiples of 16 from a zero-padded weight tile."""
+    from detectron2_centernet_b200 import deform_conv as DC
+    B, Cin, Cout, H, W = cfg
+    g = torch.Generator(device="cpu").manual_seed(7 + Cout)
+    x = torch.randn(B, Cin, H, W, generator=g).to(DEV)
+    w = (torch.randn(Cout, Cin, 3, 3, generator=g) / math.sqrt(9 * Cin)).to(DEV)
+    b = torch.randn(Cout, generator=g).to(DEV)
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        xb, wb = x.bfloat16().float(), w.bfloat16().float()
+        ref = torch.relu(torch.nn.functional.conv2d(xb.double(), wb.double(), b.double(), 1, 1)).float()
+        got = DC.conv3x3(xb, wb, b, relu=True)
+        assert float((got - ref).abs().max()) <= 1e-5 * float(ref.abs().max())
+        ref = torch.nn.functional.conv2d(x, w, b, 1, 1)
+        got = DC.conv3x3(x, w, b)
+        assert float((got - ref).norm() / ref.norm()) <= 1e-2
+        got = DC.conv3x3(x, w, None)
+        ref = torch.nn.functional.conv2d(x, w, None, 1, 1)
+        assert float((got - ref).norm() / ref.norm()) <= 1e-2
+    finally:
+        torch.backends.cudnn.allow_tf32 = True
+
+
+def test_ctdet_head_eval_uses_the_tensor_core_first_layer():
+    from detectron2_centernet_b200 import neck as N
+    torch.manual_seed(11)
+    head = N.CtdetHead(64, 80, 256).to(DEV).eval()
+    x = torch.randn(2, 64, 24, 40, device=DEV)
+    with torch.no_grad():
+        a = head(x)
+        head.fuse_first_conv = False
+        b = head(x)
+    for k in ("hm", "wh", "reg"):
+        assert float((a[k] - b[k]).norm() / b[k].norm()) <= 1e-2, k
+        assert not torch.equal(a[k], b[k])
+    head.fuse_first_conv = True
+    y = head(x.requires_grad_(True))                       # under autograd the torch modules run
+    y["hm"].sum().backward()
+    assert x.grad is not None
