@@ -205,7 +205,7 @@ dcn_forward_kernel(const DcnParams prm) {
 
   if (warp < NP) {
     // ===================================== producers ==============================================
-    if (kPlain) dcn_plain_producer_loop<NP>(prm, smem, stage_bytes, NS, geo_w, geo_g, bars, warp, lane, tile_first, my_tiles, KB);
+    if (kPlain) dcn_plain_producer_loop<NP>(prm, smem, stage_bytes, NS, bars, warp, lane, tile_first, my_tiles, KB);
     else dcn_producer_loop<kFp32Blend, NP>(prm, smem, stage_bytes, NS, geo_w, geo_g, bars, warp, lane,
                                            tile_first, my_tiles, 0, KB);
   } else if (warp < NP + 4) {
@@ -249,7 +249,7 @@ dcn_forward_kernel(const DcnParams prm) {
   } else if (warp < NP + 8) {
     // ===================================== geometry ===============================================
     const int r = ((warp - NP - 4) << 5) + lane;                          // tile row = pixel of the tile
-    for (int it = 0; it < my_tiles; ++it) {
+    for (int it = 0; it < (kPlain ? 0 : my_tiles); ++it) {                // (plain mode: integer positions, no table)
       dcn_geometry_tile<kFp32Blend>(prm, tile_first + it, it, r, geo_w, geo_g, bars);
       __syncwarp();
       if (lane == 0) dcn_mbar_arrive(&bars.geo_full[it & 1]);
@@ -501,11 +501,11 @@ extern "C" int dcnv2_forward_fused_offsets(const float* input, const float* weig
   prm.plain = 1; prm.cout_store = 27;
   const size_t stage_bytes = (size_t)kTileM * kBK * 2 + (size_t)32 * kBK * 2;
   const DcnTunables& tune = dcn_tunables();
-  static int plain_stages = 0;                  // CTDET_DCN_PLAIN_STAGES (read once): 4 (default) or 8
+  static int plain_stages = 0;                  // CTDET_DCN_PLAIN_STAGES (read once): 8 (default) or 4
   if (plain_stages == 0) {
     const char* ev = getenv("CTDET_DCN_PLAIN_STAGES");
-    plain_stages = ev ? atoi(ev) : 4;
-    if (plain_stages != 4 && plain_stages != 8) plain_stages = 4;
+    plain_stages = ev ? atoi(ev) : 8;
+    if (plain_stages != 4 && plain_stages != 8) plain_stages = 8;
   }
   const int stages = plain_stages;
   prm.stages = stages;
@@ -514,7 +514,7 @@ extern "C" int dcnv2_forward_fused_offsets(const float* input, const float* weig
   // slept) was free next to the 1568-cycle K blocks of the deformable kernel, but here it WAS the K block time (950 cycles
   // whatever the producers did: ncu showed them waiting for empty stages)
   prm.ld_sleep = 0;
-  const size_t smem = (size_t)stages * stage_bytes + kGeoBytes + 1024;
+  const size_t smem = (size_t)stages * stage_bytes + 1024;        // (plain mode: no geometry table)
   auto kern = dcn_forward_kernel<false, 16, true>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
@@ -580,7 +580,7 @@ extern "C" int ctdet_conv3x3(const float* input, const float* weight, const floa
     const size_t stage_bytes = (size_t)kTileM * kBK * 2 + (size_t)n_pad * kBK * 2;
     prm.stages = 4;
     prm.mma_sleep = 0; prm.ld_sleep = 0;
-    const size_t smem = (size_t)prm.stages * stage_bytes + kGeoBytes + 1024;
+    const size_t smem = (size_t)prm.stages * stage_bytes + 1024;   // (plain mode: no geometry table)
     auto kern = dcn_forward_kernel<false, 16, true>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }

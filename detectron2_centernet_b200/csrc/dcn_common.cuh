@@ -316,76 +316,52 @@ __device__ __forceinline__ void dcn_producer_loop(const DcnParams& prm, uint8_t*
   }
 }
 
-// Producer warps of the PLAIN 3x3 convolution (conv_offset_mask on the tensor cores): the A tile of a K block is a copy --
-// one 128-byte row of 64 channels per pixel from the integer tap position, zeros outside the image -- so a K block has
-// no arithmetic to hide its ~1000 cycles of per-block pipeline bookkeeping behind (the deformable producer loop, where all
-// NP warps build every K block together, ran this at 1180 cycles per K block against 1568 with four corners and the blend).
-// Here the NP warps are split into NS groups of NP / NS: group s owns pipeline stage s and builds blocks s, s + NS, ...
-// (a stage has ONE group of writers: parity waits on its `empty` barrier only tell consecutive phases apart), each warp of
-// the group 128 / (NP / NS) rows of the block, 8 independent 16-byte loads per lane in flight per pass of 32 rows, NS blocks
-// under construction at once.  full[s] expects NP / NS producer arrivals (+ the weight loader's).  NS = 4 (not 8): the
-// gathers live on L1 hits -- the nine taps of a tile read the same 23 KB patch -- and 8 stages of shared memory leave 30 KB
-// of L1 (measured: 119 us at 8 stages with one warp per stage, 64 channels @128^2, B = 32).
+// Producer warps of the PLAIN 3x3 convolution (conv_offset_mask and the heads' first layer on the tensor cores; stride 1,
+// padding 1, dilation 1): the A tile of a K block is a copy -- one 128-byte row of 64 channels per pixel from the integer
+// tap position, zeros outside the image.  The first form went through the deformable machinery (geometry table in shared
+// memory, 16-byte gathers into registers, swizzled stores): 950 cycles per K block whatever the warp layout, because the
+// SM's L1 / shared-memory data pipe was 62 % busy with it (ncu: per K block 174 wavefronts of table reads incl. 96 bank
+// conflicts, 127 of global loads, 168 of stores, + the tensor core's own operand reads).  This form has no table -- the
+// positions are integers, computed from the row index -- and no registers in the path: `cp.async.cg` moves 16 bytes from
+// global memory straight to their swizzled place in the stage (src-size 0 = zero fill outside the image), one pass over
+// the data pipe instead of two.  The NP warps form NS groups; group s owns pipeline stage s and builds blocks s, s + NS, ...
+// (a stage has ONE group of writers: parity waits on its `empty` barrier only tell consecutive phases apart).
 template <int NP>
 __device__ __forceinline__ void dcn_plain_producer_loop(const DcnParams& prm, uint8_t* smem, uint32_t stage_bytes, int NS,
-                                                        const uint4* geo_w, const uint32_t* geo_g, DcnBarriers& bars,
-                                                        int warp, int lane, int tile_first, int my_tiles, int KB) {
-  const int Cin = prm.Cin;
+                                                        DcnBarriers& bars, int warp, int lane, int tile_first, int my_tiles,
+                                                        int KB) {
+  const int Cin = prm.Cin, H = prm.H, W = prm.W;
   const int sub = lane >> 3, chunk = lane & 7;
   const int total = my_tiles * KB;
-  int done_tile = 0;                              // tiles [0, done_tile) were released (geo_empty) by this warp
   const int wps = NP / NS;                        // warps per stage (NP % NS == 0)
   const int s = warp / wps, part = warp - s * wps;
-  const int rows = kTileM / wps;                  // rows of a block built by this warp (a multiple of 32)
+  const int rows = kTileM / wps;                  // rows of a block built by this warp (a multiple of 4)
   for (int n = s; n < total; n += NS) {
     const int it = n / KB, kb = n - it * KB;
     const int cb = kb / 9, t = kb - 9 * cb;
-    while (done_tile < it) {                      // tiles this warp is through with (or never had a block of)
-      // (its own blocks of those tiles are complete: program order; the wait below keeps the arrivals in tile order)
-      dcn_mbar_wait(&bars.geo_full[done_tile & 1], (unsigned)((done_tile >> 1) & 1));
-      __syncwarp();
-      if (lane == 0) dcn_mbar_arrive(&bars.geo_empty[done_tile & 1]);
-      ++done_tile;
-    }
-    dcn_mbar_wait(&bars.geo_full[it & 1], (unsigned)((it >> 1) & 1));
+    const int dy = t / 3 - 1, dx = t - 3 * (t / 3) - 1;
+    int tile = tile_first + it;
+    const int b = tile / prm.tiles_per_image;
+    tile -= b * prm.tiles_per_image;
+    const int tile_y = tile / prm.tiles_x, tile_x = tile - tile_y * prm.tiles_x;
+    const __nv_bfloat16* xb = prm.xh + (size_t)b * prm.ximg + prm.xorg + chunk * 8 + cb * kBK;
+    const uint32_t a_addr = smem_u32(smem + (size_t)s * stage_bytes);
     dcn_mbar_wait(&bars.empty[s], (unsigned)(((n / NS) & 1) ^ 1));
-    const int tile = tile_first + it;
-    const __nv_bfloat16* xc = prm.xh + (size_t)(tile / prm.tiles_per_image) * prm.ximg + prm.xorg + chunk * 8 + cb * kBK;
-    const uint32_t* gg = geo_g + ((it & 1) * 9 + t) * kTileM + sub;
-    const uint4* gw = geo_w + ((it & 1) * 9 + t) * kTileM + sub;
-    uint8_t* a_tile = smem + (size_t)s * stage_bytes;
-#pragma unroll 1
-    for (int r0 = part * rows; r0 < (part + 1) * rows; r0 += 32) {   // a pass = 8 x 4 rows (sub); 8 loads per lane in flight
-      uint4 v[8];
-      uint32_t keep = 0u, g8[8];
-      // the table reads first, all of them: the volatile loads below stay in program order, and a table read between
-      // two of them would put its shared-memory latency on every load's issue
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const int row = r0 + i * 4;
-        g8[i] = gg[row] & ~3u;
-        keep |= (gw[row].x != 0u ? 1u : 0u) << i;
-      }
-#pragma unroll
-      for (int i = 0; i < 8; ++i) v[i] = ldg_gather16(xc + g8[i]);
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const uint32_t row = (uint32_t)(r0 + i * 4 + sub);
-        const uint4 q = (keep >> i) & 1u ? v[i] : make_uint4(0u, 0u, 0u, 0u);
-        *reinterpret_cast<uint4*>(a_tile + row * 128u + ((uint32_t)(chunk ^ (int)(row & 7u)) << 4)) = q;
-      }
+#pragma unroll 4
+    for (int r = part * rows + sub; r < (part + 1) * rows; r += 4) {
+      const int hi = tile_y * kTileH + (r >> 4) + dy, wi = tile_x * kTileW + (r & 15) + dx;
+      // (a pixel of a ragged tile beyond the map: its output is never stored, whatever lands here)
+      const bool inside = hi >= 0 && hi < H && wi >= 0 && wi < W;
+      const __nv_bfloat16* src = xb + (inside ? (size_t)(hi * prm.xw + wi) * Cin : 0);
+      const uint32_t dst = a_addr + (uint32_t)r * 128u + ((uint32_t)(chunk ^ (r & 7)) << 4);
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(dst), "l"(src), "r"(inside ? 16 : 0) : "memory");
     }
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> tensor-core reads
     __syncwarp();
     if (lane == 0) dcn_mbar_arrive(&bars.full[s]);
   }
-  while (done_tile < my_tiles) {
-    dcn_mbar_wait(&bars.geo_full[done_tile & 1], (unsigned)((done_tile >> 1) & 1));
-    __syncwarp();
-    if (lane == 0) dcn_mbar_arrive(&bars.geo_empty[done_tile & 1]);
-    ++done_tile;
-  }
-  (void)Cin;
 }
 
 // Geometry of one tile (thread r = pixel of the tile, all 9 taps) into geometry buffer it & 1.
