@@ -58,6 +58,7 @@ SIGNATURES = {
                                     [c_void_p, c_size_t, c_void_p]),
     "ctdet_conv3x3_workspace_bytes": (c_size_t, [c_int] * 5),
     "ctdet_conv3x3": (c_int, [c_void_p] * 4 + [c_int] * 6 + [c_void_p, c_size_t, c_void_p]),
+    "ctdet_conv3x3_multi": (c_int, [c_void_p, c_int] + [c_void_p] * 4 + [c_int] * 5 + [c_void_p, c_size_t, c_void_p]),
     "dcnv2_forward_raw27": (c_int, [c_void_p] * 6 + [c_int] * 8 + [c_void_p, c_void_p, c_int] +
                             [c_void_p, c_size_t, c_void_p]),
     "dcnv2_backward_workspace_bytes": (c_size_t, [c_int] * 7),

@@ -185,7 +185,7 @@ dcn_forward_kernel(const DcnParams prm) {
     for (int s = 0; s < NS; ++s) { dcn_mbar_init(&bars.full[s], kPlain ? NP / NS + 1 : NP + 1); dcn_mbar_init(&bars.empty[s], 1); }
     for (int i = 0; i < 2; ++i) {
       dcn_mbar_init(&bars.geo_full[i], 4);  dcn_mbar_init(&bars.geo_empty[i], NP);
-      dcn_mbar_init(&bars.acc_full[i], 1);  dcn_mbar_init(&bars.acc_empty[i], 4);
+      dcn_mbar_init(&bars.acc_full[i], 1);  dcn_mbar_init(&bars.acc_empty[i], kPlain ? 8 : 4);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -208,9 +208,14 @@ dcn_forward_kernel(const DcnParams prm) {
     if (kPlain) dcn_plain_producer_loop<NP>(prm, smem, stage_bytes, NS, bars, warp, lane, tile_first, my_tiles, KB);
     else dcn_producer_loop<kFp32Blend, NP>(prm, smem, stage_bytes, NS, geo_w, geo_g, bars, warp, lane,
                                            tile_first, my_tiles, 0, KB);
-  } else if (warp < NP + 4) {
+  } else if (warp < NP + 4 || (kPlain && warp < NP + 8)) {
     // ===================================== epilogue ===============================================
-    const int quarter = warp - NP;                                        // == warp % 4: TMEM lane quarter
+    // (plain mode: the four geometry warps have no table to build and take the second half of the channels -- with
+    // N = 256 the stores of one warp per TMEM lane quarter were what the kernel waited for)
+    const int quarter = (warp - NP) & 3;                                  // == warp % 4: TMEM lane quarter
+    const int ehalf = (warp - NP) >> 2;
+    const int c_split = kPlain ? ((Cout / 16 + 1) / 2) * 16 : Cout;
+    const int c_begin = ehalf ? c_split : 0, c_end = ehalf ? Cout : c_split;
     const int r = (quarter << 5) + lane;                                  // tile row = TMEM lane
     const int relu = prm.relu;
     for (int j = 0; j < my_tiles; ++j) {
@@ -221,11 +226,12 @@ dcn_forward_kernel(const DcnParams prm) {
       const int tile_y = tile / prm.tiles_x, tile_x = tile - tile_y * prm.tiles_x;
       const int eho = tile_y * kTileH + (r >> 4), ewo = tile_x * kTileW + (r & 15);
       const bool evalid = eho < prm.Ho && ewo < prm.Wo;
-      float* yp = prm.y + (size_t)b * (prm.y_bstride ? (size_t)prm.y_bstride : (size_t)cout_store * P) + (evalid ? eho * prm.Wo + ewo : 0);
+      float* yp = prm.y + (size_t)b * (prm.y_bstride ? (size_t)prm.y_bstride : (size_t)cout_store * P) + (evalid ? eho * prm.Wo + ewo : 0) +
+                  (size_t)c_begin * P;
       dcn_mbar_wait_relaxed(&bars.acc_full[ab], (unsigned)((j >> 1) & 1));
       tc_fence_after();
       const uint32_t tbase = tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)ab * acc_stride;
-      for (int c0 = 0; c0 < Cout; c0 += 16) {
+      for (int c0 = c_begin; c0 < c_end; c0 += 16) {
         uint32_t v[16];
         tmem_ld16(tbase + (uint32_t)c0, v);
         float sc[16], sh[16];
@@ -532,18 +538,25 @@ extern "C" int dcnv2_forward_fused_offsets(const float* input, const float* weig
 // Output channels are produced in chunks of <= 128 (two TMEM accumulators of N columns and a 4-stage ring must fit).
 extern "C" size_t ctdet_conv3x3_workspace_bytes(int B, int Cin, int H, int W, int Cout) {
   if (B <= 0 || Cin <= 0 || H <= 0 || W <= 0 || Cout <= 0) return 0;
-  return dcn_align256((size_t)B * H * W * Cin * 2) + dcn_align256((size_t)128 * Cin * 9 * 2);
+  return dcn_align256((size_t)B * H * W * Cin * 2) + dcn_align256((size_t)256 * Cin * 9 * 2);
 }
 
-extern "C" int ctdet_conv3x3(const float* input, const float* weight, const float* bias, float* output,
-                             int B, int Cin, int H, int W, int Cout, int flags,
-                             void* workspace, size_t workspace_bytes, ctdet_stream_t stream) {
+// `n` convolutions of ONE input (the ctdet heads' first layers: hm, wh, reg): x is packed once.
+extern "C" int ctdet_conv3x3_multi(const float* input, int n, const float* const* weights, const float* const* biases,
+                                   float* const* outputs, const int* couts, int B, int Cin, int H, int W, int flags,
+                                   void* workspace, size_t workspace_bytes, ctdet_stream_t stream) {
   using namespace ctdet;
-  if (B < 0 || Cin <= 0 || H <= 0 || W <= 0 || Cout <= 0 || (flags & ~DCN_FLAG_RELU)) return CTDET_EINVAL;
+  if (B < 0 || Cin <= 0 || H <= 0 || W <= 0 || n <= 0 || (flags & ~DCN_FLAG_RELU)) return CTDET_EINVAL;
   if (Cin % kBK != 0) return CTDET_EUNSUPPORTED;
+  if (!input || !weights || !outputs || !couts || !workspace) return CTDET_ENULL;
+  int cmax = 0;
+  for (int i = 0; i < n; ++i) {
+    if (couts[i] <= 0) return CTDET_EINVAL;
+    if (!weights[i] || !outputs[i]) return CTDET_ENULL;
+    if (couts[i] > cmax) cmax = couts[i];
+  }
   if (B == 0) return CTDET_OK;
-  if (!input || !weight || !output || !workspace) return CTDET_ENULL;
-  if (workspace_bytes < ctdet_conv3x3_workspace_bytes(B, Cin, H, W, Cout)) return CTDET_EWORKSPACE;
+  if (workspace_bytes < ctdet_conv3x3_workspace_bytes(B, Cin, H, W, cmax)) return CTDET_EWORKSPACE;
   if (reinterpret_cast<uintptr_t>(workspace) & 15u) return CTDET_EALIGN;
   if ((size_t)H * W >= ((size_t)1 << 31) / (size_t)Cin || B > 65535) return CTDET_EINVAL;
   cudaStream_t st = (cudaStream_t)stream;
@@ -555,38 +568,51 @@ extern "C" int ctdet_conv3x3(const float* input, const float* weight, const floa
   dcn_pack_input_kernel<<<dim3((Pin + 63) / 64, (Cin + 63) / 64, B), 256, 0, st>>>(input, xh, Cin, Pin, vec, nullptr, 1, 0);
   int rc = check_launch();
   if (rc) return rc;
-  for (int c0 = 0; c0 < Cout; c0 += 128) {
-    const int n = Cout - c0 < 128 ? Cout - c0 : 128;
-    const int n_pad = (n + 15) / 16 * 16;
-    dcn_pack_weight_kernel<<<kNumSMs, 256, 0, st>>>(weight + (size_t)c0 * Cin * 9, wk, n_pad, Cin, n);
-    rc = check_launch();
-    if (rc) return rc;
-    DcnParams prm;
-    prm.xh = xh; prm.offset = output; prm.mask = output; prm.wk = wk; prm.bias = bias ? bias + c0 : nullptr;   // (offset / mask: not read)
-    prm.off_bstride = 0; prm.mask_bstride = 0; prm.mask_logit = 0; prm.om_bias = nullptr;
-    prm.scale = nullptr; prm.shift = nullptr; prm.y = output + (size_t)c0 * Pin;
-    prm.Cin = Cin; prm.H = H; prm.W = W; prm.Ho = H; prm.Wo = W; prm.Cout = n_pad;
-    prm.stride = 1; prm.pad = 1; prm.dil = 1; prm.relu = (flags & DCN_FLAG_RELU) ? 1 : 0;
-    prm.xw = W; prm.ximg = Pin * Cin; prm.xorg = 0;
-    prm.tiles_x = (W + kTileW - 1) / kTileW;
-    prm.tiles_per_image = prm.tiles_x * ((H + kTileH - 1) / kTileH);
-    const long long tiles = (long long)B * prm.tiles_per_image;
-    if (tiles > 0x7fffffffLL) return CTDET_EINVAL;
-    prm.num_tiles = (int)tiles;
-    uint32_t cols = 32;
-    while (cols < 2u * (uint32_t)n_pad) cols <<= 1;
-    prm.tmem_cols = cols;
-    prm.plain = 1; prm.cout_store = n; prm.y_bstride = (long long)Cout * Pin;
-    const size_t stage_bytes = (size_t)kTileM * kBK * 2 + (size_t)n_pad * kBK * 2;
-    prm.stages = 4;
-    prm.mma_sleep = 0; prm.ld_sleep = 0;
-    const size_t smem = (size_t)prm.stages * stage_bytes + 1024;   // (plain mode: no geometry table)
-    auto kern = dcn_forward_kernel<false, 16, true>;
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
-    kern<<<(unsigned)(tiles < kNumSMs ? tiles : kNumSMs), (16 + 10) * 32, smem, st>>>(prm);
-    rc = check_launch();
-    if (rc) return rc;
+  for (int i = 0; i < n; ++i) {
+    const int Cout = couts[i];
+    // output channels in chunks of <= 256: two TMEM accumulators of N columns (512 in all) and a 4-stage ring of
+    // 16 KB + N * 128 B stages (192 KB at N = 256; the plain mode has no geometry table)
+    for (int c0 = 0; c0 < Cout; c0 += 256) {
+      const int nc = Cout - c0 < 256 ? Cout - c0 : 256;
+      const int n_pad = (nc + 15) / 16 * 16;
+      dcn_pack_weight_kernel<<<kNumSMs, 256, 0, st>>>(weights[i] + (size_t)c0 * Cin * 9, wk, n_pad, Cin, nc);
+      rc = check_launch();
+      if (rc) return rc;
+      DcnParams prm;
+      prm.xh = xh; prm.offset = outputs[i]; prm.mask = outputs[i]; prm.wk = wk;            // (offset / mask: not read)
+      prm.bias = (biases && biases[i]) ? biases[i] + c0 : nullptr;
+      prm.off_bstride = 0; prm.mask_bstride = 0; prm.mask_logit = 0; prm.om_bias = nullptr;
+      prm.scale = nullptr; prm.shift = nullptr; prm.y = outputs[i] + (size_t)c0 * Pin;
+      prm.Cin = Cin; prm.H = H; prm.W = W; prm.Ho = H; prm.Wo = W; prm.Cout = n_pad;
+      prm.stride = 1; prm.pad = 1; prm.dil = 1; prm.relu = (flags & DCN_FLAG_RELU) ? 1 : 0;
+      prm.xw = W; prm.ximg = Pin * Cin; prm.xorg = 0;
+      prm.tiles_x = (W + kTileW - 1) / kTileW;
+      prm.tiles_per_image = prm.tiles_x * ((H + kTileH - 1) / kTileH);
+      const long long tiles = (long long)B * prm.tiles_per_image;
+      if (tiles > 0x7fffffffLL) return CTDET_EINVAL;
+      prm.num_tiles = (int)tiles;
+      uint32_t cols = 32;
+      while (cols < 2u * (uint32_t)n_pad) cols <<= 1;
+      prm.tmem_cols = cols;
+      prm.plain = 1; prm.cout_store = nc; prm.y_bstride = (long long)Cout * Pin;
+      const size_t stage_bytes = (size_t)kTileM * kBK * 2 + (size_t)n_pad * kBK * 2;
+      prm.stages = stage_bytes <= 24 * 1024 ? 8 : 4;
+      prm.mma_sleep = 0; prm.ld_sleep = 0;
+      const size_t smem = (size_t)prm.stages * stage_bytes + 1024;   // (plain mode: no geometry table)
+      auto kern = dcn_forward_kernel<false, 16, true>;
+      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
+      kern<<<(unsigned)(tiles < kNumSMs ? tiles : kNumSMs), (16 + 10) * 32, smem, st>>>(prm);
+      rc = check_launch();
+      if (rc) return rc;
+    }
   }
   return CTDET_OK;
+}
+
+extern "C" int ctdet_conv3x3(const float* input, const float* weight, const float* bias, float* output,
+                             int B, int Cin, int H, int W, int Cout, int flags,
+                             void* workspace, size_t workspace_bytes, ctdet_stream_t stream) {
+  if (Cout <= 0) return CTDET_EINVAL;
+  return ctdet_conv3x3_multi(input, 1, &weight, &bias, &output, &Cout, B, Cin, H, W, flags, workspace, workspace_bytes, stream);
 }

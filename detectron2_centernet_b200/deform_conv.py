@@ -206,6 +206,40 @@ def conv3x3(input, weight, bias=None, relu=False):
     return out
 
 
+def conv3x3_multi(input, weights, biases, relu=False):
+    """Several `conv3x3` of ONE input (C ABI ctdet_conv3x3_multi: the input is packed to NHWC bf16 once) -- the first layers
+    of the ctdet heads' branches.  weights: list of [Cout_i,Cin,3,3]; biases: list of [Cout_i] or None.  Returns a list."""
+    if not input.is_cuda:
+        raise NotImplementedError("conv3x3 runs on CUDA tensors only")
+    lib = _lib.load()
+    input = _lib.f32c(input, "input")
+    weights = [_lib.f32c(w, "weight") for w in weights]
+    biases = [None if b is None else _lib.f32c(b, "bias") for b in biases]
+    B, Cin, H, W = input.shape
+    n = len(weights)
+    for w in weights:
+        if w.dim() != 4 or tuple(w.shape[1:]) != (Cin, 3, 3) or Cin % 64 != 0:
+            raise NotImplementedError("conv3x3: weight [Cout,Cin,3,3] with Cin % 64 == 0")
+    outs = [torch.empty((B, w.shape[0], H, W), dtype=torch.float32, device=input.device) for w in weights]
+    if B == 0 or H * W == 0:
+        return outs
+    cmax = max(w.shape[0] for w in weights)
+    nbytes = lib.ctdet_conv3x3_workspace_bytes(B, Cin, H, W, cmax)
+    ws = _workspace(max(nbytes, 16), input.device)
+    vp = ctypes.c_void_p * n
+    wp = vp(*[w.data_ptr() for w in weights])
+    bp = vp(*[(b.data_ptr() if b is not None else None) for b in biases])
+    op = vp(*[o.data_ptr() for o in outs])
+    cp = (ctypes.c_int * n)(*[w.shape[0] for w in weights])
+    with torch.cuda.device(input.device):
+        rc = lib.ctdet_conv3x3_multi(_lib.ptr(input), n, ctypes.cast(wp, ctypes.c_void_p), ctypes.cast(bp, ctypes.c_void_p),
+                                     ctypes.cast(op, ctypes.c_void_p), ctypes.cast(cp, ctypes.c_void_p), B, Cin, H, W,
+                                     FLAG_RELU if relu else 0, _lib.ptr(ws), ctypes.c_size_t(ws.numel()),
+                                     _lib.stream_ptr(input.device))
+    _lib.check(rc, "ctdet_conv3x3_multi")
+    return outs
+
+
 def dcnv2_backward(input, offset, mask, weight, grad_output, stride=1, padding=0, dilation=1, groups=1,
                    deformable_groups=1, with_bias=True, need_input_grads=True, need_weight_grad=True):
     """Low-level call: returns (grad_input, grad_offset, grad_mask, grad_weight, grad_bias); entries that were

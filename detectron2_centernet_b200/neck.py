@@ -201,24 +201,35 @@ class CtdetHead(nn.Module):
 
     fuse_first_conv = True     # eval, no autograd: the 3x3 convolution + ReLU of every branch on the tensor cores (bf16 operands)
 
-    def _trunk(self, fc, x):
-        """Everything of a branch but its last layer: Conv3x3 + ReLU (centernet.py:112-121)."""
-        c = fc[0]
-        if (self.fuse_first_conv and not torch.is_grad_enabled() and x.is_cuda and isinstance(c, nn.Conv2d) and
+    def _fusable_trunk(self, fc, x):
+        c = fc[0] if isinstance(fc, nn.Sequential) else None
+        return (self.fuse_first_conv and not torch.is_grad_enabled() and x.is_cuda and isinstance(c, nn.Conv2d) and
                 c.kernel_size == (3, 3) and c.stride == (1, 1) and c.padding == (1, 1) and c.dilation == (1, 1) and
-                c.groups == 1 and c.in_channels % 64 == 0 and len(fc) == 3 and isinstance(fc[1], nn.ReLU)):
-            from .deform_conv import conv3x3
-            return conv3x3(x, c.weight, c.bias, relu=True)
-        return fc[:-1](x)
+                c.groups == 1 and c.in_channels % 64 == 0 and len(fc) == 3 and isinstance(fc[1], nn.ReLU))
 
-    def _branch(self, name, x):
+    def _trunks(self, x):
+        """Every branch but its last layer -- Conv3x3 + ReLU (centernet.py:112-121) -- for all branches: one
+        `conv3x3_multi` call (x packed once) where the branches allow it, the torch modules otherwise."""
+        names = [n.lower() for n in self.heads]
+        fcs = {n: getattr(self, n) for n in names}
+        fused = [n for n in names if self._fusable_trunk(fcs[n], x)]
+        out = {}
+        if fused:
+            from .deform_conv import conv3x3_multi
+            feats = conv3x3_multi(x, [fcs[n][0].weight for n in fused], [fcs[n][0].bias for n in fused], relu=True)
+            out.update(zip(fused, feats))
+        for n in names:
+            if n not in out:
+                out[n] = fcs[n][:-1](x) if isinstance(fcs[n], nn.Sequential) else x
+        return out
+
+    def _last(self, name, feat):
         fc = getattr(self, name.lower())
-        if isinstance(fc, nn.Sequential):
-            return fc[-1](self._trunk(fc, x))
-        return fc(x)
+        return fc[-1](feat) if isinstance(fc, nn.Sequential) else fc(feat)
 
     def forward(self, x):
-        return {name: self._branch(name, x) for name in self.heads}
+        feats = self._trunks(x)
+        return {name: self._last(name, feats[name.lower()]) for name in self.heads}
 
     def decode(self, x, down_ratio=4, K=100, fuse=True):
         """Eval path `ctdet_decode(hm.sigmoid_(), wh, reg, K)` (centernet.py:151-166) on the heads of `x` for a batch: with
@@ -227,10 +238,11 @@ class CtdetHead(nn.Module):
         Returns boxes, scores, classes, inds."""
         from . import decode as D
         hm = self.hm
-        wh, reg = self._branch("wh", x), (self._branch("reg", x) if "reg" in self.heads else None)
+        feats = self._trunks(x)
+        wh = self._last("wh", feats["wh"])
+        reg = self._last("reg", feats["reg"]) if "reg" in feats else None
         last = hm[-1] if isinstance(hm, nn.Sequential) else None
         if (fuse and last is not None and last.kernel_size == (1, 1) and
                 D.head_decode_fusable(last.in_channels, last.out_channels, x.shape[2], x.shape[3])):
-            feat = self._trunk(hm, x)
-            return D.hm_head_decode_batch(feat, last.weight, last.bias, wh, reg, down_ratio=down_ratio, K=K)
-        return D.ctdet_decode_batch(self._branch("hm", x), wh, reg, down_ratio=down_ratio, K=K, logits=True)
+            return D.hm_head_decode_batch(feats["hm"], last.weight, last.bias, wh, reg, down_ratio=down_ratio, K=K)
+        return D.ctdet_decode_batch(self._last("hm", feats["hm"]), wh, reg, down_ratio=down_ratio, K=K, logits=True)

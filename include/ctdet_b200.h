@@ -339,6 +339,12 @@ size_t ctdet_conv3x3_workspace_bytes(int B, int Cin, int H, int W, int Cout);
 int ctdet_conv3x3(const float* input, const float* weight, const float* bias, float* output,
                   int B, int Cin, int H, int W, int Cout, int flags,
                   void* workspace, size_t workspace_bytes, ctdet_stream_t stream);
+/* `n` such convolutions of ONE input (the heads' hm / wh / reg branches): the input is packed to NHWC bf16 once.
+ * weights / biases / outputs: host arrays of n device pointers (biases or its entries may be NULL), couts: host array of n
+ * channel counts; workspace: ctdet_conv3x3_workspace_bytes() with the largest Cout. */
+int ctdet_conv3x3_multi(const float* input, int n, const float* const* weights, const float* const* biases,
+                        float* const* outputs, const int* couts, int B, int Cin, int H, int W, int flags,
+                        void* workspace, size_t workspace_bytes, ctdet_stream_t stream);
 
 /* ---------------------------------------------------------------- DCNv2 backward ---------
  * Replaces modulated_deform_conv_backward (deform_conv.h:314-338; same argument meaning, minus the
