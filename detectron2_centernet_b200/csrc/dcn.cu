@@ -154,6 +154,9 @@ __global__ void dcn_pack_weight_kernel(const float* __restrict__ w, __nv_bfloat1
 //   warp  NP+8           one lane issues tcgen05.mma / tcgen05.commit
 //   warp  NP+9           one lane streams the pre-swizzled B (weight) tiles with 1-D bulk copies
 // TMEM holds two accumulator buffers, so the epilogue of tile i overlaps the MMAs of tile i+1.
+#ifdef CTDET_PLAIN_TIMING
+__device__ unsigned long long g_pl_ts[16];
+#endif
 template <bool kFp32Blend, int NP, bool kPlain = false>
 __global__ void __launch_bounds__((NP + 10) * 32, 1)
 dcn_forward_kernel(const DcnParams prm) {
@@ -262,16 +265,31 @@ dcn_forward_kernel(const DcnParams prm) {
     }
   } else if (warp == NP + 8) {
     // ===================================== MMA issuer =============================================
-    if (lane == 0) {
+    if (elect_one()) {
       const uint32_t idesc = make_idesc_bf16(kTileM, Cout);
       int s = 0; unsigned ph = 0;
+#ifdef CTDET_PLAIN_TIMING
+      long long t_acc = 0, t_full = 0, t_issue = 0, t_all0 = clock64(), nblk = 0;
+#endif
       for (int it = 0; it < my_tiles; ++it) {
         const int ab = it & 1;
+#ifdef CTDET_PLAIN_TIMING
+        long long c0 = clock64();
+#endif
         dcn_mbar_wait(&bars.acc_empty[ab], (unsigned)(((it >> 1) & 1) ^ 1));   // epilogue drained this buffer
+#ifdef CTDET_PLAIN_TIMING
+        t_acc += clock64() - c0;
+#endif
         tc_fence_after();
         const uint32_t d_tmem = tmem + (uint32_t)ab * acc_stride;
         for (int kb = 0; kb < KB; ++kb) {
+#ifdef CTDET_PLAIN_TIMING
+          long long c1 = clock64();
+#endif
           dcn_mbar_wait_relaxed(&bars.full[s], ph, (unsigned)prm.mma_sleep);
+#ifdef CTDET_PLAIN_TIMING
+          long long c2 = clock64(); t_full += c2 - c1; ++nblk;
+#endif
           tc_fence_after();
           const uint32_t a_addr = smem_u32(smem + (size_t)s * stage_bytes);
           const uint64_t adesc = make_sw128_desc(a_addr);
@@ -280,15 +298,24 @@ dcn_forward_kernel(const DcnParams prm) {
           for (int k4 = 0; k4 < kBK / 16; ++k4)      // +32 bytes (16 bf16) along K inside the swizzle row
             umma_bf16(d_tmem, adesc + 2 * k4, bdesc + 2 * k4, idesc, (uint32_t)((kb | k4) != 0));
           umma_commit(&bars.empty[s]);               // arrives when the MMAs above have read the stage
+#ifdef CTDET_PLAIN_TIMING
+          t_issue += clock64() - c2;
+#endif
           if (++s == NS) { s = 0; ph ^= 1u; }
         }
         umma_commit(&bars.acc_full[ab]);             // accumulator of tile it complete
       }
+#ifdef CTDET_PLAIN_TIMING
+      if (kPlain && blockIdx.x == 0) {
+        g_pl_ts[0] = (unsigned long long)t_acc; g_pl_ts[1] = (unsigned long long)t_full; g_pl_ts[2] = (unsigned long long)t_issue;
+        g_pl_ts[3] = (unsigned long long)(clock64() - t_all0); g_pl_ts[4] = (unsigned long long)nblk;
+      }
+#endif
     }
     __syncwarp();
   } else {
     // ===================================== B-tile loader ==========================================
-    if (lane == 0) {
+    if (elect_one()) {
       int s = 0; unsigned ph = 0;
       for (int it = 0; it < my_tiles; ++it) {
         for (int kb = 0; kb < KB; ++kb) {
@@ -616,3 +643,9 @@ extern "C" int ctdet_conv3x3(const float* input, const float* weight, const floa
   if (Cout <= 0) return CTDET_EINVAL;
   return ctdet_conv3x3_multi(input, 1, &weight, &bias, &output, &Cout, B, Cin, H, W, flags, workspace, workspace_bytes, stream);
 }
+
+#ifdef CTDET_PLAIN_TIMING
+extern "C" int ctdet_debug_plain_times(unsigned long long* out /* [16] host */) {
+  return cudaMemcpyFromSymbol(out, ctdet::g_pl_ts, 16 * sizeof(unsigned long long)) == cudaSuccess ? 0 : 5;
+}
+#endif

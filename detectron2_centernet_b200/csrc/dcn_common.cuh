@@ -36,6 +36,14 @@ __device__ __forceinline__ void tmem_alloc(uint32_t* slot, uint32_t ncols) {    
 __device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t ncols) {     // whole warp
   asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(addr), "r"(ncols) : "memory");
 }
+// One thread of a CONVERGED warp (elect.sync): unlike `lane == 0`, the compiler knows the region runs on exactly one thread
+// and emits the uniform-datapath instructions inside it (UTCHMMA, UTCBAR, UBLKCP) straight-line instead of wrapping each in
+// an ELECT / BRA.U.ANY loop -- ~85 -> ? cycles per tcgen05.mma issue, which is what bounds a kernel whose K blocks are cheap.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {

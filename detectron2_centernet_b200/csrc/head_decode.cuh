@@ -562,7 +562,7 @@ head_decode_kernel(const float* __restrict__ feat, const float* __restrict__ wei
     if (kMode == 3 && quarter == 0 && lane == 0 && s_thr[half] == 0u) hdrs[run_b].staged = 1u;
   } else {
     // ===================================== MMA issuer ==============================================
-    if (lane == 0) {
+    if (elect_one()) {
       const uint32_t idesc = make_idesc_bf16(kTileM, C);
       const uint32_t w_addr = smem_u32(wsm);
       int s = 0; unsigned ph = 0;

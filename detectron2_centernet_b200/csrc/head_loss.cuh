@@ -200,7 +200,7 @@ head_focal_fused_kernel(const float* __restrict__ feat, const float* __restrict_
     acc = (double)t0 + (double)t1 + (double)tot_pos;
   } else {
     // ===================================== MMA issuer ==============================================
-    if (lane == 0) {
+    if (elect_one()) {
       const uint32_t idesc = make_idesc_bf16(kTileM, C);
       const uint32_t w_addr = smem_u32(wsm);
       int s = 0; unsigned ph = 0;
@@ -497,7 +497,7 @@ head_focal_fused_bwd_kernel(const float* __restrict__ feat, const float* __restr
     }
   } else {
     // ===================================== MMA issuer ==============================================
-    if (lane == 0) {
+    if (elect_one()) {
       const uint32_t idesc1 = make_idesc_bf16(kTileM, C);                          // logits: A, B K-major
       const uint32_t idesc2 = make_idesc_bf16(kTileM, Cf) | (1u << 16);            // d_feat: B = W read MN-major
       const uint32_t idesc3 = make_idesc_bf16(kTileM, C) | (1u << 15) | (1u << 16);   // dW^T: A = feat^T, B = D, both MN-major
