@@ -330,8 +330,9 @@ __device__ __forceinline__ void dcn_producer_loop(const DcnParams& prm, uint8_t*
 // memory, 16-byte gathers into registers, swizzled stores): 950 cycles per K block whatever the warp layout, because the
 // SM's L1 / shared-memory data pipe was 62 % busy with it (ncu: per K block 174 wavefronts of table reads incl. 96 bank
 // conflicts, 127 of global loads, 168 of stores, + the tensor core's own operand reads).  This form has no table -- the
-// positions are integers, computed from the row index -- and no registers in the path: `cp.async.cg` moves 16 bytes from
-// global memory straight to their swizzled place in the stage (src-size 0 = zero fill outside the image), one pass over
+// positions are integers, computed from the row index -- and no registers in the path: `cp.async.ca` moves 16 bytes from
+// global memory (through L1: the nine taps of a tile read the same pixels) straight to their swizzled place in the stage
+// (src-size 0 = zero fill outside the image), one pass over
 // the data pipe instead of two.  The NP warps form NS groups; group s owns pipeline stage s and builds blocks s, s + NS, ...
 // (a stage has ONE group of writers: parity waits on its `empty` barrier only tell consecutive phases apart).
 template <int NP>
@@ -362,7 +363,7 @@ __device__ __forceinline__ void dcn_plain_producer_loop(const DcnParams& prm, ui
       const bool inside = hi >= 0 && hi < H && wi >= 0 && wi < W;
       const __nv_bfloat16* src = xb + (inside ? (size_t)(hi * prm.xw + wi) * Cin : 0);
       const uint32_t dst = a_addr + (uint32_t)r * 128u + ((uint32_t)(chunk ^ (r & 7)) << 4);
-      asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(dst), "l"(src), "r"(inside ? 16 : 0) : "memory");
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" :: "r"(dst), "l"(src), "r"(inside ? 16 : 0) : "memory");
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
     asm volatile("cp.async.wait_group 0;" ::: "memory");
