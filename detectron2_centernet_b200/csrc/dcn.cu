@@ -265,7 +265,7 @@ dcn_forward_kernel(const DcnParams prm) {
     }
   } else if (warp == NP + 8) {
     // ===================================== MMA issuer =============================================
-    if (elect_one()) {
+    if (kPlain ? elect_one() : lane == 0) {
       const uint32_t idesc = make_idesc_bf16(kTileM, Cout);
       int s = 0; unsigned ph = 0;
 #ifdef CTDET_PLAIN_TIMING
@@ -315,7 +315,7 @@ dcn_forward_kernel(const DcnParams prm) {
     __syncwarp();
   } else {
     // ===================================== B-tile loader ==========================================
-    if (elect_one()) {
+    if (kPlain ? elect_one() : lane == 0) {
       int s = 0; unsigned ph = 0;
       for (int it = 0; it < my_tiles; ++it) {
         for (int kb = 0; kb < KB; ++kb) {

@@ -165,7 +165,7 @@ dcn_wgrad_kernel(const DcnParams prm, const DcnBwdParams bw) {
     }
   } else if (warp == NP + 8) {
     // ============ MMA issuer: D[co, ci] += gout^T[co, p] * col[p, ci] ===============================
-    if (work && elect_one()) {
+    if (lane == 0 && work) {
       const uint32_t idesc = make_idesc_bf16(kTileM, kBK) | (1u << 15) | (1u << 16);   // A and B MN-major
       const uint32_t lbo = Cout >= 128 ? (uint32_t)kTileM * 128u : 0u;   // second 64-channel atom of the M tile
       int s = 0; unsigned ph = 0;
@@ -592,7 +592,7 @@ dcn_dgrad_kernel(const DcnParams prm, const DcnBwdParams bw) {
     }
   } else if (warp == NP + 8) {
     // ===================================== MMA issuer =============================================
-    if (elect_one()) {
+    if (lane == 0) {
       const uint32_t idesc = make_idesc_bf16(kTileM, kBK);
       int ws = 0; unsigned wph = 0;
       int n = 0;
@@ -624,7 +624,7 @@ dcn_dgrad_kernel(const DcnParams prm, const DcnBwdParams bw) {
     __syncwarp();
   } else {
     // ===================================== transposed-weight tile loader ==========================
-    if (elect_one()) {
+    if (lane == 0) {
       int ws = 0; unsigned wph = 0;
       for (int it = 0; it < my_tiles; ++it) {
         for (int kb = 0; kb < KB; ++kb) {

@@ -453,7 +453,7 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
     // One lane: G = gout[128 px, Cout] * Wt_kb[Cout, 64 ci] per K block, and the 1-D bulk copies of the
     // transposed weight tiles (the slot of K block n - 1 is refilled with K block n - 1 + NW right after GEMM 1
     // of K block n has been issued: its predecessor has normally retired by then).
-    if (elect_one()) {
+    if (lane == 0) {
       const uint32_t idesc1 = make_idesc_bf16(kTileM, kBK);                       // A, B K-major
       auto load_w = [&](int slot, int kblock) {
         dcn_mbar_arrive_expect_tx(&bars.wt_full[slot], wt_bytes);
@@ -498,7 +498,7 @@ dcn_dgrad2_kernel(const DcnParams prm, const DcnBwdParams bw) {
   } else {
     // ===================================== GEMM 2 issuer ===========================================
     // One lane: patch[mb] += S_chunk[128 q, 128 px] * G[128 px, 64 ci] for the three M blocks of every K block
-    if (elect_one()) {
+    if (lane == 0) {
       const uint32_t idesc2 = make_idesc_bf16(kTileM, kBK) | (1u << 16);          // B (= the G tile) MN-major
       int t2 = 0, grp2 = 0;
       int gs2 = 0; unsigned gph2 = 0;
