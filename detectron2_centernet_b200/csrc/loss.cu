@@ -378,6 +378,107 @@ loss_kernel(const float* __restrict__ hm, const float* __restrict__ wh, const fl
   loss_tail(acc0, acc1, is_reg, s_norm[1], w_wh, w_off, losses, ws, s_red, &s_last);
 }
 
+// ------------------------------------------------------------------------------------------------
+// The same launch with the sweep's reads STAGED BY THE TMA ENGINE: each sweep CTA walks its chunks
+// (kQ float4 per thread and tensor: 8 KB of logits + 8 KB of gt at kQ = 2) through a ring of `stages`
+// shared-memory stages filled by 1-D bulk async copies (cp.async.bulk, mbarrier complete_tx); thread 0
+// keeps stages - 1 chunks in flight (it refills the stage of chunk k - 1 on entering chunk k, when every
+// warp has long since read it).  The register-pipelined form above has 64 B per thread in flight and
+// waits on the long scoreboard; here ~48 KB per CTA are in flight without a register held, the
+// consumers read conflict-free LDS.128 and the loop carries no prefetch state.  RegL1 CTAs, cell
+// arithmetic, reduction and the last-CTA tail are the ones of loss_kernel: results are bit-identical
+// per cell; only the order of the per-CTA partial sums (fp64) differs.
+template <bool kProb, int kQ>
+__global__ void __launch_bounds__(kLossThreads, 3)
+loss_kernel_tma(const float* __restrict__ hm, const float* __restrict__ wh, const float* __restrict__ reg,
+                const float* __restrict__ gt, const uint8_t* __restrict__ reg_mask,
+                const int64_t* __restrict__ ind, const float* __restrict__ gt_wh,
+                const float* __restrict__ gt_reg, const float* __restrict__ alpha,
+                const int32_t* __restrict__ num_pos_img, const float* __restrict__ norm_override,
+                int B, int C, int HW, int M, int flags, int n_reg_ctas, int stages, FastDiv div_hw4, FastDiv div_c,
+                float w_hm, float w_wh, float w_off, float* __restrict__ losses, float* __restrict__ d_hm, float* __restrict__ d_wh,
+                float* __restrict__ d_reg, LossWs* ws) {
+  constexpr int kChunk4 = kLossThreads * kQ;             // float4 per chunk and tensor
+  constexpr int kMaxStages = 8;
+  extern __shared__ __align__(128) unsigned char s_ring[];    // [stages][2][kChunk4] float4
+  __shared__ __align__(8) uint64_t s_full[kMaxStages], s_empty[kMaxStages];
+  __shared__ float s_norm[2];
+  __shared__ double s_red[2][kLossThreads / 32];
+  __shared__ bool s_last;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const bool is_reg = (int)blockIdx.x < n_reg_ctas;
+
+  if (tid == 0) {
+    for (int s = 0; s < stages; ++s) { dcn_mbar_init(&s_full[s], 1); dcn_mbar_init(&s_empty[s], kLossThreads / 32); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  loss_norms(num_pos_img, norm_override, reg_mask, B, M, is_reg, ws, s_norm);     // (ends with a CTA barrier)
+
+  double acc0 = 0.0, acc1 = 0.0;
+  if (is_reg) {
+    acc0 = regl1_block(wh, reg, reg_mask, ind, gt_wh, gt_reg, d_wh, d_reg, HW, M, w_wh, w_off, s_norm[1]);
+  } else {
+    const float npos = s_norm[0];
+    const float gscale = -(npos == 0.f ? w_hm : w_hm / npos);  // :365-368
+    const uint32_t n4 = (uint32_t)((size_t)B * C * HW / 4);    // < 2^31 (checked on the host)
+    const uint32_t n_chunks = (n4 + kChunk4 - 1) / kChunk4;
+    const uint32_t first = blockIdx.x - n_reg_ctas, G = gridDim.x - n_reg_ctas;
+    const uint32_t my_n = first < n_chunks ? (n_chunks - first + G - 1) / G : 0u;
+    const bool uniform_alpha = flags & CTDET_LOSS_ALPHA_UNIFORM;
+    const float alpha0 = __ldg(alpha);
+    float4* ring = reinterpret_cast<float4*>(s_ring);
+    auto issue = [&](uint32_t k, int s) {                      // thread 0: chunk k of this CTA into stage s
+      const uint32_t j0 = (first + k * G) * (uint32_t)kChunk4;
+      const uint32_t bytes = min((uint32_t)kChunk4, n4 - j0) * 16u;
+      dcn_mbar_arrive_expect_tx(&s_full[s], 2u * bytes);
+      dcn_bulk_g2s(ring + (size_t)s * 2 * kChunk4, hm + 4 * (size_t)j0, bytes, &s_full[s]);
+      dcn_bulk_g2s(ring + (size_t)s * 2 * kChunk4 + kChunk4, gt + 4 * (size_t)j0, bytes, &s_full[s]);
+    };
+    if (tid == 0)
+      for (uint32_t k = 0; k + 1 < (uint32_t)stages && k < my_n; ++k) issue(k, (int)k);
+    int s = 0, s_prev = stages - 1;                            // stage of chunk k / of chunk k - 1
+    uint32_t par = 0u, par_prev = 1u;                          // their phase parities
+    for (uint32_t k = 0; k < my_n; ++k) {
+      if (tid == 0 && k + stages - 1 < my_n) {                 // refill the stage chunk k - 1 used
+        if (k >= 1) dcn_mbar_wait(&s_empty[s_prev], par_prev);
+        issue(k + stages - 1, s_prev);
+      }
+      dcn_mbar_wait(&s_full[s], par);
+      const float4* sx = ring + (size_t)s * 2 * kChunk4;
+      float4 x[kQ], g[kQ];
+#pragma unroll
+      for (int q = 0; q < kQ; ++q) { x[q] = sx[q * kLossThreads + tid]; g[q] = sx[kChunk4 + q * kLossThreads + tid]; }
+      __syncwarp();
+      if (lane == 0) dcn_mbar_arrive(&s_empty[s]);             // the values are in registers: the stage may be refilled
+      const uint32_t j0 = (first + k * G) * (uint32_t)kChunk4;
+      pk2 tot = bcast2(0.f);
+      float tot_pos = 0.f;
+#pragma unroll
+      for (int q = 0; q < kQ; ++q) {
+        const uint32_t j = j0 + q * kLossThreads + tid;
+        if (j < n4) {
+          float al = alpha0;
+          if (!uniform_alpha) {
+            const uint32_t plane = div_hw4.div(j);             // b*C + c
+            al = __ldg(alpha + (plane - div_c.div(plane) * (uint32_t)C));
+          }
+          float4 dd;
+          const pk2 d01 = cell2<kProb>(x[q].x, x[q].y, g[q].x, g[q].y, al, gscale, tot, tot_pos);
+          const pk2 d23 = cell2<kProb>(x[q].z, x[q].w, g[q].z, g[q].w, al, gscale, tot, tot_pos);
+          unpack2(d01, dd.x, dd.y); unpack2(d23, dd.z, dd.w);
+          if (d_hm != nullptr) stg_stream4(d_hm + 4 * (size_t)j, dd);
+        }
+      }
+      float t0, t1;
+      unpack2(tot, t0, t1);
+      acc0 += (double)(t0 + t1) + (double)tot_pos;             // already scaled by gscale = -w_hm/num_pos
+      s_prev = s; par_prev = par;
+      if (++s == stages) { s = 0; par ^= 1u; }
+    }
+  }
+  loss_tail(acc0, acc1, is_reg, s_norm[1], w_wh, w_off, losses, ws, s_red, &s_last);
+}
+
 // ================================================================================================
 // Fused target generation + losses: the Gaussian heatmap target is built
 // per 16 KB band in SHARED memory (same binning / fp64 radius / max-reduce splat as
@@ -614,6 +715,39 @@ extern "C" int ctdet_loss_fwd_bwd(const float* hm, const float* wh, const float*
   const bool v8 = use_v8 && hm && (HW % 8 == 0) && ((reinterpret_cast<uintptr_t>(hm) | reinterpret_cast<uintptr_t>(gt_hm) |
                                                        reinterpret_cast<uintptr_t>(d_hm)) & 31u) == 0;
   const bool prob = flags & CTDET_LOSS_INPUT_PROB;
+  // TMA-staged sweep (loss_kernel_tma): tuning knobs read once -- CTDET_LOSS_TMA=0 keeps the register-pipelined
+  // kernel, CTDET_LOSS_TMA_Q = float4 per thread and chunk (1 / 2 / 4), CTDET_LOSS_TMA_STAGES = ring depth (2..8)
+  static int tma_on = -1, tma_q = 2, tma_stages = 4;
+  if (tma_on < 0) {
+    const char* e = getenv("CTDET_LOSS_TMA_Q");
+    if (e) { const int q = atoi(e); if (q == 1 || q == 2 || q == 4) tma_q = q; }
+    e = getenv("CTDET_LOSS_TMA_STAGES");
+    if (e) { const int s = atoi(e); if (s >= 2 && s <= 8) tma_stages = s; }
+    e = getenv("CTDET_LOSS_TMA");
+    tma_on = e ? (atoi(e) != 0) : 0;            // measured slower than the register-pipelined sweep: opt-in
+  }
+  if (tma_on && hm) {
+    auto tk = prob ? (tma_q == 1 ? loss_kernel_tma<true, 1> : tma_q == 2 ? loss_kernel_tma<true, 2> : loss_kernel_tma<true, 4>)
+                   : (tma_q == 1 ? loss_kernel_tma<false, 1> : tma_q == 2 ? loss_kernel_tma<false, 2> : loss_kernel_tma<false, 4>);
+    const size_t chunk4 = (size_t)kLossThreads * tma_q;
+    const size_t smem = (size_t)tma_stages * 2 * chunk4 * 16;
+    static int tma_occ[2] = {0, 0};
+    cudaError_t e = cudaFuncSetAttribute(tk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
+    if (tma_occ[prob] == 0) {
+      int o = 0;
+      if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, tk, kLossThreads, smem) != cudaSuccess || o < 1) o = 1;
+      tma_occ[prob] = o;
+    }
+    const size_t n_chunks = (n4 + chunk4 - 1) / chunk4;
+    const size_t tcap = (size_t)kNumSMs * tma_occ[prob];
+    const int tsweep = (int)(n_chunks < tcap ? n_chunks : tcap);
+    tk<<<n_reg + tsweep, kLossThreads, smem, st>>>(
+        hm, wh, reg, gt_hm, reg_mask, ind, gt_wh, gt_reg, alpha, num_pos_img, norm_override,
+        B, C, (int)HW, M, flags, n_reg, tma_stages, FastDiv((uint32_t)(HW / 4)), FastDiv((uint32_t)C), w_hm, w_wh, w_off,
+        losses, d_hm, d_wh, d_reg, ws);
+    return check_launch();
+  }
   auto kern = prob ? (v8 ? loss_kernel<true, true> : loss_kernel<true, false>)
                    : (v8 ? loss_kernel<false, true> : loss_kernel<false, false>);
   kern<<<n_reg + sweep, kLossThreads, 0, st>>>(
