@@ -331,21 +331,27 @@ loss_kernel(const float* __restrict__ hm, const float* __restrict__ wh, const fl
     // kV8 (HW % 8 == 0, 32-byte aligned tensors): a thread's two float4 chunks are adjacent and move
     // as ONE 256-bit load / store per tensor; otherwise they lie `stride` apart (128-bit accesses)
     static_assert(!kV8 || kUnroll == 2, "the 256-bit path pairs two float4 chunks");
-    auto chunk = [&](size_t base, int u) { return kV8 ? 2 * base + u : base + u * stride; };
+    // The sweep walks the tensors from their END towards their start: what the producers of `hm` (the head's last
+    // convolution) and `gt` (target-gen, or the reference's cat + H2D copy at centernet.py:197-201) wrote last is what
+    // the L2 still holds when this kernel starts -- a forward sweep would evict exactly those lines before reaching
+    // them (LRU against a sequential writer).  Cold inputs cost the same either way.
+    // Every stream of the sweep is read-once / write-once: L2 evict-first, so the incoming lines do not push the
+    // producers' lines out before the sweep reaches them.
+    const uint64_t pol = l2_policy_evict_first();
+    const size_t step = kV8 ? stride : stride * kUnroll;     // advance of `i` per iteration
+    const size_t n_it = kV8 ? n4 / 2 : n4;                   // range of `i`
     auto load = [&](size_t base, float4* xs, float4* gs) {
       if (kV8) {
-        if (2 * base < n4) { ldg_stream8(hm + 8 * base, xs[0], xs[1]); ldg_stream8(gt + 8 * base, gs[0], gs[1]); }
+        if (base < n_it) { const size_t p = n_it - 1 - base; ldg_stream8(hm + 8 * p, xs[0], xs[1], pol); ldg_stream8(gt + 8 * p, gs[0], gs[1], pol); }
       } else {
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) {
           const size_t j = base + u * stride;
-          if (j < n4) { xs[u] = ldg_stream4(hm + 4 * j); gs[u] = ldg_stream4(gt + 4 * j); }
+          if (j < n4) { const size_t p = n4 - 1 - j; xs[u] = ldg_stream4(hm + 4 * p, pol); gs[u] = ldg_stream4(gt + 4 * p, pol); }
         }
       }
     };
     float4 x[kUnroll], g[kUnroll], xn[kUnroll], gn[kUnroll], dd[kUnroll];
-    const size_t step = kV8 ? stride : stride * kUnroll;     // advance of `i` per iteration
-    const size_t n_it = kV8 ? n4 / 2 : n4;                   // range of `i`
     load(i, x, g);
     for (; i < n_it; i += step) {
       load(i + step, xn, gn);
@@ -353,8 +359,9 @@ loss_kernel(const float* __restrict__ hm, const float* __restrict__ wh, const fl
       float tot_pos = 0.f;
 #pragma unroll
       for (int u = 0; u < kUnroll; ++u) {
-        const size_t j = chunk(i, u);
-        if (j < n4) {
+        // float4 index of this chunk (kV8: the two halves of the 256-bit access at n_it - 1 - i)
+        const size_t j = kV8 ? 2 * (n_it - 1 - i) + u : n4 - 1 - (i + u * stride);
+        if (kV8 || i + u * stride < n4) {
           float al = alpha0;
           if (!uniform_alpha) {
             const uint32_t plane = div_hw4.div((uint32_t)j);         // b*C + c
@@ -363,10 +370,10 @@ loss_kernel(const float* __restrict__ hm, const float* __restrict__ wh, const fl
           const pk2 d01 = cell2<kProb>(x[u].x, x[u].y, g[u].x, g[u].y, al, gscale, tot, tot_pos);
           const pk2 d23 = cell2<kProb>(x[u].z, x[u].w, g[u].z, g[u].w, al, gscale, tot, tot_pos);
           unpack2(d01, dd[u].x, dd[u].y); unpack2(d23, dd[u].z, dd[u].w);
-          if (!kV8 && d_hm != nullptr) stg_stream4(d_hm + 4 * j, dd[u]);
+          if (!kV8 && d_hm != nullptr) stg_stream4(d_hm + 4 * j, dd[u], pol);
         }
       }
-      if (kV8 && d_hm != nullptr) stg_stream8(d_hm + 8 * i, dd[0], dd[1]);
+      if (kV8 && d_hm != nullptr) stg_stream8(d_hm + 8 * (n_it - 1 - i), dd[0], dd[1], pol);
       float t0, t1;
       unpack2(tot, t0, t1);
       acc0 += (double)(t0 + t1) + (double)tot_pos;   // already scaled by gscale = -w_hm/num_pos
