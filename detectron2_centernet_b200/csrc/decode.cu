@@ -711,7 +711,13 @@ decode_seed_kernel(const float* __restrict__ heat, int C, int H, int W, int K, i
 // A segment overflow (ties / plateaus at the bound) hands the image to the staged path, exact for any input.
 constexpr int kStrThreads = 128;
 constexpr int kStrWarps = kStrThreads / 32;
-constexpr int kTileCap = 64;                     // keys per tile on this path (~20 at K = 100)
+constexpr int kTileCap = 64;                     // keys per tile segment of the fused head decode (head_decode.cuh)
+#ifndef CTDET_DECODE_SW_TILE_CAP
+#define CTDET_DECODE_SW_TILE_CAP 16
+#endif
+constexpr int kSwTileCap = CTDET_DECODE_SW_TILE_CAP;   // keys per tile segment of decode_stream_kernel: ~5 used at K = 100, the rest spills.
+// 64 -> 16 (measured 64 / 32 / 16): the tail CTA of an image reads every segment, zeros included -- 327 KB per 512^2 image
+// at 64, 1.3 MB per 1024^2 image; B = 32: 53.3 -> 51.2 us, 1024^2 B = 8: 63.5 -> 55.4 us, class-concentrated scores unchanged
 constexpr int kSpillCap = 8192;                  // keys per image beyond their tiles' segments (class- / object-concentrated scores)
 
 template <bool kOneStrip>                        // W <= 128: a row is one warp-wide float4 load
@@ -839,13 +845,13 @@ decode_stream_kernel(const float* __restrict__ heat, int C, int H, int W, int ba
 #pragma unroll
   for (int w = 0; w < kStrWarps; ++w) { const int t = s_wtot[w]; if (w < warp) base += t; total += t; }
   u64* spill = nullptr;
-  if (total > kTileCap) {
+  if (total > kSwTileCap) {
     // More keys than the tile's segment holds (scores concentrated in a few classes or around a few objects; ties and
-    // plateaus at the bound): the first kTileCap keys go to the segment, the others to the image's spill list -- ONE
+    // plateaus at the bound): the first kSwTileCap keys go to the segment, the others to the image's spill list -- ONE
     // returning atomic per overflowing tile.  Only when that list is full too is the image handed to the staged path.
-    if (tid == 0) s_spill = atomicAdd(&hdr->s_count, (unsigned int)(total - kTileCap));
+    if (tid == 0) s_spill = atomicAdd(&hdr->s_count, (unsigned int)(total - kSwTileCap));
     __syncthreads();                                          // (CTA-uniform branch)
-    if (s_spill + (unsigned int)(total - kTileCap) > (unsigned int)spill_cap) {
+    if (s_spill + (unsigned int)(total - kSwTileCap) > (unsigned int)spill_cap) {
       if (tid == 0) hdr->staged = 1u;
       pdl_launch_dependents();
       return;
@@ -855,9 +861,9 @@ decode_stream_kernel(const float* __restrict__ heat, int C, int H, int W, int ba
   pdl_launch_dependents();
   // the segment is always written in full -- keys, then zeros -- so the tail reads it as one dense, coalesced vector
   // without knowing the counts (no count array, no dependent second trip)
-  for (int i = total + tid; i < kTileCap; i += kStrThreads) skeys_all[tile_id * kTileCap + i] = 0ull;
+  for (int i = total + tid; i < kSwTileCap; i += kStrThreads) skeys_all[tile_id * kSwTileCap + i] = 0ull;
   int pos = base + (incl - mine_n);                           // this lane's first slot in CTA order
-  u64* seg = skeys_all + tile_id * kTileCap;
+  u64* seg = skeys_all + tile_id * kSwTileCap;
   while (hits) {
     const int bit = __ffsll((long long)hits) - 1;
     hits &= hits - 1ull;
@@ -867,7 +873,7 @@ decode_stream_kernel(const float* __restrict__ heat, int C, int H, int W, int ba
     const float v = tile[(size_t)(t + 1) * W + x];
     const uint32_t flat = (uint32_t)((c * H + (y_lo + t)) * W + x);
     const u64 key = ((u64)float_to_ordered(v) << 32) | (u64)(0xffffffffu - flat);
-    if (pos < kTileCap) seg[pos] = key; else spill[pos - kTileCap] = key;
+    if (pos < kSwTileCap) seg[pos] = key; else spill[pos - kSwTileCap] = key;
     ++pos;
   }
 }
@@ -1091,7 +1097,7 @@ __global__ void __launch_bounds__(kFinThreads, 1)
 decode_tail_kernel(const float* __restrict__ heat, int B, int mode, int helpers,
                    DecodeHeader* __restrict__ hdrs, unsigned int* __restrict__ ghists,
                    u64* __restrict__ keys, size_t keys_per_image,
-                   const u64* __restrict__ skeys, int sw_tiles, int spill_cap,
+                   const u64* __restrict__ skeys, int sw_tiles, int tile_cap, int spill_cap,
                    unsigned int* __restrict__ phists,
                    int Wp, int band_rows, int sub_rows, FastDiv div_strips, int bands,
                    const float* __restrict__ wh, const float* __restrict__ reg, int C, int H,
@@ -1110,8 +1116,8 @@ decode_tail_kernel(const float* __restrict__ heat, int B, int mode, int helpers,
   // The image's key segments (every tile's segment is fully written: keys, then zeros) are ONE dense vector: the first
   // batch of 16-byte loads is requested together with the header -- independent loads, one L2 trip.
   constexpr int kBatch = 20;                                 // uint4 (2 keys) per thread and batch: 160 KB per CTA and trip
-  const int n_vec = (mode == 0 && helper == 0) ? sw_tiles * (kTileCap / 2) : 0;
-  const uint4* segv = reinterpret_cast<const uint4*>(skeys + (mode == 0 ? (size_t)b * sw_tiles * kTileCap : 0));
+  const int n_vec = (mode == 0 && helper == 0) ? sw_tiles * (tile_cap / 2) : 0;
+  const uint4* segv = reinterpret_cast<const uint4*>(skeys + (mode == 0 ? (size_t)b * sw_tiles * tile_cap : 0));
   uint4 kq[kBatch];
 #pragma unroll
   for (int u = 0; u < kBatch; ++u) {
@@ -1197,10 +1203,10 @@ decode_tail_kernel(const float* __restrict__ heat, int B, int mode, int helpers,
     TAIL_TS(3);
     const int n_keys = fs.above;                             // the slot counter = number of keys
     const bool fits = n_keys <= kTailSmemKeys;               // CTA-uniform
-    const u64* segs = skeys + (size_t)b * sw_tiles * kTileCap;
+    const u64* segs = skeys + (size_t)b * sw_tiles * tile_cap;
     // (only when the list does not fit shared memory: f(key) for every key, straight from the segments and the spill list)
     auto scan_tiles = [&](auto f) {
-      for (int i = tid; i < sw_tiles * kTileCap; i += kFinThreads) { const u64 key = __ldcg(segs + i); if (key) f(key, 0); }
+      for (int i = tid; i < sw_tiles * tile_cap; i += kFinThreads) { const u64 key = __ldcg(segs + i); if (key) f(key, 0); }
       for (int i = tid; i < n_spill; i += kFinThreads) f(__ldcg(spill + i), 0);
     };
     __syncthreads();
@@ -1318,7 +1324,7 @@ static DecodePlan make_plan(int B, int C, int H, int W, int K) {
     p.sw_rows = sr;
     p.sw_bands = (H + sr - 1) / sr;
     p.sw_smem = (size_t)(sr + 2) * W * sizeof(float);
-    if ((long long)C * p.sw_bands * kTileCap >= (1ll << 28)) p.stream = false;
+    if ((long long)C * p.sw_bands * kSwTileCap >= (1ll << 28)) p.stream = false;
   }
   {
     int tsubs = (kFinThreads / 32) / strips; if (tsubs < 1) tsubs = 1;
@@ -1333,7 +1339,7 @@ static DecodePlan make_plan(int B, int C, int H, int W, int K) {
     if (p.seed_ctas < 1) p.seed_ctas = 1;
   }
   p.scnt_bytes = 0;                                             // (tile counts of an earlier layout)
-  p.skeys_bytes = p.stream ? (size_t)B * C * p.sw_bands * kTileCap * sizeof(u64) : 0;
+  p.skeys_bytes = p.stream ? (size_t)B * C * p.sw_bands * kSwTileCap * sizeof(u64) : 0;
   // sample histograms (zero on entry, left zero: a fixed stride per image, whatever the map shape, because calls
   // of different shapes share one workspace), then the samples themselves (rewritten by every call)
   p.phist_bytes = (((size_t)B * kSeedHist * sizeof(unsigned int)) + 255) / 256 * 256;
@@ -1410,7 +1416,7 @@ extern "C" int ctdet_decode(const float* heat, const float* wh, const float* reg
     if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }
     if ((rc = check_launch())) return rc;
     e = launch_pdl(decode_tail_kernel, dim3(B * kTailHelpers), dim3(kFinThreads), p.tail_smem, st,
-                   heat, B, 0, kTailHelpers, hdr, ghist, keys, p.keys_per_image, (const u64*)skeys, C * p.sw_bands,
+                   heat, B, 0, kTailHelpers, hdr, ghist, keys, p.keys_per_image, (const u64*)skeys, C * p.sw_bands, kSwTileCap,
                    (int)std::min<size_t>(kSpillCap, p.keys_per_image), phist,
                    p.Wp, p.band_rows, p.tail_sub_rows, div_strips, p.bands,
                    wh, reg, C, H, W, K, down_ratio, flags, boxes, scores, classes, inds);
@@ -1422,7 +1428,7 @@ extern "C" int ctdet_decode(const float* heat, const float* wh, const float* reg
   if ((rc = check_launch())) return rc;
   {
     cudaError_t e = launch_pdl(decode_tail_kernel, dim3(B), dim3(kFinThreads), p.tail_smem, st,
-                               heat, B, 1, 1, hdr, ghist, keys, p.keys_per_image, (const u64*)nullptr, 0, 0, (unsigned int*)nullptr,
+                               heat, B, 1, 1, hdr, ghist, keys, p.keys_per_image, (const u64*)nullptr, 0, kSwTileCap, 0, (unsigned int*)nullptr,
                                p.Wp, p.band_rows, p.tail_sub_rows, div_strips, p.bands,
                                wh, reg, C, H, W, K, down_ratio, flags, boxes, scores, classes, inds);
     if (e != cudaSuccess) { set_last_cuda_error(e); return CTDET_ECUDA; }

@@ -699,7 +699,7 @@ extern "C" int ctdet_head_decode_fused(const float* feat, const float* weight, c
   if ((rc = check_launch())) return rc;
   const FastDiv div_strips((uint32_t)p.dec.strips);
   decode_tail_kernel<<<dim3(B * kTailHelpers), dim3(kFinThreads), p.tail_smem, st>>>(
-      logits, B, 0, kTailHelpers, hdr, ghist, keys, p.dec.keys_per_image, (const u64*)skeys, 2 * H, spill_cap, phist,
+      logits, B, 0, kTailHelpers, hdr, ghist, keys, p.dec.keys_per_image, (const u64*)skeys, 2 * H, kTileCap, spill_cap, phist,
       p.dec.Wp, p.dec.band_rows, p.dec.tail_sub_rows, div_strips, p.dec.bands,
       wh, reg, C, H, W, K, down_ratio, flags | CTDET_DECODE_LOGITS, boxes, scores, classes, inds);
   return check_launch();
