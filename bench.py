@@ -131,8 +131,9 @@ class L2Flush:
         torch.sum(self.r)
 
 
-def graph_timed_us(call, flush, reps=20):
-    """One call replayed from a CUDA graph, L2 flushed before every timed replay, CUDA events; -> microseconds."""
+def graph_timed_us(call, flush, reps=20, both=False):
+    """One call replayed from a CUDA graph, L2 flushed before every timed replay, CUDA events; -> microseconds
+    (both=True: also with the memset-only flush of the earlier records, as a second value)."""
     for _ in range(3):
         call()
     torch.cuda.synchronize()
@@ -146,16 +147,20 @@ def graph_timed_us(call, flush, reps=20):
     torch.cuda.synchronize()
     for _ in range(3):
         graph.replay()
-    tot = 0.0
-    for _ in range(reps):
-        flush.zero_()
-        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        s.record()
-        graph.replay()
-        e.record()
-        torch.cuda.synchronize()
-        tot += s.elapsed_time(e)
-    return tot / reps * 1e3
+
+    def run(fl):
+        tot = 0.0
+        for _ in range(reps):
+            fl()
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record()
+            graph.replay()
+            e.record()
+            torch.cuda.synchronize()
+            tot += s.elapsed_time(e)
+        return tot / reps * 1e3
+    us = run(flush.zero_)
+    return (us, run(flush.write_only)) if both else us
 
 
 def configs_3_4(dev, flush, peak):
@@ -692,11 +697,9 @@ def run_ours(args):
                      ("decode", lambda: D.ctdet_decode_batch(d_hm, d_wh, d_reg, down_ratio=4, K=K, logits=True)),
                      ("fused_target_loss", lambda: L._FusedTargetLoss.apply(d_hm, d_wh, d_reg, d_boxes, d_classes, d_offsets,
                                                                              alpha, None, 2, weights, slots))):
-        ms = timed(fn, max(args.steps, 10), 3, True) / max(args.steps, 10)
-        per_kernel[name] = {"us": round(ms * 1e3, 2),
-                            "GBps": round(cells * BYTES_PER_CELL[name] / (ms * 1e-3) / 1e9, 1)}
-        ms_w = timed(fn, max(args.steps, 10), 3, "write") / max(args.steps, 10)
-        per_kernel[name]["us_memset_flush_only"] = round(ms_w * 1e3, 2)
+        us, us_w = graph_timed_us(fn, flush, reps=max(args.steps, 10), both=True)     # (the decode is 3 launches)
+        per_kernel[name] = {"us": round(us, 2), "GBps": round(cells * BYTES_PER_CELL[name] / (us * 1e-6) / 1e9, 1),
+                            "us_memset_flush_only": round(us_w, 2)}
     e2e_ms = timed(step_e2e, args.steps, args.warmup, False)
 
     # host -> device copy rate of this rank alone (the e2e step moves 176 MB per step through it), all ranks at once

@@ -792,3 +792,20 @@ def test_config2_full_size_against_the_oracle():
     assert np.array_equal(det[2].cpu().numpy(), rc) and np.array_equal(det[3].cpu().numpy(), ri)
     assert np.array_equal(det[0].cpu().numpy(), rb)
     np.testing.assert_allclose(det[1].cpu().numpy(), rs, rtol=2e-7)
+
+
+def test_tma_staged_loss_sweep_in_a_fresh_process():
+    """`CTDET_LOSS_TMA=1` (read once per process) selects loss_kernel_tma -- the sweep's reads staged by bulk async copies
+    into a shared-memory ring (opt-in: measured slower than the register-pipelined sweep) -- with a
+    2-stage ring of 4 float4 per thread, so chunks end inside planes and the last chunk is partial: the same loss parity
+    tests in a child process."""
+    import os
+    import subprocess
+    import sys
+    if os.environ.get("CTDET_LOSS_TMA"):
+        pytest.skip("already the child")
+    env = dict(os.environ, CTDET_LOSS_TMA="1", CTDET_LOSS_TMA_Q="4", CTDET_LOSS_TMA_STAGES="2")
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-x", "-q", "-m", "gpu", "-k",
+                        "test_fused_losses or edge_shapes or no_positives or dropins"], env=env, capture_output=True,
+                       text=True, timeout=300, cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
