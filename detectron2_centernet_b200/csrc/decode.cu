@@ -57,6 +57,20 @@ typedef unsigned long long u64;
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
+// Whole-decode timeline (only with -DCTDET_DECODE_TIMING; scripts/decode_timeline.py): first / last %globaltimer stamp per
+// event over all CTAs -- 0/1 seed first start / last end, 2/3 first / last bound published, 4/5 sweep first start / last
+// start, 6 first sweep CTA past its bound, 7 sweep last end, 8 tail first start, 9/10 first / last tail CTA past
+// griddepcontrol.wait, 11 tail last end.
+#ifdef CTDET_DECODE_TIMING
+__device__ unsigned long long g_dec_ts[16];
+__device__ __forceinline__ unsigned long long gt_ns() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+#define DEC_TS_MIN(i) do { if (threadIdx.x == 0) atomicMin(&g_dec_ts[i], gt_ns()); } while (0)
+#define DEC_TS_MAX(i) do { if (threadIdx.x == 0) atomicMax(&g_dec_ts[i], gt_ns()); } while (0)
+#else
+#define DEC_TS_MIN(i) do {} while (0)
+#define DEC_TS_MAX(i) do {} while (0)
+#endif
+
 template <typename... KArgs, typename... Args>
 static cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
   cudaLaunchConfig_t cfg = {};
@@ -593,13 +607,20 @@ __device__ unsigned int seed_bound_of_image(const unsigned int* ph, const unsign
     return ord;
 }
 
-__global__ void __launch_bounds__(kSeedThreads)
+#ifndef CTDET_SEED_MINB
+#define CTDET_SEED_MINB 1
+#endif
+#ifndef CTDET_SEED_ITEMS_PER_WARP
+#define CTDET_SEED_ITEMS_PER_WARP 1
+#endif
+__global__ void __launch_bounds__(kSeedThreads, CTDET_SEED_MINB)
 decode_seed_kernel(const float* __restrict__ heat, int C, int H, int W, int K, int flags,
                    int groups, FastDiv div_strips, FastDiv div_groups, DecodeHeader* __restrict__ hdrs,
                    unsigned int* __restrict__ phists, unsigned int* __restrict__ pvals_all, int n_vals) {
   __shared__ unsigned int s_sub[32];
   __shared__ unsigned int s_last;
   pdl_launch_dependents();             // the sweep may be scheduled as soon as every CTA of this grid runs
+  DEC_TS_MIN(0);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int b = blockIdx.y;
   const int strips = (int)div_strips.d;
@@ -679,12 +700,14 @@ decode_seed_kernel(const float* __restrict__ heat, int C, int H, int W, int K, i
     __threadfence();
   }
   __syncthreads();
+  DEC_TS_MAX(1);
   if (!s_last || warp != 0) return;
   const unsigned int ord = seed_bound_of_image(phist, pvals, n_vals, K, s_sub);
   if (lane == 0) {
     if (ord == 0u) *((volatile unsigned int*)&hdr->staged) = 1u;      // no usable sample bound: the staged path owns the image
     else *((volatile unsigned int*)&hdr->thr_ord) = ord;              // (also the head start of the staged path after an overflow)
   }
+  DEC_TS_MIN(2); DEC_TS_MAX(3); DEC_TS_MAX(1);
 }
 
 // decode_stream_kernel: the sweep proper -- a lean TMA-staged threshold sweep.  One CTA (4 warps) per tile = a
@@ -734,6 +757,7 @@ decode_stream_kernel(const float* __restrict__ heat, int C, int H, int W, int ba
   __shared__ unsigned int s_thr, s_skip;
   float* tile = reinterpret_cast<float*>(s_raw);              // [(band_rows + 2)][W]; tile row t <-> map row y_lo - 1 + t
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  DEC_TS_MIN(4); DEC_TS_MAX(5);
   const int b = blockIdx.y;
   const int c = (int)div_bands.div(blockIdx.x), band = (int)blockIdx.x - c * bands;
   const int y_lo = band * band_rows, y_hi = min(H, y_lo + band_rows);
@@ -771,6 +795,7 @@ decode_stream_kernel(const float* __restrict__ heat, int C, int H, int W, int ba
     s_skip = (ord == 0u || st_ != 0u) ? 1u : 0u;
   }
   __syncthreads();                                            // bound, barrier init, padding rows
+  DEC_TS_MIN(6);
   const size_t tile_id = (size_t)b * gridDim.x + blockIdx.x;
   const unsigned int thr_ord = s_thr;
   if (s_skip) {                                               // CTA-uniform (the tail ignores this image's segments)
@@ -876,6 +901,7 @@ decode_stream_kernel(const float* __restrict__ heat, int C, int H, int W, int ba
     if (pos < kSwTileCap) seg[pos] = key; else spill[pos - kSwTileCap] = key;
     ++pos;
   }
+  DEC_TS_MAX(7);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1111,8 +1137,10 @@ decode_tail_kernel(const float* __restrict__ heat, int B, int mode, int helpers,
   const int helper = blockIdx.x < B ? 0 : 1 + (blockIdx.x - B) / B;
   DecodeHeader* hdr = hdrs + b;
   TAIL_TS(0);
+  DEC_TS_MIN(8);
   pdl_wait();
   TAIL_TS(1);
+  DEC_TS_MIN(9); DEC_TS_MAX(10);
   // The image's key segments (every tile's segment is fully written: keys, then zeros) are ONE dense vector: the first
   // batch of 16-byte loads is requested together with the header -- independent loads, one L2 trip.
   constexpr int kBatch = 20;                                 // uint4 (2 keys) per thread and batch: 160 KB per CTA and trip
@@ -1270,6 +1298,7 @@ decode_tail_kernel(const float* __restrict__ heat, int B, int mode, int helpers,
   finalize_emit(&fs, b, wh, reg, C, H, W, K, down_ratio, flags, boxes, scores, classes, inds);
   __syncthreads();
   TAIL_TS(6);
+  DEC_TS_MAX(11);
 }
 
 struct DecodePlan {
@@ -1334,7 +1363,7 @@ static DecodePlan make_plan(int B, int C, int H, int W, int K) {
   }
   {
     const int items = C * p.seed_groups * strips;               // one warp-item = 6 row segments of 512 B
-    p.seed_ctas = (items + kSeedWarps - 1) / kSeedWarps;
+    p.seed_ctas = (items + kSeedWarps * CTDET_SEED_ITEMS_PER_WARP - 1) / (kSeedWarps * CTDET_SEED_ITEMS_PER_WARP);
     p.seed_vals = items * kSeedRows;
     if (p.seed_ctas < 1) p.seed_ctas = 1;
   }
@@ -1437,6 +1466,14 @@ extern "C" int ctdet_decode(const float* heat, const float* wh, const float* reg
 }
 
 #ifdef CTDET_DECODE_TIMING
+extern "C" int ctdet_debug_dec_ts(unsigned long long* out /* [16] host */, int reset) {
+  if (reset) {
+    unsigned long long z[16];
+    for (int i = 0; i < 16; ++i) z[i] = (i == 0 || i == 2 || i == 4 || i == 6 || i == 8 || i == 9) ? ~0ull : 0ull;   // min slots
+    return cudaMemcpyToSymbol(ctdet::g_dec_ts, z, sizeof(z)) == cudaSuccess ? 0 : 1;
+  }
+  return cudaMemcpyFromSymbol(out, ctdet::g_dec_ts, sizeof(unsigned long long) * 16) == cudaSuccess ? 0 : 1;
+}
 extern "C" int ctdet_debug_tail_times(unsigned long long* out /* [64][8] host */) {
   return cudaMemcpyFromSymbol(out, ctdet::g_tail_ts, sizeof(unsigned long long) * 64 * 8) == cudaSuccess ? 0 : 1;
 }
