@@ -1143,7 +1143,10 @@ decode_tail_kernel(const float* __restrict__ heat, int B, int mode, int helpers,
   DEC_TS_MIN(9); DEC_TS_MAX(10);
   // The image's key segments (every tile's segment is fully written: keys, then zeros) are ONE dense vector: the first
   // batch of 16-byte loads is requested together with the header -- independent loads, one L2 trip.
-  constexpr int kBatch = 20;                                 // uint4 (2 keys) per thread and batch: 160 KB per CTA and trip
+#ifndef CTDET_TAIL_BATCH
+#define CTDET_TAIL_BATCH 20
+#endif
+  constexpr int kBatch = CTDET_TAIL_BATCH;                   // uint4 (2 keys) per thread and batch: 160 KB per CTA and trip at 20
   const int n_vec = (mode == 0 && helper == 0) ? sw_tiles * (tile_cap / 2) : 0;
   const uint4* segv = reinterpret_cast<const uint4*>(skeys + (mode == 0 ? (size_t)b * sw_tiles * tile_cap : 0));
   uint4 kq[kBatch];
