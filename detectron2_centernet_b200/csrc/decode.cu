@@ -1144,9 +1144,11 @@ decode_tail_kernel(const float* __restrict__ heat, int B, int mode, int helpers,
   // The image's key segments (every tile's segment is fully written: keys, then zeros) are ONE dense vector: the first
   // batch of 16-byte loads is requested together with the header -- independent loads, one L2 trip.
 #ifndef CTDET_TAIL_BATCH
-#define CTDET_TAIL_BATCH 20
+#define CTDET_TAIL_BATCH 5
 #endif
-  constexpr int kBatch = CTDET_TAIL_BATCH;                   // uint4 (2 keys) per thread and batch: 160 KB per CTA and trip at 20
+  constexpr int kBatch = CTDET_TAIL_BATCH;                   // uint4 (2 keys) per thread and batch (40 KB per CTA and trip); measured 20 / 10 / 5 / 4 / 2:
+  // B = 32 52.2 / 49.9 / 49.3 / 49.7 / 50.0 us -- the tail runs its code ONCE per CTA and waits for instruction fetch, so the
+  // shorter unrolled body wins over fewer trips
   const int n_vec = (mode == 0 && helper == 0) ? sw_tiles * (tile_cap / 2) : 0;
   const uint4* segv = reinterpret_cast<const uint4*>(skeys + (mode == 0 ? (size_t)b * sw_tiles * tile_cap : 0));
   uint4 kq[kBatch];
@@ -1366,7 +1368,12 @@ static DecodePlan make_plan(int B, int C, int H, int W, int K) {
   }
   {
     const int items = C * p.seed_groups * strips;               // one warp-item = 6 row segments of 512 B
-    p.seed_ctas = (items + kSeedWarps * CTDET_SEED_ITEMS_PER_WARP - 1) / (kSeedWarps * CTDET_SEED_ITEMS_PER_WARP);
+    // one item per warp while the seed grid is about one wave (4 CTAs of 16 K registers per SM; B = 32: 640 CTAs); two per
+    // warp beyond that -- the sweep's CTAs only find room as seed CTAs leave (B = 64: 79.8 -> 77.9 us; B = 32: 52.2 -> 53.3 us
+    // if applied there, the second item of a warp delays its image's bound)
+    int ipw = CTDET_SEED_ITEMS_PER_WARP;
+    if ((long long)B * ((items + kSeedWarps - 1) / kSeedWarps) >= 1024) ipw *= 2;
+    p.seed_ctas = (items + kSeedWarps * ipw - 1) / (kSeedWarps * ipw);
     p.seed_vals = items * kSeedRows;
     if (p.seed_ctas < 1) p.seed_ctas = 1;
   }
