@@ -61,9 +61,11 @@ DCN_LAYERS = [(512, 256, 16, 1), (256, 256, 32, 1), (256, 128, 32, 2), (128, 128
               (64, 64, 128, 5), (256, 64, 32, 1)]
 
 
-def dcn_stack(dev, B, reps=5):
+def dcn_stack(dev, B, reps=20):
     """BASELINE.json configs[4] (kernel part): forward and backward of the 16 DCNv2 layers of the
-    DLA-34 IDAUp/DLAUp neck, random offsets in (-2, 2), sigmoid masks; CUDA events, device-resident."""
+    DLA-34 IDAUp/DLAUp neck, random offsets in (-2, 2), sigmoid masks; CUDA events, device-resident.
+    20 back-to-back calls per timing: the GPU idles for the host time of the first call after the synchronise, which
+    with 5 calls added ~8 us to every call of the small layers."""
     import math
     from detectron2_centernet_b200 import deform_conv as DC
     g = torch.Generator(device=dev).manual_seed(0)
