@@ -772,7 +772,27 @@ decode_stream_kernel(const float* __restrict__ heat, int C, int H, int W, int ba
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     const unsigned bytes = (unsigned)((g_last - g_first + 1) * W * sizeof(float));
     mbar_expect_tx(&s_bar, bytes);
+    // The logits are read once: the tile copy carries an L2 evict-first policy, so the sweep does not push out what the
+    // neighbouring kernels of a step keep in L2 (measured in the bench step, scripts/step_overlap.py: one stream 160.9 ->
+    // 154.7 us, two-branch graph 145.7 -> 144.1 us; evict-last: no change).  -DCTDET_SWEEP_L2_HINT=0 = no hint, 1 = evict-last.
+#ifndef CTDET_SWEEP_L2_HINT
+#define CTDET_SWEEP_L2_HINT 2
+#endif
+#if CTDET_SWEEP_L2_HINT != 0
+    {
+      uint64_t pol;
+#if CTDET_SWEEP_L2_HINT == 1
+      asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+#else
+      asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+#endif
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                   :: "r"((uint32_t)__cvta_generic_to_shared(tile + (size_t)(g_first - (y_lo - 1)) * W)),
+                      "l"(plane + (size_t)g_first * W), "r"(bytes), "r"((uint32_t)__cvta_generic_to_shared(&s_bar)), "l"(pol) : "memory");
+    }
+#else
     bulk_g2s(tile + (size_t)(g_first - (y_lo - 1)) * W, plane + (size_t)g_first * W, bytes, &s_bar);
+#endif
   }
   if (y_lo == 0) for (int x = tid; x < W; x += kStrThreads) tile[x] = NEG;                      // max_pool2d padding (:401)
   if (y_hi == H) for (int x = tid; x < W; x += kStrThreads) tile[(size_t)(nrows + 1) * W + x] = NEG;
